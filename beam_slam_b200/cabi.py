@@ -1,0 +1,199 @@
+"""ctypes mirror of include/bsnls.h (the C-ABI boundary) and a numpy-backed holder for a flattened problem.
+
+Plumbing only: structs, enums and the loader for beam_slam_b200/lib/libbsnls.so. The loader raises when the
+CUDA library is missing; there is no CPU fallback anywhere in this package.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libbsnls.so")
+
+# ---- enums (include/bsnls.h) ----
+MANIFOLD_EUCLIDEAN, MANIFOLD_QUATERNION = 0, 1
+(FACTOR_REPROJECTION, FACTOR_IMU_DELTA, FACTOR_IMU_PRIOR, FACTOR_RELATIVE_POSE, FACTOR_RELATIVE_POSE_EXTRINSICS,
+ FACTOR_ABSOLUTE_POSE, FACTOR_RELATIVE_ORIENTATION, FACTOR_ABSOLUTE_VEC3, FACTOR_RELATIVE_VEC3) = range(9)
+NUM_FACTOR_TYPES = 9
+FACTOR_NBLOCKS = [3, 10, 5, 4, 6, 2, 2, 1, 2]
+FACTOR_NRES = [2, 15, 15, 6, 6, 6, 3, 3, 3]
+FACTOR_STRIDE = [2, 288, 241, 43, 43, 43, 13, 12, 12]
+FACTOR_BLOCK_SIZES = [[4, 3, 3], [4, 3, 3, 3, 3, 4, 3, 3, 3, 3], [4, 3, 3, 3, 3], [3, 4, 3, 4],
+                      [3, 4, 3, 4, 3, 4], [3, 4], [4, 4], [3], [3, 3]]
+LOSS_NONE, LOSS_CAUCHY, LOSS_HUBER = 0, 1, 2
+CAMERA_STRIDE = 20
+LINEAR_DENSE_SCHUR, LINEAR_ITERATIVE_SCHUR, LINEAR_AUTO = 0, 1, 2
+CONVERGENCE, NO_CONVERGENCE, FAILURE = 0, 1, 2
+OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_STATE = 0, -1, -2, -3, -4
+
+_pi32 = C.POINTER(C.c_int32)
+_pf64 = C.POINTER(C.c_double)
+_pu8 = C.POINTER(C.c_uint8)
+
+
+class FactorGroup(C.Structure):
+    _fields_ = [("type", C.c_int32), ("count", C.c_int32), ("blocks", _pi32), ("consts", _pf64),
+                ("aux", _pi32), ("loss_type", _pi32), ("loss_param", _pf64), ("res_index", _pi32)]
+
+
+class Problem(C.Structure):
+    _fields_ = [("num_blocks", C.c_int32), ("block_size", _pi32), ("block_manifold", _pi32),
+                ("block_constant", _pu8), ("block_group", _pi32), ("block_values", _pf64),
+                ("num_cameras", C.c_int32), ("cameras", _pf64), ("num_groups", C.c_int32),
+                ("groups", C.POINTER(FactorGroup))]
+
+
+class Options(C.Structure):
+    _fields_ = [("max_num_iterations", C.c_int32), ("max_solver_time_in_seconds", C.c_double),
+                ("function_tolerance", C.c_double), ("gradient_tolerance", C.c_double),
+                ("parameter_tolerance", C.c_double), ("initial_trust_region_radius", C.c_double),
+                ("max_trust_region_radius", C.c_double), ("min_trust_region_radius", C.c_double),
+                ("min_relative_decrease", C.c_double), ("min_lm_diagonal", C.c_double),
+                ("max_lm_diagonal", C.c_double), ("max_num_consecutive_invalid_steps", C.c_int32),
+                ("jacobi_scaling", C.c_int32), ("linear_solver", C.c_int32), ("pcg_max_iterations", C.c_int32),
+                ("pcg_tolerance", C.c_double), ("device", C.c_int32)]
+
+    @staticmethod
+    def defaults(**kw):
+        """ceres::Solver::Options defaults (the values fuse_core/src/ceres_options.cpp falls back to)."""
+        o = Options(50, 1e9, 1e-6, 1e-10, 1e-8, 1e4, 1e16, 1e-32, 1e-3, 1e-6, 1e32, 5, 1, LINEAR_AUTO, 500,
+                    1e-13, -1)
+        for k, v in kw.items():
+            if not hasattr(o, k):
+                raise AttributeError(k)
+            setattr(o, k, v)
+        return o
+
+
+class Iteration(C.Structure):
+    _fields_ = [("iteration", C.c_int32), ("step_is_valid", C.c_int32), ("step_is_successful", C.c_int32),
+                ("linear_solver_iterations", C.c_int32), ("cost", C.c_double), ("cost_change", C.c_double),
+                ("gradient_max_norm", C.c_double), ("gradient_norm", C.c_double), ("step_norm", C.c_double),
+                ("relative_decrease", C.c_double), ("trust_region_radius", C.c_double)]
+
+
+class Summary(C.Structure):
+    _fields_ = [("termination_type", C.c_int32), ("num_iterations", C.c_int32),
+                ("num_successful_steps", C.c_int32), ("num_unsuccessful_steps", C.c_int32),
+                ("initial_cost", C.c_double), ("final_cost", C.c_double), ("fixed_cost", C.c_double),
+                ("total_time_in_seconds", C.c_double), ("device_time_in_seconds", C.c_double),
+                ("num_parameter_blocks_reduced", C.c_int32), ("num_parameters_reduced", C.c_int32),
+                ("num_effective_parameters_reduced", C.c_int32), ("num_residual_blocks_reduced", C.c_int32),
+                ("num_residuals_reduced", C.c_int32), ("num_e_blocks", C.c_int32), ("num_f_blocks", C.c_int32),
+                ("reduced_system_dim", C.c_int32), ("linear_solver_used", C.c_int32),
+                ("reduced_system_nnz_blocks", C.c_int64), ("message", C.c_char * 160)]
+
+    def is_solution_usable(self):
+        """ceres::Solver::Summary::IsSolutionUsable (the only check at fixed_lag_smoother.cpp:286)."""
+        return self.termination_type in (CONVERGENCE, NO_CONVERGENCE)
+
+
+def _ptr(a, ty):
+    return a.ctypes.data_as(ty) if a is not None else ty()
+
+
+class FlatProblem:
+    """Owns the numpy arrays of one flattened graph and exposes them as a bsnls_problem.
+
+    groups: dict factor_type -> dict(blocks [n,nb] i32, consts [n,stride] f64, aux [n] i32 | None,
+                                     loss_type [n] i32 | None, loss_param [n] f64 | None, res_index [n] i32)
+    """
+
+    def __init__(self, block_size, block_manifold, block_constant, block_group, block_values, cameras, groups):
+        self.block_size = np.ascontiguousarray(block_size, np.int32)
+        self.block_manifold = np.ascontiguousarray(block_manifold, np.int32)
+        self.block_constant = np.ascontiguousarray(block_constant, np.uint8)
+        self.block_group = np.ascontiguousarray(block_group, np.int32)
+        self.block_values = np.ascontiguousarray(block_values, np.float64)
+        self.cameras = np.ascontiguousarray(cameras, np.float64).reshape(-1, CAMERA_STRIDE)
+        self.offsets = np.concatenate([[0], np.cumsum(self.block_size)]).astype(np.int64)
+        assert self.block_values.size == self.offsets[-1]
+        self.groups = {}
+        for t, g in sorted(groups.items()):
+            n = len(g["res_index"])
+            d = dict(blocks=np.ascontiguousarray(g["blocks"], np.int32).reshape(n, FACTOR_NBLOCKS[t]),
+                     consts=np.ascontiguousarray(g["consts"], np.float64).reshape(n, FACTOR_STRIDE[t]),
+                     aux=None if g.get("aux") is None else np.ascontiguousarray(g["aux"], np.int32),
+                     loss_type=None if g.get("loss_type") is None else np.ascontiguousarray(g["loss_type"], np.int32),
+                     loss_param=None if g.get("loss_param") is None else np.ascontiguousarray(g["loss_param"], np.float64),
+                     res_index=np.ascontiguousarray(g["res_index"], np.int32))
+            self.groups[t] = d
+        self._build()
+
+    def _build(self):
+        self._garr = (FactorGroup * max(1, len(self.groups)))()
+        for i, (t, g) in enumerate(self.groups.items()):
+            self._garr[i] = FactorGroup(t, len(g["res_index"]), _ptr(g["blocks"], _pi32), _ptr(g["consts"], _pf64),
+                                        _ptr(g["aux"], _pi32), _ptr(g["loss_type"], _pi32),
+                                        _ptr(g["loss_param"], _pf64), _ptr(g["res_index"], _pi32))
+        self.c = Problem(len(self.block_size), _ptr(self.block_size, _pi32), _ptr(self.block_manifold, _pi32),
+                         _ptr(self.block_constant, _pu8), _ptr(self.block_group, _pi32),
+                         _ptr(self.block_values, _pf64), len(self.cameras), _ptr(self.cameras, _pf64),
+                         len(self.groups), self._garr)
+
+    @property
+    def num_values(self):
+        return int(self.offsets[-1])
+
+    @property
+    def num_residual_blocks(self):
+        return sum(len(g["res_index"]) for g in self.groups.values())
+
+    def count(self, t):
+        return len(self.groups[t]["res_index"]) if t in self.groups else 0
+
+    def value(self, block):
+        return self.block_values[self.offsets[block]:self.offsets[block + 1]]
+
+    def with_values(self, values):
+        p = FlatProblem.__new__(FlatProblem)
+        p.__dict__.update(self.__dict__)
+        p.block_values = np.ascontiguousarray(values, np.float64).copy()
+        p._build()
+        return p
+
+
+_lib = None
+
+
+def load_library():
+    """Load the CUDA library. Raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; "
+                           "g.build()'` (nvcc, sm_100a). beam_slam_b200 has no CPU path.")
+    lib = C.CDLL(LIB_PATH)
+    H = C.c_void_p
+    lib.bsnls_default_options.argtypes = [C.POINTER(Options)]
+    lib.bsnls_default_options.restype = None
+    lib.bsnls_create.argtypes = [C.POINTER(Options), C.POINTER(H)]
+    lib.bsnls_destroy.argtypes = [H]
+    lib.bsnls_destroy.restype = None
+    lib.bsnls_last_error.argtypes = [H]
+    lib.bsnls_last_error.restype = C.c_char_p
+    lib.bsnls_set_problem.argtypes = [H, C.POINTER(Problem)]
+    lib.bsnls_set_values.argtypes = [H, _pf64]
+    lib.bsnls_set_options.argtypes = [H, C.POINTER(Options)]
+    lib.bsnls_solve.argtypes = [H, C.POINTER(Summary), C.POINTER(Iteration), C.c_int32]
+    lib.bsnls_get_values.argtypes = [H, _pf64]
+    lib.bsnls_evaluate.argtypes = [H, _pf64, _pf64, C.POINTER(C.c_int64), _pf64, C.POINTER(C.c_int64)]
+    lib.bsnls_get_ordering.argtypes = [H, _pi32, _pi32, _pi32, _pi32]
+    lib.bsnls_get_reduced_pattern.argtypes = [H, _pi32, _pi32, C.POINTER(C.c_int64)]
+    lib.bsnls_get_reduced_system.argtypes = [H, C.c_double, _pf64, _pf64, C.c_int32]
+    lib.bsnls_run_eval.argtypes = [H, _pf64]
+    lib.bsnls_run_schur.argtypes = [H, C.c_double]
+    lib.bsnls_last_kernel_ms.argtypes = [H, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    lib.bsnls_launch_count.argtypes = [H]
+    lib.bsnls_launch_count.restype = C.c_int64
+    lib.bsnls_nccl_unique_id.argtypes = [C.c_char * 128]
+    lib.bsnls_create_sharded.argtypes = [C.POINTER(Options), C.c_int32, C.c_int32, C.c_char * 128, C.POINTER(H)]
+    for name in ("bsnls_create", "bsnls_set_problem", "bsnls_set_values", "bsnls_set_options", "bsnls_solve",
+                 "bsnls_get_values", "bsnls_evaluate", "bsnls_get_ordering", "bsnls_get_reduced_pattern",
+                 "bsnls_get_reduced_system", "bsnls_run_eval", "bsnls_run_schur", "bsnls_last_kernel_ms",
+                 "bsnls_nccl_unique_id", "bsnls_create_sharded"):
+        getattr(lib, name).restype = C.c_int
+    _lib = lib
+    return lib
