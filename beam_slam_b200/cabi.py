@@ -186,6 +186,8 @@ def load_library():
     lib.bsnls_run_eval.argtypes = [H, _pf64]
     lib.bsnls_run_schur.argtypes = [H, C.c_double]
     lib.bsnls_last_kernel_ms.argtypes = [H, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    lib.bsnls_last_breakdown_ms.argtypes = [H, C.POINTER(C.c_float)]
+    lib.bsnls_last_breakdown_ms.restype = C.c_int
     lib.bsnls_launch_count.argtypes = [H]
     lib.bsnls_launch_count.restype = C.c_int64
     lib.bsnls_nccl_unique_id.argtypes = [C.c_char * 128]

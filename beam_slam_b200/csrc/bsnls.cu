@@ -1,0 +1,838 @@
+// C-ABI implementation (include/bsnls.h): host-side structure analysis of the flattened graph, device buffers,
+// and the enqueue sequence of the LM loop. The arithmetic lives in kernels.cuh; nothing here computes on the CPU.
+#include <algorithm>
+#include <chrono>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "kernels.cuh"
+
+using namespace bsnls;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+const int kNumBlocks[BSNLS_NUM_FACTOR_TYPES] = {3, 10, 5, 4, 6, 2, 2, 1, 2};
+const int kNumRes[BSNLS_NUM_FACTOR_TYPES] = {2, 15, 15, 6, 6, 6, 3, 3, 3};
+const int kStride[BSNLS_NUM_FACTOR_TYPES] = {BSNLS_REPROJECTION_STRIDE, BSNLS_IMU_DELTA_STRIDE, BSNLS_IMU_PRIOR_STRIDE,
+                                             BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE,
+                                             BSNLS_ORIENTATION_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_VEC3_STRIDE};
+
+struct DevMem {
+  void* p = nullptr; size_t bytes = 0;
+  ~DevMem() { if (p) cudaFree(p); }
+  cudaError_t alloc(size_t n) {
+    if (p && n <= bytes) return cudaSuccess;
+    if (p) { cudaFree(p); p = nullptr; bytes = 0; }
+    if (n == 0) n = 8;
+    cudaError_t e = cudaMalloc(&p, n);
+    if (e == cudaSuccess) bytes = n;
+    return e;
+  }
+  template <typename T> T* as() const { return static_cast<T*>(p); }
+};
+
+}  // namespace
+
+struct bsnls_handle {
+  bsnls_options opt{};
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+  cudaEvent_t pev[10] = {};   // per-kernel marks for bsnls_last_breakdown_ms
+  bool profiling = false; float breakdown[8] = {};
+  std::string error;
+  int64_t launches = 0;
+  bool has_problem = false, jac_valid = false;
+  float last_eval_ms = 0, last_schur_ms = 0;
+  int rank = 0, world = 1;
+
+  // host-side structure
+  int num_blocks = 0; int64_t num_values = 0;
+  std::vector<int> blk_off, blk_size, blk_tan, blk_manifold, active_blocks, eblocks, fblocks;
+  int ne = 0, nf = 0, np = 0, nobs = 0, ngf = 0, ngf_active = 0, npairs = 0, ngdest = 0, G = 8;
+  int64_t nitems = 0;
+  std::vector<int> pose_q_blk, pose_t_blk;
+  std::vector<int> pair_a, pair_b;
+  std::vector<int> gd_row, gd_col;
+  // residual-block bookkeeping for bsnls_evaluate (program order)
+  struct ResRef { int type; int idx; int row; };   // idx: sorted-observation id or generic-factor id
+  std::vector<ResRef> res_order; int64_t num_res_rows = 0;
+  int64_t gfJ_size = 0, gfR_size = 0;
+  std::vector<int> gf_roff_h, gf_nres_h;
+  int nb_obs = 0, nb_lm = 0, nb_act = 0;  // partial-sum block counts
+
+  DeviceProblem P{};
+  // device memory
+  DevMem d_blk_off, d_blk_size, d_blk_tan, d_blk_manifold, d_active, d_pose_q_off, d_pose_t_off, d_pose_q_tan,
+      d_pose_t_tan, d_pose_ptr, d_pose_obs, d_obs_pose, d_obs_lm, d_obs_cam, d_obs_pixel, d_lm_ptr, d_lm_off, d_cams,
+      d_gf_type, d_gf_nblk, d_gf_nres, d_gf_blocks, d_gf_coff, d_gf_consts, d_gf_loss_type, d_gf_loss_a, d_gf_joff,
+      d_gf_roff, d_pair_a, d_pair_b, d_pair_ptr, d_item_i, d_item_j, d_fg_ptr, d_fg_fac, d_fg_lb, d_gd_row, d_gd_col,
+      d_gd_ptr, d_gd_fac, d_gd_bi, d_gd_bj, d_is_pose;
+  DevMem d_x, d_xc, d_x0, d_Jrec, d_Vrec, d_minv, d_grad, d_colsq, d_scale, d_y, d_yf, d_rhs, d_S, d_poseH, d_gfJ,
+      d_gfR, d_cost_part, d_cand_part, d_model_part, d_step_part, d_candsq_part, d_gsq_part, d_gmax_part, d_xsq_part,
+      d_red, d_state, d_recs;
+  int max_records = 0;
+
+  int fail(int code, const char* fmt, ...) {
+    char buf[512]; va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+    error = buf; return code;
+  }
+};
+
+#define CK(expr)                                                                                      \
+  do { cudaError_t _e = (expr);                                                                      \
+    if (_e != cudaSuccess) return h->fail(BSNLS_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(_e)); } while (0)
+#define MARK(h, i) do { if ((h)->profiling) cudaEventRecord((h)->pev[i], (h)->stream); } while (0)
+#define LAUNCH(h, kernel, grid, block, ...)                                                            \
+  do { kernel<<<(grid), (block), 0, (h)->stream>>>(__VA_ARGS__); (h)->launches++; } while (0)
+
+namespace {
+
+template <typename T> cudaError_t upload(DevMem& m, const std::vector<T>& v, cudaStream_t s) {
+  cudaError_t e = m.alloc(v.size() * sizeof(T));
+  if (e != cudaSuccess || v.empty()) return e;
+  return cudaMemcpyAsync(m.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s);
+}
+
+Options MakeOptions(const bsnls_options& o) {
+  Options r;
+  r.min_lm_diagonal = o.min_lm_diagonal; r.max_lm_diagonal = o.max_lm_diagonal;
+  r.function_tolerance = o.function_tolerance; r.gradient_tolerance = o.gradient_tolerance;
+  r.parameter_tolerance = o.parameter_tolerance; r.max_radius = o.max_trust_region_radius;
+  r.min_radius = o.min_trust_region_radius; r.min_relative_decrease = o.min_relative_decrease;
+  r.max_num_iterations = o.max_num_iterations; r.max_invalid = o.max_num_consecutive_invalid_steps;
+  r.jacobi_scaling = o.jacobi_scaling;
+  return r;
+}
+
+bool ValidOptions(const bsnls_options& o, std::string* why) {
+  auto bad = [&](const char* m) { *why = m; return false; };
+  if (o.max_num_iterations < 0) return bad("max_num_iterations >= 0 violated");
+  if (o.max_solver_time_in_seconds < 0) return bad("max_solver_time_in_seconds >= 0 violated");
+  if (o.function_tolerance < 0 || o.gradient_tolerance < 0 || o.parameter_tolerance < 0) return bad("tolerances >= 0 violated");
+  if (!(o.initial_trust_region_radius > 0) || !(o.min_trust_region_radius > 0) || !(o.max_trust_region_radius > 0)) return bad("trust region radii > 0 violated");
+  if (o.min_trust_region_radius > o.max_trust_region_radius || o.initial_trust_region_radius > o.max_trust_region_radius ||
+      o.min_trust_region_radius > o.initial_trust_region_radius) return bad("trust region radius ordering violated");
+  if (o.min_relative_decrease < 0) return bad("min_relative_decrease >= 0 violated");
+  if (o.min_lm_diagonal < 0 || o.min_lm_diagonal > o.max_lm_diagonal) return bad("lm_diagonal bounds violated");
+  if (o.max_num_consecutive_invalid_steps < 0) return bad("max_num_consecutive_invalid_steps >= 0 violated");
+  if (o.linear_solver < 0 || o.linear_solver > BSNLS_LINEAR_AUTO) return bad("unknown linear_solver");
+  return true;
+}
+
+const char* MessageText(int id) {
+  switch (id) {
+    case MSG_MAX_ITER: return "Maximum number of iterations reached.";
+    case MSG_GRAD_TOL: return "Gradient tolerance reached.";
+    case MSG_MIN_RADIUS: return "Minimum trust region radius reached.";
+    case MSG_PARAM_TOL: return "Parameter tolerance reached.";
+    case MSG_FUNC_TOL: return "Function tolerance reached.";
+    case MSG_INVALID_STEPS: return "Number of consecutive invalid steps more than Solver::Options::max_num_consecutive_invalid_steps.";
+    case MSG_MAX_TIME: return "Maximum solver time reached.";
+    case MSG_NONFINITE: return "Residual and Jacobian evaluation failed (non-finite cost).";
+    default: return "";
+  }
+}
+
+int BlocksFor(int n, int per) { return std::max(1, (n + per - 1) / per); }
+
+// ---- enqueue helpers (all asynchronous on h->stream) ----
+void EnqueueEval(bsnls_handle* h) {  // phase A: residuals + Jacobians + cost at x
+  const DeviceProblem& P = h->P;
+  LMState* st = h->d_state.as<LMState>();
+  MARK(h, 0);
+  if (h->nobs) LAUNCH(h, eval_reproj_kernel<0>, h->nb_obs, 256, P, h->d_x.as<double>(), h->d_Jrec.as<double>(), h->d_cost_part.as<double>(), st);
+  MARK(h, 1);
+  if (h->ngf) LAUNCH(h, eval_generic_kernel<0>, BlocksFor(h->ngf, 4), 128, P, h->d_x.as<double>(), h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_cost_part.as<double>() + h->nb_obs, st);
+  MARK(h, 2);
+}
+template <int G> void LaunchLandmark(bsnls_handle* h, const Options& o) {
+  LAUNCH(h, landmark_kernel<G>, BlocksFor(h->ne * G, 256), 256, h->P, h->d_Jrec.as<double>(), h->d_Vrec.as<double>(), h->d_minv.as<double>(),
+         h->d_grad.as<double>(), h->d_colsq.as<double>(), h->d_scale.as<double>(), o, h->d_state.as<LMState>());
+}
+void EnqueueLandmark(bsnls_handle* h, const Options& o) {  // phase B
+  if (!h->ne) return;
+  switch (h->G) { case 4: LaunchLandmark<4>(h, o); break; case 8: LaunchLandmark<8>(h, o); break;
+                  case 16: LaunchLandmark<16>(h, o); break; default: LaunchLandmark<32>(h, o); }
+}
+__global__ void zero_f_kernel(DeviceProblem P, double* grad, double* colsq, const LMState* st) {
+  if (!gate_jac(st)) return;
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j < P.nf_dim) { grad[P.ne_dim + j] = 0.0; colsq[P.ne_dim + j] = 0.0; }
+}
+void EnqueueGradient(bsnls_handle* h, const Options& o) {  // phase C: gradient, column norms, scale, gradient norms
+  const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
+  LAUNCH(h, zero_f_kernel, BlocksFor(P.nf_dim, 256), 256, P, h->d_grad.as<double>(), h->d_colsq.as<double>(), st);
+  if (h->np) LAUNCH(h, pose_diag_kernel, BlocksFor(h->np, 4), 128, P, h->d_Jrec.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_colsq.as<double>(), st);
+  if (h->ngf) LAUNCH(h, gf_grad_kernel, BlocksFor(3 * h->nf, 128), 128, P, h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_grad.as<double>(), h->d_colsq.as<double>(), st);
+  LAUNCH(h, fscale_kernel, BlocksFor(P.nf_dim, 256), 256, P, h->d_colsq.as<double>(), h->d_scale.as<double>(), o, st);
+  LAUNCH(h, grad_norm_kernel, h->nb_act, 256, P, h->d_x.as<double>(), h->d_grad.as<double>(), h->d_gsq_part.as<double>(), h->d_gmax_part.as<double>(), st);
+  RedList L{}; L.gate = 2; L.count = 0;
+  if (h->nobs) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>(), h->nb_obs, 0, RED_COST};
+  if (h->ngf_active) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>() + h->nb_obs, h->ngf_active, 0, RED_COST};
+  if (h->ngf > h->ngf_active) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>() + h->nb_obs + h->ngf_active, h->ngf - h->ngf_active, 0, RED_FIXED};
+  L.d[L.count++] = RedDesc{h->d_gsq_part.as<double>(), h->nb_act, 0, RED_GRAD_SQ};
+  L.d[L.count++] = RedDesc{h->d_gmax_part.as<double>(), h->nb_act, 1, RED_GRAD_MAX};
+  LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), st);
+}
+void EnqueueAssemble(bsnls_handle* h, const Options& o) {  // phase D1: reduced system S, rhs
+  const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
+  MARK(h, 5);
+  cudaMemsetAsync(h->d_S.p, 0, sizeof(double) * (size_t)P.nf_dim * P.nf_dim, h->stream);
+  MARK(h, 6);
+  if (h->npairs) LAUNCH(h, pair_kernel, BlocksFor(h->npairs, 4), 128, P, h->d_Vrec.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
+  MARK(h, 7);
+  if (h->ngdest) LAUNCH(h, gf_schur_kernel, BlocksFor(h->ngdest, 16), 144, P, h->d_gfJ.as<double>(), h->d_S.as<double>(), st);
+  LAUNCH(h, finish_system_kernel, BlocksFor(P.nf_dim, 256), 256, P, h->d_grad.as<double>(), h->d_colsq.as<double>(), h->d_scale.as<double>(),
+         h->d_is_pose.as<unsigned char>(), h->d_S.as<double>(), h->d_rhs.as<double>(), o, st);
+  MARK(h, 8);
+}
+void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular solves
+  const int n = h->P.nf_dim; LMState* st = h->d_state.as<LMState>();
+  for (int j0 = 0; j0 < n; j0 += kNB) {
+    const int nb = std::min(kNB, n - j0), rest = n - j0 - nb;
+    LAUNCH(h, chol_panel_kernel, BlocksFor(rest, 64), 64, h->d_S.as<double>(), n, j0, st);
+    if (rest > 0) { const int T = (rest + 63) / 64; LAUNCH(h, chol_update_kernel, dim3(T, T), 128, h->d_S.as<double>(), n, j0, st); }
+  }
+  LAUNCH(h, chol_solve_kernel, 1, 1024, h->d_S.as<double>(), n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
+}
+template <int G> void LaunchBacksub(bsnls_handle* h) {
+  LAUNCH(h, backsub_kernel<G>, h->nb_lm, 256, h->P, h->d_Jrec.as<double>(), h->d_minv.as<double>(), h->d_grad.as<double>(), h->d_yf.as<double>(),
+         h->d_y.as<double>(), h->d_model_part.as<double>(), h->d_state.as<LMState>());
+}
+void EnqueueStep(bsnls_handle* h) {  // phase D3: back-substitution, model cost, candidate, candidate cost
+  const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
+  if (h->ne) switch (h->G) { case 4: LaunchBacksub<4>(h); break; case 8: LaunchBacksub<8>(h); break;
+                             case 16: LaunchBacksub<16>(h); break; default: LaunchBacksub<32>(h); }
+  LAUNCH(h, gf_model_kernel, BlocksFor(std::max(h->ngf, std::min(P.nf_dim, 1 << 16)), 128), 128, P, h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_yf.as<double>(), h->d_y.as<double>(),
+         h->d_model_part.as<double>() + h->nb_lm, st);
+  LAUNCH(h, candidate_kernel, h->nb_act, 256, P, h->d_x.as<double>(), h->d_y.as<double>(), h->d_xc.as<double>(), h->d_step_part.as<double>(), h->d_candsq_part.as<double>(), st);
+  if (h->nobs) LAUNCH(h, eval_reproj_kernel<1>, h->nb_obs, 256, P, h->d_xc.as<double>(), nullptr, h->d_cand_part.as<double>(), st);
+  if (h->ngf) LAUNCH(h, eval_generic_kernel<1>, BlocksFor(h->ngf, 4), 128, P, h->d_xc.as<double>(), nullptr, nullptr, h->d_cand_part.as<double>() + h->nb_obs, st);
+  RedList L{}; L.gate = 1; L.count = 0;
+  if (h->nobs) L.d[L.count++] = RedDesc{h->d_cand_part.as<double>(), h->nb_obs, 0, RED_CAND_COST};
+  if (h->ngf_active) L.d[L.count++] = RedDesc{h->d_cand_part.as<double>() + h->nb_obs, h->ngf_active, 0, RED_CAND_COST};
+  if (h->ne) L.d[L.count++] = RedDesc{h->d_model_part.as<double>(), h->nb_lm, 0, RED_MODEL};
+  if (h->ngf_active) L.d[L.count++] = RedDesc{h->d_model_part.as<double>() + h->nb_lm, h->ngf_active, 0, RED_MODEL};
+  L.d[L.count++] = RedDesc{h->d_step_part.as<double>(), h->nb_act, 0, RED_STEP_SQ};
+  L.d[L.count++] = RedDesc{h->d_candsq_part.as<double>(), h->nb_act, 0, RED_CAND_SQ};
+  LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), st);
+}
+
+int InitState(bsnls_handle* h, bool keep_scale) {
+  LMState s{};
+  s.radius = h->opt.initial_trust_region_radius; s.decrease_factor = 2.0;
+  s.need_jacobian = 1; s.scale_ready = keep_scale ? 1 : 0; s.max_records = h->max_records;
+  cudaError_t e = cudaMemcpyAsync(h->d_state.p, &s, sizeof(s), cudaMemcpyHostToDevice, h->stream);
+  if (e != cudaSuccess) return h->fail(BSNLS_ERR_CUDA, "state upload: %s", cudaGetErrorString(e));
+  e = cudaMemsetAsync(h->d_red.p, 0, sizeof(double) * 16, h->stream);
+  if (e != cudaSuccess) return h->fail(BSNLS_ERR_CUDA, "red memset: %s", cudaGetErrorString(e));
+  return BSNLS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void bsnls_default_options(bsnls_options* o) {
+  o->max_num_iterations = 50; o->max_solver_time_in_seconds = 1e9; o->function_tolerance = 1e-6;
+  o->gradient_tolerance = 1e-10; o->parameter_tolerance = 1e-8; o->initial_trust_region_radius = 1e4;
+  o->max_trust_region_radius = 1e16; o->min_trust_region_radius = 1e-32; o->min_relative_decrease = 1e-3;
+  o->min_lm_diagonal = 1e-6; o->max_lm_diagonal = 1e32; o->max_num_consecutive_invalid_steps = 5;
+  o->jacobi_scaling = 1; o->linear_solver = BSNLS_LINEAR_AUTO; o->pcg_max_iterations = 500; o->pcg_tolerance = 1e-13;
+  o->device = -1;
+}
+
+const char* bsnls_last_error(const bsnls_handle* h) { return h ? h->error.c_str() : g_create_error.c_str(); }
+int64_t bsnls_launch_count(const bsnls_handle* h) { return h ? h->launches : 0; }
+
+int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
+  if (!out) return BSNLS_ERR_INVALID;
+  *out = nullptr;
+  bsnls_options o; if (options) o = *options; else bsnls_default_options(&o);
+  std::string why;
+  if (!ValidOptions(o, &why)) { g_create_error = "invalid options: " + why; return BSNLS_ERR_INVALID; }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) + " (this library has no CPU path)";
+    return BSNLS_ERR_CUDA;
+  }
+  int dev = o.device;
+  if (dev < 0) { if (cudaGetDevice(&dev) != cudaSuccess) dev = 0; }
+  if (dev >= ndev) { g_create_error = "device ordinal out of range"; return BSNLS_ERR_INVALID; }
+  if ((e = cudaSetDevice(dev)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); return BSNLS_ERR_CUDA; }
+  auto* h = new bsnls_handle();
+  h->opt = o; h->device = dev;
+  if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+      (e = cudaEventCreate(&h->ev0)) != cudaSuccess || (e = cudaEventCreate(&h->ev1)) != cudaSuccess ||
+      (e = cudaEventCreate(&h->ev2)) != cudaSuccess) {
+    g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
+  }
+  for (auto& ev : h->pev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
+  *out = h;
+  return BSNLS_OK;
+}
+
+void bsnls_destroy(bsnls_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->ev2) cudaEventDestroy(h->ev2);
+  for (auto& ev : h->pev) if (ev) cudaEventDestroy(ev);
+  delete h;
+}
+
+int bsnls_set_options(bsnls_handle* h, const bsnls_options* o) {
+  if (!h || !o) return BSNLS_ERR_INVALID;
+  std::string why;
+  if (!ValidOptions(*o, &why)) return h->fail(BSNLS_ERR_INVALID, "invalid options: %s", why.c_str());
+  const int dev = h->opt.device; h->opt = *o; h->opt.device = dev;
+  return BSNLS_OK;
+}
+
+int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
+  if (!h || !pr) return BSNLS_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  h->has_problem = false; h->jac_valid = false;
+  const int nb = pr->num_blocks;
+  if (nb <= 0) return h->fail(BSNLS_ERR_INVALID, "problem has no parameter blocks");
+  // ---- blocks ----
+  h->num_blocks = nb; h->blk_off.resize(nb); h->blk_size.assign(pr->block_size, pr->block_size + nb);
+  h->blk_manifold.assign(pr->block_manifold, pr->block_manifold + nb);
+  int64_t off = 0;
+  for (int b = 0; b < nb; ++b) {
+    h->blk_off[b] = (int)off; off += pr->block_size[b];
+    const int sz = pr->block_size[b], mf = pr->block_manifold[b];
+    if (!((mf == BSNLS_MANIFOLD_EUCLIDEAN && sz == 3) || (mf == BSNLS_MANIFOLD_QUATERNION && sz == 4)))
+      if (!pr->block_constant[b])
+        return h->fail(BSNLS_ERR_UNSUPPORTED, "block %d: only 3-vectors and quaternions are supported (size %d, manifold %d)", b, sz, mf);
+  }
+  if (off > 0x7fffffffLL) return h->fail(BSNLS_ERR_UNSUPPORTED, "too many parameters");
+  h->num_values = off;
+  // ---- residual blocks in program order ----
+  int64_t total = 0;
+  for (int g = 0; g < pr->num_groups; ++g) {
+    if (pr->groups[g].type < 0 || pr->groups[g].type >= BSNLS_NUM_FACTOR_TYPES) return h->fail(BSNLS_ERR_UNSUPPORTED, "unknown factor type %d", pr->groups[g].type);
+    total += pr->groups[g].count;
+  }
+  // active blocks (ceres reduced program: constant blocks and unreferenced blocks drop out)
+  std::vector<char> active(nb, 0);
+  const bsnls_factor_group* rg = nullptr;
+  std::vector<const bsnls_factor_group*> gfg;
+  for (int g = 0; g < pr->num_groups; ++g) {
+    const bsnls_factor_group& G = pr->groups[g];
+    if (G.type == BSNLS_FACTOR_REPROJECTION) { if (rg) return h->fail(BSNLS_ERR_INVALID, "two reprojection groups"); rg = &G; }
+    else gfg.push_back(&G);
+    const int nbk = kNumBlocks[G.type];
+    for (int64_t i = 0; i < G.count; ++i) {
+      bool any = false;
+      for (int b = 0; b < nbk; ++b) {
+        const int blk = G.blocks[i * nbk + b];
+        if (blk < 0 || blk >= nb) return h->fail(BSNLS_ERR_INVALID, "block index out of range");
+        any = any || !pr->block_constant[blk];
+      }
+      if (any) for (int b = 0; b < nbk; ++b) { const int blk = G.blocks[i * nbk + b]; if (!pr->block_constant[blk]) active[blk] = 1; }
+    }
+  }
+  std::sort(gfg.begin(), gfg.end(), [](const bsnls_factor_group* a, const bsnls_factor_group* b) { return a->type < b->type; });
+  h->eblocks.clear(); h->fblocks.clear(); h->active_blocks.clear();
+  std::vector<int> epos(nb, -1), fpos(nb, -1);
+  for (int b = 0; b < nb; ++b) {
+    if (!active[b]) continue;
+    h->active_blocks.push_back(b);
+    if (pr->block_group[b] == 0) { epos[b] = (int)h->eblocks.size(); h->eblocks.push_back(b); }
+    else { fpos[b] = (int)h->fblocks.size(); h->fblocks.push_back(b); }
+  }
+  h->ne = (int)h->eblocks.size(); h->nf = (int)h->fblocks.size();
+  const int ne_dim = 3 * h->ne, nf_dim = 3 * h->nf;
+  h->blk_tan.assign(nb, -1);
+  for (int b = 0; b < nb; ++b) { if (epos[b] >= 0) h->blk_tan[b] = 3 * epos[b]; else if (fpos[b] >= 0) h->blk_tan[b] = ne_dim + 3 * fpos[b]; }
+  if (nf_dim == 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "no non-landmark parameter blocks to solve for");
+  const bool dense = true;  // round 1: dense reduced system
+  if (dense && nf_dim > 24000) return h->fail(BSNLS_ERR_UNSUPPORTED, "reduced system of dimension %d exceeds the dense solver limit", nf_dim);
+
+  // ---- reprojection: poses, landmark-sorted observations ----
+  std::vector<int> pose_of_q(nb, -1), pose_of_t(nb, -1);
+  h->pose_q_blk.clear(); h->pose_t_blk.clear();
+  const int nobs = rg ? rg->count : 0;
+  std::vector<int> obs_pose(nobs), obs_lm(nobs), order(nobs);
+  std::vector<int> lm_count(h->ne + 1, 0);
+  for (int i = 0; i < nobs; ++i) {
+    const int q = rg->blocks[3 * (int64_t)i], t = rg->blocks[3 * (int64_t)i + 1], p = rg->blocks[3 * (int64_t)i + 2];
+    if (epos[p] < 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "reprojection factor %d: landmark block must be non-constant and in elimination group 0", i);
+    if (epos[q] >= 0 || epos[t] >= 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "reprojection factor %d: pose blocks must not be in elimination group 0", i);
+    if (pr->block_size[q] != 4 || pr->block_size[t] != 3 || pr->block_size[p] != 3) return h->fail(BSNLS_ERR_INVALID, "reprojection factor %d: block sizes must be 4,3,3", i);
+    int pose = pose_of_q[q];
+    if (pose < 0 && pose_of_t[t] < 0) { pose = (int)h->pose_q_blk.size(); h->pose_q_blk.push_back(q); h->pose_t_blk.push_back(t); pose_of_q[q] = pose; pose_of_t[t] = pose; }
+    else if (pose < 0 || pose_of_t[t] != pose) return h->fail(BSNLS_ERR_UNSUPPORTED, "orientation/position blocks are paired inconsistently across reprojection factors");
+    if (rg->aux[i] < 0 || rg->aux[i] >= pr->num_cameras) return h->fail(BSNLS_ERR_INVALID, "camera index out of range");
+    obs_pose[i] = pose; obs_lm[i] = epos[p]; lm_count[epos[p] + 1]++;
+  }
+  h->np = (int)h->pose_q_blk.size(); h->nobs = nobs;
+  for (int e = 0; e < h->ne; ++e) { if (lm_count[e + 1] == 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "group-0 block without reprojection factors"); lm_count[e + 1] += lm_count[e]; }
+  std::vector<int> lm_ptr = lm_count;
+  { std::vector<int> cur(lm_ptr.begin(), lm_ptr.end() - 1); for (int i = 0; i < nobs; ++i) order[cur[obs_lm[i]]++] = i; }  // stable
+  std::vector<int> s_pose(nobs), s_lm(nobs), s_cam(nobs), inv_order(nobs); std::vector<double> s_pixel(2 * (size_t)nobs);
+  for (int k = 0; k < nobs; ++k) {
+    const int i = order[k]; inv_order[i] = k;
+    s_pose[k] = obs_pose[i]; s_lm[k] = obs_lm[i]; s_cam[k] = rg->aux[i];
+    s_pixel[2 * (size_t)k] = rg->consts[2 * (size_t)i]; s_pixel[2 * (size_t)k + 1] = rg->consts[2 * (size_t)i + 1];
+  }
+  std::vector<int> lm_off(h->ne);
+  for (int e = 0; e < h->ne; ++e) lm_off[e] = h->blk_off[h->eblocks[e]];
+  std::vector<int> pose_q_off(h->np), pose_t_off(h->np), pose_q_tan(h->np), pose_t_tan(h->np), pose_ptr(h->np + 1, 0), pose_obs(nobs);
+  for (int a = 0; a < h->np; ++a) {
+    pose_q_off[a] = h->blk_off[h->pose_q_blk[a]]; pose_t_off[a] = h->blk_off[h->pose_t_blk[a]];
+    pose_q_tan[a] = h->blk_tan[h->pose_q_blk[a]]; pose_t_tan[a] = h->blk_tan[h->pose_t_blk[a]];
+  }
+  for (int k = 0; k < nobs; ++k) pose_ptr[s_pose[k] + 1]++;
+  for (int a = 0; a < h->np; ++a) pose_ptr[a + 1] += pose_ptr[a];
+  { std::vector<int> cur(pose_ptr.begin(), pose_ptr.end() - 1); for (int k = 0; k < nobs; ++k) pose_obs[cur[s_pose[k]]++] = k; }
+  const double avg_track = h->ne ? (double)nobs / h->ne : 0.0;
+  h->G = avg_track <= 5.0 ? 4 : avg_track <= 12.0 ? 8 : avg_track <= 24.0 ? 16 : 32;
+
+  // ---- pose-pair blocks and items ----
+  std::vector<int> pair_ptr, item_i, item_j;
+  h->pair_a.clear(); h->pair_b.clear();
+  {
+    std::unordered_map<uint64_t, int> key_count; key_count.reserve((size_t)h->np * 16);
+    auto key_of = [&](int a, int b) { return (uint64_t)a * (uint64_t)h->np + (uint64_t)b; };
+    for (int e = 0; e < h->ne; ++e)
+      for (int i = lm_ptr[e]; i < lm_ptr[e + 1]; ++i)
+        for (int j = i; j < lm_ptr[e + 1]; ++j) {
+          const int a = s_pose[i], b = s_pose[j];
+          key_count[key_of(std::min(a, b), std::max(a, b))] += (a == b && i != j) ? 2 : 1;
+        }
+    std::vector<uint64_t> keys; keys.reserve(key_count.size());
+    for (auto& kv : key_count) keys.push_back(kv.first);
+    std::sort(keys.begin(), keys.end());
+    const int npairs = (int)keys.size();
+    std::unordered_map<uint64_t, int> key_id; key_id.reserve(keys.size() * 2);
+    pair_ptr.assign(npairs + 1, 0);
+    for (int k = 0; k < npairs; ++k) {
+      key_id[keys[k]] = k; pair_ptr[k + 1] = pair_ptr[k] + key_count[keys[k]];
+      h->pair_a.push_back((int)(keys[k] / h->np)); h->pair_b.push_back((int)(keys[k] % h->np));
+    }
+    const int64_t nitems = pair_ptr[npairs];
+    if (nitems > 0x7fffffffLL) return h->fail(BSNLS_ERR_UNSUPPORTED, "too many observation pairs");
+    item_i.resize(nitems); item_j.resize(nitems);
+    std::vector<int> cur(pair_ptr.begin(), pair_ptr.end() - 1);
+    for (int e = 0; e < h->ne; ++e)
+      for (int i = lm_ptr[e]; i < lm_ptr[e + 1]; ++i)
+        for (int j = i; j < lm_ptr[e + 1]; ++j) {
+          const int a = s_pose[i], b = s_pose[j];
+          const int id = key_id[key_of(std::min(a, b), std::max(a, b))];
+          if (a < b || i == j) { item_i[cur[id]] = i; item_j[cur[id]] = j; cur[id]++; }
+          else if (a > b) { item_i[cur[id]] = j; item_j[cur[id]] = i; cur[id]++; }
+          else { item_i[cur[id]] = i; item_j[cur[id]] = j; cur[id]++; item_i[cur[id]] = j; item_j[cur[id]] = i; cur[id]++; }
+        }
+    h->npairs = npairs; h->nitems = nitems;
+  }
+
+  // ---- generic factors (type-major; factors whose blocks are all constant go last: fixed cost) ----
+  std::vector<int> gf_type, gf_nblk, gf_nres, gf_blocks, gf_loss_type, gf_joff, gf_roff;
+  std::vector<long long> gf_coff; std::vector<double> gf_consts, gf_loss_a;
+  struct GfRef { const bsnls_factor_group* g; int i; bool removed; };
+  std::vector<GfRef> refs;
+  for (const bsnls_factor_group* G : gfg) {
+    const int nbk = kNumBlocks[G->type];
+    for (int i = 0; i < G->count; ++i) {
+      bool any = false;
+      for (int b = 0; b < nbk; ++b) {
+        const int blk = G->blocks[(int64_t)i * nbk + b];
+        any = any || !pr->block_constant[blk];
+        if (epos[blk] >= 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "a non-reprojection factor references an elimination-group-0 block");
+      }
+      refs.push_back({G, i, !any});
+    }
+  }
+  std::stable_sort(refs.begin(), refs.end(), [](const GfRef& a, const GfRef& b) { return a.removed < b.removed; });
+  h->ngf = (int)refs.size(); h->ngf_active = 0;
+  std::map<std::pair<int, int>, int> gf_id;  // (type, index in group) -> gf id
+  int64_t joff = 0, roff = 0;
+  for (int f = 0; f < h->ngf; ++f) {
+    const bsnls_factor_group* G = refs[f].g; const int i = refs[f].i, nbk = kNumBlocks[G->type], nr = kNumRes[G->type], stride = kStride[G->type];
+    if (!refs[f].removed) h->ngf_active++;
+    gf_id[{G->type, i}] = f;
+    gf_type.push_back(G->type); gf_nblk.push_back(nbk); gf_nres.push_back(nr);
+    for (int b = 0; b < kGfMaxBlocks; ++b) gf_blocks.push_back(b < nbk ? G->blocks[(int64_t)i * nbk + b] : -1);
+    gf_coff.push_back((long long)gf_consts.size());
+    gf_consts.insert(gf_consts.end(), G->consts + (int64_t)i * stride, G->consts + (int64_t)(i + 1) * stride);
+    gf_loss_type.push_back(G->loss_type ? G->loss_type[i] : 0); gf_loss_a.push_back(G->loss_param ? G->loss_param[i] : 0.0);
+    gf_joff.push_back((int)joff); gf_roff.push_back((int)roff);
+    joff += (int64_t)nr * 3 * nbk; roff += nr;
+  }
+  h->gfJ_size = joff; h->gfR_size = roff; h->gf_roff_h = gf_roff; h->gf_nres_h = gf_nres;
+  // contributions per f-block and per S destination
+  std::vector<int> fg_ptr(h->nf + 1, 0), fg_fac, fg_lb;
+  {
+    std::vector<std::vector<std::pair<int, int>>> per(h->nf);
+    for (int f = 0; f < h->ngf_active; ++f)
+      for (int b = 0; b < gf_nblk[f]; ++b) { const int blk = gf_blocks[f * kGfMaxBlocks + b]; if (fpos[blk] >= 0) per[fpos[blk]].push_back({f, b}); }
+    for (int k = 0; k < h->nf; ++k) { fg_ptr[k + 1] = fg_ptr[k] + (int)per[k].size(); for (auto& pb : per[k]) { fg_fac.push_back(pb.first); fg_lb.push_back(pb.second); } }
+  }
+  std::vector<int> gd_ptr, gd_fac, gd_bi, gd_bj; h->gd_row.clear(); h->gd_col.clear();
+  {
+    struct C { uint64_t key; int f, bi, bj; };
+    std::vector<C> cs;
+    for (int f = 0; f < h->ngf_active; ++f)
+      for (int bi = 0; bi < gf_nblk[f]; ++bi)
+        for (int bj = 0; bj < gf_nblk[f]; ++bj) {
+          const int R = fpos[gf_blocks[f * kGfMaxBlocks + bi]], Cc = fpos[gf_blocks[f * kGfMaxBlocks + bj]];
+          if (R < 0 || Cc < 0 || R < Cc) continue;
+          if (R == Cc && bi != bj) continue;
+          cs.push_back({(uint64_t)R * (uint64_t)h->nf + (uint64_t)Cc, f, bi, bj});
+        }
+    std::stable_sort(cs.begin(), cs.end(), [](const C& a, const C& b) { return a.key < b.key; });
+    gd_ptr.push_back(0);
+    for (size_t k = 0; k < cs.size(); ++k) {
+      if (k == 0 || cs[k].key != cs[k - 1].key) { if (k) gd_ptr.push_back((int)k); h->gd_row.push_back((int)(cs[k].key / h->nf)); h->gd_col.push_back((int)(cs[k].key % h->nf)); }
+      gd_fac.push_back(cs[k].f); gd_bi.push_back(cs[k].bi); gd_bj.push_back(cs[k].bj);
+    }
+    gd_ptr.push_back((int)cs.size());
+    h->ngdest = (int)h->gd_row.size();
+    if (cs.empty()) gd_ptr.assign(1, 0);
+  }
+  std::vector<unsigned char> is_pose(nf_dim, 0);
+  for (int a = 0; a < h->np; ++a) {
+    if (pose_q_tan[a] >= 0) for (int k = 0; k < 3; ++k) is_pose[pose_q_tan[a] - ne_dim + k] = 1;
+    if (pose_t_tan[a] >= 0) for (int k = 0; k < 3; ++k) is_pose[pose_t_tan[a] - ne_dim + k] = 1;
+  }
+  // residual order for bsnls_evaluate
+  h->res_order.assign(total, {0, 0, 0});
+  {
+    std::vector<char> seen(total, 0);
+    for (int g = 0; g < pr->num_groups; ++g) {
+      const bsnls_factor_group& G = pr->groups[g];
+      for (int i = 0; i < G.count; ++i) {
+        const int ri = G.res_index[i];
+        if (ri < 0 || ri >= total || seen[ri]) return h->fail(BSNLS_ERR_INVALID, "res_index is not a permutation of 0..N-1");
+        seen[ri] = 1;
+        h->res_order[ri] = {G.type, G.type == BSNLS_FACTOR_REPROJECTION ? inv_order[i] : gf_id[{G.type, i}], 0};
+      }
+    }
+    int row = 0;
+    for (auto& r : h->res_order) { r.row = row; row += kNumRes[r.type]; }
+    h->num_res_rows = row;
+  }
+
+  // ---- upload ----
+  cudaStream_t s = h->stream;
+  CK(upload(h->d_blk_off, h->blk_off, s)); CK(upload(h->d_blk_size, h->blk_size, s)); CK(upload(h->d_blk_tan, h->blk_tan, s));
+  CK(upload(h->d_blk_manifold, h->blk_manifold, s)); CK(upload(h->d_active, h->active_blocks, s));
+  CK(upload(h->d_pose_q_off, pose_q_off, s)); CK(upload(h->d_pose_t_off, pose_t_off, s)); CK(upload(h->d_pose_q_tan, pose_q_tan, s));
+  CK(upload(h->d_pose_t_tan, pose_t_tan, s)); CK(upload(h->d_pose_ptr, pose_ptr, s)); CK(upload(h->d_pose_obs, pose_obs, s));
+  CK(upload(h->d_obs_pose, s_pose, s)); CK(upload(h->d_obs_lm, s_lm, s)); CK(upload(h->d_obs_cam, s_cam, s)); CK(upload(h->d_obs_pixel, s_pixel, s));
+  CK(upload(h->d_lm_ptr, lm_ptr, s)); CK(upload(h->d_lm_off, lm_off, s));
+  { std::vector<double> cams(pr->cameras, pr->cameras + (size_t)pr->num_cameras * BSNLS_CAMERA_STRIDE); CK(upload(h->d_cams, cams, s)); }
+  CK(upload(h->d_gf_type, gf_type, s)); CK(upload(h->d_gf_nblk, gf_nblk, s)); CK(upload(h->d_gf_nres, gf_nres, s)); CK(upload(h->d_gf_blocks, gf_blocks, s));
+  CK(upload(h->d_gf_coff, gf_coff, s)); CK(upload(h->d_gf_consts, gf_consts, s)); CK(upload(h->d_gf_loss_type, gf_loss_type, s));
+  CK(upload(h->d_gf_loss_a, gf_loss_a, s)); CK(upload(h->d_gf_joff, gf_joff, s)); CK(upload(h->d_gf_roff, gf_roff, s));
+  CK(upload(h->d_pair_a, h->pair_a, s)); CK(upload(h->d_pair_b, h->pair_b, s)); CK(upload(h->d_pair_ptr, pair_ptr, s));
+  CK(upload(h->d_item_i, item_i, s)); CK(upload(h->d_item_j, item_j, s));
+  CK(upload(h->d_fg_ptr, fg_ptr, s)); CK(upload(h->d_fg_fac, fg_fac, s)); CK(upload(h->d_fg_lb, fg_lb, s));
+  CK(upload(h->d_gd_row, h->gd_row, s)); CK(upload(h->d_gd_col, h->gd_col, s)); CK(upload(h->d_gd_ptr, gd_ptr, s));
+  CK(upload(h->d_gd_fac, gd_fac, s)); CK(upload(h->d_gd_bi, gd_bi, s)); CK(upload(h->d_gd_bj, gd_bj, s)); CK(upload(h->d_is_pose, is_pose, s));
+  // work buffers
+  const int ntan = ne_dim + nf_dim;
+  h->nb_obs = nobs ? BlocksFor(nobs, 256) : 0; h->nb_lm = h->ne ? BlocksFor(h->ne * h->G, 256) : 0; h->nb_act = BlocksFor((int)h->active_blocks.size(), 256);
+  CK(h->d_x.alloc(sizeof(double) * off)); CK(h->d_xc.alloc(sizeof(double) * off)); CK(h->d_x0.alloc(sizeof(double) * off));
+  CK(h->d_Jrec.alloc(sizeof(double) * kJRec * (size_t)nobs)); CK(h->d_Vrec.alloc(sizeof(double) * kVRec * (size_t)nobs));
+  CK(h->d_minv.alloc(sizeof(double) * 6 * (size_t)h->ne)); CK(h->d_grad.alloc(sizeof(double) * ntan)); CK(h->d_colsq.alloc(sizeof(double) * ntan));
+  CK(h->d_scale.alloc(sizeof(double) * ntan)); CK(h->d_y.alloc(sizeof(double) * ntan)); CK(h->d_yf.alloc(sizeof(double) * nf_dim));
+  CK(h->d_rhs.alloc(sizeof(double) * nf_dim)); CK(h->d_S.alloc(sizeof(double) * (size_t)nf_dim * nf_dim)); CK(h->d_poseH.alloc(sizeof(double) * 21 * (size_t)std::max(1, h->np)));
+  CK(h->d_gfJ.alloc(sizeof(double) * joff)); CK(h->d_gfR.alloc(sizeof(double) * roff));
+  CK(h->d_cost_part.alloc(sizeof(double) * (h->nb_obs + h->ngf + 1))); CK(h->d_cand_part.alloc(sizeof(double) * (h->nb_obs + h->ngf + 1)));
+  CK(h->d_model_part.alloc(sizeof(double) * (h->nb_lm + h->ngf + 1)));
+  CK(h->d_step_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_candsq_part.alloc(sizeof(double) * h->nb_act));
+  CK(h->d_gsq_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_gmax_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_xsq_part.alloc(sizeof(double) * h->nb_act));
+  CK(h->d_red.alloc(sizeof(double) * 16)); CK(h->d_state.alloc(sizeof(LMState)));
+  CK(cudaMemcpyAsync(h->d_x.p, pr->block_values, sizeof(double) * off, cudaMemcpyHostToDevice, s));
+  CK(cudaMemsetAsync(h->d_y.p, 0, sizeof(double) * ntan, s));
+
+  DeviceProblem& P = h->P;
+  P.num_blocks = nb; P.num_active = (int)h->active_blocks.size(); P.blk_off = h->d_blk_off.as<int>(); P.blk_size = h->d_blk_size.as<int>();
+  P.blk_tan = h->d_blk_tan.as<int>(); P.blk_manifold = h->d_blk_manifold.as<int>(); P.active_blocks = h->d_active.as<int>();
+  P.ne = h->ne; P.nf = h->nf; P.ne_dim = ne_dim; P.nf_dim = nf_dim; P.ntan = ntan;
+  P.num_poses = h->np; P.pose_q_off = h->d_pose_q_off.as<int>(); P.pose_t_off = h->d_pose_t_off.as<int>();
+  P.pose_q_tan = h->d_pose_q_tan.as<int>(); P.pose_t_tan = h->d_pose_t_tan.as<int>(); P.pose_ptr = h->d_pose_ptr.as<int>(); P.pose_obs = h->d_pose_obs.as<int>();
+  P.num_obs = nobs; P.obs_pose = h->d_obs_pose.as<int>(); P.obs_lm = h->d_obs_lm.as<int>(); P.obs_cam = h->d_obs_cam.as<int>(); P.obs_pixel = h->d_obs_pixel.as<double>();
+  P.lm_ptr = h->d_lm_ptr.as<int>(); P.lm_off = h->d_lm_off.as<int>(); P.cams = h->d_cams.as<CameraModel>();
+  P.num_gf = h->ngf; P.gf_type = h->d_gf_type.as<int>(); P.gf_nblk = h->d_gf_nblk.as<int>(); P.gf_nres = h->d_gf_nres.as<int>(); P.gf_blocks = h->d_gf_blocks.as<int>();
+  P.gf_coff = h->d_gf_coff.as<long long>(); P.gf_consts = h->d_gf_consts.as<double>(); P.gf_loss_type = h->d_gf_loss_type.as<int>(); P.gf_loss_a = h->d_gf_loss_a.as<double>();
+  P.gf_joff = h->d_gf_joff.as<int>(); P.gf_roff = h->d_gf_roff.as<int>();
+  P.num_pairs = h->npairs; P.pair_a = h->d_pair_a.as<int>(); P.pair_b = h->d_pair_b.as<int>(); P.pair_ptr = h->d_pair_ptr.as<int>();
+  P.item_i = h->d_item_i.as<int>(); P.item_j = h->d_item_j.as<int>();
+  P.fg_ptr = h->d_fg_ptr.as<int>(); P.fg_fac = h->d_fg_fac.as<int>(); P.fg_lb = h->d_fg_lb.as<int>();
+  P.num_gdest = h->ngdest; P.gd_row = h->d_gd_row.as<int>(); P.gd_col = h->d_gd_col.as<int>(); P.gd_ptr = h->d_gd_ptr.as<int>();
+  P.gd_fac = h->d_gd_fac.as<int>(); P.gd_bi = h->d_gd_bi.as<int>(); P.gd_bj = h->d_gd_bj.as<int>();
+  CK(cudaStreamSynchronize(s));  // host vectors above go out of scope
+  h->has_problem = true;
+  return BSNLS_OK;
+}
+
+int bsnls_set_values(bsnls_handle* h, const double* v) {
+  if (!h || !v) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_set_values before bsnls_set_problem");
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpyAsync(h->d_x.p, v, sizeof(double) * h->num_values, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  h->jac_valid = false;
+  return BSNLS_OK;
+}
+
+int bsnls_get_values(bsnls_handle* h, double* v) {
+  if (!h || !v) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_get_values before bsnls_set_problem");
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpyAsync(v, h->d_x.p, sizeof(double) * h->num_values, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return BSNLS_OK;
+}
+
+int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32_t max_its_out) {
+  if (!h || !sum) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_solve before bsnls_set_problem");
+  CK(cudaSetDevice(h->device));
+  const auto t0 = std::chrono::steady_clock::now();
+  std::memset(sum, 0, sizeof(*sum));
+  const Options o = MakeOptions(h->opt);
+  const int max_it = h->opt.max_num_iterations;
+  h->max_records = max_it + 2;
+  CK(h->d_recs.alloc(sizeof(bsnls_iteration) * h->max_records));
+  int rc = InitState(h, false);
+  if (rc != BSNLS_OK) return rc;
+  LMState* st = h->d_state.as<LMState>();
+  bsnls_iteration* recs = h->d_recs.as<bsnls_iteration>();
+  CK(cudaMemcpyAsync(h->d_x0.p, h->d_x.p, sizeof(double) * h->num_values, cudaMemcpyDeviceToDevice, h->stream));
+  CK(cudaMemcpyAsync(h->d_xc.p, h->d_x.p, sizeof(double) * h->num_values, cudaMemcpyDeviceToDevice, h->stream));  // constant blocks
+  LAUNCH(h, xnorm_kernel, h->nb_act, 256, h->P, h->d_x.as<double>(), h->d_xsq_part.as<double>());
+  { RedList L{}; L.gate = 0; L.count = 1; L.d[0] = RedDesc{h->d_xsq_part.as<double>(), h->nb_act, 0, RED_X_SQ};
+    LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), st); }
+  CK(cudaEventRecord(h->ev0, h->stream));
+  const bool timed = h->opt.max_solver_time_in_seconds < 1e8;
+  for (int pass = 0; pass <= max_it; ++pass) {
+    EnqueueEval(h);
+    if (pass < max_it) EnqueueLandmark(h, o);
+    EnqueueGradient(h, o);
+    LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
+    if (pass == max_it) break;
+    EnqueueAssemble(h, o);
+    EnqueueDenseSolve(h);
+    EnqueueStep(h);
+    LAUNCH(h, ctrl_end_iteration_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
+    LAUNCH(h, apply_step_kernel, BlocksFor((int)h->num_values, 256), 256, h->d_x.as<double>(), h->d_xc.as<double>(), (int)h->num_values, st);
+    if (timed || (pass & 3) == 3) {
+      // poll the device state so that converged solves stop enqueuing; with a time budget also check the clock
+      LMState hs; CK(cudaMemcpyAsync(&hs, st, sizeof(hs), cudaMemcpyDeviceToHost, h->stream)); CK(cudaStreamSynchronize(h->stream));
+      if (hs.done) break;
+      const double el = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+      if (timed && el >= h->opt.max_solver_time_in_seconds) {
+        // an accepted step still needs its Jacobian pass to be recorded; then stop (NO_CONVERGENCE)
+        EnqueueEval(h); EnqueueGradient(h, o);
+        LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
+        LAUNCH(h, set_done_kernel, 1, 1, st, (int)BSNLS_NO_CONVERGENCE, (int)MSG_MAX_TIME);
+        break;
+      }
+    }
+  }
+  CK(cudaEventRecord(h->ev1, h->stream));
+  LMState hs;
+  CK(cudaMemcpyAsync(&hs, st, sizeof(hs), cudaMemcpyDeviceToHost, h->stream));
+  std::vector<bsnls_iteration> hrec(h->max_records);
+  CK(cudaMemcpyAsync(hrec.data(), recs, sizeof(bsnls_iteration) * h->max_records, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  CK(cudaGetLastError());
+  float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+  if (!hs.done) { hs.termination = BSNLS_NO_CONVERGENCE; hs.message_id = MSG_MAX_ITER; }
+  sum->termination_type = hs.termination;
+  std::snprintf(sum->message, sizeof(sum->message), "%s", MessageText(hs.message_id));
+  const int nrec = std::min(hs.num_records, h->max_records);
+  sum->num_iterations = nrec; sum->num_successful_steps = hs.num_successful; sum->num_unsuccessful_steps = hs.num_unsuccessful;
+  sum->fixed_cost = hs.fixed_cost;
+  sum->initial_cost = nrec ? hrec[0].cost : 0.0; sum->final_cost = sum->initial_cost;
+  for (int i = 0; i < nrec; ++i) sum->final_cost = std::min(sum->final_cost, hrec[i].cost);  // ceres solver.cc SetSummaryFinalCost
+  for (int i = 0; i < nrec && i < max_its_out && its; ++i) its[i] = hrec[i];
+  sum->num_e_blocks = h->ne; sum->num_f_blocks = h->nf; sum->reduced_system_dim = h->P.nf_dim; sum->linear_solver_used = BSNLS_LINEAR_DENSE_SCHUR;
+  sum->num_parameter_blocks_reduced = h->ne + h->nf; sum->num_effective_parameters_reduced = h->P.ntan;
+  for (int b : h->active_blocks) sum->num_parameters_reduced += h->blk_size[b];
+  sum->num_residual_blocks_reduced = h->nobs + h->ngf_active;
+  sum->num_residuals_reduced = 2 * h->nobs; for (int f = 0; f < h->ngf_active; ++f) sum->num_residuals_reduced += h->gf_nres_h[f];
+  sum->device_time_in_seconds = 1e-3 * ms;
+  if (hs.termination == BSNLS_FAILURE) {  // leave the parameters as they were
+    CK(cudaMemcpyAsync(h->d_x.p, h->d_x0.p, sizeof(double) * h->num_values, cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
+  h->jac_valid = false;
+  sum->total_time_in_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  return BSNLS_OK;
+}
+
+int bsnls_run_eval(bsnls_handle* h, double* cost) {
+  if (!h) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_run_eval before bsnls_set_problem");
+  CK(cudaSetDevice(h->device));
+  int rc = InitState(h, false);
+  if (rc != BSNLS_OK) return rc;
+  h->profiling = true;
+  CK(cudaEventRecord(h->ev0, h->stream));
+  EnqueueEval(h);
+  CK(cudaEventRecord(h->ev1, h->stream));
+  h->profiling = false;
+  RedList L{}; L.gate = 0; L.count = 0;
+  if (h->nobs) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>(), h->nb_obs, 0, RED_COST};
+  if (h->ngf) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>() + h->nb_obs, h->ngf, 0, RED_COST};
+  LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), h->d_state.as<LMState>());
+  double red[RED_NUM];
+  CK(cudaMemcpyAsync(red, h->d_red.p, sizeof(red), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream)); CK(cudaGetLastError());
+  CK(cudaEventElapsedTime(&h->last_eval_ms, h->ev0, h->ev1));
+  if (cost) *cost = red[RED_COST];
+  cudaEventElapsedTime(&h->breakdown[0], h->pev[0], h->pev[1]); cudaEventElapsedTime(&h->breakdown[1], h->pev[1], h->pev[2]);
+  h->jac_valid = true;
+  return BSNLS_OK;
+}
+
+int bsnls_run_schur(bsnls_handle* h, double radius) {
+  if (!h) return BSNLS_ERR_INVALID;
+  if (!h->has_problem || !h->jac_valid) return h->fail(BSNLS_ERR_STATE, "bsnls_run_schur needs bsnls_run_eval first");
+  if (!(radius > 0)) return h->fail(BSNLS_ERR_INVALID, "radius must be positive");
+  CK(cudaSetDevice(h->device));
+  LMState s{}; s.radius = radius; s.decrease_factor = 2.0; s.need_jacobian = 1; s.scale_ready = 0;
+  CK(cudaMemcpyAsync(h->d_state.p, &s, sizeof(s), cudaMemcpyHostToDevice, h->stream));
+  const Options o = MakeOptions(h->opt);
+  h->profiling = true;
+  CK(cudaEventRecord(h->ev0, h->stream));
+  MARK(h, 3);
+  EnqueueLandmark(h, o);
+  MARK(h, 4);
+  EnqueueGradient(h, o);
+  EnqueueAssemble(h, o);
+  CK(cudaEventRecord(h->ev1, h->stream));
+  h->profiling = false;
+  CK(cudaStreamSynchronize(h->stream)); CK(cudaGetLastError());
+  CK(cudaEventElapsedTime(&h->last_schur_ms, h->ev0, h->ev1));
+  cudaEventElapsedTime(&h->breakdown[2], h->pev[3], h->pev[4]); cudaEventElapsedTime(&h->breakdown[3], h->pev[4], h->pev[5]);
+  cudaEventElapsedTime(&h->breakdown[4], h->pev[5], h->pev[6]); cudaEventElapsedTime(&h->breakdown[5], h->pev[6], h->pev[7]);
+  cudaEventElapsedTime(&h->breakdown[6], h->pev[7], h->pev[8]);
+  return BSNLS_OK;
+}
+
+int bsnls_last_kernel_ms(bsnls_handle* h, float* eval_ms, float* schur_ms) {
+  if (!h) return BSNLS_ERR_INVALID;
+  if (eval_ms) *eval_ms = h->last_eval_ms;
+  if (schur_ms) *schur_ms = h->last_schur_ms;
+  return BSNLS_OK;
+}
+
+int bsnls_last_breakdown_ms(bsnls_handle* h, float out[8]) {
+  if (!h || !out) return BSNLS_ERR_INVALID;
+  std::memcpy(out, h->breakdown, sizeof(float) * 8);
+  return BSNLS_OK;
+}
+
+int bsnls_get_reduced_system(bsnls_handle* h, double radius, double* S, double* rhs, int32_t dim) {
+  if (!h || !S || !rhs) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "no problem");
+  if (dim != h->P.nf_dim) return h->fail(BSNLS_ERR_INVALID, "dim must be %d", h->P.nf_dim);
+  int rc = bsnls_run_eval(h, nullptr);
+  if (rc != BSNLS_OK) return rc;
+  rc = bsnls_run_schur(h, radius);
+  if (rc != BSNLS_OK) return rc;
+  CK(cudaMemcpyAsync(S, h->d_S.p, sizeof(double) * (size_t)dim * dim, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpyAsync(rhs, h->d_rhs.p, sizeof(double) * dim, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  for (int c = 0; c < dim; ++c) for (int r = 0; r < c; ++r) S[(size_t)c * dim + r] = S[(size_t)r * dim + c];  // mirror the lower triangle
+  return BSNLS_OK;
+}
+
+int bsnls_evaluate(bsnls_handle* h, double* cost, double* residuals, int64_t* num_residuals, double* gradient, int64_t* num_gradient) {
+  if (!h) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_evaluate before bsnls_set_problem");
+  CK(cudaSetDevice(h->device));
+  if (num_residuals) *num_residuals = h->num_res_rows;
+  if (num_gradient) *num_gradient = h->P.ntan;
+  int rc = InitState(h, false);
+  if (rc != BSNLS_OK) return rc;
+  const Options o = MakeOptions(h->opt);
+  LMState* st = h->d_state.as<LMState>();
+  EnqueueEval(h); EnqueueLandmark(h, o); EnqueueGradient(h, o);
+  // include factors whose blocks are all constant in the cost (Problem::Evaluate evaluates every residual block)
+  RedList L{}; L.gate = 0; L.count = 0;
+  if (h->nobs) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>(), h->nb_obs, 0, RED_COST};
+  if (h->ngf) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>() + h->nb_obs, h->ngf, 0, RED_COST};
+  LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), st);
+  double red[RED_NUM];
+  CK(cudaMemcpyAsync(red, h->d_red.p, sizeof(red), cudaMemcpyDeviceToHost, h->stream));
+  std::vector<double> jrec, gfr, grad;
+  if (residuals) {
+    jrec.resize((size_t)h->nobs * kJRec); gfr.resize(h->gfR_size);
+    if (h->nobs) CK(cudaMemcpyAsync(jrec.data(), h->d_Jrec.p, sizeof(double) * jrec.size(), cudaMemcpyDeviceToHost, h->stream));
+    if (h->gfR_size) CK(cudaMemcpyAsync(gfr.data(), h->d_gfR.p, sizeof(double) * gfr.size(), cudaMemcpyDeviceToHost, h->stream));
+  }
+  if (gradient) { grad.resize(h->P.ntan); CK(cudaMemcpyAsync(grad.data(), h->d_grad.p, sizeof(double) * grad.size(), cudaMemcpyDeviceToHost, h->stream)); }
+  CK(cudaStreamSynchronize(h->stream)); CK(cudaGetLastError());
+  if (cost) *cost = red[RED_COST];
+  if (residuals) {
+    const std::vector<int>& gf_roff = h->gf_roff_h;
+    for (const auto& r : h->res_order) {
+      if (r.type == BSNLS_FACTOR_REPROJECTION) { residuals[r.row] = jrec[(size_t)r.idx * kJRec + 6]; residuals[r.row + 1] = jrec[(size_t)r.idx * kJRec + 7]; }
+      else for (int k = 0; k < kNumRes[r.type]; ++k) residuals[r.row + k] = gfr[gf_roff[r.idx] + k];
+    }
+  }
+  if (gradient) {  // tangent gradient over active blocks in program order
+    int64_t n = 0;
+    for (int b : h->active_blocks) { for (int k = 0; k < 3; ++k) gradient[n + k] = grad[h->blk_tan[b] + k]; n += 3; }
+  }
+  h->jac_valid = true;
+  return BSNLS_OK;
+}
+
+int bsnls_get_ordering(bsnls_handle* h, int32_t* e_blocks, int32_t* num_e, int32_t* f_blocks, int32_t* num_f) {
+  if (!h) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "no problem");
+  if (num_e) *num_e = h->ne;
+  if (num_f) *num_f = h->nf;
+  if (e_blocks) std::memcpy(e_blocks, h->eblocks.data(), sizeof(int) * h->ne);
+  if (f_blocks) std::memcpy(f_blocks, h->fblocks.data(), sizeof(int) * h->nf);
+  return BSNLS_OK;
+}
+
+int bsnls_get_reduced_pattern(bsnls_handle* h, int32_t* rows, int32_t* cols, int64_t* count) {
+  if (!h || !count) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "no problem");
+  std::vector<uint64_t> keys;
+  std::vector<int> fpos(h->num_blocks, -1);
+  for (int k = 0; k < h->nf; ++k) fpos[h->fblocks[k]] = k;
+  auto add = [&](int r, int c) { if (r < 0 || c < 0) return; if (r < c) std::swap(r, c); keys.push_back((uint64_t)r * h->nf + c); };
+  for (int p = 0; p < h->npairs; ++p) {
+    const int a = h->pair_a[p], b = h->pair_b[p];
+    const int fa[2] = {fpos[h->pose_q_blk[a]], fpos[h->pose_t_blk[a]]}, fb[2] = {fpos[h->pose_q_blk[b]], fpos[h->pose_t_blk[b]]};
+    for (int i = 0; i < 2; ++i) for (int j = 0; j < 2; ++j) add(fa[i], fb[j]);
+  }
+  for (int d = 0; d < h->ngdest; ++d) add(h->gd_row[d], h->gd_col[d]);
+  for (int k = 0; k < h->nf; ++k) add(k, k);
+  std::sort(keys.begin(), keys.end()); keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
+  if (rows && cols) { if (*count < (int64_t)keys.size()) return h->fail(BSNLS_ERR_INVALID, "pattern buffers too small"); for (size_t k = 0; k < keys.size(); ++k) { rows[k] = (int)(keys[k] / h->nf); cols[k] = (int)(keys[k] % h->nf); } }
+  *count = (int64_t)keys.size();
+  return BSNLS_OK;
+}
+
+int bsnls_nccl_unique_id(char id[128]) { (void)id; g_create_error = "multi-GPU sharding is not built in this library version"; return BSNLS_ERR_UNSUPPORTED; }
+int bsnls_create_sharded(const bsnls_options* options, int32_t rank, int32_t world_size, const char nccl_id[128], bsnls_handle** handle) {
+  (void)nccl_id;
+  if (world_size == 1 && rank == 0) return bsnls_create(options, handle);
+  g_create_error = "multi-GPU sharding is not built in this library version"; return BSNLS_ERR_UNSUPPORTED;
+}
+
+}  // extern "C"

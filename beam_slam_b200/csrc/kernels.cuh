@@ -1,0 +1,859 @@
+// CUDA kernels of the B200-native LM back end (sm_100a, FP64). See DESIGN.md for the data layout and the
+// per-kernel roofline. Every kernel is gated by the device-resident LM state so that a whole solve can be
+// enqueued without host round trips (K9, device-side controller).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/bsnls.h"
+#include "device_math.cuh"
+
+namespace bsnls {
+
+constexpr int kJRec = 20;   // per observation: E[6] (2x3 wrt landmark) | r[2] | F[12] (2x6 wrt q-tangent, t)
+constexpr int kVRec = 24;   // per observation: V[18] (6x3 = F^T E C) | c[6] (= V z)
+constexpr int kGfMaxBlocks = 10, kGfMaxRes = 15, kGfMaxAmbient = 32;
+
+struct LMState {
+  // trust region (ceres LevenbergMarquardtStrategy)
+  double radius, decrease_factor;
+  double x_cost, cand_cost, model_cost_change, x_norm, cand_norm, step_norm, grad_max, grad_norm, fixed_cost;
+  // pending record of an accepted step, completed once the new Jacobian / gradient exist
+  double pend_cost_change, pend_step_norm, pend_relative_decrease;
+  int pend_linear_iters;
+  int iteration, done, need_jacobian, scale_ready, accepted, lin_fail, num_invalid;
+  int termination, message_id, num_records, num_successful, num_unsuccessful, pcg_iters;
+  int max_records;
+};
+enum MessageId { MSG_NONE = 0, MSG_MAX_ITER, MSG_GRAD_TOL, MSG_MIN_RADIUS, MSG_PARAM_TOL, MSG_FUNC_TOL,
+                 MSG_INVALID_STEPS, MSG_MAX_TIME, MSG_NONFINITE };
+
+// reduced scalars (written by reduce_kernel)
+enum RedSlot { RED_COST = 0, RED_CAND_COST, RED_MODEL, RED_STEP_SQ, RED_CAND_SQ, RED_GRAD_SQ, RED_GRAD_MAX,
+               RED_X_SQ, RED_FIXED, RED_NUM };
+
+struct DeviceProblem {
+  // parameter blocks
+  int num_blocks, num_active; const int* blk_off; const int* blk_size; const int* blk_tan; const int* blk_manifold;
+  const int* active_blocks;  // indices of active blocks
+  int ne, nf, ne_dim, nf_dim, ntan;
+  // camera poses = (q block, t block) pairs referenced by reprojection factors
+  int num_poses; const int* pose_q_off; const int* pose_t_off; const int* pose_q_tan; const int* pose_t_tan;
+  const int* pose_ptr; const int* pose_obs;   // observations of each pose (CSR), sorted observation ids
+  // observations sorted by landmark (elimination order)
+  int num_obs; const int* obs_pose; const int* obs_lm; const int* obs_cam; const double* obs_pixel;
+  const int* lm_ptr; const int* lm_off;       // per landmark: first observation, value offset
+  const CameraModel* cams;
+  // generic (non-reprojection) factors, type-major
+  int num_gf; const int* gf_type; const int* gf_nblk; const int* gf_nres; const int* gf_blocks;  // 10 per factor
+  const long long* gf_coff; const double* gf_consts; const int* gf_loss_type; const double* gf_loss_a;
+  const int* gf_joff; const int* gf_roff;     // offsets into gfJ (nres x 3*nblk row-major) and gfR
+  // S pair blocks (pose a <= pose b) and their items
+  int num_pairs; const int* pair_a; const int* pair_b; const int* pair_ptr; const int* item_i; const int* item_j;
+  // generic-factor contributions: per f-block (gradient / column norms) and per 3x3 destination of S
+  const int* fg_ptr; const int* fg_fac; const int* fg_lb;            // CSR over f-blocks (nf)
+  int num_gdest; const int* gd_row; const int* gd_col; const int* gd_ptr; const int* gd_fac; const int* gd_bi; const int* gd_bj;
+};
+
+struct Options { double min_lm_diagonal, max_lm_diagonal, function_tolerance, gradient_tolerance,
+                 parameter_tolerance, max_radius, min_radius, min_relative_decrease; int max_num_iterations,
+                 max_invalid, jacobi_scaling; };
+
+__device__ __forceinline__ bool gate_run(const LMState* st) { return !st->done; }
+__device__ __forceinline__ bool gate_jac(const LMState* st) { return !st->done && st->need_jacobian; }
+
+// deterministic block reduction (fixed tree), result valid in thread 0
+template <int BLOCK> __device__ __forceinline__ double block_sum(double v, double* sm) {
+  sm[threadIdx.x] = v; __syncthreads();
+#pragma unroll
+  for (int s = BLOCK / 2; s > 0; s >>= 1) { if (threadIdx.x < s) sm[threadIdx.x] += sm[threadIdx.x + s]; __syncthreads(); }
+  return sm[0];
+}
+template <int BLOCK> __device__ __forceinline__ double block_max(double v, double* sm) {
+  sm[threadIdx.x] = v; __syncthreads();
+#pragma unroll
+  for (int s = BLOCK / 2; s > 0; s >>= 1) { if (threadIdx.x < s) sm[threadIdx.x] = fmax(sm[threadIdx.x], sm[threadIdx.x + s]); __syncthreads(); }
+  return sm[0];
+}
+
+// ===================================================================================================
+// K1 + K4: reprojection residual / Jacobian / loss, one thread per observation (a warp = 32 consecutive
+// observations of the landmark-sorted list; camera and landmark blocks are re-used through L1).
+// mode 0: at x, writes Jrec + cost partials (gate: need_jacobian). mode 1: cost only at x_cand.
+// ===================================================================================================
+template <int MODE>
+__global__ void __launch_bounds__(256) eval_reproj_kernel(DeviceProblem P, const double* __restrict__ x,
+                                                          double* __restrict__ Jrec, double* __restrict__ cost_part,
+                                                          const LMState* st) {
+  if (MODE == 0 ? !gate_jac(st) : !gate_run(st)) return;
+  __shared__ double sm[256];
+  const int o = blockIdx.x * 256 + threadIdx.x;
+  double cost = 0.0;
+  if (o < P.num_obs) {
+    const int pose = P.obs_pose[o], lm = P.obs_lm[o];
+    const CameraModel cam = P.cams[P.obs_cam[o]];
+    const double2 px = reinterpret_cast<const double2*>(P.obs_pixel)[o];
+    const double pixel[2] = {px.x, px.y};
+    const int qo = P.pose_q_off[pose], to = P.pose_t_off[pose], po = P.lm_off[lm];
+    const double q[4] = {x[qo], x[qo + 1], x[qo + 2], x[qo + 3]};
+    const double t[3] = {x[to], x[to + 1], x[to + 2]};
+    const double Pw[3] = {x[po], x[po + 1], x[po + 2]};
+    if (MODE == 0) {
+      double r[2], Jq[6], Jt[6], JP[6];
+      cost = reprojection_evaluate(cam, pixel, q, t, Pw, r, Jq, Jt, JP);
+      if (P.pose_q_tan[pose] < 0) { for (int k = 0; k < 6; ++k) Jq[k] = 0.0; }
+      if (P.pose_t_tan[pose] < 0) { for (int k = 0; k < 6; ++k) Jt[k] = 0.0; }
+      double2* out = reinterpret_cast<double2*>(Jrec + (size_t)o * kJRec);
+      out[0] = make_double2(JP[0], JP[1]); out[1] = make_double2(JP[2], JP[3]); out[2] = make_double2(JP[4], JP[5]);
+      out[3] = make_double2(r[0], r[1]);
+      // F row-major 2x6: [Jq row0 | Jt row0 ; Jq row1 | Jt row1]
+      out[4] = make_double2(Jq[0], Jq[1]); out[5] = make_double2(Jq[2], Jt[0]); out[6] = make_double2(Jt[1], Jt[2]);
+      out[7] = make_double2(Jq[3], Jq[4]); out[8] = make_double2(Jq[5], Jt[3]); out[9] = make_double2(Jt[4], Jt[5]);
+    } else {
+      cost = reprojection_cost_only(cam, pixel, q, t, Pw);
+    }
+  }
+  const double tot = block_sum<256>(cost, sm);
+  if (threadIdx.x == 0) cost_part[blockIdx.x] = tot;
+}
+
+// ===================================================================================================
+// K2 / K3 (+K4): generic factors (IMU preintegration, 15-DoF prior, relative pose (+extrinsics), pose prior,
+// ...). One warp per factor; lane k carries d/d(ambient parameter k). MODE as above.
+// ===================================================================================================
+template <int MODE>
+__global__ void __launch_bounds__(128) eval_generic_kernel(DeviceProblem P, const double* __restrict__ x,
+                                                           double* __restrict__ gfJ, double* __restrict__ gfR,
+                                                           double* __restrict__ cost_part, const LMState* st) {
+  if (MODE == 0 ? !gate_jac(st) : !gate_run(st)) return;
+  __shared__ double sJ[4][kGfMaxRes * kGfMaxAmbient];
+  __shared__ double sR[4][kGfMaxRes + 1];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int f = blockIdx.x * 4 + warp;
+  if (f >= P.num_gf) return;
+  const int type = P.gf_type[f], nb = P.gf_nblk[f], nr = P.gf_nres[f];
+  const int* blocks = P.gf_blocks + f * kGfMaxBlocks;
+  const double* c = P.gf_consts + P.gf_coff[f];
+  // gather the ambient parameter vector
+  double pv[kGfMaxAmbient];
+  int boff[kGfMaxBlocks + 1]; boff[0] = 0;
+#pragma unroll
+  for (int b = 0; b < kGfMaxBlocks; ++b) {
+    if (b < nb) {
+      const int blk = blocks[b], sz = P.blk_size[blk], off = P.blk_off[blk];
+      for (int k = 0; k < sz; ++k) pv[boff[b] + k] = x[off + k];
+      boff[b + 1] = boff[b] + sz;
+    } else boff[b + 1] = boff[b];
+  }
+  const int namb = boff[nb];
+  double* J = sJ[warp]; double* R = sR[warp];
+  if (MODE == 0) {
+    Dual p[kGfMaxAmbient], r[kGfMaxRes];
+#pragma unroll
+    for (int k = 0; k < kGfMaxAmbient; ++k) p[k] = Dual(k < namb ? pv[k] : 0.0, k == lane ? 1.0 : 0.0);
+    EvalGenericFactor<Dual>(type, c, p, r);
+    for (int i = 0; i < nr; ++i) { J[i * kGfMaxAmbient + lane] = (lane < namb) ? r[i].v : 0.0; if (lane == 0) R[i] = r[i].a; }
+  } else {
+    if (lane == 0) { double r[kGfMaxRes]; EvalGenericFactor<double>(type, c, pv, r); for (int i = 0; i < nr; ++i) R[i] = r[i]; }
+  }
+  __syncwarp();
+  // loss
+  double s = 0.0;
+  for (int i = 0; i < nr; ++i) s += R[i] * R[i];
+  const int lt = P.gf_loss_type[f];
+  double rho[3] = {s, 1.0, 0.0};
+  if (lt != 0) loss_evaluate(lt, P.gf_loss_a[f], s, rho);
+  if (lane == 0) cost_part[f] = 0.5 * rho[0];
+  if (MODE != 0) return;
+  double sr = 1.0, rs = 1.0, asn = 0.0;
+  if (lt != 0) corrector(s, rho, &sr, &rs, &asn);
+  // ambient -> tangent (x plus-Jacobian for quaternion blocks), then the loss correction, then store.
+  // tangent column t = 3*b + k (every block on this path has tangent size 3)
+  double* Jout = gfJ + P.gf_joff[f];
+  const int ncol = 3 * nb;
+  if (lane < ncol) {
+    const int b = lane / 3, k = lane % 3;
+    const int blk = blocks[b];
+    double col[kGfMaxRes];
+    const bool constant = P.blk_tan[blk] < 0;
+    if (P.blk_manifold[blk] == BSNLS_MANIFOLD_QUATERNION) {
+      double Pj[12]; quat_plus_jacobian(pv + boff[b], Pj);
+      for (int i = 0; i < nr; ++i) {
+        double acc = 0.0;
+        for (int a = 0; a < 4; ++a) acc += J[i * kGfMaxAmbient + boff[b] + a] * Pj[3 * a + k];
+        col[i] = acc;
+      }
+    } else {
+      for (int i = 0; i < nr; ++i) col[i] = J[i * kGfMaxAmbient + boff[b] + k];
+    }
+    if (constant) for (int i = 0; i < nr; ++i) col[i] = 0.0;
+    if (lt != 0) {
+      if (asn == 0.0) { for (int i = 0; i < nr; ++i) col[i] *= sr; }
+      else {
+        double rtj = 0.0;
+        for (int i = 0; i < nr; ++i) rtj += col[i] * R[i];
+        for (int i = 0; i < nr; ++i) col[i] = sr * (col[i] - asn * R[i] * rtj);
+      }
+    }
+    for (int i = 0; i < nr; ++i) Jout[i * ncol + lane] = col[i];
+  }
+  __syncwarp();
+  if (lane < nr) gfR[P.gf_roff[f] + lane] = R[lane] * rs;
+}
+
+// ===================================================================================================
+// K5a: per-landmark elimination. G lanes per landmark; E^T E (3x3) and E^T r are reduced with warp shuffles.
+// Outputs per landmark: Minv (6, symmetric (E^T E + D^2)^-1), g_e = E^T r, c_e = diag(E^T E), Jacobi scale;
+// per observation: V = F^T E C (6x3, Minv = C C^T) and c = V (C^T g_e) so that S -= sum V_a V_b^T, rhs -= c.
+// ===================================================================================================
+template <int G>
+__global__ void __launch_bounds__(256) landmark_kernel(DeviceProblem P, const double* __restrict__ Jrec,
+                                                       double* __restrict__ Vrec, double* __restrict__ lm_minv,
+                                                       double* __restrict__ grad, double* __restrict__ colsq,
+                                                       double* __restrict__ scale, Options opt, LMState* st) {
+  if (!gate_run(st)) return;
+  const int gtid = blockIdx.x * 256 + threadIdx.x;
+  const int l = gtid / G, sub = gtid % G;
+  const bool valid = l < P.ne;
+  const int start = valid ? P.lm_ptr[l] : 0, end = valid ? P.lm_ptr[l + 1] : 0;
+  double a00 = 0, a01 = 0, a02 = 0, a11 = 0, a12 = 0, a22 = 0, g0 = 0, g1 = 0, g2 = 0;
+  for (int o = start + sub; o < end; o += G) {
+    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)o * kJRec);
+    const double2 e0 = rec[0], e1 = rec[1], e2 = rec[2], r = rec[3];
+    // E row0 = (e0.x, e0.y, e1.x), row1 = (e1.y, e2.x, e2.y)
+    a00 += e0.x * e0.x + e1.y * e1.y; a01 += e0.x * e0.y + e1.y * e2.x; a02 += e0.x * e1.x + e1.y * e2.y;
+    a11 += e0.y * e0.y + e2.x * e2.x; a12 += e0.y * e1.x + e2.x * e2.y; a22 += e1.x * e1.x + e2.y * e2.y;
+    g0 += e0.x * r.x + e1.y * r.y; g1 += e0.y * r.x + e2.x * r.y; g2 += e1.x * r.x + e2.y * r.y;
+  }
+#pragma unroll
+  for (int m = 1; m < G; m <<= 1) {
+    a00 += __shfl_xor_sync(0xffffffffu, a00, m); a01 += __shfl_xor_sync(0xffffffffu, a01, m);
+    a02 += __shfl_xor_sync(0xffffffffu, a02, m); a11 += __shfl_xor_sync(0xffffffffu, a11, m);
+    a12 += __shfl_xor_sync(0xffffffffu, a12, m); a22 += __shfl_xor_sync(0xffffffffu, a22, m);
+    g0 += __shfl_xor_sync(0xffffffffu, g0, m); g1 += __shfl_xor_sync(0xffffffffu, g1, m);
+    g2 += __shfl_xor_sync(0xffffffffu, g2, m);
+  }
+  if (!valid) return;
+  const int te = 3 * l;  // e-blocks occupy the first ne_dim tangent entries, 3 each
+  double s0, s1, s2;
+  if (!st->scale_ready) {
+    s0 = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(a00)) : 1.0; s1 = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(a11)) : 1.0;
+    s2 = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(a22)) : 1.0;
+    if (sub == 0) { scale[te] = s0; scale[te + 1] = s1; scale[te + 2] = s2; }
+  } else { s0 = scale[te]; s1 = scale[te + 1]; s2 = scale[te + 2]; }
+  // LM diagonal in unscaled coordinates: D^2 = clamp(c s^2) / (radius s^2)
+  const double radius = st->radius;
+  const double d0 = fmin(fmax(a00 * s0 * s0, opt.min_lm_diagonal), opt.max_lm_diagonal) / (radius * s0 * s0);
+  const double d1 = fmin(fmax(a11 * s1 * s1, opt.min_lm_diagonal), opt.max_lm_diagonal) / (radius * s1 * s1);
+  const double d2 = fmin(fmax(a22 * s2 * s2, opt.min_lm_diagonal), opt.max_lm_diagonal) / (radius * s2 * s2);
+  // Cholesky of M = E^T E + D^2 (lower L), Minv = L^-T L^-1, C = L^-T (upper), z = L^-1 g
+  const double m00 = a00 + d0, m11 = a11 + d1, m22 = a22 + d2;
+  const double l00 = sqrt(m00), l10 = a01 / l00, l20 = a02 / l00;
+  const double t11 = m11 - l10 * l10; const double l11 = sqrt(t11), l21 = (a12 - l20 * l10) / l11;
+  const double t22 = m22 - l20 * l20 - l21 * l21; const double l22 = sqrt(t22);
+  if (!(m00 > 0.0) || !(t11 > 0.0) || !(t22 > 0.0)) { st->lin_fail = 1; }
+  // Linv (lower): i00 = 1/l00, i10 = -l10 i00 / l11, i11 = 1/l11, i20 = -(l20 i00 + l21 i10)/l22, i21 = -l21 i11/l22, i22 = 1/l22
+  const double i00 = 1.0 / l00, i11 = 1.0 / l11, i22 = 1.0 / l22;
+  const double i10 = -l10 * i00 * i11, i21 = -l21 * i11 * i22, i20 = -(l20 * i00 + l21 * i10) * i22;
+  const double z0 = i00 * g0, z1 = i10 * g0 + i11 * g1, z2 = i20 * g0 + i21 * g1 + i22 * g2;
+  if (sub == 0) {
+    double* mi = lm_minv + (size_t)l * 6;  // Minv = Linv^T Linv, stored (00,01,02,11,12,22)
+    mi[0] = i00 * i00 + i10 * i10 + i20 * i20; mi[1] = i10 * i11 + i20 * i21; mi[2] = i20 * i22;
+    mi[3] = i11 * i11 + i21 * i21; mi[4] = i21 * i22; mi[5] = i22 * i22;
+    grad[te] = g0; grad[te + 1] = g1; grad[te + 2] = g2;
+    colsq[te] = a00; colsq[te + 1] = a11; colsq[te + 2] = a22;
+  }
+  // pass 2: V = (F^T E) C with C = Linv^T (upper):  V[:,0] = W0 i00; V[:,1] = W0 i10 + W1 i11; V[:,2] = W0 i20 + W1 i21 + W2 i22
+  for (int o = start + sub; o < end; o += G) {
+    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)o * kJRec);
+    const double2 e0 = rec[0], e1 = rec[1], e2 = rec[2];
+    const double E0[3] = {e0.x, e0.y, e1.x}, E1[3] = {e1.y, e2.x, e2.y};
+    double F0[6], F1[6];
+    { const double2 f0 = rec[4], f1 = rec[5], f2 = rec[6], f3 = rec[7], f4 = rec[8], f5 = rec[9];
+      F0[0] = f0.x; F0[1] = f0.y; F0[2] = f1.x; F0[3] = f1.y; F0[4] = f2.x; F0[5] = f2.y;
+      F1[0] = f3.x; F1[1] = f3.y; F1[2] = f4.x; F1[3] = f4.y; F1[4] = f5.x; F1[5] = f5.y; }
+    double2* out = reinterpret_cast<double2*>(Vrec + (size_t)o * kVRec);
+    double v[24];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) {
+      const double w0 = F0[a] * E0[0] + F1[a] * E1[0], w1 = F0[a] * E0[1] + F1[a] * E1[1], w2 = F0[a] * E0[2] + F1[a] * E1[2];
+      const double v0 = w0 * i00, v1 = w0 * i10 + w1 * i11, v2 = w0 * i20 + w1 * i21 + w2 * i22;
+      v[3 * a] = v0; v[3 * a + 1] = v1; v[3 * a + 2] = v2;
+      v[18 + a] = v0 * z0 + v1 * z1 + v2 * z2;
+    }
+#pragma unroll
+    for (int k = 0; k < 12; ++k) out[k] = make_double2(v[2 * k], v[2 * k + 1]);
+  }
+}
+
+// ===================================================================================================
+// K6a: per-pose diagonal data independent of the damping: H_a = sum F^T F (6x6, 21 unique), g_a = sum F^T r.
+// One warp per pose, lanes stride over the pose's observations, butterfly reduction.
+// Writes grad / colsq entries of the pose's q and t blocks and pose_H (21 per pose).
+// ===================================================================================================
+__global__ void __launch_bounds__(128) pose_diag_kernel(DeviceProblem P, const double* __restrict__ Jrec,
+                                                        double* __restrict__ pose_H, double* __restrict__ grad,
+                                                        double* __restrict__ colsq, const LMState* st) {
+  if (!gate_jac(st)) return;
+  const int a = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (a >= P.num_poses) return;
+  double acc[27];
+#pragma unroll
+  for (int k = 0; k < 27; ++k) acc[k] = 0.0;
+  for (int it = P.pose_ptr[a] + lane; it < P.pose_ptr[a + 1]; it += 32) {
+    const int o = P.pose_obs[it];
+    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)o * kJRec);
+    const double2 r = rec[3];
+    double F0[6], F1[6];
+    { const double2 f0 = rec[4], f1 = rec[5], f2 = rec[6], f3 = rec[7], f4 = rec[8], f5 = rec[9];
+      F0[0] = f0.x; F0[1] = f0.y; F0[2] = f1.x; F0[3] = f1.y; F0[4] = f2.x; F0[5] = f2.y;
+      F1[0] = f3.x; F1[1] = f3.y; F1[2] = f4.x; F1[3] = f4.y; F1[4] = f5.x; F1[5] = f5.y; }
+    int k = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+      for (int j = i; j < 6; ++j) acc[k++] += F0[i] * F0[j] + F1[i] * F1[j];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) acc[21 + i] += F0[i] * r.x + F1[i] * r.y;
+  }
+#pragma unroll
+  for (int m = 1; m < 32; m <<= 1)
+#pragma unroll
+    for (int k = 0; k < 27; ++k) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], m);
+  if (lane == 0) {
+    double* H = pose_H + (size_t)a * 21;
+#pragma unroll
+    for (int k = 0; k < 21; ++k) H[k] = acc[k];
+    const int tq = P.pose_q_tan[a], tt = P.pose_t_tan[a];
+    // diagonal entries of the 21-packed upper triangle: index of (i,i) = i*6 - i(i-1)/2
+    const int dg[6] = {0, 6, 11, 15, 18, 20};
+    if (tq >= 0) for (int k = 0; k < 3; ++k) { grad[tq + k] = acc[21 + k]; colsq[tq + k] = acc[dg[k]]; }
+    if (tt >= 0) for (int k = 0; k < 3; ++k) { grad[tt + k] = acc[24 + k]; colsq[tt + k] = acc[dg[3 + k]]; }
+  }
+}
+
+// K6b: generic-factor contributions to the gradient and the column norms of every f-block.
+// One thread per (f-block, component); fixed summation order.
+__global__ void __launch_bounds__(128) gf_grad_kernel(DeviceProblem P, const double* __restrict__ gfJ,
+                                                      const double* __restrict__ gfR, double* __restrict__ grad,
+                                                      double* __restrict__ colsq, const LMState* st) {
+  if (!gate_jac(st)) return;
+  const int tid = blockIdx.x * 128 + threadIdx.x;
+  const int fb = tid / 3, k = tid % 3;
+  if (fb >= P.nf) return;
+  double g = 0.0, c = 0.0;
+  for (int it = P.fg_ptr[fb]; it < P.fg_ptr[fb + 1]; ++it) {
+    const int f = P.fg_fac[it], lb = P.fg_lb[it];
+    const int nr = P.gf_nres[f], ncol = 3 * P.gf_nblk[f];
+    const double* J = gfJ + P.gf_joff[f]; const double* R = gfR + P.gf_roff[f];
+    for (int i = 0; i < nr; ++i) { const double v = J[i * ncol + 3 * lb + k]; g += v * R[i]; c += v * v; }
+  }
+  const int t = P.ne_dim + 3 * fb + k;
+  grad[t] += g; colsq[t] += c;
+}
+
+// Jacobi scale of the f-blocks (iteration 0) and LM diagonal D_f^2; also gradient norms:
+// |x - (x (+) -g)| per active block (TrustRegionMinimizer::EvaluateGradientAndJacobian).
+__global__ void __launch_bounds__(256) fscale_kernel(DeviceProblem P, const double* __restrict__ colsq,
+                                                     double* __restrict__ scale, Options opt, const LMState* st) {
+  if (!gate_jac(st) || st->scale_ready) return;
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j >= P.nf_dim) return;
+  scale[P.ne_dim + j] = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(colsq[P.ne_dim + j])) : 1.0;
+}
+__device__ __forceinline__ void quat_plus(const double* x, const double* d, double* out) {
+  double qd[4]; AngleAxisToQuaternion<double>(d, qd); QuaternionProduct<double>(x, qd, out);
+}
+__global__ void __launch_bounds__(256) grad_norm_kernel(DeviceProblem P, const double* __restrict__ x,
+                                                        const double* __restrict__ grad, double* __restrict__ part_sq,
+                                                        double* __restrict__ part_max, const LMState* st) {
+  if (!gate_jac(st)) return;
+  __shared__ double sm[256];
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  double sq = 0.0, mx = 0.0;
+  if (i < P.num_active) {
+    const int b = P.active_blocks[i], off = P.blk_off[b], t = P.blk_tan[b];
+    if (P.blk_manifold[b] == BSNLS_MANIFOLD_QUATERNION) {
+      const double ng[3] = {-grad[t], -grad[t + 1], -grad[t + 2]};
+      double out[4]; quat_plus(x + off, ng, out);
+      for (int k = 0; k < 4; ++k) { const double d = x[off + k] - out[k]; sq += d * d; mx = fmax(mx, fabs(d)); }
+    } else {
+      for (int k = 0; k < P.blk_size[b]; ++k) { const double d = x[off + k] - (x[off + k] + (-grad[t + k])); sq += d * d; mx = fmax(mx, fabs(d)); }
+    }
+  }
+  const double ts = block_sum<256>(sq, sm); __syncthreads();
+  const double tm = block_max<256>(mx, sm);
+  if (threadIdx.x == 0) { part_sq[blockIdx.x] = ts; part_max[blockIdx.x] = tm; }
+}
+
+// ===================================================================================================
+// K5b: reduced-system assembly, atomics-free. One warp per pose-pair block (a <= b): lanes stride over the
+// items (observation pairs sharing a landmark), each lane accumulates a full 6x6, butterfly reduction gives a
+// fixed summation order. Diagonal blocks add sum F^T F and produce the reduced right-hand side.
+// S is dense column-major (ld = nf_dim), lower triangle.
+// ===================================================================================================
+__device__ __forceinline__ void store_sub3(double* S, int ld, int rt, int ct, const double* B /*3x3 row-major (rt rows, ct cols)*/) {
+  // write the 3x3 block at rows rt.., cols ct.. into the lower triangle (transposed if it lies above)
+  if (rt >= ct) { for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) S[(size_t)(ct + j) * ld + rt + i] = B[3 * i + j]; }
+  else { for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) S[(size_t)(rt + i) * ld + ct + j] = B[3 * i + j]; }
+}
+__global__ void __launch_bounds__(128) pair_kernel(DeviceProblem P, const double* __restrict__ Vrec,
+                                                   const double* __restrict__ pose_H, const double* __restrict__ grad,
+                                                   double* __restrict__ S, double* __restrict__ rhs, const LMState* st) {
+  if (!gate_run(st)) return;
+  const int pb = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (pb >= P.num_pairs) return;
+  const int a = P.pair_a[pb], b = P.pair_b[pb];
+  double acc[36], cacc[6];
+#pragma unroll
+  for (int k = 0; k < 36; ++k) acc[k] = 0.0;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) cacc[k] = 0.0;
+  for (int it = P.pair_ptr[pb] + lane; it < P.pair_ptr[pb + 1]; it += 32) {
+    const int oi = P.item_i[it], oj = P.item_j[it];
+    const double2* vi = reinterpret_cast<const double2*>(Vrec + (size_t)oi * kVRec);
+    const double2* vj = reinterpret_cast<const double2*>(Vrec + (size_t)oj * kVRec);
+    double Vi[18], Vj[18];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) { const double2 u = vi[k]; Vi[2 * k] = u.x; Vi[2 * k + 1] = u.y; }
+#pragma unroll
+    for (int k = 0; k < 9; ++k) { const double2 u = vj[k]; Vj[2 * k] = u.x; Vj[2 * k + 1] = u.y; }
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+      for (int j = 0; j < 6; ++j)
+        acc[6 * i + j] += Vi[3 * i] * Vj[3 * j] + Vi[3 * i + 1] * Vj[3 * j + 1] + Vi[3 * i + 2] * Vj[3 * j + 2];
+    if (oi == oj) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) { const double2 u = vi[9 + k]; cacc[2 * k] += u.x; cacc[2 * k + 1] += u.y; }
+    }
+  }
+#pragma unroll
+  for (int m = 1; m < 32; m <<= 1) {
+#pragma unroll
+    for (int k = 0; k < 36; ++k) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], m);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) cacc[k] += __shfl_xor_sync(0xffffffffu, cacc[k], m);
+  }
+  if (lane != 0) return;
+  const int ld = P.nf_dim;
+  const int ta[2] = {P.pose_q_tan[a] < 0 ? -1 : P.pose_q_tan[a] - P.ne_dim, P.pose_t_tan[a] < 0 ? -1 : P.pose_t_tan[a] - P.ne_dim};
+  const int tb[2] = {P.pose_q_tan[b] < 0 ? -1 : P.pose_q_tan[b] - P.ne_dim, P.pose_t_tan[b] < 0 ? -1 : P.pose_t_tan[b] - P.ne_dim};
+  double blk[36];
+  if (a == b) {
+    const double* H = pose_H + (size_t)a * 21;
+    int k = 0;
+    for (int i = 0; i < 6; ++i) for (int j = i; j < 6; ++j) { const double h = H[k++]; blk[6 * i + j] = h - acc[6 * i + j]; if (j != i) blk[6 * j + i] = h - acc[6 * j + i]; }
+    for (int s = 0; s < 2; ++s) if (ta[s] >= 0) for (int k2 = 0; k2 < 3; ++k2) rhs[ta[s] + k2] = grad[P.ne_dim + ta[s] + k2] - cacc[3 * s + k2];
+  } else {
+    for (int k = 0; k < 36; ++k) blk[k] = -acc[k];
+  }
+  for (int sa = 0; sa < 2; ++sa)
+    for (int sb = 0; sb < 2; ++sb) {
+      if (ta[sa] < 0 || tb[sb] < 0) continue;
+      if (a == b && sa > sb) continue;             // (t,q) duplicates (q,t)^T
+      double B[9];
+      for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) B[3 * i + j] = blk[6 * (3 * sa + i) + 3 * sb + j];
+      store_sub3(S, ld, ta[sa], tb[sb], B);
+    }
+}
+
+// K6c: generic-factor contributions to S (3x3 destinations, row >= col) and to rhs. 9 threads per destination.
+__global__ void __launch_bounds__(144) gf_schur_kernel(DeviceProblem P, const double* __restrict__ gfJ,
+                                                       double* __restrict__ S, const LMState* st) {
+  if (!gate_run(st)) return;
+  const int d = blockIdx.x * 16 + threadIdx.x / 9, e = threadIdx.x % 9;
+  if (d >= P.num_gdest) return;
+  const int i = e / 3, j = e % 3;
+  double acc = 0.0;
+  for (int it = P.gd_ptr[d]; it < P.gd_ptr[d + 1]; ++it) {
+    const int f = P.gd_fac[it], bi = P.gd_bi[it], bj = P.gd_bj[it];
+    const int nr = P.gf_nres[f], ncol = 3 * P.gf_nblk[f];
+    const double* J = gfJ + P.gf_joff[f];
+    for (int r = 0; r < nr; ++r) acc += J[r * ncol + 3 * bi + i] * J[r * ncol + 3 * bj + j];
+  }
+  const int rt = 3 * P.gd_row[d] + i, ct = 3 * P.gd_col[d] + j;
+  if (rt >= ct) S[(size_t)ct * P.nf_dim + rt] += acc;
+}
+// rhs of f-blocks that are not camera poses, then D_f^2 on the diagonal.
+__global__ void __launch_bounds__(256) finish_system_kernel(DeviceProblem P, const double* __restrict__ grad,
+                                                            const double* __restrict__ colsq, const double* __restrict__ scale,
+                                                            const unsigned char* __restrict__ is_pose_entry, double* __restrict__ S,
+                                                            double* __restrict__ rhs, Options opt, const LMState* st) {
+  if (!gate_run(st)) return;
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j >= P.nf_dim) return;
+  const double s = scale[P.ne_dim + j];
+  const double d = fmin(fmax(colsq[P.ne_dim + j] * s * s, opt.min_lm_diagonal), opt.max_lm_diagonal) / (st->radius * s * s);
+  S[(size_t)j * P.nf_dim + j] += d;
+  if (!is_pose_entry[j]) rhs[j] = grad[P.ne_dim + j];
+}
+
+// ===================================================================================================
+// K8: dense FP64 Cholesky of the reduced system (column-major, lower), blocked right-looking, NB = 32.
+// chol_panel: every CTA factors the 32x32 diagonal block redundantly in shared memory (deterministic), CTA 0
+// writes it back, each CTA then solves its 64 rows of the panel. chol_update: trailing update with DMMA
+// (mma.sync.m8n8k4.f64), 64x64 tiles, operands staged in shared memory.
+// ===================================================================================================
+constexpr int kNB = 32;
+__global__ void __launch_bounds__(64) chol_panel_kernel(double* __restrict__ S, int n, int j0, LMState* st) {
+  __shared__ double D[kNB][kNB + 1];
+  __shared__ int go;
+  const int nb = min(kNB, n - j0), tid = threadIdx.x;
+  if (tid == 0) go = gate_run(st) && !st->lin_fail;   // one read per CTA: lin_fail may be set by a sibling CTA
+  __syncthreads();
+  if (!go) return;
+  for (int e = tid; e < kNB * kNB; e += 64) {
+    const int r = e % kNB, c = e / kNB;
+    D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(j0 + c) * n + j0 + r] : 0.0;
+  }
+  __syncthreads();
+  if (tid < 32) {
+    for (int k = 0; k < nb; ++k) {
+      if (tid == k) { const double d = D[k][k]; if (!(d > 0.0)) { st->lin_fail = 1; } D[k][k] = sqrt(d); }
+      __syncwarp();
+      const double dk = D[k][k];
+      if (tid > k && tid < nb) D[tid][k] /= dk;
+      __syncwarp();
+      if (tid > k && tid < nb) { const double lik = D[tid][k]; for (int j = k + 1; j <= tid; ++j) D[tid][j] -= lik * D[j][k]; }
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+  if (blockIdx.x == 0)
+    for (int e = tid; e < kNB * kNB; e += 64) { const int r = e % kNB, c = e / kNB; if (r < nb && c < nb && r >= c) S[(size_t)(j0 + c) * n + j0 + r] = D[r][c]; }
+  const int row = j0 + nb + blockIdx.x * 64 + tid;
+  if (row >= n) return;
+  double xv[kNB];
+#pragma unroll
+  for (int c = 0; c < kNB; ++c) {
+    if (c < nb) {
+      double a = S[(size_t)(j0 + c) * n + row];
+#pragma unroll
+      for (int p = 0; p < kNB; ++p) if (p < c) a -= xv[p] * D[c][p];
+      xv[c] = a / D[c][c];
+      S[(size_t)(j0 + c) * n + row] = xv[c];
+    } else xv[c] = 0.0;
+  }
+}
+__device__ __forceinline__ void dmma_m8n8k4(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+__global__ void __launch_bounds__(128) chol_update_kernel(double* __restrict__ S, int n, int j0, const LMState* st) {
+  if (!gate_run(st) || st->lin_fail) return;
+  const int base = j0 + kNB;            // first trailing row / column
+  const int ti = blockIdx.y, tj = blockIdx.x;
+  if (ti < tj) return;
+  constexpr int LD = kNB + 4;
+  __shared__ double As[64 * LD];
+  __shared__ double Bs[64 * LD];
+  const int i0 = base + ti * 64, c0 = base + tj * 64, tid = threadIdx.x;
+  for (int e = tid; e < 64 * kNB; e += 128) {
+    const int r = e % 64, p = e / 64;
+    As[r * LD + p] = (i0 + r < n) ? S[(size_t)(j0 + p) * n + i0 + r] : 0.0;
+    Bs[r * LD + p] = (c0 + r < n) ? S[(size_t)(j0 + p) * n + c0 + r] : 0.0;
+  }
+  __syncthreads();
+  const int warp = tid >> 5, lane = tid & 31, gr = lane >> 2, gc = lane & 3;
+  // warp w owns row band [16w, 16w+16) x all 64 columns = 2 x 8 subtiles of 8x8
+  double acc[2][8][2];
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int b = 0; b < 8; ++b) { acc[a][b][0] = 0.0; acc[a][b][1] = 0.0; }
+#pragma unroll
+  for (int k0 = 0; k0 < kNB; k0 += 4) {
+    double af[2], bf[8];
+#pragma unroll
+    for (int a = 0; a < 2; ++a) af[a] = As[(16 * warp + 8 * a + gr) * LD + k0 + gc];
+#pragma unroll
+    for (int b = 0; b < 8; ++b) bf[b] = Bs[(8 * b + gr) * LD + k0 + gc];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int b = 0; b < 8; ++b) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+  }
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int b = 0; b < 8; ++b)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int row = i0 + 16 * warp + 8 * a + gr, col = c0 + 8 * b + 2 * gc + h;
+        if (row < n && col < n && row >= col) S[(size_t)col * n + row] -= acc[a][b][h];
+      }
+}
+// Triangular solves L y = b, L^T x = y with the factor in the lower triangle of S (single CTA, blocked by 32).
+__global__ void __launch_bounds__(1024) chol_solve_kernel(const double* __restrict__ S, int n, const double* __restrict__ rhs,
+                                                          double* __restrict__ y, LMState* st) {
+  if (!gate_run(st) || st->lin_fail) return;
+  __shared__ double D[kNB][kNB + 1];
+  __shared__ double xs[kNB];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < n; i += 1024) y[i] = rhs[i];
+  __syncthreads();
+  for (int jb = 0; jb < n; jb += kNB) {  // forward
+    const int nb = min(kNB, n - jb);
+    { const int r = tid % kNB, c = tid / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(jb + c) * n + jb + r] : 0.0; }
+    __syncthreads();
+    if (tid < 32) {
+      double b = tid < nb ? y[jb + tid] : 0.0;
+      for (int k = 0; k < nb; ++k) {
+        const double yk = __shfl_sync(0xffffffffu, b, k) / D[k][k];
+        if (tid == k) b = yk; else if (tid > k) b -= D[tid][k] * yk;
+      }
+      if (tid < nb) { y[jb + tid] = b; xs[tid] = b; }
+    }
+    __syncthreads();
+    for (int i = jb + nb + tid; i < n; i += 1024) {
+      double a = y[i];
+      for (int k = 0; k < nb; ++k) a -= S[(size_t)(jb + k) * n + i] * xs[k];
+      y[i] = a;
+    }
+    __syncthreads();
+  }
+  const int nblk = (n + kNB - 1) / kNB;
+  for (int bb = nblk - 1; bb >= 0; --bb) {  // backward
+    const int jb = bb * kNB, nb = min(kNB, n - jb);
+    { const int r = tid % kNB, c = tid / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(jb + c) * n + jb + r] : 0.0; }
+    __syncthreads();
+    if (tid < 32) {
+      double b = tid < nb ? y[jb + tid] : 0.0;
+      for (int k = nb - 1; k >= 0; --k) {
+        const double xk = __shfl_sync(0xffffffffu, b, k) / D[k][k];
+        if (tid == k) b = xk; else if (tid < k) b -= D[k][tid] * xk;
+      }
+      if (tid < nb) { y[jb + tid] = b; xs[tid] = b; }
+    }
+    __syncthreads();
+    for (int i = tid; i < jb; i += 1024) {
+      double a = y[i];
+      const double* col = S + (size_t)i * n + jb;
+      for (int k = 0; k < nb; ++k) a -= col[k] * xs[k];
+      y[i] = a;
+    }
+    __syncthreads();
+  }
+}
+
+// ===================================================================================================
+// K5c: back-substitution of the landmark steps and the model cost change
+//   y_e = Minv (g_e - sum E^T F y_f);  model_cost_change = sum_rows m (r - m/2), m = F y_f + E y_e  (delta = -y)
+// ===================================================================================================
+template <int G>
+__global__ void __launch_bounds__(256) backsub_kernel(DeviceProblem P, const double* __restrict__ Jrec,
+                                                      const double* __restrict__ lm_minv, const double* __restrict__ grad,
+                                                      const double* __restrict__ yf, double* __restrict__ y,
+                                                      double* __restrict__ model_part, const LMState* st) {
+  if (!gate_run(st) || st->lin_fail) return;
+  __shared__ double sm[256];
+  const int gtid = blockIdx.x * 256 + threadIdx.x;
+  const int l = gtid / G, sub = gtid % G;
+  const bool valid = l < P.ne;
+  const int start = valid ? P.lm_ptr[l] : 0, end = valid ? P.lm_ptr[l + 1] : 0;
+  double t0 = 0, t1 = 0, t2 = 0;
+  for (int o = start + sub; o < end; o += G) {
+    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)o * kJRec);
+    const int pose = P.obs_pose[o];
+    const int tq = P.pose_q_tan[pose], tt = P.pose_t_tan[pose];
+    double yp[6];
+    for (int k = 0; k < 3; ++k) { yp[k] = tq >= 0 ? yf[tq - P.ne_dim + k] : 0.0; yp[3 + k] = tt >= 0 ? yf[tt - P.ne_dim + k] : 0.0; }
+    const double2 f0 = rec[4], f1 = rec[5], f2 = rec[6], f3 = rec[7], f4 = rec[8], f5 = rec[9];
+    const double u0 = f0.x * yp[0] + f0.y * yp[1] + f1.x * yp[2] + f1.y * yp[3] + f2.x * yp[4] + f2.y * yp[5];
+    const double u1 = f3.x * yp[0] + f3.y * yp[1] + f4.x * yp[2] + f4.y * yp[3] + f5.x * yp[4] + f5.y * yp[5];
+    const double2 e0 = rec[0], e1 = rec[1], e2 = rec[2];
+    t0 += e0.x * u0 + e1.y * u1; t1 += e0.y * u0 + e2.x * u1; t2 += e1.x * u0 + e2.y * u1;
+  }
+#pragma unroll
+  for (int m = 1; m < G; m <<= 1) {
+    t0 += __shfl_xor_sync(0xffffffffu, t0, m); t1 += __shfl_xor_sync(0xffffffffu, t1, m); t2 += __shfl_xor_sync(0xffffffffu, t2, m);
+  }
+  double ye0 = 0, ye1 = 0, ye2 = 0;
+  if (valid) {
+    const double* mi = lm_minv + (size_t)l * 6;
+    const double b0 = grad[3 * l] - t0, b1 = grad[3 * l + 1] - t1, b2 = grad[3 * l + 2] - t2;
+    ye0 = mi[0] * b0 + mi[1] * b1 + mi[2] * b2; ye1 = mi[1] * b0 + mi[3] * b1 + mi[4] * b2; ye2 = mi[2] * b0 + mi[4] * b1 + mi[5] * b2;
+    if (sub == 0) { y[3 * l] = ye0; y[3 * l + 1] = ye1; y[3 * l + 2] = ye2; }
+  }
+  double mc = 0.0;
+  for (int o = start + sub; o < end; o += G) {
+    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)o * kJRec);
+    const int pose = P.obs_pose[o];
+    const int tq = P.pose_q_tan[pose], tt = P.pose_t_tan[pose];
+    double yp[6];
+    for (int k = 0; k < 3; ++k) { yp[k] = tq >= 0 ? yf[tq - P.ne_dim + k] : 0.0; yp[3 + k] = tt >= 0 ? yf[tt - P.ne_dim + k] : 0.0; }
+    const double2 f0 = rec[4], f1 = rec[5], f2 = rec[6], f3 = rec[7], f4 = rec[8], f5 = rec[9];
+    const double2 e0 = rec[0], e1 = rec[1], e2 = rec[2], r = rec[3];
+    const double m0 = f0.x * yp[0] + f0.y * yp[1] + f1.x * yp[2] + f1.y * yp[3] + f2.x * yp[4] + f2.y * yp[5] + e0.x * ye0 + e0.y * ye1 + e1.x * ye2;
+    const double m1 = f3.x * yp[0] + f3.y * yp[1] + f4.x * yp[2] + f4.y * yp[3] + f5.x * yp[4] + f5.y * yp[5] + e1.y * ye0 + e2.x * ye1 + e2.y * ye2;
+    mc += m0 * (r.x - 0.5 * m0) + m1 * (r.y - 0.5 * m1);
+  }
+  const double tot = block_sum<256>(mc, sm);
+  if (threadIdx.x == 0) model_part[blockIdx.x] = tot;
+}
+// model cost change of the generic factors + copy y_f into the full step vector. One thread per factor.
+__global__ void __launch_bounds__(128) gf_model_kernel(DeviceProblem P, const double* __restrict__ gfJ,
+                                                       const double* __restrict__ gfR, const double* __restrict__ yf,
+                                                       double* __restrict__ y, double* __restrict__ model_part, const LMState* st) {
+  if (!gate_run(st) || st->lin_fail) return;
+  const int tid = blockIdx.x * 128 + threadIdx.x;
+  for (int j = tid; j < P.nf_dim; j += gridDim.x * 128) y[P.ne_dim + j] = yf[j];
+  if (tid >= P.num_gf) return;
+  const int f = tid, nb = P.gf_nblk[f], nr = P.gf_nres[f], ncol = 3 * nb;
+  const double* J = gfJ + P.gf_joff[f]; const double* R = gfR + P.gf_roff[f];
+  double yl[3 * kGfMaxBlocks];
+  for (int b = 0; b < nb; ++b) {
+    const int t = P.blk_tan[P.gf_blocks[f * kGfMaxBlocks + b]];
+    for (int k = 0; k < 3; ++k) yl[3 * b + k] = t >= 0 ? yf[t - P.ne_dim + k] : 0.0;
+  }
+  double mc = 0.0;
+  for (int i = 0; i < nr; ++i) {
+    double m = 0.0;
+    for (int c = 0; c < ncol; ++c) m += J[i * ncol + c] * yl[c];
+    mc += m * (R[i] - 0.5 * m);
+  }
+  model_part[f] = mc;
+}
+
+// candidate point x_cand = x (+) (-y) and the ambient norms ParameterToleranceReached needs.
+__global__ void __launch_bounds__(256) candidate_kernel(DeviceProblem P, const double* __restrict__ x,
+                                                        const double* __restrict__ y, double* __restrict__ xc,
+                                                        double* __restrict__ part_step, double* __restrict__ part_cand,
+                                                        const LMState* st) {
+  if (!gate_run(st) || st->lin_fail) return;
+  __shared__ double sm[256];
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  double ss = 0.0, cs = 0.0;
+  if (i < P.num_active) {
+    const int b = P.active_blocks[i], off = P.blk_off[b], t = P.blk_tan[b];
+    if (P.blk_manifold[b] == BSNLS_MANIFOLD_QUATERNION) {
+      const double d[3] = {-y[t], -y[t + 1], -y[t + 2]};
+      double out[4]; quat_plus(x + off, d, out);
+      for (int k = 0; k < 4; ++k) { xc[off + k] = out[k]; const double dd = x[off + k] - out[k]; ss += dd * dd; cs += out[k] * out[k]; }
+    } else {
+      for (int k = 0; k < P.blk_size[b]; ++k) { const double v = x[off + k] + (-y[t + k]); xc[off + k] = v; const double dd = x[off + k] - v; ss += dd * dd; cs += v * v; }
+    }
+  }
+  const double a = block_sum<256>(ss, sm); __syncthreads();
+  const double c = block_sum<256>(cs, sm);
+  if (threadIdx.x == 0) { part_step[blockIdx.x] = a; part_cand[blockIdx.x] = c; }
+}
+__global__ void __launch_bounds__(256) xnorm_kernel(DeviceProblem P, const double* __restrict__ x, double* __restrict__ part) {
+  __shared__ double sm[256];
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  double s = 0.0;
+  if (i < P.num_active) { const int b = P.active_blocks[i], off = P.blk_off[b]; for (int k = 0; k < P.blk_size[b]; ++k) s += x[off + k] * x[off + k]; }
+  const double a = block_sum<256>(s, sm);
+  if (threadIdx.x == 0) part[blockIdx.x] = a;
+}
+
+// Deterministic final reductions: one CTA walks a list of (array, length, op) descriptors.
+struct RedDesc { const double* src; int n; int op; int slot; };  // op 0 = sum, 1 = max
+struct RedList { RedDesc d[6]; int count; int gate; };           // gate 0 always, 1 run, 2 jac
+__global__ void __launch_bounds__(256) reduce_kernel(RedList L, double* __restrict__ red, const LMState* st) {
+  if (L.gate == 1 && !gate_run(st)) return;
+  if (L.gate == 2 && !gate_jac(st)) return;
+  __shared__ double sm[256];
+  for (int q = 0; q < L.count; ++q) {
+    const RedDesc d = L.d[q];
+    double v = 0.0;
+    for (int i = threadIdx.x; i < d.n; i += 256) v = d.op ? fmax(v, d.src[i]) : v + d.src[i];
+    const double t = d.op ? block_max<256>(v, sm) : block_sum<256>(v, sm);
+    if (threadIdx.x == 0) red[d.slot] = (q > 0 && L.d[q - 1].slot == d.slot) ? red[d.slot] + t : t;
+    __syncthreads();
+  }
+}
+
+// ===================================================================================================
+// K9: device-side LM controller (ceres TrustRegionMinimizer + LevenbergMarquardtStrategy).
+// ===================================================================================================
+__device__ __forceinline__ void push_record(LMState* st, bsnls_iteration* recs, const bsnls_iteration& r) {
+  if (st->num_records < st->max_records) recs[st->num_records] = r;
+  st->num_records++;
+}
+// FinalizeIterationAndCheckIfMinimizerCanContinue after a record was pushed
+__device__ __forceinline__ void finalize_checks(LMState* st, const bsnls_iteration& r, const Options& opt) {
+  if (r.step_is_successful) st->num_successful++;
+  if (r.iteration >= opt.max_num_iterations) { st->done = 1; st->termination = BSNLS_NO_CONVERGENCE; st->message_id = MSG_MAX_ITER; return; }
+  if (r.step_is_successful && r.gradient_max_norm <= opt.gradient_tolerance) { st->done = 1; st->termination = BSNLS_CONVERGENCE; st->message_id = MSG_GRAD_TOL; return; }
+  if (st->radius < opt.min_radius) { st->done = 1; st->termination = BSNLS_CONVERGENCE; st->message_id = MSG_MIN_RADIUS; return; }
+}
+// after a Jacobian evaluation: IterationZero, or the tail of HandleSuccessfulStep
+__global__ void ctrl_after_jacobian_kernel(LMState* st, const double* red, bsnls_iteration* recs, Options opt) {
+  if (!gate_jac(st)) return;
+  st->x_cost = red[RED_COST]; st->fixed_cost = red[RED_FIXED]; st->accepted = 0;
+  st->grad_max = red[RED_GRAD_MAX]; st->grad_norm = sqrt(red[RED_GRAD_SQ]);
+  bsnls_iteration r;
+  r.iteration = st->iteration; r.step_is_valid = 1; r.step_is_successful = 1;
+  r.linear_solver_iterations = st->iteration == 0 ? 0 : st->pend_linear_iters;
+  r.cost = st->x_cost + st->fixed_cost;
+  r.cost_change = st->iteration == 0 ? 0.0 : st->pend_cost_change;
+  r.gradient_max_norm = st->grad_max; r.gradient_norm = st->grad_norm;
+  r.step_norm = st->iteration == 0 ? 0.0 : st->pend_step_norm;
+  r.relative_decrease = st->iteration == 0 ? 0.0 : st->pend_relative_decrease;
+  r.trust_region_radius = st->radius;
+  if (st->iteration == 0) st->x_norm = sqrt(red[RED_X_SQ]);
+  st->need_jacobian = 0; st->scale_ready = 1;
+  if (!isfinite(st->x_cost)) { st->done = 1; st->termination = BSNLS_FAILURE; st->message_id = MSG_NONFINITE; push_record(st, recs, r); return; }
+  push_record(st, recs, r);
+  finalize_checks(st, r, opt);
+}
+// end of an iteration: step validity, tolerances, acceptance, trust-region update
+__global__ void ctrl_end_iteration_kernel(LMState* st, const double* red, bsnls_iteration* recs, Options opt) {
+  if (!gate_run(st)) return;
+  st->iteration += 1;
+  bsnls_iteration r;
+  r.iteration = st->iteration; r.step_is_valid = 0; r.step_is_successful = 0; r.linear_solver_iterations = st->pcg_iters;
+  r.cost = st->x_cost + st->fixed_cost; r.cost_change = 0.0; r.gradient_max_norm = st->grad_max; r.gradient_norm = st->grad_norm;
+  r.step_norm = 0.0; r.relative_decrease = 0.0;
+  const double mc = red[RED_MODEL];
+  const bool solved = !st->lin_fail && isfinite(mc) && isfinite(red[RED_STEP_SQ]);
+  st->lin_fail = 0;
+  if (!solved || !(mc > 0.0)) {  // HandleInvalidStep
+    st->num_invalid += 1;
+    if (st->num_invalid >= opt.max_invalid) { st->done = 1; st->termination = BSNLS_FAILURE; st->message_id = MSG_INVALID_STEPS; return; }
+    st->radius = st->radius / st->decrease_factor; st->decrease_factor *= 2.0;
+    st->num_unsuccessful++;
+    r.trust_region_radius = st->radius;
+    push_record(st, recs, r); finalize_checks(st, r, opt);
+    return;
+  }
+  st->num_invalid = 0;
+  r.step_is_valid = 1;
+  st->model_cost_change = mc;
+  st->step_norm = sqrt(red[RED_STEP_SQ]); st->cand_norm = sqrt(red[RED_CAND_SQ]); st->cand_cost = red[RED_CAND_COST];
+  r.step_norm = st->step_norm;
+  // ParameterToleranceReached
+  if (st->step_norm <= opt.parameter_tolerance * (st->x_norm + opt.parameter_tolerance)) {
+    st->done = 1; st->termination = BSNLS_CONVERGENCE; st->message_id = MSG_PARAM_TOL; return; }
+  // FunctionToleranceReached
+  r.cost_change = st->x_cost - st->cand_cost;
+  if (fabs(r.cost_change) <= opt.function_tolerance * st->x_cost) {
+    st->done = 1; st->termination = BSNLS_CONVERGENCE; st->message_id = MSG_FUNC_TOL; return; }
+  r.relative_decrease = (st->x_cost - st->cand_cost) / mc;
+  if (r.relative_decrease > opt.min_relative_decrease) {  // HandleSuccessfulStep (completed by ctrl_after_jacobian)
+    st->accepted = 1; st->need_jacobian = 1;
+    st->x_norm = st->cand_norm;
+    st->pend_cost_change = r.cost_change; st->pend_step_norm = r.step_norm; st->pend_relative_decrease = r.relative_decrease;
+    st->pend_linear_iters = st->pcg_iters;
+    const double q = 2.0 * r.relative_decrease - 1.0;
+    st->radius = st->radius / fmax(1.0 / 3.0, 1.0 - q * q * q);
+    st->radius = fmin(opt.max_radius, st->radius);
+    st->decrease_factor = 2.0;
+  } else {  // HandleUnsuccessfulStep
+    st->radius = st->radius / st->decrease_factor; st->decrease_factor *= 2.0;
+    st->num_unsuccessful++;
+    r.cost = st->cand_cost + st->fixed_cost; r.trust_region_radius = st->radius;
+    push_record(st, recs, r); finalize_checks(st, r, opt);
+  }
+}
+__global__ void __launch_bounds__(256) apply_step_kernel(double* __restrict__ x, const double* __restrict__ xc, int n, LMState* st) {
+  if (!st->accepted) return;
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i < n) x[i] = xc[i];
+}
+__global__ void clear_accepted_kernel(LMState* st) { st->accepted = 0; }
+__global__ void set_done_kernel(LMState* st, int termination, int msg) { if (!st->done) { st->done = 1; st->termination = termination; st->message_id = msg; } }
+
+}  // namespace bsnls

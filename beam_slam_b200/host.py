@@ -1,0 +1,151 @@
+"""ctypes plumbing over lib/libbsfuse.so: the C++ host mirror of the fuse graph interface (host/), its
+createProblem-order flattener and the synthetic-graph generator. `HashGraph.optimize` is the drop-in call
+(GpuHashGraph::optimize, host/gpu_hash_graph.cpp) and runs on the GPU only."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import cabi
+
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libbsfuse.so")
+_lib = None
+
+
+def load_library():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run __graft_entry__.build()")
+    lib = C.CDLL(LIB_PATH)
+    G = C.c_void_p
+    lib.bsfuse_graph_new.restype = G
+    lib.bsfuse_graph_free.argtypes = [G]
+    lib.bsfuse_last_error.argtypes = [G]
+    lib.bsfuse_last_error.restype = C.c_char_p
+    lib.bsfuse_build_synthetic.argtypes = [G, C.c_int, C.c_double, C.c_uint64, C.POINTER(C.c_longlong)]
+    lib.bsfuse_synthetic_options.argtypes = [C.c_int, C.POINTER(cabi.Options)]
+    lib.bsfuse_flatten.argtypes = [G]
+    lib.bsfuse_flatten.restype = C.POINTER(cabi.Problem)
+    lib.bsfuse_num_values.argtypes = [G]
+    lib.bsfuse_num_values.restype = C.c_longlong
+    lib.bsfuse_block_uuid.argtypes = [G, C.c_int, C.c_char_p]
+    lib.bsfuse_truth_values.argtypes = [G, C.POINTER(C.c_double)]
+    lib.bsfuse_current_values.argtypes = [G, C.POINTER(C.c_double)]
+    lib.bsfuse_set_values.argtypes = [G, C.POINTER(C.c_double)]
+    lib.bsfuse_optimize.argtypes = [G, C.POINTER(cabi.Options), C.POINTER(cabi.Summary), C.POINTER(cabi.Iteration), C.c_int]
+    lib.bsfuse_evaluate.argtypes = [G, C.POINTER(C.c_double)]
+    lib.bsfuse_uuid_name.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t, C.c_char_p]
+    lib.bsfuse_uuid_stamped.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_char_p]
+    lib.bsfuse_uuid_landmark.argtypes = [C.c_char_p, C.c_uint64, C.c_char_p]
+    lib.bsfuse_uuid_hash.argtypes = [C.c_char_p]
+    lib.bsfuse_uuid_hash.restype = C.c_uint64
+    lib.bsfuse_selftest_containers.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+def _np(ptr, n, dtype):
+    if n == 0:
+        return np.zeros(0, dtype)
+    return np.ctypeslib.as_array(ptr, shape=(n,)).astype(dtype, copy=True)
+
+
+def problem_to_numpy(cp):
+    """Copy a C bsnls_problem (owned by C++) into a numpy-backed cabi.FlatProblem."""
+    nb = cp.num_blocks
+    size = _np(cp.block_size, nb, np.int32)
+    nv = int(size.sum())
+    groups = {}
+    for gi in range(cp.num_groups):
+        g = cp.groups[gi]
+        t, n = g.type, g.count
+        groups[t] = dict(blocks=_np(g.blocks, n * cabi.FACTOR_NBLOCKS[t], np.int32),
+                         consts=_np(g.consts, n * cabi.FACTOR_STRIDE[t], np.float64),
+                         aux=_np(g.aux, n, np.int32) if g.aux else None,
+                         loss_type=_np(g.loss_type, n, np.int32) if g.loss_type else None,
+                         loss_param=_np(g.loss_param, n, np.float64) if g.loss_param else None,
+                         res_index=_np(g.res_index, n, np.int32))
+    return cabi.FlatProblem(size, _np(cp.block_manifold, nb, np.int32), _np(cp.block_constant, nb, np.uint8),
+                            _np(cp.block_group, nb, np.int32), _np(cp.block_values, nv, np.float64),
+                            _np(cp.cameras, cp.num_cameras * cabi.CAMERA_STRIDE, np.float64), groups)
+
+
+class HashGraph:
+    """Python face of bsfuse::GpuHashGraph (mirrors fuse_graphs::HashGraph's optimize/evaluate)."""
+
+    INFO = ("num_keyframes", "num_landmarks", "num_observations", "num_imu", "num_relative_pose", "num_priors",
+            "num_variables", "num_constraints")
+
+    def __init__(self):
+        self._lib = load_library()
+        self._g = self._lib.bsfuse_graph_new()
+        self.info = {}
+
+    def __del__(self):
+        if getattr(self, "_g", None):
+            self._lib.bsfuse_graph_free(self._g)
+            self._g = None
+
+    @classmethod
+    def synthetic(cls, config, scale=1.0, seed=0):
+        g = cls()
+        out = (C.c_longlong * 8)()
+        if g._lib.bsfuse_build_synthetic(g._g, config, scale, seed, out) != 0:
+            raise ValueError(g._lib.bsfuse_last_error(g._g).decode())
+        g.info = dict(zip(cls.INFO, [int(v) for v in out]))
+        g.config = config
+        return g
+
+    @staticmethod
+    def synthetic_options(config):
+        o = cabi.Options()
+        load_library().bsfuse_synthetic_options(config, C.byref(o))
+        return o
+
+    def flatten(self):
+        cp = self._lib.bsfuse_flatten(self._g)
+        if not cp:
+            raise ValueError(self._lib.bsfuse_last_error(self._g).decode())
+        return problem_to_numpy(cp.contents)
+
+    def block_uuids(self, n):
+        out = []
+        buf = C.create_string_buffer(16)
+        for i in range(n):
+            self._lib.bsfuse_block_uuid(self._g, i, buf)
+            out.append(buf.raw)
+        return out
+
+    def truth_values(self):
+        v = np.zeros(self._lib.bsfuse_num_values(self._g))
+        self._lib.bsfuse_truth_values(self._g, v.ctypes.data_as(C.POINTER(C.c_double)))
+        return v
+
+    def current_values(self):
+        v = np.zeros(self._lib.bsfuse_num_values(self._g))
+        self._lib.bsfuse_current_values(self._g, v.ctypes.data_as(C.POINTER(C.c_double)))
+        return v
+
+    def set_values(self, values):
+        v = np.ascontiguousarray(values, np.float64)
+        self._lib.bsfuse_set_values(self._g, v.ctypes.data_as(C.POINTER(C.c_double)))
+
+    def optimize(self, options=None, max_iters=256):
+        """GpuHashGraph::optimize: flatten in createProblem order, solve on the GPU, write variables back."""
+        options = options or cabi.Options.defaults()
+        s = cabi.Summary()
+        its = (cabi.Iteration * max_iters)()
+        rc = self._lib.bsfuse_optimize(self._g, C.byref(options), C.byref(s), its, max_iters)
+        if rc == -1:
+            raise ValueError(self._lib.bsfuse_last_error(self._g).decode())
+        if rc != 0:
+            raise RuntimeError(self._lib.bsfuse_last_error(self._g).decode())
+        return s, [its[i] for i in range(min(s.num_iterations, max_iters))]
+
+    def evaluate(self):
+        c = C.c_double()
+        if self._lib.bsfuse_evaluate(self._g, C.byref(c)) != 0:
+            raise RuntimeError(self._lib.bsfuse_last_error(self._g).decode())
+        return c.value

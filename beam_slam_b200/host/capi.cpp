@@ -1,0 +1,146 @@
+// C interface over the host-side mirror, for the ctypes plumbing in beam_slam_b200/host.py.
+#include <cstring>
+#include <memory>
+
+#include "gpu_hash_graph.h"
+#include "synthetic.h"
+
+using namespace bsfuse;
+
+struct bsfuse_graph {
+  GpuHashGraph graph;
+  FlatProblem flat;
+  std::vector<std::pair<UUID, std::vector<double>>> truth;
+  SolverSummary last;
+  std::string error;
+};
+
+extern "C" {
+
+bsfuse_graph* bsfuse_graph_new() { return new bsfuse_graph(); }
+void bsfuse_graph_free(bsfuse_graph* g) { delete g; }
+const char* bsfuse_last_error(bsfuse_graph* g) { return g->error.c_str(); }
+
+int bsfuse_build_synthetic(bsfuse_graph* g, int config, double scale, uint64_t seed, long long info_out[8]) {
+  try {
+    g->truth.clear();
+    const SyntheticInfo i = BuildSynthetic(config, scale, seed, &g->graph, &g->truth);
+    const long long v[8] = {i.num_keyframes, i.num_landmarks, i.num_observations, i.num_imu, i.num_relative_pose,
+                            i.num_priors, i.num_variables, i.num_constraints};
+    std::memcpy(info_out, v, sizeof(v));
+    return 0;
+  } catch (const std::exception& e) { g->error = e.what(); return -1; }
+}
+void bsfuse_synthetic_options(int config, bsnls_options* out) { ToCOptions(SyntheticSolverOptions(config), out); }
+
+// createProblem-order flattening; the returned struct and its arrays stay valid until the next flatten/free.
+const bsnls_problem* bsfuse_flatten(bsfuse_graph* g) {
+  try { Flatten(g->graph, &g->flat); return &g->flat.c; }
+  catch (const std::exception& e) { g->error = e.what(); return nullptr; }
+}
+long long bsfuse_num_values(bsfuse_graph* g) { return static_cast<long long>(g->flat.block_values.size()); }
+void bsfuse_block_uuid(bsfuse_graph* g, int block, unsigned char out[16]) { std::memcpy(out, g->flat.block_uuid[block].data.data(), 16); }
+// ground truth in the flattened block order (NaN where unknown)
+void bsfuse_truth_values(bsfuse_graph* g, double* out) {
+  std::unordered_map<UUID, const std::vector<double>*, UuidHash> m;
+  for (const auto& kv : g->truth) m[kv.first] = &kv.second;
+  for (size_t b = 0; b < g->flat.block_uuid.size(); ++b) {
+    auto it = m.find(g->flat.block_uuid[b]);
+    for (int k = 0; k < g->flat.block_size[b]; ++k)
+      out[g->flat.block_offset[b] + k] = it == m.end() ? std::nan("") : (*it->second)[k];
+  }
+}
+// current Variable::data() in the flattened block order
+void bsfuse_current_values(bsfuse_graph* g, double* out) {
+  for (size_t b = 0; b < g->flat.block_variable.size(); ++b)
+    std::memcpy(out + g->flat.block_offset[b], g->flat.block_variable[b]->data(), sizeof(double) * g->flat.block_size[b]);
+}
+void bsfuse_set_values(bsfuse_graph* g, const double* values) { g->flat.ScatterValues(values); }
+
+// GpuHashGraph::optimize through the public interface; fills the C summary for python.
+int bsfuse_optimize(bsfuse_graph* g, const bsnls_options* o, bsnls_summary* s, bsnls_iteration* its, int max_its) {
+  try {
+    SolverOptions so;
+    so.max_num_iterations = o->max_num_iterations; so.max_solver_time_in_seconds = o->max_solver_time_in_seconds;
+    so.function_tolerance = o->function_tolerance; so.gradient_tolerance = o->gradient_tolerance;
+    so.parameter_tolerance = o->parameter_tolerance; so.initial_trust_region_radius = o->initial_trust_region_radius;
+    so.max_trust_region_radius = o->max_trust_region_radius; so.min_trust_region_radius = o->min_trust_region_radius;
+    so.min_relative_decrease = o->min_relative_decrease; so.min_lm_diagonal = o->min_lm_diagonal;
+    so.max_lm_diagonal = o->max_lm_diagonal; so.max_num_consecutive_invalid_steps = o->max_num_consecutive_invalid_steps;
+    so.jacobi_scaling = o->jacobi_scaling != 0; so.linear_solver = o->linear_solver;
+    g->last = g->graph.optimize(so);
+    const SolverSummary& r = g->last;
+    std::memset(s, 0, sizeof(*s));
+    s->termination_type = r.termination_type; s->num_iterations = static_cast<int>(r.iterations.size());
+    s->num_successful_steps = r.num_successful_steps; s->num_unsuccessful_steps = r.num_unsuccessful_steps;
+    s->initial_cost = r.initial_cost; s->final_cost = r.final_cost; s->fixed_cost = r.fixed_cost;
+    s->total_time_in_seconds = r.total_time_in_seconds; s->device_time_in_seconds = r.device_time_in_seconds;
+    s->num_e_blocks = r.num_e_blocks; s->num_f_blocks = r.num_f_blocks; s->reduced_system_dim = r.reduced_system_dim;
+    s->linear_solver_used = r.linear_solver_used; s->reduced_system_nnz_blocks = r.reduced_system_nnz_blocks;
+    std::snprintf(s->message, sizeof(s->message), "%s", r.message.c_str());
+    for (int i = 0; i < s->num_iterations && i < max_its && its; ++i) {
+      const IterationSummary& a = r.iterations[i];
+      its[i] = bsnls_iteration{a.iteration, a.step_is_valid, a.step_is_successful, a.linear_solver_iterations, a.cost,
+                               a.cost_change, a.gradient_max_norm, a.gradient_norm, a.step_norm, a.relative_decrease,
+                               a.trust_region_radius};
+    }
+    // keep g->flat in step with the graph the solve used
+    g->flat = g->graph.lastProblem(); g->flat.Finalize();
+    return 0;
+  } catch (const std::invalid_argument& e) { g->error = e.what(); return -1; }
+  catch (const std::exception& e) { g->error = e.what(); return -3; }
+}
+int bsfuse_evaluate(bsfuse_graph* g, double* cost) {
+  try { return g->graph.evaluate(cost, nullptr, nullptr) ? 0 : -3; }
+  catch (const std::exception& e) { g->error = e.what(); return -3; }
+}
+
+// ---- host-logic probes for the CPU tests ----
+void bsfuse_uuid_name(const unsigned char ns[16], const void* data, size_t n, unsigned char out[16]) {
+  UUID u; std::memcpy(u.data.data(), ns, 16);
+  const UUID r = uuid::name_uuid(u, data, n);
+  std::memcpy(out, r.data.data(), 16);
+}
+void bsfuse_uuid_stamped(const char* type, uint32_t sec, uint32_t nsec, unsigned char out[16]) {
+  const UUID r = uuid::generate(type, sec, nsec, uuid::nil());
+  std::memcpy(out, r.data.data(), 16);
+}
+void bsfuse_uuid_landmark(const char* type, uint64_t id, unsigned char out[16]) {
+  const UUID r = uuid::generate(type, id);
+  std::memcpy(out, r.data.data(), 16);
+}
+uint64_t bsfuse_uuid_hash(const unsigned char in[16]) { UUID u; std::memcpy(u.data.data(), in, 16); return UuidHash()(u); }
+
+// Container semantics of fuse_graphs::HashGraph (hash_graph.cpp:100-301): returns 0 when every check holds,
+// else the number of the failed check.
+int bsfuse_selftest_containers() {
+  GpuHashGraph g;
+  auto q = variables::Orientation3DStamped(Time(1, 0)); auto p = variables::Position3DStamped(Time(1, 0));
+  auto lm = variables::Point3DLandmark(7);
+  if (!g.addVariable(q) || !g.addVariable(p)) return 1;
+  const double T[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1}, K[9] = {100, 0, 50, 0, 100, 50, 0, 0, 1}, px[2] = {50, 50};
+  auto c = constraints::EuclideanReprojection("t", *q, *p, *lm, T, K, px, 1.0);
+  try { g.addConstraint(c); return 2; } catch (const std::logic_error&) {}       // unknown variable
+  g.addVariable(lm);
+  if (!g.addConstraint(c)) return 3;
+  if (g.addConstraint(c)) return 4;                                               // duplicate
+  try { g.removeVariable(lm->uuid()); return 5; } catch (const std::logic_error&) {}  // still in use
+  try { g.getVariable(variables::Point3DLandmark(8)->uuid()); return 6; } catch (const std::out_of_range&) {}
+  try { g.getConstraint(NextConstraintUuid()); return 7; } catch (const std::out_of_range&) {}
+  if (g.getConnectedConstraints(lm->uuid()).size() != 1) return 8;
+  g.holdVariable(p->uuid());
+  if (!g.isVariableOnHold(p->uuid())) return 9;
+  FlatProblem f; Flatten(g, &f);
+  int held = 0; for (auto cst : f.block_constant) held += cst;
+  if (held != 1 || f.c.num_blocks != 3 || f.cgroups.size() != 1) return 10;
+  if (!g.removeConstraint(c->uuid()) || !g.removeVariable(lm->uuid())) return 11;
+  SolverOptions bad; bad.max_num_iterations = -1;
+  try { g.optimize(bad); return 12; } catch (const std::invalid_argument&) {}
+  auto unknown = std::make_shared<Constraint>(NextConstraintUuid(), "fuse_constraints::AbsolutePose2DStampedConstraint", "t",
+                                              std::vector<UUID>{p->uuid()}, std::vector<double>{});
+  g.addConstraint(unknown);
+  try { Flatten(g, &f); return 13; } catch (const std::invalid_argument&) {}
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,119 @@
+#include "flatten.h"
+
+#include <cstring>
+#include <map>
+
+namespace bsfuse {
+
+namespace {
+struct TypeInfo { int type; int nblocks; int stride; };
+const std::unordered_map<std::string, TypeInfo>& TypeTable() {
+  static const std::unordered_map<std::string, TypeInfo> t = {
+      {"bs_constraints::EuclideanReprojectionConstraint", {BSNLS_FACTOR_REPROJECTION, 3, BSNLS_REPROJECTION_STRIDE}},
+      {"bs_constraints::RelativeImuState3DStampedConstraint", {BSNLS_FACTOR_IMU_DELTA, 10, BSNLS_IMU_DELTA_STRIDE}},
+      {"bs_constraints::AbsoluteImuState3DStampedConstraint", {BSNLS_FACTOR_IMU_PRIOR, 5, BSNLS_IMU_PRIOR_STRIDE}},
+      {"fuse_constraints::RelativePose3DStampedConstraint", {BSNLS_FACTOR_RELATIVE_POSE, 4, BSNLS_POSE_STRIDE}},
+      {"bs_constraints::RelativePose3DStampedWithExtrinsicsConstraint", {BSNLS_FACTOR_RELATIVE_POSE_EXTRINSICS, 6, BSNLS_POSE_STRIDE}},
+      {"fuse_constraints::AbsolutePose3DStampedConstraint", {BSNLS_FACTOR_ABSOLUTE_POSE, 2, BSNLS_POSE_STRIDE}},
+      {"fuse_constraints::RelativeOrientation3DStampedConstraint", {BSNLS_FACTOR_RELATIVE_ORIENTATION, 2, BSNLS_ORIENTATION_STRIDE}},
+      {"bs_constraints::AbsoluteConstraint3D", {BSNLS_FACTOR_ABSOLUTE_VEC3, 1, BSNLS_VEC3_STRIDE}},
+      {"bs_constraints::RelativeConstraint3D", {BSNLS_FACTOR_RELATIVE_VEC3, 2, BSNLS_VEC3_STRIDE}},
+  };
+  return t;
+}
+}  // namespace
+
+void FlatProblem::Finalize() {
+  cgroups.clear();
+  for (auto& g : groups) {
+    if (g.res_index.empty()) continue;
+    bsnls_factor_group cg{};
+    cg.type = g.type; cg.count = static_cast<int32_t>(g.res_index.size());
+    cg.blocks = g.blocks.data(); cg.consts = g.consts.data();
+    cg.aux = g.aux.empty() ? nullptr : g.aux.data();
+    cg.loss_type = g.loss_type.empty() ? nullptr : g.loss_type.data();
+    cg.loss_param = g.loss_param.empty() ? nullptr : g.loss_param.data();
+    cg.res_index = g.res_index.data();
+    cgroups.push_back(cg);
+  }
+  c.num_blocks = static_cast<int32_t>(block_size.size());
+  c.block_size = block_size.data(); c.block_manifold = block_manifold.data();
+  c.block_constant = block_constant.data(); c.block_group = block_group.data();
+  c.block_values = block_values.data();
+  c.num_cameras = static_cast<int32_t>(cameras.size() / BSNLS_CAMERA_STRIDE);
+  c.cameras = cameras.data();
+  c.num_groups = static_cast<int32_t>(cgroups.size());
+  c.groups = cgroups.data();
+}
+
+void FlatProblem::ScatterValues(const double* values) const {
+  for (size_t b = 0; b < block_variable.size(); ++b)
+    std::memcpy(block_variable[b]->data(), values + block_offset[b], sizeof(double) * block_size[b]);
+}
+
+void Flatten(const HashGraph& graph, FlatProblem* out) {
+  FlatProblem& P = *out;
+  P = FlatProblem();
+  const auto& vars = graph.getVariables();
+  std::unordered_map<UUID, int32_t, UuidHash> index;
+  index.reserve(vars.size() * 2);
+  P.block_size.reserve(vars.size());
+  int64_t off = 0;
+  // createProblem, first loop (hash_graph.cpp:478-504)
+  for (const auto& kv : vars) {
+    Variable& v = *kv.second;
+    for (size_t i = 0; i < v.size(); ++i)
+      if (v.lowerBound(i) > std::numeric_limits<double>::lowest() || v.upperBound(i) < std::numeric_limits<double>::max())
+        throw std::invalid_argument("bounded variables are not supported by the GPU path: " + v.type());
+    index.emplace(kv.first, static_cast<int32_t>(P.block_size.size()));
+    P.block_size.push_back(static_cast<int32_t>(v.size()));
+    P.block_manifold.push_back(v.manifold() == Variable::kQuaternion ? BSNLS_MANIFOLD_QUATERNION : BSNLS_MANIFOLD_EUCLIDEAN);
+    P.block_constant.push_back((v.holdConstant() || graph.isVariableOnHold(kv.first)) ? 1 : 0);
+    // elimination groups: landmarks first (explicit two-group ordering)
+    const bool landmark = v.type() == "bs_variables::Point3DLandmark" || v.type() == "bs_variables::InverseDepthLandmark";
+    P.block_group.push_back(landmark ? 0 : 1);
+    P.block_offset.push_back(off);
+    P.block_variable.push_back(&v);
+    P.block_uuid.push_back(kv.first);
+    for (size_t i = 0; i < v.size(); ++i) P.block_values.push_back(v.data()[i]);
+    off += static_cast<int64_t>(v.size());
+  }
+  P.groups.assign(BSNLS_NUM_FACTOR_TYPES, FlatProblem::Group());
+  for (int t = 0; t < BSNLS_NUM_FACTOR_TYPES; ++t) P.groups[t].type = t;
+  std::map<std::vector<double>, int32_t> camera_index;
+  int32_t res_index = 0;
+  // createProblem, second loop (hash_graph.cpp:506-521)
+  for (const auto& kv : graph.getConstraints()) {
+    const Constraint& c = *kv.second;
+    auto ti = TypeTable().find(c.type());
+    if (ti == TypeTable().end()) throw std::invalid_argument("constraint type not supported by the GPU path: " + c.type());
+    const TypeInfo& info = ti->second;
+    FlatProblem::Group& g = P.groups[info.type];
+    if (static_cast<int>(c.variables().size()) != info.nblocks)
+      throw std::invalid_argument("unexpected variable count for " + c.type());
+    for (const UUID& u : c.variables()) g.blocks.push_back(index.at(u));  // variables_.at(uuid), :515
+    const int lt = c.loss() ? static_cast<int>(c.loss()->type) : BSNLS_LOSS_NONE;
+    const double la = c.loss() ? c.loss()->a : 0.0;
+    const auto& pl = c.payload();
+    if (info.type == BSNLS_FACTOR_REPROJECTION) {
+      g.consts.push_back(pl[0]); g.consts.push_back(pl[1]);
+      std::vector<double> cam(pl.begin() + 2, pl.begin() + 19);  // K(4), T(12), w
+      cam.push_back(static_cast<double>(lt)); cam.push_back(la); cam.push_back(0.0);
+      auto it = camera_index.find(cam);
+      if (it == camera_index.end()) {
+        it = camera_index.emplace(cam, static_cast<int32_t>(P.cameras.size() / BSNLS_CAMERA_STRIDE)).first;
+        P.cameras.insert(P.cameras.end(), cam.begin(), cam.end());
+      }
+      g.aux.push_back(it->second);
+    } else {
+      const size_t n0 = g.consts.size();
+      g.consts.resize(n0 + info.stride, 0.0);
+      std::memcpy(g.consts.data() + n0, pl.data(), sizeof(double) * std::min<size_t>(pl.size(), info.stride));
+      g.loss_type.push_back(lt); g.loss_param.push_back(la);
+    }
+    g.res_index.push_back(res_index++);
+  }
+  P.Finalize();
+}
+
+}  // namespace bsfuse

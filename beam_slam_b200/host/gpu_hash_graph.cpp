@@ -1,0 +1,107 @@
+#include "gpu_hash_graph.h"
+
+#include <chrono>
+
+namespace bsfuse {
+
+void ToCOptions(const SolverOptions& o, bsnls_options* c) {
+  bsnls_default_options(c);
+  c->max_num_iterations = o.max_num_iterations;
+  c->max_solver_time_in_seconds = o.max_solver_time_in_seconds;
+  c->function_tolerance = o.function_tolerance; c->gradient_tolerance = o.gradient_tolerance;
+  c->parameter_tolerance = o.parameter_tolerance;
+  c->initial_trust_region_radius = o.initial_trust_region_radius;
+  c->max_trust_region_radius = o.max_trust_region_radius; c->min_trust_region_radius = o.min_trust_region_radius;
+  c->min_relative_decrease = o.min_relative_decrease;
+  c->min_lm_diagonal = o.min_lm_diagonal; c->max_lm_diagonal = o.max_lm_diagonal;
+  c->max_num_consecutive_invalid_steps = o.max_num_consecutive_invalid_steps;
+  c->jacobi_scaling = o.jacobi_scaling ? 1 : 0;
+  c->linear_solver = o.linear_solver;
+}
+
+GpuHashGraph::GpuHashGraph() = default;
+GpuHashGraph::~GpuHashGraph() { if (handle_) bsnls_destroy(handle_); }
+
+void GpuHashGraph::EnsureHandle(const SolverOptions& options) const {
+  bsnls_options c; ToCOptions(options, &c);
+  if (!handle_) {
+    if (bsnls_create(&c, &handle_) != BSNLS_OK) {
+      const char* e = bsnls_last_error(nullptr);
+      throw std::runtime_error(std::string("bsnls_create failed: ") + (e ? e : "?"));
+    }
+  } else if (bsnls_set_options(handle_, &c) != BSNLS_OK) {
+    throw std::invalid_argument(bsnls_last_error(handle_));
+  }
+}
+
+SolverSummary GpuHashGraph::optimize(const SolverOptions& options) {
+  const auto t0 = std::chrono::steady_clock::now();
+  std::string err;
+  if (!options.IsValid(&err)) throw std::invalid_argument("Invalid solver options: " + err);
+  Flatten(*this, &flat_);  // createProblem
+  SolverSummary s;
+  if (flat_.cgroups.empty() || flat_.block_size.empty()) {  // empty problem: Ceres converges at once
+    s.termination_type = SolverSummary::CONVERGENCE; s.message = "Function tolerance reached. No non-constant parameter blocks found.";
+    return s;
+  }
+  EnsureHandle(options);
+  bsnls_summary cs{};
+  std::vector<bsnls_iteration> its(static_cast<size_t>(options.max_num_iterations) + 2);
+  int rc = bsnls_set_problem(handle_, &flat_.c);
+  if (rc == BSNLS_OK) rc = bsnls_solve(handle_, &cs, its.data(), static_cast<int32_t>(its.size()));
+  if (rc != BSNLS_OK) {
+    s.termination_type = SolverSummary::FAILURE;
+    s.message = std::string("bsnls: ") + bsnls_last_error(handle_);
+    return s;  // variables untouched; caller sees !IsSolutionUsable() (fixed_lag_smoother.cpp:286)
+  }
+  s.termination_type = static_cast<SolverSummary::TerminationType>(cs.termination_type);
+  s.message = cs.message;
+  s.initial_cost = cs.initial_cost; s.final_cost = cs.final_cost; s.fixed_cost = cs.fixed_cost;
+  s.device_time_in_seconds = cs.device_time_in_seconds;
+  s.num_successful_steps = cs.num_successful_steps; s.num_unsuccessful_steps = cs.num_unsuccessful_steps;
+  s.num_e_blocks = cs.num_e_blocks; s.num_f_blocks = cs.num_f_blocks; s.reduced_system_dim = cs.reduced_system_dim;
+  s.linear_solver_used = cs.linear_solver_used; s.reduced_system_nnz_blocks = cs.reduced_system_nnz_blocks;
+  for (int i = 0; i < cs.num_iterations && i < static_cast<int>(its.size()); ++i) {
+    IterationSummary it;
+    it.iteration = its[i].iteration; it.step_is_valid = its[i].step_is_valid; it.step_is_successful = its[i].step_is_successful;
+    it.linear_solver_iterations = its[i].linear_solver_iterations;
+    it.cost = its[i].cost; it.cost_change = its[i].cost_change; it.gradient_max_norm = its[i].gradient_max_norm;
+    it.gradient_norm = its[i].gradient_norm; it.step_norm = its[i].step_norm;
+    it.relative_decrease = its[i].relative_decrease; it.trust_region_radius = its[i].trust_region_radius;
+    s.iterations.push_back(it);
+  }
+  if (s.IsSolutionUsable()) {
+    if (bsnls_get_values(handle_, flat_.block_values.data()) != BSNLS_OK) {
+      s.termination_type = SolverSummary::FAILURE; s.message = std::string("bsnls: ") + bsnls_last_error(handle_);
+      return s;
+    }
+    flat_.ScatterValues(flat_.block_values.data());  // Ceres' in-place update of Variable::data()
+  }
+  s.total_time_in_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  return s;
+}
+
+SolverSummary GpuHashGraph::optimizeFor(double max_time_s, const SolverOptions& options) {
+  // The reference subtracts the createProblem time from the budget (hash_graph.cpp:433-439); flattening happens
+  // inside optimize(), so the whole budget is handed down and the device loop checks its own clock.
+  SolverOptions o = options;
+  o.max_solver_time_in_seconds = std::max(0.0, max_time_s);
+  return optimize(o);
+}
+
+bool GpuHashGraph::evaluate(double* cost, std::vector<double>* residuals, std::vector<double>* gradient) const {
+  Flatten(*this, &flat_);
+  if (flat_.cgroups.empty()) { if (cost) *cost = 0.0; if (residuals) residuals->clear(); if (gradient) gradient->clear(); return true; }
+  EnsureHandle(SolverOptions());
+  if (bsnls_set_problem(handle_, &flat_.c) != BSNLS_OK) return false;
+  int64_t nr = 0, ng = 0;
+  if (bsnls_evaluate(handle_, cost, nullptr, &nr, nullptr, &ng) != BSNLS_OK) return false;
+  if (residuals) residuals->assign(nr, 0.0);
+  if (gradient) gradient->assign(ng, 0.0);
+  if (residuals || gradient)
+    return bsnls_evaluate(handle_, cost, residuals ? residuals->data() : nullptr, &nr,
+                          gradient ? gradient->data() : nullptr, &ng) == BSNLS_OK;
+  return true;
+}
+
+}  // namespace bsfuse

@@ -1,0 +1,123 @@
+"""Thin object wrapper over the C-ABI (include/bsnls.h). Every method is one C call; errors raise with the
+library's message. There is no fallback: without libbsnls.so or without a CUDA device these calls fail."""
+import ctypes as C
+
+import numpy as np
+
+from . import cabi
+
+_pf64 = C.POINTER(C.c_double)
+_pi32 = C.POINTER(C.c_int32)
+
+
+class BsnlsError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"bsnls error {code}: {message}")
+        self.code = code
+
+
+class Solver:
+    def __init__(self, options=None, sharded=None):
+        """sharded = (rank, world_size, nccl_id bytes) for the landmark-sharded multi-GPU solve."""
+        self._lib = cabi.load_library()
+        self._h = C.c_void_p()
+        self.options = options or cabi.Options.defaults()
+        if sharded is None:
+            rc = self._lib.bsnls_create(C.byref(self.options), C.byref(self._h))
+        else:
+            rank, world, nccl_id = sharded
+            buf = (C.c_char * 128).from_buffer_copy(nccl_id)
+            rc = self._lib.bsnls_create_sharded(C.byref(self.options), rank, world, buf, C.byref(self._h))
+        if rc != 0:
+            msg = self._lib.bsnls_last_error(None)
+            raise BsnlsError(rc, msg.decode() if msg else "?")
+        self.problem = None
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.bsnls_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def _check(self, rc):
+        if rc != 0:
+            raise BsnlsError(rc, self._lib.bsnls_last_error(self._h).decode())
+
+    def set_options(self, options):
+        self.options = options
+        self._check(self._lib.bsnls_set_options(self._h, C.byref(options)))
+
+    def set_problem(self, problem):
+        self.problem = problem
+        self._check(self._lib.bsnls_set_problem(self._h, C.byref(problem.c)))
+
+    def set_values(self, values):
+        v = np.ascontiguousarray(values, np.float64)
+        assert v.size == self.problem.num_values
+        self._check(self._lib.bsnls_set_values(self._h, v.ctypes.data_as(_pf64)))
+
+    def get_values(self, out=None):
+        v = out if out is not None else np.zeros(self.problem.num_values)
+        self._check(self._lib.bsnls_get_values(self._h, v.ctypes.data_as(_pf64)))
+        return v
+
+    def solve(self, max_iters=None):
+        n = (max_iters or self.options.max_num_iterations) + 2
+        s = cabi.Summary()
+        its = (cabi.Iteration * n)()
+        self._check(self._lib.bsnls_solve(self._h, C.byref(s), its, n))
+        return s, [its[i] for i in range(min(s.num_iterations, n))]
+
+    def evaluate(self):
+        cost = C.c_double()
+        nr, ng = C.c_int64(), C.c_int64()
+        self._check(self._lib.bsnls_evaluate(self._h, C.byref(cost), None, C.byref(nr), None, C.byref(ng)))
+        res, grad = np.zeros(nr.value), np.zeros(ng.value)
+        self._check(self._lib.bsnls_evaluate(self._h, C.byref(cost), res.ctypes.data_as(_pf64), C.byref(nr),
+                                             grad.ctypes.data_as(_pf64), C.byref(ng)))
+        return cost.value, res, grad
+
+    def ordering(self):
+        nb = len(self.problem.block_size)
+        e, f = np.zeros(nb, np.int32), np.zeros(nb, np.int32)
+        ne, nf = C.c_int32(), C.c_int32()
+        self._check(self._lib.bsnls_get_ordering(self._h, e.ctypes.data_as(_pi32), C.byref(ne), f.ctypes.data_as(_pi32), C.byref(nf)))
+        return e[:ne.value].copy(), f[:nf.value].copy()
+
+    def reduced_pattern(self):
+        n = C.c_int64(0)
+        self._check(self._lib.bsnls_get_reduced_pattern(self._h, None, None, C.byref(n)))
+        r, c = np.zeros(n.value, np.int32), np.zeros(n.value, np.int32)
+        self._check(self._lib.bsnls_get_reduced_pattern(self._h, r.ctypes.data_as(_pi32), c.ctypes.data_as(_pi32), C.byref(n)))
+        return r, c
+
+    def reduced_system(self, radius):
+        _, f = self.ordering()
+        dim = 3 * len(f)
+        S, rhs = np.zeros((dim, dim)), np.zeros(dim)
+        self._check(self._lib.bsnls_get_reduced_system(self._h, radius, S.ctypes.data_as(_pf64), rhs.ctypes.data_as(_pf64), dim))
+        return S, rhs  # S is symmetric, so the column-major buffer reads the same row-major
+
+    def run_eval(self):
+        c = C.c_double()
+        self._check(self._lib.bsnls_run_eval(self._h, C.byref(c)))
+        return c.value
+
+    def run_schur(self, radius=1e4):
+        self._check(self._lib.bsnls_run_schur(self._h, radius))
+
+    def last_kernel_ms(self):
+        a, b = C.c_float(), C.c_float()
+        self._check(self._lib.bsnls_last_kernel_ms(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    BREAKDOWN = ("eval_reproj", "eval_generic", "landmark", "gradient", "clear_S", "pair", "generic_rows")
+
+    def last_breakdown_ms(self):
+        out = (C.c_float * 8)()
+        self._check(self._lib.bsnls_last_breakdown_ms(self._h, out))
+        return dict(zip(self.BREAKDOWN, [float(v) for v in out]))
+
+    def launch_count(self):
+        return int(self._lib.bsnls_launch_count(self._h))

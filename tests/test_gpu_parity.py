@@ -1,0 +1,190 @@
+"""GPU parity proper: the CUDA path, called through the C-ABI, against the CPU oracle on the same seeded graphs.
+Tolerances: ordering / sparsity pattern bit-exact; residuals 1e-13 relative; reduced system 1e-9 relative;
+per-iteration cost, step norm and final cost 1e-9 relative (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+
+import oracle_lib as orc
+from beam_slam_b200 import cabi, host
+from beam_slam_b200.builder import ProblemBuilder
+from beam_slam_b200.solver import BsnlsError, Solver
+
+pytestmark = pytest.mark.gpu
+
+CASES = [(1, 1.0), (2, 0.25), (3, 0.02)]
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+@pytest.fixture(scope="module", params=CASES, ids=lambda c: f"C{c[0]}x{c[1]}")
+def case(request):
+    cfg, scale = request.param
+    g = host.HashGraph.synthetic(cfg, scale=scale)
+    return cfg, g, g.flatten(), host.HashGraph.synthetic_options(cfg)
+
+
+def test_ordering_and_sparsity_pattern_bit_exact(case):
+    cfg, g, p, opts = case
+    s = Solver(opts)
+    s.set_problem(p)
+    e, f = s.ordering()
+    eo, fo = orc.ordering(p)
+    assert np.array_equal(e, eo) and np.array_equal(f, fo)
+    # pattern of the reduced system in 3x3 blocks == nonzero blocks of the oracle's dense S
+    S, _ = orc.reduced_system(p, 1e4, opts)
+    nf = len(f)
+    blk = np.abs(S.reshape(nf, 3, nf, 3)).max(axis=(1, 3)) > 0
+    ro, co = np.nonzero(np.tril(blk))
+    r, c = s.reduced_pattern()
+    assert np.array_equal(np.stack([r, c]), np.stack([ro, co]))
+
+
+def test_evaluate_matches_oracle(case):
+    cfg, g, p, opts = case
+    s = Solver(opts)
+    s.set_problem(p)
+    cost, res, grad = s.evaluate()
+    co, ro, go = orc.evaluate(p)
+    assert res.shape == ro.shape and grad.shape == go.shape
+    assert abs(cost - co) <= 1e-12 * co
+    assert _rel(res, ro) < 1e-13
+    assert _rel(grad, go) < 1e-10
+
+
+def test_reduced_system_matches_oracle(case):
+    cfg, g, p, opts = case
+    s = Solver(opts)
+    s.set_problem(p)
+    for radius in (1e4, 3.0):
+        S, rhs = s.reduced_system(radius)
+        So, rhso = orc.reduced_system(p, radius, opts)
+        assert _rel(S, So) < 1e-9
+        assert _rel(rhs, rhso) < 1e-9
+
+
+def test_solve_matches_oracle_per_iteration(case):
+    cfg, g, p, opts = case
+    s = Solver(opts)
+    s.set_problem(p)
+    summ, its = s.solve()
+    so, ito, xo = orc.solve(p, opts)
+    assert summ.termination_type == so.termination_type, (summ.message, so.message)
+    assert summ.message == so.message
+    assert len(its) == len(ito)
+    for a, b in zip(its, ito):
+        assert a.iteration == b.iteration and a.step_is_successful == b.step_is_successful
+        assert abs(a.cost - b.cost) <= 1e-9 * abs(b.cost)
+        assert abs(a.step_norm - b.step_norm) <= 1e-9 * max(abs(b.step_norm), 1e-12)
+        assert abs(a.trust_region_radius - b.trust_region_radius) <= 1e-9 * b.trust_region_radius
+    assert abs(summ.final_cost - so.final_cost) <= 1e-9 * so.final_cost
+    assert abs(summ.initial_cost - so.initial_cost) <= 1e-12 * so.initial_cost
+    x = s.get_values()
+    assert _rel(x, xo) < 1e-7
+    assert summ.num_e_blocks == so.num_e_blocks and summ.reduced_system_dim == so.reduced_system_dim
+
+
+def test_dropin_hash_graph_optimize_updates_variables_in_place():
+    g = host.HashGraph.synthetic(1, scale=0.5)
+    p = g.flatten()
+    opts = host.HashGraph.synthetic_options(1)
+    so, ito, xo = orc.solve(p, opts)
+    before = g.current_values()
+    summ, its = g.optimize(opts)
+    after = g.current_values()
+    assert summ.is_solution_usable()
+    assert not np.array_equal(before, after)
+    assert _rel(after, xo) < 1e-7
+    assert abs(summ.final_cost - so.final_cost) <= 1e-9 * so.final_cost
+    assert abs(g.evaluate() - so.final_cost) <= 1e-9 * so.final_cost
+
+
+def test_relative_pose_known_answer_no_landmarks():
+    """test_relative_pose_3d_stamped_constraint.cpp:124-232 on the GPU: pure pose graph (no e-blocks)."""
+    b = ProblemBuilder()
+    o1 = b.add_quaternion([0.952, 0.038, -0.189, 0.239]); p1 = b.add_block([1.5, -3.0, 10.0])
+    o2 = b.add_quaternion([0.944, -0.128, 0.145, -0.269]); p2 = b.add_block([-1.5, 3.0, -10.0])
+    I6 = np.eye(6).ravel()
+    b.add_factor(cabi.FACTOR_ABSOLUTE_POSE, [p1, o1], np.concatenate([[0, 0, 0, 1, 0, 0, 0], I6]))
+    b.add_factor(cabi.FACTOR_RELATIVE_POSE, [p1, o1, p2, o2], np.concatenate([[1, 0, 0, 1, 0, 0, 0], I6]))
+    p = b.build()
+    s = Solver()
+    s.set_problem(p)
+    summ, its = s.solve()
+    x = s.get_values()
+    assert summ.is_solution_usable()
+    assert np.abs(x[4:7]).max() < 1e-5 and np.abs(x[11:14] - [1, 0, 0]).max() < 1e-5
+    assert np.abs(x[0:4] - [1, 0, 0, 0]).max() < 1e-3 and np.abs(x[7:11] - [1, 0, 0, 0]).max() < 1e-3
+    so, ito, xo = orc.solve(p)
+    assert len(its) == len(ito)
+    for a, c in zip(its, ito):
+        assert abs(a.cost - c.cost) <= 1e-9 * max(abs(c.cost), 1e-30) + 1e-25
+
+
+def test_imu_prior_known_answer_and_constant_blocks():
+    """absolute_imu_state_3d_stamped_constraint_test.cpp:85-298 on the GPU + a held block (hash_graph.cpp:500-503)."""
+    import test_oracle_golden as tg
+    cov = tg._cov15()
+    mean = np.array([1.0, 0, 0, 0, 1, 2, 3, 1, 2, 3, 0.1, 0.2, 0.3, 0.1, 0.2, 0.3])
+    A = np.linalg.cholesky(np.linalg.inv(cov)).T
+    for hold in (False, True):
+        b = ProblemBuilder()
+        ids = [b.add_quaternion([0.952, 0.038, -0.189, 0.239]), b.add_block([1.5, -3.0, 10.0]),
+               b.add_block([1.5, -3.0, 10.0], constant=hold), b.add_block([0.15, -0.30, 1.0]), b.add_block([0.15, -0.30, 1.0])]
+        b.add_factor(cabi.FACTOR_IMU_PRIOR, ids, np.concatenate([mean, A.ravel()]))
+        p = b.build()
+        s = Solver()
+        s.set_problem(p)
+        summ, its = s.solve()
+        x = s.get_values()
+        so, ito, xo = orc.solve(p)
+        assert summ.termination_type == so.termination_type
+        assert _rel(x, xo) < 1e-8
+        if not hold:
+            assert np.abs(x[:4] - mean[:4]).max() < 1e-3 and np.abs(x[4:] - mean[4:]).max() < 1e-5
+        else:
+            assert np.array_equal(x[7:10], [1.5, -3.0, 10.0])
+
+
+def test_unsupported_and_invalid_inputs_fail_loudly():
+    b = ProblemBuilder()
+    v = b.add_block([1.0, 2.0])  # 2-vector: not on this path
+    b.add_factor(cabi.FACTOR_ABSOLUTE_VEC3, [v], np.zeros(12))
+    s = Solver()
+    with pytest.raises(BsnlsError) as e:
+        s.set_problem(b.build())
+    assert e.value.code == cabi.ERR_UNSUPPORTED
+    with pytest.raises(BsnlsError) as e:
+        s.solve()
+    assert e.value.code == cabi.ERR_STATE
+    with pytest.raises(BsnlsError):
+        Solver(cabi.Options.defaults(min_trust_region_radius=-1.0))
+
+
+def test_failure_leaves_parameters_unchanged():
+    """On FAILURE the caller's IsSolutionUsable() is false and values stay put (fixed_lag_smoother.cpp:286)."""
+    b = ProblemBuilder()
+    v = b.add_block([1.0, 2.0, 3.0])
+    A = np.eye(3).ravel()
+    b.add_factor(cabi.FACTOR_ABSOLUTE_VEC3, [v], np.concatenate([[np.nan, 0.0, 0.0], A]))
+    p = b.build()
+    s = Solver()
+    s.set_problem(p)
+    summ, its = s.solve()
+    assert summ.termination_type == cabi.FAILURE and not summ.is_solution_usable()
+    assert np.array_equal(s.get_values(), [1.0, 2.0, 3.0])
+
+
+def test_run_to_run_determinism():
+    g = host.HashGraph.synthetic(2, scale=0.25)
+    p = g.flatten()
+    opts = host.HashGraph.synthetic_options(2)
+    out = []
+    for _ in range(2):
+        s = Solver(opts)
+        s.set_problem(p)
+        summ, its = s.solve()
+        out.append((s.get_values().tobytes(), [i.cost for i in its]))
+    assert out[0] == out[1]
