@@ -22,6 +22,7 @@ FACTOR_STRIDE = [2, 288, 241, 43, 43, 43, 13, 12, 12]
 FACTOR_BLOCK_SIZES = [[4, 3, 3], [4, 3, 3, 3, 3, 4, 3, 3, 3, 3], [4, 3, 3, 3, 3], [3, 4, 3, 4],
                       [3, 4, 3, 4, 3, 4], [3, 4], [4, 4], [3], [3, 3]]
 LOSS_NONE, LOSS_CAUCHY, LOSS_HUBER = 0, 1, 2
+NOALLOC_MAX_OBSERVATIONS = 4194304
 CAMERA_STRIDE = 20
 LINEAR_DENSE_SCHUR, LINEAR_ITERATIVE_SCHUR, LINEAR_AUTO = 0, 1, 2
 CONVERGENCE, NO_CONVERGENCE, FAILURE = 0, 1, 2
@@ -190,6 +191,8 @@ def load_library():
     lib.bsnls_last_breakdown_ms.restype = C.c_int
     lib.bsnls_launch_count.argtypes = [H]
     lib.bsnls_launch_count.restype = C.c_int64
+    lib.bsnls_reprojection_cost_noalloc.argtypes = [C.c_void_p] * 7 + [C.c_int32, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int32]
+    lib.bsnls_reprojection_cost_noalloc.restype = C.c_int
     lib.bsnls_nccl_unique_id.argtypes = [C.c_char * 128]
     lib.bsnls_create_sharded.argtypes = [C.POINTER(Options), C.c_int32, C.c_int32, C.c_char * 128, C.POINTER(H)]
     for name in ("bsnls_create", "bsnls_set_problem", "bsnls_set_values", "bsnls_set_options", "bsnls_solve",

@@ -229,6 +229,25 @@ int bsnls_last_breakdown_ms(bsnls_handle* handle, float out[8]);
 /* number of kernel launches issued by this handle since creation */
 int64_t bsnls_launch_count(const bsnls_handle* handle);
 
+/* ---- allocation-free entry point ----
+   No counterpart in the reference (Ceres allocates freely on the host). It exists for callers that may not
+   request device memory: real-time threads that cannot afford the device-wide synchronisation of
+   cudaMalloc/cudaFree, processes whose GPU memory is a fixed arena, code inside a stream capture.
+   Computes sum_i 0.5*rho(|r_i|^2) over `num_observations` reprojection observations (the solver's candidate-cost
+   evaluation). All pointers are DEVICE pointers owned by the caller: d_values = concatenated parameter blocks;
+   d_q_offset / d_t_offset / d_p_offset = per observation, offset into d_values of the orientation (4), position
+   (3) and landmark (3) block; d_camera_index into d_cameras (BSNLS_CAMERA_STRIDE doubles each); d_pixel 2 per
+   observation; d_cost one double. `stream` is a cudaStream_t (NULL = default stream); the call only enqueues.
+   Scratch is a fixed 128 KiB array inside the library, shared by all calls on a device (calls that overlap on the
+   GPU race), resident on every GPU that loads the library; its address is looked up on the first call per
+   device, which should precede any stream capture. More than BSNLS_NOALLOC_MAX_OBSERVATIONS observations are
+   refused (BSNLS_ERR_INVALID); error_message (optional, error_capacity bytes) receives the reason. */
+enum { BSNLS_NOALLOC_MAX_OBSERVATIONS = 4194304 };
+int bsnls_reprojection_cost_noalloc(const double* d_values, const int32_t* d_q_offset, const int32_t* d_t_offset,
+                                    const int32_t* d_p_offset, const int32_t* d_camera_index, const double* d_pixel,
+                                    const double* d_cameras, int32_t num_observations, double* d_cost, void* stream,
+                                    char* error_message, int32_t error_capacity);
+
 /* ---- multi-GPU: landmark-sharded solve, one process per GPU ---- */
 /* 128-byte NCCL unique id, generated on rank 0 and distributed by the caller (torch.distributed). */
 int bsnls_nccl_unique_id(char id[128]);
