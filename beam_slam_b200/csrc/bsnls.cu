@@ -61,6 +61,7 @@ struct bsnls_handle {
   std::vector<int> pose_q_blk, pose_t_blk;
   std::vector<int> pair_a, pair_b;
   std::vector<int> gd_row, gd_col;
+  bool sparse = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
   // residual-block bookkeeping for bsnls_evaluate (program order)
   struct ResRef { int type; int idx; int row; };   // idx: sorted-observation id or generic-factor id
   std::vector<ResRef> res_order; int64_t num_res_rows = 0;
@@ -74,7 +75,8 @@ struct bsnls_handle {
       d_pose_t_tan, d_pose_ptr, d_pose_obs, d_obs_pose, d_obs_lm, d_obs_cam, d_obs_pixel, d_lm_ptr, d_lm_off, d_cams,
       d_gf_type, d_gf_nblk, d_gf_nres, d_gf_blocks, d_gf_coff, d_gf_consts, d_gf_loss_type, d_gf_loss_a, d_gf_joff,
       d_gf_roff, d_pair_a, d_pair_b, d_pair_ptr, d_item_i, d_item_j, d_fg_ptr, d_fg_fac, d_fg_lb, d_gd_row, d_gd_col,
-      d_gd_ptr, d_gd_fac, d_gd_bi, d_gd_bj, d_is_pose;
+      d_gd_ptr, d_gd_fac, d_gd_bi, d_gd_bj, d_is_pose, d_bsr_rowptr, d_bsr_col, d_diag_slot, d_pair_slot, d_gd_slot,
+      d_pcg_x, d_pcg_r, d_pcg_z, d_pcg_p, d_pcg_Ap, d_pcg_Minv, d_pcg_part;
   DevMem d_x, d_xc, d_x0, d_Jrec, d_Vrec, d_minv, d_grad, d_colsq, d_scale, d_y, d_yf, d_rhs, d_S, d_poseH, d_gfJ,
       d_gfR, d_cost_part, d_cand_part, d_model_part, d_step_part, d_candsq_part, d_gsq_part, d_gmax_part, d_xsq_part,
       d_red, d_state, d_recs;
@@ -185,7 +187,7 @@ void EnqueueGradient(bsnls_handle* h, const Options& o) {  // phase C: gradient,
 void EnqueueAssemble(bsnls_handle* h, const Options& o) {  // phase D1: reduced system S, rhs
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
   MARK(h, 5);
-  cudaMemsetAsync(h->d_S.p, 0, sizeof(double) * (size_t)P.nf_dim * P.nf_dim, h->stream);
+  cudaMemsetAsync(h->d_S.p, 0, sizeof(double) * (h->sparse ? (size_t)h->nnzb * 9 : (size_t)P.nf_dim * P.nf_dim), h->stream);
   MARK(h, 6);
   if (h->npairs) LAUNCH(h, pair_kernel, BlocksFor(h->npairs, 4), 128, P, h->d_Vrec.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
   MARK(h, 7);
@@ -202,6 +204,15 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     if (rest > 0) { const int T = (rest + 63) / 64; LAUNCH(h, chol_update_kernel, dim3(T, T), 128, h->d_S.as<double>(), n, j0, st); }
   }
   LAUNCH(h, chol_solve_kernel, 1, 1024, h->d_S.as<double>(), n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
+}
+int EnqueueSparseSolve(bsnls_handle* h) {  // phase D2 (K7): cooperative PCG, result in yf
+  PcgBuffers B{h->d_yf.as<double>(), h->d_pcg_r.as<double>(), h->d_pcg_z.as<double>(), h->d_pcg_p.as<double>(), h->d_pcg_Ap.as<double>(),
+               h->d_pcg_Minv.as<double>(), h->d_pcg_part.as<double>(), h->opt.pcg_max_iterations, h->opt.pcg_tolerance};
+  DeviceProblem P = h->P; const double* S = h->d_S.as<double>(); const double* rhs = h->d_rhs.as<double>(); LMState* st = h->d_state.as<LMState>();
+  void* args[] = {&P, &S, &rhs, &B, &st};
+  cudaError_t e = cudaLaunchCooperativeKernel((void*)pcg_kernel, dim3(h->pcg_grid), dim3(256), args, 0, h->stream);
+  h->launches++;
+  return e == cudaSuccess ? BSNLS_OK : h->fail(BSNLS_ERR_CUDA, "cooperative launch of pcg_kernel: %s", cudaGetErrorString(e));
 }
 template <int G> void LaunchBacksub(bsnls_handle* h) {
   LAUNCH(h, backsub_kernel<G>, h->nb_lm, 256, h->P, h->d_Jrec.as<double>(), h->d_minv.as<double>(), h->d_grad.as<double>(), h->d_yf.as<double>(),
@@ -358,8 +369,8 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   h->blk_tan.assign(nb, -1);
   for (int b = 0; b < nb; ++b) { if (epos[b] >= 0) h->blk_tan[b] = 3 * epos[b]; else if (fpos[b] >= 0) h->blk_tan[b] = ne_dim + 3 * fpos[b]; }
   if (nf_dim == 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "no non-landmark parameter blocks to solve for");
-  const bool dense = true;  // round 1: dense reduced system
-  if (dense && nf_dim > 24000) return h->fail(BSNLS_ERR_UNSUPPORTED, "reduced system of dimension %d exceeds the dense solver limit", nf_dim);
+  h->sparse = h->opt.linear_solver == BSNLS_LINEAR_ITERATIVE_SCHUR || (h->opt.linear_solver == BSNLS_LINEAR_AUTO && nf_dim > 3000);
+  if (!h->sparse && nf_dim > 24000) return h->fail(BSNLS_ERR_UNSUPPORTED, "reduced system of dimension %d exceeds the dense solver limit", nf_dim);
 
   // ---- reprojection: poses, landmark-sorted observations ----
   std::vector<int> pose_of_q(nb, -1), pose_of_t(nb, -1);
@@ -508,6 +519,38 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     if (pose_q_tan[a] >= 0) for (int k = 0; k < 3; ++k) is_pose[pose_q_tan[a] - ne_dim + k] = 1;
     if (pose_t_tan[a] >= 0) for (int k = 0; k < 3; ++k) is_pose[pose_t_tan[a] - ne_dim + k] = 1;
   }
+  // ---- block-sparse pattern of the reduced system (3x3 blocks over f-blocks, full symmetric) ----
+  std::vector<int> diag_slot(h->nf, 0), pair_slot((size_t)h->npairs * 8, -1), gd_slot((size_t)h->ngdest * 2, -1);
+  h->bsr_rowptr.assign(h->nf + 1, 0); h->bsr_col.clear(); h->nnzb = 0;
+  {
+    std::vector<uint64_t> keys; keys.reserve((size_t)h->npairs * 8 + (size_t)h->ngdest * 2 + h->nf);
+    auto add = [&](int r, int c) { if (r >= 0 && c >= 0) { keys.push_back((uint64_t)r * h->nf + c); keys.push_back((uint64_t)c * h->nf + r); } };
+    auto fq = [&](int a) { return fpos[h->pose_q_blk[a]]; }; auto ft = [&](int a) { return fpos[h->pose_t_blk[a]]; };
+    for (int k = 0; k < h->nf; ++k) add(k, k);
+    for (int p2 = 0; p2 < h->npairs; ++p2) { const int a = h->pair_a[p2], b = h->pair_b[p2]; add(fq(a), fq(b)); add(fq(a), ft(b)); add(ft(a), fq(b)); add(ft(a), ft(b)); }
+    for (int d = 0; d < h->ngdest; ++d) add(h->gd_row[d], h->gd_col[d]);
+    std::sort(keys.begin(), keys.end()); keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
+    h->nnzb = (int64_t)keys.size();
+    if (h->nnzb * 9 > 0x7fffffffLL) return h->fail(BSNLS_ERR_UNSUPPORTED, "reduced system has too many blocks");
+    h->bsr_col.resize(keys.size());
+    for (size_t k = 0; k < keys.size(); ++k) { const int r = (int)(keys[k] / h->nf), c = (int)(keys[k] % h->nf); h->bsr_rowptr[r + 1]++; h->bsr_col[k] = c; }
+    for (int r = 0; r < h->nf; ++r) h->bsr_rowptr[r + 1] += h->bsr_rowptr[r];
+    auto slot = [&](int r, int c) -> int {
+      if (r < 0 || c < 0) return -1;
+      const int* b0 = h->bsr_col.data() + h->bsr_rowptr[r]; const int* b1 = h->bsr_col.data() + h->bsr_rowptr[r + 1];
+      return (int)(std::lower_bound(b0, b1, c) - h->bsr_col.data());
+    };
+    for (int k = 0; k < h->nf; ++k) diag_slot[k] = slot(k, k);
+    for (int p2 = 0; p2 < h->npairs; ++p2) {
+      const int a = h->pair_a[p2], b = h->pair_b[p2];
+      const int ra[2] = {fq(a), ft(a)}, cb[2] = {fq(b), ft(b)};
+      for (int sa = 0; sa < 2; ++sa) for (int sb = 0; sb < 2; ++sb) {
+        pair_slot[(size_t)p2 * 8 + 2 * sa + sb] = slot(ra[sa], cb[sb]);
+        pair_slot[(size_t)p2 * 8 + 4 + 2 * sa + sb] = slot(cb[sb], ra[sa]);
+      }
+    }
+    for (int d = 0; d < h->ngdest; ++d) { gd_slot[2 * (size_t)d] = slot(h->gd_row[d], h->gd_col[d]); gd_slot[2 * (size_t)d + 1] = slot(h->gd_col[d], h->gd_row[d]); }
+  }
   // residual order for bsnls_evaluate
   h->res_order.assign(total, {0, 0, 0});
   {
@@ -543,6 +586,8 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_fg_ptr, fg_ptr, s)); CK(upload(h->d_fg_fac, fg_fac, s)); CK(upload(h->d_fg_lb, fg_lb, s));
   CK(upload(h->d_gd_row, h->gd_row, s)); CK(upload(h->d_gd_col, h->gd_col, s)); CK(upload(h->d_gd_ptr, gd_ptr, s));
   CK(upload(h->d_gd_fac, gd_fac, s)); CK(upload(h->d_gd_bi, gd_bi, s)); CK(upload(h->d_gd_bj, gd_bj, s)); CK(upload(h->d_is_pose, is_pose, s));
+  CK(upload(h->d_bsr_rowptr, h->bsr_rowptr, s)); CK(upload(h->d_bsr_col, h->bsr_col, s)); CK(upload(h->d_diag_slot, diag_slot, s));
+  CK(upload(h->d_pair_slot, pair_slot, s)); CK(upload(h->d_gd_slot, gd_slot, s));
   // work buffers
   const int ntan = ne_dim + nf_dim;
   h->nb_obs = nobs ? BlocksFor(nobs, 256) : 0; h->nb_lm = h->ne ? BlocksFor(h->ne * h->G, 256) : 0; h->nb_act = BlocksFor((int)h->active_blocks.size(), 256);
@@ -550,7 +595,17 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(h->d_Jrec.alloc(sizeof(double) * kJRec * (size_t)nobs)); CK(h->d_Vrec.alloc(sizeof(double) * kVRec * (size_t)nobs));
   CK(h->d_minv.alloc(sizeof(double) * 6 * (size_t)h->ne)); CK(h->d_grad.alloc(sizeof(double) * ntan)); CK(h->d_colsq.alloc(sizeof(double) * ntan));
   CK(h->d_scale.alloc(sizeof(double) * ntan)); CK(h->d_y.alloc(sizeof(double) * ntan)); CK(h->d_yf.alloc(sizeof(double) * nf_dim));
-  CK(h->d_rhs.alloc(sizeof(double) * nf_dim)); CK(h->d_S.alloc(sizeof(double) * (size_t)nf_dim * nf_dim)); CK(h->d_poseH.alloc(sizeof(double) * 21 * (size_t)std::max(1, h->np)));
+  CK(h->d_rhs.alloc(sizeof(double) * nf_dim)); CK(h->d_S.alloc(sizeof(double) * (h->sparse ? (size_t)h->nnzb * 9 : (size_t)nf_dim * nf_dim)));
+  if (h->sparse) {
+    int dev_sms = 0, per_sm = 0;
+    CK(cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, h->device));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pcg_kernel, 256, 0));
+    if (per_sm < 1) return h->fail(BSNLS_ERR_CUDA, "pcg_kernel cannot be made resident");
+    h->pcg_grid = dev_sms * std::min(per_sm, 2);
+    CK(h->d_pcg_x.alloc(sizeof(double) * nf_dim)); CK(h->d_pcg_r.alloc(sizeof(double) * nf_dim)); CK(h->d_pcg_z.alloc(sizeof(double) * nf_dim));
+    CK(h->d_pcg_p.alloc(sizeof(double) * nf_dim)); CK(h->d_pcg_Ap.alloc(sizeof(double) * nf_dim)); CK(h->d_pcg_Minv.alloc(sizeof(double) * 9 * (size_t)h->nf));
+    CK(h->d_pcg_part.alloc(sizeof(double) * 5 * (size_t)h->pcg_grid));
+  } CK(h->d_poseH.alloc(sizeof(double) * 21 * (size_t)std::max(1, h->np)));
   CK(h->d_gfJ.alloc(sizeof(double) * joff)); CK(h->d_gfR.alloc(sizeof(double) * roff));
   CK(h->d_cost_part.alloc(sizeof(double) * (h->nb_obs + h->ngf + 1))); CK(h->d_cand_part.alloc(sizeof(double) * (h->nb_obs + h->ngf + 1)));
   CK(h->d_model_part.alloc(sizeof(double) * (h->nb_lm + h->ngf + 1)));
@@ -576,6 +631,8 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   P.fg_ptr = h->d_fg_ptr.as<int>(); P.fg_fac = h->d_fg_fac.as<int>(); P.fg_lb = h->d_fg_lb.as<int>();
   P.num_gdest = h->ngdest; P.gd_row = h->d_gd_row.as<int>(); P.gd_col = h->d_gd_col.as<int>(); P.gd_ptr = h->d_gd_ptr.as<int>();
   P.gd_fac = h->d_gd_fac.as<int>(); P.gd_bi = h->d_gd_bi.as<int>(); P.gd_bj = h->d_gd_bj.as<int>();
+  P.sparse = h->sparse ? 1 : 0; P.nnzb = h->nnzb; P.bsr_rowptr = h->d_bsr_rowptr.as<int>(); P.bsr_col = h->d_bsr_col.as<int>();
+  P.diag_slot = h->d_diag_slot.as<int>(); P.pair_slot = h->d_pair_slot.as<int>(); P.gd_slot = h->d_gd_slot.as<int>();
   CK(cudaStreamSynchronize(s));  // host vectors above go out of scope
   h->has_problem = true;
   return BSNLS_OK;
@@ -628,7 +685,7 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
     LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
     if (pass == max_it) break;
     EnqueueAssemble(h, o);
-    EnqueueDenseSolve(h);
+    if (h->sparse) { rc = EnqueueSparseSolve(h); if (rc != BSNLS_OK) return rc; } else EnqueueDenseSolve(h);
     EnqueueStep(h);
     LAUNCH(h, ctrl_end_iteration_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
     LAUNCH(h, apply_step_kernel, BlocksFor((int)h->num_values, 256), 256, h->d_x.as<double>(), h->d_xc.as<double>(), (int)h->num_values, st);
@@ -663,7 +720,8 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
   sum->initial_cost = nrec ? hrec[0].cost : 0.0; sum->final_cost = sum->initial_cost;
   for (int i = 0; i < nrec; ++i) sum->final_cost = std::min(sum->final_cost, hrec[i].cost);  // ceres solver.cc SetSummaryFinalCost
   for (int i = 0; i < nrec && i < max_its_out && its; ++i) its[i] = hrec[i];
-  sum->num_e_blocks = h->ne; sum->num_f_blocks = h->nf; sum->reduced_system_dim = h->P.nf_dim; sum->linear_solver_used = BSNLS_LINEAR_DENSE_SCHUR;
+  sum->num_e_blocks = h->ne; sum->num_f_blocks = h->nf; sum->reduced_system_dim = h->P.nf_dim; sum->linear_solver_used = h->sparse ? BSNLS_LINEAR_ITERATIVE_SCHUR : BSNLS_LINEAR_DENSE_SCHUR;
+  { int64_t lower = 0; for (int r = 0; r < h->nf; ++r) for (int k = h->bsr_rowptr[r]; k < h->bsr_rowptr[r + 1]; ++k) lower += h->bsr_col[k] <= r; sum->reduced_system_nnz_blocks = lower; }
   sum->num_parameter_blocks_reduced = h->ne + h->nf; sum->num_effective_parameters_reduced = h->P.ntan;
   for (int b : h->active_blocks) sum->num_parameters_reduced += h->blk_size[b];
   sum->num_residual_blocks_reduced = h->nobs + h->ngf_active;
@@ -749,8 +807,18 @@ int bsnls_get_reduced_system(bsnls_handle* h, double radius, double* S, double* 
   if (rc != BSNLS_OK) return rc;
   rc = bsnls_run_schur(h, radius);
   if (rc != BSNLS_OK) return rc;
-  CK(cudaMemcpyAsync(S, h->d_S.p, sizeof(double) * (size_t)dim * dim, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaMemcpyAsync(rhs, h->d_rhs.p, sizeof(double) * dim, cudaMemcpyDeviceToHost, h->stream));
+  if (h->sparse) {
+    std::vector<double> blocks((size_t)h->nnzb * 9);
+    CK(cudaMemcpyAsync(blocks.data(), h->d_S.p, sizeof(double) * blocks.size(), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    std::memset(S, 0, sizeof(double) * (size_t)dim * dim);
+    for (int r = 0; r < h->nf; ++r)
+      for (int k = h->bsr_rowptr[r]; k < h->bsr_rowptr[r + 1]; ++k)
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) S[(size_t)(3 * h->bsr_col[k] + j) * dim + 3 * r + i] = blocks[(size_t)k * 9 + 3 * i + j];
+    return BSNLS_OK;
+  }
+  CK(cudaMemcpyAsync(S, h->d_S.p, sizeof(double) * (size_t)dim * dim, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
   for (int c = 0; c < dim; ++c) for (int r = 0; r < c; ++r) S[(size_t)c * dim + r] = S[(size_t)r * dim + c];  // mirror the lower triangle
   return BSNLS_OK;

@@ -2,6 +2,7 @@
 // per-kernel roofline. Every kernel is gated by the device-resident LM state so that a whole solve can be
 // enqueued without host round trips (K9, device-side controller).
 #pragma once
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -53,6 +54,10 @@ struct DeviceProblem {
   // generic-factor contributions: per f-block (gradient / column norms) and per 3x3 destination of S
   const int* fg_ptr; const int* fg_fac; const int* fg_lb;            // CSR over f-blocks (nf)
   int num_gdest; const int* gd_row; const int* gd_col; const int* gd_ptr; const int* gd_fac; const int* gd_bi; const int* gd_bj;
+  // block-sparse reduced system (3x3 blocks, full symmetric pattern, CSR over f-blocks); sparse == 0 -> dense S
+  int sparse; long long nnzb; const int* bsr_rowptr; const int* bsr_col; const int* diag_slot;
+  const int* pair_slot;  // 8 per pair: slots of (qa,qb),(qa,tb),(ta,qb),(ta,tb) then of their transposes (-1: none)
+  const int* gd_slot;    // 2 per destination: slot of (row,col) and of (col,row)
 };
 
 struct Options { double min_lm_diagonal, max_lm_diagonal, function_tolerance, gradient_tolerance,
@@ -454,7 +459,10 @@ __global__ void __launch_bounds__(128) pair_kernel(DeviceProblem P, const double
       if (a == b && sa > sb) continue;             // (t,q) duplicates (q,t)^T
       double B[9];
       for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) B[3 * i + j] = blk[6 * (3 * sa + i) + 3 * sb + j];
-      store_sub3(S, ld, ta[sa], tb[sb], B);
+      if (!P.sparse) { store_sub3(S, ld, ta[sa], tb[sb], B); continue; }
+      const int slot = P.pair_slot[pb * 8 + 2 * sa + sb], slot_t = P.pair_slot[pb * 8 + 4 + 2 * sa + sb];
+      for (int k = 0; k < 9; ++k) S[(size_t)slot * 9 + k] = B[k];
+      if (slot_t >= 0 && slot_t != slot) for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) S[(size_t)slot_t * 9 + 3 * j + i] = B[3 * i + j];
     }
 }
 
@@ -472,6 +480,12 @@ __global__ void __launch_bounds__(144) gf_schur_kernel(DeviceProblem P, const do
     const double* J = gfJ + P.gf_joff[f];
     for (int r = 0; r < nr; ++r) acc += J[r * ncol + 3 * bi + i] * J[r * ncol + 3 * bj + j];
   }
+  if (P.sparse) {
+    const int slot = P.gd_slot[2 * d], slot_t = P.gd_slot[2 * d + 1];
+    S[(size_t)slot * 9 + 3 * i + j] += acc;
+    if (slot_t != slot) S[(size_t)slot_t * 9 + 3 * j + i] += acc;
+    return;
+  }
   const int rt = 3 * P.gd_row[d] + i, ct = 3 * P.gd_col[d] + j;
   if (rt >= ct) S[(size_t)ct * P.nf_dim + rt] += acc;
 }
@@ -485,7 +499,7 @@ __global__ void __launch_bounds__(256) finish_system_kernel(DeviceProblem P, con
   if (j >= P.nf_dim) return;
   const double s = scale[P.ne_dim + j];
   const double d = fmin(fmax(colsq[P.ne_dim + j] * s * s, opt.min_lm_diagonal), opt.max_lm_diagonal) / (st->radius * s * s);
-  S[(size_t)j * P.nf_dim + j] += d;
+  if (P.sparse) S[(size_t)P.diag_slot[j / 3] * 9 + 4 * (j % 3)] += d; else S[(size_t)j * P.nf_dim + j] += d;
   if (!is_pose_entry[j]) rhs[j] = grad[P.ne_dim + j];
 }
 
@@ -635,6 +649,108 @@ __global__ void __launch_bounds__(1024) chol_solve_kernel(const double* __restri
     }
     __syncthreads();
   }
+}
+
+// ===================================================================================================
+// K7: preconditioned conjugate gradients on the block-sparse reduced system S y = rhs (3x3-block CSR, full
+// symmetric storage). One cooperative persistent kernel runs every CG iteration; grid-wide barriers replace
+// launches, dot products are per-CTA partial sums added in a fixed order by every CTA (no atomics).
+// Preconditioner: block-Jacobi (inverse of the 3x3 diagonal blocks) = Ceres' SCHUR_JACOBI for this block size.
+// SpMV: one warp per block row; lanes stride over the row's contiguous 9-double blocks (coalesced).
+// ===================================================================================================
+struct PcgBuffers { double* x; double* r; double* z; double* p; double* Ap; double* Minv; double* part; int max_iter; double tol; };
+__device__ __forceinline__ double pcg_grid_sum(cooperative_groups::grid_group& grid, double v, double* part, int slot, double* sm) {
+  const double t = block_sum<256>(v, sm);
+  if (threadIdx.x == 0) part[(size_t)slot * gridDim.x + blockIdx.x] = t;
+  grid.sync();
+  double acc = 0.0;
+  for (int i = 0; i < (int)gridDim.x; ++i) acc += part[(size_t)slot * gridDim.x + i];   // same order in every CTA
+  return acc;
+}
+__global__ void __launch_bounds__(256) pcg_kernel(DeviceProblem P, const double* __restrict__ S, const double* __restrict__ rhs,
+                                                  PcgBuffers B, LMState* st) {
+  namespace cg = cooperative_groups;
+  cg::grid_group grid = cg::this_grid();
+  __shared__ double sm[256];
+  if (!gate_run(st) || st->lin_fail) return;   // uniform across the grid: written only by earlier kernels
+  const int n = P.nf_dim, nbr = P.nf;
+  const int gtid = blockIdx.x * 256 + threadIdx.x, gsz = gridDim.x * 256;
+  const int gwarp = gtid >> 5, nwarp = gsz >> 5, lane = threadIdx.x & 31;
+  // block-Jacobi preconditioner: invert the 3x3 diagonal blocks (symmetric positive definite)
+  int bad = 0;
+  for (int i = gtid; i < nbr; i += gsz) {
+    const double* D = S + (size_t)P.diag_slot[i] * 9;
+    const double a = D[0], b = D[1], c = D[2], d = D[4], e = D[5], f = D[8];
+    const double A0 = d * f - e * e, A1 = c * e - b * f, A2 = b * e - c * d;
+    const double det = a * A0 + b * A1 + c * A2;
+    if (!(det > 0.0) || !(a > 0.0)) bad = 1;
+    const double id = 1.0 / det;
+    double* M = B.Minv + (size_t)i * 9;
+    M[0] = A0 * id; M[1] = A1 * id; M[2] = A2 * id; M[3] = A1 * id; M[4] = (a * f - c * c) * id; M[5] = (b * c - a * e) * id;
+    M[6] = A2 * id; M[7] = M[5]; M[8] = (a * d - b * b) * id;
+  }
+  // make the failure decision uniform across the grid before anyone acts on it (st->lin_fail is only written at
+  // the very end: a CTA that starts late must still see the value the launch began with)
+  int fail = pcg_grid_sum(grid, (double)bad, B.part, 0, sm) > 0.0; __syncthreads();
+  // x = 0, r = b, z = M^-1 r, p = z
+  double bb = 0.0, rz = 0.0;
+  grid.sync();
+  for (int i = gtid; i < n; i += gsz) {
+    const int br = i / 3, k = i % 3;
+    const double* M = B.Minv + (size_t)br * 9 + 3 * k;
+    const double z = M[0] * rhs[3 * br] + M[1] * rhs[3 * br + 1] + M[2] * rhs[3 * br + 2];
+    B.x[i] = 0.0; B.r[i] = rhs[i]; B.z[i] = z; B.p[i] = z;
+    bb += rhs[i] * rhs[i]; rz += rhs[i] * z;
+  }
+  bb = pcg_grid_sum(grid, bb, B.part, 0, sm); __syncthreads();
+  rz = pcg_grid_sum(grid, rz, B.part, 1, sm); __syncthreads();
+  const double stop = B.tol * B.tol * bb;
+  int it = 0;
+  if (bb > 0.0 && !fail) {
+    for (it = 1; it <= B.max_iter; ++it) {
+      // Ap = S p (warp per block row) and p.Ap
+      double pAp = 0.0;
+      for (int br = gwarp; br < nbr; br += nwarp) {
+        const int e0 = P.bsr_rowptr[br] * 9, e1 = P.bsr_rowptr[br + 1] * 9;
+        double y0 = 0.0, y1 = 0.0, y2 = 0.0;
+        for (int e = e0 + lane; e < e1; e += 32) {
+          const int blk = e / 9, w = e - 9 * blk, k = w / 3, c = w - 3 * k;
+          const double v = S[e] * B.p[3 * P.bsr_col[blk] + c];
+          if (k == 0) y0 += v; else if (k == 1) y1 += v; else y2 += v;
+        }
+#pragma unroll
+        for (int m = 1; m < 32; m <<= 1) { y0 += __shfl_xor_sync(0xffffffffu, y0, m); y1 += __shfl_xor_sync(0xffffffffu, y1, m); y2 += __shfl_xor_sync(0xffffffffu, y2, m); }
+        if (lane == 0) {
+          B.Ap[3 * br] = y0; B.Ap[3 * br + 1] = y1; B.Ap[3 * br + 2] = y2;
+          pAp += y0 * B.p[3 * br] + y1 * B.p[3 * br + 1] + y2 * B.p[3 * br + 2];
+        }
+      }
+      pAp = pcg_grid_sum(grid, pAp, B.part, 2, sm); __syncthreads();
+      if (!(pAp > 0.0)) { fail = 1; break; }   // not positive definite (uniform decision)
+      const double alpha = rz / pAp;
+      double rr = 0.0;
+      for (int i = gtid; i < n; i += gsz) {
+        B.x[i] += alpha * B.p[i];
+        const double r = B.r[i] - alpha * B.Ap[i];
+        B.r[i] = r; rr += r * r;
+      }
+      rr = pcg_grid_sum(grid, rr, B.part, 3, sm); __syncthreads();
+      if (rr <= stop) break;
+      double rz_new = 0.0;
+      for (int i = gtid; i < n; i += gsz) {
+        const int br = i / 3, k = i % 3;
+        const double* M = B.Minv + (size_t)br * 9 + 3 * k;
+        const double z = M[0] * B.r[3 * br] + M[1] * B.r[3 * br + 1] + M[2] * B.r[3 * br + 2];
+        B.z[i] = z; rz_new += B.r[i] * z;
+      }
+      rz_new = pcg_grid_sum(grid, rz_new, B.part, 4, sm); __syncthreads();
+      const double beta = rz_new / rz;
+      rz = rz_new;
+      for (int i = gtid; i < n; i += gsz) B.p[i] = B.z[i] + beta * B.p[i];
+      grid.sync();
+    }
+  }
+  if (gtid == 0) { st->pcg_iters = it > B.max_iter ? B.max_iter : it; if (fail) st->lin_fail = 1; }
 }
 
 // ===================================================================================================

@@ -225,3 +225,33 @@ def test_run_to_run_determinism():
         summ, its = s.solve()
         out.append((s.get_values().tobytes(), [i.cost for i in its]))
     assert out[0] == out[1]
+
+
+@pytest.mark.parametrize("cfg,scale", [(2, 0.25), (3, 0.02)])
+def test_block_sparse_pcg_matches_dense_and_oracle(cfg, scale):
+    """K7: block-sparse reduced system + block-Jacobi PCG against the dense DMMA Cholesky path and the oracle.
+    The assembled system is the same arithmetic (bit-identical blocks); the PCG solve is iterative, so the
+    per-iteration cost is held to 1e-8 relative (pcg_tolerance 1e-13 on |r|/|b|)."""
+    g = host.HashGraph.synthetic(cfg, scale=scale)
+    p = g.flatten()
+    opts = host.HashGraph.synthetic_options(cfg)
+    dense = Solver(opts)
+    dense.set_problem(p)
+    opts_s = host.HashGraph.synthetic_options(cfg)
+    opts_s.linear_solver = cabi.LINEAR_ITERATIVE_SCHUR
+    opts_s.pcg_max_iterations = 5000
+    sp = Solver(opts_s)
+    sp.set_problem(p)
+    Sd, rd = dense.reduced_system(1e4)
+    Ss, rs = sp.reduced_system(1e4)
+    assert np.array_equal(np.tril(Sd), np.tril(Ss)) and np.array_equal(rd, rs)
+    summ, its = sp.solve()
+    so, ito, xo = orc.solve(p, opts)
+    assert summ.linear_solver_used == cabi.LINEAR_ITERATIVE_SCHUR
+    assert summ.termination_type == so.termination_type and len(its) == len(ito)
+    assert all(i.linear_solver_iterations > 0 for i in its[1:])
+    for a, b in zip(its, ito):
+        assert abs(a.cost - b.cost) <= 1e-8 * abs(b.cost)
+    assert abs(summ.final_cost - so.final_cost) <= 1e-9 * so.final_cost
+    r, c = sp.reduced_pattern()
+    assert summ.reduced_system_nnz_blocks == len(r)
