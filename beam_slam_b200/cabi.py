@@ -193,6 +193,8 @@ def load_library():
     lib.bsnls_launch_count.restype = C.c_int64
     lib.bsnls_reprojection_cost_noalloc.argtypes = [C.c_void_p] * 7 + [C.c_int32, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int32]
     lib.bsnls_reprojection_cost_noalloc.restype = C.c_int
+    lib.bsnls_shard_range.argtypes = [_pi32, C.c_int32, C.c_int32, C.c_int32, _pi32, _pi32]
+    lib.bsnls_shard_range.restype = C.c_int
     lib.bsnls_nccl_unique_id.argtypes = [C.c_char * 128]
     lib.bsnls_create_sharded.argtypes = [C.POINTER(Options), C.c_int32, C.c_int32, C.c_char * 128, C.POINTER(H)]
     for name in ("bsnls_create", "bsnls_set_problem", "bsnls_set_values", "bsnls_set_options", "bsnls_solve",

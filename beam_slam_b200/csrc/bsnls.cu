@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "kernels.cuh"
+#include "nccl_dyn.h"
 
 using namespace bsnls;
 
@@ -51,7 +52,8 @@ struct bsnls_handle {
   int64_t launches = 0;
   bool has_problem = false, jac_valid = false;
   float last_eval_ms = 0, last_schur_ms = 0;
-  int rank = 0, world = 1;
+  int rank = 0, world = 1; NcclComm comm = nullptr;
+  int lm_lo = 0, lm_hi = 0, ne_global = 0, nobs_global = 0, nb_act_e = 0; DevMem d_owned;
 
   // host-side structure
   int num_blocks = 0; int64_t num_values = 0;
@@ -61,7 +63,7 @@ struct bsnls_handle {
   std::vector<int> pose_q_blk, pose_t_blk;
   std::vector<int> pair_a, pair_b;
   std::vector<int> gd_row, gd_col;
-  bool sparse = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
+  bool sparse = false, pcg = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
   // residual-block bookkeeping for bsnls_evaluate (program order)
   struct ResRef { int type; int idx; int row; };   // idx: sorted-observation id or generic-factor id
   std::vector<ResRef> res_order; int64_t num_res_rows = 0;
@@ -77,6 +79,7 @@ struct bsnls_handle {
       d_gf_roff, d_pair_a, d_pair_b, d_pair_ptr, d_item_i, d_item_j, d_fg_ptr, d_fg_fac, d_fg_lb, d_gd_row, d_gd_col,
       d_gd_ptr, d_gd_fac, d_gd_bi, d_gd_bj, d_is_pose, d_bsr_rowptr, d_bsr_col, d_diag_slot, d_pair_slot, d_gd_slot,
       d_pcg_x, d_pcg_r, d_pcg_z, d_pcg_p, d_pcg_Ap, d_pcg_Minv, d_pcg_part;
+  DevMem d_Sdense, d_gradL, d_colsqL, d_gradS, d_colsqS;
   DevMem d_x, d_xc, d_x0, d_Jrec, d_Vrec, d_minv, d_grad, d_colsq, d_scale, d_y, d_yf, d_rhs, d_S, d_poseH, d_gfJ,
       d_gfR, d_cost_part, d_cand_part, d_model_part, d_step_part, d_candsq_part, d_gsq_part, d_gmax_part, d_xsq_part,
       d_red, d_state, d_recs;
@@ -146,6 +149,22 @@ const char* MessageText(int id) {
 int BlocksFor(int n, int per) { return std::max(1, (n + per - 1) / per); }
 
 // ---- enqueue helpers (all asynchronous on h->stream) ----
+// ---- NCCL exchange of the landmark-sharded solve (no-ops on a single GPU) ----
+int AllReduce(bsnls_handle* h, double* buf, size_t count, int op) {
+  if (h->world <= 1 || count == 0) return BSNLS_OK;
+  const int rc = Nccl().AllReduce(buf, buf, count, kNcclFloat64, op, h->comm, h->stream);
+  return rc == kNcclSuccess ? BSNLS_OK : h->fail(BSNLS_ERR_CUDA, "ncclAllReduce: %s", Nccl().GetErrorString(rc));
+}
+int AllReduceScalars(bsnls_handle* h) {  // rank-local partial sums and the local max of red[]
+  if (h->world <= 1) return BSNLS_OK;
+  Nccl().GroupStart();
+  int rc = AllReduce(h, h->d_red.as<double>(), RED_NUM, kNcclSum);
+  if (rc == BSNLS_OK) rc = AllReduce(h, h->d_red.as<double>() + kRedLocalMax, 1, kNcclMax);
+  Nccl().GroupEnd();
+  return rc;
+}
+RedDesc Desc(const double* src, int n, int op, int slot, bool replicated) { return RedDesc{src, n, op, op ? (replicated ? kRedReplMax : kRedLocalMax) : slot + (replicated ? RED_NUM : 0)}; }
+
 void EnqueueEval(bsnls_handle* h) {  // phase A: residuals + Jacobians + cost at x
   const DeviceProblem& P = h->P;
   LMState* st = h->d_state.as<LMState>();
@@ -164,46 +183,78 @@ void EnqueueLandmark(bsnls_handle* h, const Options& o) {  // phase B
   switch (h->G) { case 4: LaunchLandmark<4>(h, o); break; case 8: LaunchLandmark<8>(h, o); break;
                   case 16: LaunchLandmark<16>(h, o); break; default: LaunchLandmark<32>(h, o); }
 }
-__global__ void zero_f_kernel(DeviceProblem P, double* grad, double* colsq, const LMState* st) {
+__global__ void zero_f_kernel(DeviceProblem P, double* gradL, double* colsqL, const LMState* st) {
   if (!gate_jac(st)) return;
   const int j = blockIdx.x * 256 + threadIdx.x;
-  if (j < P.nf_dim) { grad[P.ne_dim + j] = 0.0; colsq[P.ne_dim + j] = 0.0; }
+  if (j < P.nf_dim) { gradL[j] = 0.0; colsqL[j] = 0.0; }
 }
-void EnqueueGradient(bsnls_handle* h, const Options& o) {  // phase C: gradient, column norms, scale, gradient norms
+int EnqueueGradient(bsnls_handle* h, const Options& o) {  // phase C: gradient, column norms, scale, gradient norms
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
-  LAUNCH(h, zero_f_kernel, BlocksFor(P.nf_dim, 256), 256, P, h->d_grad.as<double>(), h->d_colsq.as<double>(), st);
-  if (h->np) LAUNCH(h, pose_diag_kernel, BlocksFor(h->np, 4), 128, P, h->d_Jrec.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_colsq.as<double>(), st);
-  if (h->ngf) LAUNCH(h, gf_grad_kernel, BlocksFor(3 * h->nf, 128), 128, P, h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_grad.as<double>(), h->d_colsq.as<double>(), st);
+  LAUNCH(h, zero_f_kernel, BlocksFor(P.nf_dim, 256), 256, P, h->d_gradL.as<double>(), h->d_colsqL.as<double>(), st);
+  if (h->np) LAUNCH(h, pose_diag_kernel, BlocksFor(h->np, 4), 128, P, h->d_Jrec.as<double>(), h->d_poseH.as<double>(), h->d_gradL.as<double>(), h->d_colsqL.as<double>(), st);
+  const double* gS = h->d_gradL.as<double>(); const double* cS = h->d_colsqL.as<double>();
+  if (h->world > 1) {
+    // pose gradient / column norms are sums over the observations of every rank. Out of place: the kernels above are
+    // gated by the device state, the collective is not, so it must be idempotent when they did not run.
+    Nccl().GroupStart();
+    int rc = Nccl().AllReduce(h->d_gradL.p, h->d_gradS.p, P.nf_dim, kNcclFloat64, kNcclSum, h->comm, h->stream);
+    if (rc == kNcclSuccess) rc = Nccl().AllReduce(h->d_colsqL.p, h->d_colsqS.p, P.nf_dim, kNcclFloat64, kNcclSum, h->comm, h->stream);
+    Nccl().GroupEnd();
+    if (rc != kNcclSuccess) return h->fail(BSNLS_ERR_CUDA, "ncclAllReduce(gradient): %s", Nccl().GetErrorString(rc));
+    gS = h->d_gradS.as<double>(); cS = h->d_colsqS.as<double>();
+  }
+  LAUNCH(h, gf_grad_kernel, BlocksFor(3 * h->nf, 128), 128, P, h->d_gfJ.as<double>(), h->d_gfR.as<double>(), gS, cS, h->d_grad.as<double>(), h->d_colsq.as<double>(), st);
   LAUNCH(h, fscale_kernel, BlocksFor(P.nf_dim, 256), 256, P, h->d_colsq.as<double>(), h->d_scale.as<double>(), o, st);
   LAUNCH(h, grad_norm_kernel, h->nb_act, 256, P, h->d_x.as<double>(), h->d_grad.as<double>(), h->d_gsq_part.as<double>(), h->d_gmax_part.as<double>(), st);
   RedList L{}; L.gate = 2; L.count = 0;
-  if (h->nobs) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>(), h->nb_obs, 0, RED_COST};
-  if (h->ngf_active) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>() + h->nb_obs, h->ngf_active, 0, RED_COST};
-  if (h->ngf > h->ngf_active) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>() + h->nb_obs + h->ngf_active, h->ngf - h->ngf_active, 0, RED_FIXED};
-  L.d[L.count++] = RedDesc{h->d_gsq_part.as<double>(), h->nb_act, 0, RED_GRAD_SQ};
-  L.d[L.count++] = RedDesc{h->d_gmax_part.as<double>(), h->nb_act, 1, RED_GRAD_MAX};
+  const int nbe = h->nb_act_e, nbf = h->nb_act - h->nb_act_e;
+  if (h->nobs) L.d[L.count++] = Desc(h->d_cost_part.as<double>(), h->nb_obs, 0, RED_COST, false);
+  if (h->ngf_active) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_obs, h->ngf_active, 0, RED_COST, true);
+  if (h->ngf > h->ngf_active) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_obs + h->ngf_active, h->ngf - h->ngf_active, 0, RED_FIXED, true);
+  if (nbe) L.d[L.count++] = Desc(h->d_gsq_part.as<double>(), nbe, 0, RED_GRAD_SQ, false);
+  if (nbf) L.d[L.count++] = Desc(h->d_gsq_part.as<double>() + nbe, nbf, 0, RED_GRAD_SQ, true);
+  if (nbe) L.d[L.count++] = Desc(h->d_gmax_part.as<double>(), nbe, 1, 0, false);
+  if (nbf) L.d[L.count++] = Desc(h->d_gmax_part.as<double>() + nbe, nbf, 1, 0, true);
   LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), st);
+  return AllReduceScalars(h);
 }
-void EnqueueAssemble(bsnls_handle* h, const Options& o) {  // phase D1: reduced system S, rhs
+int EnqueueAssemble(bsnls_handle* h, const Options& o) {  // phase D1: reduced system S, rhs
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
+  const size_t s_count = h->sparse ? (size_t)h->nnzb * 9 : (size_t)P.nf_dim * P.nf_dim;
   MARK(h, 5);
-  cudaMemsetAsync(h->d_S.p, 0, sizeof(double) * (h->sparse ? (size_t)h->nnzb * 9 : (size_t)P.nf_dim * P.nf_dim), h->stream);
+  cudaMemsetAsync(h->d_S.p, 0, sizeof(double) * s_count, h->stream);
+  if (h->world > 1) cudaMemsetAsync(h->d_rhs.p, 0, sizeof(double) * P.nf_dim, h->stream);
   MARK(h, 6);
   if (h->npairs) LAUNCH(h, pair_kernel, BlocksFor(h->npairs, 4), 128, P, h->d_Vrec.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
   MARK(h, 7);
+  if (h->world > 1) {  // the one exchange step of the path: sum the per-shard reduced camera systems over NVLink
+    Nccl().GroupStart();
+    int rc = AllReduce(h, h->d_S.as<double>(), s_count, kNcclSum);
+    if (rc == BSNLS_OK) rc = AllReduce(h, h->d_rhs.as<double>(), P.nf_dim, kNcclSum);
+    Nccl().GroupEnd();
+    if (rc != BSNLS_OK) return rc;
+  }
+  MARK(h, 9);
   if (h->ngdest) LAUNCH(h, gf_schur_kernel, BlocksFor(h->ngdest, 16), 144, P, h->d_gfJ.as<double>(), h->d_S.as<double>(), st);
   LAUNCH(h, finish_system_kernel, BlocksFor(P.nf_dim, 256), 256, P, h->d_grad.as<double>(), h->d_colsq.as<double>(), h->d_scale.as<double>(),
          h->d_is_pose.as<unsigned char>(), h->d_S.as<double>(), h->d_rhs.as<double>(), o, st);
   MARK(h, 8);
+  return BSNLS_OK;
 }
 void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular solves
   const int n = h->P.nf_dim; LMState* st = h->d_state.as<LMState>();
+  double* Sd = h->d_S.as<double>();
+  if (h->sparse) {
+    Sd = h->d_Sdense.as<double>();
+    cudaMemsetAsync(Sd, 0, sizeof(double) * (size_t)n * n, h->stream);
+    LAUNCH(h, bsr_to_dense_kernel, (unsigned)((h->nnzb * 9 + 255) / 256), 256, h->P, h->d_S.as<double>(), Sd, st);
+  }
   for (int j0 = 0; j0 < n; j0 += kNB) {
     const int nb = std::min(kNB, n - j0), rest = n - j0 - nb;
-    LAUNCH(h, chol_panel_kernel, BlocksFor(rest, 64), 64, h->d_S.as<double>(), n, j0, st);
-    if (rest > 0) { const int T = (rest + 63) / 64; LAUNCH(h, chol_update_kernel, dim3(T, T), 128, h->d_S.as<double>(), n, j0, st); }
+    LAUNCH(h, chol_panel_kernel, BlocksFor(rest, 64), 64, Sd, n, j0, st);
+    if (rest > 0) { const int T = (rest + 63) / 64; LAUNCH(h, chol_update_kernel, dim3(T, T), 128, Sd, n, j0, st); }
   }
-  LAUNCH(h, chol_solve_kernel, 1, 1024, h->d_S.as<double>(), n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
+  LAUNCH(h, chol_solve_kernel, 1, 1024, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
 }
 int EnqueueSparseSolve(bsnls_handle* h) {  // phase D2 (K7): cooperative PCG, result in yf
   PcgBuffers B{h->d_yf.as<double>(), h->d_pcg_r.as<double>(), h->d_pcg_z.as<double>(), h->d_pcg_p.as<double>(), h->d_pcg_Ap.as<double>(),
@@ -218,7 +269,7 @@ template <int G> void LaunchBacksub(bsnls_handle* h) {
   LAUNCH(h, backsub_kernel<G>, h->nb_lm, 256, h->P, h->d_Jrec.as<double>(), h->d_minv.as<double>(), h->d_grad.as<double>(), h->d_yf.as<double>(),
          h->d_y.as<double>(), h->d_model_part.as<double>(), h->d_state.as<LMState>());
 }
-void EnqueueStep(bsnls_handle* h) {  // phase D3: back-substitution, model cost, candidate, candidate cost
+int EnqueueStep(bsnls_handle* h) {  // phase D3: back-substitution, model cost, candidate, candidate cost
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
   if (h->ne) switch (h->G) { case 4: LaunchBacksub<4>(h); break; case 8: LaunchBacksub<8>(h); break;
                              case 16: LaunchBacksub<16>(h); break; default: LaunchBacksub<32>(h); }
@@ -228,13 +279,35 @@ void EnqueueStep(bsnls_handle* h) {  // phase D3: back-substitution, model cost,
   if (h->nobs) LAUNCH(h, eval_reproj_kernel<1>, h->nb_obs, 256, P, h->d_xc.as<double>(), nullptr, h->d_cand_part.as<double>(), st);
   if (h->ngf) LAUNCH(h, eval_generic_kernel<1>, BlocksFor(h->ngf, 4), 128, P, h->d_xc.as<double>(), nullptr, nullptr, h->d_cand_part.as<double>() + h->nb_obs, st);
   RedList L{}; L.gate = 1; L.count = 0;
-  if (h->nobs) L.d[L.count++] = RedDesc{h->d_cand_part.as<double>(), h->nb_obs, 0, RED_CAND_COST};
-  if (h->ngf_active) L.d[L.count++] = RedDesc{h->d_cand_part.as<double>() + h->nb_obs, h->ngf_active, 0, RED_CAND_COST};
-  if (h->ne) L.d[L.count++] = RedDesc{h->d_model_part.as<double>(), h->nb_lm, 0, RED_MODEL};
-  if (h->ngf_active) L.d[L.count++] = RedDesc{h->d_model_part.as<double>() + h->nb_lm, h->ngf_active, 0, RED_MODEL};
-  L.d[L.count++] = RedDesc{h->d_step_part.as<double>(), h->nb_act, 0, RED_STEP_SQ};
-  L.d[L.count++] = RedDesc{h->d_candsq_part.as<double>(), h->nb_act, 0, RED_CAND_SQ};
+  const int nbe = h->nb_act_e, nbf = h->nb_act - h->nb_act_e;
+  if (h->nobs) L.d[L.count++] = Desc(h->d_cand_part.as<double>(), h->nb_obs, 0, RED_CAND_COST, false);
+  if (h->ngf_active) L.d[L.count++] = Desc(h->d_cand_part.as<double>() + h->nb_obs, h->ngf_active, 0, RED_CAND_COST, true);
+  if (h->ne) L.d[L.count++] = Desc(h->d_model_part.as<double>(), h->nb_lm, 0, RED_MODEL, false);
+  if (h->ngf_active) L.d[L.count++] = Desc(h->d_model_part.as<double>() + h->nb_lm, h->ngf_active, 0, RED_MODEL, true);
+  if (nbe) L.d[L.count++] = Desc(h->d_step_part.as<double>(), nbe, 0, RED_STEP_SQ, false);
+  if (nbf) L.d[L.count++] = Desc(h->d_step_part.as<double>() + nbe, nbf, 0, RED_STEP_SQ, true);
+  if (nbe) L.d[L.count++] = Desc(h->d_candsq_part.as<double>(), nbe, 0, RED_CAND_SQ, false);
+  if (nbf) L.d[L.count++] = Desc(h->d_candsq_part.as<double>() + nbe, nbf, 0, RED_CAND_SQ, true);
   LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), st);
+  return AllReduceScalars(h);
+}
+int EnqueueXNorm(bsnls_handle* h) {  // |x| over the reduced program's blocks -> st->x_norm
+  LMState* st = h->d_state.as<LMState>();
+  LAUNCH(h, xnorm_kernel, h->nb_act, 256, h->P, h->d_x.as<double>(), h->d_xsq_part.as<double>());
+  RedList L{}; L.gate = 0; L.count = 0;
+  const int nbe = h->nb_act_e, nbf = h->nb_act - h->nb_act_e;
+  if (nbe) L.d[L.count++] = Desc(h->d_xsq_part.as<double>(), nbe, 0, RED_X_SQ, false);
+  if (nbf) L.d[L.count++] = Desc(h->d_xsq_part.as<double>() + nbe, nbf, 0, RED_X_SQ, true);
+  LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), st);
+  const int rc = AllReduceScalars(h);
+  LAUNCH(h, init_xnorm_kernel, 1, 1, st, h->d_red.as<double>());
+  return rc;
+}
+// after a sharded solve every rank holds the complete parameter vector: owners keep their entries, others zero, sum
+int GatherValues(bsnls_handle* h) {
+  if (h->world <= 1) return BSNLS_OK;
+  LAUNCH(h, mask_owned_kernel, BlocksFor((int)h->num_values, 256), 256, h->d_x.as<double>(), h->d_owned.as<unsigned char>(), (int)h->num_values);
+  return AllReduce(h, h->d_x.as<double>(), (size_t)h->num_values, kNcclSum);
 }
 
 int InitState(bsnls_handle* h, bool keep_scale) {
@@ -243,7 +316,7 @@ int InitState(bsnls_handle* h, bool keep_scale) {
   s.need_jacobian = 1; s.scale_ready = keep_scale ? 1 : 0; s.max_records = h->max_records;
   cudaError_t e = cudaMemcpyAsync(h->d_state.p, &s, sizeof(s), cudaMemcpyHostToDevice, h->stream);
   if (e != cudaSuccess) return h->fail(BSNLS_ERR_CUDA, "state upload: %s", cudaGetErrorString(e));
-  e = cudaMemsetAsync(h->d_red.p, 0, sizeof(double) * 16, h->stream);
+  e = cudaMemsetAsync(h->d_red.p, 0, sizeof(double) * 32, h->stream);
   if (e != cudaSuccess) return h->fail(BSNLS_ERR_CUDA, "red memset: %s", cudaGetErrorString(e));
   return BSNLS_OK;
 }
@@ -295,7 +368,9 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
 void bsnls_destroy(bsnls_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  if (h->comm) Nccl().CommDestroy(h->comm);
+  if (h->stream) cudaStreamDestroy(h->stream);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->ev2) cudaEventDestroy(h->ev2);
@@ -364,20 +439,22 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     if (pr->block_group[b] == 0) { epos[b] = (int)h->eblocks.size(); h->eblocks.push_back(b); }
     else { fpos[b] = (int)h->fblocks.size(); h->fblocks.push_back(b); }
   }
-  h->ne = (int)h->eblocks.size(); h->nf = (int)h->fblocks.size();
-  const int ne_dim = 3 * h->ne, nf_dim = 3 * h->nf;
-  h->blk_tan.assign(nb, -1);
-  for (int b = 0; b < nb; ++b) { if (epos[b] >= 0) h->blk_tan[b] = 3 * epos[b]; else if (fpos[b] >= 0) h->blk_tan[b] = ne_dim + 3 * fpos[b]; }
+  const int ne_g = (int)h->eblocks.size();   // eliminated blocks of the whole graph; this rank keeps [lm_lo, lm_hi)
+  h->ne_global = ne_g; h->nf = (int)h->fblocks.size();
+  const int nf_dim = 3 * h->nf;
   if (nf_dim == 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "no non-landmark parameter blocks to solve for");
-  h->sparse = h->opt.linear_solver == BSNLS_LINEAR_ITERATIVE_SCHUR || (h->opt.linear_solver == BSNLS_LINEAR_AUTO && nf_dim > 3000);
-  if (!h->sparse && nf_dim > 24000) return h->fail(BSNLS_ERR_UNSUPPORTED, "reduced system of dimension %d exceeds the dense solver limit", nf_dim);
+  // assembly layout and linear solver: small windows dense + dense; mid-size block-sparse assembly expanded into the
+  // dense Cholesky; large (or on request) block-sparse + PCG
+  h->pcg = h->opt.linear_solver == BSNLS_LINEAR_ITERATIVE_SCHUR || (h->opt.linear_solver == BSNLS_LINEAR_AUTO && nf_dim > 16000);
+  h->sparse = h->pcg || nf_dim > 3000;
+  if (!h->pcg && nf_dim > 24000) return h->fail(BSNLS_ERR_UNSUPPORTED, "reduced system of dimension %d exceeds the dense solver limit", nf_dim);
 
   // ---- reprojection: poses, landmark-sorted observations ----
   std::vector<int> pose_of_q(nb, -1), pose_of_t(nb, -1);
   h->pose_q_blk.clear(); h->pose_t_blk.clear();
   const int nobs = rg ? rg->count : 0;
   std::vector<int> obs_pose(nobs), obs_lm(nobs), order(nobs);
-  std::vector<int> lm_count(h->ne + 1, 0);
+  std::vector<int> lm_count(ne_g + 1, 0);
   for (int i = 0; i < nobs; ++i) {
     const int q = rg->blocks[3 * (int64_t)i], t = rg->blocks[3 * (int64_t)i + 1], p = rg->blocks[3 * (int64_t)i + 2];
     if (epos[p] < 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "reprojection factor %d: landmark block must be non-constant and in elimination group 0", i);
@@ -389,27 +466,50 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     if (rg->aux[i] < 0 || rg->aux[i] >= pr->num_cameras) return h->fail(BSNLS_ERR_INVALID, "camera index out of range");
     obs_pose[i] = pose; obs_lm[i] = epos[p]; lm_count[epos[p] + 1]++;
   }
-  h->np = (int)h->pose_q_blk.size(); h->nobs = nobs;
-  for (int e = 0; e < h->ne; ++e) { if (lm_count[e + 1] == 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "group-0 block without reprojection factors"); lm_count[e + 1] += lm_count[e]; }
+  h->np = (int)h->pose_q_blk.size(); h->nobs_global = nobs;
+  for (int e = 0; e < ne_g; ++e) { if (lm_count[e + 1] == 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "group-0 block without reprojection factors"); lm_count[e + 1] += lm_count[e]; }
   std::vector<int> lm_ptr = lm_count;
   { std::vector<int> cur(lm_ptr.begin(), lm_ptr.end() - 1); for (int i = 0; i < nobs; ++i) order[cur[obs_lm[i]]++] = i; }  // stable
-  std::vector<int> s_pose(nobs), s_lm(nobs), s_cam(nobs), inv_order(nobs); std::vector<double> s_pixel(2 * (size_t)nobs);
-  for (int k = 0; k < nobs; ++k) {
-    const int i = order[k]; inv_order[i] = k;
-    s_pose[k] = obs_pose[i]; s_lm[k] = obs_lm[i]; s_cam[k] = rg->aux[i];
-    s_pixel[2 * (size_t)k] = rg->consts[2 * (size_t)i]; s_pixel[2 * (size_t)k + 1] = rg->consts[2 * (size_t)i + 1];
+  // ---- landmark shard of this rank: contiguous range in elimination order, balanced by observation count ----
+  int lo = 0, hi = ne_g;
+  bsnls_shard_range(lm_ptr.data(), ne_g, h->rank, h->world, &lo, &hi);
+  h->lm_lo = lo; h->lm_hi = hi; h->ne = hi - lo;
+  const int ne_dim = 3 * h->ne;
+  const int obs_base = lm_ptr[lo], nobs_local = lm_ptr[hi] - lm_ptr[lo];
+  h->nobs = nobs_local;
+  h->blk_tan.assign(nb, -1);
+  for (int b = 0; b < nb; ++b) {
+    if (epos[b] >= lo && epos[b] < hi) h->blk_tan[b] = 3 * (epos[b] - lo);
+    else if (fpos[b] >= 0) h->blk_tan[b] = ne_dim + 3 * fpos[b];
   }
+  // active list: local landmarks, padded to a CTA boundary, then the (replicated) f-blocks
+  h->active_blocks.clear();
+  for (int e = lo; e < hi; ++e) h->active_blocks.push_back(h->eblocks[e]);
+  while (h->active_blocks.size() % 256) h->active_blocks.push_back(-1);
+  h->nb_act_e = (int)h->active_blocks.size() / 256;
+  for (int b : h->fblocks) h->active_blocks.push_back(b);
+  std::vector<int> g_pose(nobs);   // pose of every observation of the graph in sorted order (pair pattern is global)
+  std::vector<int> s_pose(nobs_local), s_lm(nobs_local), s_cam(nobs_local), inv_order(nobs, -1); std::vector<double> s_pixel(2 * (size_t)nobs_local);
+  for (int k = 0; k < nobs; ++k) {
+    const int i = order[k]; g_pose[k] = obs_pose[i];
+    if (k < obs_base || k >= obs_base + nobs_local) continue;
+    const int kl = k - obs_base; inv_order[i] = kl;
+    s_pose[kl] = obs_pose[i]; s_lm[kl] = obs_lm[i] - lo; s_cam[kl] = rg->aux[i];
+    s_pixel[2 * (size_t)kl] = rg->consts[2 * (size_t)i]; s_pixel[2 * (size_t)kl + 1] = rg->consts[2 * (size_t)i + 1];
+  }
+  std::vector<int> lm_ptr_local(h->ne + 1);
+  for (int e = 0; e <= h->ne; ++e) lm_ptr_local[e] = lm_ptr[lo + e] - obs_base;
   std::vector<int> lm_off(h->ne);
-  for (int e = 0; e < h->ne; ++e) lm_off[e] = h->blk_off[h->eblocks[e]];
-  std::vector<int> pose_q_off(h->np), pose_t_off(h->np), pose_q_tan(h->np), pose_t_tan(h->np), pose_ptr(h->np + 1, 0), pose_obs(nobs);
+  for (int e = 0; e < h->ne; ++e) lm_off[e] = h->blk_off[h->eblocks[lo + e]];
+  std::vector<int> pose_q_off(h->np), pose_t_off(h->np), pose_q_tan(h->np), pose_t_tan(h->np), pose_ptr(h->np + 1, 0), pose_obs(nobs_local);
   for (int a = 0; a < h->np; ++a) {
     pose_q_off[a] = h->blk_off[h->pose_q_blk[a]]; pose_t_off[a] = h->blk_off[h->pose_t_blk[a]];
     pose_q_tan[a] = h->blk_tan[h->pose_q_blk[a]]; pose_t_tan[a] = h->blk_tan[h->pose_t_blk[a]];
   }
-  for (int k = 0; k < nobs; ++k) pose_ptr[s_pose[k] + 1]++;
+  for (int k = 0; k < nobs_local; ++k) pose_ptr[s_pose[k] + 1]++;
   for (int a = 0; a < h->np; ++a) pose_ptr[a + 1] += pose_ptr[a];
-  { std::vector<int> cur(pose_ptr.begin(), pose_ptr.end() - 1); for (int k = 0; k < nobs; ++k) pose_obs[cur[s_pose[k]]++] = k; }
-  const double avg_track = h->ne ? (double)nobs / h->ne : 0.0;
+  { std::vector<int> cur(pose_ptr.begin(), pose_ptr.end() - 1); for (int k = 0; k < nobs_local; ++k) pose_obs[cur[s_pose[k]]++] = k; }
+  const double avg_track = ne_g ? (double)nobs / ne_g : 0.0;
   h->G = avg_track <= 5.0 ? 4 : avg_track <= 12.0 ? 8 : avg_track <= 24.0 ? 16 : 32;
 
   // ---- pose-pair blocks and items ----
@@ -418,12 +518,14 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   {
     std::unordered_map<uint64_t, int> key_count; key_count.reserve((size_t)h->np * 16);
     auto key_of = [&](int a, int b) { return (uint64_t)a * (uint64_t)h->np + (uint64_t)b; };
-    for (int e = 0; e < h->ne; ++e)
+    for (int e = 0; e < ne_g; ++e) {   // keys: every rank needs the pattern of the WHOLE graph; counts: local items only
+      const bool mine = e >= lo && e < hi;
       for (int i = lm_ptr[e]; i < lm_ptr[e + 1]; ++i)
         for (int j = i; j < lm_ptr[e + 1]; ++j) {
-          const int a = s_pose[i], b = s_pose[j];
-          key_count[key_of(std::min(a, b), std::max(a, b))] += (a == b && i != j) ? 2 : 1;
+          const int a = g_pose[i], b = g_pose[j];
+          key_count[key_of(std::min(a, b), std::max(a, b))] += !mine ? 0 : (a == b && i != j) ? 2 : 1;
         }
+    }
     std::vector<uint64_t> keys; keys.reserve(key_count.size());
     for (auto& kv : key_count) keys.push_back(kv.first);
     std::sort(keys.begin(), keys.end());
@@ -438,10 +540,10 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     if (nitems > 0x7fffffffLL) return h->fail(BSNLS_ERR_UNSUPPORTED, "too many observation pairs");
     item_i.resize(nitems); item_j.resize(nitems);
     std::vector<int> cur(pair_ptr.begin(), pair_ptr.end() - 1);
-    for (int e = 0; e < h->ne; ++e)
-      for (int i = lm_ptr[e]; i < lm_ptr[e + 1]; ++i)
-        for (int j = i; j < lm_ptr[e + 1]; ++j) {
-          const int a = s_pose[i], b = s_pose[j];
+    for (int e = lo; e < hi; ++e)
+      for (int i0 = lm_ptr[e]; i0 < lm_ptr[e + 1]; ++i0)
+        for (int j0 = i0; j0 < lm_ptr[e + 1]; ++j0) {
+          const int a = g_pose[i0], b = g_pose[j0], i = i0 - obs_base, j = j0 - obs_base;
           const int id = key_id[key_of(std::min(a, b), std::max(a, b))];
           if (a < b || i == j) { item_i[cur[id]] = i; item_j[cur[id]] = j; cur[id]++; }
           else if (a > b) { item_i[cur[id]] = j; item_j[cur[id]] = i; cur[id]++; }
@@ -576,7 +678,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_pose_q_off, pose_q_off, s)); CK(upload(h->d_pose_t_off, pose_t_off, s)); CK(upload(h->d_pose_q_tan, pose_q_tan, s));
   CK(upload(h->d_pose_t_tan, pose_t_tan, s)); CK(upload(h->d_pose_ptr, pose_ptr, s)); CK(upload(h->d_pose_obs, pose_obs, s));
   CK(upload(h->d_obs_pose, s_pose, s)); CK(upload(h->d_obs_lm, s_lm, s)); CK(upload(h->d_obs_cam, s_cam, s)); CK(upload(h->d_obs_pixel, s_pixel, s));
-  CK(upload(h->d_lm_ptr, lm_ptr, s)); CK(upload(h->d_lm_off, lm_off, s));
+  CK(upload(h->d_lm_ptr, lm_ptr_local, s)); CK(upload(h->d_lm_off, lm_off, s));
   { std::vector<double> cams(pr->cameras, pr->cameras + (size_t)pr->num_cameras * BSNLS_CAMERA_STRIDE); CK(upload(h->d_cams, cams, s)); }
   CK(upload(h->d_gf_type, gf_type, s)); CK(upload(h->d_gf_nblk, gf_nblk, s)); CK(upload(h->d_gf_nres, gf_nres, s)); CK(upload(h->d_gf_blocks, gf_blocks, s));
   CK(upload(h->d_gf_coff, gf_coff, s)); CK(upload(h->d_gf_consts, gf_consts, s)); CK(upload(h->d_gf_loss_type, gf_loss_type, s));
@@ -588,15 +690,23 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_gd_fac, gd_fac, s)); CK(upload(h->d_gd_bi, gd_bi, s)); CK(upload(h->d_gd_bj, gd_bj, s)); CK(upload(h->d_is_pose, is_pose, s));
   CK(upload(h->d_bsr_rowptr, h->bsr_rowptr, s)); CK(upload(h->d_bsr_col, h->bsr_col, s)); CK(upload(h->d_diag_slot, diag_slot, s));
   CK(upload(h->d_pair_slot, pair_slot, s)); CK(upload(h->d_gd_slot, gd_slot, s));
+  { // ownership of parameter entries for the final gather of the sharded solve
+    std::vector<unsigned char> owned((size_t)off, h->rank == 0 ? 1 : 0);
+    for (int b = 0; b < nb; ++b) if (epos[b] >= 0) { const unsigned char mine = (epos[b] >= lo && epos[b] < hi) ? 1 : 0; for (int k = 0; k < h->blk_size[b]; ++k) owned[h->blk_off[b] + k] = mine; }
+    CK(upload(h->d_owned, owned, s));
+  }
   // work buffers
   const int ntan = ne_dim + nf_dim;
-  h->nb_obs = nobs ? BlocksFor(nobs, 256) : 0; h->nb_lm = h->ne ? BlocksFor(h->ne * h->G, 256) : 0; h->nb_act = BlocksFor((int)h->active_blocks.size(), 256);
+  h->nb_obs = h->nobs ? BlocksFor(h->nobs, 256) : 0; h->nb_lm = h->ne ? BlocksFor(h->ne * h->G, 256) : 0; h->nb_act = BlocksFor((int)h->active_blocks.size(), 256);
   CK(h->d_x.alloc(sizeof(double) * off)); CK(h->d_xc.alloc(sizeof(double) * off)); CK(h->d_x0.alloc(sizeof(double) * off));
-  CK(h->d_Jrec.alloc(sizeof(double) * kJRec * (size_t)nobs)); CK(h->d_Vrec.alloc(sizeof(double) * kVRec * (size_t)nobs));
+  CK(h->d_Jrec.alloc(sizeof(double) * kJRec * (size_t)h->nobs)); CK(h->d_Vrec.alloc(sizeof(double) * kVRec * (size_t)h->nobs));
   CK(h->d_minv.alloc(sizeof(double) * 6 * (size_t)h->ne)); CK(h->d_grad.alloc(sizeof(double) * ntan)); CK(h->d_colsq.alloc(sizeof(double) * ntan));
+  CK(h->d_gradL.alloc(sizeof(double) * nf_dim)); CK(h->d_colsqL.alloc(sizeof(double) * nf_dim));
+  if (h->world > 1) { CK(h->d_gradS.alloc(sizeof(double) * nf_dim)); CK(h->d_colsqS.alloc(sizeof(double) * nf_dim)); }
   CK(h->d_scale.alloc(sizeof(double) * ntan)); CK(h->d_y.alloc(sizeof(double) * ntan)); CK(h->d_yf.alloc(sizeof(double) * nf_dim));
   CK(h->d_rhs.alloc(sizeof(double) * nf_dim)); CK(h->d_S.alloc(sizeof(double) * (h->sparse ? (size_t)h->nnzb * 9 : (size_t)nf_dim * nf_dim)));
-  if (h->sparse) {
+  if (h->sparse && !h->pcg) CK(h->d_Sdense.alloc(sizeof(double) * (size_t)nf_dim * nf_dim));
+  if (h->pcg) {
     int dev_sms = 0, per_sm = 0;
     CK(cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, h->device));
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pcg_kernel, 256, 0));
@@ -611,7 +721,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(h->d_model_part.alloc(sizeof(double) * (h->nb_lm + h->ngf + 1)));
   CK(h->d_step_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_candsq_part.alloc(sizeof(double) * h->nb_act));
   CK(h->d_gsq_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_gmax_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_xsq_part.alloc(sizeof(double) * h->nb_act));
-  CK(h->d_red.alloc(sizeof(double) * 16)); CK(h->d_state.alloc(sizeof(LMState)));
+  CK(h->d_red.alloc(sizeof(double) * 32)); CK(h->d_state.alloc(sizeof(LMState)));
   CK(cudaMemcpyAsync(h->d_x.p, pr->block_values, sizeof(double) * off, cudaMemcpyHostToDevice, s));
   CK(cudaMemsetAsync(h->d_y.p, 0, sizeof(double) * ntan, s));
 
@@ -621,7 +731,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   P.ne = h->ne; P.nf = h->nf; P.ne_dim = ne_dim; P.nf_dim = nf_dim; P.ntan = ntan;
   P.num_poses = h->np; P.pose_q_off = h->d_pose_q_off.as<int>(); P.pose_t_off = h->d_pose_t_off.as<int>();
   P.pose_q_tan = h->d_pose_q_tan.as<int>(); P.pose_t_tan = h->d_pose_t_tan.as<int>(); P.pose_ptr = h->d_pose_ptr.as<int>(); P.pose_obs = h->d_pose_obs.as<int>();
-  P.num_obs = nobs; P.obs_pose = h->d_obs_pose.as<int>(); P.obs_lm = h->d_obs_lm.as<int>(); P.obs_cam = h->d_obs_cam.as<int>(); P.obs_pixel = h->d_obs_pixel.as<double>();
+  P.num_obs = h->nobs; P.obs_pose = h->d_obs_pose.as<int>(); P.obs_lm = h->d_obs_lm.as<int>(); P.obs_cam = h->d_obs_cam.as<int>(); P.obs_pixel = h->d_obs_pixel.as<double>();
   P.lm_ptr = h->d_lm_ptr.as<int>(); P.lm_off = h->d_lm_off.as<int>(); P.cams = h->d_cams.as<CameraModel>();
   P.num_gf = h->ngf; P.gf_type = h->d_gf_type.as<int>(); P.gf_nblk = h->d_gf_nblk.as<int>(); P.gf_nres = h->d_gf_nres.as<int>(); P.gf_blocks = h->d_gf_blocks.as<int>();
   P.gf_coff = h->d_gf_coff.as<long long>(); P.gf_consts = h->d_gf_consts.as<double>(); P.gf_loss_type = h->d_gf_loss_type.as<int>(); P.gf_loss_a = h->d_gf_loss_a.as<double>();
@@ -673,20 +783,20 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
   bsnls_iteration* recs = h->d_recs.as<bsnls_iteration>();
   CK(cudaMemcpyAsync(h->d_x0.p, h->d_x.p, sizeof(double) * h->num_values, cudaMemcpyDeviceToDevice, h->stream));
   CK(cudaMemcpyAsync(h->d_xc.p, h->d_x.p, sizeof(double) * h->num_values, cudaMemcpyDeviceToDevice, h->stream));  // constant blocks
-  LAUNCH(h, xnorm_kernel, h->nb_act, 256, h->P, h->d_x.as<double>(), h->d_xsq_part.as<double>());
-  { RedList L{}; L.gate = 0; L.count = 1; L.d[0] = RedDesc{h->d_xsq_part.as<double>(), h->nb_act, 0, RED_X_SQ};
-    LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), st); }
   CK(cudaEventRecord(h->ev0, h->stream));
-  const bool timed = h->opt.max_solver_time_in_seconds < 1e8;
+  if ((rc = EnqueueXNorm(h)) != BSNLS_OK) return rc;
+  // a wall-clock budget is a per-process decision; ranks of a sharded solve must issue identical collectives, so the
+  // budget is only honoured on a single GPU
+  const bool timed = h->opt.max_solver_time_in_seconds < 1e8 && h->world == 1;
   for (int pass = 0; pass <= max_it; ++pass) {
     EnqueueEval(h);
     if (pass < max_it) EnqueueLandmark(h, o);
-    EnqueueGradient(h, o);
+    if ((rc = EnqueueGradient(h, o)) != BSNLS_OK) return rc;
     LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
     if (pass == max_it) break;
-    EnqueueAssemble(h, o);
-    if (h->sparse) { rc = EnqueueSparseSolve(h); if (rc != BSNLS_OK) return rc; } else EnqueueDenseSolve(h);
-    EnqueueStep(h);
+    if ((rc = EnqueueAssemble(h, o)) != BSNLS_OK) return rc;
+    if (h->pcg) { rc = EnqueueSparseSolve(h); if (rc != BSNLS_OK) return rc; } else EnqueueDenseSolve(h);
+    if ((rc = EnqueueStep(h)) != BSNLS_OK) return rc;
     LAUNCH(h, ctrl_end_iteration_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
     LAUNCH(h, apply_step_kernel, BlocksFor((int)h->num_values, 256), 256, h->d_x.as<double>(), h->d_xc.as<double>(), (int)h->num_values, st);
     if (timed || (pass & 3) == 3) {
@@ -696,13 +806,14 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
       const double el = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
       if (timed && el >= h->opt.max_solver_time_in_seconds) {
         // an accepted step still needs its Jacobian pass to be recorded; then stop (NO_CONVERGENCE)
-        EnqueueEval(h); EnqueueGradient(h, o);
+        EnqueueEval(h); if ((rc = EnqueueGradient(h, o)) != BSNLS_OK) return rc;
         LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
         LAUNCH(h, set_done_kernel, 1, 1, st, (int)BSNLS_NO_CONVERGENCE, (int)MSG_MAX_TIME);
         break;
       }
     }
   }
+  if ((rc = GatherValues(h)) != BSNLS_OK) return rc;
   CK(cudaEventRecord(h->ev1, h->stream));
   LMState hs;
   CK(cudaMemcpyAsync(&hs, st, sizeof(hs), cudaMemcpyDeviceToHost, h->stream));
@@ -720,12 +831,12 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
   sum->initial_cost = nrec ? hrec[0].cost : 0.0; sum->final_cost = sum->initial_cost;
   for (int i = 0; i < nrec; ++i) sum->final_cost = std::min(sum->final_cost, hrec[i].cost);  // ceres solver.cc SetSummaryFinalCost
   for (int i = 0; i < nrec && i < max_its_out && its; ++i) its[i] = hrec[i];
-  sum->num_e_blocks = h->ne; sum->num_f_blocks = h->nf; sum->reduced_system_dim = h->P.nf_dim; sum->linear_solver_used = h->sparse ? BSNLS_LINEAR_ITERATIVE_SCHUR : BSNLS_LINEAR_DENSE_SCHUR;
+  sum->num_e_blocks = h->ne_global; sum->num_f_blocks = h->nf; sum->reduced_system_dim = h->P.nf_dim; sum->linear_solver_used = h->pcg ? BSNLS_LINEAR_ITERATIVE_SCHUR : BSNLS_LINEAR_DENSE_SCHUR;
   { int64_t lower = 0; for (int r = 0; r < h->nf; ++r) for (int k = h->bsr_rowptr[r]; k < h->bsr_rowptr[r + 1]; ++k) lower += h->bsr_col[k] <= r; sum->reduced_system_nnz_blocks = lower; }
-  sum->num_parameter_blocks_reduced = h->ne + h->nf; sum->num_effective_parameters_reduced = h->P.ntan;
-  for (int b : h->active_blocks) sum->num_parameters_reduced += h->blk_size[b];
-  sum->num_residual_blocks_reduced = h->nobs + h->ngf_active;
-  sum->num_residuals_reduced = 2 * h->nobs; for (int f = 0; f < h->ngf_active; ++f) sum->num_residuals_reduced += h->gf_nres_h[f];
+  sum->num_parameter_blocks_reduced = h->ne_global + h->nf; sum->num_effective_parameters_reduced = 3 * (h->ne_global + h->nf);
+  sum->num_parameters_reduced = 3 * h->ne_global; for (int b : h->fblocks) sum->num_parameters_reduced += h->blk_size[b];
+  sum->num_residual_blocks_reduced = h->nobs_global + h->ngf_active;
+  sum->num_residuals_reduced = 2 * h->nobs_global; for (int f = 0; f < h->ngf_active; ++f) sum->num_residuals_reduced += h->gf_nres_h[f];
   sum->device_time_in_seconds = 1e-3 * ms;
   if (hs.termination == BSNLS_FAILURE) {  // leave the parameters as they were
     CK(cudaMemcpyAsync(h->d_x.p, h->d_x0.p, sizeof(double) * h->num_values, cudaMemcpyDeviceToDevice, h->stream));
@@ -748,14 +859,15 @@ int bsnls_run_eval(bsnls_handle* h, double* cost) {
   CK(cudaEventRecord(h->ev1, h->stream));
   h->profiling = false;
   RedList L{}; L.gate = 0; L.count = 0;
-  if (h->nobs) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>(), h->nb_obs, 0, RED_COST};
-  if (h->ngf) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>() + h->nb_obs, h->ngf, 0, RED_COST};
+  if (h->nobs) L.d[L.count++] = Desc(h->d_cost_part.as<double>(), h->nb_obs, 0, RED_COST, false);
+  if (h->ngf) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_obs, h->ngf, 0, RED_COST, true);
   LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), h->d_state.as<LMState>());
-  double red[RED_NUM];
+  if ((rc = AllReduceScalars(h)) != BSNLS_OK) return rc;
+  double red[kRedSize];
   CK(cudaMemcpyAsync(red, h->d_red.p, sizeof(red), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream)); CK(cudaGetLastError());
   CK(cudaEventElapsedTime(&h->last_eval_ms, h->ev0, h->ev1));
-  if (cost) *cost = red[RED_COST];
+  if (cost) *cost = red[RED_COST] + red[RED_NUM + RED_COST];
   cudaEventElapsedTime(&h->breakdown[0], h->pev[0], h->pev[1]); cudaEventElapsedTime(&h->breakdown[1], h->pev[1], h->pev[2]);
   h->jac_valid = true;
   return BSNLS_OK;
@@ -774,15 +886,16 @@ int bsnls_run_schur(bsnls_handle* h, double radius) {
   MARK(h, 3);
   EnqueueLandmark(h, o);
   MARK(h, 4);
-  EnqueueGradient(h, o);
-  EnqueueAssemble(h, o);
+  int rc = EnqueueGradient(h, o);
+  if (rc == BSNLS_OK) rc = EnqueueAssemble(h, o);
+  if (rc != BSNLS_OK) { h->profiling = false; return rc; }
   CK(cudaEventRecord(h->ev1, h->stream));
   h->profiling = false;
   CK(cudaStreamSynchronize(h->stream)); CK(cudaGetLastError());
   CK(cudaEventElapsedTime(&h->last_schur_ms, h->ev0, h->ev1));
   cudaEventElapsedTime(&h->breakdown[2], h->pev[3], h->pev[4]); cudaEventElapsedTime(&h->breakdown[3], h->pev[4], h->pev[5]);
   cudaEventElapsedTime(&h->breakdown[4], h->pev[5], h->pev[6]); cudaEventElapsedTime(&h->breakdown[5], h->pev[6], h->pev[7]);
-  cudaEventElapsedTime(&h->breakdown[6], h->pev[7], h->pev[8]);
+  cudaEventElapsedTime(&h->breakdown[7], h->pev[7], h->pev[9]); cudaEventElapsedTime(&h->breakdown[6], h->pev[9], h->pev[8]);
   return BSNLS_OK;
 }
 
@@ -834,13 +947,15 @@ int bsnls_evaluate(bsnls_handle* h, double* cost, double* residuals, int64_t* nu
   if (rc != BSNLS_OK) return rc;
   const Options o = MakeOptions(h->opt);
   LMState* st = h->d_state.as<LMState>();
-  EnqueueEval(h); EnqueueLandmark(h, o); EnqueueGradient(h, o);
+  if (h->world > 1) return h->fail(BSNLS_ERR_UNSUPPORTED, "bsnls_evaluate is a single-GPU call (residuals live on the rank that owns their landmark)");
+  EnqueueEval(h); EnqueueLandmark(h, o); rc = EnqueueGradient(h, o);
+  if (rc != BSNLS_OK) return rc;
   // include factors whose blocks are all constant in the cost (Problem::Evaluate evaluates every residual block)
   RedList L{}; L.gate = 0; L.count = 0;
-  if (h->nobs) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>(), h->nb_obs, 0, RED_COST};
-  if (h->ngf) L.d[L.count++] = RedDesc{h->d_cost_part.as<double>() + h->nb_obs, h->ngf, 0, RED_COST};
+  if (h->nobs) L.d[L.count++] = Desc(h->d_cost_part.as<double>(), h->nb_obs, 0, RED_COST, false);
+  if (h->ngf) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_obs, h->ngf, 0, RED_COST, true);
   LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), st);
-  double red[RED_NUM];
+  double red[kRedSize];
   CK(cudaMemcpyAsync(red, h->d_red.p, sizeof(red), cudaMemcpyDeviceToHost, h->stream));
   std::vector<double> jrec, gfr, grad;
   if (residuals) {
@@ -850,7 +965,7 @@ int bsnls_evaluate(bsnls_handle* h, double* cost, double* residuals, int64_t* nu
   }
   if (gradient) { grad.resize(h->P.ntan); CK(cudaMemcpyAsync(grad.data(), h->d_grad.p, sizeof(double) * grad.size(), cudaMemcpyDeviceToHost, h->stream)); }
   CK(cudaStreamSynchronize(h->stream)); CK(cudaGetLastError());
-  if (cost) *cost = red[RED_COST];
+  if (cost) *cost = red[RED_COST] + red[RED_NUM + RED_COST];
   if (residuals) {
     const std::vector<int>& gf_roff = h->gf_roff_h;
     for (const auto& r : h->res_order) {
@@ -860,7 +975,7 @@ int bsnls_evaluate(bsnls_handle* h, double* cost, double* residuals, int64_t* nu
   }
   if (gradient) {  // tangent gradient over active blocks in program order
     int64_t n = 0;
-    for (int b : h->active_blocks) { for (int k = 0; k < 3; ++k) gradient[n + k] = grad[h->blk_tan[b] + k]; n += 3; }
+    for (int b = 0; b < h->num_blocks; ++b) { if (h->blk_tan[b] < 0) continue; for (int k = 0; k < 3; ++k) gradient[n + k] = grad[h->blk_tan[b] + k]; n += 3; }
   }
   h->jac_valid = true;
   return BSNLS_OK;
@@ -869,9 +984,9 @@ int bsnls_evaluate(bsnls_handle* h, double* cost, double* residuals, int64_t* nu
 int bsnls_get_ordering(bsnls_handle* h, int32_t* e_blocks, int32_t* num_e, int32_t* f_blocks, int32_t* num_f) {
   if (!h) return BSNLS_ERR_INVALID;
   if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "no problem");
-  if (num_e) *num_e = h->ne;
+  if (num_e) *num_e = h->ne_global;
   if (num_f) *num_f = h->nf;
-  if (e_blocks) std::memcpy(e_blocks, h->eblocks.data(), sizeof(int) * h->ne);
+  if (e_blocks) std::memcpy(e_blocks, h->eblocks.data(), sizeof(int) * h->ne_global);
   if (f_blocks) std::memcpy(f_blocks, h->fblocks.data(), sizeof(int) * h->nf);
   return BSNLS_OK;
 }
@@ -896,11 +1011,41 @@ int bsnls_get_reduced_pattern(bsnls_handle* h, int32_t* rows, int32_t* cols, int
   return BSNLS_OK;
 }
 
-int bsnls_nccl_unique_id(char id[128]) { (void)id; g_create_error = "multi-GPU sharding is not built in this library version"; return BSNLS_ERR_UNSUPPORTED; }
+// Landmark shard of one rank: contiguous range [lo, hi) of the elimination order whose observation count is closest
+// to an equal share. lm_ptr = prefix sums of observations per landmark (num_landmarks + 1 entries). Pure host logic.
+int bsnls_shard_range(const int32_t* lm_ptr, int32_t num_landmarks, int32_t rank, int32_t world_size, int32_t* lo, int32_t* hi) {
+  if (!lm_ptr || !lo || !hi || num_landmarks < 0 || world_size < 1 || rank < 0 || rank >= world_size) return BSNLS_ERR_INVALID;
+  const long long total = lm_ptr[num_landmarks];
+  auto cut = [&](int r) {
+    if (r <= 0) return 0;
+    if (r >= world_size) return (int)num_landmarks;
+    const long long target = total * r / world_size;
+    return (int)(std::lower_bound(lm_ptr, lm_ptr + num_landmarks + 1, (int32_t)target) - lm_ptr);
+  };
+  *lo = std::min<int>(num_landmarks, cut(rank)); *hi = std::max<int>(*lo, std::min<int>(num_landmarks, cut(rank + 1)));
+  return BSNLS_OK;
+}
+
+int bsnls_nccl_unique_id(char id[128]) {
+  if (!id) return BSNLS_ERR_INVALID;
+  if (!Nccl().Load()) { g_create_error = Nccl().error; return BSNLS_ERR_CUDA; }
+  NcclUniqueId u;
+  const int rc = Nccl().GetUniqueId(&u);
+  if (rc != kNcclSuccess) { g_create_error = std::string("ncclGetUniqueId: ") + Nccl().GetErrorString(rc); return BSNLS_ERR_CUDA; }
+  std::memcpy(id, u.internal, 128);
+  return BSNLS_OK;
+}
 int bsnls_create_sharded(const bsnls_options* options, int32_t rank, int32_t world_size, const char nccl_id[128], bsnls_handle** handle) {
-  (void)nccl_id;
-  if (world_size == 1 && rank == 0) return bsnls_create(options, handle);
-  g_create_error = "multi-GPU sharding is not built in this library version"; return BSNLS_ERR_UNSUPPORTED;
+  if (world_size < 1 || rank < 0 || rank >= world_size) { g_create_error = "bad rank / world_size"; return BSNLS_ERR_INVALID; }
+  int rc = bsnls_create(options, handle);
+  if (rc != BSNLS_OK || world_size == 1) return rc;
+  bsnls_handle* h = *handle;
+  if (!nccl_id || !Nccl().Load()) { g_create_error = nccl_id ? Nccl().error : "nccl_id is required"; bsnls_destroy(h); *handle = nullptr; return BSNLS_ERR_CUDA; }
+  NcclUniqueId u; std::memcpy(u.internal, nccl_id, 128);
+  const int nrc = Nccl().CommInitRank(&h->comm, world_size, u, rank);   // collective over all ranks
+  if (nrc != kNcclSuccess) { g_create_error = std::string("ncclCommInitRank: ") + Nccl().GetErrorString(nrc); bsnls_destroy(h); *handle = nullptr; return BSNLS_ERR_CUDA; }
+  h->rank = rank; h->world = world_size;
+  return BSNLS_OK;
 }
 
 }  // extern "C"

@@ -332,15 +332,17 @@ __global__ void __launch_bounds__(128) pose_diag_kernel(DeviceProblem P, const d
     const int tq = P.pose_q_tan[a], tt = P.pose_t_tan[a];
     // diagonal entries of the 21-packed upper triangle: index of (i,i) = i*6 - i(i-1)/2
     const int dg[6] = {0, 6, 11, 15, 18, 20};
-    if (tq >= 0) for (int k = 0; k < 3; ++k) { grad[tq + k] = acc[21 + k]; colsq[tq + k] = acc[dg[k]]; }
-    if (tt >= 0) for (int k = 0; k < 3; ++k) { grad[tt + k] = acc[24 + k]; colsq[tt + k] = acc[dg[3 + k]]; }
+    // grad / colsq here are the rank-local partial buffers over the f-blocks (index = tangent - ne_dim)
+    if (tq >= 0) for (int k = 0; k < 3; ++k) { grad[tq - P.ne_dim + k] = acc[21 + k]; colsq[tq - P.ne_dim + k] = acc[dg[k]]; }
+    if (tt >= 0) for (int k = 0; k < 3; ++k) { grad[tt - P.ne_dim + k] = acc[24 + k]; colsq[tt - P.ne_dim + k] = acc[dg[3 + k]]; }
   }
 }
 
 // K6b: generic-factor contributions to the gradient and the column norms of every f-block.
 // One thread per (f-block, component); fixed summation order.
 __global__ void __launch_bounds__(128) gf_grad_kernel(DeviceProblem P, const double* __restrict__ gfJ,
-                                                      const double* __restrict__ gfR, double* __restrict__ grad,
+                                                      const double* __restrict__ gfR, const double* __restrict__ pose_grad,
+                                                      const double* __restrict__ pose_colsq, double* __restrict__ grad,
                                                       double* __restrict__ colsq, const LMState* st) {
   if (!gate_jac(st)) return;
   const int tid = blockIdx.x * 128 + threadIdx.x;
@@ -354,7 +356,7 @@ __global__ void __launch_bounds__(128) gf_grad_kernel(DeviceProblem P, const dou
     for (int i = 0; i < nr; ++i) { const double v = J[i * ncol + 3 * lb + k]; g += v * R[i]; c += v * v; }
   }
   const int t = P.ne_dim + 3 * fb + k;
-  grad[t] += g; colsq[t] += c;
+  grad[t] = pose_grad[3 * fb + k] + g; colsq[t] = pose_colsq[3 * fb + k] + c;   // pose part: summed over all ranks' observations
 }
 
 // Jacobi scale of the f-blocks (iteration 0) and LM diagonal D_f^2; also gradient norms:
@@ -376,7 +378,7 @@ __global__ void __launch_bounds__(256) grad_norm_kernel(DeviceProblem P, const d
   __shared__ double sm[256];
   const int i = blockIdx.x * 256 + threadIdx.x;
   double sq = 0.0, mx = 0.0;
-  if (i < P.num_active) {
+  if (i < P.num_active && P.active_blocks[i] >= 0) {
     const int b = P.active_blocks[i], off = P.blk_off[b], t = P.blk_tan[b];
     if (P.blk_manifold[b] == BSNLS_MANIFOLD_QUATERNION) {
       const double ng[3] = {-grad[t], -grad[t + 1], -grad[t + 2]};
@@ -449,7 +451,7 @@ __global__ void __launch_bounds__(128) pair_kernel(DeviceProblem P, const double
     const double* H = pose_H + (size_t)a * 21;
     int k = 0;
     for (int i = 0; i < 6; ++i) for (int j = i; j < 6; ++j) { const double h = H[k++]; blk[6 * i + j] = h - acc[6 * i + j]; if (j != i) blk[6 * j + i] = h - acc[6 * j + i]; }
-    for (int s = 0; s < 2; ++s) if (ta[s] >= 0) for (int k2 = 0; k2 < 3; ++k2) rhs[ta[s] + k2] = grad[P.ne_dim + ta[s] + k2] - cacc[3 * s + k2];
+    for (int s = 0; s < 2; ++s) if (ta[s] >= 0) for (int k2 = 0; k2 < 3; ++k2) rhs[ta[s] + k2] = -cacc[3 * s + k2];   // + gradient in finish_system
   } else {
     for (int k = 0; k < 36; ++k) blk[k] = -acc[k];
   }
@@ -500,7 +502,21 @@ __global__ void __launch_bounds__(256) finish_system_kernel(DeviceProblem P, con
   const double s = scale[P.ne_dim + j];
   const double d = fmin(fmax(colsq[P.ne_dim + j] * s * s, opt.min_lm_diagonal), opt.max_lm_diagonal) / (st->radius * s * s);
   if (P.sparse) S[(size_t)P.diag_slot[j / 3] * 9 + 4 * (j % 3)] += d; else S[(size_t)j * P.nf_dim + j] += d;
-  if (!is_pose_entry[j]) rhs[j] = grad[P.ne_dim + j];
+  rhs[j] = (is_pose_entry[j] ? rhs[j] : 0.0) + grad[P.ne_dim + j];
+}
+
+// Expand the block-sparse S into the dense lower triangle the Cholesky factors (mid-size systems are assembled
+// block-sparse, which avoids clearing and re-reading n^2 doubles in the assembly, and factored densely).
+__global__ void __launch_bounds__(256) bsr_to_dense_kernel(DeviceProblem P, const double* __restrict__ Sb, double* __restrict__ Sd, const LMState* st) {
+  if (!gate_run(st)) return;
+  const long long e = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (e >= P.nnzb * 9) return;
+  const int blk = (int)(e / 9), w = (int)(e - 9LL * blk), i = w / 3, j = w - 3 * i;
+  // row of this block: binary search in rowptr
+  int lo = 0, hi = P.nf;
+  while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (P.bsr_rowptr[mid] <= blk) lo = mid; else hi = mid; }
+  const int r = 3 * lo + i, c = 3 * P.bsr_col[blk] + j;
+  if (r >= c) Sd[(size_t)c * P.nf_dim + r] = Sb[e];
 }
 
 // ===================================================================================================
@@ -841,7 +857,7 @@ __global__ void __launch_bounds__(256) candidate_kernel(DeviceProblem P, const d
   __shared__ double sm[256];
   const int i = blockIdx.x * 256 + threadIdx.x;
   double ss = 0.0, cs = 0.0;
-  if (i < P.num_active) {
+  if (i < P.num_active && P.active_blocks[i] >= 0) {
     const int b = P.active_blocks[i], off = P.blk_off[b], t = P.blk_tan[b];
     if (P.blk_manifold[b] == BSNLS_MANIFOLD_QUATERNION) {
       const double d[3] = {-y[t], -y[t + 1], -y[t + 2]};
@@ -859,18 +875,25 @@ __global__ void __launch_bounds__(256) xnorm_kernel(DeviceProblem P, const doubl
   __shared__ double sm[256];
   const int i = blockIdx.x * 256 + threadIdx.x;
   double s = 0.0;
-  if (i < P.num_active) { const int b = P.active_blocks[i], off = P.blk_off[b]; for (int k = 0; k < P.blk_size[b]; ++k) s += x[off + k] * x[off + k]; }
+  if (i < P.num_active && P.active_blocks[i] >= 0) { const int b = P.active_blocks[i], off = P.blk_off[b]; for (int k = 0; k < P.blk_size[b]; ++k) s += x[off + k] * x[off + k]; }
   const double a = block_sum<256>(s, sm);
   if (threadIdx.x == 0) part[blockIdx.x] = a;
 }
 
 // Deterministic final reductions: one CTA walks a list of (array, length, op) descriptors.
-struct RedDesc { const double* src; int n; int op; int slot; };  // op 0 = sum, 1 = max
-struct RedList { RedDesc d[6]; int count; int gate; };           // gate 0 always, 1 run, 2 jac
+// red[] layout: [0, RED_NUM) sums over rank-local data (observations, landmarks) — all-reduced across ranks in the
+// sharded solve; [RED_NUM, 2 RED_NUM) sums over replicated data (generic factors, f-blocks); then local max, replicated max.
+constexpr int kRedLocalMax = 2 * RED_NUM, kRedReplMax = 2 * RED_NUM + 1, kRedSize = 2 * RED_NUM + 2;
+__device__ __forceinline__ double red_sum(const double* red, int slot) { return red[slot] + red[RED_NUM + slot]; }
+__device__ __forceinline__ double red_max(const double* red) { return fmax(red[kRedLocalMax], red[kRedReplMax]); }
+struct RedDesc { const double* src; int n; int op; int slot; };  // op 0 = sum, 1 = max; slot already offset by RED_NUM when replicated
+struct RedList { RedDesc d[10]; int count; int gate; };          // gate 0 always, 1 run, 2 jac
 __global__ void __launch_bounds__(256) reduce_kernel(RedList L, double* __restrict__ red, const LMState* st) {
   if (L.gate == 1 && !gate_run(st)) return;
   if (L.gate == 2 && !gate_jac(st)) return;
   __shared__ double sm[256];
+  if (threadIdx.x < kRedSize) red[threadIdx.x] = 0.0;   // slots not produced by this phase must not carry stale sums
+  __syncthreads();
   for (int q = 0; q < L.count; ++q) {
     const RedDesc d = L.d[q];
     double v = 0.0;
@@ -898,8 +921,8 @@ __device__ __forceinline__ void finalize_checks(LMState* st, const bsnls_iterati
 // after a Jacobian evaluation: IterationZero, or the tail of HandleSuccessfulStep
 __global__ void ctrl_after_jacobian_kernel(LMState* st, const double* red, bsnls_iteration* recs, Options opt) {
   if (!gate_jac(st)) return;
-  st->x_cost = red[RED_COST]; st->fixed_cost = red[RED_FIXED]; st->accepted = 0;
-  st->grad_max = red[RED_GRAD_MAX]; st->grad_norm = sqrt(red[RED_GRAD_SQ]);
+  st->x_cost = red_sum(red, RED_COST); st->fixed_cost = red_sum(red, RED_FIXED); st->accepted = 0;
+  st->grad_max = red_max(red); st->grad_norm = sqrt(red_sum(red, RED_GRAD_SQ));
   bsnls_iteration r;
   r.iteration = st->iteration; r.step_is_valid = 1; r.step_is_successful = 1;
   r.linear_solver_iterations = st->iteration == 0 ? 0 : st->pend_linear_iters;
@@ -909,7 +932,6 @@ __global__ void ctrl_after_jacobian_kernel(LMState* st, const double* red, bsnls
   r.step_norm = st->iteration == 0 ? 0.0 : st->pend_step_norm;
   r.relative_decrease = st->iteration == 0 ? 0.0 : st->pend_relative_decrease;
   r.trust_region_radius = st->radius;
-  if (st->iteration == 0) st->x_norm = sqrt(red[RED_X_SQ]);
   st->need_jacobian = 0; st->scale_ready = 1;
   if (!isfinite(st->x_cost)) { st->done = 1; st->termination = BSNLS_FAILURE; st->message_id = MSG_NONFINITE; push_record(st, recs, r); return; }
   push_record(st, recs, r);
@@ -923,8 +945,8 @@ __global__ void ctrl_end_iteration_kernel(LMState* st, const double* red, bsnls_
   r.iteration = st->iteration; r.step_is_valid = 0; r.step_is_successful = 0; r.linear_solver_iterations = st->pcg_iters;
   r.cost = st->x_cost + st->fixed_cost; r.cost_change = 0.0; r.gradient_max_norm = st->grad_max; r.gradient_norm = st->grad_norm;
   r.step_norm = 0.0; r.relative_decrease = 0.0;
-  const double mc = red[RED_MODEL];
-  const bool solved = !st->lin_fail && isfinite(mc) && isfinite(red[RED_STEP_SQ]);
+  const double mc = red_sum(red, RED_MODEL);
+  const bool solved = !st->lin_fail && isfinite(mc) && isfinite(red_sum(red, RED_STEP_SQ));
   st->lin_fail = 0;
   if (!solved || !(mc > 0.0)) {  // HandleInvalidStep
     st->num_invalid += 1;
@@ -938,7 +960,7 @@ __global__ void ctrl_end_iteration_kernel(LMState* st, const double* red, bsnls_
   st->num_invalid = 0;
   r.step_is_valid = 1;
   st->model_cost_change = mc;
-  st->step_norm = sqrt(red[RED_STEP_SQ]); st->cand_norm = sqrt(red[RED_CAND_SQ]); st->cand_cost = red[RED_CAND_COST];
+  st->step_norm = sqrt(red_sum(red, RED_STEP_SQ)); st->cand_norm = sqrt(red_sum(red, RED_CAND_SQ)); st->cand_cost = red_sum(red, RED_CAND_COST);
   r.step_norm = st->step_norm;
   // ParameterToleranceReached
   if (st->step_norm <= opt.parameter_tolerance * (st->x_norm + opt.parameter_tolerance)) {
@@ -969,7 +991,12 @@ __global__ void __launch_bounds__(256) apply_step_kernel(double* __restrict__ x,
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i < n) x[i] = xc[i];
 }
-__global__ void clear_accepted_kernel(LMState* st) { st->accepted = 0; }
+__global__ void init_xnorm_kernel(LMState* st, const double* red) { st->x_norm = sqrt(red_sum(red, RED_X_SQ)); }
+// complete parameter vector on every rank of the sharded solve: each entry is kept by its owner, then summed
+__global__ void __launch_bounds__(256) mask_owned_kernel(double* __restrict__ x, const unsigned char* __restrict__ owned, int n) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i < n && !owned[i]) x[i] = 0.0;
+}
 __global__ void set_done_kernel(LMState* st, int termination, int msg) { if (!st->done) { st->done = 1; st->termination = termination; st->message_id = msg; } }
 
 }  // namespace bsnls

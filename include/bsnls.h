@@ -249,6 +249,10 @@ int bsnls_reprojection_cost_noalloc(const double* d_values, const int32_t* d_q_o
                                     char* error_message, int32_t error_capacity);
 
 /* ---- multi-GPU: landmark-sharded solve, one process per GPU ---- */
+/* Partition used by the sharded solve: rank r keeps the landmarks [lo, hi) of the elimination order, chosen so that
+   every rank holds about the same number of observations (lm_ptr: prefix sums of observations per landmark,
+   num_landmarks + 1 entries). Host-only helper, no device needed. */
+int bsnls_shard_range(const int32_t* lm_ptr, int32_t num_landmarks, int32_t rank, int32_t world_size, int32_t* lo, int32_t* hi);
 /* 128-byte NCCL unique id, generated on rank 0 and distributed by the caller (torch.distributed). */
 int bsnls_nccl_unique_id(char id[128]);
 /* Collective over all ranks. Every rank then calls bsnls_set_problem with the SAME full problem; the
