@@ -112,7 +112,7 @@ class Solver:
         self._check(self._lib.bsnls_last_kernel_ms(self._h, C.byref(a), C.byref(b)))
         return a.value, b.value
 
-    BREAKDOWN = ("eval_reproj", "eval_generic", "landmark", "gradient", "clear_S", "pair", "generic_rows")
+    BREAKDOWN = ("eval_reproj", "eval_generic", "landmark", "gradient", "clear_S", "pair", "generic_rows", "exchange")
 
     def last_breakdown_ms(self):
         out = (C.c_float * 8)()

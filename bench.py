@@ -122,7 +122,7 @@ def run_reference(args):
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from beam_slam_b200 import cabi, host
+    from beam_slam_b200 import cabi, host, sharding
     from beam_slam_b200.solver import Solver
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -138,7 +138,7 @@ def run_ours(args):
     nobs = info["num_observations"]
     opts = host.HashGraph.synthetic_options(args.config)
     opts.device = local
-    s = Solver(opts)
+    s = sharding.create_sharded_solver(opts) if world > 1 else Solver(opts)   # landmark shard per rank, NCCL exchange
     t0 = time.time()
     s.set_problem(p)
     t_setup = time.time() - t0
@@ -168,13 +168,20 @@ def run_ours(args):
         parts.append(s.last_breakdown_ms())
     barrier()
     wall = time.time() - wall0
-    clocks = sampler.stop()
     launches = s.launch_count() - launches0
     dev_ms = sum(ev_ms) + sum(sc_ms)
     if world > 1:
         t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms = float(t.item())
+    if wall < 0.6:
+        # the timed region is shorter than nvidia-smi's sampling period: keep the same kernels running (untimed) so
+        # that the clock / throttle record is taken under the same load. Same count on every rank (collectives inside).
+        for _ in range(min(4000, int(0.8 / max(dev_ms / args.steps * 1e-3, 1e-5)) + 1)):
+            s.run_eval()
+            s.run_schur(1e4)
+    clocks = sampler.stop()
+    clocks["sampled"] = "during the timed region" if wall >= 0.6 else "same kernels looped for 0.8 s right after the timed region (region too short to sample)" 
     value = nobs * args.steps / (dev_ms * 1e-3)
 
     # end to end through the C-ABI with host buffers: H2D of the step's parameter values, eval + Schur, D2H of the cost
@@ -201,7 +208,11 @@ def run_ours(args):
 
     mean = lambda k: float(np.mean([q[k] for q in parts]))
     br = {k: mean(k) for k in Solver.BREAKDOWN}
-    eval_b, schur_b = algorithmic_bytes(info, nf_dim, True)
+    dense = nf_dim <= 3000
+    eval_b, schur_b = algorithmic_bytes(info, nf_dim, dense)
+    if not dense:
+        schur_b += 72 * (2 * summ.reduced_system_nnz_blocks - nf_dim // 3)   # block-sparse S write (full symmetric storage)
+    eval_b, schur_b = eval_b // world, schur_b // world   # per-rank share of the algorithmic bytes
     stages = {"eval_reproj": (br["eval_reproj"], eval_b), "schur(landmark+pair+rows)": (br["landmark"] + br["pair"] + br["generic_rows"] + br["clear_S"], schur_b)}
     dom = max(stages, key=lambda k: stages[k][0])
     dom_ms, dom_bytes = stages[dom]
@@ -212,10 +223,10 @@ def run_ours(args):
            "config": {"workload": CONFIG_NAMES[args.config], "scale": args.scale, "keyframes": info["num_keyframes"],
                       "landmarks": info["num_landmarks"], "observations": nobs, "reduced_system_dim": nf_dim,
                       "l2": "inputs larger than L2 (Jacobian + elimination records %.0f MB)" % (352e-6 * nobs) if nobs * 352 > 130e6 else "inputs fit in L2 (latency-bound config)",
-                      "multi_gpu": "single GPU" if world == 1 else "replicated (landmark sharding lands in a later round)"},
+                      "multi_gpu": "single GPU" if world == 1 else f"landmarks sharded over {world} GPUs, NCCL all-reduce of the reduced camera system per step"},
            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                         "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms": dom_ms,
-                        "whole_pass_frac": (eval_b + schur_b) / (dev_ms / args.steps * 1e-3) / 1e9 / peak},
+                        "whole_pass_frac": (eval_b + schur_b) / (dev_ms / args.steps * 1e-3) / 1e9 / peak, "per": "GPU"},
            "kernel_ms": br,
            "e2e": {"value": e2e, "unit": "obs/s", "h2d_bytes_per_step": int(8 * p.num_values), "d2h_bytes_per_step": 8 * 16},
            "gpu_launches": launches, "clocks": clocks,

@@ -224,7 +224,8 @@ int bsnls_run_schur(bsnls_handle* handle, double radius);
 int bsnls_last_kernel_ms(bsnls_handle* handle, float* eval_ms, float* schur_ms);
 /* per-kernel split of the last run_eval + run_schur, milliseconds:
    [0] reprojection eval, [1] generic-factor eval, [2] landmark elimination, [3] gradient / column norms,
-   [4] reduced-system clear, [5] pair (S assembly), [6] generic-factor S rows + damping, [7] unused */
+   [4] reduced-system clear, [5] pair (S assembly), [6] generic-factor S rows + damping,
+   [7] NCCL exchange of the reduced system (sharded solve; 0 on one GPU) */
 int bsnls_last_breakdown_ms(bsnls_handle* handle, float out[8]);
 /* number of kernel launches issued by this handle since creation */
 int64_t bsnls_launch_count(const bsnls_handle* handle);
