@@ -51,6 +51,10 @@ struct bsnls_handle {
   std::string error;
   int64_t launches = 0;
   bool has_problem = false, jac_valid = false;
+  // one LM pass / the closing Jacobian pass captured as CUDA graphs (single GPU): the kernel sequence is static, every
+  // kernel is gated by the device state, so replaying the graph replaces ~40 stream launches per iteration
+  int64_t graph_pass_launches = 0, graph_tail_launches = 0; const void* graph_recs = nullptr;
+  cudaGraphExec_t graph_pass = nullptr, graph_tail = nullptr; bool graphs_valid = false; bool use_graphs = true;
   float last_eval_ms = 0, last_schur_ms = 0;
   int rank = 0, world = 1; NcclComm comm = nullptr;
   int lm_lo = 0, lm_hi = 0, ne_global = 0, nobs_global = 0, nb_act_e = 0; DevMem d_owned;
@@ -369,6 +373,8 @@ void bsnls_destroy(bsnls_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
+  if (h->graph_pass) cudaGraphExecDestroy(h->graph_pass);
+  if (h->graph_tail) cudaGraphExecDestroy(h->graph_tail);
   if (h->comm) Nccl().CommDestroy(h->comm);
   if (h->stream) cudaStreamDestroy(h->stream);
   if (h->ev0) cudaEventDestroy(h->ev0);
@@ -383,6 +389,7 @@ int bsnls_set_options(bsnls_handle* h, const bsnls_options* o) {
   std::string why;
   if (!ValidOptions(*o, &why)) return h->fail(BSNLS_ERR_INVALID, "invalid options: %s", why.c_str());
   const int dev = h->opt.device; h->opt = *o; h->opt.device = dev;
+  h->graphs_valid = false;   // kernel arguments (options) are baked into the captured graphs
   return BSNLS_OK;
 }
 
@@ -744,7 +751,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   P.sparse = h->sparse ? 1 : 0; P.nnzb = h->nnzb; P.bsr_rowptr = h->d_bsr_rowptr.as<int>(); P.bsr_col = h->d_bsr_col.as<int>();
   P.diag_slot = h->d_diag_slot.as<int>(); P.pair_slot = h->d_pair_slot.as<int>(); P.gd_slot = h->d_gd_slot.as<int>();
   CK(cudaStreamSynchronize(s));  // host vectors above go out of scope
-  h->has_problem = true;
+  h->has_problem = true; h->graphs_valid = false;
   return BSNLS_OK;
 }
 
@@ -788,17 +795,53 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
   // a wall-clock budget is a per-process decision; ranks of a sharded solve must issue identical collectives, so the
   // budget is only honoured on a single GPU
   const bool timed = h->opt.max_solver_time_in_seconds < 1e8 && h->world == 1;
-  for (int pass = 0; pass <= max_it; ++pass) {
+  auto enqueue_tail = [&]() -> int {   // Jacobian pass that closes an accepted step (or IterationZero)
     EnqueueEval(h);
-    if (pass < max_it) EnqueueLandmark(h, o);
-    if ((rc = EnqueueGradient(h, o)) != BSNLS_OK) return rc;
+    int r2 = EnqueueGradient(h, o);
     LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
-    if (pass == max_it) break;
-    if ((rc = EnqueueAssemble(h, o)) != BSNLS_OK) return rc;
-    if (h->pcg) { rc = EnqueueSparseSolve(h); if (rc != BSNLS_OK) return rc; } else EnqueueDenseSolve(h);
-    if ((rc = EnqueueStep(h)) != BSNLS_OK) return rc;
+    return r2;
+  };
+  auto enqueue_pass = [&]() -> int {   // one LM iteration
+    EnqueueEval(h);
+    EnqueueLandmark(h, o);
+    int r2 = EnqueueGradient(h, o);
+    if (r2 != BSNLS_OK) return r2;
+    LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
+    if ((r2 = EnqueueAssemble(h, o)) != BSNLS_OK) return r2;
+    if (h->pcg) { r2 = EnqueueSparseSolve(h); if (r2 != BSNLS_OK) return r2; } else EnqueueDenseSolve(h);
+    if ((r2 = EnqueueStep(h)) != BSNLS_OK) return r2;
     LAUNCH(h, ctrl_end_iteration_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
     LAUNCH(h, apply_step_kernel, BlocksFor((int)h->num_values, 256), 256, h->d_x.as<double>(), h->d_xc.as<double>(), (int)h->num_values, st);
+    return BSNLS_OK;
+  };
+  // Small reduced systems are launch-latency bound: replay captured graphs instead of enqueuing kernel by kernel.
+  const bool graphs = h->use_graphs && h->world == 1 && h->P.nf_dim <= 4096 && !h->pcg;
+  if (graphs && (!h->graphs_valid || h->graph_recs != recs)) {
+    if (h->graph_pass) { cudaGraphExecDestroy(h->graph_pass); h->graph_pass = nullptr; }
+    if (h->graph_tail) { cudaGraphExecDestroy(h->graph_tail); h->graph_tail = nullptr; }
+    cudaGraph_t g = nullptr;
+    const int64_t launches_before = h->launches;
+    CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+    rc = enqueue_pass();
+    cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
+    if (rc != BSNLS_OK || ce != cudaSuccess) return h->fail(BSNLS_ERR_CUDA, "graph capture (pass): %s", cudaGetErrorString(ce));
+    CK(cudaGraphInstantiate(&h->graph_pass, g, 0)); cudaGraphDestroy(g);
+    h->graph_pass_launches = h->launches - launches_before;
+    CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+    rc = enqueue_tail();
+    ce = cudaStreamEndCapture(h->stream, &g);
+    if (rc != BSNLS_OK || ce != cudaSuccess) return h->fail(BSNLS_ERR_CUDA, "graph capture (tail): %s", cudaGetErrorString(ce));
+    CK(cudaGraphInstantiate(&h->graph_tail, g, 0)); cudaGraphDestroy(g);
+    h->graph_tail_launches = h->launches - launches_before - h->graph_pass_launches; h->launches = launches_before;
+    h->graph_recs = recs;
+    h->graphs_valid = true;
+  }
+  for (int pass = 0; pass <= max_it; ++pass) {
+    if (pass == max_it) {
+      if (graphs) { CK(cudaGraphLaunch(h->graph_tail, h->stream)); h->launches += h->graph_tail_launches; } else if ((rc = enqueue_tail()) != BSNLS_OK) return rc;
+      break;
+    }
+    if (graphs) { CK(cudaGraphLaunch(h->graph_pass, h->stream)); h->launches += h->graph_pass_launches; } else if ((rc = enqueue_pass()) != BSNLS_OK) return rc;
     if (timed || (pass & 3) == 3) {
       // poll the device state so that converged solves stop enqueuing; with a time budget also check the clock
       LMState hs; CK(cudaMemcpyAsync(&hs, st, sizeof(hs), cudaMemcpyDeviceToHost, h->stream)); CK(cudaStreamSynchronize(h->stream));
@@ -806,8 +849,7 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
       const double el = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
       if (timed && el >= h->opt.max_solver_time_in_seconds) {
         // an accepted step still needs its Jacobian pass to be recorded; then stop (NO_CONVERGENCE)
-        EnqueueEval(h); if ((rc = EnqueueGradient(h, o)) != BSNLS_OK) return rc;
-        LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
+        if ((rc = enqueue_tail()) != BSNLS_OK) return rc;
         LAUNCH(h, set_done_kernel, 1, 1, st, (int)BSNLS_NO_CONVERGENCE, (int)MSG_MAX_TIME);
         break;
       }
