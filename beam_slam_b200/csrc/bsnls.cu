@@ -99,6 +99,8 @@ struct bsnls_handle {
   do { cudaError_t _e = (expr);                                                                      \
     if (_e != cudaSuccess) return h->fail(BSNLS_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(_e)); } while (0)
 #define MARK(h, i) do { if ((h)->profiling) cudaEventRecord((h)->pev[i], (h)->stream); } while (0)
+#define LAUNCH_SMEM(h, kernel, grid, block, smem, ...)                                                 \
+  do { kernel<<<(grid), (block), (smem), (h)->stream>>>(__VA_ARGS__); (h)->launches++; } while (0)
 #define LAUNCH(h, kernel, grid, block, ...)                                                            \
   do { kernel<<<(grid), (block), 0, (h)->stream>>>(__VA_ARGS__); (h)->launches++; } while (0)
 
@@ -253,6 +255,11 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     cudaMemsetAsync(Sd, 0, sizeof(double) * (size_t)n * n, h->stream);
     LAUNCH(h, bsr_to_dense_kernel, (unsigned)((h->nnzb * 9 + 255) / 256), 256, h->P, h->d_S.as<double>(), Sd, st);
   }
+  if (n <= kSmallMax) {  // sliding windows: factor + solve in one single-CTA launch
+    const size_t smem = sizeof(double) * (size_t)std::max(1, n - 1) * (kNB + 1);
+    LAUNCH_SMEM(h, chol_small_kernel, 1, 1024, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
+    return;
+  }
   for (int j0 = 0; j0 < n; j0 += kNB) {
     const int nb = std::min(kNB, n - j0), rest = n - j0 - nb;
     LAUNCH(h, chol_panel_kernel, BlocksFor(rest, 64), 64, Sd, n, j0, st);
@@ -277,7 +284,7 @@ int EnqueueStep(bsnls_handle* h) {  // phase D3: back-substitution, model cost, 
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
   if (h->ne) switch (h->G) { case 4: LaunchBacksub<4>(h); break; case 8: LaunchBacksub<8>(h); break;
                              case 16: LaunchBacksub<16>(h); break; default: LaunchBacksub<32>(h); }
-  LAUNCH(h, gf_model_kernel, BlocksFor(std::max(h->ngf, std::min(P.nf_dim, 1 << 16)), 128), 128, P, h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_yf.as<double>(), h->d_y.as<double>(),
+  LAUNCH(h, gf_model_kernel, BlocksFor(std::max(32 * h->ngf, std::min(P.nf_dim, 1 << 16)), 128), 128, P, h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_yf.as<double>(), h->d_y.as<double>(),
          h->d_model_part.as<double>() + h->nb_lm, st);
   LAUNCH(h, candidate_kernel, h->nb_act, 256, P, h->d_x.as<double>(), h->d_y.as<double>(), h->d_xc.as<double>(), h->d_step_part.as<double>(), h->d_candsq_part.as<double>(), st);
   if (h->nobs) LAUNCH(h, eval_reproj_kernel<1>, h->nb_obs, 256, P, h->d_xc.as<double>(), nullptr, h->d_cand_part.as<double>(), st);
@@ -364,6 +371,7 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
       (e = cudaEventCreate(&h->ev2)) != cudaSuccess) {
     g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
   }
+  if ((e = cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * kSmallMax * (kNB + 1)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   for (auto& ev : h->pev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   *out = h;
   return BSNLS_OK;

@@ -614,6 +614,131 @@ __global__ void __launch_bounds__(128) chol_update_kernel(double* __restrict__ S
         if (row < n && col < n && row >= col) S[(size_t)col * n + row] -= acc[a][b][h];
       }
 }
+// Small reduced systems (n <= 512: the sliding windows): the whole factorisation and both triangular solves in ONE
+// single-CTA launch. The matrix stays in global memory (L2 resident, <= 2 MB); per 32-column panel the diagonal block
+// is factored by one warp in shared memory, the panel rows are solved one row per thread, the panel is staged in
+// shared memory and the trailing matrix is updated in 4x4 register micro-tiles.
+constexpr int kSmallMax = 512;
+__global__ void __launch_bounds__(1024) chol_small_kernel(double* __restrict__ S, int n, const double* __restrict__ rhs,
+                                                          double* __restrict__ y, LMState* st) {
+  extern __shared__ double smem_dyn[];
+  __shared__ double D[kNB][kNB + 1];
+  __shared__ double xs[kNB];
+  __shared__ int failed;
+  if (!gate_run(st) || st->lin_fail) return;
+  const int tid = threadIdx.x;
+  double* Ls = smem_dyn;                 // panel rows below the diagonal block: [rows][kNB + 1]
+  if (tid == 0) failed = 0;
+  for (int j0 = 0; j0 < n; j0 += kNB) {
+    const int nb = min(kNB, n - j0), r0 = j0 + nb, rest = n - r0;
+    { const int r = tid % kNB, c = tid / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(j0 + c) * n + j0 + r] : 0.0; }
+    __syncthreads();
+    if (tid < 32) {
+      for (int k = 0; k < nb; ++k) {
+        if (tid == k) { const double d = D[k][k]; if (!(d > 0.0)) failed = 1; D[k][k] = sqrt(d); }
+        __syncwarp();
+        const double dk = D[k][k];
+        if (tid > k && tid < nb) D[tid][k] /= dk;
+        __syncwarp();
+        if (tid > k && tid < nb) { const double lik = D[tid][k]; for (int j = k + 1; j <= tid; ++j) D[tid][j] -= lik * D[j][k]; }
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+    { const int r = tid % kNB, c = tid / kNB; if (r < nb && c < nb && r >= c) S[(size_t)(j0 + c) * n + j0 + r] = D[r][c]; }
+    // panel solve: one row per thread, result to global and to the shared panel
+    for (int i = tid; i < rest; i += 1024) {
+      double xv[kNB];
+#pragma unroll
+      for (int c = 0; c < kNB; ++c) {
+        if (c < nb) {
+          double a = S[(size_t)(j0 + c) * n + r0 + i];
+#pragma unroll
+          for (int p = 0; p < kNB; ++p) if (p < c) a -= xv[p] * D[c][p];
+          xv[c] = a / D[c][c];
+          S[(size_t)(j0 + c) * n + r0 + i] = xv[c];
+          Ls[i * (kNB + 1) + c] = xv[c];
+        } else { xv[c] = 0.0; Ls[i * (kNB + 1) + c] = 0.0; }
+      }
+    }
+    __syncthreads();
+    // trailing update A[r0+i][r0+j] -= sum_p L[i][p] L[j][p], i >= j, in 4x4 micro-tiles
+    const int mt = (rest + 3) / 4;
+    for (int t = tid; t < mt * mt; t += 1024) {
+      const int ti = t / mt, tj = t % mt;
+      if (ti < tj) continue;
+      double acc[4][4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+      const int i0 = 4 * ti, c0 = 4 * tj;
+      for (int p = 0; p < nb; ++p) {
+        double li[4], lj[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) { li[a] = (i0 + a < rest) ? Ls[(i0 + a) * (kNB + 1) + p] : 0.0; lj[a] = (c0 + a < rest) ? Ls[(c0 + a) * (kNB + 1) + p] : 0.0; }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[a][b] += li[a] * lj[b];
+      }
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const int i = i0 + a, j = c0 + b;
+          if (i < rest && j < rest && i >= j) S[(size_t)(r0 + j) * n + r0 + i] -= acc[a][b];
+        }
+    }
+    __syncthreads();
+  }
+  if (failed) { if (tid == 0) st->lin_fail = 1; return; }   // `failed` is uniform after the last barrier
+  // triangular solves L z = rhs, L^T y = z
+  for (int i = tid; i < n; i += 1024) y[i] = rhs[i];
+  __syncthreads();
+  for (int jb = 0; jb < n; jb += kNB) {
+    const int nb = min(kNB, n - jb);
+    { const int r = tid % kNB, c = tid / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(jb + c) * n + jb + r] : 0.0; }
+    __syncthreads();
+    if (tid < 32) {
+      double b = tid < nb ? y[jb + tid] : 0.0;
+      for (int k = 0; k < nb; ++k) {
+        const double yk = __shfl_sync(0xffffffffu, b, k) / D[k][k];
+        if (tid == k) b = yk; else if (tid > k) b -= D[tid][k] * yk;
+      }
+      if (tid < nb) { y[jb + tid] = b; xs[tid] = b; }
+    }
+    __syncthreads();
+    for (int i = jb + nb + tid; i < n; i += 1024) {
+      double a = y[i];
+      for (int k = 0; k < nb; ++k) a -= S[(size_t)(jb + k) * n + i] * xs[k];
+      y[i] = a;
+    }
+    __syncthreads();
+  }
+  for (int bb = (n + kNB - 1) / kNB - 1; bb >= 0; --bb) {
+    const int jb = bb * kNB, nb = min(kNB, n - jb);
+    { const int r = tid % kNB, c = tid / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(jb + c) * n + jb + r] : 0.0; }
+    __syncthreads();
+    if (tid < 32) {
+      double b = tid < nb ? y[jb + tid] : 0.0;
+      for (int k = nb - 1; k >= 0; --k) {
+        const double xk = __shfl_sync(0xffffffffu, b, k) / D[k][k];
+        if (tid == k) b = xk; else if (tid < k) b -= D[k][tid] * xk;
+      }
+      if (tid < nb) { y[jb + tid] = b; xs[tid] = b; }
+    }
+    __syncthreads();
+    for (int i = tid; i < jb; i += 1024) {
+      double a = y[i];
+      const double* col = S + (size_t)i * n + jb;
+      for (int k = 0; k < nb; ++k) a -= col[k] * xs[k];
+      y[i] = a;
+    }
+    __syncthreads();
+  }
+}
+
 // Triangular solves L y = b, L^T x = y with the factor in the lower triangle of S (single CTA, blocked by 32).
 __global__ void __launch_bounds__(1024) chol_solve_kernel(const double* __restrict__ S, int n, const double* __restrict__ rhs,
                                                           double* __restrict__ y, LMState* st) {
@@ -824,28 +949,28 @@ __global__ void __launch_bounds__(256) backsub_kernel(DeviceProblem P, const dou
   const double tot = block_sum<256>(mc, sm);
   if (threadIdx.x == 0) model_part[blockIdx.x] = tot;
 }
-// model cost change of the generic factors + copy y_f into the full step vector. One thread per factor.
+// model cost change of the generic factors + copy y_f into the full step vector. One warp per factor: lane c holds the
+// step entry of tangent column c (<= 30 columns), rows are reduced with a butterfly.
 __global__ void __launch_bounds__(128) gf_model_kernel(DeviceProblem P, const double* __restrict__ gfJ,
                                                        const double* __restrict__ gfR, const double* __restrict__ yf,
                                                        double* __restrict__ y, double* __restrict__ model_part, const LMState* st) {
   if (!gate_run(st) || st->lin_fail) return;
   const int tid = blockIdx.x * 128 + threadIdx.x;
   for (int j = tid; j < P.nf_dim; j += gridDim.x * 128) y[P.ne_dim + j] = yf[j];
-  if (tid >= P.num_gf) return;
-  const int f = tid, nb = P.gf_nblk[f], nr = P.gf_nres[f], ncol = 3 * nb;
+  const int f = tid >> 5, lane = threadIdx.x & 31;
+  if (f >= P.num_gf) return;
+  const int nb = P.gf_nblk[f], nr = P.gf_nres[f], ncol = 3 * nb;
   const double* J = gfJ + P.gf_joff[f]; const double* R = gfR + P.gf_roff[f];
-  double yl[3 * kGfMaxBlocks];
-  for (int b = 0; b < nb; ++b) {
-    const int t = P.blk_tan[P.gf_blocks[f * kGfMaxBlocks + b]];
-    for (int k = 0; k < 3; ++k) yl[3 * b + k] = t >= 0 ? yf[t - P.ne_dim + k] : 0.0;
-  }
+  double yl = 0.0;
+  if (lane < ncol) { const int t = P.blk_tan[P.gf_blocks[f * kGfMaxBlocks + lane / 3]]; yl = t >= 0 ? yf[t - P.ne_dim + lane % 3] : 0.0; }
   double mc = 0.0;
   for (int i = 0; i < nr; ++i) {
-    double m = 0.0;
-    for (int c = 0; c < ncol; ++c) m += J[i * ncol + c] * yl[c];
+    double m = lane < ncol ? J[i * ncol + lane] * yl : 0.0;
+#pragma unroll
+    for (int w = 1; w < 32; w <<= 1) m += __shfl_xor_sync(0xffffffffu, m, w);
     mc += m * (R[i] - 0.5 * m);
   }
-  model_part[f] = mc;
+  if (lane == 0) model_part[f] = mc;
 }
 
 // candidate point x_cand = x (+) (-y) and the ambient norms ParameterToleranceReached needs.
