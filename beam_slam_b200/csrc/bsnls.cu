@@ -83,7 +83,7 @@ struct bsnls_handle {
       d_gf_roff, d_pair_a, d_pair_b, d_pair_ptr, d_item_i, d_item_j, d_fg_ptr, d_fg_fac, d_fg_lb, d_gd_row, d_gd_col,
       d_gd_ptr, d_gd_fac, d_gd_bi, d_gd_bj, d_is_pose, d_bsr_rowptr, d_bsr_col, d_diag_slot, d_pair_slot, d_gd_slot,
       d_pcg_x, d_pcg_r, d_pcg_z, d_pcg_p, d_pcg_Ap, d_pcg_Minv, d_pcg_part;
-  DevMem d_Sdense, d_gradL, d_colsqL, d_gradS, d_colsqS;
+  DevMem d_invd, d_Sdense, d_gradL, d_colsqL, d_gradS, d_colsqS;
   DevMem d_x, d_xc, d_x0, d_Jrec, d_Vrec, d_minv, d_grad, d_colsq, d_scale, d_y, d_yf, d_rhs, d_S, d_poseH, d_gfJ,
       d_gfR, d_cost_part, d_cand_part, d_model_part, d_step_part, d_candsq_part, d_gsq_part, d_gmax_part, d_xsq_part,
       d_red, d_state, d_recs;
@@ -256,13 +256,14 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     LAUNCH(h, bsr_to_dense_kernel, (unsigned)((h->nnzb * 9 + 255) / 256), 256, h->P, h->d_S.as<double>(), Sd, st);
   }
   if (n <= kSmallMax) {  // sliding windows: factor + solve in one single-CTA launch
-    const size_t smem = sizeof(double) * (size_t)std::max(1, n - 1) * (kNB + 1);
+    const size_t smem = sizeof(double) * ((size_t)kSmallMax * (kNB + 1) + kSmallMax);
     LAUNCH_SMEM(h, chol_small_kernel, 1, 1024, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
     return;
   }
   for (int j0 = 0; j0 < n; j0 += kNB) {
     const int nb = std::min(kNB, n - j0), rest = n - j0 - nb;
-    LAUNCH(h, chol_panel_kernel, BlocksFor(rest, 64), 64, Sd, n, j0, st);
+    LAUNCH(h, chol_diag_kernel, 1, 256, Sd, n, j0, h->d_invd.as<double>(), st);
+    if (rest > 0) LAUNCH(h, chol_trsm_kernel, BlocksFor(rest, 256), 256, Sd, n, j0, h->d_invd.as<double>(), st);
     if (rest > 0) { const int T = (rest + 63) / 64; LAUNCH(h, chol_update_kernel, dim3(T, T), 128, Sd, n, j0, st); }
   }
   LAUNCH(h, chol_solve_kernel, 1, 1024, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
@@ -371,7 +372,7 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
       (e = cudaEventCreate(&h->ev2)) != cudaSuccess) {
     g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
   }
-  if ((e = cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * kSmallMax * (kNB + 1)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
+  if ((e = cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kSmallMax * (kNB + 1) + kSmallMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   for (auto& ev : h->pev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   *out = h;
   return BSNLS_OK;
@@ -736,7 +737,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(h->d_model_part.alloc(sizeof(double) * (h->nb_lm + h->ngf + 1)));
   CK(h->d_step_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_candsq_part.alloc(sizeof(double) * h->nb_act));
   CK(h->d_gsq_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_gmax_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_xsq_part.alloc(sizeof(double) * h->nb_act));
-  CK(h->d_red.alloc(sizeof(double) * 32)); CK(h->d_state.alloc(sizeof(LMState)));
+  CK(h->d_red.alloc(sizeof(double) * 32)); CK(h->d_invd.alloc(sizeof(double) * 64)); CK(h->d_state.alloc(sizeof(LMState)));
   CK(cudaMemcpyAsync(h->d_x.p, pr->block_values, sizeof(double) * off, cudaMemcpyHostToDevice, s));
   CK(cudaMemsetAsync(h->d_y.p, 0, sizeof(double) * ntan, s));
 

@@ -526,33 +526,55 @@ __global__ void __launch_bounds__(256) bsr_to_dense_kernel(DeviceProblem P, cons
 // (mma.sync.m8n8k4.f64), 64x64 tiles, operands staged in shared memory.
 // ===================================================================================================
 constexpr int kNB = 32;
-__global__ void __launch_bounds__(64) chol_panel_kernel(double* __restrict__ S, int n, int j0, LMState* st) {
+// Cholesky of the nb x nb diagonal block held in shared memory, all NT threads of the CTA cooperating: step k scales
+// column k, then every thread updates its share of the trailing entries (one barrier-separated rank-1 update per
+// step). invd[k] receives 1 / L[k][k]. Returns through *failed (shared) whether a pivot was not positive.
+template <int NT>
+__device__ __forceinline__ void chol_diag_block(double (*D)[kNB + 1], double* invd, int nb, int* failed) {
+  const int tid = threadIdx.x;
+  for (int k = 0; k < nb; ++k) {
+    if (tid == 0) { const double d = D[k][k]; if (!(d > 0.0)) *failed = 1; const double l = sqrt(d); D[k][k] = l; invd[k] = 1.0 / l; }
+    __syncthreads();
+    const double ik = invd[k];
+    for (int i = k + 1 + tid; i < nb; i += NT) D[i][k] *= ik;
+    __syncthreads();
+    const int m = nb - k - 1;   // trailing block is m x m, lower part only
+    for (int e = tid; e < m * m; e += NT) { const int i = k + 1 + e / m, j = k + 1 + e % m; if (i >= j) D[i][j] -= D[i][k] * D[j][k]; }
+    __syncthreads();
+  }
+}
+// Panel step for larger systems, two launches so that no CTA can read a diagonal block another CTA is overwriting:
+// chol_diag_kernel (1 CTA) factors the diagonal block in place and leaves 1/L[k][k] in invd_out; chol_trsm_kernel
+// solves the rows below it, one row per thread.
+__global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ S, int n, int j0, double* __restrict__ invd_out, LMState* st) {
   __shared__ double D[kNB][kNB + 1];
-  __shared__ int go;
+  __shared__ double invd[kNB];
+  __shared__ int failed;
+  if (!gate_run(st) || st->lin_fail) return;   // single CTA; lin_fail is written only after the last barrier
   const int nb = min(kNB, n - j0), tid = threadIdx.x;
-  if (tid == 0) go = gate_run(st) && !st->lin_fail;   // one read per CTA: lin_fail may be set by a sibling CTA
-  __syncthreads();
-  if (!go) return;
-  for (int e = tid; e < kNB * kNB; e += 64) {
+  if (tid == 0) failed = 0;
+  for (int e = tid; e < kNB * kNB; e += 256) {
     const int r = e % kNB, c = e / kNB;
     D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(j0 + c) * n + j0 + r] : 0.0;
   }
   __syncthreads();
-  if (tid < 32) {
-    for (int k = 0; k < nb; ++k) {
-      if (tid == k) { const double d = D[k][k]; if (!(d > 0.0)) { st->lin_fail = 1; } D[k][k] = sqrt(d); }
-      __syncwarp();
-      const double dk = D[k][k];
-      if (tid > k && tid < nb) D[tid][k] /= dk;
-      __syncwarp();
-      if (tid > k && tid < nb) { const double lik = D[tid][k]; for (int j = k + 1; j <= tid; ++j) D[tid][j] -= lik * D[j][k]; }
-      __syncwarp();
-    }
+  chol_diag_block<256>(D, invd, nb, &failed);
+  for (int e = tid; e < kNB * kNB; e += 256) { const int r = e % kNB, c = e / kNB; if (r < nb && c < nb && r >= c) S[(size_t)(j0 + c) * n + j0 + r] = D[r][c]; }
+  if (tid < kNB) invd_out[tid] = tid < nb ? invd[tid] : 0.0;
+  if (failed && tid == 0) st->lin_fail = 1;
+}
+__global__ void __launch_bounds__(256) chol_trsm_kernel(double* __restrict__ S, int n, int j0, const double* __restrict__ invd_in, const LMState* st) {
+  __shared__ double D[kNB][kNB + 1];
+  __shared__ double invd[kNB];
+  if (!gate_run(st) || st->lin_fail) return;   // both written by earlier kernels only
+  const int nb = min(kNB, n - j0), tid = threadIdx.x;
+  for (int e = tid; e < kNB * kNB; e += 256) {
+    const int r = e % kNB, c = e / kNB;
+    D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(j0 + c) * n + j0 + r] : 0.0;
   }
+  if (tid < kNB) invd[tid] = invd_in[tid];
   __syncthreads();
-  if (blockIdx.x == 0)
-    for (int e = tid; e < kNB * kNB; e += 64) { const int r = e % kNB, c = e / kNB; if (r < nb && c < nb && r >= c) S[(size_t)(j0 + c) * n + j0 + r] = D[r][c]; }
-  const int row = j0 + nb + blockIdx.x * 64 + tid;
+  const int row = j0 + nb + blockIdx.x * 256 + tid;
   if (row >= n) return;
   double xv[kNB];
 #pragma unroll
@@ -561,7 +583,7 @@ __global__ void __launch_bounds__(64) chol_panel_kernel(double* __restrict__ S, 
       double a = S[(size_t)(j0 + c) * n + row];
 #pragma unroll
       for (int p = 0; p < kNB; ++p) if (p < c) a -= xv[p] * D[c][p];
-      xv[c] = a / D[c][c];
+      xv[c] = a * invd[c];
       S[(size_t)(j0 + c) * n + row] = xv[c];
     } else xv[c] = 0.0;
   }
@@ -624,27 +646,19 @@ __global__ void __launch_bounds__(1024) chol_small_kernel(double* __restrict__ S
   extern __shared__ double smem_dyn[];
   __shared__ double D[kNB][kNB + 1];
   __shared__ double xs[kNB];
+  __shared__ double invd[kNB];
   __shared__ int failed;
   if (!gate_run(st) || st->lin_fail) return;
   const int tid = threadIdx.x;
   double* Ls = smem_dyn;                 // panel rows below the diagonal block: [rows][kNB + 1]
+  double* invdiag = smem_dyn + (size_t)kSmallMax * (kNB + 1);   // 1 / L[k][k] of the whole factor (n entries)
   if (tid == 0) failed = 0;
   for (int j0 = 0; j0 < n; j0 += kNB) {
     const int nb = min(kNB, n - j0), r0 = j0 + nb, rest = n - r0;
     { const int r = tid % kNB, c = tid / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(j0 + c) * n + j0 + r] : 0.0; }
     __syncthreads();
-    if (tid < 32) {
-      for (int k = 0; k < nb; ++k) {
-        if (tid == k) { const double d = D[k][k]; if (!(d > 0.0)) failed = 1; D[k][k] = sqrt(d); }
-        __syncwarp();
-        const double dk = D[k][k];
-        if (tid > k && tid < nb) D[tid][k] /= dk;
-        __syncwarp();
-        if (tid > k && tid < nb) { const double lik = D[tid][k]; for (int j = k + 1; j <= tid; ++j) D[tid][j] -= lik * D[j][k]; }
-        __syncwarp();
-      }
-    }
-    __syncthreads();
+    chol_diag_block<1024>(D, invd, nb, &failed);
+    if (tid < nb) invdiag[j0 + tid] = invd[tid];
     { const int r = tid % kNB, c = tid / kNB; if (r < nb && c < nb && r >= c) S[(size_t)(j0 + c) * n + j0 + r] = D[r][c]; }
     // panel solve: one row per thread, result to global and to the shared panel
     for (int i = tid; i < rest; i += 1024) {
@@ -655,7 +669,7 @@ __global__ void __launch_bounds__(1024) chol_small_kernel(double* __restrict__ S
           double a = S[(size_t)(j0 + c) * n + r0 + i];
 #pragma unroll
           for (int p = 0; p < kNB; ++p) if (p < c) a -= xv[p] * D[c][p];
-          xv[c] = a / D[c][c];
+          xv[c] = a * invd[c];
           S[(size_t)(j0 + c) * n + r0 + i] = xv[c];
           Ls[i * (kNB + 1) + c] = xv[c];
         } else { xv[c] = 0.0; Ls[i * (kNB + 1) + c] = 0.0; }
@@ -703,7 +717,7 @@ __global__ void __launch_bounds__(1024) chol_small_kernel(double* __restrict__ S
     if (tid < 32) {
       double b = tid < nb ? y[jb + tid] : 0.0;
       for (int k = 0; k < nb; ++k) {
-        const double yk = __shfl_sync(0xffffffffu, b, k) / D[k][k];
+        const double yk = __shfl_sync(0xffffffffu, b, k) * invdiag[jb + k];
         if (tid == k) b = yk; else if (tid > k) b -= D[tid][k] * yk;
       }
       if (tid < nb) { y[jb + tid] = b; xs[tid] = b; }
@@ -723,7 +737,7 @@ __global__ void __launch_bounds__(1024) chol_small_kernel(double* __restrict__ S
     if (tid < 32) {
       double b = tid < nb ? y[jb + tid] : 0.0;
       for (int k = nb - 1; k >= 0; --k) {
-        const double xk = __shfl_sync(0xffffffffu, b, k) / D[k][k];
+        const double xk = __shfl_sync(0xffffffffu, b, k) * invdiag[jb + k];
         if (tid == k) b = xk; else if (tid < k) b -= D[k][tid] * xk;
       }
       if (tid < nb) { y[jb + tid] = b; xs[tid] = b; }
