@@ -256,8 +256,8 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     LAUNCH(h, bsr_to_dense_kernel, (unsigned)((h->nnzb * 9 + 255) / 256), 256, h->P, h->d_S.as<double>(), Sd, st);
   }
   if (n <= kSmallMax) {  // sliding windows: factor + solve in one single-CTA launch
-    const size_t smem = sizeof(double) * ((size_t)kSmallMax * (kNB + 1) + kSmallMax);
-    LAUNCH_SMEM(h, chol_small_kernel, 1, 1024, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
+    const size_t smem = sizeof(double) * ((size_t)kSmallMax * kNB + kSmallMax);
+    LAUNCH_SMEM(h, chol_small_kernel, 1, kSmallThreads, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
     return;
   }
   for (int j0 = 0; j0 < n; j0 += kNB) {
@@ -372,7 +372,7 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
       (e = cudaEventCreate(&h->ev2)) != cudaSuccess) {
     g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
   }
-  if ((e = cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kSmallMax * (kNB + 1) + kSmallMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
+  if ((e = cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kSmallMax * kNB + kSmallMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   for (auto& ev : h->pev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   *out = h;
   return BSNLS_OK;

@@ -640,79 +640,84 @@ __global__ void __launch_bounds__(128) chol_update_kernel(double* __restrict__ S
 // single-CTA launch. The matrix stays in global memory (L2 resident, <= 2 MB); per 32-column panel the diagonal block
 // is factored by one warp in shared memory, the panel rows are solved one row per thread, the panel is staged in
 // shared memory and the trailing matrix is updated in 4x4 register micro-tiles.
-constexpr int kSmallMax = 512;
-__global__ void __launch_bounds__(1024) chol_small_kernel(double* __restrict__ S, int n, const double* __restrict__ rhs,
-                                                          double* __restrict__ y, LMState* st) {
-  extern __shared__ double smem_dyn[];
+constexpr int kSmallMax = 512, kSmallThreads = 256;
+__global__ void __launch_bounds__(kSmallThreads) chol_small_kernel(double* __restrict__ S, int n, const double* __restrict__ rhs,
+                                                                   double* __restrict__ y, LMState* st) {
+  extern __shared__ __align__(16) double smem_dyn[];
   __shared__ double D[kNB][kNB + 1];
   __shared__ double xs[kNB];
   __shared__ double invd[kNB];
   __shared__ int failed;
   if (!gate_run(st) || st->lin_fail) return;
+  constexpr int NT = kSmallThreads, LDR = kSmallMax;
   const int tid = threadIdx.x;
-  double* Ls = smem_dyn;                 // panel rows below the diagonal block: [rows][kNB + 1]
-  double* invdiag = smem_dyn + (size_t)kSmallMax * (kNB + 1);   // 1 / L[k][k] of the whole factor (n entries)
+  double* Ls = smem_dyn;                                  // panel below the diagonal block, column-major: Ls[p * LDR + row]
+  double* invdiag = smem_dyn + (size_t)kNB * LDR;         // 1 / L[k][k] of the whole factor (n entries)
   if (tid == 0) failed = 0;
   for (int j0 = 0; j0 < n; j0 += kNB) {
     const int nb = min(kNB, n - j0), r0 = j0 + nb, rest = n - r0;
-    { const int r = tid % kNB, c = tid / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(j0 + c) * n + j0 + r] : 0.0; }
+    for (int e = tid; e < kNB * kNB; e += NT) { const int r = e % kNB, c = e / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(j0 + c) * n + j0 + r] : 0.0; }
     __syncthreads();
-    chol_diag_block<1024>(D, invd, nb, &failed);
+    chol_diag_block<NT>(D, invd, nb, &failed);
     if (tid < nb) invdiag[j0 + tid] = invd[tid];
-    { const int r = tid % kNB, c = tid / kNB; if (r < nb && c < nb && r >= c) S[(size_t)(j0 + c) * n + j0 + r] = D[r][c]; }
-    // panel solve: one row per thread, result to global and to the shared panel
-    for (int i = tid; i < rest; i += 1024) {
+    for (int e = tid; e < kNB * kNB; e += NT) { const int r = e % kNB, c = e / kNB; if (r < nb && c < nb && r >= c) S[(size_t)(j0 + c) * n + j0 + r] = D[r][c]; }
+    // panel solve: one row per thread, result to global and to the shared panel (rows padded to a multiple of 4 with zeros)
+    const int rest4 = (rest + 3) & ~3;
+    for (int i = tid; i < rest4; i += NT) {
       double xv[kNB];
 #pragma unroll
       for (int c = 0; c < kNB; ++c) {
-        if (c < nb) {
+        if (c < nb && i < rest) {
           double a = S[(size_t)(j0 + c) * n + r0 + i];
 #pragma unroll
           for (int p = 0; p < kNB; ++p) if (p < c) a -= xv[p] * D[c][p];
           xv[c] = a * invd[c];
           S[(size_t)(j0 + c) * n + r0 + i] = xv[c];
-          Ls[i * (kNB + 1) + c] = xv[c];
-        } else { xv[c] = 0.0; Ls[i * (kNB + 1) + c] = 0.0; }
+        } else xv[c] = 0.0;
+        Ls[c * LDR + i] = xv[c];
       }
     }
     __syncthreads();
-    // trailing update A[r0+i][r0+j] -= sum_p L[i][p] L[j][p], i >= j, in 4x4 micro-tiles
-    const int mt = (rest + 3) / 4;
-    for (int t = tid; t < mt * mt; t += 1024) {
-      const int ti = t / mt, tj = t % mt;
-      if (ti < tj) continue;
+    // trailing update A[r0+i][r0+j] -= sum_p L[i][p] L[j][p], i >= j, in 4x4 register micro-tiles (vector loads)
+    const int mt = rest4 / 4, ntile = mt * (mt + 1) / 2;
+    for (int t = tid; t < ntile; t += NT) {
+      // t -> (ti >= tj) of the lower triangle
+      int ti = (int)((sqrt(8.0 * t + 1.0) - 1.0) * 0.5);
+      while ((ti + 1) * (ti + 2) / 2 <= t) ++ti;
+      while (ti * (ti + 1) / 2 > t) --ti;
+      const int tj = t - ti * (ti + 1) / 2;
       double acc[4][4];
 #pragma unroll
       for (int a = 0; a < 4; ++a)
 #pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+        for (int b2 = 0; b2 < 4; ++b2) acc[a][b2] = 0.0;
       const int i0 = 4 * ti, c0 = 4 * tj;
       for (int p = 0; p < nb; ++p) {
-        double li[4], lj[4];
-#pragma unroll
-        for (int a = 0; a < 4; ++a) { li[a] = (i0 + a < rest) ? Ls[(i0 + a) * (kNB + 1) + p] : 0.0; lj[a] = (c0 + a < rest) ? Ls[(c0 + a) * (kNB + 1) + p] : 0.0; }
+        const double2 la = *reinterpret_cast<const double2*>(Ls + p * LDR + i0), lb = *reinterpret_cast<const double2*>(Ls + p * LDR + i0 + 2);
+        const double2 ca = *reinterpret_cast<const double2*>(Ls + p * LDR + c0), cb = *reinterpret_cast<const double2*>(Ls + p * LDR + c0 + 2);
+        const double li[4] = {la.x, la.y, lb.x, lb.y}, lj[4] = {ca.x, ca.y, cb.x, cb.y};
 #pragma unroll
         for (int a = 0; a < 4; ++a)
 #pragma unroll
-          for (int b = 0; b < 4; ++b) acc[a][b] += li[a] * lj[b];
+          for (int b2 = 0; b2 < 4; ++b2) acc[a][b2] += li[a] * lj[b2];
       }
 #pragma unroll
       for (int a = 0; a < 4; ++a)
 #pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          const int i = i0 + a, j = c0 + b;
-          if (i < rest && j < rest && i >= j) S[(size_t)(r0 + j) * n + r0 + i] -= acc[a][b];
+        for (int b2 = 0; b2 < 4; ++b2) {
+          const int i = i0 + a, j = c0 + b2;
+          if (i < rest && j < rest && i >= j) S[(size_t)(r0 + j) * n + r0 + i] -= acc[a][b2];
         }
     }
     __syncthreads();
   }
   if (failed) { if (tid == 0) st->lin_fail = 1; return; }   // `failed` is uniform after the last barrier
   // triangular solves L z = rhs, L^T y = z
-  for (int i = tid; i < n; i += 1024) y[i] = rhs[i];
+  for (int i = tid; i < n; i += NT) y[i] = rhs[i];
   __syncthreads();
   for (int jb = 0; jb < n; jb += kNB) {
     const int nb = min(kNB, n - jb);
-    { const int r = tid % kNB, c = tid / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(jb + c) * n + jb + r] : 0.0; }
+    for (int e = tid; e < kNB * kNB; e += NT) { const int r = e % kNB, c = e / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(jb + c) * n + jb + r] : 0.0; }
     __syncthreads();
     if (tid < 32) {
       double b = tid < nb ? y[jb + tid] : 0.0;
@@ -723,7 +728,7 @@ __global__ void __launch_bounds__(1024) chol_small_kernel(double* __restrict__ S
       if (tid < nb) { y[jb + tid] = b; xs[tid] = b; }
     }
     __syncthreads();
-    for (int i = jb + nb + tid; i < n; i += 1024) {
+    for (int i = jb + nb + tid; i < n; i += NT) {
       double a = y[i];
       for (int k = 0; k < nb; ++k) a -= S[(size_t)(jb + k) * n + i] * xs[k];
       y[i] = a;
@@ -732,7 +737,7 @@ __global__ void __launch_bounds__(1024) chol_small_kernel(double* __restrict__ S
   }
   for (int bb = (n + kNB - 1) / kNB - 1; bb >= 0; --bb) {
     const int jb = bb * kNB, nb = min(kNB, n - jb);
-    { const int r = tid % kNB, c = tid / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(jb + c) * n + jb + r] : 0.0; }
+    for (int e = tid; e < kNB * kNB; e += NT) { const int r = e % kNB, c = e / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(jb + c) * n + jb + r] : 0.0; }
     __syncthreads();
     if (tid < 32) {
       double b = tid < nb ? y[jb + tid] : 0.0;
@@ -743,7 +748,7 @@ __global__ void __launch_bounds__(1024) chol_small_kernel(double* __restrict__ S
       if (tid < nb) { y[jb + tid] = b; xs[tid] = b; }
     }
     __syncthreads();
-    for (int i = tid; i < jb; i += 1024) {
+    for (int i = tid; i < jb; i += NT) {
       double a = y[i];
       const double* col = S + (size_t)i * n + jb;
       for (int k = 0; k < nb; ++k) a -= col[k] * xs[k];
