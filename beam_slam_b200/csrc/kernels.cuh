@@ -636,6 +636,55 @@ __global__ void __launch_bounds__(128) chol_update_kernel(double* __restrict__ S
         if (row < n && col < n && row >= col) S[(size_t)col * n + row] -= acc[a][b][h];
       }
 }
+// Tiny reduced systems (n <= 160: the 10-keyframe VIO window): the whole matrix lives in shared memory for the
+// factorisation and both triangular solves; one launch, one CTA.
+constexpr int kTinyMax = 160, kTinyThreads = 512;
+__global__ void __launch_bounds__(kTinyThreads) chol_tiny_kernel(const double* __restrict__ S, int n, const double* __restrict__ rhs,
+                                                                 double* __restrict__ y, LMState* st) {
+  extern __shared__ __align__(16) double smem_dyn[];
+  __shared__ int failed;
+  if (!gate_run(st) || st->lin_fail) return;
+  constexpr int NT = kTinyThreads;
+  const int tid = threadIdx.x, ld = n | 1;   // odd leading dimension: column accesses are conflict-free
+  double* A = smem_dyn;                       // A[r * ld + c], lower triangle
+  double* inv = smem_dyn + (size_t)kTinyMax * (kTinyMax + 1);
+  double* b = inv + kTinyMax;
+  if (tid == 0) failed = 0;
+  for (int e = tid; e < n * n; e += NT) { const int r = e % n, c = e / n; if (r >= c) A[r * ld + c] = S[(size_t)c * n + r]; }
+  for (int i = tid; i < n; i += NT) b[i] = rhs[i];
+  __syncthreads();
+  for (int k = 0; k < n; ++k) {
+    if (tid == 0) { const double d = A[k * ld + k]; if (!(d > 0.0)) failed = 1; const double l = sqrt(d); A[k * ld + k] = l; inv[k] = 1.0 / l; }
+    __syncthreads();
+    const double ik = inv[k];
+    for (int i = k + 1 + tid; i < n; i += NT) A[i * ld + k] *= ik;
+    __syncthreads();
+    // rank-1 update of the trailing lower triangle: thread -> (row i, strip of columns)
+    for (int i = k + 1 + (tid >> 4); i < n; i += NT / 16) {
+      const double aik = A[i * ld + k];
+      for (int j = k + 1 + (tid & 15); j <= i; j += 16) A[i * ld + j] -= aik * A[j * ld + k];
+    }
+    __syncthreads();
+  }
+  if (failed) { if (tid == 0) st->lin_fail = 1; return; }
+  // L z = b (column sweep), then L^T y = z
+  for (int k = 0; k < n; ++k) {
+    if (tid == 0) b[k] *= inv[k];
+    __syncthreads();
+    const double zk = b[k];
+    for (int i = k + 1 + tid; i < n; i += NT) b[i] -= A[i * ld + k] * zk;
+    __syncthreads();
+  }
+  for (int k = n - 1; k >= 0; --k) {
+    if (tid == 0) b[k] *= inv[k];
+    __syncthreads();
+    const double xk = b[k];
+    for (int i = tid; i < k; i += NT) b[i] -= A[k * ld + i] * xk;
+    __syncthreads();
+  }
+  for (int i = tid; i < n; i += NT) y[i] = b[i];
+}
+
 // Small reduced systems (n <= 512: the sliding windows): the whole factorisation and both triangular solves in ONE
 // single-CTA launch. The matrix stays in global memory (L2 resident, <= 2 MB); per 32-column panel the diagonal block
 // is factored by one warp in shared memory, the panel rows are solved one row per thread, the panel is staged in
@@ -665,10 +714,13 @@ __global__ void __launch_bounds__(kSmallThreads) chol_small_kernel(double* __res
     const int rest4 = (rest + 3) & ~3;
     for (int i = tid; i < rest4; i += NT) {
       double xv[kNB];
+      const int ir = min(i, rest - 1);   // clamp so that the loads below are unconditional (issued together)
+#pragma unroll
+      for (int c = 0; c < kNB; ++c) xv[c] = S[(size_t)(j0 + min(c, nb - 1)) * n + r0 + ir];
 #pragma unroll
       for (int c = 0; c < kNB; ++c) {
         if (c < nb && i < rest) {
-          double a = S[(size_t)(j0 + c) * n + r0 + i];
+          double a = xv[c];
 #pragma unroll
           for (int p = 0; p < kNB; ++p) if (p < c) a -= xv[p] * D[c][p];
           xv[c] = a * invd[c];
