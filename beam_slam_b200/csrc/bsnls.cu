@@ -256,7 +256,7 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     LAUNCH(h, bsr_to_dense_kernel, (unsigned)((h->nnzb * 9 + 255) / 256), 256, h->P, h->d_S.as<double>(), Sd, st);
   }
   if (n <= kTinyMax && !h->sparse) {  // whole matrix in shared memory
-    const size_t smem = sizeof(double) * ((size_t)kTinyMax * (kTinyMax + 1) + 2 * kTinyMax);
+    const size_t smem = sizeof(double) * ((size_t)kTinyMax * (kTinyMax + 1) + 3 * kTinyMax);
     LAUNCH_SMEM(h, chol_tiny_kernel, 1, kTinyThreads, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
     return;
   }
@@ -377,7 +377,7 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
       (e = cudaEventCreate(&h->ev2)) != cudaSuccess) {
     g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
   }
-  if ((e = cudaFuncSetAttribute(chol_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kTinyMax * (kTinyMax + 1) + 2 * kTinyMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
+  if ((e = cudaFuncSetAttribute(chol_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kTinyMax * (kTinyMax + 1) + 3 * kTinyMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kSmallMax * kNB + kSmallMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   for (auto& ev : h->pev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   *out = h;

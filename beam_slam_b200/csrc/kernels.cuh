@@ -653,16 +653,34 @@ __global__ void __launch_bounds__(kTinyThreads) chol_tiny_kernel(const double* _
   for (int e = tid; e < n * n; e += NT) { const int r = e % n, c = e / n; if (r >= c) A[r * ld + c] = S[(size_t)c * n + r]; }
   for (int i = tid; i < n; i += NT) b[i] = rhs[i];
   __syncthreads();
+  double* colk = b + kTinyMax;               // scaled column of the current step
+  if (tid == 0) { const double d = A[0]; if (!(d > 0.0)) failed = 1; const double r = rsqrt(d); inv[0] = r; A[0] = d * r; }
+  __syncthreads();
   for (int k = 0; k < n; ++k) {
-    if (tid == 0) { const double d = A[k * ld + k]; if (!(d > 0.0)) failed = 1; const double l = sqrt(d); A[k * ld + k] = l; inv[k] = 1.0 / l; }
-    __syncthreads();
+    // column k of L (the pivot's reciprocal square root was produced during the previous step's update)
     const double ik = inv[k];
-    for (int i = k + 1 + tid; i < n; i += NT) A[i * ld + k] *= ik;
+    for (int i = k + 1 + tid; i < n; i += NT) { const double v = A[i * ld + k] * ik; colk[i] = v; A[i * ld + k] = v; }
     __syncthreads();
-    // rank-1 update of the trailing lower triangle: thread -> (row i, strip of columns)
+    // rank-1 update of the trailing lower triangle: 16 lanes per row, 4 independent columns in flight per lane
     for (int i = k + 1 + (tid >> 4); i < n; i += NT / 16) {
-      const double aik = A[i * ld + k];
-      for (int j = k + 1 + (tid & 15); j <= i; j += 16) A[i * ld + j] -= aik * A[j * ld + k];
+      const double aik = colk[i];
+      double* Ai = A + i * ld;
+      for (int j = k + 1 + (tid & 15); j <= i; j += 64) {
+        const int j1 = j + 16, j2 = j + 32, j3 = j + 48;
+        const double a0 = Ai[j], c0 = colk[j];
+        const double a1 = j1 <= i ? Ai[j1] : 0.0, c1 = j1 <= i ? colk[j1] : 0.0;
+        const double a2 = j2 <= i ? Ai[j2] : 0.0, c2 = j2 <= i ? colk[j2] : 0.0;
+        const double a3 = j3 <= i ? Ai[j3] : 0.0, c3 = j3 <= i ? colk[j3] : 0.0;
+        const double r0 = a0 - aik * c0;
+        Ai[j] = r0;
+        if (j1 <= i) Ai[j1] = a1 - aik * c1;
+        if (j2 <= i) Ai[j2] = a2 - aik * c2;
+        if (j3 <= i) Ai[j3] = a3 - aik * c3;
+        if (i == k + 1 && j == k + 1) {   // next pivot is final now: take its reciprocal square root off the critical path
+          if (!(r0 > 0.0)) failed = 1;
+          const double r = rsqrt(r0); inv[k + 1] = r; Ai[j] = r0 * r;
+        }
+      }
     }
     __syncthreads();
   }
