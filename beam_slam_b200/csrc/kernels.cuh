@@ -653,54 +653,44 @@ __global__ void __launch_bounds__(kTinyThreads) chol_tiny_kernel(const double* _
   for (int e = tid; e < n * n; e += NT) { const int r = e % n, c = e / n; if (r >= c) A[r * ld + c] = S[(size_t)c * n + r]; }
   for (int i = tid; i < n; i += NT) b[i] = rhs[i];
   __syncthreads();
-  double* colk = b + kTinyMax;               // scaled column of the current step
-  if (tid == 0) { const double d = A[0]; if (!(d > 0.0)) failed = 1; const double r = rsqrt(d); inv[0] = r; A[0] = d * r; }
-  __syncthreads();
   for (int k = 0; k < n; ++k) {
-    // column k of L (the pivot's reciprocal square root was produced during the previous step's update)
-    const double ik = inv[k];
-    for (int i = k + 1 + tid; i < n; i += NT) { const double v = A[i * ld + k] * ik; colk[i] = v; A[i * ld + k] = v; }
+    if (tid == 0) { const double d = A[k * ld + k]; if (!(d > 0.0)) failed = 1; const double r = rsqrt(d); A[k * ld + k] = d * r; inv[k] = r; }
     __syncthreads();
-    // rank-1 update of the trailing lower triangle: 16 lanes per row, 4 independent columns in flight per lane
+    const double ik = inv[k];
+    for (int i = k + 1 + tid; i < n; i += NT) A[i * ld + k] *= ik;
+    __syncthreads();
     for (int i = k + 1 + (tid >> 4); i < n; i += NT / 16) {
-      const double aik = colk[i];
-      double* Ai = A + i * ld;
-      for (int j = k + 1 + (tid & 15); j <= i; j += 64) {
-        const int j1 = j + 16, j2 = j + 32, j3 = j + 48;
-        const double a0 = Ai[j], c0 = colk[j];
-        const double a1 = j1 <= i ? Ai[j1] : 0.0, c1 = j1 <= i ? colk[j1] : 0.0;
-        const double a2 = j2 <= i ? Ai[j2] : 0.0, c2 = j2 <= i ? colk[j2] : 0.0;
-        const double a3 = j3 <= i ? Ai[j3] : 0.0, c3 = j3 <= i ? colk[j3] : 0.0;
-        const double r0 = a0 - aik * c0;
-        Ai[j] = r0;
-        if (j1 <= i) Ai[j1] = a1 - aik * c1;
-        if (j2 <= i) Ai[j2] = a2 - aik * c2;
-        if (j3 <= i) Ai[j3] = a3 - aik * c3;
-        if (i == k + 1 && j == k + 1) {   // next pivot is final now: take its reciprocal square root off the critical path
-          if (!(r0 > 0.0)) failed = 1;
-          const double r = rsqrt(r0); inv[k + 1] = r; Ai[j] = r0 * r;
-        }
-      }
+      const double aik = A[i * ld + k];
+      for (int j = k + 1 + (tid & 15); j <= i; j += 16) A[i * ld + j] -= aik * A[j * ld + k];
     }
     __syncthreads();
   }
   if (failed) { if (tid == 0) st->lin_fail = 1; return; }
-  // L z = b (column sweep), then L^T y = z
-  for (int k = 0; k < n; ++k) {
-    if (tid == 0) b[k] *= inv[k];
-    __syncthreads();
-    const double zk = b[k];
-    for (int i = k + 1 + tid; i < n; i += NT) b[i] -= A[i * ld + k] * zk;
-    __syncthreads();
+  // L z = b, then L^T y = z: one warp, entries of b held in registers (lane owns i = lane, lane + 32, ...), no block barriers
+  if (tid < 32) {
+    constexpr int PER = (kTinyMax + 31) / 32;
+    double bl[PER];
+#pragma unroll
+    for (int q = 0; q < PER; ++q) { const int i = tid + 32 * q; bl[q] = i < n ? b[i] : 0.0; }
+    for (int k = 0; k < n; ++k) {
+      double zk = 0.0;
+#pragma unroll
+      for (int q = 0; q < PER; ++q) if ((k >> 5) == q) zk = bl[q];
+      zk = __shfl_sync(0xffffffffu, zk, k & 31) * inv[k];
+#pragma unroll
+      for (int q = 0; q < PER; ++q) { const int i = tid + 32 * q; if (i == k) bl[q] = zk; else if (i > k && i < n) bl[q] -= A[i * ld + k] * zk; }
+    }
+    for (int k = n - 1; k >= 0; --k) {
+      double xk = 0.0;
+#pragma unroll
+      for (int q = 0; q < PER; ++q) if ((k >> 5) == q) xk = bl[q];
+      xk = __shfl_sync(0xffffffffu, xk, k & 31) * inv[k];
+#pragma unroll
+      for (int q = 0; q < PER; ++q) { const int i = tid + 32 * q; if (i == k) bl[q] = xk; else if (i < k) bl[q] -= A[k * ld + i] * xk; }
+    }
+#pragma unroll
+    for (int q = 0; q < PER; ++q) { const int i = tid + 32 * q; if (i < n) y[i] = bl[q]; }
   }
-  for (int k = n - 1; k >= 0; --k) {
-    if (tid == 0) b[k] *= inv[k];
-    __syncthreads();
-    const double xk = b[k];
-    for (int i = tid; i < k; i += NT) b[i] -= A[k * ld + i] * xk;
-    __syncthreads();
-  }
-  for (int i = tid; i < n; i += NT) y[i] = b[i];
 }
 
 // Small reduced systems (n <= 512: the sliding windows): the whole factorisation and both triangular solves in ONE
