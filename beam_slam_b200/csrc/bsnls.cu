@@ -196,7 +196,6 @@ __global__ void zero_f_kernel(DeviceProblem P, double* gradL, double* colsqL, co
 }
 int EnqueueGradient(bsnls_handle* h, const Options& o) {  // phase C: gradient, column norms, scale, gradient norms
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
-  LAUNCH(h, zero_f_kernel, BlocksFor(P.nf_dim, 256), 256, P, h->d_gradL.as<double>(), h->d_colsqL.as<double>(), st);
   if (h->np) LAUNCH(h, pose_diag_kernel, BlocksFor(h->np, 4), 128, P, h->d_Jrec.as<double>(), h->d_poseH.as<double>(), h->d_gradL.as<double>(), h->d_colsqL.as<double>(), st);
   const double* gS = h->d_gradL.as<double>(); const double* cS = h->d_colsqL.as<double>();
   if (h->world > 1) {
@@ -209,8 +208,8 @@ int EnqueueGradient(bsnls_handle* h, const Options& o) {  // phase C: gradient, 
     if (rc != kNcclSuccess) return h->fail(BSNLS_ERR_CUDA, "ncclAllReduce(gradient): %s", Nccl().GetErrorString(rc));
     gS = h->d_gradS.as<double>(); cS = h->d_colsqS.as<double>();
   }
-  LAUNCH(h, gf_grad_kernel, BlocksFor(3 * h->nf, 128), 128, P, h->d_gfJ.as<double>(), h->d_gfR.as<double>(), gS, cS, h->d_grad.as<double>(), h->d_colsq.as<double>(), st);
-  LAUNCH(h, fscale_kernel, BlocksFor(P.nf_dim, 256), 256, P, h->d_colsq.as<double>(), h->d_scale.as<double>(), o, st);
+  LAUNCH(h, gf_grad_kernel, BlocksFor(3 * h->nf, 128), 128, P, h->d_gfJ.as<double>(), h->d_gfR.as<double>(), gS, cS, h->d_is_pose.as<unsigned char>(),
+         h->d_grad.as<double>(), h->d_colsq.as<double>(), h->d_scale.as<double>(), o, st);
   LAUNCH(h, grad_norm_kernel, h->nb_act, 256, P, h->d_x.as<double>(), h->d_grad.as<double>(), h->d_gsq_part.as<double>(), h->d_gmax_part.as<double>(), st);
   RedList L{}; L.gate = 2; L.count = 0;
   const int nbe = h->nb_act_e, nbf = h->nb_act - h->nb_act_e;
@@ -256,8 +255,9 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     LAUNCH(h, bsr_to_dense_kernel, (unsigned)((h->nnzb * 9 + 255) / 256), 256, h->P, h->d_S.as<double>(), Sd, st);
   }
   if (n <= kTinyMax && !h->sparse) {  // whole matrix in shared memory
-    const size_t smem = sizeof(double) * ((size_t)kTinyMax * (kTinyMax + 1) + 3 * kTinyMax);
-    LAUNCH_SMEM(h, chol_tiny_kernel, 1, kTinyThreads, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
+    const size_t smem = sizeof(double) * ((size_t)kTinyMax * (kTinyMax + 1) + 2 * kTinyMax);
+    static const int tiny_threads = [] { const char* e = std::getenv("BSNLS_TINY_THREADS"); const int v = e ? std::atoi(e) : 0; return (v >= 32 && v <= kTinyThreads && v % 32 == 0) ? v : kTinyThreads; }();
+    LAUNCH_SMEM(h, chol_tiny_kernel, 1, tiny_threads, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
     return;
   }
   if (n <= kSmallMax) {  // sliding windows: factor + solve in one single-CTA launch
@@ -377,7 +377,7 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
       (e = cudaEventCreate(&h->ev2)) != cudaSuccess) {
     g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
   }
-  if ((e = cudaFuncSetAttribute(chol_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kTinyMax * (kTinyMax + 1) + 3 * kTinyMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
+  if ((e = cudaFuncSetAttribute(chol_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kTinyMax * (kTinyMax + 1) + 2 * kTinyMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kSmallMax * kNB + kSmallMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   for (auto& ev : h->pev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   *out = h;
@@ -724,6 +724,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(h->d_Jrec.alloc(sizeof(double) * kJRec * (size_t)h->nobs)); CK(h->d_Vrec.alloc(sizeof(double) * kVRec * (size_t)h->nobs));
   CK(h->d_minv.alloc(sizeof(double) * 6 * (size_t)h->ne)); CK(h->d_grad.alloc(sizeof(double) * ntan)); CK(h->d_colsq.alloc(sizeof(double) * ntan));
   CK(h->d_gradL.alloc(sizeof(double) * nf_dim)); CK(h->d_colsqL.alloc(sizeof(double) * nf_dim));
+  CK(cudaMemsetAsync(h->d_gradL.p, 0, sizeof(double) * nf_dim, s)); CK(cudaMemsetAsync(h->d_colsqL.p, 0, sizeof(double) * nf_dim, s));  // non-pose entries stay 0
   if (h->world > 1) { CK(h->d_gradS.alloc(sizeof(double) * nf_dim)); CK(h->d_colsqS.alloc(sizeof(double) * nf_dim)); }
   CK(h->d_scale.alloc(sizeof(double) * ntan)); CK(h->d_y.alloc(sizeof(double) * ntan)); CK(h->d_yf.alloc(sizeof(double) * nf_dim));
   CK(h->d_rhs.alloc(sizeof(double) * nf_dim)); CK(h->d_S.alloc(sizeof(double) * (h->sparse ? (size_t)h->nnzb * 9 : (size_t)nf_dim * nf_dim)));

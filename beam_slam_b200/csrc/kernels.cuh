@@ -342,8 +342,9 @@ __global__ void __launch_bounds__(128) pose_diag_kernel(DeviceProblem P, const d
 // One thread per (f-block, component); fixed summation order.
 __global__ void __launch_bounds__(128) gf_grad_kernel(DeviceProblem P, const double* __restrict__ gfJ,
                                                       const double* __restrict__ gfR, const double* __restrict__ pose_grad,
-                                                      const double* __restrict__ pose_colsq, double* __restrict__ grad,
-                                                      double* __restrict__ colsq, const LMState* st) {
+                                                      const double* __restrict__ pose_colsq, const unsigned char* __restrict__ is_pose_entry,
+                                                      double* __restrict__ grad, double* __restrict__ colsq, double* __restrict__ scale,
+                                                      Options opt, const LMState* st) {
   if (!gate_jac(st)) return;
   const int tid = blockIdx.x * 128 + threadIdx.x;
   const int fb = tid / 3, k = tid % 3;
@@ -356,7 +357,10 @@ __global__ void __launch_bounds__(128) gf_grad_kernel(DeviceProblem P, const dou
     for (int i = 0; i < nr; ++i) { const double v = J[i * ncol + 3 * lb + k]; g += v * R[i]; c += v * v; }
   }
   const int t = P.ne_dim + 3 * fb + k;
-  grad[t] = pose_grad[3 * fb + k] + g; colsq[t] = pose_colsq[3 * fb + k] + c;   // pose part: summed over all ranks' observations
+  const bool pose = is_pose_entry[3 * fb + k];   // pose part: summed over all ranks' observations; other f-blocks have none
+  const double cs = (pose ? pose_colsq[3 * fb + k] : 0.0) + c;
+  grad[t] = (pose ? pose_grad[3 * fb + k] : 0.0) + g; colsq[t] = cs;
+  if (!st->scale_ready) scale[t] = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(cs)) : 1.0;   // Jacobi scale, frozen at iteration 0
 }
 
 // Jacobi scale of the f-blocks (iteration 0) and LM diagonal D_f^2; also gradient norms:
@@ -638,13 +642,13 @@ __global__ void __launch_bounds__(128) chol_update_kernel(double* __restrict__ S
 }
 // Tiny reduced systems (n <= 160: the 10-keyframe VIO window): the whole matrix lives in shared memory for the
 // factorisation and both triangular solves; one launch, one CTA.
-constexpr int kTinyMax = 160, kTinyThreads = 512;
+constexpr int kTinyMax = 160, kTinyThreads = 1024;
 __global__ void __launch_bounds__(kTinyThreads) chol_tiny_kernel(const double* __restrict__ S, int n, const double* __restrict__ rhs,
                                                                  double* __restrict__ y, LMState* st) {
   extern __shared__ __align__(16) double smem_dyn[];
   __shared__ int failed;
   if (!gate_run(st) || st->lin_fail) return;
-  constexpr int NT = kTinyThreads;
+  const int NT = blockDim.x;   // launch-time choice: barrier cost grows with the warp count, update work shrinks
   const int tid = threadIdx.x, ld = n | 1;   // odd leading dimension: column accesses are conflict-free
   double* A = smem_dyn;                       // A[r * ld + c], lower triangle
   double* inv = smem_dyn + (size_t)kTinyMax * (kTinyMax + 1);
@@ -654,11 +658,12 @@ __global__ void __launch_bounds__(kTinyThreads) chol_tiny_kernel(const double* _
   for (int i = tid; i < n; i += NT) b[i] = rhs[i];
   __syncthreads();
   for (int k = 0; k < n; ++k) {
-    if (tid == 0) { const double d = A[k * ld + k]; if (!(d > 0.0)) failed = 1; const double r = rsqrt(d); A[k * ld + k] = d * r; inv[k] = r; }
+    if (tid == 0) { const double d = A[k * ld + k]; if (!(d > 0.0)) failed = 1; const double l = sqrt(d); A[k * ld + k] = l; inv[k] = 1.0 / l; }
     __syncthreads();
     const double ik = inv[k];
     for (int i = k + 1 + tid; i < n; i += NT) A[i * ld + k] *= ik;
     __syncthreads();
+    // rank-1 update of the trailing lower triangle: thread -> (row i, strip of columns)
     for (int i = k + 1 + (tid >> 4); i < n; i += NT / 16) {
       const double aik = A[i * ld + k];
       for (int j = k + 1 + (tid & 15); j <= i; j += 16) A[i * ld + j] -= aik * A[j * ld + k];
@@ -666,31 +671,22 @@ __global__ void __launch_bounds__(kTinyThreads) chol_tiny_kernel(const double* _
     __syncthreads();
   }
   if (failed) { if (tid == 0) st->lin_fail = 1; return; }
-  // L z = b, then L^T y = z: one warp, entries of b held in registers (lane owns i = lane, lane + 32, ...), no block barriers
-  if (tid < 32) {
-    constexpr int PER = (kTinyMax + 31) / 32;
-    double bl[PER];
-#pragma unroll
-    for (int q = 0; q < PER; ++q) { const int i = tid + 32 * q; bl[q] = i < n ? b[i] : 0.0; }
-    for (int k = 0; k < n; ++k) {
-      double zk = 0.0;
-#pragma unroll
-      for (int q = 0; q < PER; ++q) if ((k >> 5) == q) zk = bl[q];
-      zk = __shfl_sync(0xffffffffu, zk, k & 31) * inv[k];
-#pragma unroll
-      for (int q = 0; q < PER; ++q) { const int i = tid + 32 * q; if (i == k) bl[q] = zk; else if (i > k && i < n) bl[q] -= A[i * ld + k] * zk; }
-    }
-    for (int k = n - 1; k >= 0; --k) {
-      double xk = 0.0;
-#pragma unroll
-      for (int q = 0; q < PER; ++q) if ((k >> 5) == q) xk = bl[q];
-      xk = __shfl_sync(0xffffffffu, xk, k & 31) * inv[k];
-#pragma unroll
-      for (int q = 0; q < PER; ++q) { const int i = tid + 32 * q; if (i == k) bl[q] = xk; else if (i < k) bl[q] -= A[k * ld + i] * xk; }
-    }
-#pragma unroll
-    for (int q = 0; q < PER; ++q) { const int i = tid + 32 * q; if (i < n) y[i] = bl[q]; }
+  // L z = b (column sweep), then L^T y = z
+  for (int k = 0; k < n; ++k) {
+    if (tid == 0) b[k] *= inv[k];
+    __syncthreads();
+    const double zk = b[k];
+    for (int i = k + 1 + tid; i < n; i += NT) b[i] -= A[i * ld + k] * zk;
+    __syncthreads();
   }
+  for (int k = n - 1; k >= 0; --k) {
+    if (tid == 0) b[k] *= inv[k];
+    __syncthreads();
+    const double xk = b[k];
+    for (int i = tid; i < k; i += NT) b[i] -= A[k * ld + i] * xk;
+    __syncthreads();
+  }
+  for (int i = tid; i < n; i += NT) y[i] = b[i];
 }
 
 // Small reduced systems (n <= 512: the sliding windows): the whole factorisation and both triangular solves in ONE
