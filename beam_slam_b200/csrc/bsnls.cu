@@ -67,6 +67,7 @@ struct bsnls_handle {
   std::vector<int> pose_q_blk, pose_t_blk;
   std::vector<int> pair_a, pair_b;
   std::vector<int> gd_row, gd_col;
+  int nchunks = 0; DevMem d_obs_slot, d_chunk_begin, d_chunk_nslots, d_chunk_part_off, d_chunk_cpart_off, d_pp_ptr, d_pp_off, d_pp_coff, d_part, d_cpart;
   bool sparse = false, pcg = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
   // residual-block bookkeeping for bsnls_evaluate (program order)
   struct ResRef { int type; int idx; int row; };   // idx: sorted-observation id or generic-factor id
@@ -230,7 +231,8 @@ int EnqueueAssemble(bsnls_handle* h, const Options& o) {  // phase D1: reduced s
   cudaMemsetAsync(h->d_S.p, 0, sizeof(double) * s_count, h->stream);
   if (h->world > 1) cudaMemsetAsync(h->d_rhs.p, 0, sizeof(double) * P.nf_dim, h->stream);
   MARK(h, 6);
-  if (h->npairs) LAUNCH(h, pair_kernel, BlocksFor(h->npairs, 4), 128, P, h->d_Vrec.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
+  if (h->nchunks) LAUNCH_SMEM(h, chunk_accum_kernel, h->nchunks, 256, kChunkSmemBytes, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), st);
+  if (h->npairs) LAUNCH(h, pair_kernel, BlocksFor(h->npairs, 4), 128, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
   MARK(h, 7);
   if (h->world > 1) {  // the one exchange step of the path: sum the per-shard reduced camera systems over NVLink
     Nccl().GroupStart();
@@ -377,6 +379,7 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
       (e = cudaEventCreate(&h->ev2)) != cudaSuccess) {
     g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
   }
+  if ((e = cudaFuncSetAttribute(chunk_accum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kChunkSmemBytes)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chol_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kTinyMax * (kTinyMax + 1) + 2 * kTinyMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kSmallMax * kNB + kSmallMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   for (auto& ev : h->pev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
@@ -497,32 +500,81 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   bsnls_shard_range(lm_ptr.data(), ne_g, h->rank, h->world, &lo, &hi);
   h->lm_lo = lo; h->lm_hi = hi; h->ne = hi - lo;
   const int ne_dim = 3 * h->ne;
-  const int obs_base = lm_ptr[lo], nobs_local = lm_ptr[hi] - lm_ptr[lo];
+  const int nobs_local = lm_ptr[hi] - lm_ptr[lo];
   h->nobs = nobs_local;
-  h->blk_tan.assign(nb, -1);
-  for (int b = 0; b < nb; ++b) {
-    if (epos[b] >= lo && epos[b] < hi) h->blk_tan[b] = 3 * (epos[b] - lo);
-    else if (fpos[b] >= 0) h->blk_tan[b] = ne_dim + 3 * fpos[b];
+  std::vector<int> g_pose(nobs);   // pose of every observation of the graph, landmark-sorted (the pair pattern is global)
+  for (int k = 0; k < nobs; ++k) g_pose[k] = obs_pose[order[k]];
+
+  // ---- pose-pair blocks of the reduced system: pattern of the WHOLE graph (identical on every rank) ----
+  std::unordered_map<uint64_t, int> key_id;
+  auto key_of = [&](int a2, int b2) { return (uint64_t)std::min(a2, b2) * (uint64_t)h->np + (uint64_t)std::max(a2, b2); };
+  h->pair_a.clear(); h->pair_b.clear();
+  {
+    key_id.reserve((size_t)h->np * 16);
+    for (int e = 0; e < ne_g; ++e)
+      for (int i = lm_ptr[e]; i < lm_ptr[e + 1]; ++i)
+        for (int j = i; j < lm_ptr[e + 1]; ++j) key_id.emplace(key_of(g_pose[i], g_pose[j]), 0);
+    std::vector<uint64_t> keys; keys.reserve(key_id.size());
+    for (auto& kv : key_id) keys.push_back(kv.first);
+    std::sort(keys.begin(), keys.end());
+    for (size_t k = 0; k < keys.size(); ++k) { key_id[keys[k]] = (int)k; h->pair_a.push_back((int)(keys[k] / h->np)); h->pair_b.push_back((int)(keys[k] % h->np)); }
+    h->npairs = (int)keys.size();
   }
+  // ---- pose ranking for locality: breadth-first order of the co-visibility graph from a peripheral pose ----
+  std::vector<int> pose_rank(h->np, -1);
+  {
+    std::vector<std::vector<int>> adj(h->np);
+    for (int p2 = 0; p2 < h->npairs; ++p2) if (h->pair_a[p2] != h->pair_b[p2]) { adj[h->pair_a[p2]].push_back(h->pair_b[p2]); adj[h->pair_b[p2]].push_back(h->pair_a[p2]); }
+    auto bfs = [&](int start, std::vector<int>& out) {
+      std::vector<char> seen(h->np, 0); out.clear(); out.push_back(start); seen[start] = 1;
+      for (size_t q = 0; q < out.size(); ++q) {
+        std::vector<int> nb2; for (int v : adj[out[q]]) if (!seen[v]) { seen[v] = 1; nb2.push_back(v); }
+        std::sort(nb2.begin(), nb2.end(), [&](int x, int y2) { return adj[x].size() != adj[y2].size() ? adj[x].size() < adj[y2].size() : x < y2; });
+        out.insert(out.end(), nb2.begin(), nb2.end());
+      }
+    };
+    int next_rank = 0; std::vector<int> comp, comp2;
+    for (int p0 = 0; p0 < h->np; ++p0) {
+      if (pose_rank[p0] >= 0) continue;
+      bfs(p0, comp); bfs(comp.back(), comp2);      // second sweep starts at a far end of the component
+      for (int v : comp2) pose_rank[v] = next_rank++;
+    }
+  }
+  // ---- internal landmark order of this shard: by the earliest pose that sees the landmark (keeps chunks local) ----
+  std::vector<int> lperm(h->ne);                   // new position -> position inside [lo, hi)
+  {
+    std::vector<std::pair<int, int>> key(h->ne);
+    for (int e = 0; e < h->ne; ++e) {
+      int mn = 1 << 30, mx = -1;
+      for (int k = lm_ptr[lo + e]; k < lm_ptr[lo + e + 1]; ++k) { mn = std::min(mn, pose_rank[g_pose[k]]); mx = std::max(mx, pose_rank[g_pose[k]]); }
+      key[e] = {mn, mx}; lperm[e] = e;
+    }
+    std::stable_sort(lperm.begin(), lperm.end(), [&](int x, int y2) { return key[x] < key[y2]; });
+  }
+  h->blk_tan.assign(nb, -1);
+  for (int b = 0; b < nb; ++b) if (fpos[b] >= 0) h->blk_tan[b] = ne_dim + 3 * fpos[b];
+  for (int e = 0; e < h->ne; ++e) h->blk_tan[h->eblocks[lo + lperm[e]]] = 3 * e;
   // active list: local landmarks, padded to a CTA boundary, then the (replicated) f-blocks
   h->active_blocks.clear();
-  for (int e = lo; e < hi; ++e) h->active_blocks.push_back(h->eblocks[e]);
+  for (int e = 0; e < h->ne; ++e) h->active_blocks.push_back(h->eblocks[lo + lperm[e]]);
   while (h->active_blocks.size() % 256) h->active_blocks.push_back(-1);
   h->nb_act_e = (int)h->active_blocks.size() / 256;
   for (int b : h->fblocks) h->active_blocks.push_back(b);
-  std::vector<int> g_pose(nobs);   // pose of every observation of the graph in sorted order (pair pattern is global)
-  std::vector<int> s_pose(nobs_local), s_lm(nobs_local), s_cam(nobs_local), inv_order(nobs, -1); std::vector<double> s_pixel(2 * (size_t)nobs_local);
-  for (int k = 0; k < nobs; ++k) {
-    const int i = order[k]; g_pose[k] = obs_pose[i];
-    if (k < obs_base || k >= obs_base + nobs_local) continue;
-    const int kl = k - obs_base; inv_order[i] = kl;
-    s_pose[kl] = obs_pose[i]; s_lm[kl] = obs_lm[i] - lo; s_cam[kl] = rg->aux[i];
-    s_pixel[2 * (size_t)kl] = rg->consts[2 * (size_t)i]; s_pixel[2 * (size_t)kl + 1] = rg->consts[2 * (size_t)i + 1];
+  std::vector<int> s_pose(nobs_local), s_lm(nobs_local), s_cam(nobs_local), inv_order(nobs, -1), lm_ptr_local(h->ne + 1, 0), lm_off(h->ne);
+  std::vector<double> s_pixel(2 * (size_t)nobs_local);
+  {
+    int kl = 0;
+    for (int e = 0; e < h->ne; ++e) {
+      const int ge = lo + lperm[e];
+      lm_off[e] = h->blk_off[h->eblocks[ge]];
+      for (int k = lm_ptr[ge]; k < lm_ptr[ge + 1]; ++k, ++kl) {
+        const int i = order[k]; inv_order[i] = kl;
+        s_pose[kl] = obs_pose[i]; s_lm[kl] = e; s_cam[kl] = rg->aux[i];
+        s_pixel[2 * (size_t)kl] = rg->consts[2 * (size_t)i]; s_pixel[2 * (size_t)kl + 1] = rg->consts[2 * (size_t)i + 1];
+      }
+      lm_ptr_local[e + 1] = kl;
+    }
   }
-  std::vector<int> lm_ptr_local(h->ne + 1);
-  for (int e = 0; e <= h->ne; ++e) lm_ptr_local[e] = lm_ptr[lo + e] - obs_base;
-  std::vector<int> lm_off(h->ne);
-  for (int e = 0; e < h->ne; ++e) lm_off[e] = h->blk_off[h->eblocks[lo + e]];
   std::vector<int> pose_q_off(h->np), pose_t_off(h->np), pose_q_tan(h->np), pose_t_tan(h->np), pose_ptr(h->np + 1, 0), pose_obs(nobs_local);
   for (int a = 0; a < h->np; ++a) {
     pose_q_off[a] = h->blk_off[h->pose_q_blk[a]]; pose_t_off[a] = h->blk_off[h->pose_t_blk[a]];
@@ -534,44 +586,85 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   const double avg_track = ne_g ? (double)nobs / ne_g : 0.0;
   h->G = avg_track <= 5.0 ? 4 : avg_track <= 12.0 ? 8 : avg_track <= 24.0 ? 16 : 32;
 
-  // ---- pose-pair blocks and items ----
-  std::vector<int> pair_ptr, item_i, item_j;
-  h->pair_a.clear(); h->pair_b.clear();
+  // ---- chunks: consecutive landmarks whose poses fit kChunkSlots slots are accumulated on chip by one CTA ----
+  std::vector<unsigned char> obs_slot(nobs_local, 255);
+  std::vector<int> chunk_begin, chunk_nslots, chunk_pose;      // chunk_begin: landmark ranges (nchunks + 1)
+  std::vector<long long> chunk_part_off, chunk_cpart_off;
+  std::vector<char> wide(h->ne, 0);
+  long long part_size = 0, cpart_size = 0;
   {
-    std::unordered_map<uint64_t, int> key_count; key_count.reserve((size_t)h->np * 16);
-    auto key_of = [&](int a, int b) { return (uint64_t)a * (uint64_t)h->np + (uint64_t)b; };
-    for (int e = 0; e < ne_g; ++e) {   // keys: every rank needs the pattern of the WHOLE graph; counts: local items only
-      const bool mine = e >= lo && e < hi;
-      for (int i = lm_ptr[e]; i < lm_ptr[e + 1]; ++i)
-        for (int j = i; j < lm_ptr[e + 1]; ++j) {
-          const int a = g_pose[i], b = g_pose[j];
-          key_count[key_of(std::min(a, b), std::max(a, b))] += !mine ? 0 : (a == b && i != j) ? 2 : 1;
-        }
+    std::vector<int> stamp(h->np, -1), cur_poses;
+    int c_begin = 0, c_obs = 0;
+    auto close_chunk = [&](int end) {
+      if (end == c_begin) return;
+      std::sort(cur_poses.begin(), cur_poses.end());           // slots in increasing pose id: slot A < B  <=>  pose a < b
+      for (size_t q = 0; q < cur_poses.size(); ++q) stamp[cur_poses[q]] = (int)q;
+      for (int e = c_begin; e < end; ++e) if (!wide[e]) for (int k = lm_ptr_local[e]; k < lm_ptr_local[e + 1]; ++k) obs_slot[k] = (unsigned char)stamp[s_pose[k]];
+      chunk_begin.push_back(c_begin); chunk_nslots.push_back((int)cur_poses.size());
+      for (int q = 0; q < kChunkSlots; ++q) chunk_pose.push_back(q < (int)cur_poses.size() ? cur_poses[q] : -1);
+      chunk_part_off.push_back(part_size); chunk_cpart_off.push_back(cpart_size);
+      const long long ns = (long long)cur_poses.size();
+      part_size += ns * (ns + 1) / 2 * 36; cpart_size += ns * 6;
+      for (int pz : cur_poses) stamp[pz] = -1;
+      cur_poses.clear(); c_begin = end; c_obs = 0;
+    };
+    for (int e = 0; e < h->ne; ++e) {
+      const int k0 = lm_ptr_local[e], k1 = lm_ptr_local[e + 1];
+      // wide landmark: more poses than slots, or seen twice by one pose -> handled through the item list
+      bool is_wide = k1 - k0 > kChunkSlots;
+      for (int k = k0; k < k1 && !is_wide; ++k) for (int k2 = k0; k2 < k; ++k2) if (s_pose[k2] == s_pose[k]) { is_wide = true; break; }
+      if (is_wide) { wide[e] = 1; continue; }
+      int fresh = 0;
+      for (int k = k0; k < k1; ++k) if (stamp[s_pose[k]] == -1) ++fresh;
+      if ((int)cur_poses.size() + fresh > kChunkSlots || c_obs + (k1 - k0) > kChunkMaxObs) { close_chunk(e); }
+      for (int k = k0; k < k1; ++k) if (stamp[s_pose[k]] == -1) { stamp[s_pose[k]] = -3; cur_poses.push_back(s_pose[k]); }
+      c_obs += k1 - k0;
     }
-    std::vector<uint64_t> keys; keys.reserve(key_count.size());
-    for (auto& kv : key_count) keys.push_back(kv.first);
-    std::sort(keys.begin(), keys.end());
-    const int npairs = (int)keys.size();
-    std::unordered_map<uint64_t, int> key_id; key_id.reserve(keys.size() * 2);
-    pair_ptr.assign(npairs + 1, 0);
-    for (int k = 0; k < npairs; ++k) {
-      key_id[keys[k]] = k; pair_ptr[k + 1] = pair_ptr[k] + key_count[keys[k]];
-      h->pair_a.push_back((int)(keys[k] / h->np)); h->pair_b.push_back((int)(keys[k] % h->np));
+    // note: stamp == -3 marks "in the current chunk" while it is being built
+    close_chunk(h->ne);
+    chunk_begin.push_back(h->ne);
+  }
+  h->nchunks = (int)chunk_nslots.size();
+  // ---- per pair: partial blocks produced by the chunks, and items of the wide landmarks ----
+  std::vector<int> pair_ptr(h->npairs + 1, 0), item_i, item_j, pp_ptr(h->npairs + 1, 0);
+  std::vector<long long> pp_off, pp_coff;
+  {
+    std::vector<int> cnt(h->npairs, 0), pcnt(h->npairs, 0);
+    for (int e = 0; e < h->ne; ++e) {
+      if (!wide[e]) continue;
+      for (int i = lm_ptr_local[e]; i < lm_ptr_local[e + 1]; ++i)
+        for (int j = i; j < lm_ptr_local[e + 1]; ++j) cnt[key_id[key_of(s_pose[i], s_pose[j])]] += (s_pose[i] == s_pose[j] && i != j) ? 2 : 1;
     }
-    const int64_t nitems = pair_ptr[npairs];
-    if (nitems > 0x7fffffffLL) return h->fail(BSNLS_ERR_UNSUPPORTED, "too many observation pairs");
-    item_i.resize(nitems); item_j.resize(nitems);
-    std::vector<int> cur(pair_ptr.begin(), pair_ptr.end() - 1);
-    for (int e = lo; e < hi; ++e)
-      for (int i0 = lm_ptr[e]; i0 < lm_ptr[e + 1]; ++i0)
-        for (int j0 = i0; j0 < lm_ptr[e + 1]; ++j0) {
-          const int a = g_pose[i0], b = g_pose[j0], i = i0 - obs_base, j = j0 - obs_base;
-          const int id = key_id[key_of(std::min(a, b), std::max(a, b))];
+    for (int c = 0; c < h->nchunks; ++c) {
+      const int ns = chunk_nslots[c];
+      for (int A = 0; A < ns; ++A) for (int B = A; B < ns; ++B) pcnt[key_id[key_of(chunk_pose[(size_t)c * kChunkSlots + A], chunk_pose[(size_t)c * kChunkSlots + B])]]++;
+    }
+    for (int k = 0; k < h->npairs; ++k) { pair_ptr[k + 1] = pair_ptr[k] + cnt[k]; pp_ptr[k + 1] = pp_ptr[k] + pcnt[k]; }
+    const int64_t nitems = pair_ptr[h->npairs];
+    item_i.resize(nitems); item_j.resize(nitems); pp_off.resize(pp_ptr[h->npairs]); pp_coff.resize(pp_ptr[h->npairs]);
+    std::vector<int> cur(pair_ptr.begin(), pair_ptr.end() - 1), pcur(pp_ptr.begin(), pp_ptr.end() - 1);
+    for (int e = 0; e < h->ne; ++e) {
+      if (!wide[e]) continue;
+      for (int i = lm_ptr_local[e]; i < lm_ptr_local[e + 1]; ++i)
+        for (int j = i; j < lm_ptr_local[e + 1]; ++j) {
+          const int a = s_pose[i], b = s_pose[j];
+          const int id = key_id[key_of(a, b)];
           if (a < b || i == j) { item_i[cur[id]] = i; item_j[cur[id]] = j; cur[id]++; }
           else if (a > b) { item_i[cur[id]] = j; item_j[cur[id]] = i; cur[id]++; }
           else { item_i[cur[id]] = i; item_j[cur[id]] = j; cur[id]++; item_i[cur[id]] = j; item_j[cur[id]] = i; cur[id]++; }
         }
-    h->npairs = npairs; h->nitems = nitems;
+    }
+    for (int c = 0; c < h->nchunks; ++c) {
+      const int ns = chunk_nslots[c];
+      int q = 0;
+      for (int A = 0; A < ns; ++A) for (int B = A; B < ns; ++B, ++q) {
+        const int id = key_id[key_of(chunk_pose[(size_t)c * kChunkSlots + A], chunk_pose[(size_t)c * kChunkSlots + B])];
+        pp_off[pcur[id]] = chunk_part_off[c] + (long long)q * 36;
+        pp_coff[pcur[id]] = A == B ? chunk_cpart_off[c] + (long long)A * 6 : -1;
+        pcur[id]++;
+      }
+    }
+    h->nitems = nitems;
   }
 
   // ---- generic factors (type-major; factors whose blocks are all constant go last: fixed cost) ----
@@ -707,6 +800,10 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_gf_loss_a, gf_loss_a, s)); CK(upload(h->d_gf_joff, gf_joff, s)); CK(upload(h->d_gf_roff, gf_roff, s));
   CK(upload(h->d_pair_a, h->pair_a, s)); CK(upload(h->d_pair_b, h->pair_b, s)); CK(upload(h->d_pair_ptr, pair_ptr, s));
   CK(upload(h->d_item_i, item_i, s)); CK(upload(h->d_item_j, item_j, s));
+  CK(upload(h->d_obs_slot, obs_slot, s)); CK(upload(h->d_chunk_begin, chunk_begin, s)); CK(upload(h->d_chunk_nslots, chunk_nslots, s));
+  CK(upload(h->d_chunk_part_off, chunk_part_off, s)); CK(upload(h->d_chunk_cpart_off, chunk_cpart_off, s));
+  CK(upload(h->d_pp_ptr, pp_ptr, s)); CK(upload(h->d_pp_off, pp_off, s)); CK(upload(h->d_pp_coff, pp_coff, s));
+  CK(h->d_part.alloc(sizeof(double) * (size_t)part_size)); CK(h->d_cpart.alloc(sizeof(double) * (size_t)cpart_size));
   CK(upload(h->d_fg_ptr, fg_ptr, s)); CK(upload(h->d_fg_fac, fg_fac, s)); CK(upload(h->d_fg_lb, fg_lb, s));
   CK(upload(h->d_gd_row, h->gd_row, s)); CK(upload(h->d_gd_col, h->gd_col, s)); CK(upload(h->d_gd_ptr, gd_ptr, s));
   CK(upload(h->d_gd_fac, gd_fac, s)); CK(upload(h->d_gd_bi, gd_bi, s)); CK(upload(h->d_gd_bj, gd_bj, s)); CK(upload(h->d_is_pose, is_pose, s));
@@ -761,6 +858,9 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   P.gf_joff = h->d_gf_joff.as<int>(); P.gf_roff = h->d_gf_roff.as<int>();
   P.num_pairs = h->npairs; P.pair_a = h->d_pair_a.as<int>(); P.pair_b = h->d_pair_b.as<int>(); P.pair_ptr = h->d_pair_ptr.as<int>();
   P.item_i = h->d_item_i.as<int>(); P.item_j = h->d_item_j.as<int>();
+  P.num_chunks = h->nchunks; P.obs_slot = h->d_obs_slot.as<unsigned char>(); P.chunk_begin = h->d_chunk_begin.as<int>(); P.chunk_nslots = h->d_chunk_nslots.as<int>();
+  P.chunk_part_off = h->d_chunk_part_off.as<long long>(); P.chunk_cpart_off = h->d_chunk_cpart_off.as<long long>();
+  P.pp_ptr = h->d_pp_ptr.as<int>(); P.pp_off = h->d_pp_off.as<long long>(); P.pp_coff = h->d_pp_coff.as<long long>();
   P.fg_ptr = h->d_fg_ptr.as<int>(); P.fg_fac = h->d_fg_fac.as<int>(); P.fg_lb = h->d_fg_lb.as<int>();
   P.num_gdest = h->ngdest; P.gd_row = h->d_gd_row.as<int>(); P.gd_col = h->d_gd_col.as<int>(); P.gd_ptr = h->d_gd_ptr.as<int>();
   P.gd_fac = h->d_gd_fac.as<int>(); P.gd_bi = h->d_gd_bi.as<int>(); P.gd_bj = h->d_gd_bj.as<int>();

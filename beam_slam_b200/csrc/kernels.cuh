@@ -14,6 +14,10 @@ namespace bsnls {
 constexpr int kJRec = 20;   // per observation: E[6] (2x3 wrt landmark) | r[2] | F[12] (2x6 wrt q-tangent, t)
 constexpr int kVRec = 24;   // per observation: V[18] (6x3 = F^T E C) | c[6] (= V z)
 constexpr int kGfMaxBlocks = 10, kGfMaxRes = 15, kGfMaxAmbient = 32;
+constexpr int kChunkSlots = 22;        // poses per chunk: 22*23/2 = 253 pair blocks <= 256 threads
+constexpr int kChunkMaxObs = 4096;     // observations per chunk (load balance vs. partial-block traffic)
+constexpr int kChunkStageDoubles = 17920;   // staging buffer (140 KiB) for the V records of a batch of landmarks
+constexpr int kChunkSmemBytes = kChunkStageDoubles * 8;
 
 struct LMState {
   // trust region (ceres LevenbergMarquardtStrategy)
@@ -51,6 +55,11 @@ struct DeviceProblem {
   const int* gf_joff; const int* gf_roff;     // offsets into gfJ (nres x 3*nblk row-major) and gfR
   // S pair blocks (pose a <= pose b) and their items
   int num_pairs; const int* pair_a; const int* pair_b; const int* pair_ptr; const int* item_i; const int* item_j;
+  // chunks: landmark ranges accumulated on chip (chunk_accum_kernel); per observation the slot of its pose in its chunk
+  // (255: landmark handled through the item list); per pair the partial blocks the chunks produced
+  int num_chunks; const unsigned char* obs_slot; const int* chunk_begin; const int* chunk_nslots;
+  const long long* chunk_part_off; const long long* chunk_cpart_off;
+  const int* pp_ptr; const long long* pp_off; const long long* pp_coff;
   // generic-factor contributions: per f-block (gradient / column norms) and per 3x3 destination of S
   const int* fg_ptr; const int* fg_fac; const int* fg_lb;            // CSR over f-blocks (nf)
   int num_gdest; const int* gd_row; const int* gd_col; const int* gd_ptr; const int* gd_fac; const int* gd_bi; const int* gd_bj;
@@ -398,6 +407,107 @@ __global__ void __launch_bounds__(256) grad_norm_kernel(DeviceProblem P, const d
 }
 
 // ===================================================================================================
+// K5b (on-chip): S -= sum_l V_a V_b^T accumulated per CHUNK of landmarks. One CTA per chunk; the poses of the chunk
+// occupy <= 22 slots, every (slot A <= slot B) pair block is owned by one thread (36 register accumulators), so
+// there are no conflicts and no atomics: a thread walks the landmarks of the chunk in order and adds V_A V_B^T
+// whenever the landmark is seen by both poses. V records are staged batch-wise in shared memory (each record is
+// read from HBM exactly once, coalesced). When fewer than 128 pair blocks exist, several thread groups take
+// alternate landmarks and are combined in a fixed order. Output: partial pair blocks + per-slot sums of c = V z,
+// reduced across chunks by pair_kernel.
+// ===================================================================================================
+__global__ void __launch_bounds__(256) chunk_accum_kernel(DeviceProblem P, const double* __restrict__ Vrec,
+                                                          double* __restrict__ part, double* __restrict__ cpart,
+                                                          const LMState* st) {
+  extern __shared__ __align__(16) double stage[];   // [landmark in batch][slot][25]  (24 used; odd stride: conflict-free)
+  __shared__ unsigned int mask[512];
+  __shared__ unsigned char pA[256], pB[256];
+  if (!gate_run(st)) return;
+  const int c = blockIdx.x, tid = threadIdx.x;
+  const int ns = P.chunk_nslots[c], npair = ns * (ns + 1) / 2;
+  const int groups = max(1, 256 / npair);
+  const int l_begin = P.chunk_begin[c], l_end = P.chunk_begin[c + 1];
+  if (tid < npair) {   // q -> (A <= B), row-major over the upper triangle
+    int q = tid, A = 0;
+    while (q >= ns - A) { q -= ns - A; ++A; }
+    pA[tid] = (unsigned char)A; pB[tid] = (unsigned char)(A + q);
+  }
+  __syncthreads();
+  const int grp = tid / npair, q = tid - grp * npair;
+  const bool worker = grp < groups;
+  const int A = worker ? pA[q] : 0, B = worker ? pB[q] : 0;
+  double acc[36], cacc[6];
+#pragma unroll
+  for (int k = 0; k < 36; ++k) acc[k] = 0.0;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) cacc[k] = 0.0;
+  const int lstride = ns * 25;
+  const int batch = min(512, kChunkStageDoubles / lstride);
+  for (int l0 = l_begin; l0 < l_end; l0 += batch) {
+    const int l1 = min(l_end, l0 + batch);
+    const int o0 = P.lm_ptr[l0], o1 = P.lm_ptr[l1];
+    for (int l = tid; l < l1 - l0; l += 256) mask[l] = 0u;
+    __syncthreads();
+    for (int e = tid; e < (o1 - o0) * 24; e += 256) {
+      const int o = o0 + e / 24, w = e - 24 * (e / 24);
+      const int sl = P.obs_slot[o];
+      if (sl == 255) continue;
+      const int l = P.obs_lm[o] - l0;
+      stage[l * lstride + sl * 25 + w] = Vrec[(size_t)o * kVRec + w];
+      if (w == 0) atomicOr(&mask[l], 1u << sl);
+    }
+    __syncthreads();
+    if (worker) {
+      for (int l = grp; l < l1 - l0; l += groups) {
+        const unsigned int m = mask[l];
+        if (!((m >> A) & 1u) || !((m >> B) & 1u)) continue;
+        const double* va = stage + l * lstride + A * 25;
+        const double* vb = stage + l * lstride + B * 25;
+        double Va[18], Vb[18];
+#pragma unroll
+        for (int k = 0; k < 18; ++k) { Va[k] = va[k]; Vb[k] = vb[k]; }
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+#pragma unroll
+          for (int j = 0; j < 6; ++j)
+            acc[6 * i + j] += Va[3 * i] * Vb[3 * j] + Va[3 * i + 1] * Vb[3 * j + 1] + Va[3 * i + 2] * Vb[3 * j + 2];
+        if (A == B) {
+#pragma unroll
+          for (int k = 0; k < 6; ++k) cacc[k] += va[18 + k];
+        }
+      }
+    }
+    __syncthreads();
+  }
+  // combine the thread groups in a fixed order (group 0 + group 1 + ...) and write the chunk's partial blocks
+  double* out = part + P.chunk_part_off[c];
+  double* cout = cpart + P.chunk_cpart_off[c];
+  for (int g = 1; g < groups; ++g) {
+    if (worker && grp == g) {
+#pragma unroll
+      for (int k = 0; k < 36; ++k) stage[q * 43 + k] = acc[k];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) stage[q * 43 + 36 + k] = cacc[k];
+    }
+    __syncthreads();
+    if (worker && grp == 0) {
+#pragma unroll
+      for (int k = 0; k < 36; ++k) acc[k] += stage[q * 43 + k];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) cacc[k] += stage[q * 43 + 36 + k];
+    }
+    __syncthreads();
+  }
+  if (worker && grp == 0) {
+#pragma unroll
+    for (int k = 0; k < 36; ++k) out[(size_t)q * 36 + k] = acc[k];
+    if (A == B) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) cout[A * 6 + k] = cacc[k];
+    }
+  }
+}
+
+// ===================================================================================================
 // K5b: reduced-system assembly, atomics-free. One warp per pose-pair block (a <= b): lanes stride over the
 // items (observation pairs sharing a landmark), each lane accumulates a full 6x6, butterfly reduction gives a
 // fixed summation order. Diagonal blocks add sum F^T F and produce the reduced right-hand side.
@@ -409,6 +519,7 @@ __device__ __forceinline__ void store_sub3(double* S, int ld, int rt, int ct, co
   else { for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) S[(size_t)(rt + i) * ld + ct + j] = B[3 * i + j]; }
 }
 __global__ void __launch_bounds__(128) pair_kernel(DeviceProblem P, const double* __restrict__ Vrec,
+                                                   const double* __restrict__ part, const double* __restrict__ cpart,
                                                    const double* __restrict__ pose_H, const double* __restrict__ grad,
                                                    double* __restrict__ S, double* __restrict__ rhs, const LMState* st) {
   if (!gate_run(st)) return;
@@ -437,6 +548,17 @@ __global__ void __launch_bounds__(128) pair_kernel(DeviceProblem P, const double
     if (oi == oj) {
 #pragma unroll
       for (int k = 0; k < 3; ++k) { const double2 u = vi[9 + k]; cacc[2 * k] += u.x; cacc[2 * k + 1] += u.y; }
+    }
+  }
+  // partial blocks accumulated on chip by the chunks that contain both poses (fixed list order)
+  for (int it = P.pp_ptr[pb] + lane; it < P.pp_ptr[pb + 1]; it += 32) {
+    const double2* pp = reinterpret_cast<const double2*>(part + P.pp_off[it]);
+#pragma unroll
+    for (int k = 0; k < 18; ++k) { const double2 u = pp[k]; acc[2 * k] += u.x; acc[2 * k + 1] += u.y; }
+    const long long co = P.pp_coff[it];
+    if (co >= 0) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) cacc[k] += cpart[co + k];
     }
   }
 #pragma unroll
@@ -642,7 +764,7 @@ __global__ void __launch_bounds__(128) chol_update_kernel(double* __restrict__ S
 }
 // Tiny reduced systems (n <= 160: the 10-keyframe VIO window): the whole matrix lives in shared memory for the
 // factorisation and both triangular solves; one launch, one CTA.
-constexpr int kTinyMax = 160, kTinyThreads = 1024;
+constexpr int kTinyMax = 160, kTinyThreads = 512;
 __global__ void __launch_bounds__(kTinyThreads) chol_tiny_kernel(const double* __restrict__ S, int n, const double* __restrict__ rhs,
                                                                  double* __restrict__ y, LMState* st) {
   extern __shared__ __align__(16) double smem_dyn[];
