@@ -625,6 +625,11 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     chunk_begin.push_back(h->ne);
   }
   h->nchunks = (int)chunk_nslots.size();
+  if (std::getenv("BSNLS_DEBUG")) {
+    long long slots = 0, nwide = 0; for (int v : chunk_nslots) slots += v; for (char w : wide) nwide += w;
+    std::fprintf(stderr, "[bsnls] rank %d: %d landmarks, %d obs, %d poses, %d pairs, %d chunks (avg %.1f slots, %.1f landmarks), %lld wide landmarks, partial buffer %.1f MB\n",
+                 h->rank, h->ne, nobs_local, h->np, h->npairs, h->nchunks, h->nchunks ? (double)slots / h->nchunks : 0.0, h->nchunks ? (double)h->ne / h->nchunks : 0.0, nwide, part_size * 8e-6);
+  }
   // ---- per pair: partial blocks produced by the chunks, and items of the wide landmarks ----
   std::vector<int> pair_ptr(h->npairs + 1, 0), item_i, item_j, pp_ptr(h->npairs + 1, 0);
   std::vector<long long> pp_off, pp_coff;

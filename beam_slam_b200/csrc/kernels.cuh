@@ -447,13 +447,28 @@ __global__ void __launch_bounds__(256) chunk_accum_kernel(DeviceProblem P, const
     const int o0 = P.lm_ptr[l0], o1 = P.lm_ptr[l1];
     for (int l = tid; l < l1 - l0; l += 256) mask[l] = 0u;
     __syncthreads();
-    for (int e = tid; e < (o1 - o0) * 24; e += 256) {
-      const int o = o0 + e / 24, w = e - 24 * (e / 24);
-      const int sl = P.obs_slot[o];
-      if (sl == 255) continue;
-      const int l = P.obs_lm[o] - l0;
-      stage[l * lstride + sl * 25 + w] = Vrec[(size_t)o * kVRec + w];
-      if (w == 0) atomicOr(&mask[l], 1u << sl);
+    // staging: 12 lanes per record (one double2 each), 21 records in flight per sweep, 4 sweeps unrolled so that the
+    // independent global loads overlap (8 warps per SM cannot hide HBM latency otherwise)
+    if (tid < 252) {
+      const int sub = tid % 12, oo = tid / 12;
+      for (int ob = o0 + oo; ob < o1; ob += 84) {
+        double2 v[4]; int sl[4], ll[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int o = ob + 21 * u;
+          const bool ok = o < o1;
+          sl[u] = ok ? (int)P.obs_slot[o] : 255;
+          ll[u] = ok ? P.obs_lm[o] - l0 : 0;
+          v[u] = ok ? reinterpret_cast<const double2*>(Vrec + (size_t)o * kVRec)[sub] : make_double2(0.0, 0.0);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (sl[u] == 255) continue;
+          double* dst = stage + ll[u] * lstride + sl[u] * 25 + 2 * sub;
+          dst[0] = v[u].x; dst[1] = v[u].y;
+          if (sub == 0) atomicOr(&mask[ll[u]], 1u << sl[u]);
+        }
+      }
     }
     __syncthreads();
     if (worker) {
