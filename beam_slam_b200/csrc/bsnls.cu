@@ -594,7 +594,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   long long part_size = 0, cpart_size = 0;
   {
     std::vector<int> stamp(h->np, -1), cur_poses;
-    int c_begin = 0, c_obs = 0;
+    int c_begin = 0, c_obs = 0, c_kmax = 0;
     auto close_chunk = [&](int end) {
       if (end == c_begin) return;
       std::sort(cur_poses.begin(), cur_poses.end());           // slots in increasing pose id: slot A < B  <=>  pose a < b
@@ -606,7 +606,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       const long long ns = (long long)cur_poses.size();
       part_size += ns * (ns + 1) / 2 * 36; cpart_size += ns * 6;
       for (int pz : cur_poses) stamp[pz] = -1;
-      cur_poses.clear(); c_begin = end; c_obs = 0;
+      cur_poses.clear(); c_begin = end; c_obs = 0; c_kmax = 0;
     };
     for (int e = 0; e < h->ne; ++e) {
       const int k0 = lm_ptr_local[e], k1 = lm_ptr_local[e + 1];
@@ -616,7 +616,9 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       if (is_wide) { wide[e] = 1; continue; }
       int fresh = 0;
       for (int k = k0; k < k1; ++k) if (stamp[s_pose[k]] == -1) ++fresh;
-      if ((int)cur_poses.size() + fresh > kChunkSlots || c_obs + (k1 - k0) > kChunkMaxObs) { close_chunk(e); }
+      const int limit = std::min(kChunkSlots, std::max(c_kmax, k1 - k0) + kChunkSlack);
+      if ((int)cur_poses.size() + fresh > limit || c_obs + (k1 - k0) > kChunkMaxObs) { close_chunk(e); }
+      c_kmax = std::max(c_kmax, k1 - k0);
       for (int k = k0; k < k1; ++k) if (stamp[s_pose[k]] == -1) { stamp[s_pose[k]] = -3; cur_poses.push_back(s_pose[k]); }
       c_obs += k1 - k0;
     }

@@ -16,7 +16,8 @@ constexpr int kVRec = 24;   // per observation: V[18] (6x3 = F^T E C) | c[6] (= 
 constexpr int kGfMaxBlocks = 10, kGfMaxRes = 15, kGfMaxAmbient = 32;
 constexpr int kChunkSlots = 22;        // poses per chunk: 22*23/2 = 253 pair blocks <= 256 threads
 constexpr int kChunkMaxObs = 4096;     // observations per chunk (load balance vs. partial-block traffic)
-constexpr int kChunkStageDoubles = 17920;   // staging buffer (140 KiB) for the V records of a batch of landmarks
+constexpr int kChunkSlack = 2;          // a chunk closes when its pose set exceeds (longest track in it) + slack: keeps most pairs present
+constexpr int kChunkStageDoubles = 11008;   // staging buffer (86 KiB): two CTAs per SM
 constexpr int kChunkSmemBytes = kChunkStageDoubles * 8;
 
 struct LMState {
@@ -415,7 +416,7 @@ __global__ void __launch_bounds__(256) grad_norm_kernel(DeviceProblem P, const d
 // alternate landmarks and are combined in a fixed order. Output: partial pair blocks + per-slot sums of c = V z,
 // reduced across chunks by pair_kernel.
 // ===================================================================================================
-__global__ void __launch_bounds__(256) chunk_accum_kernel(DeviceProblem P, const double* __restrict__ Vrec,
+__global__ void __launch_bounds__(256, 2) chunk_accum_kernel(DeviceProblem P, const double* __restrict__ Vrec,
                                                           double* __restrict__ part, double* __restrict__ cpart,
                                                           const LMState* st) {
   extern __shared__ __align__(16) double stage[];   // [landmark in batch][slot][25]  (24 used; odd stride: conflict-free)
@@ -477,14 +478,15 @@ __global__ void __launch_bounds__(256) chunk_accum_kernel(DeviceProblem P, const
         if (!((m >> A) & 1u) || !((m >> B) & 1u)) continue;
         const double* va = stage + l * lstride + A * 25;
         const double* vb = stage + l * lstride + B * 25;
-        double Va[18], Vb[18];
+        double Vb[18];
 #pragma unroll
-        for (int k = 0; k < 18; ++k) { Va[k] = va[k]; Vb[k] = vb[k]; }
+        for (int k = 0; k < 18; ++k) Vb[k] = vb[k];
 #pragma unroll
-        for (int i = 0; i < 6; ++i)
+        for (int i = 0; i < 6; ++i) {
+          const double a0 = va[3 * i], a1 = va[3 * i + 1], a2 = va[3 * i + 2];   // rows of V_A are streamed (register budget)
 #pragma unroll
-          for (int j = 0; j < 6; ++j)
-            acc[6 * i + j] += Va[3 * i] * Vb[3 * j] + Va[3 * i + 1] * Vb[3 * j + 1] + Va[3 * i + 2] * Vb[3 * j + 2];
+          for (int j = 0; j < 6; ++j) acc[6 * i + j] += a0 * Vb[3 * j] + a1 * Vb[3 * j + 1] + a2 * Vb[3 * j + 2];
+        }
         if (A == B) {
 #pragma unroll
           for (int k = 0; k < 6; ++k) cacc[k] += va[18 + k];
