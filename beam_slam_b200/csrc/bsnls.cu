@@ -232,7 +232,7 @@ int EnqueueAssemble(bsnls_handle* h, const Options& o) {  // phase D1: reduced s
   if (h->world > 1) cudaMemsetAsync(h->d_rhs.p, 0, sizeof(double) * P.nf_dim, h->stream);
   MARK(h, 6);
   if (h->nchunks) LAUNCH_SMEM(h, chunk_accum_kernel, h->nchunks, 256, kChunkSmemBytes, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), st);
-  if (h->npairs) LAUNCH(h, pair_kernel, BlocksFor(h->npairs, 4), 128, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
+  if (h->npairs) LAUNCH(h, pair_reduce_kernel, BlocksFor(h->npairs, 4), 144, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), h->d_poseH.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
   MARK(h, 7);
   if (h->world > 1) {  // the one exchange step of the path: sum the per-shard reduced camera systems over NVLink
     Nccl().GroupStart();

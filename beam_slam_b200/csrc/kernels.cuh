@@ -611,6 +611,51 @@ __global__ void __launch_bounds__(128) pair_kernel(DeviceProblem P, const double
     }
 }
 
+// K5b (reduce): final reduction of the reduced-system blocks. One thread per (pose pair, block element): sums the
+// chunk partials of its element in list order (coalesced: the 36 elements of a partial block are contiguous), adds the
+// contributions of wide landmarks from the item list, subtracts from sum F^T F on the diagonal blocks and writes
+// S (dense lower triangle or 3x3 block-sparse) and the reduced right-hand side. 4 pairs per 144-thread CTA.
+__global__ void __launch_bounds__(144) pair_reduce_kernel(DeviceProblem P, const double* __restrict__ Vrec,
+                                                          const double* __restrict__ part, const double* __restrict__ cpart,
+                                                          const double* __restrict__ pose_H, double* __restrict__ S,
+                                                          double* __restrict__ rhs, const LMState* st) {
+  if (!gate_run(st)) return;
+  const int pb = blockIdx.x * 4 + threadIdx.x / 36, e = threadIdx.x % 36;
+  if (pb >= P.num_pairs) return;
+  const int a = P.pair_a[pb], b = P.pair_b[pb];
+  const int i = e / 6, j = e - 6 * i;
+  double acc = 0.0, cacc = 0.0;
+  for (int it = P.pp_ptr[pb]; it < P.pp_ptr[pb + 1]; ++it) {
+    acc += part[P.pp_off[it] + e];
+    if (e < 6 && P.pp_coff[it] >= 0) cacc += cpart[P.pp_coff[it] + e];
+  }
+  for (int it = P.pair_ptr[pb]; it < P.pair_ptr[pb + 1]; ++it) {   // wide landmarks
+    const int oi = P.item_i[it], oj = P.item_j[it];
+    const double* vi = Vrec + (size_t)oi * kVRec + 3 * i; const double* vj = Vrec + (size_t)oj * kVRec + 3 * j;
+    acc += vi[0] * vj[0] + vi[1] * vj[1] + vi[2] * vj[2];
+    if (e < 6 && oi == oj) cacc += Vrec[(size_t)oi * kVRec + 18 + e];
+  }
+  const int sa = i / 3, sb = j / 3, ii = i - 3 * sa, jj = j - 3 * sb;
+  const int ta = (sa ? P.pose_t_tan[a] : P.pose_q_tan[a]), tb = (sb ? P.pose_t_tan[b] : P.pose_q_tan[b]);
+  double v = -acc;
+  if (a == b) {
+    const int lo = min(i, j), hi = max(i, j);
+    v += pose_H[(size_t)a * 21 + lo * 6 - lo * (lo - 1) / 2 + (hi - lo)];   // packed upper triangle, row-major
+    if (e < 6) { const int t = (e < 3 ? P.pose_q_tan[a] : P.pose_t_tan[a]); if (t >= 0) rhs[t - P.ne_dim + e % 3] = -cacc; }   // + gradient in finish_system
+  }
+  if (ta < 0 || tb < 0) return;
+  if (P.sparse) {
+    if (a == b && sa > sb) return;   // the (q,t) threads write both the block and its transpose
+    const int slot = P.pair_slot[pb * 8 + 2 * sa + sb], slot_t = P.pair_slot[pb * 8 + 4 + 2 * sa + sb];
+    S[(size_t)slot * 9 + 3 * ii + jj] = v;
+    if (slot_t >= 0 && slot_t != slot) S[(size_t)slot_t * 9 + 3 * jj + ii] = v;
+    return;
+  }
+  const int r = ta - P.ne_dim + ii, c = tb - P.ne_dim + jj, ld = P.nf_dim;
+  if (a == b) { if (r >= c) S[(size_t)c * ld + r] = v; }     // symmetric block: the mirrored thread holds the other triangle
+  else if (r >= c) S[(size_t)c * ld + r] = v; else S[(size_t)r * ld + c] = v;
+}
+
 // K6c: generic-factor contributions to S (3x3 destinations, row >= col) and to rhs. 9 threads per destination.
 __global__ void __launch_bounds__(144) gf_schur_kernel(DeviceProblem P, const double* __restrict__ gfJ,
                                                        double* __restrict__ S, const LMState* st) {
