@@ -644,7 +644,11 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     }
     for (int c = 0; c < h->nchunks; ++c) {
       const int ns = chunk_nslots[c];
-      for (int A = 0; A < ns; ++A) for (int B = A; B < ns; ++B) pcnt[key_id[key_of(chunk_pose[(size_t)c * kChunkSlots + A], chunk_pose[(size_t)c * kChunkSlots + B])]]++;
+      for (int A = 0; A < ns; ++A) for (int B = A; B < ns; ++B) {
+        // two poses of a chunk need not share a landmark: such a slot pair is not a block of S (its partial block stays zero)
+        auto kit = key_id.find(key_of(chunk_pose[(size_t)c * kChunkSlots + A], chunk_pose[(size_t)c * kChunkSlots + B]));
+        if (kit != key_id.end()) pcnt[kit->second]++;
+      }
     }
     for (int k = 0; k < h->npairs; ++k) { pair_ptr[k + 1] = pair_ptr[k] + cnt[k]; pp_ptr[k + 1] = pp_ptr[k] + pcnt[k]; }
     const int64_t nitems = pair_ptr[h->npairs];
@@ -665,13 +669,20 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       const int ns = chunk_nslots[c];
       int q = 0;
       for (int A = 0; A < ns; ++A) for (int B = A; B < ns; ++B, ++q) {
-        const int id = key_id[key_of(chunk_pose[(size_t)c * kChunkSlots + A], chunk_pose[(size_t)c * kChunkSlots + B])];
+        auto kit = key_id.find(key_of(chunk_pose[(size_t)c * kChunkSlots + A], chunk_pose[(size_t)c * kChunkSlots + B]));
+        if (kit == key_id.end()) continue;
+        const int id = kit->second;
         pp_off[pcur[id]] = chunk_part_off[c] + (long long)q * 36;
         pp_coff[pcur[id]] = A == B ? chunk_cpart_off[c] + (long long)A * 6 : -1;
         pcur[id]++;
       }
     }
     h->nitems = nitems;
+    if (std::getenv("BSNLS_DEBUG")) {
+      int mx = 0, mxc = 0; long long tot = 0; for (int k = 0; k < h->npairs; ++k) { mx = std::max(mx, pp_ptr[k + 1] - pp_ptr[k]); tot += pp_ptr[k + 1] - pp_ptr[k]; }
+      for (int c = 0; c < h->nchunks; ++c) mxc = std::max(mxc, chunk_begin[c + 1] - chunk_begin[c]);
+      std::fprintf(stderr, "[bsnls] partial lists: total %lld, max per pair %d, avg %.2f; items %lld; largest chunk %d landmarks\n", tot, mx, h->npairs ? (double)tot / h->npairs : 0.0, (long long)nitems, mxc);
+    }
   }
 
   // ---- generic factors (type-major; factors whose blocks are all constant go last: fixed cost) ----

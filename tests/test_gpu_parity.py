@@ -113,8 +113,9 @@ def test_solve_matches_oracle_per_iteration(case):
     for a, b in zip(its, ito):
         assert a.iteration == b.iteration and a.step_is_successful == b.step_is_successful
         assert abs(a.cost - b.cost) <= 1e-9 * abs(b.cost)
-        step_tol = 1e-9 if a.iteration <= 1 else 1e-5   # see the module docstring (finite-difference J_q)
-        assert abs(a.step_norm - b.step_norm) <= step_tol * max(abs(b.step_norm), 1e-12)
+        # see the module docstring (finite-difference J_q): later steps drift by ~1e-8 of the first step's length
+        step_tol = 1e-9 * b.step_norm if a.iteration <= 1 else 1e-5 * b.step_norm + 1e-6 * ito[1].step_norm
+        assert abs(a.step_norm - b.step_norm) <= max(step_tol, 1e-21)
         assert abs(a.trust_region_radius - b.trust_region_radius) <= 1e-9 * b.trust_region_radius
     assert abs(summ.final_cost - so.final_cost) <= 1e-9 * so.final_cost
     assert abs(summ.initial_cost - so.initial_cost) <= 1e-12 * so.initial_cost
