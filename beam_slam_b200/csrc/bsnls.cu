@@ -84,7 +84,7 @@ struct bsnls_handle {
       d_gf_roff, d_pair_a, d_pair_b, d_pair_ptr, d_item_i, d_item_j, d_fg_ptr, d_fg_fac, d_fg_lb, d_gd_row, d_gd_col,
       d_gd_ptr, d_gd_fac, d_gd_bi, d_gd_bj, d_is_pose, d_bsr_rowptr, d_bsr_col, d_diag_slot, d_pair_slot, d_gd_slot,
       d_pcg_x, d_pcg_r, d_pcg_z, d_pcg_p, d_pcg_Ap, d_pcg_Minv, d_pcg_part;
-  DevMem d_invd, d_Sdense, d_gradL, d_colsqL, d_gradS, d_colsqS;
+  DevMem d_lmz, d_invd, d_Sdense, d_gradL, d_colsqL, d_gradS, d_colsqS;
   DevMem d_x, d_xc, d_x0, d_Jrec, d_Vrec, d_minv, d_grad, d_colsq, d_scale, d_y, d_yf, d_rhs, d_S, d_poseH, d_gfJ,
       d_gfR, d_cost_part, d_cand_part, d_model_part, d_step_part, d_candsq_part, d_gsq_part, d_gmax_part, d_xsq_part,
       d_red, d_state, d_recs;
@@ -183,7 +183,7 @@ void EnqueueEval(bsnls_handle* h) {  // phase A: residuals + Jacobians + cost at
 }
 template <int G> void LaunchLandmark(bsnls_handle* h, const Options& o) {
   LAUNCH(h, landmark_kernel<G>, BlocksFor(h->ne * G, 256), 256, h->P, h->d_Jrec.as<double>(), h->d_Vrec.as<double>(), h->d_minv.as<double>(),
-         h->d_grad.as<double>(), h->d_colsq.as<double>(), h->d_scale.as<double>(), o, h->d_state.as<LMState>());
+         h->d_grad.as<double>(), h->d_colsq.as<double>(), h->d_scale.as<double>(), h->d_lmz.as<double>(), o, h->d_state.as<LMState>());
 }
 void EnqueueLandmark(bsnls_handle* h, const Options& o) {  // phase B
   if (!h->ne) return;
@@ -231,7 +231,11 @@ int EnqueueAssemble(bsnls_handle* h, const Options& o) {  // phase D1: reduced s
   cudaMemsetAsync(h->d_S.p, 0, sizeof(double) * s_count, h->stream);
   if (h->world > 1) cudaMemsetAsync(h->d_rhs.p, 0, sizeof(double) * P.nf_dim, h->stream);
   MARK(h, 6);
-  if (h->nchunks) LAUNCH_SMEM(h, chunk_accum_kernel, h->nchunks, 256, kChunkSmemBytes, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), st);
+  if (h->nchunks) {
+    static const bool use_fma = std::getenv("BSNLS_CHUNK_FMA") != nullptr;   // scalar-FMA variant kept for comparison
+    if (use_fma) LAUNCH_SMEM(h, chunk_accum_kernel, h->nchunks, 256, kChunkSmemBytes, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), st);
+    else LAUNCH_SMEM(h, chunk_syrk_kernel, h->nchunks, 256, kSyrkSmemBytes, P, h->d_Vrec.as<double>(), h->d_lmz.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), st);
+  }
   if (h->npairs) LAUNCH(h, pair_reduce_kernel, BlocksFor(h->npairs, 4), 144, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), h->d_poseH.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
   MARK(h, 7);
   if (h->world > 1) {  // the one exchange step of the path: sum the per-shard reduced camera systems over NVLink
@@ -379,6 +383,7 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
       (e = cudaEventCreate(&h->ev2)) != cudaSuccess) {
     g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
   }
+  if ((e = cudaFuncSetAttribute(chunk_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkSmemBytes)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chunk_accum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kChunkSmemBytes)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chol_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kTinyMax * (kTinyMax + 1) + 2 * kTinyMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kSmallMax * kNB + kSmallMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
@@ -837,7 +842,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   h->nb_obs = h->nobs ? BlocksFor(h->nobs, 256) : 0; h->nb_lm = h->ne ? BlocksFor(h->ne * h->G, 256) : 0; h->nb_act = BlocksFor((int)h->active_blocks.size(), 256);
   CK(h->d_x.alloc(sizeof(double) * off)); CK(h->d_xc.alloc(sizeof(double) * off)); CK(h->d_x0.alloc(sizeof(double) * off));
   CK(h->d_Jrec.alloc(sizeof(double) * kJRec * (size_t)h->nobs)); CK(h->d_Vrec.alloc(sizeof(double) * kVRec * (size_t)h->nobs));
-  CK(h->d_minv.alloc(sizeof(double) * 6 * (size_t)h->ne)); CK(h->d_grad.alloc(sizeof(double) * ntan)); CK(h->d_colsq.alloc(sizeof(double) * ntan));
+  CK(h->d_minv.alloc(sizeof(double) * 6 * (size_t)h->ne)); CK(h->d_lmz.alloc(sizeof(double) * 3 * (size_t)h->ne)); CK(h->d_grad.alloc(sizeof(double) * ntan)); CK(h->d_colsq.alloc(sizeof(double) * ntan));
   CK(h->d_gradL.alloc(sizeof(double) * nf_dim)); CK(h->d_colsqL.alloc(sizeof(double) * nf_dim));
   CK(cudaMemsetAsync(h->d_gradL.p, 0, sizeof(double) * nf_dim, s)); CK(cudaMemsetAsync(h->d_colsqL.p, 0, sizeof(double) * nf_dim, s));  // non-pose entries stay 0
   if (h->world > 1) { CK(h->d_gradS.alloc(sizeof(double) * nf_dim)); CK(h->d_colsqS.alloc(sizeof(double) * nf_dim)); }

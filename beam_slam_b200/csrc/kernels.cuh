@@ -77,6 +77,13 @@ struct Options { double min_lm_diagonal, max_lm_diagonal, function_tolerance, gr
 __device__ __forceinline__ bool gate_run(const LMState* st) { return !st->done; }
 __device__ __forceinline__ bool gate_jac(const LMState* st) { return !st->done && st->need_jacobian; }
 
+// FP64 tensor-core MMA (DMMA): D(8x8) += A(8x4, row) * B(4x8, col). Lane fragments: a = A[lane/4][lane%4],
+// b = B[lane%4][lane/4], d0/d1 = D[lane/4][2*(lane%4) + {0,1}].
+__device__ __forceinline__ void dmma_m8n8k4(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
 // deterministic block reduction (fixed tree), result valid in thread 0
 template <int BLOCK> __device__ __forceinline__ double block_sum(double v, double* sm) {
   sm[threadIdx.x] = v; __syncthreads();
@@ -225,7 +232,7 @@ template <int G>
 __global__ void __launch_bounds__(256) landmark_kernel(DeviceProblem P, const double* __restrict__ Jrec,
                                                        double* __restrict__ Vrec, double* __restrict__ lm_minv,
                                                        double* __restrict__ grad, double* __restrict__ colsq,
-                                                       double* __restrict__ scale, Options opt, LMState* st) {
+                                                       double* __restrict__ scale, double* __restrict__ lm_z, Options opt, LMState* st) {
   if (!gate_run(st)) return;
   const int gtid = blockIdx.x * 256 + threadIdx.x;
   const int l = gtid / G, sub = gtid % G;
@@ -277,6 +284,7 @@ __global__ void __launch_bounds__(256) landmark_kernel(DeviceProblem P, const do
     mi[3] = i11 * i11 + i21 * i21; mi[4] = i21 * i22; mi[5] = i22 * i22;
     grad[te] = g0; grad[te + 1] = g1; grad[te + 2] = g2;
     colsq[te] = a00; colsq[te + 1] = a11; colsq[te + 2] = a22;
+    lm_z[te] = z0; lm_z[te + 1] = z1; lm_z[te + 2] = z2;   // z = C^T E^T r: the Schur right-hand side is sum V z
   }
   // pass 2: V = (F^T E) C with C = Linv^T (upper):  V[:,0] = W0 i00; V[:,1] = W0 i10 + W1 i11; V[:,2] = W0 i20 + W1 i21 + W2 i22
   for (int o = start + sub; o < end; o += G) {
@@ -520,6 +528,102 @@ __global__ void __launch_bounds__(256, 2) chunk_accum_kernel(DeviceProblem P, co
     if (A == B) {
 #pragma unroll
       for (int k = 0; k < 6; ++k) cout[A * 6 + k] = cacc[k];
+    }
+  }
+}
+
+// ===================================================================================================
+// K5b (tensor): the chunk accumulation as a symmetric rank-k update on the FP64 tensor cores. For a chunk with ns pose
+// slots, stack the V records of landmark l into a (6 ns + 1) x 3 block column W_l (rows of absent slots zero, last
+// row = z_l^T); then  sum_l W_l W_l^T  holds every pair block sum_l V_A V_B^T and, in its last column, sum_l V_A z_l
+// (the Schur right-hand side). W is staged in shared memory 32 landmarks (96 columns) at a time; each warp owns a
+// contiguous range of the upper-triangular 8x8 tiles and issues mma.sync.m8n8k4.f64 (DMMA) on them.
+// Deterministic: fixed tile ownership, fixed k order. Same outputs as chunk_accum_kernel.
+// ===================================================================================================
+constexpr int kSyrkKB = 96, kSyrkLD = 100, kSyrkMaxRows = 136, kSyrkMaxTiles = 20;
+constexpr int kSyrkSmemBytes = kSyrkMaxRows * kSyrkLD * 8;
+__global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, const double* __restrict__ Vrec, const double* __restrict__ lm_z,
+                                                            double* __restrict__ part, double* __restrict__ cpart, const LMState* st) {
+  extern __shared__ __align__(16) double W[];    // W[row * kSyrkLD + k]
+  __shared__ unsigned char tI[160], tJ[160];
+  if (!gate_run(st)) return;
+  const int c = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
+  const int ns = P.chunk_nslots[c], nrow = 6 * ns + 1, nt = (nrow + 7) >> 3, T = nt * (nt + 1) / 2, nrow8 = nt * 8;
+  const int l_begin = P.chunk_begin[c], l_end = P.chunk_begin[c + 1];
+  for (int t = tid; t < T; t += 256) { int q = t, I = 0; while (q >= nt - I) { q -= nt - I; ++I; } tI[t] = (unsigned char)I; tJ[t] = (unsigned char)(I + q); }
+  const int t0 = warp * T / 8, t1 = (warp + 1) * T / 8;
+  double acc[kSyrkMaxTiles][2];
+#pragma unroll
+  for (int i = 0; i < kSyrkMaxTiles; ++i) { acc[i][0] = 0.0; acc[i][1] = 0.0; }
+  for (int l0 = l_begin; l0 < l_end; l0 += 32) {
+    const int l1 = min(l_end, l0 + 32);
+    const int o0 = P.lm_ptr[l0], o1 = P.lm_ptr[l1];
+    for (int e = tid; e < nrow8 * (kSyrkKB / 2); e += 256) {   // clear the live part of W (double2 stores)
+      const int r = e / (kSyrkKB / 2), k2 = e - r * (kSyrkKB / 2);
+      reinterpret_cast<double2*>(W + r * kSyrkLD)[k2] = make_double2(0.0, 0.0);
+    }
+    __syncthreads();
+    if (tid < 252) {   // 12 lanes per V record, the first 9 carry V (6x3 row-major), 4 records in flight per lane
+      const int sub = tid % 12, oo = tid / 12;
+      for (int ob = o0 + oo; ob < o1; ob += 84) {
+        double2 v[4]; int sl[4], ll[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int o = ob + 21 * u;
+          const bool ok = o < o1 && sub < 9;
+          sl[u] = ok ? (int)P.obs_slot[o] : 255;
+          ll[u] = ok ? P.obs_lm[o] - l0 : 0;
+          v[u] = ok ? reinterpret_cast<const double2*>(Vrec + (size_t)o * kVRec)[sub] : make_double2(0.0, 0.0);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (sl[u] == 255) continue;
+          const int e0 = 2 * sub, e1 = 2 * sub + 1;   // element e of the record = V[e / 3][e % 3]
+          W[(6 * sl[u] + e0 / 3) * kSyrkLD + 3 * ll[u] + e0 % 3] = v[u].x;
+          W[(6 * sl[u] + e1 / 3) * kSyrkLD + 3 * ll[u] + e1 % 3] = v[u].y;
+        }
+      }
+    }
+    for (int e = tid; e < 3 * (l1 - l0); e += 256) W[(6 * ns) * kSyrkLD + e] = lm_z[3 * (size_t)l0 + e];
+    __syncthreads();
+    const int ksteps = (3 * (l1 - l0) + 3) >> 2;
+    for (int ks = 0; ks < ksteps; ++ks) {
+      const int k0 = 4 * ks + tg;
+      int lastI = -1; double a = 0.0;
+#pragma unroll
+      for (int ti = 0; ti < kSyrkMaxTiles; ++ti) {
+        const int t = t0 + ti;
+        if (t < t1) {
+          const int I = tI[t], J = tJ[t];
+          if (I != lastI) { a = W[(8 * I + g) * kSyrkLD + k0]; lastI = I; }   // consecutive tiles of a warp mostly share the row strip
+          const double b = W[(8 * J + g) * kSyrkLD + k0];
+          dmma_m8n8k4(acc[ti][0], acc[ti][1], a, b);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  // scatter the tiles into the chunk's pair blocks: entry (r, c), slots A = r / 6 <= B = c / 6
+  double* out = part + P.chunk_part_off[c];
+  double* cout = cpart + P.chunk_cpart_off[c];
+  const int zrow = 6 * ns;
+#pragma unroll
+  for (int ti = 0; ti < kSyrkMaxTiles; ++ti) {
+    const int t = t0 + ti;
+    if (t >= t1) continue;
+    const int I = tI[t], J = tJ[t];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int r = 8 * I + g, cc = 8 * J + 2 * tg + h;
+      const double v = acc[ti][h];
+      if (r >= zrow || cc > zrow) continue;
+      const int A = r / 6, i = r - 6 * A;
+      if (cc == zrow) { cout[A * 6 + i] = v; continue; }
+      const int B = cc / 6, j = cc - 6 * B;
+      if (A > B) continue;                         // mirrored entry of a diagonal tile
+      double* blk = out + (size_t)(A * ns - A * (A - 1) / 2 + (B - A)) * 36;
+      blk[6 * i + j] = v;
+      if (A == B && i != j) blk[6 * j + i] = v;    // the diagonal blocks are symmetric; take both halves from the upper entry
     }
   }
 }
@@ -775,10 +879,6 @@ __global__ void __launch_bounds__(256) chol_trsm_kernel(double* __restrict__ S, 
       S[(size_t)(j0 + c) * n + row] = xv[c];
     } else xv[c] = 0.0;
   }
-}
-__device__ __forceinline__ void dmma_m8n8k4(double& d0, double& d1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-               : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 __global__ void __launch_bounds__(128) chol_update_kernel(double* __restrict__ S, int n, int j0, const LMState* st) {
   if (!gate_run(st) || st->lin_fail) return;
