@@ -551,10 +551,11 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
   const int ns = P.chunk_nslots[c], nrow = 6 * ns + 1, nt = (nrow + 7) >> 3, T = nt * (nt + 1) / 2, nrow8 = nt * 8;
   const int l_begin = P.chunk_begin[c], l_end = P.chunk_begin[c + 1];
   for (int t = tid; t < T; t += 256) { int q = t, I = 0; while (q >= nt - I) { q -= nt - I; ++I; } tI[t] = (unsigned char)I; tJ[t] = (unsigned char)(I + q); }
-  const int t0 = warp * T / 8, t1 = (warp + 1) * T / 8;
-  double acc[kSyrkMaxTiles][2];
+  const int t0 = warp * T / 8, t1 = (warp + 1) * T / 8, ngrp = (t1 - t0 + 3) >> 2;
+  // accumulators of this warp's tiles, 4 tiles at a time in registers; the rest waits in (L1-resident) local memory
+  double accs[kSyrkMaxTiles][2];
 #pragma unroll
-  for (int i = 0; i < kSyrkMaxTiles; ++i) { acc[i][0] = 0.0; acc[i][1] = 0.0; }
+  for (int i = 0; i < kSyrkMaxTiles; ++i) { accs[i][0] = 0.0; accs[i][1] = 0.0; }
   for (int l0 = l_begin; l0 < l_end; l0 += 32) {
     const int l1 = min(l_end, l0 + 32);
     const int o0 = P.lm_ptr[l0], o1 = P.lm_ptr[l1];
@@ -565,6 +566,8 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
     __syncthreads();
     if (tid < 252) {   // 12 lanes per V record, the first 9 carry V (6x3 row-major), 4 records in flight per lane
       const int sub = tid % 12, oo = tid / 12;
+      const int e0 = 2 * sub, e1 = 2 * sub + 1;   // element e of the record = V[e / 3][e % 3]
+      const int off0 = (e0 / 3) * kSyrkLD + e0 % 3, off1 = (e1 / 3) * kSyrkLD + e1 % 3;
       for (int ob = o0 + oo; ob < o1; ob += 84) {
         double2 v[4]; int sl[4], ll[4];
 #pragma unroll
@@ -578,28 +581,28 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           if (sl[u] == 255) continue;
-          const int e0 = 2 * sub, e1 = 2 * sub + 1;   // element e of the record = V[e / 3][e % 3]
-          W[(6 * sl[u] + e0 / 3) * kSyrkLD + 3 * ll[u] + e0 % 3] = v[u].x;
-          W[(6 * sl[u] + e1 / 3) * kSyrkLD + 3 * ll[u] + e1 % 3] = v[u].y;
+          double* base = W + 6 * sl[u] * kSyrkLD + 3 * ll[u];
+          base[off0] = v[u].x; base[off1] = v[u].y;
         }
       }
     }
     for (int e = tid; e < 3 * (l1 - l0); e += 256) W[(6 * ns) * kSyrkLD + e] = lm_z[3 * (size_t)l0 + e];
     __syncthreads();
     const int ksteps = (3 * (l1 - l0) + 3) >> 2;
-    for (int ks = 0; ks < ksteps; ++ks) {
-      const int k0 = 4 * ks + tg;
-      int lastI = -1; double a = 0.0;
+    for (int gq = 0; gq < ngrp; ++gq) {
+      const double* pa[4]; const double* pb[4]; double a4[4][2];
 #pragma unroll
-      for (int ti = 0; ti < kSyrkMaxTiles; ++ti) {
-        const int t = t0 + ti;
-        if (t < t1) {
-          const int I = tI[t], J = tJ[t];
-          if (I != lastI) { a = W[(8 * I + g) * kSyrkLD + k0]; lastI = I; }   // consecutive tiles of a warp mostly share the row strip
-          const double b = W[(8 * J + g) * kSyrkLD + k0];
-          dmma_m8n8k4(acc[ti][0], acc[ti][1], a, b);
-        }
+      for (int u = 0; u < 4; ++u) {
+        const int t = min(t0 + 4 * gq + u, t1 - 1);                 // the tail repeats the last tile; its result is dropped
+        pa[u] = W + (8 * tI[t] + g) * kSyrkLD + tg; pb[u] = W + (8 * tJ[t] + g) * kSyrkLD + tg;
+        a4[u][0] = accs[4 * gq + u][0]; a4[u][1] = accs[4 * gq + u][1];
       }
+      for (int ks = 0; ks < ksteps; ++ks) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) dmma_m8n8k4(a4[u][0], a4[u][1], pa[u][4 * ks], pb[u][4 * ks]);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) if (t0 + 4 * gq + u < t1) { accs[4 * gq + u][0] = a4[u][0]; accs[4 * gq + u][1] = a4[u][1]; }
     }
     __syncthreads();
   }
@@ -607,15 +610,13 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
   double* out = part + P.chunk_part_off[c];
   double* cout = cpart + P.chunk_cpart_off[c];
   const int zrow = 6 * ns;
-#pragma unroll
-  for (int ti = 0; ti < kSyrkMaxTiles; ++ti) {
+  for (int ti = 0; ti < t1 - t0; ++ti) {
     const int t = t0 + ti;
-    if (t >= t1) continue;
     const int I = tI[t], J = tJ[t];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       const int r = 8 * I + g, cc = 8 * J + 2 * tg + h;
-      const double v = acc[ti][h];
+      const double v = accs[ti][h];
       if (r >= zrow || cc > zrow) continue;
       const int A = r / 6, i = r - 6 * A;
       if (cc == zrow) { cout[A * 6 + i] = v; continue; }
