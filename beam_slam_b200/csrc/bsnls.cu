@@ -236,7 +236,8 @@ int EnqueueAssemble(bsnls_handle* h, const Options& o) {  // phase D1: reduced s
     if (use_fma) LAUNCH_SMEM(h, chunk_accum_kernel, h->nchunks, 256, kChunkSmemBytes, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), st);
     else LAUNCH_SMEM(h, chunk_syrk_kernel, h->nchunks, 256, kSyrkSmemBytes, P, h->d_Vrec.as<double>(), h->d_lmz.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), st);
   }
-  if (h->npairs) LAUNCH(h, pair_reduce_kernel, BlocksFor(h->npairs, 4), 144, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), h->d_poseH.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
+  if (h->npairs && h->nchunks) LAUNCH(h, pair_reduce_kernel, BlocksFor(h->npairs, 4), 144, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), h->d_poseH.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
+  else if (h->npairs) LAUNCH(h, pair_kernel, BlocksFor(h->npairs, 4), 128, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
   MARK(h, 7);
   if (h->world > 1) {  // the one exchange step of the path: sum the per-shard reduced camera systems over NVLink
     Nccl().GroupStart();
@@ -616,7 +617,9 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     for (int e = 0; e < h->ne; ++e) {
       const int k0 = lm_ptr_local[e], k1 = lm_ptr_local[e + 1];
       // wide landmark: more poses than slots, or seen twice by one pose -> handled through the item list
-      bool is_wide = k1 - k0 > kChunkSlots;
+      // small shards: the on-chip chunk path needs a few hundred chunks to fill the GPU; below that every landmark goes
+      // through the item list (warp-per-block pair_kernel)
+      bool is_wide = k1 - k0 > kChunkSlots || nobs_local < kChunkMinObs;
       for (int k = k0; k < k1 && !is_wide; ++k) for (int k2 = k0; k2 < k; ++k2) if (s_pose[k2] == s_pose[k]) { is_wide = true; break; }
       if (is_wide) { wide[e] = 1; continue; }
       int fresh = 0;

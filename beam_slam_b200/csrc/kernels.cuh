@@ -15,6 +15,7 @@ constexpr int kJRec = 20;   // per observation: E[6] (2x3 wrt landmark) | r[2] |
 constexpr int kVRec = 24;   // per observation: V[18] (6x3 = F^T E C) | c[6] (= V z)
 constexpr int kGfMaxBlocks = 10, kGfMaxRes = 15, kGfMaxAmbient = 32;
 constexpr int kChunkSlots = 22;        // poses per chunk: 22*23/2 = 253 pair blocks <= 256 threads
+constexpr int kChunkMinObs = 100000;   // below this many observations per shard the item-list path is used instead
 constexpr int kChunkMaxObs = 4096;     // observations per chunk (load balance vs. partial-block traffic)
 constexpr int kChunkSlack = 2;          // a chunk closes when its pose set exceeds (longest track in it) + slack: keeps most pairs present
 constexpr int kChunkStageDoubles = 11008;   // staging buffer (86 KiB): two CTAs per SM
