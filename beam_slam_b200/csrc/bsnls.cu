@@ -67,7 +67,7 @@ struct bsnls_handle {
   std::vector<int> pose_q_blk, pose_t_blk;
   std::vector<int> pair_a, pair_b;
   std::vector<int> gd_row, gd_col;
-  int nchunks = 0; DevMem d_obs_slot, d_chunk_begin, d_chunk_nslots, d_chunk_part_off, d_chunk_cpart_off, d_pp_ptr, d_pp_off, d_pp_coff, d_part, d_cpart;
+  int nchunks = 0; DevMem d_obs_slot, d_chunk_end, d_chunk_begin, d_chunk_nslots, d_chunk_part_off, d_chunk_cpart_off, d_pp_ptr, d_pp_off, d_pp_coff, d_part, d_cpart;
   bool sparse = false, pcg = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
   // residual-block bookkeeping for bsnls_evaluate (program order)
   struct ResRef { int type; int idx; int row; };   // idx: sorted-observation id or generic-factor id
@@ -594,7 +594,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
 
   // ---- chunks: consecutive landmarks whose poses fit kChunkSlots slots are accumulated on chip by one CTA ----
   std::vector<unsigned char> obs_slot(nobs_local, 255);
-  std::vector<int> chunk_begin, chunk_nslots, chunk_pose;      // chunk_begin: landmark ranges (nchunks + 1)
+  std::vector<int> chunk_begin, chunk_end, chunk_nslots, chunk_pose;      // landmark range [begin, end) of each chunk
   std::vector<long long> chunk_part_off, chunk_cpart_off;
   std::vector<char> wide(h->ne, 0);
   long long part_size = 0, cpart_size = 0;
@@ -603,10 +603,11 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     int c_begin = 0, c_obs = 0, c_kmax = 0;
     auto close_chunk = [&](int end) {
       if (end == c_begin) return;
+      if (cur_poses.empty()) { c_begin = end; c_obs = 0; c_kmax = 0; return; }   // only wide landmarks: nothing to accumulate on chip
       std::sort(cur_poses.begin(), cur_poses.end());           // slots in increasing pose id: slot A < B  <=>  pose a < b
       for (size_t q = 0; q < cur_poses.size(); ++q) stamp[cur_poses[q]] = (int)q;
       for (int e = c_begin; e < end; ++e) if (!wide[e]) for (int k = lm_ptr_local[e]; k < lm_ptr_local[e + 1]; ++k) obs_slot[k] = (unsigned char)stamp[s_pose[k]];
-      chunk_begin.push_back(c_begin); chunk_nslots.push_back((int)cur_poses.size());
+      chunk_begin.push_back(c_begin); chunk_end.push_back(end); chunk_nslots.push_back((int)cur_poses.size());
       for (int q = 0; q < kChunkSlots; ++q) chunk_pose.push_back(q < (int)cur_poses.size() ? cur_poses[q] : -1);
       chunk_part_off.push_back(part_size); chunk_cpart_off.push_back(cpart_size);
       const long long ns = (long long)cur_poses.size();
@@ -632,7 +633,6 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     }
     // note: stamp == -3 marks "in the current chunk" while it is being built
     close_chunk(h->ne);
-    chunk_begin.push_back(h->ne);
   }
   h->nchunks = (int)chunk_nslots.size();
   if (std::getenv("BSNLS_DEBUG")) {
@@ -688,7 +688,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     h->nitems = nitems;
     if (std::getenv("BSNLS_DEBUG")) {
       int mx = 0, mxc = 0; long long tot = 0; for (int k = 0; k < h->npairs; ++k) { mx = std::max(mx, pp_ptr[k + 1] - pp_ptr[k]); tot += pp_ptr[k + 1] - pp_ptr[k]; }
-      for (int c = 0; c < h->nchunks; ++c) mxc = std::max(mxc, chunk_begin[c + 1] - chunk_begin[c]);
+      for (int c = 0; c < h->nchunks; ++c) mxc = std::max(mxc, chunk_end[c] - chunk_begin[c]);
       std::fprintf(stderr, "[bsnls] partial lists: total %lld, max per pair %d, avg %.2f; items %lld; largest chunk %d landmarks\n", tot, mx, h->npairs ? (double)tot / h->npairs : 0.0, (long long)nitems, mxc);
     }
   }
@@ -826,7 +826,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_gf_loss_a, gf_loss_a, s)); CK(upload(h->d_gf_joff, gf_joff, s)); CK(upload(h->d_gf_roff, gf_roff, s));
   CK(upload(h->d_pair_a, h->pair_a, s)); CK(upload(h->d_pair_b, h->pair_b, s)); CK(upload(h->d_pair_ptr, pair_ptr, s));
   CK(upload(h->d_item_i, item_i, s)); CK(upload(h->d_item_j, item_j, s));
-  CK(upload(h->d_obs_slot, obs_slot, s)); CK(upload(h->d_chunk_begin, chunk_begin, s)); CK(upload(h->d_chunk_nslots, chunk_nslots, s));
+  CK(upload(h->d_obs_slot, obs_slot, s)); CK(upload(h->d_chunk_begin, chunk_begin, s)); CK(upload(h->d_chunk_end, chunk_end, s)); CK(upload(h->d_chunk_nslots, chunk_nslots, s));
   CK(upload(h->d_chunk_part_off, chunk_part_off, s)); CK(upload(h->d_chunk_cpart_off, chunk_cpart_off, s));
   CK(upload(h->d_pp_ptr, pp_ptr, s)); CK(upload(h->d_pp_off, pp_off, s)); CK(upload(h->d_pp_coff, pp_coff, s));
   CK(h->d_part.alloc(sizeof(double) * (size_t)part_size)); CK(h->d_cpart.alloc(sizeof(double) * (size_t)cpart_size));
@@ -884,7 +884,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   P.gf_joff = h->d_gf_joff.as<int>(); P.gf_roff = h->d_gf_roff.as<int>();
   P.num_pairs = h->npairs; P.pair_a = h->d_pair_a.as<int>(); P.pair_b = h->d_pair_b.as<int>(); P.pair_ptr = h->d_pair_ptr.as<int>();
   P.item_i = h->d_item_i.as<int>(); P.item_j = h->d_item_j.as<int>();
-  P.num_chunks = h->nchunks; P.obs_slot = h->d_obs_slot.as<unsigned char>(); P.chunk_begin = h->d_chunk_begin.as<int>(); P.chunk_nslots = h->d_chunk_nslots.as<int>();
+  P.num_chunks = h->nchunks; P.obs_slot = h->d_obs_slot.as<unsigned char>(); P.chunk_begin = h->d_chunk_begin.as<int>(); P.chunk_end = h->d_chunk_end.as<int>(); P.chunk_nslots = h->d_chunk_nslots.as<int>();
   P.chunk_part_off = h->d_chunk_part_off.as<long long>(); P.chunk_cpart_off = h->d_chunk_cpart_off.as<long long>();
   P.pp_ptr = h->d_pp_ptr.as<int>(); P.pp_off = h->d_pp_off.as<long long>(); P.pp_coff = h->d_pp_coff.as<long long>();
   P.fg_ptr = h->d_fg_ptr.as<int>(); P.fg_fac = h->d_fg_fac.as<int>(); P.fg_lb = h->d_fg_lb.as<int>();

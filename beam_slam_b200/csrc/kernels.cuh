@@ -59,7 +59,7 @@ struct DeviceProblem {
   int num_pairs; const int* pair_a; const int* pair_b; const int* pair_ptr; const int* item_i; const int* item_j;
   // chunks: landmark ranges accumulated on chip (chunk_accum_kernel); per observation the slot of its pose in its chunk
   // (255: landmark handled through the item list); per pair the partial blocks the chunks produced
-  int num_chunks; const unsigned char* obs_slot; const int* chunk_begin; const int* chunk_nslots;
+  int num_chunks; const unsigned char* obs_slot; const int* chunk_begin; const int* chunk_end; const int* chunk_nslots;
   const long long* chunk_part_off; const long long* chunk_cpart_off;
   const int* pp_ptr; const long long* pp_off; const long long* pp_coff;
   // generic-factor contributions: per f-block (gradient / column norms) and per 3x3 destination of S
@@ -435,7 +435,7 @@ __global__ void __launch_bounds__(256, 2) chunk_accum_kernel(DeviceProblem P, co
   const int c = blockIdx.x, tid = threadIdx.x;
   const int ns = P.chunk_nslots[c], npair = ns * (ns + 1) / 2;
   const int groups = max(1, 256 / npair);
-  const int l_begin = P.chunk_begin[c], l_end = P.chunk_begin[c + 1];
+  const int l_begin = P.chunk_begin[c], l_end = P.chunk_end[c];
   if (tid < npair) {   // q -> (A <= B), row-major over the upper triangle
     int q = tid, A = 0;
     while (q >= ns - A) { q -= ns - A; ++A; }
@@ -550,7 +550,7 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
   if (!gate_run(st)) return;
   const int c = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
   const int ns = P.chunk_nslots[c], nrow = 6 * ns + 1, nt = (nrow + 7) >> 3, T = nt * (nt + 1) / 2, nrow8 = nt * 8;
-  const int l_begin = P.chunk_begin[c], l_end = P.chunk_begin[c + 1];
+  const int l_begin = P.chunk_begin[c], l_end = P.chunk_end[c];
   for (int t = tid; t < T; t += 256) { int q = t, I = 0; while (q >= nt - I) { q -= nt - I; ++I; } tI[t] = (unsigned char)I; tJ[t] = (unsigned char)(I + q); }
   const int t0 = warp * T / 8, t1 = (warp + 1) * T / 8, ngrp = (t1 - t0 + 3) >> 2;
   // accumulators of this warp's tiles, 4 tiles at a time in registers; the rest waits in (L1-resident) local memory
