@@ -272,11 +272,22 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     LAUNCH_SMEM(h, chol_small_kernel, 1, kSmallThreads, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
     return;
   }
-  for (int j0 = 0; j0 < n; j0 += kNB) {
-    const int nb = std::min(kNB, n - j0), rest = n - j0 - nb;
-    LAUNCH(h, chol_diag_kernel, 1, 256, Sd, n, j0, h->d_invd.as<double>(), st);
-    if (rest > 0) LAUNCH(h, chol_trsm_kernel, BlocksFor(rest, 256), 256, Sd, n, j0, h->d_invd.as<double>(), st);
-    if (rest > 0) { const int T = (rest + 63) / 64; LAUNCH(h, chol_update_kernel, dim3(T, T), 128, Sd, n, j0, st); }
+  // two-level right-looking blocking: outer panels of 128 columns are factored with 32-column steps whose tensor-core
+  // updates stay inside the panel; the rest of the matrix is then updated once with the whole 128-column panel
+  constexpr int kOuter = 128;
+  auto update = [&](int kbase, int kw, int cbase, int cend) {
+    const int Tc = (cend - cbase + 63) / 64, Tr = (n - cbase + 63) / 64;
+    if (Tc > 0 && Tr > 0) LAUNCH(h, chol_update_kernel, dim3(Tc, Tr), 128, Sd, n, kbase, kw, cbase, cend, st);
+  };
+  for (int J0 = 0; J0 < n; J0 += kOuter) {
+    const int W = std::min(kOuter, n - J0);
+    for (int jj = 0; jj < W; jj += kNB) {
+      const int j0 = J0 + jj, nb = std::min(kNB, n - j0), rest = n - j0 - nb;
+      LAUNCH(h, chol_diag_kernel, 1, 256, Sd, n, j0, h->d_invd.as<double>(), st);
+      if (rest > 0) LAUNCH(h, chol_trsm_kernel, BlocksFor(rest, 256), 256, Sd, n, j0, h->d_invd.as<double>(), st);
+      if (jj + kNB < W) update(j0, nb, j0 + kNB, J0 + W);
+    }
+    if (J0 + W < n) update(J0, W, J0 + W, n);
   }
   LAUNCH(h, chol_solve_kernel, 1, 1024, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
 }

@@ -882,21 +882,19 @@ __global__ void __launch_bounds__(256) chol_trsm_kernel(double* __restrict__ S, 
     } else xv[c] = 0.0;
   }
 }
-__global__ void __launch_bounds__(128) chol_update_kernel(double* __restrict__ S, int n, int j0, const LMState* st) {
+// Trailing update C -= L_panel L_panel^T with the FP64 tensor cores: columns [cbase, cend), rows >= column, where the
+// panel is L[:, kbase : kbase + kw] (kw a multiple of 4, <= 128). 64x64 tiles of C, the K dimension is walked in chunks of
+// 32 staged in shared memory (leading dimension padded to 36: conflict-free DMMA fragment loads). With kw = 128 (outer
+// panels of the two-level blocking) the update does 4x the flops per byte of S moved.
+__global__ void __launch_bounds__(128) chol_update_kernel(double* __restrict__ S, int n, int kbase, int kw, int cbase, int cend,
+                                                          const LMState* st) {
   if (!gate_run(st) || st->lin_fail) return;
-  const int base = j0 + kNB;            // first trailing row / column
   const int ti = blockIdx.y, tj = blockIdx.x;
   if (ti < tj) return;
   constexpr int LD = kNB + 4;
   __shared__ double As[64 * LD];
   __shared__ double Bs[64 * LD];
-  const int i0 = base + ti * 64, c0 = base + tj * 64, tid = threadIdx.x;
-  for (int e = tid; e < 64 * kNB; e += 128) {
-    const int r = e % 64, p = e / 64;
-    As[r * LD + p] = (i0 + r < n) ? S[(size_t)(j0 + p) * n + i0 + r] : 0.0;
-    Bs[r * LD + p] = (c0 + r < n) ? S[(size_t)(j0 + p) * n + c0 + r] : 0.0;
-  }
-  __syncthreads();
+  const int i0 = cbase + ti * 64, c0 = cbase + tj * 64, tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31, gr = lane >> 2, gc = lane & 3;
   // warp w owns row band [16w, 16w+16) x all 64 columns = 2 x 8 subtiles of 8x8
   double acc[2][8][2];
@@ -904,17 +902,28 @@ __global__ void __launch_bounds__(128) chol_update_kernel(double* __restrict__ S
   for (int a = 0; a < 2; ++a)
 #pragma unroll
     for (int b = 0; b < 8; ++b) { acc[a][b][0] = 0.0; acc[a][b][1] = 0.0; }
+  for (int kc = 0; kc < kw; kc += kNB) {
+    const int kn = min(kNB, kw - kc);
+    for (int e = tid; e < 64 * kNB; e += 128) {
+      const int r = e % 64, p = e / 64;
+      const bool kp = p < kn;
+      As[r * LD + p] = (kp && i0 + r < n) ? S[(size_t)(kbase + kc + p) * n + i0 + r] : 0.0;
+      Bs[r * LD + p] = (kp && c0 + r < n) ? S[(size_t)(kbase + kc + p) * n + c0 + r] : 0.0;
+    }
+    __syncthreads();
 #pragma unroll
-  for (int k0 = 0; k0 < kNB; k0 += 4) {
-    double af[2], bf[8];
+    for (int k0 = 0; k0 < kNB; k0 += 4) {
+      double af[2], bf[8];
 #pragma unroll
-    for (int a = 0; a < 2; ++a) af[a] = As[(16 * warp + 8 * a + gr) * LD + k0 + gc];
+      for (int a = 0; a < 2; ++a) af[a] = As[(16 * warp + 8 * a + gr) * LD + k0 + gc];
 #pragma unroll
-    for (int b = 0; b < 8; ++b) bf[b] = Bs[(8 * b + gr) * LD + k0 + gc];
+      for (int b = 0; b < 8; ++b) bf[b] = Bs[(8 * b + gr) * LD + k0 + gc];
 #pragma unroll
-    for (int a = 0; a < 2; ++a)
+      for (int a = 0; a < 2; ++a)
 #pragma unroll
-      for (int b = 0; b < 8; ++b) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+        for (int b = 0; b < 8; ++b) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+    }
+    __syncthreads();
   }
 #pragma unroll
   for (int a = 0; a < 2; ++a)
@@ -923,7 +932,7 @@ __global__ void __launch_bounds__(128) chol_update_kernel(double* __restrict__ S
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         const int row = i0 + 16 * warp + 8 * a + gr, col = c0 + 8 * b + 2 * gc + h;
-        if (row < n && col < n && row >= col) S[(size_t)col * n + row] -= acc[a][b][h];
+        if (row < n && col < cend && row >= col) S[(size_t)col * n + row] -= acc[a][b][h];
       }
 }
 // Tiny reduced systems (n <= 160: the 10-keyframe VIO window): the whole matrix lives in shared memory for the
