@@ -17,6 +17,7 @@ constexpr int kGfMaxBlocks = 10, kGfMaxRes = 15, kGfMaxAmbient = 32;
 constexpr int kChunkSlots = 22;        // poses per chunk: 22*23/2 = 253 pair blocks <= 256 threads
 constexpr int kChunkMinObs = 100000;   // below this many observations per shard the item-list path is used instead
 constexpr int kChunkMaxObs = 4096;     // observations per chunk (load balance vs. partial-block traffic)
+constexpr int kChunkMaxLm = 4096;      // landmarks per chunk (bounds the stage table of chunk_syrk_kernel)
 constexpr int kChunkSlack = 2;          // a chunk closes when its pose set exceeds (longest track in it) + slack: keeps most pairs present
 constexpr int kChunkStageDoubles = 11008;   // staging buffer (86 KiB): two CTAs per SM
 constexpr int kChunkSmemBytes = kChunkStageDoubles * 8;
@@ -62,6 +63,9 @@ struct DeviceProblem {
   int num_chunks; const unsigned char* obs_slot; const int* chunk_begin; const int* chunk_end; const int* chunk_nslots;
   const long long* chunk_part_off; const long long* chunk_cpart_off;
   const int* pp_ptr; const long long* pp_off; const long long* pp_coff;
+  // tile format of the tensor-core chunk kernel: raw 8x8 tiles of sum W W^T per chunk; per partial-list entry the
+  // chunk's tile offset and (slot A | slot B << 8 | slots << 16)
+  int tile_mode; const long long* chunk_tile_off; const long long* pp_toff; const int* pp_info;
   // generic-factor contributions: per f-block (gradient / column norms) and per 3x3 destination of S
   const int* fg_ptr; const int* fg_fac; const int* fg_lb;            // CSR over f-blocks (nf)
   int num_gdest; const int* gd_row; const int* gd_col; const int* gd_ptr; const int* gd_fac; const int* gd_bi; const int* gd_bj;
@@ -541,93 +545,131 @@ __global__ void __launch_bounds__(256, 2) chunk_accum_kernel(DeviceProblem P, co
 // contiguous range of the upper-triangular 8x8 tiles and issues mma.sync.m8n8k4.f64 (DMMA) on them.
 // Deterministic: fixed tile ownership, fixed k order. Same outputs as chunk_accum_kernel.
 // ===================================================================================================
-constexpr int kSyrkKB = 96, kSyrkLD = 100, kSyrkMaxRows = 136, kSyrkMaxTiles = 20;
-constexpr int kSyrkSmemBytes = kSyrkMaxRows * kSyrkLD * 8;
+constexpr int kSyrkStageLm = 16;                 // landmarks per stage
+constexpr int kSyrkKB = 3 * kSyrkStageLm;        // 48 columns of W per stage = 12 k-steps
+constexpr int kSyrkLD = 52;                      // row pitch in doubles: 52 mod 16 = 4 keeps the 64-bit fragment loads conflict-free
+constexpr int kSyrkMaxTiles = 20;                // tiles per warp at 22 slots: ceil(153 / 8)
+constexpr int kSyrkMaxStages = kChunkMaxLm / kSyrkStageLm + 2;
+constexpr int kSyrkLanesPerRec = 9, kSyrkRecPerPass = 28, kSyrkInFlight = 8;   // 9 lanes x double2 = V (18 doubles); 28 records per pass of 252 threads
+__host__ __device__ inline int syrk_smem_bytes(int nslots) { return 2 * (((6 * nslots + 1 + 7) >> 3) * 8) * kSyrkLD * 8; }
+
+// U consecutive tiles of one warp over the k-steps of a stage. Consecutive tiles in row-major upper-triangular order mostly
+// share their row block, so the A fragment is reloaded only when the row block changes.
+template <int U>
+__device__ __forceinline__ void syrk_group(const double* __restrict__ Wb, const unsigned char* tI, const unsigned char* tJ, int tb,
+                                           int frag, int ksteps, double (*accs)[2], int ab) {
+  int oa[U], ob[U]; bool same[U]; double acc[U][2];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int I = tI[tb + u], J = tJ[tb + u];
+    oa[u] = 8 * I * kSyrkLD + frag; ob[u] = 8 * J * kSyrkLD + frag;
+    same[u] = u > 0 && I == (int)tI[tb + u - 1];
+    acc[u][0] = accs[ab + u][0]; acc[u][1] = accs[ab + u][1];
+  }
+#pragma unroll 4
+  for (int ks = 0; ks < ksteps; ++ks) {
+    double av = 0.0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!same[u]) av = Wb[oa[u] + 4 * ks];
+      dmma_m8n8k4(acc[u][0], acc[u][1], av, Wb[ob[u] + 4 * ks]);
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < U; ++u) { accs[ab + u][0] = acc[u][0]; accs[ab + u][1] = acc[u][1]; }
+}
+
 __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, const double* __restrict__ Vrec, const double* __restrict__ lm_z,
-                                                            double* __restrict__ part, double* __restrict__ cpart, const LMState* st) {
-  extern __shared__ __align__(16) double W[];    // W[row * kSyrkLD + k]
+                                                            double* __restrict__ part, const LMState* st) {
+  extern __shared__ __align__(16) double Wsm[];    // two stage buffers W[row * kSyrkLD + k]
   __shared__ unsigned char tI[160], tJ[160];
+  __shared__ int sO[kSyrkMaxStages];               // first observation of every stage of this chunk
   if (!gate_run(st)) return;
   const int c = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
   const int ns = P.chunk_nslots[c], nrow = 6 * ns + 1, nt = (nrow + 7) >> 3, T = nt * (nt + 1) / 2, nrow8 = nt * 8;
   const int l_begin = P.chunk_begin[c], l_end = P.chunk_end[c];
+  const int nst = (l_end - l_begin + kSyrkStageLm - 1) / kSyrkStageLm;
+  double* const buf0 = Wsm; double* const buf1 = Wsm + nrow8 * kSyrkLD;
   for (int t = tid; t < T; t += 256) { int q = t, I = 0; while (q >= nt - I) { q -= nt - I; ++I; } tI[t] = (unsigned char)I; tJ[t] = (unsigned char)(I + q); }
-  const int t0 = warp * T / 8, t1 = (warp + 1) * T / 8, ngrp = (t1 - t0 + 3) >> 2;
-  // accumulators of this warp's tiles, 4 tiles at a time in registers; the rest waits in (L1-resident) local memory
+  for (int s = tid; s <= nst; s += 256) sO[s] = P.lm_ptr[min(l_begin + s * kSyrkStageLm, l_end)];
+  const int t0 = warp * T / 8, t1 = (warp + 1) * T / 8, nw = t1 - t0;
+  const int ngrp = (nw + 3) >> 2, gsz = ngrp ? nw / ngrp : 0, grem = ngrp ? nw % ngrp : 0;   // groups of gsz + 1 (the first grem) or gsz tiles
+  const int frag = g * kSyrkLD + tg;
+  // accumulators of this warp's tiles; a group at a time in registers, the rest waits in (L1-resident) local memory
   double accs[kSyrkMaxTiles][2];
 #pragma unroll
   for (int i = 0; i < kSyrkMaxTiles; ++i) { accs[i][0] = 0.0; accs[i][1] = 0.0; }
-  for (int l0 = l_begin; l0 < l_end; l0 += 32) {
-    const int l1 = min(l_end, l0 + 32);
-    const int o0 = P.lm_ptr[l0], o1 = P.lm_ptr[l1];
-    for (int e = tid; e < nrow8 * (kSyrkKB / 2); e += 256) {   // clear the live part of W (double2 stores)
+  // staging: 9 lanes per V record (6x3 row-major, one double2 each), 8 records in flight per lane, loaded one stage
+  // ahead into registers and written to the other buffer after the tensor work of the current stage
+  const int sub = tid % kSyrkLanesPerRec, oo = tid / kSyrkLanesPerRec;
+  const int e0 = 2 * sub, e1 = 2 * sub + 1;   // element e of the record = V[e / 3][e % 3]
+  const int off0 = (e0 / 3) * kSyrkLD + e0 % 3, off1 = (e1 / 3) * kSyrkLD + e1 % 3;
+  double2 v[kSyrkInFlight]; int meta[kSyrkInFlight]; double zreg = 0.0;
+  auto prefetch = [&](int s) {
+    const int la = l_begin + s * kSyrkStageLm, o0 = sO[s], o1 = sO[s + 1];
+#pragma unroll
+    for (int u = 0; u < kSyrkInFlight; ++u) {
+      const int o = o0 + oo + kSyrkRecPerPass * u;
+      const bool ok = o < o1 && tid < kSyrkLanesPerRec * kSyrkRecPerPass;
+      meta[u] = ok ? ((int)P.obs_slot[o] | ((P.obs_lm[o] - la) << 8)) : 255;
+      v[u] = ok ? reinterpret_cast<const double2*>(Vrec + (size_t)o * kVRec)[sub] : make_double2(0.0, 0.0);
+    }
+    zreg = tid < 3 * (min(l_end, la + kSyrkStageLm) - la) ? lm_z[3 * (size_t)la + tid] : 0.0;
+  };
+  auto clear = [&](double* Wb) {
+    for (int e = tid; e < nrow8 * (kSyrkKB / 2); e += 256) {
       const int r = e / (kSyrkKB / 2), k2 = e - r * (kSyrkKB / 2);
-      reinterpret_cast<double2*>(W + r * kSyrkLD)[k2] = make_double2(0.0, 0.0);
+      reinterpret_cast<double2*>(Wb + r * kSyrkLD)[k2] = make_double2(0.0, 0.0);
     }
-    __syncthreads();
-    if (tid < 252) {   // 12 lanes per V record, the first 9 carry V (6x3 row-major), 4 records in flight per lane
-      const int sub = tid % 12, oo = tid / 12;
-      const int e0 = 2 * sub, e1 = 2 * sub + 1;   // element e of the record = V[e / 3][e % 3]
-      const int off0 = (e0 / 3) * kSyrkLD + e0 % 3, off1 = (e1 / 3) * kSyrkLD + e1 % 3;
-      for (int ob = o0 + oo; ob < o1; ob += 84) {
-        double2 v[4]; int sl[4], ll[4];
+  };
+  auto commit = [&](double* Wb, int s) {
+    const int la = l_begin + s * kSyrkStageLm, o0 = sO[s], o1 = sO[s + 1];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int o = ob + 21 * u;
-          const bool ok = o < o1 && sub < 9;
-          sl[u] = ok ? (int)P.obs_slot[o] : 255;
-          ll[u] = ok ? P.obs_lm[o] - l0 : 0;
-          v[u] = ok ? reinterpret_cast<const double2*>(Vrec + (size_t)o * kVRec)[sub] : make_double2(0.0, 0.0);
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          if (sl[u] == 255) continue;
-          double* base = W + 6 * sl[u] * kSyrkLD + 3 * ll[u];
-          base[off0] = v[u].x; base[off1] = v[u].y;
-        }
+    for (int u = 0; u < kSyrkInFlight; ++u) {
+      if ((meta[u] & 255) == 255) continue;   // out of range, or a wide landmark (handled through the item list)
+      double* base = Wb + 6 * (meta[u] & 255) * kSyrkLD + 3 * (meta[u] >> 8);
+      base[off0] = v[u].x; base[off1] = v[u].y;
+    }
+    if (tid < kSyrkLanesPerRec * kSyrkRecPerPass)   // stages with more records than fit in flight (long tracks)
+      for (int o = o0 + oo + kSyrkRecPerPass * kSyrkInFlight; o < o1; o += kSyrkRecPerPass) {
+        const int sl = P.obs_slot[o];
+        if (sl == 255) continue;
+        const double2 w = reinterpret_cast<const double2*>(Vrec + (size_t)o * kVRec)[sub];
+        double* base = Wb + 6 * sl * kSyrkLD + 3 * (P.obs_lm[o] - la);
+        base[off0] = w.x; base[off1] = w.y;
       }
-    }
-    for (int e = tid; e < 3 * (l1 - l0); e += 256) W[(6 * ns) * kSyrkLD + e] = lm_z[3 * (size_t)l0 + e];
+    if (tid < 3 * (min(l_end, la + kSyrkStageLm) - la)) Wb[(6 * ns) * kSyrkLD + tid] = zreg;
+  };
+  __syncthreads();
+  prefetch(0); clear(buf0);
+  __syncthreads();
+  commit(buf0, 0);
+  __syncthreads();
+  for (int s = 0; s < nst; ++s) {
+    const double* cur = (s & 1) ? buf1 : buf0; double* nxt = (s & 1) ? buf0 : buf1;
+    const bool more = s + 1 < nst;
+    if (more) { prefetch(s + 1); clear(nxt); }
     __syncthreads();
-    const int ksteps = (3 * (l1 - l0) + 3) >> 2;
+    const int nl = min(l_end, l_begin + (s + 1) * kSyrkStageLm) - (l_begin + s * kSyrkStageLm);
+    const int ksteps = (3 * nl + 3) >> 2;
+    int tb = t0, ab = 0;
     for (int gq = 0; gq < ngrp; ++gq) {
-      const double* pa[4]; const double* pb[4]; double a4[4][2];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int t = min(t0 + 4 * gq + u, t1 - 1);                 // the tail repeats the last tile; its result is dropped
-        pa[u] = W + (8 * tI[t] + g) * kSyrkLD + tg; pb[u] = W + (8 * tJ[t] + g) * kSyrkLD + tg;
-        a4[u][0] = accs[4 * gq + u][0]; a4[u][1] = accs[4 * gq + u][1];
+      const int U = gsz + (gq < grem ? 1 : 0);
+      switch (U) {
+        case 4: syrk_group<4>(cur, tI, tJ, tb, frag, ksteps, accs, ab); break;
+        case 3: syrk_group<3>(cur, tI, tJ, tb, frag, ksteps, accs, ab); break;
+        case 2: syrk_group<2>(cur, tI, tJ, tb, frag, ksteps, accs, ab); break;
+        default: syrk_group<1>(cur, tI, tJ, tb, frag, ksteps, accs, ab); break;
       }
-      for (int ks = 0; ks < ksteps; ++ks) {
-#pragma unroll
-        for (int u = 0; u < 4; ++u) dmma_m8n8k4(a4[u][0], a4[u][1], pa[u][4 * ks], pb[u][4 * ks]);
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) if (t0 + 4 * gq + u < t1) { accs[4 * gq + u][0] = a4[u][0]; accs[4 * gq + u][1] = a4[u][1]; }
+      tb += U; ab += U;
     }
+    if (more) commit(nxt, s + 1);
     __syncthreads();
   }
-  // scatter the tiles into the chunk's pair blocks: entry (r, c), slots A = r / 6 <= B = c / 6
-  double* out = part + P.chunk_part_off[c];
-  double* cout = cpart + P.chunk_cpart_off[c];
-  const int zrow = 6 * ns;
-  for (int ti = 0; ti < t1 - t0; ++ti) {
-    const int t = t0 + ti;
-    const int I = tI[t], J = tJ[t];
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int r = 8 * I + g, cc = 8 * J + 2 * tg + h;
-      const double v = accs[ti][h];
-      if (r >= zrow || cc > zrow) continue;
-      const int A = r / 6, i = r - 6 * A;
-      if (cc == zrow) { cout[A * 6 + i] = v; continue; }
-      const int B = cc / 6, j = cc - 6 * B;
-      if (A > B) continue;                         // mirrored entry of a diagonal tile
-      double* blk = out + (size_t)(A * ns - A * (A - 1) / 2 + (B - A)) * 36;
-      blk[6 * i + j] = v;
-      if (A == B && i != j) blk[6 * j + i] = v;    // the diagonal blocks are symmetric; take both halves from the upper entry
-    }
-  }
+  // raw tiles out, coalesced (a lane's two entries are adjacent); pair_reduce_kernel maps block elements to tile entries
+  double* tout = part + P.chunk_tile_off[c];
+  for (int ti = 0; ti < nw; ++ti)
+    reinterpret_cast<double2*>(tout + (size_t)(t0 + ti) * 64)[lane] = make_double2(accs[ti][0], accs[ti][1]);
 }
 
 // ===================================================================================================
@@ -731,9 +773,25 @@ __global__ void __launch_bounds__(144) pair_reduce_kernel(DeviceProblem P, const
   const int a = P.pair_a[pb], b = P.pair_b[pb];
   const int i = e / 6, j = e - 6 * i;
   double acc = 0.0, cacc = 0.0;
-  for (int it = P.pp_ptr[pb]; it < P.pp_ptr[pb + 1]; ++it) {
-    acc += part[P.pp_off[it] + e];
-    if (e < 6 && P.pp_coff[it] >= 0) cacc += cpart[P.pp_coff[it] + e];
+  if (P.tile_mode) {
+    for (int it = P.pp_ptr[pb]; it < P.pp_ptr[pb + 1]; ++it) {
+      const int info = P.pp_info[it], A = info & 255, B = (info >> 8) & 255, ns = info >> 16;
+      const int nt = (6 * ns + 8) >> 3;
+      const double* tp = part + P.pp_toff[it];
+      int r = 6 * A + i, c = 6 * B + j;
+      if (r > c) { const int t = r; r = c; c = t; }          // only on diagonal blocks (A == B): symmetric
+      int I = r >> 3, J = c >> 3;
+      acc += tp[(size_t)(I * nt - I * (I - 1) / 2 + (J - I)) * 64 + (r & 7) * 8 + (c & 7)];
+      if (e < 6 && A == B) {                                  // last column of W W^T: sum V_A z
+        r = 6 * A + e; c = 6 * ns; I = r >> 3; J = c >> 3;
+        cacc += tp[(size_t)(I * nt - I * (I - 1) / 2 + (J - I)) * 64 + (r & 7) * 8 + (c & 7)];
+      }
+    }
+  } else {
+    for (int it = P.pp_ptr[pb]; it < P.pp_ptr[pb + 1]; ++it) {
+      acc += part[P.pp_off[it] + e];
+      if (e < 6 && P.pp_coff[it] >= 0) cacc += cpart[P.pp_coff[it] + e];
+    }
   }
   for (int it = P.pair_ptr[pb]; it < P.pair_ptr[pb + 1]; ++it) {   // wide landmarks
     const int oi = P.item_i[it], oj = P.item_j[it];
