@@ -67,7 +67,7 @@ struct bsnls_handle {
   std::vector<int> pose_q_blk, pose_t_blk;
   std::vector<int> pair_a, pair_b;
   std::vector<int> gd_row, gd_col;
-  bool chunk_fma = false; int chunk_max_slots = 1; DevMem d_chunk_tile_off, d_pp_toff, d_pp_info;
+  bool chunk_fma = false; int chunk_max_slots = 1; DevMem d_syrk_plan, d_chunk_tile_off, d_pp_toff, d_pp_info;
   int nchunks = 0; DevMem d_obs_slot, d_chunk_end, d_chunk_begin, d_chunk_nslots, d_chunk_part_off, d_chunk_cpart_off, d_pp_ptr, d_pp_off, d_pp_coff, d_part, d_cpart;
   bool sparse = false, pcg = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
   // residual-block bookkeeping for bsnls_evaluate (program order)
@@ -76,6 +76,9 @@ struct bsnls_handle {
   int64_t gfJ_size = 0, gfR_size = 0;
   std::vector<int> gf_roff_h, gf_nres_h;
   int nb_obs = 0, nb_lm = 0, nb_act = 0;  // partial-sum block counts
+  int n_eval_items = 0, nb_eval = 0;      // pose-major Jacobian pass: warp items, blocks of 8 items (cost partials at x)
+  std::vector<int> obs_pm_h; DevMem d_obs_pm;
+  DevMem d_eval_items, d_eval_item_ptr, d_pm_lm_off, d_pm_cam, d_pm_pixel, d_pose_tab, d_pose_part;
 
   DeviceProblem P{};
   // device memory
@@ -177,9 +180,12 @@ void EnqueueEval(bsnls_handle* h) {  // phase A: residuals + Jacobians + cost at
   const DeviceProblem& P = h->P;
   LMState* st = h->d_state.as<LMState>();
   MARK(h, 0);
-  if (h->nobs) LAUNCH(h, eval_reproj_kernel<0>, h->nb_obs, 256, P, h->d_x.as<double>(), h->d_Jrec.as<double>(), h->d_cost_part.as<double>(), st);
+  if (h->nobs) {
+    LAUNCH(h, pose_prep_kernel, BlocksFor(h->np, 128), 128, P, h->d_x.as<double>(), h->d_pose_tab.as<double>(), st);
+    LAUNCH(h, eval_reproj_pose_kernel, h->nb_eval, 256, P, h->d_x.as<double>(), h->d_pose_tab.as<double>(), h->d_Jrec.as<double>(), h->d_cost_part.as<double>(), h->d_pose_part.as<double>(), st);
+  }
   MARK(h, 1);
-  if (h->ngf) LAUNCH(h, eval_generic_kernel<0>, BlocksFor(h->ngf, 4), 128, P, h->d_x.as<double>(), h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_cost_part.as<double>() + h->nb_obs, st);
+  if (h->ngf) LAUNCH(h, eval_generic_kernel<0>, BlocksFor(h->ngf, 4), 128, P, h->d_x.as<double>(), h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_cost_part.as<double>() + h->nb_eval, st);
   MARK(h, 2);
 }
 template <int G> void LaunchLandmark(bsnls_handle* h, const Options& o) {
@@ -198,7 +204,7 @@ __global__ void zero_f_kernel(DeviceProblem P, double* gradL, double* colsqL, co
 }
 int EnqueueGradient(bsnls_handle* h, const Options& o) {  // phase C: gradient, column norms, scale, gradient norms
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
-  if (h->np) LAUNCH(h, pose_diag_kernel, BlocksFor(h->np, 4), 128, P, h->d_Jrec.as<double>(), h->d_poseH.as<double>(), h->d_gradL.as<double>(), h->d_colsqL.as<double>(), st);
+  if (h->np) LAUNCH(h, pose_reduce_kernel, BlocksFor(h->np * 27, 128), 128, P, h->d_pose_part.as<double>(), h->d_poseH.as<double>(), h->d_gradL.as<double>(), h->d_colsqL.as<double>(), st);
   const double* gS = h->d_gradL.as<double>(); const double* cS = h->d_colsqL.as<double>();
   if (h->world > 1) {
     // pose gradient / column norms are sums over the observations of every rank. Out of place: the kernels above are
@@ -215,9 +221,9 @@ int EnqueueGradient(bsnls_handle* h, const Options& o) {  // phase C: gradient, 
   LAUNCH(h, grad_norm_kernel, h->nb_act, 256, P, h->d_x.as<double>(), h->d_grad.as<double>(), h->d_gsq_part.as<double>(), h->d_gmax_part.as<double>(), st);
   RedList L{}; L.gate = 2; L.count = 0;
   const int nbe = h->nb_act_e, nbf = h->nb_act - h->nb_act_e;
-  if (h->nobs) L.d[L.count++] = Desc(h->d_cost_part.as<double>(), h->nb_obs, 0, RED_COST, false);
-  if (h->ngf_active) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_obs, h->ngf_active, 0, RED_COST, true);
-  if (h->ngf > h->ngf_active) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_obs + h->ngf_active, h->ngf - h->ngf_active, 0, RED_FIXED, true);
+  if (h->nobs) L.d[L.count++] = Desc(h->d_cost_part.as<double>(), h->nb_eval, 0, RED_COST, false);
+  if (h->ngf_active) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_eval, h->ngf_active, 0, RED_COST, true);
+  if (h->ngf > h->ngf_active) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_eval + h->ngf_active, h->ngf - h->ngf_active, 0, RED_FIXED, true);
   if (nbe) L.d[L.count++] = Desc(h->d_gsq_part.as<double>(), nbe, 0, RED_GRAD_SQ, false);
   if (nbf) L.d[L.count++] = Desc(h->d_gsq_part.as<double>() + nbe, nbf, 0, RED_GRAD_SQ, true);
   if (nbe) L.d[L.count++] = Desc(h->d_gmax_part.as<double>(), nbe, 1, 0, false);
@@ -600,11 +606,24 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   for (int k = 0; k < nobs_local; ++k) pose_ptr[s_pose[k] + 1]++;
   for (int a = 0; a < h->np; ++a) pose_ptr[a + 1] += pose_ptr[a];
   { std::vector<int> cur(pose_ptr.begin(), pose_ptr.end() - 1); for (int k = 0; k < nobs_local; ++k) pose_obs[cur[s_pose[k]]++] = k; }
+  // pose-major evaluation items: <= kEvalSeg observations of one pose per warp, plus that order's copies of the inputs
+  std::vector<int> eval_items, eval_item_ptr(h->np + 1, 0), pm_lm_off(nobs_local), pm_cam(nobs_local);
+  std::vector<double> pm_pixel(2 * (size_t)nobs_local);
+  for (int a = 0; a < h->np; ++a) {
+    for (int b = pose_ptr[a]; b < pose_ptr[a + 1]; b += kEvalSeg) { eval_items.push_back(a); eval_items.push_back(b); eval_items.push_back(std::min(b + kEvalSeg, pose_ptr[a + 1])); eval_items.push_back(0); }
+    eval_item_ptr[a + 1] = (int)(eval_items.size() / 4);
+  }
+  for (int it = 0; it < nobs_local; ++it) {
+    const int o = pose_obs[it];
+    pm_lm_off[it] = lm_off[s_lm[o]]; pm_cam[it] = s_cam[o]; pm_pixel[2 * (size_t)it] = s_pixel[2 * (size_t)o]; pm_pixel[2 * (size_t)it + 1] = s_pixel[2 * (size_t)o + 1];
+  }
+  h->n_eval_items = (int)(eval_items.size() / 4); h->nb_eval = h->n_eval_items;
+  h->obs_pm_h.assign(nobs_local, 0); for (int it = 0; it < nobs_local; ++it) h->obs_pm_h[pose_obs[it]] = it;
   const double avg_track = ne_g ? (double)nobs / ne_g : 0.0;
   h->G = avg_track <= 5.0 ? 4 : avg_track <= 12.0 ? 8 : avg_track <= 24.0 ? 16 : 32;
 
   // ---- chunks: consecutive landmarks whose poses fit kChunkSlots slots are accumulated on chip by one CTA ----
-  std::vector<unsigned char> obs_slot(nobs_local, 255);
+  std::vector<unsigned short> obs_slot(nobs_local, 0xFFFF);
   std::vector<int> chunk_begin, chunk_end, chunk_nslots, chunk_pose;      // landmark range [begin, end) of each chunk
   std::vector<long long> chunk_part_off, chunk_cpart_off, chunk_tile_off;
   long long tile_size = 0;
@@ -612,13 +631,17 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   long long part_size = 0, cpart_size = 0;
   {
     std::vector<int> stamp(h->np, -1), cur_poses;
+    // chunk size: about 1400 chunks (~5 waves of 2 CTAs x 148 SMs) balances the tail of the last wave against the
+    // partial-tile traffic of many small chunks; BSNLS_CHUNK_OBS overrides (tuning knob)
+    int chunk_max_obs = std::min(kChunkMaxObs, std::max(512, nobs_local / 1400));
+    if (const char* ev = std::getenv("BSNLS_CHUNK_OBS")) chunk_max_obs = std::min(kChunkMaxObs, std::max(64, std::atoi(ev)));
     int c_begin = 0, c_obs = 0, c_kmax = 0;
     auto close_chunk = [&](int end) {
       if (end == c_begin) return;
       if (cur_poses.empty()) { c_begin = end; c_obs = 0; c_kmax = 0; return; }   // only wide landmarks: nothing to accumulate on chip
       std::sort(cur_poses.begin(), cur_poses.end());           // slots in increasing pose id: slot A < B  <=>  pose a < b
       for (size_t q = 0; q < cur_poses.size(); ++q) stamp[cur_poses[q]] = (int)q;
-      for (int e = c_begin; e < end; ++e) if (!wide[e]) for (int k = lm_ptr_local[e]; k < lm_ptr_local[e + 1]; ++k) obs_slot[k] = (unsigned char)stamp[s_pose[k]];
+      for (int e = c_begin; e < end; ++e) if (!wide[e]) for (int k = lm_ptr_local[e]; k < lm_ptr_local[e + 1]; ++k) obs_slot[k] = (unsigned short)(stamp[s_pose[k]] | (((e - c_begin) % kSyrkStageLm) << 8));
       chunk_begin.push_back(c_begin); chunk_end.push_back(end); chunk_nslots.push_back((int)cur_poses.size());
       for (int q = 0; q < kChunkSlots; ++q) chunk_pose.push_back(q < (int)cur_poses.size() ? cur_poses[q] : -1);
       chunk_part_off.push_back(part_size); chunk_cpart_off.push_back(cpart_size); chunk_tile_off.push_back(tile_size);
@@ -640,7 +663,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       int fresh = 0;
       for (int k = k0; k < k1; ++k) if (stamp[s_pose[k]] == -1) ++fresh;
       const int limit = std::min(kChunkSlots, std::max(c_kmax, k1 - k0) + kChunkSlack);
-      if ((int)cur_poses.size() + fresh > limit || c_obs + (k1 - k0) > kChunkMaxObs) { close_chunk(e); }
+      if ((int)cur_poses.size() + fresh > limit || c_obs + (k1 - k0) > chunk_max_obs) { close_chunk(e); }
       c_kmax = std::max(c_kmax, k1 - k0);
       for (int k = k0; k < k1; ++k) if (stamp[s_pose[k]] == -1) { stamp[s_pose[k]] = -3; cur_poses.push_back(s_pose[k]); }
       c_obs += k1 - k0;
@@ -836,6 +859,9 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_pose_t_tan, pose_t_tan, s)); CK(upload(h->d_pose_ptr, pose_ptr, s)); CK(upload(h->d_pose_obs, pose_obs, s));
   CK(upload(h->d_obs_pose, s_pose, s)); CK(upload(h->d_obs_lm, s_lm, s)); CK(upload(h->d_obs_cam, s_cam, s)); CK(upload(h->d_obs_pixel, s_pixel, s));
   CK(upload(h->d_lm_ptr, lm_ptr_local, s)); CK(upload(h->d_lm_off, lm_off, s));
+  CK(upload(h->d_obs_pm, h->obs_pm_h, s)); CK(upload(h->d_eval_items, eval_items, s)); CK(upload(h->d_eval_item_ptr, eval_item_ptr, s)); CK(upload(h->d_pm_lm_off, pm_lm_off, s));
+  CK(upload(h->d_pm_cam, pm_cam, s)); CK(upload(h->d_pm_pixel, pm_pixel, s));
+  CK(h->d_pose_tab.alloc(sizeof(double) * kPoseTab * (size_t)std::max(1, h->np))); CK(h->d_pose_part.alloc(sizeof(double) * 27 * (size_t)std::max(1, h->n_eval_items)));
   { std::vector<double> cams(pr->cameras, pr->cameras + (size_t)pr->num_cameras * BSNLS_CAMERA_STRIDE); CK(upload(h->d_cams, cams, s)); }
   CK(upload(h->d_gf_type, gf_type, s)); CK(upload(h->d_gf_nblk, gf_nblk, s)); CK(upload(h->d_gf_nres, gf_nres, s)); CK(upload(h->d_gf_blocks, gf_blocks, s));
   CK(upload(h->d_gf_coff, gf_coff, s)); CK(upload(h->d_gf_consts, gf_consts, s)); CK(upload(h->d_gf_loss_type, gf_loss_type, s));
@@ -846,6 +872,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_chunk_part_off, chunk_part_off, s)); CK(upload(h->d_chunk_cpart_off, chunk_cpart_off, s));
   CK(upload(h->d_pp_ptr, pp_ptr, s)); CK(upload(h->d_pp_off, pp_off, s)); CK(upload(h->d_pp_coff, pp_coff, s));
   h->chunk_fma = std::getenv("BSNLS_CHUNK_FMA") != nullptr;   // scalar-FMA chunk kernel (pair-block partial format), kept for comparison
+  { std::vector<int> plan((kSyrkMaxNt + 1) * 8 * kSyrkMaxStrips); syrk_build_plan(plan.data()); CK(upload(h->d_syrk_plan, plan, s)); }
   CK(upload(h->d_chunk_tile_off, chunk_tile_off, s)); CK(upload(h->d_pp_toff, pp_toff, s)); CK(upload(h->d_pp_info, pp_info, s));
   CK(h->d_part.alloc(sizeof(double) * (size_t)std::max(part_size, tile_size))); CK(h->d_cpart.alloc(sizeof(double) * (size_t)cpart_size));
   CK(upload(h->d_fg_ptr, fg_ptr, s)); CK(upload(h->d_fg_fac, fg_fac, s)); CK(upload(h->d_fg_lb, fg_lb, s));
@@ -881,7 +908,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     CK(h->d_pcg_part.alloc(sizeof(double) * 5 * (size_t)h->pcg_grid));
   } CK(h->d_poseH.alloc(sizeof(double) * 21 * (size_t)std::max(1, h->np)));
   CK(h->d_gfJ.alloc(sizeof(double) * joff)); CK(h->d_gfR.alloc(sizeof(double) * roff));
-  CK(h->d_cost_part.alloc(sizeof(double) * (h->nb_obs + h->ngf + 1))); CK(h->d_cand_part.alloc(sizeof(double) * (h->nb_obs + h->ngf + 1)));
+  CK(h->d_cost_part.alloc(sizeof(double) * (h->nb_eval + h->ngf + 1))); CK(h->d_cand_part.alloc(sizeof(double) * (h->nb_obs + h->ngf + 1)));
   CK(h->d_model_part.alloc(sizeof(double) * (h->nb_lm + h->ngf + 1)));
   CK(h->d_step_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_candsq_part.alloc(sizeof(double) * h->nb_act));
   CK(h->d_gsq_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_gmax_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_xsq_part.alloc(sizeof(double) * h->nb_act));
@@ -896,13 +923,15 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   P.num_poses = h->np; P.pose_q_off = h->d_pose_q_off.as<int>(); P.pose_t_off = h->d_pose_t_off.as<int>();
   P.pose_q_tan = h->d_pose_q_tan.as<int>(); P.pose_t_tan = h->d_pose_t_tan.as<int>(); P.pose_ptr = h->d_pose_ptr.as<int>(); P.pose_obs = h->d_pose_obs.as<int>();
   P.num_obs = h->nobs; P.obs_pose = h->d_obs_pose.as<int>(); P.obs_lm = h->d_obs_lm.as<int>(); P.obs_cam = h->d_obs_cam.as<int>(); P.obs_pixel = h->d_obs_pixel.as<double>();
+  P.num_eval_items = h->n_eval_items; P.obs_pm = h->d_obs_pm.as<int>(); P.eval_items = h->d_eval_items.as<int4>(); P.eval_item_ptr = h->d_eval_item_ptr.as<int>();
+  P.pm_lm_off = h->d_pm_lm_off.as<int>(); P.pm_cam = h->d_pm_cam.as<int>(); P.pm_pixel = h->d_pm_pixel.as<double>();
   P.lm_ptr = h->d_lm_ptr.as<int>(); P.lm_off = h->d_lm_off.as<int>(); P.cams = h->d_cams.as<CameraModel>();
   P.num_gf = h->ngf; P.gf_type = h->d_gf_type.as<int>(); P.gf_nblk = h->d_gf_nblk.as<int>(); P.gf_nres = h->d_gf_nres.as<int>(); P.gf_blocks = h->d_gf_blocks.as<int>();
   P.gf_coff = h->d_gf_coff.as<long long>(); P.gf_consts = h->d_gf_consts.as<double>(); P.gf_loss_type = h->d_gf_loss_type.as<int>(); P.gf_loss_a = h->d_gf_loss_a.as<double>();
   P.gf_joff = h->d_gf_joff.as<int>(); P.gf_roff = h->d_gf_roff.as<int>();
   P.num_pairs = h->npairs; P.pair_a = h->d_pair_a.as<int>(); P.pair_b = h->d_pair_b.as<int>(); P.pair_ptr = h->d_pair_ptr.as<int>();
   P.item_i = h->d_item_i.as<int>(); P.item_j = h->d_item_j.as<int>();
-  P.num_chunks = h->nchunks; P.obs_slot = h->d_obs_slot.as<unsigned char>(); P.chunk_begin = h->d_chunk_begin.as<int>(); P.chunk_end = h->d_chunk_end.as<int>(); P.chunk_nslots = h->d_chunk_nslots.as<int>();
+  P.num_chunks = h->nchunks; P.obs_slot = h->d_obs_slot.as<unsigned short>(); P.syrk_plan = h->d_syrk_plan.as<int>(); P.chunk_begin = h->d_chunk_begin.as<int>(); P.chunk_end = h->d_chunk_end.as<int>(); P.chunk_nslots = h->d_chunk_nslots.as<int>();
   P.chunk_part_off = h->d_chunk_part_off.as<long long>(); P.chunk_cpart_off = h->d_chunk_cpart_off.as<long long>();
   P.pp_ptr = h->d_pp_ptr.as<int>(); P.pp_off = h->d_pp_off.as<long long>(); P.pp_coff = h->d_pp_coff.as<long long>();
   P.tile_mode = h->chunk_fma ? 0 : 1; P.chunk_tile_off = h->d_chunk_tile_off.as<long long>(); P.pp_toff = h->d_pp_toff.as<long long>(); P.pp_info = h->d_pp_info.as<int>();
@@ -1062,8 +1091,8 @@ int bsnls_run_eval(bsnls_handle* h, double* cost) {
   CK(cudaEventRecord(h->ev1, h->stream));
   h->profiling = false;
   RedList L{}; L.gate = 0; L.count = 0;
-  if (h->nobs) L.d[L.count++] = Desc(h->d_cost_part.as<double>(), h->nb_obs, 0, RED_COST, false);
-  if (h->ngf) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_obs, h->ngf, 0, RED_COST, true);
+  if (h->nobs) L.d[L.count++] = Desc(h->d_cost_part.as<double>(), h->nb_eval, 0, RED_COST, false);
+  if (h->ngf) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_eval, h->ngf, 0, RED_COST, true);
   LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), h->d_state.as<LMState>());
   if ((rc = AllReduceScalars(h)) != BSNLS_OK) return rc;
   double red[kRedSize];
@@ -1155,8 +1184,8 @@ int bsnls_evaluate(bsnls_handle* h, double* cost, double* residuals, int64_t* nu
   if (rc != BSNLS_OK) return rc;
   // include factors whose blocks are all constant in the cost (Problem::Evaluate evaluates every residual block)
   RedList L{}; L.gate = 0; L.count = 0;
-  if (h->nobs) L.d[L.count++] = Desc(h->d_cost_part.as<double>(), h->nb_obs, 0, RED_COST, false);
-  if (h->ngf) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_obs, h->ngf, 0, RED_COST, true);
+  if (h->nobs) L.d[L.count++] = Desc(h->d_cost_part.as<double>(), h->nb_eval, 0, RED_COST, false);
+  if (h->ngf) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_eval, h->ngf, 0, RED_COST, true);
   LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), st);
   double red[kRedSize];
   CK(cudaMemcpyAsync(red, h->d_red.p, sizeof(red), cudaMemcpyDeviceToHost, h->stream));
@@ -1172,7 +1201,7 @@ int bsnls_evaluate(bsnls_handle* h, double* cost, double* residuals, int64_t* nu
   if (residuals) {
     const std::vector<int>& gf_roff = h->gf_roff_h;
     for (const auto& r : h->res_order) {
-      if (r.type == BSNLS_FACTOR_REPROJECTION) { residuals[r.row] = jrec[(size_t)r.idx * kJRec + 6]; residuals[r.row + 1] = jrec[(size_t)r.idx * kJRec + 7]; }
+      if (r.type == BSNLS_FACTOR_REPROJECTION) { residuals[r.row] = jrec[(size_t)h->obs_pm_h[r.idx] * kJRec + 6]; residuals[r.row + 1] = jrec[(size_t)h->obs_pm_h[r.idx] * kJRec + 7]; }
       else for (int k = 0; k < kNumRes[r.type]; ++k) residuals[r.row + k] = gfr[gf_roff[r.idx] + k];
     }
   }

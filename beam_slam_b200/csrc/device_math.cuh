@@ -195,6 +195,144 @@ __device__ __forceinline__ double reprojection_evaluate(const CameraModel& cam, 
   r[0] *= rs; r[1] *= rs;
   return 0.5 * rho[0];
 }
+// ---------------------------------------------------------------------------------------------------
+// Pose table. Everything in the reprojection Jacobian that depends on the pose alone is computed once per pose and
+// pass instead of once per observation: the rotation of the raw quaternion (residual, t and P blocks) and the five
+// rotations of point_transformation (normalised q and q + 1e-8 e_i, the forward difference of
+// euclidean_reprojection_function.h:15-24, 77-90), each with R^T t. Same operations in the same order as
+// reprojection_evaluate, so the results are bit-identical; only the redundancy across observations is gone.
+// Layout: 6 sets x (R[9] row-major, R^T t [3]).
+// ---------------------------------------------------------------------------------------------------
+constexpr int kPoseTab = 72;
+__device__ __forceinline__ void pose_table_set(const double* R, const double* t, double* out) {
+#pragma unroll
+  for (int k = 0; k < 9; ++k) out[k] = R[k];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) out[9 + i] = xdot3(R[i], t[0], R[3 + i], t[1], R[6 + i], t[2]);
+}
+__device__ __forceinline__ void pose_table_build(const double* q, const double* t, double* tab) {
+  double R[9];
+  quat_to_rot_exact(q[0], q[1], q[2], q[3], R);
+  pose_table_set(R, t, tab);
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    double qp[4] = {q[0], q[1], q[2], q[3]};
+    if (k > 0) qp[k - 1] = xadd(q[k - 1], 1e-8);
+    const double n2 = xadd(xadd(xmul(qp[1], qp[1]), xmul(qp[3], qp[3])), xadd(xmul(qp[2], qp[2]), xmul(qp[0], qp[0])));
+    double w = qp[0], x = qp[1], y = qp[2], z = qp[3];
+    if (n2 > 0.0) { const double n = __dsqrt_rn(n2); w = __ddiv_rn(w, n); x = __ddiv_rn(x, n); y = __ddiv_rn(y, n); z = __ddiv_rn(z, n); }
+    quat_to_rot_exact(w, x, y, z, R);
+    pose_table_set(R, t, tab + 12 * (k + 1));
+  }
+}
+// x / 1e-8 correctly rounded (== __ddiv_rn(x, 1e-8)) without the general division sequence: RN(1 / 1e-8) = 1e8 exactly,
+// two Markstein corrections with exact FMA residuals. |x| here is a difference of O(1..100) coordinates: no underflow.
+__device__ __forceinline__ double fd_quotient(double x) {
+  const double c = 1e-8, rc = 1e8;
+  const double q0 = __dmul_rn(x, rc), r0 = __fma_rn(-c, q0, x), q1 = __fma_rn(r0, rc, q0), r1 = __fma_rn(-c, q1, x);
+  return __fma_rn(r1, rc, q1);
+}
+// reprojection_evaluate with the pose-only parts read from the pose table (T = the pose's 72 doubles).
+__device__ __forceinline__ double reprojection_evaluate_tab(const CameraModel& cam, const double* pixel, const double* q,
+                                                            const double* __restrict__ T, const double* P,
+                                                            double* r, double* Jq, double* Jt, double* JP) {
+  double R[9], Pc[3], Pb[3];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) R[k] = T[k];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) Pb[i] = xsub(xdot3(R[i], P[0], R[3 + i], P[1], R[6 + i], P[2]), T[9 + i]);
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+    Pc[i] = xadd(xdot3(cam.T[4 * i], Pb[0], cam.T[4 * i + 1], Pb[1], cam.T[4 * i + 2], Pb[2]), cam.T[4 * i + 3]);
+  {
+    const double k0 = xdot3(cam.fx, Pc[0], 0.0, Pc[1], cam.cx, Pc[2]);
+    const double k1 = xdot3(0.0, Pc[0], cam.fy, Pc[1], cam.cy, Pc[2]);
+    const double k2 = xdot3(0.0, Pc[0], 0.0, Pc[1], 1.0, Pc[2]);
+    const double u = __ddiv_rn(k0, k2), v = __ddiv_rn(k1, k2);
+    const double e0 = xsub(pixel[0], u), e1 = xsub(pixel[1], v);
+    r[0] = xadd(xmul(cam.w, e0), xmul(0.0, e1));
+    r[1] = xadd(xmul(0.0, e0), xmul(cam.w, e1));
+  }
+  const double z = Pc[2], z2 = z * z;
+  const double dE[6] = {cam.fx / z, 0.0, -cam.fx * Pc[0] / z2, 0.0, cam.fy / z, -cam.fy * Pc[1] / z2};
+  double A[6];  // d_E_d_P_CAMERA * R_cb
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      A[3 * i + j] = xdot3(dE[3 * i], cam.T[j], dE[3 * i + 1], cam.T[4 + j], dE[3 * i + 2], cam.T[8 + j]);
+  double res0[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) res0[k] = xsub(xdot3(T[12 + k], P[0], T[15 + k], P[1], T[18 + k], P[2]), T[21 + k]);
+  double D[12];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const double* Tp = T + 24 + 12 * i;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const double rp = xsub(xdot3(Tp[k], P[0], Tp[3 + k], P[1], Tp[6 + k], P[2]), Tp[9 + k]);
+      D[4 * k + i] = fd_quotient(xsub(rp, res0[k]));
+    }
+  }
+  double J4[8];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      J4[4 * i + j] = xdot3(A[3 * i], D[j], A[3 * i + 1], D[4 + j], A[3 * i + 2], D[8 + j]);
+  const double mw = -cam.w;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const double a = J4[j], b = J4[4 + j];
+    J4[j] = xadd(xmul(mw, a), xmul(-0.0, b)); J4[4 + j] = xadd(xmul(-0.0, a), xmul(mw, b));
+  }
+  double Pj[12]; quat_plus_jacobian(q, Pj);
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      double acc = 0.0;
+#pragma unroll
+      for (int a = 0; a < 4; ++a) acc += J4[4 * i + a] * Pj[3 * a + k];
+      Jq[3 * i + k] = acc;
+    }
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const double jt = xdot3(A[3 * i], -R[3 * j], A[3 * i + 1], -R[3 * j + 1], A[3 * i + 2], -R[3 * j + 2]);
+      const double jp = xdot3(A[3 * i], R[3 * j], A[3 * i + 1], R[3 * j + 1], A[3 * i + 2], R[3 * j + 2]);
+      Jt[3 * i + j] = jt; JP[3 * i + j] = jp;
+    }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    double a = Jt[j], b = Jt[3 + j];
+    Jt[j] = xadd(xmul(mw, a), xmul(-0.0, b)); Jt[3 + j] = xadd(xmul(-0.0, a), xmul(mw, b));
+    a = JP[j]; b = JP[3 + j];
+    JP[j] = xadd(xmul(mw, a), xmul(-0.0, b)); JP[3 + j] = xadd(xmul(-0.0, a), xmul(mw, b));
+  }
+  const double s = r[0] * r[0] + r[1] * r[1];
+  const int lt = static_cast<int>(cam.loss_type);
+  if (lt == 0) return 0.5 * s;
+  double rho[3]; loss_evaluate(lt, cam.loss_a, s, rho);
+  double sr, rs, asn; corrector(s, rho, &sr, &rs, &asn);
+  if (asn == 0.0) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) { Jq[k] *= sr; Jt[k] *= sr; JP[k] *= sr; }
+  } else {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      double rtj = Jq[c] * r[0] + Jq[3 + c] * r[1];
+      Jq[c] = sr * (Jq[c] - asn * r[0] * rtj); Jq[3 + c] = sr * (Jq[3 + c] - asn * r[1] * rtj);
+      rtj = Jt[c] * r[0] + Jt[3 + c] * r[1];
+      Jt[c] = sr * (Jt[c] - asn * r[0] * rtj); Jt[3 + c] = sr * (Jt[3 + c] - asn * r[1] * rtj);
+      rtj = JP[c] * r[0] + JP[3 + c] * r[1];
+      JP[c] = sr * (JP[c] - asn * r[0] * rtj); JP[3 + c] = sr * (JP[3 + c] - asn * r[1] * rtj);
+    }
+  }
+  r[0] *= rs; r[1] *= rs;
+  return 0.5 * rho[0];
+}
 __device__ __forceinline__ double reprojection_cost_only(const CameraModel& cam, const double* pixel,
                                                          const double* q, const double* t, const double* P) {
   double R[9], Pc[3], r[2];

@@ -60,7 +60,9 @@ struct DeviceProblem {
   int num_pairs; const int* pair_a; const int* pair_b; const int* pair_ptr; const int* item_i; const int* item_j;
   // chunks: landmark ranges accumulated on chip (chunk_accum_kernel); per observation the slot of its pose in its chunk
   // (255: landmark handled through the item list); per pair the partial blocks the chunks produced
-  int num_chunks; const unsigned char* obs_slot; const int* chunk_begin; const int* chunk_end; const int* chunk_nslots;
+    // pose-major evaluation: items (pose, begin, end, 0) over the pose-sorted observation list and that list's inputs
+  int num_eval_items; const int* obs_pm /* position of a (landmark-major) observation in the pose-major list = its Jacobian record */; const int4* eval_items; const int* eval_item_ptr; const int* pm_lm_off; const int* pm_cam; const double* pm_pixel;
+  int num_chunks; const unsigned short* obs_slot /* slot | (landmark - chunk begin) % 16 << 8; slot 255 = not in a chunk */; const int* syrk_plan; const int* chunk_begin; const int* chunk_end; const int* chunk_nslots;
   const long long* chunk_part_off; const long long* chunk_cpart_off;
   const int* pp_ptr; const long long* pp_off; const long long* pp_coff;
   // tile format of the tensor-core chunk kernel: raw 8x8 tiles of sum W W^T per chunk; per partial-list entry the
@@ -142,6 +144,116 @@ __global__ void __launch_bounds__(256) eval_reproj_kernel(DeviceProblem P, const
   }
   const double tot = block_sum<256>(cost, sm);
   if (threadIdx.x == 0) cost_part[blockIdx.x] = tot;
+}
+
+// ===================================================================================================
+// K1 (pose-major): the Jacobian pass. Observations are walked in pose order: a warp takes up to kEvalSeg observations of
+// ONE pose (host-built items), so everything that depends on the pose alone comes from the pose table (pose_prep_kernel)
+// and the pose's diagonal data  H_a = sum F^T F (21 unique), g_a = sum F^T r  is reduced in the same pass with warp
+// shuffles instead of re-reading the Jacobian records. Per-item partials are summed per pose by pose_reduce_kernel in item
+// order: deterministic, no atomics. Jacobian records are written at their landmark-major position as before.
+// ===================================================================================================
+constexpr int kEvalSeg = 256;
+__global__ void __launch_bounds__(128) pose_prep_kernel(DeviceProblem P, const double* __restrict__ x, double* __restrict__ tab, const LMState* st) {
+  if (!gate_jac(st)) return;
+  const int a = blockIdx.x * 128 + threadIdx.x;
+  if (a >= P.num_poses) return;
+  const int qo = P.pose_q_off[a], to = P.pose_t_off[a];
+  const double q[4] = {x[qo], x[qo + 1], x[qo + 2], x[qo + 3]};
+  const double t[3] = {x[to], x[to + 1], x[to + 2]};
+  double T[kPoseTab]; pose_table_build(q, t, T);
+  double2* out = reinterpret_cast<double2*>(tab + (size_t)a * kPoseTab);
+#pragma unroll
+  for (int k = 0; k < kPoseTab / 2; ++k) out[k] = make_double2(T[2 * k], T[2 * k + 1]);
+}
+// Sum of v[k] over the 32 lanes for all k at once; lane k returns total k. Each butterfly stage halves the number of
+// values a lane carries (31 exchanges instead of 32 x 5). Fixed order: deterministic.
+__device__ __forceinline__ double warp_transpose_sum32(double (&v)[32], int lane) {
+#pragma unroll
+  for (int m = 16; m >= 1; m >>= 1) {
+    const bool up = (lane & m) != 0;
+#pragma unroll
+    for (int i = 0; i < m; ++i) {
+      const double send = up ? v[i] : v[i + m], keep = up ? v[i + m] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
+    }
+  }
+  return v[0];
+}
+// One CTA per item = up to 256 consecutive observations of one pose in the pose-major list; one observation per thread.
+// Jacobian records are written at the pose-major position (contiguous per CTA); consumers go through obs_pm.
+__global__ void __launch_bounds__(256) eval_reproj_pose_kernel(DeviceProblem P, const double* __restrict__ x, const double* __restrict__ tab,
+                                                               double* __restrict__ Jrec, double* __restrict__ cost_part,
+                                                               double* __restrict__ pose_part, const LMState* st) {
+  if (!gate_jac(st)) return;
+  __shared__ double sm[8][33];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int4 iv = P.eval_items[blockIdx.x];   // pose, begin, end in the pose-major list
+  const int a = iv.x, it = iv.y + threadIdx.x;
+  double cost = 0.0;
+  double v[32];
+#pragma unroll
+  for (int k = 0; k < 32; ++k) v[k] = 0.0;
+  if (it < iv.z) {
+    const int qo = P.pose_q_off[a];
+    const double q[4] = {x[qo], x[qo + 1], x[qo + 2], x[qo + 3]};
+    const double* T = tab + (size_t)a * kPoseTab;
+    const int po = P.pm_lm_off[it];
+    const CameraModel cam = P.cams[P.pm_cam[it]];
+    const double2 px = reinterpret_cast<const double2*>(P.pm_pixel)[it];
+    const double pixel[2] = {px.x, px.y};
+    const double Pw[3] = {x[po], x[po + 1], x[po + 2]};
+    double r[2], Jq[6], Jt[6], JP[6];
+    cost = reprojection_evaluate_tab(cam, pixel, q, T, Pw, r, Jq, Jt, JP);
+    if (P.pose_q_tan[a] < 0) { for (int k = 0; k < 6; ++k) Jq[k] = 0.0; }
+    if (P.pose_t_tan[a] < 0) { for (int k = 0; k < 6; ++k) Jt[k] = 0.0; }
+    double2* out = reinterpret_cast<double2*>(Jrec + (size_t)it * kJRec);
+    out[0] = make_double2(JP[0], JP[1]); out[1] = make_double2(JP[2], JP[3]); out[2] = make_double2(JP[4], JP[5]);
+    out[3] = make_double2(r[0], r[1]);
+    // F row-major 2x6: [Jq row0 | Jt row0 ; Jq row1 | Jt row1]
+    out[4] = make_double2(Jq[0], Jq[1]); out[5] = make_double2(Jq[2], Jt[0]); out[6] = make_double2(Jt[1], Jt[2]);
+    out[7] = make_double2(Jq[3], Jq[4]); out[8] = make_double2(Jq[5], Jt[3]); out[9] = make_double2(Jt[4], Jt[5]);
+    const double F0[6] = {Jq[0], Jq[1], Jq[2], Jt[0], Jt[1], Jt[2]}, F1[6] = {Jq[3], Jq[4], Jq[5], Jt[3], Jt[4], Jt[5]};
+    int k = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+      for (int j = i; j < 6; ++j) v[k++] = F0[i] * F0[j] + F1[i] * F1[j];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) v[21 + i] = F0[i] * r[0] + F1[i] * r[1];
+    v[27] = cost;
+  }
+  sm[warp][lane] = warp_transpose_sum32(v, lane);   // entry `lane` of this warp: 0..26 pose data, 27 cost
+  __syncthreads();
+  if (threadIdx.x < 28) {
+    double tot = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) tot += sm[w][threadIdx.x];
+    if (threadIdx.x < 27) pose_part[(size_t)blockIdx.x * 27 + threadIdx.x] = tot; else cost_part[blockIdx.x] = tot;
+  }
+}
+// One thread per (pose, entry): sums the pose's item partials in item order; writes pose_H and the rank-local gradient /
+// column-norm entries of the pose's q and t blocks (index = tangent - ne_dim).
+__global__ void __launch_bounds__(128) pose_reduce_kernel(DeviceProblem P, const double* __restrict__ pose_part, double* __restrict__ pose_H,
+                                                          double* __restrict__ grad, double* __restrict__ colsq, const LMState* st) {
+  if (!gate_jac(st)) return;
+  const int tid = blockIdx.x * 128 + threadIdx.x;
+  const int a = tid / 27, k = tid - a * 27;
+  if (a >= P.num_poses) return;
+  double sum = 0.0;
+  for (int it = P.eval_item_ptr[a]; it < P.eval_item_ptr[a + 1]; ++it) sum += pose_part[(size_t)it * 27 + k];
+  const int tq = P.pose_q_tan[a], tt = P.pose_t_tan[a];
+  if (k < 21) {
+    pose_H[(size_t)a * 21 + k] = sum;
+    // diagonal entries of the 21-packed upper triangle: index of (i,i) = i*6 - i(i-1)/2 = 0, 6, 11, 15, 18, 20
+    const int i = k == 0 ? 0 : k == 6 ? 1 : k == 11 ? 2 : k == 15 ? 3 : k == 18 ? 4 : k == 20 ? 5 : -1;
+    if (i >= 0 && i < 3 && tq >= 0) colsq[tq - P.ne_dim + i] = sum;
+    if (i >= 3 && tt >= 0) colsq[tt - P.ne_dim + i - 3] = sum;
+  } else {
+    const int i = k - 21;
+    if (i < 3 && tq >= 0) grad[tq - P.ne_dim + i] = sum;
+    if (i >= 3 && tt >= 0) grad[tt - P.ne_dim + i - 3] = sum;
+  }
 }
 
 // ===================================================================================================
@@ -245,7 +357,7 @@ __global__ void __launch_bounds__(256) landmark_kernel(DeviceProblem P, const do
   const int start = valid ? P.lm_ptr[l] : 0, end = valid ? P.lm_ptr[l + 1] : 0;
   double a00 = 0, a01 = 0, a02 = 0, a11 = 0, a12 = 0, a22 = 0, g0 = 0, g1 = 0, g2 = 0;
   for (int o = start + sub; o < end; o += G) {
-    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)o * kJRec);
+    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec);
     const double2 e0 = rec[0], e1 = rec[1], e2 = rec[2], r = rec[3];
     // E row0 = (e0.x, e0.y, e1.x), row1 = (e1.y, e2.x, e2.y)
     a00 += e0.x * e0.x + e1.y * e1.y; a01 += e0.x * e0.y + e1.y * e2.x; a02 += e0.x * e1.x + e1.y * e2.y;
@@ -293,7 +405,7 @@ __global__ void __launch_bounds__(256) landmark_kernel(DeviceProblem P, const do
   }
   // pass 2: V = (F^T E) C with C = Linv^T (upper):  V[:,0] = W0 i00; V[:,1] = W0 i10 + W1 i11; V[:,2] = W0 i20 + W1 i21 + W2 i22
   for (int o = start + sub; o < end; o += G) {
-    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)o * kJRec);
+    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec);
     const double2 e0 = rec[0], e1 = rec[1], e2 = rec[2];
     const double E0[3] = {e0.x, e0.y, e1.x}, E1[3] = {e1.y, e2.x, e2.y};
     double F0[6], F1[6];
@@ -311,53 +423,6 @@ __global__ void __launch_bounds__(256) landmark_kernel(DeviceProblem P, const do
     }
 #pragma unroll
     for (int k = 0; k < 12; ++k) out[k] = make_double2(v[2 * k], v[2 * k + 1]);
-  }
-}
-
-// ===================================================================================================
-// K6a: per-pose diagonal data independent of the damping: H_a = sum F^T F (6x6, 21 unique), g_a = sum F^T r.
-// One warp per pose, lanes stride over the pose's observations, butterfly reduction.
-// Writes grad / colsq entries of the pose's q and t blocks and pose_H (21 per pose).
-// ===================================================================================================
-__global__ void __launch_bounds__(128) pose_diag_kernel(DeviceProblem P, const double* __restrict__ Jrec,
-                                                        double* __restrict__ pose_H, double* __restrict__ grad,
-                                                        double* __restrict__ colsq, const LMState* st) {
-  if (!gate_jac(st)) return;
-  const int a = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (a >= P.num_poses) return;
-  double acc[27];
-#pragma unroll
-  for (int k = 0; k < 27; ++k) acc[k] = 0.0;
-  for (int it = P.pose_ptr[a] + lane; it < P.pose_ptr[a + 1]; it += 32) {
-    const int o = P.pose_obs[it];
-    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)o * kJRec);
-    const double2 r = rec[3];
-    double F0[6], F1[6];
-    { const double2 f0 = rec[4], f1 = rec[5], f2 = rec[6], f3 = rec[7], f4 = rec[8], f5 = rec[9];
-      F0[0] = f0.x; F0[1] = f0.y; F0[2] = f1.x; F0[3] = f1.y; F0[4] = f2.x; F0[5] = f2.y;
-      F1[0] = f3.x; F1[1] = f3.y; F1[2] = f4.x; F1[3] = f4.y; F1[4] = f5.x; F1[5] = f5.y; }
-    int k = 0;
-#pragma unroll
-    for (int i = 0; i < 6; ++i)
-#pragma unroll
-      for (int j = i; j < 6; ++j) acc[k++] += F0[i] * F0[j] + F1[i] * F1[j];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) acc[21 + i] += F0[i] * r.x + F1[i] * r.y;
-  }
-#pragma unroll
-  for (int m = 1; m < 32; m <<= 1)
-#pragma unroll
-    for (int k = 0; k < 27; ++k) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], m);
-  if (lane == 0) {
-    double* H = pose_H + (size_t)a * 21;
-#pragma unroll
-    for (int k = 0; k < 21; ++k) H[k] = acc[k];
-    const int tq = P.pose_q_tan[a], tt = P.pose_t_tan[a];
-    // diagonal entries of the 21-packed upper triangle: index of (i,i) = i*6 - i(i-1)/2
-    const int dg[6] = {0, 6, 11, 15, 18, 20};
-    // grad / colsq here are the rank-local partial buffers over the f-blocks (index = tangent - ne_dim)
-    if (tq >= 0) for (int k = 0; k < 3; ++k) { grad[tq - P.ne_dim + k] = acc[21 + k]; colsq[tq - P.ne_dim + k] = acc[dg[k]]; }
-    if (tt >= 0) for (int k = 0; k < 3; ++k) { grad[tt - P.ne_dim + k] = acc[24 + k]; colsq[tt - P.ne_dim + k] = acc[dg[3 + k]]; }
   }
 }
 
@@ -471,7 +536,7 @@ __global__ void __launch_bounds__(256, 2) chunk_accum_kernel(DeviceProblem P, co
         for (int u = 0; u < 4; ++u) {
           const int o = ob + 21 * u;
           const bool ok = o < o1;
-          sl[u] = ok ? (int)P.obs_slot[o] : 255;
+          sl[u] = ok ? (int)(P.obs_slot[o] & 255) : 255;
           ll[u] = ok ? P.obs_lm[o] - l0 : 0;
           v[u] = ok ? reinterpret_cast<const double2*>(Vrec + (size_t)o * kVRec)[sub] : make_double2(0.0, 0.0);
         }
@@ -548,31 +613,63 @@ __global__ void __launch_bounds__(256, 2) chunk_accum_kernel(DeviceProblem P, co
 constexpr int kSyrkStageLm = 16;                 // landmarks per stage
 constexpr int kSyrkKB = 3 * kSyrkStageLm;        // 48 columns of W per stage = 12 k-steps
 constexpr int kSyrkLD = 52;                      // row pitch in doubles: 52 mod 16 = 4 keeps the 64-bit fragment loads conflict-free
-constexpr int kSyrkMaxTiles = 20;                // tiles per warp at 22 slots: ceil(153 / 8)
+constexpr int kSyrkMaxTiles = 22;                // tiles per warp at 22 slots: ceil(153 / 8) + imbalance of the strip plan
 constexpr int kSyrkMaxStages = kChunkMaxLm / kSyrkStageLm + 2;
 constexpr int kSyrkLanesPerRec = 9, kSyrkRecPerPass = 28, kSyrkInFlight = 8;   // 9 lanes x double2 = V (18 doubles); 28 records per pass of 252 threads
 __host__ __device__ inline int syrk_smem_bytes(int nslots) { return 2 * (((6 * nslots + 1 + 7) >> 3) * 8) * kSyrkLD * 8; }
 
-// U consecutive tiles of one warp over the k-steps of a stage. Consecutive tiles in row-major upper-triangular order mostly
-// share their row block, so the A fragment is reloaded only when the row block changes.
-template <int U>
-__device__ __forceinline__ void syrk_group(const double* __restrict__ Wb, const unsigned char* tI, const unsigned char* tJ, int tb,
-                                           int frag, int ksteps, double (*accs)[2], int ab) {
-  int oa[U], ob[U]; bool same[U]; double acc[U][2];
-#pragma unroll
-  for (int u = 0; u < U; ++u) {
-    const int I = tI[tb + u], J = tJ[tb + u];
-    oa[u] = 8 * I * kSyrkLD + frag; ob[u] = 8 * J * kSyrkLD + frag;
-    same[u] = u > 0 && I == (int)tI[tb + u - 1];
-    acc[u][0] = accs[ab + u][0]; acc[u][1] = accs[ab + u][1];
+// Work plan: the upper-triangular tiles of row block I are cut into strips of up to 4 consecutive tiles (I, J0 .. J0+U-1),
+// so that the A fragment is loaded once per strip and k-step; strips are dealt to the 8 warps longest-first onto the
+// least loaded warp. One table for every tile count nt, built on the host (syrk_build_plan) and read from global memory.
+constexpr int kSyrkMaxNt = (6 * kChunkSlots + 1 + 7) / 8, kSyrkMaxStrips = 12;
+inline void syrk_build_plan(int* plan /* [(kSyrkMaxNt + 1) * 8 * kSyrkMaxStrips], entry = I | J0 << 8 | U << 16, 0 ends a list */) {
+  for (int i = 0; i < (kSyrkMaxNt + 1) * 8 * kSyrkMaxStrips; ++i) plan[i] = 0;
+  for (int nt = 1; nt <= kSyrkMaxNt; ++nt) {
+    int strips[256], nstrips = 0;
+    for (int I = 0; I < nt; ++I) {
+      const int n = nt - I, k = (n + 3) / 4;
+      for (int q = 0, J = I; q < k; ++q) { const int U = n / k + (q < n % k ? 1 : 0); strips[nstrips++] = I | (J << 8) | (U << 16); J += U; }
+    }
+    int load[8] = {0, 0, 0, 0, 0, 0, 0, 0}, cnt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int* pl = plan + nt * 8 * kSyrkMaxStrips;
+    for (int U = 4; U >= 1; --U)
+      for (int q = 0; q < nstrips; ++q) if ((strips[q] >> 16) == U) {
+        int w = 0; for (int x = 1; x < 8; ++x) if (load[x] < load[w]) w = x;
+        pl[w * kSyrkMaxStrips + cnt[w]++] = strips[q]; load[w] += U;
+      }
+    // level the remaining imbalance: peel single tiles off the busiest warp's strips
+    for (int round = 0; round < 64; ++round) {
+      int hi = 0, lo = 0;
+      for (int x = 1; x < 8; ++x) { if (load[x] > load[hi]) hi = x; if (load[x] < load[lo]) lo = x; }
+      if (load[hi] - load[lo] < 2 || cnt[lo] >= kSyrkMaxStrips) break;
+      int q = -1; for (int x = 0; x < cnt[hi]; ++x) if ((pl[hi * kSyrkMaxStrips + x] >> 16) >= 2) q = x;
+      if (q < 0) break;
+      int& sp = pl[hi * kSyrkMaxStrips + q];
+      const int I = sp & 255, J0 = (sp >> 8) & 255, U = sp >> 16;
+      sp = I | (J0 << 8) | ((U - 1) << 16);
+      pl[lo * kSyrkMaxStrips + cnt[lo]++] = I | ((J0 + U - 1) << 8) | (1 << 16);
+      --load[hi]; ++load[lo];
+    }
   }
-#pragma unroll 4
-  for (int ks = 0; ks < ksteps; ++ks) {
-    double av = 0.0;
+}
+
+template <int U, bool FULL>
+__device__ __forceinline__ void syrk_strip(const double* __restrict__ pa, const double* __restrict__ pb, int ksteps, double (*accs)[2], int ab) {
+  double acc[U][2];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      if (!same[u]) av = Wb[oa[u] + 4 * ks];
-      dmma_m8n8k4(acc[u][0], acc[u][1], av, Wb[ob[u] + 4 * ks]);
+  for (int u = 0; u < U; ++u) { acc[u][0] = accs[ab + u][0]; acc[u][1] = accs[ab + u][1]; }
+  if (FULL) {
+#pragma unroll
+    for (int ks = 0; ks < kSyrkKB / 4; ++ks) {
+      const double av = pa[4 * ks];
+#pragma unroll
+      for (int u = 0; u < U; ++u) dmma_m8n8k4(acc[u][0], acc[u][1], av, pb[u * 8 * kSyrkLD + 4 * ks]);
+    }
+  } else {
+    for (int ks = 0; ks < ksteps; ++ks) {
+      const double av = pa[4 * ks];
+#pragma unroll
+      for (int u = 0; u < U; ++u) dmma_m8n8k4(acc[u][0], acc[u][1], av, pb[u * 8 * kSyrkLD + 4 * ks]);
     }
   }
 #pragma unroll
@@ -582,7 +679,7 @@ __device__ __forceinline__ void syrk_group(const double* __restrict__ Wb, const 
 __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, const double* __restrict__ Vrec, const double* __restrict__ lm_z,
                                                             double* __restrict__ part, const LMState* st) {
   extern __shared__ __align__(16) double Wsm[];    // two stage buffers W[row * kSyrkLD + k]
-  __shared__ unsigned char tI[160], tJ[160];
+  __shared__ int sPlan[8 * kSyrkMaxStrips];
   __shared__ int sO[kSyrkMaxStages];               // first observation of every stage of this chunk
   if (!gate_run(st)) return;
   const int c = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
@@ -590,10 +687,8 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
   const int l_begin = P.chunk_begin[c], l_end = P.chunk_end[c];
   const int nst = (l_end - l_begin + kSyrkStageLm - 1) / kSyrkStageLm;
   double* const buf0 = Wsm; double* const buf1 = Wsm + nrow8 * kSyrkLD;
-  for (int t = tid; t < T; t += 256) { int q = t, I = 0; while (q >= nt - I) { q -= nt - I; ++I; } tI[t] = (unsigned char)I; tJ[t] = (unsigned char)(I + q); }
+  if (tid < 8 * kSyrkMaxStrips) sPlan[tid] = P.syrk_plan[nt * 8 * kSyrkMaxStrips + tid];
   for (int s = tid; s <= nst; s += 256) sO[s] = P.lm_ptr[min(l_begin + s * kSyrkStageLm, l_end)];
-  const int t0 = warp * T / 8, t1 = (warp + 1) * T / 8, nw = t1 - t0;
-  const int ngrp = (nw + 3) >> 2, gsz = ngrp ? nw / ngrp : 0, grem = ngrp ? nw % ngrp : 0;   // groups of gsz + 1 (the first grem) or gsz tiles
   const int frag = g * kSyrkLD + tg;
   // accumulators of this warp's tiles; a group at a time in registers, the rest waits in (L1-resident) local memory
   double accs[kSyrkMaxTiles][2];
@@ -611,7 +706,7 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
     for (int u = 0; u < kSyrkInFlight; ++u) {
       const int o = o0 + oo + kSyrkRecPerPass * u;
       const bool ok = o < o1 && tid < kSyrkLanesPerRec * kSyrkRecPerPass;
-      meta[u] = ok ? ((int)P.obs_slot[o] | ((P.obs_lm[o] - la) << 8)) : 255;
+      meta[u] = ok ? (int)P.obs_slot[o] : 255;
       v[u] = ok ? reinterpret_cast<const double2*>(Vrec + (size_t)o * kVRec)[sub] : make_double2(0.0, 0.0);
     }
     zreg = tid < 3 * (min(l_end, la + kSyrkStageLm) - la) ? lm_z[3 * (size_t)la + tid] : 0.0;
@@ -632,10 +727,10 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
     }
     if (tid < kSyrkLanesPerRec * kSyrkRecPerPass)   // stages with more records than fit in flight (long tracks)
       for (int o = o0 + oo + kSyrkRecPerPass * kSyrkInFlight; o < o1; o += kSyrkRecPerPass) {
-        const int sl = P.obs_slot[o];
-        if (sl == 255) continue;
+        const int m = P.obs_slot[o];
+        if ((m & 255) == 255) continue;
         const double2 w = reinterpret_cast<const double2*>(Vrec + (size_t)o * kVRec)[sub];
-        double* base = Wb + 6 * sl * kSyrkLD + 3 * (P.obs_lm[o] - la);
+        double* base = Wb + 6 * (m & 255) * kSyrkLD + 3 * (m >> 8);
         base[off0] = w.x; base[off1] = w.y;
       }
     if (tid < 3 * (min(l_end, la + kSyrkStageLm) - la)) Wb[(6 * ns) * kSyrkLD + tid] = zreg;
@@ -652,24 +747,41 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
     __syncthreads();
     const int nl = min(l_end, l_begin + (s + 1) * kSyrkStageLm) - (l_begin + s * kSyrkStageLm);
     const int ksteps = (3 * nl + 3) >> 2;
-    int tb = t0, ab = 0;
-    for (int gq = 0; gq < ngrp; ++gq) {
-      const int U = gsz + (gq < grem ? 1 : 0);
-      switch (U) {
-        case 4: syrk_group<4>(cur, tI, tJ, tb, frag, ksteps, accs, ab); break;
-        case 3: syrk_group<3>(cur, tI, tJ, tb, frag, ksteps, accs, ab); break;
-        case 2: syrk_group<2>(cur, tI, tJ, tb, frag, ksteps, accs, ab); break;
-        default: syrk_group<1>(cur, tI, tJ, tb, frag, ksteps, accs, ab); break;
+    int ab = 0;
+    for (int q = 0; q < kSyrkMaxStrips; ++q) {
+      const int sp = sPlan[warp * kSyrkMaxStrips + q], U = sp >> 16;
+      if (U == 0) break;
+      const double* pa = cur + 8 * (sp & 255) * kSyrkLD + frag; const double* pb = cur + 8 * ((sp >> 8) & 255) * kSyrkLD + frag;
+      if (ksteps == kSyrkKB / 4) {
+        switch (U) {
+          case 4: syrk_strip<4, true>(pa, pb, ksteps, accs, ab); break;
+          case 3: syrk_strip<3, true>(pa, pb, ksteps, accs, ab); break;
+          case 2: syrk_strip<2, true>(pa, pb, ksteps, accs, ab); break;
+          default: syrk_strip<1, true>(pa, pb, ksteps, accs, ab); break;
+        }
+      } else {
+        switch (U) {
+          case 4: syrk_strip<4, false>(pa, pb, ksteps, accs, ab); break;
+          case 3: syrk_strip<3, false>(pa, pb, ksteps, accs, ab); break;
+          case 2: syrk_strip<2, false>(pa, pb, ksteps, accs, ab); break;
+          default: syrk_strip<1, false>(pa, pb, ksteps, accs, ab); break;
+        }
       }
-      tb += U; ab += U;
+      ab += U;
     }
     if (more) commit(nxt, s + 1);
     __syncthreads();
   }
   // raw tiles out, coalesced (a lane's two entries are adjacent); pair_reduce_kernel maps block elements to tile entries
   double* tout = part + P.chunk_tile_off[c];
-  for (int ti = 0; ti < nw; ++ti)
-    reinterpret_cast<double2*>(tout + (size_t)(t0 + ti) * 64)[lane] = make_double2(accs[ti][0], accs[ti][1]);
+  int ab = 0;
+  for (int q = 0; q < kSyrkMaxStrips; ++q) {
+    const int sp = sPlan[warp * kSyrkMaxStrips + q], U = sp >> 16, I = sp & 255, J0 = (sp >> 8) & 255;
+    if (U == 0) break;
+    const int t = I * nt - I * (I - 1) / 2 + (J0 - I);
+    for (int u = 0; u < U; ++u, ++ab)
+      reinterpret_cast<double2*>(tout + (size_t)(t + u) * 64)[lane] = make_double2(accs[ab][0], accs[ab][1]);
+  }
 }
 
 // ===================================================================================================
@@ -1339,7 +1451,7 @@ __global__ void __launch_bounds__(256) backsub_kernel(DeviceProblem P, const dou
   const int start = valid ? P.lm_ptr[l] : 0, end = valid ? P.lm_ptr[l + 1] : 0;
   double t0 = 0, t1 = 0, t2 = 0;
   for (int o = start + sub; o < end; o += G) {
-    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)o * kJRec);
+    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec);
     const int pose = P.obs_pose[o];
     const int tq = P.pose_q_tan[pose], tt = P.pose_t_tan[pose];
     double yp[6];
@@ -1363,7 +1475,7 @@ __global__ void __launch_bounds__(256) backsub_kernel(DeviceProblem P, const dou
   }
   double mc = 0.0;
   for (int o = start + sub; o < end; o += G) {
-    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)o * kJRec);
+    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec);
     const int pose = P.obs_pose[o];
     const int tq = P.pose_q_tan[pose], tt = P.pose_t_tan[pose];
     double yp[6];
