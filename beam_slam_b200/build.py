@@ -33,7 +33,8 @@ def build_cuda(force=False, verbose=False):
     out = os.path.join(LIB, "libbsnls.so")
     deps = _deps(CSRC, (".cu", ".cuh")) + [os.path.join(HERE, "..", "include", "bsnls.h")]
     if force or _newer(out, deps):
-        cmd = [NVCC] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", out, os.path.join(CSRC, "bsnls.cu"), os.path.join(CSRC, "noalloc.cu")]
+        extra = os.environ.get("BSNLS_NVCC_EXTRA", "").split()   # A/B tuning of compile-time knobs (-DNAME=value)
+        cmd = [NVCC] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", out, os.path.join(CSRC, "bsnls.cu"), os.path.join(CSRC, "noalloc.cu")]
         subprocess.check_call(cmd)
     return out
 

@@ -317,7 +317,7 @@ int EnqueueStep(bsnls_handle* h) {  // phase D3: back-substitution, model cost, 
   LAUNCH(h, gf_model_kernel, BlocksFor(std::max(32 * h->ngf, std::min(P.nf_dim, 1 << 16)), 128), 128, P, h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_yf.as<double>(), h->d_y.as<double>(),
          h->d_model_part.as<double>() + h->nb_lm, st);
   LAUNCH(h, candidate_kernel, h->nb_act, 256, P, h->d_x.as<double>(), h->d_y.as<double>(), h->d_xc.as<double>(), h->d_step_part.as<double>(), h->d_candsq_part.as<double>(), st);
-  if (h->nobs) LAUNCH(h, eval_reproj_kernel<1>, h->nb_obs, 256, P, h->d_xc.as<double>(), nullptr, h->d_cand_part.as<double>(), st);
+  if (h->nobs) LAUNCH(h, eval_reproj_cost_kernel, h->nb_obs, 256, P, h->d_xc.as<double>(), h->d_cand_part.as<double>(), st);
   if (h->ngf) LAUNCH(h, eval_generic_kernel<1>, BlocksFor(h->ngf, 4), 128, P, h->d_xc.as<double>(), nullptr, nullptr, h->d_cand_part.as<double>() + h->nb_obs, st);
   RedList L{}; L.gate = 1; L.count = 0;
   const int nbe = h->nb_act_e, nbf = h->nb_act - h->nb_act_e;
@@ -922,7 +922,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   P.ne = h->ne; P.nf = h->nf; P.ne_dim = ne_dim; P.nf_dim = nf_dim; P.ntan = ntan;
   P.num_poses = h->np; P.pose_q_off = h->d_pose_q_off.as<int>(); P.pose_t_off = h->d_pose_t_off.as<int>();
   P.pose_q_tan = h->d_pose_q_tan.as<int>(); P.pose_t_tan = h->d_pose_t_tan.as<int>(); P.pose_ptr = h->d_pose_ptr.as<int>(); P.pose_obs = h->d_pose_obs.as<int>();
-  P.num_obs = h->nobs; P.obs_pose = h->d_obs_pose.as<int>(); P.obs_lm = h->d_obs_lm.as<int>(); P.obs_cam = h->d_obs_cam.as<int>(); P.obs_pixel = h->d_obs_pixel.as<double>();
+  P.num_cams = pr->num_cameras; P.num_obs = h->nobs; P.obs_pose = h->d_obs_pose.as<int>(); P.obs_lm = h->d_obs_lm.as<int>(); P.obs_cam = h->d_obs_cam.as<int>(); P.obs_pixel = h->d_obs_pixel.as<double>();
   P.num_eval_items = h->n_eval_items; P.obs_pm = h->d_obs_pm.as<int>(); P.eval_items = h->d_eval_items.as<int4>(); P.eval_item_ptr = h->d_eval_item_ptr.as<int>();
   P.pm_lm_off = h->d_pm_lm_off.as<int>(); P.pm_cam = h->d_pm_cam.as<int>(); P.pm_pixel = h->d_pm_pixel.as<double>();
   P.lm_ptr = h->d_lm_ptr.as<int>(); P.lm_off = h->d_lm_off.as<int>(); P.cams = h->d_cams.as<CameraModel>();

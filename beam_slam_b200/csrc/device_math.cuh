@@ -99,102 +99,15 @@ __device__ __forceinline__ void reprojection_residual(const CameraModel& cam, co
 #pragma unroll
   for (int i = 0; i < 3; ++i)
     Pc[i] = xadd(xdot3(cam.T[4 * i], Pb[0], cam.T[4 * i + 1], Pb[1], cam.T[4 * i + 2], Pb[2]), cam.T[4 * i + 3]);
-  const double k0 = xdot3(cam.fx, Pc[0], 0.0, Pc[1], cam.cx, Pc[2]);
-  const double k1 = xdot3(0.0, Pc[0], cam.fy, Pc[1], cam.cy, Pc[2]);
-  const double k2 = xdot3(0.0, Pc[0], 0.0, Pc[1], 1.0, Pc[2]);
-  const double u = __ddiv_rn(k0, k2), v = __ddiv_rn(k1, k2);
-  const double e0 = xsub(pixel[0], u), e1 = xsub(pixel[1], v);
-  r[0] = xadd(xmul(cam.w, e0), xmul(0.0, e1));
-  r[1] = xadd(xmul(0.0, e0), xmul(cam.w, e1));
+  // K = [fx 0 cx; 0 fy cy; 0 0 1] and W = w I: the reference's products with the structural zeros add +-0 and are
+  // dropped here (identical values; only the sign of an exact zero could differ)
+  const double k0 = xadd(xmul(cam.fx, Pc[0]), xmul(cam.cx, Pc[2]));
+  const double k1 = xadd(xmul(cam.fy, Pc[1]), xmul(cam.cy, Pc[2]));
+  const double u = __ddiv_rn(k0, Pc[2]), v = __ddiv_rn(k1, Pc[2]);
+  r[0] = xmul(cam.w, xsub(pixel[0], u));
+  r[1] = xmul(cam.w, xsub(pixel[1], v));
 }
 
-// Full evaluation: residual + tangent Jacobian (2x3 wrt q tangent, 2x3 wrt t, 2x3 wrt P), loss-corrected.
-// Returns the cost contribution 0.5*rho(s). Jq/Jt/JP row-major 2x3.
-__device__ __forceinline__ double reprojection_evaluate(const CameraModel& cam, const double* pixel,
-                                                        const double* q, const double* t, const double* P,
-                                                        double* r, double* Jq, double* Jt, double* JP) {
-  double R[9], Pc[3];
-  reprojection_residual(cam, pixel, q, t, P, r, R, Pc);
-  const double z = Pc[2], z2 = z * z;
-  const double dE[6] = {cam.fx / z, 0.0, -cam.fx * Pc[0] / z2, 0.0, cam.fy / z, -cam.fy * Pc[1] / z2};
-  double A[6];  // d_E_d_P_CAMERA * R_cb
-#pragma unroll
-  for (int i = 0; i < 2; ++i)
-#pragma unroll
-    for (int j = 0; j < 3; ++j)
-      A[3 * i + j] = xdot3(dE[3 * i], cam.T[j], dE[3 * i + 1], cam.T[4 + j], dE[3 * i + 2], cam.T[8 + j]);
-  // quaternion block: forward difference of point_transformation, then (A * D) and the plus-Jacobian
-  double res0[3]; point_transformation_exact(q, t, P, res0);
-  double D[12];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    double qp[4] = {q[0], q[1], q[2], q[3]};
-    qp[i] = xadd(q[i], 1e-8);
-    double rp[3]; point_transformation_exact(qp, t, P, rp);
-#pragma unroll
-    for (int k = 0; k < 3; ++k) D[4 * k + i] = __ddiv_rn(xsub(rp[k], res0[k]), 1e-8);
-  }
-  double J4[8];
-#pragma unroll
-  for (int i = 0; i < 2; ++i)
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-      J4[4 * i + j] = xdot3(A[3 * i], D[j], A[3 * i + 1], D[4 + j], A[3 * i + 2], D[8 + j]);
-  // applyOnTheLeft(-W), W = w I2
-  const double mw = -cam.w;
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const double a = J4[j], b = J4[4 + j];
-    J4[j] = xadd(xmul(mw, a), xmul(-0.0, b)); J4[4 + j] = xadd(xmul(-0.0, a), xmul(mw, b));
-  }
-  double Pj[12]; quat_plus_jacobian(q, Pj);
-#pragma unroll
-  for (int i = 0; i < 2; ++i)
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      double acc = 0.0;
-#pragma unroll
-      for (int a = 0; a < 4; ++a) acc += J4[4 * i + a] * Pj[3 * a + k];
-      Jq[3 * i + k] = acc;
-    }
-#pragma unroll
-  for (int i = 0; i < 2; ++i)
-#pragma unroll
-    for (int j = 0; j < 3; ++j) {
-      const double jt = xdot3(A[3 * i], -R[3 * j], A[3 * i + 1], -R[3 * j + 1], A[3 * i + 2], -R[3 * j + 2]);
-      const double jp = xdot3(A[3 * i], R[3 * j], A[3 * i + 1], R[3 * j + 1], A[3 * i + 2], R[3 * j + 2]);
-      Jt[3 * i + j] = jt; JP[3 * i + j] = jp;
-    }
-#pragma unroll
-  for (int j = 0; j < 3; ++j) {
-    double a = Jt[j], b = Jt[3 + j];
-    Jt[j] = xadd(xmul(mw, a), xmul(-0.0, b)); Jt[3 + j] = xadd(xmul(-0.0, a), xmul(mw, b));
-    a = JP[j]; b = JP[3 + j];
-    JP[j] = xadd(xmul(mw, a), xmul(-0.0, b)); JP[3 + j] = xadd(xmul(-0.0, a), xmul(mw, b));
-  }
-  // robust loss (ResidualBlock::Evaluate order: Jacobians corrected with the uncorrected residual, then r)
-  const double s = r[0] * r[0] + r[1] * r[1];
-  const int lt = static_cast<int>(cam.loss_type);
-  if (lt == 0) return 0.5 * s;
-  double rho[3]; loss_evaluate(lt, cam.loss_a, s, rho);
-  double sr, rs, asn; corrector(s, rho, &sr, &rs, &asn);
-  if (asn == 0.0) {
-#pragma unroll
-    for (int k = 0; k < 6; ++k) { Jq[k] *= sr; Jt[k] *= sr; JP[k] *= sr; }
-  } else {
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      double rtj = Jq[c] * r[0] + Jq[3 + c] * r[1];
-      Jq[c] = sr * (Jq[c] - asn * r[0] * rtj); Jq[3 + c] = sr * (Jq[3 + c] - asn * r[1] * rtj);
-      rtj = Jt[c] * r[0] + Jt[3 + c] * r[1];
-      Jt[c] = sr * (Jt[c] - asn * r[0] * rtj); Jt[3 + c] = sr * (Jt[3 + c] - asn * r[1] * rtj);
-      rtj = JP[c] * r[0] + JP[3 + c] * r[1];
-      JP[c] = sr * (JP[c] - asn * r[0] * rtj); JP[3 + c] = sr * (JP[3 + c] - asn * r[1] * rtj);
-    }
-  }
-  r[0] *= rs; r[1] *= rs;
-  return 0.5 * rho[0];
-}
 // ---------------------------------------------------------------------------------------------------
 // Pose table. Everything in the reprojection Jacobian that depends on the pose alone is computed once per pose and
 // pass instead of once per observation: the rotation of the raw quaternion (residual, t and P blocks) and the five
@@ -232,10 +145,13 @@ __device__ __forceinline__ double fd_quotient(double x) {
   const double q0 = __dmul_rn(x, rc), r0 = __fma_rn(-c, q0, x), q1 = __fma_rn(r0, rc, q0), r1 = __fma_rn(-c, q1, x);
   return __fma_rn(r1, rc, q1);
 }
-// reprojection_evaluate with the pose-only parts read from the pose table (T = the pose's 72 doubles).
+// Full evaluation: residual + tangent Jacobian (2x3 wrt the q tangent, 2x3 wrt P), loss-corrected, with the pose-only
+// parts read from the pose table (T = the pose's 72 doubles). Returns the cost contribution 0.5*rho(s). Jq/JP row-major
+// 2x3. The block wrt t is not computed: the reference forms it as A * (-R) against A * R for P, and negation is exact
+// through every step (products, the -W scaling, the loss correction), so Jt == -JP bit for bit.
 __device__ __forceinline__ double reprojection_evaluate_tab(const CameraModel& cam, const double* pixel, const double* q,
                                                             const double* __restrict__ T, const double* P,
-                                                            double* r, double* Jq, double* Jt, double* JP) {
+                                                            double* r, double* Jq, double* JP) {
   double R[9], Pc[3], Pb[3];
 #pragma unroll
   for (int k = 0; k < 9; ++k) R[k] = T[k];
@@ -245,22 +161,21 @@ __device__ __forceinline__ double reprojection_evaluate_tab(const CameraModel& c
   for (int i = 0; i < 3; ++i)
     Pc[i] = xadd(xdot3(cam.T[4 * i], Pb[0], cam.T[4 * i + 1], Pb[1], cam.T[4 * i + 2], Pb[2]), cam.T[4 * i + 3]);
   {
-    const double k0 = xdot3(cam.fx, Pc[0], 0.0, Pc[1], cam.cx, Pc[2]);
-    const double k1 = xdot3(0.0, Pc[0], cam.fy, Pc[1], cam.cy, Pc[2]);
-    const double k2 = xdot3(0.0, Pc[0], 0.0, Pc[1], 1.0, Pc[2]);
-    const double u = __ddiv_rn(k0, k2), v = __ddiv_rn(k1, k2);
-    const double e0 = xsub(pixel[0], u), e1 = xsub(pixel[1], v);
-    r[0] = xadd(xmul(cam.w, e0), xmul(0.0, e1));
-    r[1] = xadd(xmul(0.0, e0), xmul(cam.w, e1));
+    const double k0 = xadd(xmul(cam.fx, Pc[0]), xmul(cam.cx, Pc[2]));
+    const double k1 = xadd(xmul(cam.fy, Pc[1]), xmul(cam.cy, Pc[2]));
+    const double u = __ddiv_rn(k0, Pc[2]), v = __ddiv_rn(k1, Pc[2]);
+    r[0] = xmul(cam.w, xsub(pixel[0], u));
+    r[1] = xmul(cam.w, xsub(pixel[1], v));
   }
   const double z = Pc[2], z2 = z * z;
-  const double dE[6] = {cam.fx / z, 0.0, -cam.fx * Pc[0] / z2, 0.0, cam.fy / z, -cam.fy * Pc[1] / z2};
-  double A[6];  // d_E_d_P_CAMERA * R_cb
+  // d_E_d_P_CAMERA = [fx/z 0 -fx X/z^2; 0 fy/z -fy Y/z^2]; A = d_E_d_P_CAMERA * R_cb without the structural-zero products
+  const double d00 = cam.fx / z, d02 = -cam.fx * Pc[0] / z2, d11 = cam.fy / z, d12 = -cam.fy * Pc[1] / z2;
+  double A[6];
 #pragma unroll
-  for (int i = 0; i < 2; ++i)
-#pragma unroll
-    for (int j = 0; j < 3; ++j)
-      A[3 * i + j] = xdot3(dE[3 * i], cam.T[j], dE[3 * i + 1], cam.T[4 + j], dE[3 * i + 2], cam.T[8 + j]);
+  for (int j = 0; j < 3; ++j) {
+    A[j] = xadd(xmul(d00, cam.T[j]), xmul(d02, cam.T[8 + j]));
+    A[3 + j] = xadd(xmul(d11, cam.T[4 + j]), xmul(d12, cam.T[8 + j]));
+  }
   double res0[3];
 #pragma unroll
   for (int k = 0; k < 3; ++k) res0[k] = xsub(xdot3(T[12 + k], P[0], T[15 + k], P[1], T[18 + k], P[2]), T[21 + k]);
@@ -282,10 +197,7 @@ __device__ __forceinline__ double reprojection_evaluate_tab(const CameraModel& c
       J4[4 * i + j] = xdot3(A[3 * i], D[j], A[3 * i + 1], D[4 + j], A[3 * i + 2], D[8 + j]);
   const double mw = -cam.w;
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const double a = J4[j], b = J4[4 + j];
-    J4[j] = xadd(xmul(mw, a), xmul(-0.0, b)); J4[4 + j] = xadd(xmul(-0.0, a), xmul(mw, b));
-  }
+  for (int j = 0; j < 8; ++j) J4[j] = xmul(mw, J4[j]);   // applyOnTheLeft(-W), W = w I2
   double Pj[12]; quat_plus_jacobian(q, Pj);
 #pragma unroll
   for (int i = 0; i < 2; ++i)
@@ -299,18 +211,8 @@ __device__ __forceinline__ double reprojection_evaluate_tab(const CameraModel& c
 #pragma unroll
   for (int i = 0; i < 2; ++i)
 #pragma unroll
-    for (int j = 0; j < 3; ++j) {
-      const double jt = xdot3(A[3 * i], -R[3 * j], A[3 * i + 1], -R[3 * j + 1], A[3 * i + 2], -R[3 * j + 2]);
-      const double jp = xdot3(A[3 * i], R[3 * j], A[3 * i + 1], R[3 * j + 1], A[3 * i + 2], R[3 * j + 2]);
-      Jt[3 * i + j] = jt; JP[3 * i + j] = jp;
-    }
-#pragma unroll
-  for (int j = 0; j < 3; ++j) {
-    double a = Jt[j], b = Jt[3 + j];
-    Jt[j] = xadd(xmul(mw, a), xmul(-0.0, b)); Jt[3 + j] = xadd(xmul(-0.0, a), xmul(mw, b));
-    a = JP[j]; b = JP[3 + j];
-    JP[j] = xadd(xmul(mw, a), xmul(-0.0, b)); JP[3 + j] = xadd(xmul(-0.0, a), xmul(mw, b));
-  }
+    for (int j = 0; j < 3; ++j)
+      JP[3 * i + j] = xmul(mw, xdot3(A[3 * i], R[3 * j], A[3 * i + 1], R[3 * j + 1], A[3 * i + 2], R[3 * j + 2]));
   const double s = r[0] * r[0] + r[1] * r[1];
   const int lt = static_cast<int>(cam.loss_type);
   if (lt == 0) return 0.5 * s;
@@ -318,14 +220,12 @@ __device__ __forceinline__ double reprojection_evaluate_tab(const CameraModel& c
   double sr, rs, asn; corrector(s, rho, &sr, &rs, &asn);
   if (asn == 0.0) {
 #pragma unroll
-    for (int k = 0; k < 6; ++k) { Jq[k] *= sr; Jt[k] *= sr; JP[k] *= sr; }
+    for (int k = 0; k < 6; ++k) { Jq[k] *= sr; JP[k] *= sr; }
   } else {
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
       double rtj = Jq[c] * r[0] + Jq[3 + c] * r[1];
       Jq[c] = sr * (Jq[c] - asn * r[0] * rtj); Jq[3 + c] = sr * (Jq[3 + c] - asn * r[1] * rtj);
-      rtj = Jt[c] * r[0] + Jt[3 + c] * r[1];
-      Jt[c] = sr * (Jt[c] - asn * r[0] * rtj); Jt[3 + c] = sr * (Jt[3 + c] - asn * r[1] * rtj);
       rtj = JP[c] * r[0] + JP[3 + c] * r[1];
       JP[c] = sr * (JP[c] - asn * r[0] * rtj); JP[3 + c] = sr * (JP[3 + c] - asn * r[1] * rtj);
     }

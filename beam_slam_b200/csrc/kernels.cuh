@@ -11,7 +11,8 @@
 
 namespace bsnls {
 
-constexpr int kJRec = 20;   // per observation: E[6] (2x3 wrt landmark) | r[2] | F[12] (2x6 wrt q-tangent, t)
+constexpr int kJRec = 16;   // per observation, one 128-byte line: E[6] (2x3 wrt landmark) | r[2] | Fq[6] (2x3 wrt the q tangent) | ts | 0
+                            // the 2x3 block wrt t is ts * E with ts = -1 (0 when t is held constant): see reprojection_evaluate_tab
 constexpr int kVRec = 24;   // per observation: V[18] (6x3 = F^T E C) | c[6] (= V z)
 constexpr int kGfMaxBlocks = 10, kGfMaxRes = 15, kGfMaxAmbient = 32;
 constexpr int kChunkSlots = 22;        // poses per chunk: 22*23/2 = 253 pair blocks <= 256 threads
@@ -49,6 +50,7 @@ struct DeviceProblem {
   int num_poses; const int* pose_q_off; const int* pose_t_off; const int* pose_q_tan; const int* pose_t_tan;
   const int* pose_ptr; const int* pose_obs;   // observations of each pose (CSR), sorted observation ids
   // observations sorted by landmark (elimination order)
+  int num_cams;
   int num_obs; const int* obs_pose; const int* obs_lm; const int* obs_cam; const double* obs_pixel;
   const int* lm_ptr; const int* lm_off;       // per landmark: first observation, value offset
   const CameraModel* cams;
@@ -106,15 +108,11 @@ template <int BLOCK> __device__ __forceinline__ double block_max(double v, doubl
 }
 
 // ===================================================================================================
-// K1 + K4: reprojection residual / Jacobian / loss, one thread per observation (a warp = 32 consecutive
-// observations of the landmark-sorted list; camera and landmark blocks are re-used through L1).
-// mode 0: at x, writes Jrec + cost partials (gate: need_jacobian). mode 1: cost only at x_cand.
+// K4: candidate cost. Reprojection cost only at x_cand, one thread per observation of the landmark-sorted list.
 // ===================================================================================================
-template <int MODE>
-__global__ void __launch_bounds__(256) eval_reproj_kernel(DeviceProblem P, const double* __restrict__ x,
-                                                          double* __restrict__ Jrec, double* __restrict__ cost_part,
-                                                          const LMState* st) {
-  if (MODE == 0 ? !gate_jac(st) : !gate_run(st)) return;
+__global__ void __launch_bounds__(256) eval_reproj_cost_kernel(DeviceProblem P, const double* __restrict__ x,
+                                                               double* __restrict__ cost_part, const LMState* st) {
+  if (!gate_run(st)) return;
   __shared__ double sm[256];
   const int o = blockIdx.x * 256 + threadIdx.x;
   double cost = 0.0;
@@ -127,20 +125,7 @@ __global__ void __launch_bounds__(256) eval_reproj_kernel(DeviceProblem P, const
     const double q[4] = {x[qo], x[qo + 1], x[qo + 2], x[qo + 3]};
     const double t[3] = {x[to], x[to + 1], x[to + 2]};
     const double Pw[3] = {x[po], x[po + 1], x[po + 2]};
-    if (MODE == 0) {
-      double r[2], Jq[6], Jt[6], JP[6];
-      cost = reprojection_evaluate(cam, pixel, q, t, Pw, r, Jq, Jt, JP);
-      if (P.pose_q_tan[pose] < 0) { for (int k = 0; k < 6; ++k) Jq[k] = 0.0; }
-      if (P.pose_t_tan[pose] < 0) { for (int k = 0; k < 6; ++k) Jt[k] = 0.0; }
-      double2* out = reinterpret_cast<double2*>(Jrec + (size_t)o * kJRec);
-      out[0] = make_double2(JP[0], JP[1]); out[1] = make_double2(JP[2], JP[3]); out[2] = make_double2(JP[4], JP[5]);
-      out[3] = make_double2(r[0], r[1]);
-      // F row-major 2x6: [Jq row0 | Jt row0 ; Jq row1 | Jt row1]
-      out[4] = make_double2(Jq[0], Jq[1]); out[5] = make_double2(Jq[2], Jt[0]); out[6] = make_double2(Jt[1], Jt[2]);
-      out[7] = make_double2(Jq[3], Jq[4]); out[8] = make_double2(Jq[5], Jt[3]); out[9] = make_double2(Jt[4], Jt[5]);
-    } else {
-      cost = reprojection_cost_only(cam, pixel, q, t, Pw);
-    }
+    cost = reprojection_cost_only(cam, pixel, q, t, Pw);
   }
   const double tot = block_sum<256>(cost, sm);
   if (threadIdx.x == 0) cost_part[blockIdx.x] = tot;
@@ -153,7 +138,11 @@ __global__ void __launch_bounds__(256) eval_reproj_kernel(DeviceProblem P, const
 // shuffles instead of re-reading the Jacobian records. Per-item partials are summed per pose by pose_reduce_kernel in item
 // order: deterministic, no atomics. Jacobian records are written at their landmark-major position as before.
 // ===================================================================================================
-constexpr int kEvalSeg = 256;
+constexpr int kEvalSeg = 256, kEvalSmemCams = 8;
+static_assert(kPoseTab + kEvalSmemCams * BSNLS_CAMERA_STRIDE <= 256, "one staging pass");
+#ifndef EVAL_MINB
+#define EVAL_MINB 3
+#endif
 __global__ void __launch_bounds__(128) pose_prep_kernel(DeviceProblem P, const double* __restrict__ x, double* __restrict__ tab, const LMState* st) {
   if (!gate_jac(st)) return;
   const int a = blockIdx.x * 128 + threadIdx.x;
@@ -182,14 +171,20 @@ __device__ __forceinline__ double warp_transpose_sum32(double (&v)[32], int lane
 }
 // One CTA per item = up to 256 consecutive observations of one pose in the pose-major list; one observation per thread.
 // Jacobian records are written at the pose-major position (contiguous per CTA); consumers go through obs_pm.
-__global__ void __launch_bounds__(256) eval_reproj_pose_kernel(DeviceProblem P, const double* __restrict__ x, const double* __restrict__ tab,
+__global__ void __launch_bounds__(256, EVAL_MINB) eval_reproj_pose_kernel(DeviceProblem P, const double* __restrict__ x, const double* __restrict__ tab,
                                                                double* __restrict__ Jrec, double* __restrict__ cost_part,
                                                                double* __restrict__ pose_part, const LMState* st) {
   if (!gate_jac(st)) return;
   __shared__ double sm[8][33];
+  __shared__ __align__(16) double sT[kPoseTab];                          // the pose's table: read by every thread (broadcast)
+  __shared__ __align__(16) double sCam[kEvalSmemCams * BSNLS_CAMERA_STRIDE];   // the first few cameras (usually all of them)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int4 iv = P.eval_items[blockIdx.x];   // pose, begin, end in the pose-major list
   const int a = iv.x, it = iv.y + threadIdx.x;
+  if (threadIdx.x < kPoseTab) sT[threadIdx.x] = tab[(size_t)a * kPoseTab + threadIdx.x];
+  else if (threadIdx.x - kPoseTab < min(P.num_cams, kEvalSmemCams) * BSNLS_CAMERA_STRIDE)
+    sCam[threadIdx.x - kPoseTab] = reinterpret_cast<const double*>(P.cams)[threadIdx.x - kPoseTab];
+  __syncthreads();
   double cost = 0.0;
   double v[32];
 #pragma unroll
@@ -197,23 +192,22 @@ __global__ void __launch_bounds__(256) eval_reproj_pose_kernel(DeviceProblem P, 
   if (it < iv.z) {
     const int qo = P.pose_q_off[a];
     const double q[4] = {x[qo], x[qo + 1], x[qo + 2], x[qo + 3]};
-    const double* T = tab + (size_t)a * kPoseTab;
-    const int po = P.pm_lm_off[it];
-    const CameraModel cam = P.cams[P.pm_cam[it]];
+    const double* T = sT;
+    const int po = P.pm_lm_off[it], ci = P.pm_cam[it];
+    const CameraModel cam = ci < kEvalSmemCams ? reinterpret_cast<const CameraModel*>(sCam)[ci] : P.cams[ci];
     const double2 px = reinterpret_cast<const double2*>(P.pm_pixel)[it];
     const double pixel[2] = {px.x, px.y};
     const double Pw[3] = {x[po], x[po + 1], x[po + 2]};
-    double r[2], Jq[6], Jt[6], JP[6];
-    cost = reprojection_evaluate_tab(cam, pixel, q, T, Pw, r, Jq, Jt, JP);
+    double r[2], Jq[6], JP[6];
+    cost = reprojection_evaluate_tab(cam, pixel, q, T, Pw, r, Jq, JP);
     if (P.pose_q_tan[a] < 0) { for (int k = 0; k < 6; ++k) Jq[k] = 0.0; }
-    if (P.pose_t_tan[a] < 0) { for (int k = 0; k < 6; ++k) Jt[k] = 0.0; }
+    const double ts = P.pose_t_tan[a] < 0 ? 0.0 : -1.0;   // d r / d t = ts * d r / d P
     double2* out = reinterpret_cast<double2*>(Jrec + (size_t)it * kJRec);
     out[0] = make_double2(JP[0], JP[1]); out[1] = make_double2(JP[2], JP[3]); out[2] = make_double2(JP[4], JP[5]);
     out[3] = make_double2(r[0], r[1]);
-    // F row-major 2x6: [Jq row0 | Jt row0 ; Jq row1 | Jt row1]
-    out[4] = make_double2(Jq[0], Jq[1]); out[5] = make_double2(Jq[2], Jt[0]); out[6] = make_double2(Jt[1], Jt[2]);
-    out[7] = make_double2(Jq[3], Jq[4]); out[8] = make_double2(Jq[5], Jt[3]); out[9] = make_double2(Jt[4], Jt[5]);
-    const double F0[6] = {Jq[0], Jq[1], Jq[2], Jt[0], Jt[1], Jt[2]}, F1[6] = {Jq[3], Jq[4], Jq[5], Jt[3], Jt[4], Jt[5]};
+    out[4] = make_double2(Jq[0], Jq[1]); out[5] = make_double2(Jq[2], Jq[3]); out[6] = make_double2(Jq[4], Jq[5]);
+    out[7] = make_double2(ts, 0.0);
+    const double F0[6] = {Jq[0], Jq[1], Jq[2], ts * JP[0], ts * JP[1], ts * JP[2]}, F1[6] = {Jq[3], Jq[4], Jq[5], ts * JP[3], ts * JP[4], ts * JP[5]};
     int k = 0;
 #pragma unroll
     for (int i = 0; i < 6; ++i)
@@ -409,9 +403,9 @@ __global__ void __launch_bounds__(256) landmark_kernel(DeviceProblem P, const do
     const double2 e0 = rec[0], e1 = rec[1], e2 = rec[2];
     const double E0[3] = {e0.x, e0.y, e1.x}, E1[3] = {e1.y, e2.x, e2.y};
     double F0[6], F1[6];
-    { const double2 f0 = rec[4], f1 = rec[5], f2 = rec[6], f3 = rec[7], f4 = rec[8], f5 = rec[9];
-      F0[0] = f0.x; F0[1] = f0.y; F0[2] = f1.x; F0[3] = f1.y; F0[4] = f2.x; F0[5] = f2.y;
-      F1[0] = f3.x; F1[1] = f3.y; F1[2] = f4.x; F1[3] = f4.y; F1[4] = f5.x; F1[5] = f5.y; }
+    { const double2 f0 = rec[4], f1 = rec[5], f2 = rec[6]; const double ts = rec[7].x;
+      F0[0] = f0.x; F0[1] = f0.y; F0[2] = f1.x; F0[3] = ts * E0[0]; F0[4] = ts * E0[1]; F0[5] = ts * E0[2];
+      F1[0] = f1.y; F1[1] = f2.x; F1[2] = f2.y; F1[3] = ts * E1[0]; F1[4] = ts * E1[1]; F1[5] = ts * E1[2]; }
     double2* out = reinterpret_cast<double2*>(Vrec + (size_t)o * kVRec);
     double v[24];
 #pragma unroll
@@ -1456,10 +1450,10 @@ __global__ void __launch_bounds__(256) backsub_kernel(DeviceProblem P, const dou
     const int tq = P.pose_q_tan[pose], tt = P.pose_t_tan[pose];
     double yp[6];
     for (int k = 0; k < 3; ++k) { yp[k] = tq >= 0 ? yf[tq - P.ne_dim + k] : 0.0; yp[3 + k] = tt >= 0 ? yf[tt - P.ne_dim + k] : 0.0; }
-    const double2 f0 = rec[4], f1 = rec[5], f2 = rec[6], f3 = rec[7], f4 = rec[8], f5 = rec[9];
-    const double u0 = f0.x * yp[0] + f0.y * yp[1] + f1.x * yp[2] + f1.y * yp[3] + f2.x * yp[4] + f2.y * yp[5];
-    const double u1 = f3.x * yp[0] + f3.y * yp[1] + f4.x * yp[2] + f4.y * yp[3] + f5.x * yp[4] + f5.y * yp[5];
+    const double2 f0 = rec[4], f1 = rec[5], f2 = rec[6]; const double ts = rec[7].x;
     const double2 e0 = rec[0], e1 = rec[1], e2 = rec[2];
+    const double u0 = f0.x * yp[0] + f0.y * yp[1] + f1.x * yp[2] + ts * (e0.x * yp[3] + e0.y * yp[4] + e1.x * yp[5]);
+    const double u1 = f1.y * yp[0] + f2.x * yp[1] + f2.y * yp[2] + ts * (e1.y * yp[3] + e2.x * yp[4] + e2.y * yp[5]);
     t0 += e0.x * u0 + e1.y * u1; t1 += e0.y * u0 + e2.x * u1; t2 += e1.x * u0 + e2.y * u1;
   }
 #pragma unroll
@@ -1480,10 +1474,10 @@ __global__ void __launch_bounds__(256) backsub_kernel(DeviceProblem P, const dou
     const int tq = P.pose_q_tan[pose], tt = P.pose_t_tan[pose];
     double yp[6];
     for (int k = 0; k < 3; ++k) { yp[k] = tq >= 0 ? yf[tq - P.ne_dim + k] : 0.0; yp[3 + k] = tt >= 0 ? yf[tt - P.ne_dim + k] : 0.0; }
-    const double2 f0 = rec[4], f1 = rec[5], f2 = rec[6], f3 = rec[7], f4 = rec[8], f5 = rec[9];
+    const double2 f0 = rec[4], f1 = rec[5], f2 = rec[6]; const double ts = rec[7].x;
     const double2 e0 = rec[0], e1 = rec[1], e2 = rec[2], r = rec[3];
-    const double m0 = f0.x * yp[0] + f0.y * yp[1] + f1.x * yp[2] + f1.y * yp[3] + f2.x * yp[4] + f2.y * yp[5] + e0.x * ye0 + e0.y * ye1 + e1.x * ye2;
-    const double m1 = f3.x * yp[0] + f3.y * yp[1] + f4.x * yp[2] + f4.y * yp[3] + f5.x * yp[4] + f5.y * yp[5] + e1.y * ye0 + e2.x * ye1 + e2.y * ye2;
+    const double m0 = f0.x * yp[0] + f0.y * yp[1] + f1.x * yp[2] + ts * (e0.x * yp[3] + e0.y * yp[4] + e1.x * yp[5]) + e0.x * ye0 + e0.y * ye1 + e1.x * ye2;
+    const double m1 = f1.y * yp[0] + f2.x * yp[1] + f2.y * yp[2] + ts * (e1.y * yp[3] + e2.x * yp[4] + e2.y * yp[5]) + e1.y * ye0 + e2.x * ye1 + e2.y * ye2;
     mc += m0 * (r.x - 0.5 * m0) + m1 * (r.y - 0.5 * m1);
   }
   const double tot = block_sum<256>(mc, sm);
