@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "kernels.cuh"
+#include "tile_chol.cuh"
 #include "nccl_dyn.h"
 
 using namespace bsnls;
@@ -67,6 +68,8 @@ struct bsnls_handle {
   std::vector<int> pose_q_blk, pose_t_blk;
   std::vector<int> pair_a, pair_b;
   std::vector<int> gd_row, gd_col;
+  bool tiled = false; std::vector<int> f_api;   // tile-sparse Cholesky; internal f position -> API (program-order) position
+  TileChol TC{}; std::vector<int> tc_col_ptr; DevMem d_tc_tile_off, d_tc_col_ptr, d_tc_col_rows, d_tc_T, d_tc_W, d_tc_b; size_t tc_T_bytes = 0;
   bool chunk_fma = false; int chunk_max_slots = 1; DevMem d_syrk_plan, d_chunk_tile_off, d_pp_toff, d_pp_info;
   int nchunks = 0; DevMem d_obs_slot, d_chunk_end, d_chunk_begin, d_chunk_nslots, d_chunk_part_off, d_chunk_cpart_off, d_pp_ptr, d_pp_off, d_pp_coff, d_part, d_cpart;
   bool sparse = false, pcg = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
@@ -262,10 +265,21 @@ int EnqueueAssemble(bsnls_handle* h, const Options& o) {  // phase D1: reduced s
 void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular solves
   const int n = h->P.nf_dim; LMState* st = h->d_state.as<LMState>();
   double* Sd = h->d_S.as<double>();
-  if (h->sparse) {
-    Sd = h->d_Sdense.as<double>();
-    cudaMemsetAsync(Sd, 0, sizeof(double) * (size_t)n * n, h->stream);
-    LAUNCH(h, bsr_to_dense_kernel, (unsigned)((h->nnzb * 9 + 255) / 256), 256, h->P, h->d_S.as<double>(), Sd, st);
+  if (h->tiled) {
+    const TileChol& TC = h->TC;
+    const size_t smem = sizeof(double) * 2 * kTS * kTLd;
+    cudaMemsetAsync(TC.T, 0, h->tc_T_bytes, h->stream);
+    LAUNCH(h, bsr_to_tiles_kernel, (unsigned)((h->nnzb * 9 + kTS + 255) / 256), 256, h->P, TC, h->d_S.as<double>(), st);
+    for (int k = 0; k < TC.nT; ++k) {
+      const int a = h->tc_col_ptr[k + 1] - h->tc_col_ptr[k];
+      LAUNCH(h, tile_potrf_kernel, 1, 256, TC, k, st);
+      if (a > 0) {
+        LAUNCH_SMEM(h, tile_trsm_kernel, a, 256, smem, TC, k, st);
+        LAUNCH_SMEM(h, tile_syrk_kernel, a * (a + 1) / 2, 256, smem, TC, k, st);
+      }
+    }
+    LAUNCH(h, tile_solve_kernel, 1, 1024, TC, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
+    return;
   }
   if (n <= kTinyMax && !h->sparse) {  // whole matrix in shared memory
     const size_t smem = sizeof(double) * ((size_t)kTinyMax * (kTinyMax + 1) + 2 * kTinyMax);
@@ -402,6 +416,8 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
     g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
   }
   if ((e = cudaFuncSetAttribute(chunk_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, syrk_smem_bytes(kChunkSlots))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
+  if ((e = cudaFuncSetAttribute(tile_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * 2 * kTS * kTLd))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
+  if ((e = cudaFuncSetAttribute(tile_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * 2 * kTS * kTLd))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chunk_accum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kChunkSmemBytes)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chol_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kTinyMax * (kTinyMax + 1) + 2 * kTinyMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kSmallMax * kNB + kSmallMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
@@ -493,9 +509,12 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   if (nf_dim == 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "no non-landmark parameter blocks to solve for");
   // assembly layout and linear solver: small windows dense + dense; mid-size block-sparse assembly expanded into the
   // dense Cholesky; large (or on request) block-sparse + PCG
-  h->pcg = h->opt.linear_solver == BSNLS_LINEAR_ITERATIVE_SCHUR || (h->opt.linear_solver == BSNLS_LINEAR_AUTO && nf_dim > 16000);
-  h->sparse = h->pcg || nf_dim > 3000;
-  if (!h->pcg && nf_dim > 24000) return h->fail(BSNLS_ERR_UNSUPPORTED, "reduced system of dimension %d exceeds the dense solver limit", nf_dim);
+  // assembly layout and linear solver: sliding windows (<= kSmallMax) dense storage + a single-CTA Cholesky; everything
+  // larger is assembled block-sparse and factored by the tile-sparse Cholesky in a bandwidth-reducing order, unless the
+  // iterative solver is requested or the fill of the tile factor is too large (decided after the symbolic step below)
+  h->pcg = h->opt.linear_solver == BSNLS_LINEAR_ITERATIVE_SCHUR;
+  h->tiled = !h->pcg && nf_dim > kSmallMax;
+  h->sparse = h->pcg || h->tiled;
 
   // ---- reprojection: poses, landmark-sorted observations ----
   std::vector<int> pose_of_q(nb, -1), pose_of_t(nb, -1);
@@ -573,6 +592,46 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       key[e] = {mn, mx}; lperm[e] = e;
     }
     std::stable_sort(lperm.begin(), lperm.end(), [&](int x, int y2) { return key[x] < key[y2]; });
+  }
+  // ---- internal order of the f-blocks. The API order (h->fblocks, program order) keeps the two blocks of a pose far
+  // apart, which makes the reduced system's envelope nearly full. For the tile-sparse factorisation the blocks are
+  // renumbered with reverse Cuthill-McKee on the block graph (pose pairs + generic-factor cliques): a trajectory becomes
+  // a band, loop closures a few long rows. From here on fpos[] is the INTERNAL position; f_api[] maps back.
+  h->f_api.resize(h->nf); for (int k = 0; k < h->nf; ++k) h->f_api[k] = k;
+  if (h->tiled) {
+    std::vector<std::vector<int>> adj(h->nf);
+    auto link = [&](int x, int y2) { if (x >= 0 && y2 >= 0 && x != y2) { adj[x].push_back(y2); adj[y2].push_back(x); } };
+    for (int p2 = 0; p2 < h->npairs; ++p2) {
+      const int a = h->pair_a[p2], b = h->pair_b[p2];
+      const int va[2] = {fpos[h->pose_q_blk[a]], fpos[h->pose_t_blk[a]]}, vb[2] = {fpos[h->pose_q_blk[b]], fpos[h->pose_t_blk[b]]};
+      if (a == b) link(va[0], va[1]); else for (int i = 0; i < 2; ++i) for (int j = 0; j < 2; ++j) link(va[i], vb[j]);
+    }
+    for (const bsnls_factor_group* G : gfg) {
+      const int nbk = kNumBlocks[G->type];
+      for (int64_t i = 0; i < G->count; ++i)
+        for (int b1 = 0; b1 < nbk; ++b1) for (int b2 = 0; b2 < b1; ++b2) link(fpos[G->blocks[i * nbk + b1]], fpos[G->blocks[i * nbk + b2]]);
+    }
+    for (auto& v : adj) { std::sort(v.begin(), v.end()); v.erase(std::unique(v.begin(), v.end()), v.end()); }
+    std::vector<int> rank(h->nf, -1), orderv; orderv.reserve(h->nf);
+    std::vector<char> seen(h->nf, 0);
+    auto bfs = [&](int start, std::vector<int>& out, bool mark) {
+      std::vector<char> local; std::vector<char>& sn = mark ? seen : local; if (!mark) local.assign(h->nf, 0);
+      const size_t first = out.size(); out.push_back(start); sn[start] = 1;
+      for (size_t q = first; q < out.size(); ++q) {
+        std::vector<int> nb2; for (int v : adj[out[q]]) if (!sn[v] && (mark || !seen[v])) { sn[v] = 1; nb2.push_back(v); }
+        std::sort(nb2.begin(), nb2.end(), [&](int x, int y2) { return adj[x].size() != adj[y2].size() ? adj[x].size() < adj[y2].size() : x < y2; });
+        out.insert(out.end(), nb2.begin(), nb2.end());
+      }
+    };
+    for (int v0 = 0; v0 < h->nf; ++v0) {
+      if (seen[v0]) continue;
+      std::vector<int> probe; bfs(v0, probe, false);           // pseudo-peripheral start: the far end of a sweep from v0
+      std::vector<int> probe2; bfs(probe.back(), probe2, false);
+      bfs(probe2.back(), orderv, true);
+    }
+    std::reverse(orderv.begin(), orderv.end());
+    for (int k = 0; k < h->nf; ++k) { rank[orderv[k]] = k; h->f_api[k] = orderv[k]; }
+    for (int b = 0; b < nb; ++b) if (fpos[b] >= 0) fpos[b] = rank[fpos[b]];
   }
   h->blk_tan.assign(nb, -1);
   for (int b = 0; b < nb; ++b) if (fpos[b] >= 0) h->blk_tan[b] = ne_dim + 3 * fpos[b];
@@ -887,6 +946,42 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   }
   // work buffers
   const int ntan = ne_dim + nf_dim;
+  // ---- tile-sparse Cholesky: symbolic factorisation at 64x64-tile granularity (structure only; fixed per problem) ----
+  std::vector<long long> tc_tile_off; std::vector<int> tc_col_rows; long long tc_tiles = 0;
+  h->tc_col_ptr.clear();
+  if (h->tiled) {
+    const int nT = (nf_dim + kTS - 1) / kTS;
+    std::vector<std::vector<int>> col(nT);     // non-zero tiles strictly below the diagonal, per tile column
+    for (int r = 0; r < h->nf; ++r)
+      for (int k = h->bsr_rowptr[r]; k < h->bsr_rowptr[r + 1]; ++k) {
+        const int c = h->bsr_col[k];
+        if (c > r) continue;
+        // a 3x3 block may straddle tile boundaries: mark every tile it touches
+        for (int tr = (3 * r) / kTS; tr <= (3 * r + 2) / kTS; ++tr)
+          for (int tc = (3 * c) / kTS; tc <= (3 * c + 2) / kTS; ++tc) if (tr > tc) col[tc].push_back(tr);
+      }
+    for (int k = 0; k < nT; ++k) {
+      std::sort(col[k].begin(), col[k].end()); col[k].erase(std::unique(col[k].begin(), col[k].end()), col[k].end());
+      // fill: eliminating tile column k couples all of its rows; it is enough to hand the rows below the first one to
+      // that first row's column (elimination-tree parent): later columns propagate them further
+      if (!col[k].empty()) { const int par = col[k][0]; col[par].insert(col[par].end(), col[k].begin() + 1, col[k].end()); }
+    }
+    h->tc_col_ptr.assign(nT + 1, 0);
+    for (int k = 0; k < nT; ++k) { h->tc_col_ptr[k + 1] = h->tc_col_ptr[k] + (int)col[k].size(); tc_tiles += 1 + (long long)col[k].size(); }
+    const double tile_gb = (double)tc_tiles * kTileDoubles * 8 / 1e9;
+    if (std::getenv("BSNLS_DEBUG")) std::fprintf(stderr, "[bsnls] tile Cholesky: n %d, %d tile columns, %lld tiles (%.3f GB), dense lower would be %lld\n", nf_dim, nT, tc_tiles, tile_gb, (long long)nT * (nT + 1) / 2);
+    if (tile_gb > 24.0 || (long long)nT * nT > (1LL << 28)) {
+      if (h->opt.linear_solver == BSNLS_LINEAR_DENSE_SCHUR) return h->fail(BSNLS_ERR_UNSUPPORTED, "tile factor of the reduced system needs %.1f GB; use the iterative solver", tile_gb);
+      h->tiled = false; h->pcg = true;     // AUTO: fall back to conjugate gradients
+    } else {
+      tc_tile_off.assign((size_t)nT * nT, -1);
+      long long t = 0;
+      for (int k = 0; k < nT; ++k) {
+        tc_tile_off[(size_t)k * nT + k] = (t++) * kTileDoubles;
+        for (int i : col[k]) { tc_tile_off[(size_t)i * nT + k] = (t++) * kTileDoubles; tc_col_rows.push_back(i); }
+      }
+    }
+  }
   h->nb_obs = h->nobs ? BlocksFor(h->nobs, 256) : 0; h->nb_lm = h->ne ? BlocksFor(h->ne * h->G, 256) : 0; h->nb_act = BlocksFor((int)h->active_blocks.size(), 256);
   CK(h->d_x.alloc(sizeof(double) * off)); CK(h->d_xc.alloc(sizeof(double) * off)); CK(h->d_x0.alloc(sizeof(double) * off));
   CK(h->d_Jrec.alloc(sizeof(double) * kJRec * (size_t)h->nobs)); CK(h->d_Vrec.alloc(sizeof(double) * kVRec * (size_t)h->nobs));
@@ -896,7 +991,15 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   if (h->world > 1) { CK(h->d_gradS.alloc(sizeof(double) * nf_dim)); CK(h->d_colsqS.alloc(sizeof(double) * nf_dim)); }
   CK(h->d_scale.alloc(sizeof(double) * ntan)); CK(h->d_y.alloc(sizeof(double) * ntan)); CK(h->d_yf.alloc(sizeof(double) * nf_dim));
   CK(h->d_rhs.alloc(sizeof(double) * nf_dim)); CK(h->d_S.alloc(sizeof(double) * (h->sparse ? (size_t)h->nnzb * 9 : (size_t)nf_dim * nf_dim)));
-  if (h->sparse && !h->pcg) CK(h->d_Sdense.alloc(sizeof(double) * (size_t)nf_dim * nf_dim));
+  if (h->tiled) {
+    const int nT = (nf_dim + kTS - 1) / kTS;
+    if (tc_col_rows.empty()) tc_col_rows.push_back(0);
+    CK(upload(h->d_tc_tile_off, tc_tile_off, s)); CK(upload(h->d_tc_col_ptr, h->tc_col_ptr, s)); CK(upload(h->d_tc_col_rows, tc_col_rows, s));
+    h->tc_T_bytes = sizeof(double) * kTileDoubles * (size_t)tc_tiles;
+    CK(h->d_tc_T.alloc(h->tc_T_bytes)); CK(h->d_tc_W.alloc(sizeof(double) * kTileDoubles * (size_t)nT)); CK(h->d_tc_b.alloc(sizeof(double) * kTS * (size_t)nT));
+    h->TC.nT = nT; h->TC.n = nf_dim; h->TC.tile_off = h->d_tc_tile_off.as<long long>(); h->TC.col_ptr = h->d_tc_col_ptr.as<int>();
+    h->TC.col_rows = h->d_tc_col_rows.as<int>(); h->TC.T = h->d_tc_T.as<double>(); h->TC.W = h->d_tc_W.as<double>(); h->TC.b = h->d_tc_b.as<double>();
+  }
   if (h->pcg) {
     int dev_sms = 0, per_sm = 0;
     CK(cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, h->device));
@@ -1158,9 +1261,12 @@ int bsnls_get_reduced_system(bsnls_handle* h, double radius, double* S, double* 
     CK(cudaMemcpyAsync(blocks.data(), h->d_S.p, sizeof(double) * blocks.size(), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     std::memset(S, 0, sizeof(double) * (size_t)dim * dim);
+    // internal (bandwidth-reducing) f-block order -> API (program) order
     for (int r = 0; r < h->nf; ++r)
       for (int k = h->bsr_rowptr[r]; k < h->bsr_rowptr[r + 1]; ++k)
-        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) S[(size_t)(3 * h->bsr_col[k] + j) * dim + 3 * r + i] = blocks[(size_t)k * 9 + 3 * i + j];
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) S[(size_t)(3 * h->f_api[h->bsr_col[k]] + j) * dim + 3 * h->f_api[r] + i] = blocks[(size_t)k * 9 + 3 * i + j];
+    std::vector<double> tmp(rhs, rhs + dim);
+    for (int r = 0; r < h->nf; ++r) for (int i = 0; i < 3; ++i) rhs[3 * h->f_api[r] + i] = tmp[3 * r + i];
     return BSNLS_OK;
   }
   CK(cudaMemcpyAsync(S, h->d_S.p, sizeof(double) * (size_t)dim * dim, cudaMemcpyDeviceToHost, h->stream));
@@ -1235,7 +1341,7 @@ int bsnls_get_reduced_pattern(bsnls_handle* h, int32_t* rows, int32_t* cols, int
     const int fa[2] = {fpos[h->pose_q_blk[a]], fpos[h->pose_t_blk[a]]}, fb[2] = {fpos[h->pose_q_blk[b]], fpos[h->pose_t_blk[b]]};
     for (int i = 0; i < 2; ++i) for (int j = 0; j < 2; ++j) add(fa[i], fb[j]);
   }
-  for (int d = 0; d < h->ngdest; ++d) add(h->gd_row[d], h->gd_col[d]);
+  for (int d = 0; d < h->ngdest; ++d) add(h->f_api[h->gd_row[d]], h->f_api[h->gd_col[d]]);   // gd_* are internal positions
   for (int k = 0; k < h->nf; ++k) add(k, k);
   std::sort(keys.begin(), keys.end()); keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
   if (rows && cols) { if (*count < (int64_t)keys.size()) return h->fail(BSNLS_ERR_INVALID, "pattern buffers too small"); for (size_t k = 0; k < keys.size(); ++k) { rows[k] = (int)(keys[k] / h->nf); cols[k] = (int)(keys[k] % h->nf); } }
