@@ -272,11 +272,8 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     LAUNCH(h, bsr_to_tiles_kernel, (unsigned)((h->nnzb * 9 + kTS + 255) / 256), 256, h->P, TC, h->d_S.as<double>(), st);
     for (int k = 0; k < TC.nT; ++k) {
       const int a = h->tc_col_ptr[k + 1] - h->tc_col_ptr[k];
-      LAUNCH(h, tile_potrf_kernel, 1, 256, TC, k, st);
-      if (a > 0) {
-        LAUNCH_SMEM(h, tile_trsm_kernel, a, 256, smem, TC, k, st);
-        LAUNCH_SMEM(h, tile_syrk_kernel, a * (a + 1) / 2, 256, smem, TC, k, st);
-      }
+      LAUNCH_SMEM(h, tile_panel_kernel, std::max(1, a), 256, sizeof(double) * kPanelSmemDoubles, TC, k, st);
+      if (a > 0) LAUNCH_SMEM(h, tile_syrk_kernel, a * (a + 1) / 2, 256, smem, TC, k, st);
     }
     LAUNCH(h, tile_solve_kernel, 1, 1024, TC, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
     return;
@@ -416,7 +413,7 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
     g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
   }
   if ((e = cudaFuncSetAttribute(chunk_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, syrk_smem_bytes(kChunkSlots))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
-  if ((e = cudaFuncSetAttribute(tile_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * 2 * kTS * kTLd))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
+  if ((e = cudaFuncSetAttribute(tile_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * kPanelSmemDoubles))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(tile_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * 2 * kTS * kTLd))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chunk_accum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kChunkSmemBytes)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chol_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kTinyMax * (kTinyMax + 1) + 2 * kTinyMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
