@@ -3,8 +3,8 @@
 // The reduced camera system of a trajectory is banded once poses are ordered along the trajectory (plus a few long
 // rows per loop closure). It is stored as 64x64 tiles, only those that are structurally non-zero after a symbolic
 // factorisation at tile granularity (host, set_problem), and factored right-looking one tile column at a time:
-//   potrf  diagonal tile (one CTA, shared memory), also L_kk^-1
-//   trsm   L(i,k) = A(i,k) L_kk^-T as a tile product with the inverse      (one CTA per non-zero tile below the diagonal)
+//   panel  potrf of the diagonal tile together with W = L_kk^-1, then L(i,k) = A(i,k) W^T as a tile product
+//          (one CTA per non-zero tile below the diagonal, each factoring the diagonal tile redundantly)
 //   syrk   A(i,j) -= L(i,k) L(j,k)^T                                        (one CTA per pair of non-zero tiles)
 // The two products run on the FP64 tensor cores (mma.sync m8n8k4). The launch sequence depends on the structure only,
 // so it is fixed per problem. Replaces SuiteSparse/Eigen sparse Cholesky inside ceres' SPARSE_SCHUR.
@@ -47,10 +47,18 @@ __global__ void __launch_bounds__(256) bsr_to_tiles_kernel(DeviceProblem P, Tile
 
 // ---- tile loads / the tensor-core product C = A B^T of two 64x64 tiles held in shared memory ----
 __device__ __forceinline__ void tile_load(const double* __restrict__ g, double* __restrict__ s) {
-  for (int e = threadIdx.x; e < kTileDoubles / 2; e += 256) {
-    const int c = e >> 5, r2 = e & 31;
-    reinterpret_cast<double2*>(s + c * kTLd)[r2] = reinterpret_cast<const double2*>(g)[e];
-  }
+  double2 v[8];   // all eight loads of a thread in flight before the first store
+#pragma unroll
+  for (int u = 0; u < 8; ++u) v[u] = reinterpret_cast<const double2*>(g)[threadIdx.x + 256 * u];
+#pragma unroll
+  for (int u = 0; u < 8; ++u) { const int e = threadIdx.x + 256 * u; reinterpret_cast<double2*>(s + (e >> 5) * kTLd)[e & 31] = v[u]; }
+}
+__device__ __forceinline__ void tile_load2(const double* __restrict__ g0, double* __restrict__ s0, const double* __restrict__ g1, double* __restrict__ s1) {
+  double2 v[16];
+#pragma unroll
+  for (int u = 0; u < 8; ++u) { v[u] = reinterpret_cast<const double2*>(g0)[threadIdx.x + 256 * u]; v[8 + u] = reinterpret_cast<const double2*>(g1)[threadIdx.x + 256 * u]; }
+#pragma unroll
+  for (int u = 0; u < 8; ++u) { const int e = threadIdx.x + 256 * u; reinterpret_cast<double2*>(s0 + (e >> 5) * kTLd)[e & 31] = v[u]; reinterpret_cast<double2*>(s1 + (e >> 5) * kTLd)[e & 31] = v[8 + u]; }
 }
 // warp `I` (0..7) computes rows 8I..8I+7 of C: acc[J] = the lane's two entries (row 8I+g, cols 8J+2tg, 8J+2tg+1)
 __device__ __forceinline__ void tile_abt(const double* __restrict__ As, const double* __restrict__ Bs, int I, int lane, double (&acc)[8][2]) {
@@ -71,20 +79,30 @@ __device__ __forceinline__ void tile_abt(const double* __restrict__ As, const do
 // One CTA per non-zero tile below the diagonal (at least one CTA). Every CTA factors the 64x64 diagonal tile itself --
 // the same arithmetic, so the same bits, and no dependency between CTAs -- then multiplies its own tile:
 // L(i,k) = A(i,k) L_kk^-T = A(i,k) W^T with W = L_kk^-1. CTA 0 also stores W (the solve needs it).
-constexpr int kPanelSmemDoubles = kTS * (kTS + 1) + 2 * kTS * kTLd + 32 * 33 + 2 * kTS + kTS;
+// The factorisation is right-looking on 4x4 register blocks (thread (ty, tx) owns rows 4ty.., columns 4tx..), four pivots
+// per step: the owner of the diagonal block factors it in registers and publishes the inverse of that 4x4 factor; the
+// threads of the block column multiply their blocks by it (the panel), and the rest of the matrix gets a rank-4 update.
+// The same row operations are applied to an identity, which turns it into W = L_kk^-1 in the same sweep: blocks right of
+// the pivot column update A entries, blocks left of it update W entries. Two barriers per four pivots.
+constexpr int kPanelSmemDoubles = 2 * kTS * kTLd + 16 + kTS * 4 + 4 * kTS;
+#ifdef PANEL_PROF
+__device__ long long g_panel_prof[80];
+#endif
 __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int k, LMState* st) {
   extern __shared__ __align__(16) double sm[];
   double* As = sm;                          // A(i,k), column-major, pitch kTLd
   double* Bs = As + kTS * kTLd;             // W, column-major, pitch kTLd
-  double (*A)[kTS + 1] = reinterpret_cast<double (*)[kTS + 1]>(Bs + kTS * kTLd);   // L_kk, A[r][c]
-  double (*Tm)[33] = reinterpret_cast<double (*)[33]>(&A[kTS][0]);                 // 32x32 scratch of the blocked inverse
-  double (*raw)[kTS] = reinterpret_cast<double (*)[kTS]>(&Tm[32][0]);             // [2][64] column exchange of the potrf
-  double* invd = &raw[2][0];
+  double* sLi = Bs + kTS * kTLd;            // inverse of the 4x4 diagonal factor, row-major (lower)
+  double* sPan = sLi + 16;                  // the panel: L(r, 4 jb + c) at sPan[((r & 3) * 16 + (r >> 2)) * 4 + c]: the rows 4 ty + i of
+                                            // the 16 block rows of a warp are adjacent (no bank conflicts)
+  double* sWrow = sPan + kTS * 4;           // final rows 4 jb.. of W: sWrow[i * 64 + c]
   __shared__ int failed;
   if (!gate_run(st) || st->lin_fail) return;   // lin_fail is written only at the very end (by CTA 0)
-  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;   // potrf: thread owns rows 4ty.., cols 4tx.. (ty >= tx matters)
+  // a warp holds two block columns (tx) and all block rows (ty): at any step it is either left of the pivot column (W
+  // updates only) or right of it (A updates only), so the two roles do not serialise inside a warp
+  const int tid = threadIdx.x, tx = tid >> 4, ty = tid & 15;
   const int na = TC.col_ptr[k + 1] - TC.col_ptr[k];
-  double* G = TC.T + TC.tile_off[(long long)k * TC.nT + k];
+  const double* G = TC.T + TC.tile_off[(long long)k * TC.nT + k];
   double* Gi = nullptr;
   if (na > 0) {   // start fetching this CTA's tile; it is not needed before the product
     Gi = TC.T + TC.tile_off[(long long)TC.col_rows[TC.col_ptr[k] + blockIdx.x] * TC.nT + k];
@@ -95,111 +113,131 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int k, LMS
     }
     asm volatile("cp.async.commit_group;");
   }
+#ifdef PANEL_PROF
+  if (tid == 255) g_panel_prof[70] = clock64();
+#endif
   if (tid == 0) failed = 0;
-  double a[4][4];
+  double a[4][4], w[4][4];
 #pragma unroll
   for (int c = 0; c < 4; ++c)
 #pragma unroll
-    for (int i = 0; i < 4; ++i) a[i][c] = G[(4 * tx + c) * kTS + 4 * ty + i];
-  if (tx == 0) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) raw[0][4 * ty + i] = a[i][0];
-  }
+    for (int i = 0; i < 4; ++i) { a[i][c] = ty >= tx ? G[(4 * tx + c) * kTS + 4 * ty + i] : 0.0; w[i][c] = (ty == tx && i == c) ? 1.0 : 0.0; }
   bool bad = false;
 #pragma unroll 1
   for (int jb = 0; jb < kTS / 4; ++jb) {
+    if (ty == jb && tx == jb) {   // 4x4 Cholesky of the diagonal block and the inverse of its factor
+#ifdef PANEL_PROF
+      const long long ta = clock64();
+#endif
+      const double r0 = rsqrt(a[0][0]);
+      const double l10 = a[1][0] * r0, l20 = a[2][0] * r0, l30 = a[3][0] * r0;
+      const double d1 = a[1][1] - l10 * l10, r1 = rsqrt(d1);
+      const double l21 = (a[2][1] - l20 * l10) * r1, l31 = (a[3][1] - l30 * l10) * r1;
+      const double d2 = a[2][2] - l20 * l20 - l21 * l21, r2 = rsqrt(d2);
+      const double l32 = (a[3][2] - l30 * l20 - l31 * l21) * r2;
+      const double d3 = a[3][3] - l30 * l30 - l31 * l31 - l32 * l32, r3 = rsqrt(d3);
+      bad = bad || !(a[0][0] > 0.0) || !(d1 > 0.0) || !(d2 > 0.0) || !(d3 > 0.0);
+      const double i10 = -l10 * r0 * r1, i21 = -l21 * r1 * r2, i32 = -l32 * r2 * r3;
+      const double i20 = -(l20 * r0 + l21 * i10) * r2, i31 = -(l31 * r1 + l32 * i21) * r3;
+      const double i30 = -(l30 * r0 + l31 * i10 + l32 * i20) * r3;
+      sLi[0] = r0; sLi[1] = 0.0; sLi[2] = 0.0; sLi[3] = 0.0;
+      sLi[4] = i10; sLi[5] = r1; sLi[6] = 0.0; sLi[7] = 0.0;
+      sLi[8] = i20; sLi[9] = i21; sLi[10] = r2; sLi[11] = 0.0;
+      sLi[12] = i30; sLi[13] = i31; sLi[14] = i32; sLi[15] = r3;
+#ifdef PANEL_PROF
+      if (jb == 5) g_panel_prof[71] = clock64() - ta;
+#endif
+    }
+    __syncthreads();
+#ifdef PANEL_PROF
+    if (tid == 255) g_panel_prof[4 * jb] = clock64();
+#endif
+    if (ty >= jb && (tx == jb || ty == jb)) {
+      double Li[4][4];
 #pragma unroll
-    for (int cj = 0; cj < 4; ++cj) {
-      const int j = 4 * jb + cj, p = j & 1;
-      __syncthreads();
-      if (4 * ty + 3 < j) continue;           // all rows of this thread are above the pivot: nothing left to do but the barriers
-      const double x = raw[p][j];
-      bad = bad || !(x > 0.0);
-      const double inv = rsqrt(x);
-      double lr[4], lc[4];
+      for (int i = 0; i < 4; ++i) { const double2 u0 = reinterpret_cast<const double2*>(sLi)[2 * i], u1 = reinterpret_cast<const double2*>(sLi)[2 * i + 1]; Li[i][0] = u0.x; Li[i][1] = u0.y; Li[i][2] = u1.x; Li[i][3] = u1.y; }
+      if (tx == jb && ty > jb) {   // panel block: L = A Li^T
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { lr[i] = raw[p][4 * ty + i] * inv; lc[i] = raw[p][4 * tx + i] * inv; }
-      if (tx == jb) {
+        for (int i = 0; i < 4; ++i) {
+          double l[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { const int r = 4 * ty + i; if (r > j) a[i][cj] = lr[i]; else if (r == j) a[i][cj] = x * inv; }
+          for (int c = 0; c < 4; ++c) { double sacc = 0.0;
+#pragma unroll
+            for (int m = 0; m <= c; ++m) sacc += a[i][m] * Li[c][m];
+            l[c] = sacc; }
+#pragma unroll
+          for (int c = 0; c < 4; ++c) a[i][c] = l[c];
+          reinterpret_cast<double2*>(sPan)[2 * (16 * i + ty)] = make_double2(l[0], l[1]);
+          reinterpret_cast<double2*>(sPan)[2 * (16 * i + ty) + 1] = make_double2(l[2], l[3]);
+        }
       }
-      if (ty >= tx && tx >= jb) {
+      if (ty == jb) {              // rows 4 jb.. of W are final: W = Li W
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
+        for (int c = 0; c < 4; ++c) {
+          double f[4];
 #pragma unroll
-          for (int i = 0; i < 4; ++i) if (4 * tx + c > j && 4 * ty + i >= 4 * tx + c) a[i][c] -= lr[i] * lc[c];
-      }
-      if (j + 1 < kTS && tx == (j + 1) / 4) {   // raw column j + 1 for the next step
+          for (int i = 0; i < 4; ++i) { double sacc = 0.0;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) raw[p ^ 1][4 * ty + i] = (cj == 3) ? a[i][0] : a[i][(cj + 1) & 3];
+            for (int m = 0; m <= i; ++m) sacc += Li[i][m] * w[m][c];
+            f[i] = sacc; }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { w[i][c] = f[i]; sWrow[i * kTS + 4 * tx + c] = f[i]; }
+        }
       }
     }
+#ifdef PANEL_PROF
+    if (tid == 255 && jb == 5) g_panel_prof[72] = clock64();
+#endif
+    __syncthreads();
+#ifdef PANEL_PROF
+    if (tid == 255 && jb == 5) g_panel_prof[73] = clock64();
+#endif
+    if (ty > jb && ty >= tx) {    // rank-4 update with the panel rows of this thread
+      double Pr[4][4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { const double2 u0 = reinterpret_cast<const double2*>(sPan)[2 * (16 * i + ty)], u1 = reinterpret_cast<const double2*>(sPan)[2 * (16 * i + ty) + 1]; Pr[i][0] = u0.x; Pr[i][1] = u0.y; Pr[i][2] = u1.x; Pr[i][3] = u1.y; }
+      if (tx > jb) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const double2 u0 = reinterpret_cast<const double2*>(sPan)[2 * (16 * c + tx)], u1 = reinterpret_cast<const double2*>(sPan)[2 * (16 * c + tx) + 1];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) a[i][c] -= Pr[i][0] * u0.x + Pr[i][1] * u0.y + Pr[i][2] * u1.x + Pr[i][3] * u1.y;
+        }
+      } else {
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          const double2 u0 = reinterpret_cast<const double2*>(sWrow + m * kTS)[2 * tx], u1 = reinterpret_cast<const double2*>(sWrow + m * kTS)[2 * tx + 1];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { w[i][0] -= Pr[i][m] * u0.x; w[i][1] -= Pr[i][m] * u0.y; w[i][2] -= Pr[i][m] * u1.x; w[i][3] -= Pr[i][m] * u1.y; }
+        }
+      }
+    }
+#ifdef PANEL_PROF
+    if (tid == 255 && jb == 5) g_panel_prof[74] = clock64();
+#endif
   }
+#ifdef PANEL_PROF
+  if (tid == 255) g_panel_prof[64] = clock64();
+#endif
   if (bad) failed = 1;
-#pragma unroll
-  for (int c = 0; c < 4; ++c)
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int r = 4 * ty + i, cc = 4 * tx + c;
-      if (r >= cc) { A[r][cc] = a[i][c]; if (r == cc) invd[r] = 1.0 / a[i][c]; }   // L_kk itself is not stored: other CTAs may still be reading A_kk, and only W is used later
-    }
-  for (int e = tid; e < kTS * kTLd; e += 256) Bs[e] = 0.0;
-  __syncthreads();
-  // ---- W = L^-1, blocked: 16x16 diagonal blocks by substitution, then two levels of block products ----
-  // W(r, c) lives at Bs[c * kTLd + r]
+  // W (lower triangular) for the product and, from CTA 0, for the triangular solves
   {
-    const int blk = tid >> 6, c = 16 * blk + ((tid >> 2) & 15), sub = tid & 3, r0 = 16 * blk;
-    for (int rr = 0; rr < 16; ++rr) {
-      const int r = r0 + rr;
-      double sum = 0.0;
-      if (r > c) for (int m = c + sub; m < r; m += 4) sum += A[r][m] * Bs[c * kTLd + m];
-      sum += __shfl_xor_sync(0xffffffffu, sum, 1); sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-      if (sub == 0 && r >= c) Bs[c * kTLd + r] = r == c ? invd[r] : -sum * invd[r];
-      __syncwarp();
-    }
-  }
-  __syncthreads();
-  // level 1: W[b+1][b] = -W[b+1][b+1] (L[b+1][b] W[b][b]) for b = 0, 2 (16x16 blocks)
-  {
-    const int pr = tid >> 7, b = 2 * pr, o = tid & 127;     // two outputs per thread: (r, c) and (r + 8, c)
-    const int r = o >> 4, c = o & 15;
-    double t0 = 0.0, t1 = 0.0;
-    for (int m = c; m < 16; ++m) { const double w = Bs[(16 * b + c) * kTLd + 16 * b + m]; t0 += A[16 * (b + 1) + r][16 * b + m] * w; t1 += A[16 * (b + 1) + r + 8][16 * b + m] * w; }
-    Tm[16 * pr + r][c] = t0; Tm[16 * pr + r + 8][c] = t1;
-    __syncthreads();
-    double u0 = 0.0, u1 = 0.0;
-    for (int m = 0; m <= r + 8; ++m) { const double t = Tm[16 * pr + m][c]; if (m <= r) u0 += Bs[(16 * (b + 1) + m) * kTLd + 16 * (b + 1) + r] * t; u1 += Bs[(16 * (b + 1) + m) * kTLd + 16 * (b + 1) + r + 8] * t; }
-    Bs[(16 * b + c) * kTLd + 16 * (b + 1) + r] = -u0; Bs[(16 * b + c) * kTLd + 16 * (b + 1) + r + 8] = -u1;
-  }
-  __syncthreads();
-  // level 2: W[32:64][0:32] = -W22 (L21 W11), 32x32 blocks; four outputs per thread: rows r, r+8, r+16, r+24 of column c
-  {
-    const int r = tid >> 5, c = tid & 31;
-    double t[4] = {0.0, 0.0, 0.0, 0.0};
-    for (int m = c; m < 32; ++m) {
-      const double w = Bs[c * kTLd + m];
+    double* Wk = TC.W + (size_t)k * kTileDoubles;
 #pragma unroll
-      for (int q = 0; q < 4; ++q) t[q] += A[32 + r + 8 * q][m] * w;
-    }
+    for (int c = 0; c < 4; ++c)
 #pragma unroll
-    for (int q = 0; q < 4; ++q) Tm[r + 8 * q][c] = t[q];
-    __syncthreads();
-    double u[4] = {0.0, 0.0, 0.0, 0.0};
-    for (int m = 0; m < 32; ++m) {
-      const double tv = Tm[m][c];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) if (m <= r + 8 * q) u[q] += Bs[(32 + m) * kTLd + 32 + r + 8 * q] * tv;
-    }
-#pragma unroll
-    for (int q = 0; q < 4; ++q) Bs[c * kTLd + 32 + r + 8 * q] = -u[q];
+      for (int i = 0; i < 4; ++i) {
+        const double v = (ty > tx || (ty == tx && i >= c)) ? w[i][c] : 0.0;
+        Bs[(4 * tx + c) * kTLd + 4 * ty + i] = v;
+        if (blockIdx.x == 0) Wk[(4 * tx + c) * kTS + 4 * ty + i] = v;
+      }
   }
   if (na > 0) asm volatile("cp.async.wait_group 0;");
   __syncthreads();
-  if (blockIdx.x == 0) {
-    double* Wk = TC.W + (size_t)k * kTileDoubles;
-    for (int e = tid; e < kTileDoubles; e += 256) Wk[e] = Bs[(e >> 6) * kTLd + (e & 63)];
-    if (failed && tid == 0) st->lin_fail = 1;
-  }
+  if (blockIdx.x == 0 && tid == 0 && failed) st->lin_fail = 1;
+#ifdef PANEL_PROF
+  if (tid == 255) g_panel_prof[65] = clock64();
+#endif
   if (na == 0) return;
   const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
   double acc[8][2];
@@ -223,17 +261,20 @@ __global__ void __launch_bounds__(256) tile_syrk_kernel(TileChol TC, int k, cons
   while ((x + 1) * (x + 2) / 2 <= p) ++x;
   const int y = p - x * (x + 1) / 2;
   const int base = TC.col_ptr[k], i = TC.col_rows[base + x], j = TC.col_rows[base + y];
-  tile_load(TC.T + TC.tile_off[(long long)i * TC.nT + k], As);
-  if (i != j) tile_load(TC.T + TC.tile_off[(long long)j * TC.nT + k], Bs);
-  __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tg = lane & 3;
+  double* C = TC.T + TC.tile_off[(long long)i * TC.nT + j];
+  double cv[8][2];                      // the destination entries, fetched alongside the operands
+#pragma unroll
+  for (int J = 0; J < 8; ++J) { cv[J][0] = C[(8 * J + 2 * tg) * kTS + 8 * warp + g]; cv[J][1] = C[(8 * J + 2 * tg + 1) * kTS + 8 * warp + g]; }
+  if (i != j) tile_load2(TC.T + TC.tile_off[(long long)i * TC.nT + k], As, TC.T + TC.tile_off[(long long)j * TC.nT + k], Bs);
+  else tile_load(TC.T + TC.tile_off[(long long)i * TC.nT + k], As);
+  __syncthreads();
   double acc[8][2];
   tile_abt(As, i != j ? Bs : As, warp, lane, acc);
-  double* C = TC.T + TC.tile_off[(long long)i * TC.nT + j];
 #pragma unroll
   for (int J = 0; J < 8; ++J) {
-    C[(8 * J + 2 * tg) * kTS + 8 * warp + g] -= acc[J][0];
-    C[(8 * J + 2 * tg + 1) * kTS + 8 * warp + g] -= acc[J][1];
+    C[(8 * J + 2 * tg) * kTS + 8 * warp + g] = cv[J][0] - acc[J][0];
+    C[(8 * J + 2 * tg + 1) * kTS + 8 * warp + g] = cv[J][1] - acc[J][1];
   }
 }
 

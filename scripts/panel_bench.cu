@@ -1,0 +1,67 @@
+// Stand-alone timing + correctness check of the tile Cholesky kernels on one tile column (k = 0) with `na` tiles below the
+// diagonal. Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I beam_slam_b200/csrc -o build_tmp/panel_bench scripts/panel_bench.cu
+#include <cstdio>
+#include <cmath>
+#include <vector>
+#include "kernels.cuh"
+#include "tile_chol.cuh"
+using namespace bsnls;
+int main(int argc, char** argv) {
+  const int na = argc > 1 ? atoi(argv[1]) : 3, nT = na + 1, reps = 200;
+  std::vector<double> T((size_t)(nT + nT * nT) * kTileDoubles, 0.0);
+  // SPD diagonal tile + random tiles below
+  std::vector<double> M(64 * 64);
+  srand(1);
+  for (auto& v : M) v = rand() / (double)RAND_MAX - 0.5;
+  for (int r = 0; r < 64; ++r) for (int c = 0; c < 64; ++c) { double s = 0; for (int m = 0; m < 64; ++m) s += M[r * 64 + m] * M[c * 64 + m]; T[c * 64 + r] = s + (r == c ? 8.0 : 0.0); }
+  for (int t = 1; t < nT; ++t) for (int e = 0; e < kTileDoubles; ++e) T[(size_t)t * kTileDoubles + e] = rand() / (double)RAND_MAX - 0.5;
+  std::vector<long long> off((size_t)nT * nT, -1); std::vector<int> col_ptr(nT + 1, na), col_rows;
+  col_ptr[0] = 0; off[0] = 0;
+  for (int t = 1; t < nT; ++t) { off[(size_t)t * nT] = (long long)t * kTileDoubles; col_rows.push_back(t); }
+  long long next = nT;
+  for (int i = 1; i < nT; ++i) for (int j = 1; j <= i; ++j) off[(size_t)i * nT + j] = (next++) * kTileDoubles;
+  double *dT, *dT0, *dW, *db; long long* doff; int *dcp, *dcr; LMState* dst;
+  cudaMalloc(&dT, T.size() * 8); cudaMalloc(&dT0, T.size() * 8); cudaMalloc(&dW, (size_t)nT * kTileDoubles * 8); cudaMalloc(&db, nT * 64 * 8);
+  cudaMalloc(&doff, off.size() * 8); cudaMalloc(&dcp, col_ptr.size() * 4); cudaMalloc(&dcr, (col_rows.size() + 1) * 4); cudaMalloc(&dst, sizeof(LMState));
+  cudaMemcpy(dT0, T.data(), T.size() * 8, cudaMemcpyHostToDevice); cudaMemcpy(doff, off.data(), off.size() * 8, cudaMemcpyHostToDevice);
+  cudaMemcpy(dcp, col_ptr.data(), col_ptr.size() * 4, cudaMemcpyHostToDevice); if (na) cudaMemcpy(dcr, col_rows.data(), col_rows.size() * 4, cudaMemcpyHostToDevice);
+  cudaMemset(dst, 0, sizeof(LMState));
+  TileChol TC{nT, nT * 64, doff, dcp, dcr, dT, dW, db};
+  const size_t psm = sizeof(double) * kPanelSmemDoubles, ssm = sizeof(double) * 2 * kTS * kTLd;
+  cudaFuncSetAttribute(tile_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psm);
+  cudaFuncSetAttribute(tile_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssm);
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  float ms;
+  for (int pass = 0; pass < 2; ++pass) {
+    cudaEventRecord(e0);
+    for (int r = 0; r < reps; ++r) { cudaMemcpyAsync(dT, dT0, T.size() * 8, cudaMemcpyDeviceToDevice); tile_panel_kernel<<<na > 0 ? na : 1, 256, psm>>>(TC, 0, dst); }
+    cudaEventRecord(e1); cudaEventSynchronize(e1); cudaEventElapsedTime(&ms, e0, e1);
+  }
+  float base;
+  cudaEventRecord(e0); for (int r = 0; r < reps; ++r) cudaMemcpyAsync(dT, dT0, T.size() * 8, cudaMemcpyDeviceToDevice); cudaEventRecord(e1); cudaEventSynchronize(e1); cudaEventElapsedTime(&base, e0, e1);
+  printf("panel (na=%d): %.2f us per launch (copy alone %.2f us)\n", na, 1e3 * ms / reps, 1e3 * base / reps);
+  if (na) {
+    cudaEventRecord(e0);
+    for (int r = 0; r < reps; ++r) tile_syrk_kernel<<<na * (na + 1) / 2, 256, ssm>>>(TC, 0, dst);
+    cudaEventRecord(e1); cudaEventSynchronize(e1); cudaEventElapsedTime(&ms, e0, e1);
+    printf("syrk (%d pairs): %.2f us per launch\n", na * (na + 1) / 2, 1e3 * ms / reps);
+  }
+  // check W L = I and L(1,0) L_kk^T = A(1,0) using the host factor
+  cudaMemcpyAsync(dT, dT0, T.size() * 8, cudaMemcpyDeviceToDevice); tile_panel_kernel<<<na > 0 ? na : 1, 256, psm>>>(TC, 0, dst);
+  std::vector<double> W(kTileDoubles), L(64 * 64, 0.0), X(kTileDoubles);
+  cudaMemcpy(W.data(), dW, kTileDoubles * 8, cudaMemcpyDeviceToHost);
+  for (int j = 0; j < 64; ++j) { double d = T[j * 64 + j]; for (int m = 0; m < j; ++m) d -= L[j * 64 + m] * L[j * 64 + m]; d = std::sqrt(d); L[j * 64 + j] = d;
+    for (int r = j + 1; r < 64; ++r) { double s = T[j * 64 + r]; for (int m = 0; m < j; ++m) s -= L[r * 64 + m] * L[j * 64 + m]; L[r * 64 + j] = s / d; } }
+  double err = 0; for (int r = 0; r < 64; ++r) for (int c = 0; c < 64; ++c) { double s = 0; for (int m = 0; m < 64; ++m) s += W[m * 64 + r] * L[m * 64 + c]; err = std::fmax(err, std::fabs(s - (r == c))); }
+  printf("max |W L - I| = %.3e\n", err);
+  if (na) { cudaMemcpy(X.data(), dT + kTileDoubles, kTileDoubles * 8, cudaMemcpyDeviceToHost); double e2 = 0;
+    for (int r = 0; r < 64; ++r) for (int c = 0; c < 64; ++c) { double s = 0; for (int m = 0; m <= c; ++m) s += X[m * 64 + r] * L[c * 64 + m]; e2 = std::fmax(e2, std::fabs(s - T[kTileDoubles + c * 64 + r])); }
+    printf("max |L10 Lkk^T - A10| = %.3e\n", e2); }
+#ifdef PANEL_PROF
+  { long long pr[80]; cudaMemcpyFromSymbol(pr, g_panel_prof, sizeof(pr));
+    printf("start->step0 %lld, steps:", pr[0] - pr[70]); for (int j = 4; j <= 64; j += 4) printf(" %lld", pr[j] - pr[j - 4]); printf(", epilogue %lld\n", pr[65] - pr[64]);
+    printf("step 5: diag block %lld cycles; observer: barrier1->end of (b) %lld, barrier2 wait %lld, (c) %lld\n", pr[71], pr[72] - pr[20], pr[73] - pr[72], pr[74] - pr[73]); }
+#endif
+  LMState hs; cudaMemcpy(&hs, dst, sizeof(hs), cudaMemcpyDeviceToHost); printf("lin_fail %d, cuda: %s\n", hs.lin_fail, cudaGetErrorString(cudaGetLastError()));
+  return 0;
+}
