@@ -91,7 +91,7 @@ struct bsnls_handle {
       d_gf_roff, d_pair_a, d_pair_b, d_pair_ptr, d_item_i, d_item_j, d_fg_ptr, d_fg_fac, d_fg_lb, d_gd_row, d_gd_col,
       d_gd_ptr, d_gd_fac, d_gd_bi, d_gd_bj, d_is_pose, d_bsr_rowptr, d_bsr_col, d_diag_slot, d_pair_slot, d_gd_slot,
       d_pcg_x, d_pcg_r, d_pcg_z, d_pcg_p, d_pcg_Ap, d_pcg_Minv, d_pcg_part;
-  DevMem d_lmz, d_invd, d_Sdense, d_gradL, d_colsqL, d_gradS, d_colsqS;
+  DevMem d_lmz, d_gradL, d_colsqL, d_gradS, d_colsqS;
   DevMem d_x, d_xc, d_x0, d_Jrec, d_Vrec, d_minv, d_grad, d_colsq, d_scale, d_y, d_yf, d_rhs, d_S, d_poseH, d_gfJ,
       d_gfR, d_cost_part, d_cand_part, d_model_part, d_step_part, d_candsq_part, d_gsq_part, d_gmax_part, d_xsq_part,
       d_red, d_state, d_recs;
@@ -200,11 +200,6 @@ void EnqueueLandmark(bsnls_handle* h, const Options& o) {  // phase B
   switch (h->G) { case 4: LaunchLandmark<4>(h, o); break; case 8: LaunchLandmark<8>(h, o); break;
                   case 16: LaunchLandmark<16>(h, o); break; default: LaunchLandmark<32>(h, o); }
 }
-__global__ void zero_f_kernel(DeviceProblem P, double* gradL, double* colsqL, const LMState* st) {
-  if (!gate_jac(st)) return;
-  const int j = blockIdx.x * 256 + threadIdx.x;
-  if (j < P.nf_dim) { gradL[j] = 0.0; colsqL[j] = 0.0; }
-}
 int EnqueueGradient(bsnls_handle* h, const Options& o) {  // phase C: gradient, column norms, scale, gradient norms
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
   if (h->np) LAUNCH(h, pose_reduce_kernel, BlocksFor(h->np * 27, 128), 128, P, h->d_pose_part.as<double>(), h->d_poseH.as<double>(), h->d_gradL.as<double>(), h->d_colsqL.as<double>(), st);
@@ -284,29 +279,9 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     LAUNCH_SMEM(h, chol_tiny_kernel, 1, tiny_threads, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
     return;
   }
-  if (n <= kSmallMax) {  // sliding windows: factor + solve in one single-CTA launch
-    const size_t smem = sizeof(double) * ((size_t)kSmallMax * kNB + kSmallMax);
-    LAUNCH_SMEM(h, chol_small_kernel, 1, kSmallThreads, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
-    return;
-  }
-  // two-level right-looking blocking: outer panels of 128 columns are factored with 32-column steps whose tensor-core
-  // updates stay inside the panel; the rest of the matrix is then updated once with the whole 128-column panel
-  constexpr int kOuter = 128;
-  auto update = [&](int kbase, int kw, int cbase, int cend) {
-    const int Tc = (cend - cbase + 63) / 64, Tr = (n - cbase + 63) / 64;
-    if (Tc > 0 && Tr > 0) LAUNCH(h, chol_update_kernel, dim3(Tc, Tr), 128, Sd, n, kbase, kw, cbase, cend, st);
-  };
-  for (int J0 = 0; J0 < n; J0 += kOuter) {
-    const int W = std::min(kOuter, n - J0);
-    for (int jj = 0; jj < W; jj += kNB) {
-      const int j0 = J0 + jj, nb = std::min(kNB, n - j0), rest = n - j0 - nb;
-      LAUNCH(h, chol_diag_kernel, 1, 256, Sd, n, j0, h->d_invd.as<double>(), st);
-      if (rest > 0) LAUNCH(h, chol_trsm_kernel, BlocksFor(rest, 256), 256, Sd, n, j0, h->d_invd.as<double>(), st);
-      if (jj + kNB < W) update(j0, nb, j0 + kNB, J0 + W);
-    }
-    if (J0 + W < n) update(J0, W, J0 + W, n);
-  }
-  LAUNCH(h, chol_solve_kernel, 1, 1024, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
+  // sliding windows: factor + solve in one single-CTA launch (n <= kSmallMax; larger systems take the tile path above)
+  const size_t smem = sizeof(double) * ((size_t)kSmallMax * kNB + kSmallMax);
+  LAUNCH_SMEM(h, chol_small_kernel, 1, kSmallThreads, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
 }
 int EnqueueSparseSolve(bsnls_handle* h) {  // phase D2 (K7): cooperative PCG, result in yf
   PcgBuffers B{h->d_yf.as<double>(), h->d_pcg_r.as<double>(), h->d_pcg_z.as<double>(), h->d_pcg_p.as<double>(), h->d_pcg_Ap.as<double>(),
@@ -1012,7 +987,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(h->d_model_part.alloc(sizeof(double) * (h->nb_lm + h->ngf + 1)));
   CK(h->d_step_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_candsq_part.alloc(sizeof(double) * h->nb_act));
   CK(h->d_gsq_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_gmax_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_xsq_part.alloc(sizeof(double) * h->nb_act));
-  CK(h->d_red.alloc(sizeof(double) * 32)); CK(h->d_invd.alloc(sizeof(double) * 64)); CK(h->d_state.alloc(sizeof(LMState)));
+  CK(h->d_red.alloc(sizeof(double) * 32)); CK(h->d_state.alloc(sizeof(LMState)));
   CK(cudaMemcpyAsync(h->d_x.p, pr->block_values, sizeof(double) * off, cudaMemcpyHostToDevice, s));
   CK(cudaMemsetAsync(h->d_y.p, 0, sizeof(double) * ntan, s));
 

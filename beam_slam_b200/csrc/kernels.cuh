@@ -677,7 +677,7 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
   __shared__ int sO[kSyrkMaxStages];               // first observation of every stage of this chunk
   if (!gate_run(st)) return;
   const int c = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
-  const int ns = P.chunk_nslots[c], nrow = 6 * ns + 1, nt = (nrow + 7) >> 3, T = nt * (nt + 1) / 2, nrow8 = nt * 8;
+  const int ns = P.chunk_nslots[c], nrow = 6 * ns + 1, nt = (nrow + 7) >> 3, nrow8 = nt * 8;
   const int l_begin = P.chunk_begin[c], l_end = P.chunk_end[c];
   const int nst = (l_end - l_begin + kSyrkStageLm - 1) / kSyrkStageLm;
   double* const buf0 = Wsm; double* const buf1 = Wsm + nrow8 * kSyrkLD;
@@ -963,25 +963,11 @@ __global__ void __launch_bounds__(256) finish_system_kernel(DeviceProblem P, con
   rhs[j] = (is_pose_entry[j] ? rhs[j] : 0.0) + grad[P.ne_dim + j];
 }
 
-// Expand the block-sparse S into the dense lower triangle the Cholesky factors (mid-size systems are assembled
-// block-sparse, which avoids clearing and re-reading n^2 doubles in the assembly, and factored densely).
-__global__ void __launch_bounds__(256) bsr_to_dense_kernel(DeviceProblem P, const double* __restrict__ Sb, double* __restrict__ Sd, const LMState* st) {
-  if (!gate_run(st)) return;
-  const long long e = (long long)blockIdx.x * 256 + threadIdx.x;
-  if (e >= P.nnzb * 9) return;
-  const int blk = (int)(e / 9), w = (int)(e - 9LL * blk), i = w / 3, j = w - 3 * i;
-  // row of this block: binary search in rowptr
-  int lo = 0, hi = P.nf;
-  while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (P.bsr_rowptr[mid] <= blk) lo = mid; else hi = mid; }
-  const int r = 3 * lo + i, c = 3 * P.bsr_col[blk] + j;
-  if (r >= c) Sd[(size_t)c * P.nf_dim + r] = Sb[e];
-}
 
 // ===================================================================================================
-// K8: dense FP64 Cholesky of the reduced system (column-major, lower), blocked right-looking, NB = 32.
-// chol_panel: every CTA factors the 32x32 diagonal block redundantly in shared memory (deterministic), CTA 0
-// writes it back, each CTA then solves its 64 rows of the panel. chol_update: trailing update with DMMA
-// (mma.sync.m8n8k4.f64), 64x64 tiles, operands staged in shared memory.
+// K8: dense FP64 Cholesky of the reduced system for sliding windows (column-major, lower), blocked right-looking with
+// NB = 32, entirely inside one CTA: chol_tiny_kernel (n <= 160, the whole matrix in shared memory) and chol_small_kernel
+// (n <= 512, one panel in shared memory at a time). Larger systems go to the tile-sparse Cholesky (tile_chol.cuh).
 // ===================================================================================================
 constexpr int kNB = 32;
 // Cholesky of the nb x nb diagonal block held in shared memory, all NT threads of the CTA cooperating: step k scales
@@ -1000,104 +986,6 @@ __device__ __forceinline__ void chol_diag_block(double (*D)[kNB + 1], double* in
     for (int e = tid; e < m * m; e += NT) { const int i = k + 1 + e / m, j = k + 1 + e % m; if (i >= j) D[i][j] -= D[i][k] * D[j][k]; }
     __syncthreads();
   }
-}
-// Panel step for larger systems, two launches so that no CTA can read a diagonal block another CTA is overwriting:
-// chol_diag_kernel (1 CTA) factors the diagonal block in place and leaves 1/L[k][k] in invd_out; chol_trsm_kernel
-// solves the rows below it, one row per thread.
-__global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ S, int n, int j0, double* __restrict__ invd_out, LMState* st) {
-  __shared__ double D[kNB][kNB + 1];
-  __shared__ double invd[kNB];
-  __shared__ int failed;
-  if (!gate_run(st) || st->lin_fail) return;   // single CTA; lin_fail is written only after the last barrier
-  const int nb = min(kNB, n - j0), tid = threadIdx.x;
-  if (tid == 0) failed = 0;
-  for (int e = tid; e < kNB * kNB; e += 256) {
-    const int r = e % kNB, c = e / kNB;
-    D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(j0 + c) * n + j0 + r] : 0.0;
-  }
-  __syncthreads();
-  chol_diag_block<256>(D, invd, nb, &failed);
-  for (int e = tid; e < kNB * kNB; e += 256) { const int r = e % kNB, c = e / kNB; if (r < nb && c < nb && r >= c) S[(size_t)(j0 + c) * n + j0 + r] = D[r][c]; }
-  if (tid < kNB) invd_out[tid] = tid < nb ? invd[tid] : 0.0;
-  if (failed && tid == 0) st->lin_fail = 1;
-}
-__global__ void __launch_bounds__(256) chol_trsm_kernel(double* __restrict__ S, int n, int j0, const double* __restrict__ invd_in, const LMState* st) {
-  __shared__ double D[kNB][kNB + 1];
-  __shared__ double invd[kNB];
-  if (!gate_run(st) || st->lin_fail) return;   // both written by earlier kernels only
-  const int nb = min(kNB, n - j0), tid = threadIdx.x;
-  for (int e = tid; e < kNB * kNB; e += 256) {
-    const int r = e % kNB, c = e / kNB;
-    D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(j0 + c) * n + j0 + r] : 0.0;
-  }
-  if (tid < kNB) invd[tid] = invd_in[tid];
-  __syncthreads();
-  const int row = j0 + nb + blockIdx.x * 256 + tid;
-  if (row >= n) return;
-  double xv[kNB];
-#pragma unroll
-  for (int c = 0; c < kNB; ++c) {
-    if (c < nb) {
-      double a = S[(size_t)(j0 + c) * n + row];
-#pragma unroll
-      for (int p = 0; p < kNB; ++p) if (p < c) a -= xv[p] * D[c][p];
-      xv[c] = a * invd[c];
-      S[(size_t)(j0 + c) * n + row] = xv[c];
-    } else xv[c] = 0.0;
-  }
-}
-// Trailing update C -= L_panel L_panel^T with the FP64 tensor cores: columns [cbase, cend), rows >= column, where the
-// panel is L[:, kbase : kbase + kw] (kw a multiple of 4, <= 128). 64x64 tiles of C, the K dimension is walked in chunks of
-// 32 staged in shared memory (leading dimension padded to 36: conflict-free DMMA fragment loads). With kw = 128 (outer
-// panels of the two-level blocking) the update does 4x the flops per byte of S moved.
-__global__ void __launch_bounds__(128) chol_update_kernel(double* __restrict__ S, int n, int kbase, int kw, int cbase, int cend,
-                                                          const LMState* st) {
-  if (!gate_run(st) || st->lin_fail) return;
-  const int ti = blockIdx.y, tj = blockIdx.x;
-  if (ti < tj) return;
-  constexpr int LD = kNB + 4;
-  __shared__ double As[64 * LD];
-  __shared__ double Bs[64 * LD];
-  const int i0 = cbase + ti * 64, c0 = cbase + tj * 64, tid = threadIdx.x;
-  const int warp = tid >> 5, lane = tid & 31, gr = lane >> 2, gc = lane & 3;
-  // warp w owns row band [16w, 16w+16) x all 64 columns = 2 x 8 subtiles of 8x8
-  double acc[2][8][2];
-#pragma unroll
-  for (int a = 0; a < 2; ++a)
-#pragma unroll
-    for (int b = 0; b < 8; ++b) { acc[a][b][0] = 0.0; acc[a][b][1] = 0.0; }
-  for (int kc = 0; kc < kw; kc += kNB) {
-    const int kn = min(kNB, kw - kc);
-    for (int e = tid; e < 64 * kNB; e += 128) {
-      const int r = e % 64, p = e / 64;
-      const bool kp = p < kn;
-      As[r * LD + p] = (kp && i0 + r < n) ? S[(size_t)(kbase + kc + p) * n + i0 + r] : 0.0;
-      Bs[r * LD + p] = (kp && c0 + r < n) ? S[(size_t)(kbase + kc + p) * n + c0 + r] : 0.0;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int k0 = 0; k0 < kNB; k0 += 4) {
-      double af[2], bf[8];
-#pragma unroll
-      for (int a = 0; a < 2; ++a) af[a] = As[(16 * warp + 8 * a + gr) * LD + k0 + gc];
-#pragma unroll
-      for (int b = 0; b < 8; ++b) bf[b] = Bs[(8 * b + gr) * LD + k0 + gc];
-#pragma unroll
-      for (int a = 0; a < 2; ++a)
-#pragma unroll
-        for (int b = 0; b < 8; ++b) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
-    }
-    __syncthreads();
-  }
-#pragma unroll
-  for (int a = 0; a < 2; ++a)
-#pragma unroll
-    for (int b = 0; b < 8; ++b)
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int row = i0 + 16 * warp + 8 * a + gr, col = c0 + 8 * b + 2 * gc + h;
-        if (row < n && col < cend && row >= col) S[(size_t)col * n + row] -= acc[a][b][h];
-      }
 }
 // Tiny reduced systems (n <= 160: the 10-keyframe VIO window): the whole matrix lives in shared memory for the
 // factorisation and both triangular solves; one launch, one CTA.
@@ -1273,58 +1161,6 @@ __global__ void __launch_bounds__(kSmallThreads) chol_small_kernel(double* __res
   }
 }
 
-// Triangular solves L y = b, L^T x = y with the factor in the lower triangle of S (single CTA, blocked by 32).
-__global__ void __launch_bounds__(1024) chol_solve_kernel(const double* __restrict__ S, int n, const double* __restrict__ rhs,
-                                                          double* __restrict__ y, LMState* st) {
-  if (!gate_run(st) || st->lin_fail) return;
-  __shared__ double D[kNB][kNB + 1];
-  __shared__ double xs[kNB];
-  const int tid = threadIdx.x;
-  for (int i = tid; i < n; i += 1024) y[i] = rhs[i];
-  __syncthreads();
-  for (int jb = 0; jb < n; jb += kNB) {  // forward
-    const int nb = min(kNB, n - jb);
-    { const int r = tid % kNB, c = tid / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(jb + c) * n + jb + r] : 0.0; }
-    __syncthreads();
-    if (tid < 32) {
-      double b = tid < nb ? y[jb + tid] : 0.0;
-      for (int k = 0; k < nb; ++k) {
-        const double yk = __shfl_sync(0xffffffffu, b, k) / D[k][k];
-        if (tid == k) b = yk; else if (tid > k) b -= D[tid][k] * yk;
-      }
-      if (tid < nb) { y[jb + tid] = b; xs[tid] = b; }
-    }
-    __syncthreads();
-    for (int i = jb + nb + tid; i < n; i += 1024) {
-      double a = y[i];
-      for (int k = 0; k < nb; ++k) a -= S[(size_t)(jb + k) * n + i] * xs[k];
-      y[i] = a;
-    }
-    __syncthreads();
-  }
-  const int nblk = (n + kNB - 1) / kNB;
-  for (int bb = nblk - 1; bb >= 0; --bb) {  // backward
-    const int jb = bb * kNB, nb = min(kNB, n - jb);
-    { const int r = tid % kNB, c = tid / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(jb + c) * n + jb + r] : 0.0; }
-    __syncthreads();
-    if (tid < 32) {
-      double b = tid < nb ? y[jb + tid] : 0.0;
-      for (int k = nb - 1; k >= 0; --k) {
-        const double xk = __shfl_sync(0xffffffffu, b, k) / D[k][k];
-        if (tid == k) b = xk; else if (tid < k) b -= D[k][tid] * xk;
-      }
-      if (tid < nb) { y[jb + tid] = b; xs[tid] = b; }
-    }
-    __syncthreads();
-    for (int i = tid; i < jb; i += 1024) {
-      double a = y[i];
-      const double* col = S + (size_t)i * n + jb;
-      for (int k = 0; k < nb; ++k) a -= col[k] * xs[k];
-      y[i] = a;
-    }
-    __syncthreads();
-  }
-}
 
 // ===================================================================================================
 // K7: preconditioned conjugate gradients on the block-sparse reduced system S y = rhs (3x3-block CSR, full
