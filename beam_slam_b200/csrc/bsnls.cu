@@ -273,10 +273,11 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     LAUNCH(h, tile_solve_kernel, 1, 1024, TC, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
     return;
   }
-  if (n <= kTinyMax && !h->sparse) {  // whole matrix in shared memory
+  if (n <= kRbMaxN && !h->sparse) {  // whole matrix in registers, one CTA
+    static const bool old_tiny = std::getenv("BSNLS_TINY_SMEM") != nullptr;   // shared-memory variant kept for comparison
+    if (!old_tiny) { LAUNCH(h, chol_reg_kernel, 1, kRbThreads, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st); return; }
     const size_t smem = sizeof(double) * ((size_t)kTinyMax * (kTinyMax + 1) + 2 * kTinyMax);
-    static const int tiny_threads = [] { const char* e = std::getenv("BSNLS_TINY_THREADS"); const int v = e ? std::atoi(e) : 0; return (v >= 32 && v <= kTinyThreads && v % 32 == 0) ? v : kTinyThreads; }();
-    LAUNCH_SMEM(h, chol_tiny_kernel, 1, tiny_threads, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
+    LAUNCH_SMEM(h, chol_tiny_kernel, 1, kTinyThreads, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
     return;
   }
   // sliding windows: factor + solve in one single-CTA launch (n <= kSmallMax; larger systems take the tile path above)

@@ -1036,6 +1036,140 @@ __global__ void __launch_bounds__(kTinyThreads) chol_tiny_kernel(const double* _
   for (int i = tid; i < n; i += NT) y[i] = b[i];
 }
 
+// Register-blocked variant for n <= 160 (a 10-keyframe VIO window has 150 unknowns): the lower triangle lives in
+// registers as 4x4 blocks, two per thread, plus one extra block row that carries the right-hand side, so the forward
+// substitution happens inside the factorisation sweep. Four pivots per step and two barriers per step: the owner of
+// the diagonal block factors it and publishes the inverse of its 4x4 factor, the block column is multiplied by it and
+// published, every block to the right gets a rank-4 update. The backward substitution walks the block columns once
+// more (partial products of a column are combined by one warp). ~80 barriers instead of ~1000.
+constexpr int kRbMaxN = 160, kRbNB = kRbMaxN / 4, kRbThreads = 512, kRbMaxBlocks = kRbNB * (kRbNB + 3) / 2;
+struct RbBlock { double a[4][4]; int bi, bj; };   // bj < 0: unused slot
+__device__ __forceinline__ void rb_panel(RbBlock& B, int jb, int nb, const double2* __restrict__ sLi, double2 (*sPan)[kRbNB + 4], double* ys) {
+  if (B.bj != jb || B.bi <= jb) return;
+  double Li[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const double2 u0 = sLi[2 * i], u1 = sLi[2 * i + 1]; Li[i][0] = u0.x; Li[i][1] = u0.y; Li[i][2] = u1.x; Li[i][3] = u1.y; }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    double l[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) { double acc = 0.0;
+#pragma unroll
+      for (int m = 0; m <= c; ++m) acc += B.a[i][m] * Li[c][m];
+      l[c] = acc; }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) B.a[i][c] = l[c];
+    sPan[2 * i][B.bi] = make_double2(l[0], l[1]); sPan[2 * i + 1][B.bi] = make_double2(l[2], l[3]);
+  }
+  if (B.bi == nb) {   // the right-hand-side row: y of this block column is final
+#pragma unroll
+    for (int c = 0; c < 4; ++c) ys[4 * jb + c] = B.a[0][c];
+  }
+}
+__device__ __forceinline__ void rb_update(RbBlock& B, int jb, const double2 (*sPan)[kRbNB + 4]) {
+  if (B.bj <= jb) return;
+  double Pr[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const double2 u0 = sPan[2 * i][B.bi], u1 = sPan[2 * i + 1][B.bi]; Pr[i][0] = u0.x; Pr[i][1] = u0.y; Pr[i][2] = u1.x; Pr[i][3] = u1.y; }
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const double2 u0 = sPan[2 * c][B.bj], u1 = sPan[2 * c + 1][B.bj];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) B.a[i][c] -= Pr[i][0] * u0.x + Pr[i][1] * u0.y + Pr[i][2] * u1.x + Pr[i][3] * u1.y;
+  }
+}
+__device__ __forceinline__ void rb_back(const RbBlock& B, int jb, int nb, const double* xs, double (*part)[4]) {
+  if (B.bj != jb || B.bi <= jb || B.bi >= nb) return;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) part[B.bi][c] = B.a[0][c] * xs[4 * B.bi] + B.a[1][c] * xs[4 * B.bi + 1] + B.a[2][c] * xs[4 * B.bi + 2] + B.a[3][c] * xs[4 * B.bi + 3];
+}
+__global__ void __launch_bounds__(kRbThreads, 1) chol_reg_kernel(const double* __restrict__ S, int n, const double* __restrict__ rhs,
+                                                                 double* __restrict__ y, LMState* st) {
+  __shared__ double2 sPan[8][kRbNB + 4];       // the block column, element-major: sPan[e][bi] (rows of a warp's blocks are adjacent)
+  __shared__ double2 sLiAll[kRbNB][8];         // inverse of every 4x4 diagonal factor, row-major
+  __shared__ double xs[kRbMaxN + 4], ys[kRbMaxN + 4];
+  __shared__ double part[kRbNB + 1][4];
+  __shared__ unsigned short sBlk[kRbMaxBlocks];
+  __shared__ int failed;
+  if (!gate_run(st) || st->lin_fail) return;
+  const int tid = threadIdx.x, nb = (n + 3) >> 2, total = nb * (nb + 3) / 2;
+  if (tid == 0) failed = 0;
+  // blocks in column-major order: column bj holds rows bj..nb (row nb = the right-hand side)
+  if (tid < nb) { int o = tid * (nb + 1) - tid * (tid - 1) / 2; for (int bi = tid; bi <= nb; ++bi) sBlk[o++] = (unsigned short)(bi | (tid << 8)); }
+  __syncthreads();
+  RbBlock B0, B1;
+  auto load = [&](RbBlock& B, int L) {
+    if (L >= total) { B.bi = -1; B.bj = -1; return; }
+    B.bi = sBlk[L] & 255; B.bj = sBlk[L] >> 8;
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = 4 * B.bi + i, cc = 4 * B.bj + c;
+        double v;
+        if (B.bi == nb) v = (i == 0 && cc < n) ? rhs[cc] : 0.0;
+        else if (r < n && cc < n) v = r >= cc ? S[(size_t)cc * n + r] : 0.0;
+        else v = r == cc ? 1.0 : 0.0;     // padding up to a multiple of four
+        B.a[i][c] = v;
+      }
+  };
+  load(B0, tid); load(B1, tid + kRbThreads);
+  bool bad = false;
+  auto diag = [&](RbBlock& B, int jb) {
+    if (B.bi != jb || B.bj != jb) return;
+    const double r0 = rsqrt(B.a[0][0]);
+    const double l10 = B.a[1][0] * r0, l20 = B.a[2][0] * r0, l30 = B.a[3][0] * r0;
+    const double d1 = B.a[1][1] - l10 * l10, r1 = rsqrt(d1);
+    const double l21 = (B.a[2][1] - l20 * l10) * r1, l31 = (B.a[3][1] - l30 * l10) * r1;
+    const double d2 = B.a[2][2] - l20 * l20 - l21 * l21, r2 = rsqrt(d2);
+    const double l32 = (B.a[3][2] - l30 * l20 - l31 * l21) * r2;
+    const double d3 = B.a[3][3] - l30 * l30 - l31 * l31 - l32 * l32, r3 = rsqrt(d3);
+    bad = bad || !(B.a[0][0] > 0.0) || !(d1 > 0.0) || !(d2 > 0.0) || !(d3 > 0.0);
+    const double i10 = -l10 * r0 * r1, i21 = -l21 * r1 * r2, i32 = -l32 * r2 * r3;
+    const double i20 = -(l20 * r0 + l21 * i10) * r2, i31 = -(l31 * r1 + l32 * i21) * r3;
+    const double i30 = -(l30 * r0 + l31 * i10 + l32 * i20) * r3;
+    double2* o = sLiAll[jb];
+    o[0] = make_double2(r0, 0.0); o[1] = make_double2(0.0, 0.0); o[2] = make_double2(i10, r1); o[3] = make_double2(0.0, 0.0);
+    o[4] = make_double2(i20, i21); o[5] = make_double2(r2, 0.0); o[6] = make_double2(i30, i31); o[7] = make_double2(i32, r3);
+  };
+  for (int jb = 0; jb < nb; ++jb) {
+    diag(B0, jb); diag(B1, jb);
+    __syncthreads();
+    rb_panel(B0, jb, nb, sLiAll[jb], sPan, ys); rb_panel(B1, jb, nb, sLiAll[jb], sPan, ys);
+    __syncthreads();
+    rb_update(B0, jb, sPan); rb_update(B1, jb, sPan);
+  }
+  if (bad) failed = 1;
+  __syncthreads();
+  if (failed) { if (tid == 0) st->lin_fail = 1; return; }
+  // backward substitution: x_jb = Li^T (y_jb - sum_{bi > jb} L(bi,jb)^T x_bi)
+  for (int jb = nb - 1; jb >= 0; --jb) {
+    rb_back(B0, jb, nb, xs, part); rb_back(B1, jb, nb, xs, part);
+    __syncthreads();
+    if (tid < 32) {
+      double v[4] = {0.0, 0.0, 0.0, 0.0};
+      for (int bi = jb + 1 + tid; bi < nb; bi += 32) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) v[c] += part[bi][c];
+      }
+#pragma unroll
+      for (int m = 1; m < 32; m <<= 1) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) v[c] += __shfl_xor_sync(0xffffffffu, v[c], m);
+      }
+      if (tid < 4) {   // lane m: x[m] = sum_{c >= m} Li[c][m] r[c]
+        const double* Li = reinterpret_cast<const double*>(sLiAll[jb]);
+        double x = 0.0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) if (c >= tid) x += Li[4 * c + tid] * (ys[4 * jb + c] - v[c]);
+        xs[4 * jb + tid] = x;
+      }
+    }
+    __syncthreads();
+  }
+  for (int i = tid; i < n; i += kRbThreads) y[i] = xs[i];
+}
+
 // Small reduced systems (n <= 512: the sliding windows): the whole factorisation and both triangular solves in ONE
 // single-CTA launch. The matrix stays in global memory (L2 resident, <= 2 MB); per 32-column panel the diagonal block
 // is factored by one warp in shared memory, the panel rows are solved one row per thread, the panel is staged in
