@@ -273,16 +273,8 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     LAUNCH(h, tile_solve_kernel, 1, 1024, TC, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
     return;
   }
-  if (n <= kRbMaxN && !h->sparse) {  // whole matrix in registers, one CTA
-    static const bool old_tiny = std::getenv("BSNLS_TINY_SMEM") != nullptr;   // shared-memory variant kept for comparison
-    if (!old_tiny) { LAUNCH(h, chol_reg_kernel, 1, kRbThreads, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st); return; }
-    const size_t smem = sizeof(double) * ((size_t)kTinyMax * (kTinyMax + 1) + 2 * kTinyMax);
-    LAUNCH_SMEM(h, chol_tiny_kernel, 1, kTinyThreads, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
-    return;
-  }
-  // sliding windows: factor + solve in one single-CTA launch (n <= kSmallMax; larger systems take the tile path above)
-  const size_t smem = sizeof(double) * ((size_t)kSmallMax * kNB + kSmallMax);
-  LAUNCH_SMEM(h, chol_small_kernel, 1, kSmallThreads, smem, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
+  // sliding windows (n <= kRbMaxN): the whole matrix in registers, one CTA, factorisation and both substitutions
+  LAUNCH(h, chol_reg_kernel, 1, kRbThreads, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
 }
 int EnqueueSparseSolve(bsnls_handle* h) {  // phase D2 (K7): cooperative PCG, result in yf
   PcgBuffers B{h->d_yf.as<double>(), h->d_pcg_r.as<double>(), h->d_pcg_z.as<double>(), h->d_pcg_p.as<double>(), h->d_pcg_Ap.as<double>(),
@@ -392,8 +384,6 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
   if ((e = cudaFuncSetAttribute(tile_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * kPanelSmemDoubles))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(tile_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * 2 * kTS * kTLd))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chunk_accum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kChunkSmemBytes)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
-  if ((e = cudaFuncSetAttribute(chol_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kTinyMax * (kTinyMax + 1) + 2 * kTinyMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
-  if ((e = cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (kSmallMax * kNB + kSmallMax)))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   for (auto& ev : h->pev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   *out = h;
   return BSNLS_OK;
@@ -482,11 +472,11 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   if (nf_dim == 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "no non-landmark parameter blocks to solve for");
   // assembly layout and linear solver: small windows dense + dense; mid-size block-sparse assembly expanded into the
   // dense Cholesky; large (or on request) block-sparse + PCG
-  // assembly layout and linear solver: sliding windows (<= kSmallMax) dense storage + a single-CTA Cholesky; everything
+  // assembly layout and linear solver: sliding windows (<= kRbMaxN unknowns) dense storage + a single-CTA Cholesky; everything
   // larger is assembled block-sparse and factored by the tile-sparse Cholesky in a bandwidth-reducing order, unless the
   // iterative solver is requested or the fill of the tile factor is too large (decided after the symbolic step below)
   h->pcg = h->opt.linear_solver == BSNLS_LINEAR_ITERATIVE_SCHUR;
-  h->tiled = !h->pcg && nf_dim > kSmallMax;
+  h->tiled = !h->pcg && nf_dim > kRbMaxN;
   h->sparse = h->pcg || h->tiled;
 
   // ---- reprojection: poses, landmark-sorted observations ----

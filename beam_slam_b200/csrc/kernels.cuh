@@ -965,78 +965,10 @@ __global__ void __launch_bounds__(256) finish_system_kernel(DeviceProblem P, con
 
 
 // ===================================================================================================
-// K8: dense FP64 Cholesky of the reduced system for sliding windows (column-major, lower), blocked right-looking with
-// NB = 32, entirely inside one CTA: chol_tiny_kernel (n <= 160, the whole matrix in shared memory) and chol_small_kernel
-// (n <= 512, one panel in shared memory at a time). Larger systems go to the tile-sparse Cholesky (tile_chol.cuh).
+// K8: dense FP64 Cholesky of the reduced system for sliding windows (column-major, lower), one CTA. Larger systems go
+// to the tile-sparse Cholesky (tile_chol.cuh).
 // ===================================================================================================
-constexpr int kNB = 32;
-// Cholesky of the nb x nb diagonal block held in shared memory, all NT threads of the CTA cooperating: step k scales
-// column k, then every thread updates its share of the trailing entries (one barrier-separated rank-1 update per
-// step). invd[k] receives 1 / L[k][k]. Returns through *failed (shared) whether a pivot was not positive.
-template <int NT>
-__device__ __forceinline__ void chol_diag_block(double (*D)[kNB + 1], double* invd, int nb, int* failed) {
-  const int tid = threadIdx.x;
-  for (int k = 0; k < nb; ++k) {
-    if (tid == 0) { const double d = D[k][k]; if (!(d > 0.0)) *failed = 1; const double l = sqrt(d); D[k][k] = l; invd[k] = 1.0 / l; }
-    __syncthreads();
-    const double ik = invd[k];
-    for (int i = k + 1 + tid; i < nb; i += NT) D[i][k] *= ik;
-    __syncthreads();
-    const int m = nb - k - 1;   // trailing block is m x m, lower part only
-    for (int e = tid; e < m * m; e += NT) { const int i = k + 1 + e / m, j = k + 1 + e % m; if (i >= j) D[i][j] -= D[i][k] * D[j][k]; }
-    __syncthreads();
-  }
-}
-// Tiny reduced systems (n <= 160: the 10-keyframe VIO window): the whole matrix lives in shared memory for the
-// factorisation and both triangular solves; one launch, one CTA.
-constexpr int kTinyMax = 160, kTinyThreads = 512;
-__global__ void __launch_bounds__(kTinyThreads) chol_tiny_kernel(const double* __restrict__ S, int n, const double* __restrict__ rhs,
-                                                                 double* __restrict__ y, LMState* st) {
-  extern __shared__ __align__(16) double smem_dyn[];
-  __shared__ int failed;
-  if (!gate_run(st) || st->lin_fail) return;
-  const int NT = blockDim.x;   // launch-time choice: barrier cost grows with the warp count, update work shrinks
-  const int tid = threadIdx.x, ld = n | 1;   // odd leading dimension: column accesses are conflict-free
-  double* A = smem_dyn;                       // A[r * ld + c], lower triangle
-  double* inv = smem_dyn + (size_t)kTinyMax * (kTinyMax + 1);
-  double* b = inv + kTinyMax;
-  if (tid == 0) failed = 0;
-  for (int e = tid; e < n * n; e += NT) { const int r = e % n, c = e / n; if (r >= c) A[r * ld + c] = S[(size_t)c * n + r]; }
-  for (int i = tid; i < n; i += NT) b[i] = rhs[i];
-  __syncthreads();
-  for (int k = 0; k < n; ++k) {
-    if (tid == 0) { const double d = A[k * ld + k]; if (!(d > 0.0)) failed = 1; const double l = sqrt(d); A[k * ld + k] = l; inv[k] = 1.0 / l; }
-    __syncthreads();
-    const double ik = inv[k];
-    for (int i = k + 1 + tid; i < n; i += NT) A[i * ld + k] *= ik;
-    __syncthreads();
-    // rank-1 update of the trailing lower triangle: thread -> (row i, strip of columns)
-    for (int i = k + 1 + (tid >> 4); i < n; i += NT / 16) {
-      const double aik = A[i * ld + k];
-      for (int j = k + 1 + (tid & 15); j <= i; j += 16) A[i * ld + j] -= aik * A[j * ld + k];
-    }
-    __syncthreads();
-  }
-  if (failed) { if (tid == 0) st->lin_fail = 1; return; }
-  // L z = b (column sweep), then L^T y = z
-  for (int k = 0; k < n; ++k) {
-    if (tid == 0) b[k] *= inv[k];
-    __syncthreads();
-    const double zk = b[k];
-    for (int i = k + 1 + tid; i < n; i += NT) b[i] -= A[i * ld + k] * zk;
-    __syncthreads();
-  }
-  for (int k = n - 1; k >= 0; --k) {
-    if (tid == 0) b[k] *= inv[k];
-    __syncthreads();
-    const double xk = b[k];
-    for (int i = tid; i < k; i += NT) b[i] -= A[k * ld + i] * xk;
-    __syncthreads();
-  }
-  for (int i = tid; i < n; i += NT) y[i] = b[i];
-}
-
-// Register-blocked variant for n <= 160 (a 10-keyframe VIO window has 150 unknowns): the lower triangle lives in
+// n <= 160 (a 10-keyframe VIO window has 150 unknowns): the lower triangle lives in
 // registers as 4x4 blocks, two per thread, plus one extra block row that carries the right-hand side, so the forward
 // substitution happens inside the factorisation sweep. Four pivots per step and two barriers per step: the owner of
 // the diagonal block factors it and publishes the inverse of its 4x4 factor, the block column is multiplied by it and
@@ -1169,132 +1101,6 @@ __global__ void __launch_bounds__(kRbThreads, 1) chol_reg_kernel(const double* _
   }
   for (int i = tid; i < n; i += kRbThreads) y[i] = xs[i];
 }
-
-// Small reduced systems (n <= 512: the sliding windows): the whole factorisation and both triangular solves in ONE
-// single-CTA launch. The matrix stays in global memory (L2 resident, <= 2 MB); per 32-column panel the diagonal block
-// is factored by one warp in shared memory, the panel rows are solved one row per thread, the panel is staged in
-// shared memory and the trailing matrix is updated in 4x4 register micro-tiles.
-constexpr int kSmallMax = 512, kSmallThreads = 256;
-__global__ void __launch_bounds__(kSmallThreads) chol_small_kernel(double* __restrict__ S, int n, const double* __restrict__ rhs,
-                                                                   double* __restrict__ y, LMState* st) {
-  extern __shared__ __align__(16) double smem_dyn[];
-  __shared__ double D[kNB][kNB + 1];
-  __shared__ double xs[kNB];
-  __shared__ double invd[kNB];
-  __shared__ int failed;
-  if (!gate_run(st) || st->lin_fail) return;
-  constexpr int NT = kSmallThreads, LDR = kSmallMax;
-  const int tid = threadIdx.x;
-  double* Ls = smem_dyn;                                  // panel below the diagonal block, column-major: Ls[p * LDR + row]
-  double* invdiag = smem_dyn + (size_t)kNB * LDR;         // 1 / L[k][k] of the whole factor (n entries)
-  if (tid == 0) failed = 0;
-  for (int j0 = 0; j0 < n; j0 += kNB) {
-    const int nb = min(kNB, n - j0), r0 = j0 + nb, rest = n - r0;
-    for (int e = tid; e < kNB * kNB; e += NT) { const int r = e % kNB, c = e / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(j0 + c) * n + j0 + r] : 0.0; }
-    __syncthreads();
-    chol_diag_block<NT>(D, invd, nb, &failed);
-    if (tid < nb) invdiag[j0 + tid] = invd[tid];
-    for (int e = tid; e < kNB * kNB; e += NT) { const int r = e % kNB, c = e / kNB; if (r < nb && c < nb && r >= c) S[(size_t)(j0 + c) * n + j0 + r] = D[r][c]; }
-    // panel solve: one row per thread, result to global and to the shared panel (rows padded to a multiple of 4 with zeros)
-    const int rest4 = (rest + 3) & ~3;
-    for (int i = tid; i < rest4; i += NT) {
-      double xv[kNB];
-      const int ir = min(i, rest - 1);   // clamp so that the loads below are unconditional (issued together)
-#pragma unroll
-      for (int c = 0; c < kNB; ++c) xv[c] = S[(size_t)(j0 + min(c, nb - 1)) * n + r0 + ir];
-#pragma unroll
-      for (int c = 0; c < kNB; ++c) {
-        if (c < nb && i < rest) {
-          double a = xv[c];
-#pragma unroll
-          for (int p = 0; p < kNB; ++p) if (p < c) a -= xv[p] * D[c][p];
-          xv[c] = a * invd[c];
-          S[(size_t)(j0 + c) * n + r0 + i] = xv[c];
-        } else xv[c] = 0.0;
-        Ls[c * LDR + i] = xv[c];
-      }
-    }
-    __syncthreads();
-    // trailing update A[r0+i][r0+j] -= sum_p L[i][p] L[j][p], i >= j, in 4x4 register micro-tiles (vector loads)
-    const int mt = rest4 / 4, ntile = mt * (mt + 1) / 2;
-    for (int t = tid; t < ntile; t += NT) {
-      // t -> (ti >= tj) of the lower triangle
-      int ti = (int)((sqrt(8.0 * t + 1.0) - 1.0) * 0.5);
-      while ((ti + 1) * (ti + 2) / 2 <= t) ++ti;
-      while (ti * (ti + 1) / 2 > t) --ti;
-      const int tj = t - ti * (ti + 1) / 2;
-      double acc[4][4];
-#pragma unroll
-      for (int a = 0; a < 4; ++a)
-#pragma unroll
-        for (int b2 = 0; b2 < 4; ++b2) acc[a][b2] = 0.0;
-      const int i0 = 4 * ti, c0 = 4 * tj;
-      for (int p = 0; p < nb; ++p) {
-        const double2 la = *reinterpret_cast<const double2*>(Ls + p * LDR + i0), lb = *reinterpret_cast<const double2*>(Ls + p * LDR + i0 + 2);
-        const double2 ca = *reinterpret_cast<const double2*>(Ls + p * LDR + c0), cb = *reinterpret_cast<const double2*>(Ls + p * LDR + c0 + 2);
-        const double li[4] = {la.x, la.y, lb.x, lb.y}, lj[4] = {ca.x, ca.y, cb.x, cb.y};
-#pragma unroll
-        for (int a = 0; a < 4; ++a)
-#pragma unroll
-          for (int b2 = 0; b2 < 4; ++b2) acc[a][b2] += li[a] * lj[b2];
-      }
-#pragma unroll
-      for (int a = 0; a < 4; ++a)
-#pragma unroll
-        for (int b2 = 0; b2 < 4; ++b2) {
-          const int i = i0 + a, j = c0 + b2;
-          if (i < rest && j < rest && i >= j) S[(size_t)(r0 + j) * n + r0 + i] -= acc[a][b2];
-        }
-    }
-    __syncthreads();
-  }
-  if (failed) { if (tid == 0) st->lin_fail = 1; return; }   // `failed` is uniform after the last barrier
-  // triangular solves L z = rhs, L^T y = z
-  for (int i = tid; i < n; i += NT) y[i] = rhs[i];
-  __syncthreads();
-  for (int jb = 0; jb < n; jb += kNB) {
-    const int nb = min(kNB, n - jb);
-    for (int e = tid; e < kNB * kNB; e += NT) { const int r = e % kNB, c = e / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(jb + c) * n + jb + r] : 0.0; }
-    __syncthreads();
-    if (tid < 32) {
-      double b = tid < nb ? y[jb + tid] : 0.0;
-      for (int k = 0; k < nb; ++k) {
-        const double yk = __shfl_sync(0xffffffffu, b, k) * invdiag[jb + k];
-        if (tid == k) b = yk; else if (tid > k) b -= D[tid][k] * yk;
-      }
-      if (tid < nb) { y[jb + tid] = b; xs[tid] = b; }
-    }
-    __syncthreads();
-    for (int i = jb + nb + tid; i < n; i += NT) {
-      double a = y[i];
-      for (int k = 0; k < nb; ++k) a -= S[(size_t)(jb + k) * n + i] * xs[k];
-      y[i] = a;
-    }
-    __syncthreads();
-  }
-  for (int bb = (n + kNB - 1) / kNB - 1; bb >= 0; --bb) {
-    const int jb = bb * kNB, nb = min(kNB, n - jb);
-    for (int e = tid; e < kNB * kNB; e += NT) { const int r = e % kNB, c = e / kNB; D[r][c] = (r < nb && c < nb && r >= c) ? S[(size_t)(jb + c) * n + jb + r] : 0.0; }
-    __syncthreads();
-    if (tid < 32) {
-      double b = tid < nb ? y[jb + tid] : 0.0;
-      for (int k = nb - 1; k >= 0; --k) {
-        const double xk = __shfl_sync(0xffffffffu, b, k) * invdiag[jb + k];
-        if (tid == k) b = xk; else if (tid < k) b -= D[k][tid] * xk;
-      }
-      if (tid < nb) { y[jb + tid] = b; xs[tid] = b; }
-    }
-    __syncthreads();
-    for (int i = tid; i < jb; i += NT) {
-      double a = y[i];
-      const double* col = S + (size_t)i * n + jb;
-      for (int k = 0; k < nb; ++k) a -= col[k] * xs[k];
-      y[i] = a;
-    }
-    __syncthreads();
-  }
-}
-
 
 // ===================================================================================================
 // K7: preconditioned conjugate gradients on the block-sparse reduced system S y = rhs (3x3-block CSR, full
