@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <map>
 #include <string>
 #include <unordered_map>
@@ -70,6 +71,9 @@ struct bsnls_handle {
   std::vector<int> gd_row, gd_col;
   bool tiled = false; std::vector<int> f_api;   // tile-sparse Cholesky; internal f position -> API (program-order) position
   TileChol TC{}; std::vector<int> tc_col_ptr; DevMem d_tc_tile_off, d_tc_col_ptr, d_tc_col_rows, d_tc_T, d_tc_W, d_tc_b; size_t tc_T_bytes = 0;
+  struct TcLevel { int col_begin, ncols, pan_begin, npan, upd_begin, nupd, fw_begin, nfw; };   // one level of the elimination tree
+  std::vector<TcLevel> tc_levels;
+  DevMem d_tc_pan_k, d_tc_pan_x, d_tc_upd_ptr, d_tc_upd_dst, d_tc_upd_a, d_tc_upd_b, d_tc_fw_ptr, d_tc_fw_row, d_tc_fw_tail, d_tc_fw_src, d_tc_fw_k, d_tc_lev_cols;
   bool chunk_fma = false; int chunk_max_slots = 1; DevMem d_syrk_plan, d_chunk_tile_off, d_pp_toff, d_pp_info;
   int nchunks = 0; DevMem d_obs_slot, d_chunk_end, d_chunk_begin, d_chunk_nslots, d_chunk_part_off, d_chunk_cpart_off, d_pp_ptr, d_pp_off, d_pp_coff, d_part, d_cpart;
   bool sparse = false, pcg = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
@@ -264,13 +268,17 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     const TileChol& TC = h->TC;
     const size_t smem = sizeof(double) * 2 * kTS * kTLd;
     cudaMemsetAsync(TC.T, 0, h->tc_T_bytes, h->stream);
-    LAUNCH(h, bsr_to_tiles_kernel, (unsigned)((h->nnzb * 9 + kTS + 255) / 256), 256, h->P, TC, h->d_S.as<double>(), st);
-    for (int k = 0; k < TC.nT; ++k) {
-      const int a = h->tc_col_ptr[k + 1] - h->tc_col_ptr[k];
-      LAUNCH_SMEM(h, tile_panel_kernel, std::max(1, a), 256, sizeof(double) * kPanelSmemDoubles, TC, k, st);
-      if (a > 0) LAUNCH_SMEM(h, tile_syrk_kernel, a * (a + 1) / 2, 256, smem, TC, k, st);
+    LAUNCH(h, bsr_to_tiles_kernel, (unsigned)((h->nnzb * 9 + (long long)TC.nT * kTS + 255) / 256), 256, h->P, TC, h->d_S.as<double>(), st);
+    for (const auto& L : h->tc_levels) {   // factorisation, one level of the elimination tree at a time
+      LAUNCH_SMEM(h, tile_panel_kernel, L.npan, 256, sizeof(double) * kPanelSmemDoubles, TC, L.pan_begin, st);
+      if (L.nupd > 0) LAUNCH_SMEM(h, tile_syrk_kernel, L.nupd, 256, smem, TC, L.upd_begin, st);
     }
-    LAUNCH(h, tile_solve_kernel, 1, 1024, TC, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
+    // substitutions, level by level: forward (bottom-up), backward (top-down)
+    LAUNCH(h, tile_rhs_kernel, (TC.nT * kTS + 255) / 256, 256, TC, h->d_rhs.as<double>(), st);
+    LAUNCH(h, tile_fwd_first_kernel, h->tc_levels[0].ncols, 256, TC, h->tc_levels[0].col_begin, st);
+    for (const auto& L : h->tc_levels) if (L.nfw > 0) LAUNCH(h, tile_fwd_kernel, L.nfw, 256, TC, L.fw_begin, st);
+    for (size_t lv = h->tc_levels.size(); lv-- > 0;) LAUNCH(h, tile_bwd_kernel, h->tc_levels[lv].ncols, 256, TC, h->tc_levels[lv].col_begin, st);
+    LAUNCH(h, tile_out_kernel, (TC.n + 255) / 256, 256, TC, h->d_yf.as<double>(), st);
     return;
   }
   // sliding windows (n <= kRbMaxN): the whole matrix in registers, one CTA, factorisation and both substitutions
@@ -593,6 +601,44 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       bfs(probe2.back(), orderv, true);
     }
     std::reverse(orderv.begin(), orderv.end());
+    // Nested dissection at tile granularity on top of the RCM line. A tile holds kTileBlocks consecutive blocks; the
+    // line of tiles is cut in the middle by a separator as wide as the band (plus one endpoint of every long edge --
+    // loop closures -- that crosses the cut), the halves are ordered recursively and the separator goes last. Tile
+    // columns of different leaves are then independent, so the factorisation advances level by level of the
+    // elimination tree instead of one tile column at a time.
+    {
+      const int nTf = h->nf / kTileBlocks;            // full tiles; a partial last tile stays last
+      if (nTf > kNdLeaf) {
+        std::vector<int> pos(h->nf); for (int k = 0; k < h->nf; ++k) pos[orderv[k]] = k;
+        std::vector<std::vector<int>> tadj(nTf);
+        for (int u = 0; u < h->nf; ++u) {
+          const int tu = pos[u] / kTileBlocks; if (tu >= nTf) continue;
+          for (int v : adj[u]) { const int tv = pos[v] / kTileBlocks; if (tv < nTf && tv != tu) tadj[tu].push_back(tv); }
+        }
+        for (auto& v : tadj) { std::sort(v.begin(), v.end()); v.erase(std::unique(v.begin(), v.end()), v.end()); }
+        std::vector<int> torder, idx(nTf, -1); torder.reserve(nTf);
+        std::function<void(std::vector<int>&)> nd = [&](std::vector<int>& tl) {
+          const int m = (int)tl.size();
+          if (m <= kNdLeaf) { torder.insert(torder.end(), tl.begin(), tl.end()); return; }
+          for (int a = 0; a < m; ++a) idx[tl[a]] = a;
+          const int mid = m / 2; int w = 0;
+          for (int a = 0; a < mid; ++a) for (int v : tadj[tl[a]]) { const int b = idx[v]; if (b >= mid && b - a <= kNdShort) w = std::max(w, b - mid + 1); }
+          std::vector<char> insep(m, 0);
+          for (int a = mid; a < std::min(m, mid + w); ++a) insep[a] = 1;
+          for (int a = 0; a < mid; ++a) for (int v : tadj[tl[a]]) { const int b = idx[v]; if (b >= mid + w) insep[b] = 1; }
+          for (int a = 0; a < m; ++a) idx[tl[a]] = -1;
+          std::vector<int> left(tl.begin(), tl.begin() + mid), right, sep;
+          for (int a = mid; a < m; ++a) (insep[a] ? sep : right).push_back(tl[a]);
+          nd(left); nd(right); torder.insert(torder.end(), sep.begin(), sep.end());
+        };
+        std::vector<int> all(nTf); for (int t = 0; t < nTf; ++t) all[t] = t;
+        nd(all);
+        std::vector<int> order2; order2.reserve(h->nf);
+        for (int tp = 0; tp < nTf; ++tp) for (int j = 0; j < kTileBlocks; ++j) order2.push_back(orderv[torder[tp] * kTileBlocks + j]);
+        for (int k = nTf * kTileBlocks; k < h->nf; ++k) order2.push_back(orderv[k]);
+        orderv.swap(order2);
+      }
+    }
     for (int k = 0; k < h->nf; ++k) { rank[orderv[k]] = k; h->f_api[k] = orderv[k]; }
     for (int b = 0; b < nb; ++b) if (fpos[b] >= 0) fpos[b] = rank[fpos[b]];
   }
@@ -909,30 +955,32 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   }
   // work buffers
   const int ntan = ne_dim + nf_dim;
-  // ---- tile-sparse Cholesky: symbolic factorisation at 64x64-tile granularity (structure only; fixed per problem) ----
+  // ---- tile-sparse Cholesky: symbolic factorisation at tile granularity (structure only; fixed per problem) ----
+  // A tile holds kTileBlocks = 21 f-blocks (63 unknowns, the 64th row/column is an identity pad), so tiles never cut a block.
   std::vector<long long> tc_tile_off; std::vector<int> tc_col_rows; long long tc_tiles = 0;
-  h->tc_col_ptr.clear();
+  std::vector<int> tc_pan_k, tc_pan_x, tc_upd_ptr, tc_fw_ptr, tc_fw_row, tc_fw_tail, tc_lev_cols;
+  std::vector<long long> tc_upd_dst, tc_upd_a, tc_upd_b, tc_fw_src; std::vector<int> tc_fw_k;
+  h->tc_col_ptr.clear(); h->tc_levels.clear();
   if (h->tiled) {
-    const int nT = (nf_dim + kTS - 1) / kTS;
+    const int nT = (h->nf + kTileBlocks - 1) / kTileBlocks;
     std::vector<std::vector<int>> col(nT);     // non-zero tiles strictly below the diagonal, per tile column
     for (int r = 0; r < h->nf; ++r)
       for (int k = h->bsr_rowptr[r]; k < h->bsr_rowptr[r + 1]; ++k) {
         const int c = h->bsr_col[k];
-        if (c > r) continue;
-        // a 3x3 block may straddle tile boundaries: mark every tile it touches
-        for (int tr = (3 * r) / kTS; tr <= (3 * r + 2) / kTS; ++tr)
-          for (int tc = (3 * c) / kTS; tc <= (3 * c + 2) / kTS; ++tc) if (tr > tc) col[tc].push_back(tr);
+        if (c < r && r / kTileBlocks > c / kTileBlocks) col[c / kTileBlocks].push_back(r / kTileBlocks);
       }
+    std::vector<int> level(nT, 0);
     for (int k = 0; k < nT; ++k) {
       std::sort(col[k].begin(), col[k].end()); col[k].erase(std::unique(col[k].begin(), col[k].end()), col[k].end());
       // fill: eliminating tile column k couples all of its rows; it is enough to hand the rows below the first one to
       // that first row's column (elimination-tree parent): later columns propagate them further
-      if (!col[k].empty()) { const int par = col[k][0]; col[par].insert(col[par].end(), col[k].begin() + 1, col[k].end()); }
+      if (!col[k].empty()) { const int par = col[k][0]; col[par].insert(col[par].end(), col[k].begin() + 1, col[k].end()); level[par] = std::max(level[par], level[k] + 1); }
     }
     h->tc_col_ptr.assign(nT + 1, 0);
     for (int k = 0; k < nT; ++k) { h->tc_col_ptr[k + 1] = h->tc_col_ptr[k] + (int)col[k].size(); tc_tiles += 1 + (long long)col[k].size(); }
     const double tile_gb = (double)tc_tiles * kTileDoubles * 8 / 1e9;
-    if (std::getenv("BSNLS_DEBUG")) std::fprintf(stderr, "[bsnls] tile Cholesky: n %d, %d tile columns, %lld tiles (%.3f GB), dense lower would be %lld\n", nf_dim, nT, tc_tiles, tile_gb, (long long)nT * (nT + 1) / 2);
+    const int nlev = 1 + *std::max_element(level.begin(), level.end());
+    if (std::getenv("BSNLS_DEBUG")) std::fprintf(stderr, "[bsnls] tile Cholesky: n %d, %d tile columns in %d levels, %lld tiles (%.3f GB), dense lower would be %lld\n", nf_dim, nT, nlev, tc_tiles, tile_gb, (long long)nT * (nT + 1) / 2);
     if (tile_gb > 24.0 || (long long)nT * nT > (1LL << 28)) {
       if (h->opt.linear_solver == BSNLS_LINEAR_DENSE_SCHUR) return h->fail(BSNLS_ERR_UNSUPPORTED, "tile factor of the reduced system needs %.1f GB; use the iterative solver", tile_gb);
       h->tiled = false; h->pcg = true;     // AUTO: fall back to conjugate gradients
@@ -942,6 +990,39 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       for (int k = 0; k < nT; ++k) {
         tc_tile_off[(size_t)k * nT + k] = (t++) * kTileDoubles;
         for (int i : col[k]) { tc_tile_off[(size_t)i * nT + k] = (t++) * kTileDoubles; tc_col_rows.push_back(i); }
+      }
+      // level schedule: tile columns of one level of the elimination tree are independent. Per level: the panel CTAs
+      // (column, tile below the diagonal), the destination tiles of the updates with their source columns, and for
+      // the forward substitution the destination rows with their source tiles.
+      std::vector<std::vector<int>> by_level(nlev);
+      for (int k = 0; k < nT; ++k) by_level[level[k]].push_back(k);
+      tc_upd_ptr.push_back(0); tc_fw_ptr.push_back(0);
+      for (int lv = 0; lv < nlev; ++lv) {
+        bsnls_handle::TcLevel L{};
+        L.col_begin = (int)tc_lev_cols.size(); L.pan_begin = (int)tc_pan_k.size(); L.upd_begin = (int)tc_upd_ptr.size() - 1; L.fw_begin = (int)tc_fw_ptr.size() - 1;
+        struct U { long long key; int k; }; std::vector<U> us; struct F { int row, k; }; std::vector<F> fs;
+        for (int k : by_level[lv]) {
+          tc_lev_cols.push_back(k);
+          const int a = (int)col[k].size();
+          if (a == 0) { tc_pan_k.push_back(k); tc_pan_x.push_back(-1); }
+          for (int x = 0; x < a; ++x) { tc_pan_k.push_back(k); tc_pan_x.push_back(h->tc_col_ptr[k] + x); fs.push_back({col[k][x], k}); for (int y2 = 0; y2 <= x; ++y2) us.push_back({(long long)col[k][x] * nT + col[k][y2], k}); }
+        }
+        std::stable_sort(us.begin(), us.end(), [](const U& a2, const U& b2) { return a2.key < b2.key; });
+        for (size_t q = 0; q < us.size(); ++q) {
+          const int i = (int)(us[q].key / nT), j = (int)(us[q].key % nT), k = us[q].k;
+          if (q == 0 || us[q].key != us[q - 1].key) { if (q) tc_upd_ptr.push_back((int)tc_upd_a.size()); tc_upd_dst.push_back(tc_tile_off[(size_t)i * nT + j]); }
+          tc_upd_a.push_back(tc_tile_off[(size_t)i * nT + k]); tc_upd_b.push_back(tc_tile_off[(size_t)j * nT + k]);
+        }
+        if (!us.empty()) tc_upd_ptr.push_back((int)tc_upd_a.size());
+        std::stable_sort(fs.begin(), fs.end(), [](const F& a2, const F& b2) { return a2.row < b2.row; });
+        for (size_t q = 0; q < fs.size(); ++q) {
+          if (q == 0 || fs[q].row != fs[q - 1].row) { if (q) tc_fw_ptr.push_back((int)tc_fw_src.size()); tc_fw_row.push_back(fs[q].row); tc_fw_tail.push_back(level[fs[q].row] == lv + 1 ? 1 : 0); }
+          tc_fw_src.push_back(tc_tile_off[(size_t)fs[q].row * nT + fs[q].k]); tc_fw_k.push_back(fs[q].k);
+        }
+        if (!fs.empty()) tc_fw_ptr.push_back((int)tc_fw_src.size());
+        L.ncols = (int)tc_lev_cols.size() - L.col_begin; L.npan = (int)tc_pan_k.size() - L.pan_begin;
+        L.nupd = (int)tc_upd_ptr.size() - 1 - L.upd_begin; L.nfw = (int)tc_fw_ptr.size() - 1 - L.fw_begin;
+        h->tc_levels.push_back(L);
       }
     }
   }
@@ -955,8 +1036,16 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(h->d_scale.alloc(sizeof(double) * ntan)); CK(h->d_y.alloc(sizeof(double) * ntan)); CK(h->d_yf.alloc(sizeof(double) * nf_dim));
   CK(h->d_rhs.alloc(sizeof(double) * nf_dim)); CK(h->d_S.alloc(sizeof(double) * (h->sparse ? (size_t)h->nnzb * 9 : (size_t)nf_dim * nf_dim)));
   if (h->tiled) {
-    const int nT = (nf_dim + kTS - 1) / kTS;
+    const int nT = (h->nf + kTileBlocks - 1) / kTileBlocks;
     if (tc_col_rows.empty()) tc_col_rows.push_back(0);
+    if (tc_upd_dst.empty()) { tc_upd_dst.push_back(0); tc_upd_a.push_back(0); tc_upd_b.push_back(0); }
+    if (tc_fw_row.empty()) { tc_fw_row.push_back(0); tc_fw_tail.push_back(0); tc_fw_src.push_back(0); tc_fw_k.push_back(0); }
+    CK(upload(h->d_tc_pan_k, tc_pan_k, s)); CK(upload(h->d_tc_pan_x, tc_pan_x, s)); CK(upload(h->d_tc_upd_ptr, tc_upd_ptr, s)); CK(upload(h->d_tc_upd_dst, tc_upd_dst, s));
+    CK(upload(h->d_tc_upd_a, tc_upd_a, s)); CK(upload(h->d_tc_upd_b, tc_upd_b, s)); CK(upload(h->d_tc_fw_ptr, tc_fw_ptr, s)); CK(upload(h->d_tc_fw_row, tc_fw_row, s));
+    CK(upload(h->d_tc_fw_tail, tc_fw_tail, s)); CK(upload(h->d_tc_fw_src, tc_fw_src, s)); CK(upload(h->d_tc_fw_k, tc_fw_k, s)); CK(upload(h->d_tc_lev_cols, tc_lev_cols, s));
+    h->TC.pan_k = h->d_tc_pan_k.as<int>(); h->TC.pan_x = h->d_tc_pan_x.as<int>(); h->TC.upd_ptr = h->d_tc_upd_ptr.as<int>(); h->TC.upd_dst = h->d_tc_upd_dst.as<long long>();
+    h->TC.upd_a = h->d_tc_upd_a.as<long long>(); h->TC.upd_b = h->d_tc_upd_b.as<long long>(); h->TC.fw_ptr = h->d_tc_fw_ptr.as<int>(); h->TC.fw_row = h->d_tc_fw_row.as<int>();
+    h->TC.fw_tail = h->d_tc_fw_tail.as<int>(); h->TC.fw_src = h->d_tc_fw_src.as<long long>(); h->TC.fw_k = h->d_tc_fw_k.as<int>(); h->TC.lev_cols = h->d_tc_lev_cols.as<int>();
     CK(upload(h->d_tc_tile_off, tc_tile_off, s)); CK(upload(h->d_tc_col_ptr, h->tc_col_ptr, s)); CK(upload(h->d_tc_col_rows, tc_col_rows, s));
     h->tc_T_bytes = sizeof(double) * kTileDoubles * (size_t)tc_tiles;
     CK(h->d_tc_T.alloc(h->tc_T_bytes)); CK(h->d_tc_W.alloc(sizeof(double) * kTileDoubles * (size_t)nT)); CK(h->d_tc_b.alloc(sizeof(double) * kTS * (size_t)nT));

@@ -1,20 +1,27 @@
 // Tile-sparse FP64 Cholesky of the reduced system (K8 for everything larger than a sliding window).
 //
 // The reduced camera system of a trajectory is banded once poses are ordered along the trajectory (plus a few long
-// rows per loop closure). It is stored as 64x64 tiles, only those that are structurally non-zero after a symbolic
-// factorisation at tile granularity (host, set_problem), and factored right-looking one tile column at a time:
+// rows per loop closure). It is stored as 64x64 tiles (21 f-blocks = 63 unknowns + one identity pad row each), only
+// those that are structurally non-zero after a symbolic factorisation at tile granularity (host, set_problem).
+// The tile order is a nested dissection of the band, so tile columns on one level of the elimination tree are
+// independent; the right-looking factorisation advances one LEVEL per launch pair:
 //   panel  potrf of the diagonal tile together with W = L_kk^-1, then L(i,k) = A(i,k) W^T as a tile product
-//          (one CTA per non-zero tile below the diagonal, each factoring the diagonal tile redundantly)
-//   syrk   A(i,j) -= L(i,k) L(j,k)^T                                        (one CTA per pair of non-zero tiles)
-// The two products run on the FP64 tensor cores (mma.sync m8n8k4). The launch sequence depends on the structure only,
-// so it is fixed per problem. Replaces SuiteSparse/Eigen sparse Cholesky inside ceres' SPARSE_SCHUR.
+//          (one CTA per non-zero tile below the diagonal of every column of the level, each factoring the diagonal
+//          tile redundantly)
+//   syrk   A(i,j) -= sum_k L(i,k) L(j,k)^T over the level's columns k (one CTA per destination tile, fixed k order)
+// and so do the two substitutions. The tile products run on the FP64 tensor cores (mma.sync m8n8k4). The launch
+// sequence depends on the structure only, so it is fixed per problem. Replaces SuiteSparse/Eigen sparse Cholesky inside
+// ceres' SPARSE_SCHUR.
 #pragma once
 
 namespace bsnls {
 
 constexpr int kTS = 64;              // tile edge
+constexpr int kTileBlocks = 21;      // f-blocks per tile
+constexpr int kTU = 3 * kTileBlocks; // unknowns per tile (63); row/column 63 of every tile is an identity pad
 constexpr int kTLd = 68;             // shared-memory pitch of a tile (68 mod 16 = 4: conflict-free 64-bit fragment loads)
 constexpr int kTileDoubles = kTS * kTS;
+constexpr int kNdLeaf = 8, kNdShort = 6;   // nested dissection: tiles per leaf, longest edge (in tiles) that counts as band
 
 struct TileChol {
   int nT, n;
@@ -24,6 +31,11 @@ struct TileChol {
   double* T;                   // tile storage, each tile column-major 64x64
   double* W;                   // [nT][64*64] inverses of the diagonal factors (lower triangular, column-major)
   double* b;                   // [nT * 64] right-hand side / solution scratch
+  // level schedule (see set_problem)
+  const int* lev_cols;         // tile columns grouped by level
+  const int* pan_k; const int* pan_x;   // panel CTAs: column, index into col_rows (-1: the column has no tile below the diagonal)
+  const int* upd_ptr; const long long* upd_dst; const long long* upd_a; const long long* upd_b;   // update destinations and their source tile pairs
+  const int* fw_ptr; const int* fw_row; const int* fw_tail; const long long* fw_src; const int* fw_k;   // forward substitution
 };
 
 // ---- scatter the 3x3-block CSR system into the tiles (lower triangle), identity on the padding ----
@@ -34,14 +46,17 @@ __global__ void __launch_bounds__(256) bsr_to_tiles_kernel(DeviceProblem P, Tile
     const int blk = (int)(e / 9), w = (int)(e - 9LL * blk), i = w / 3, j = w - 3 * i;
     int lo = 0, hi = P.nf;   // row of this block: binary search in rowptr
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (P.bsr_rowptr[mid] <= blk) lo = mid; else hi = mid; }
-    const int r = 3 * lo + i, c = 3 * P.bsr_col[blk] + j;
-    if (r >= c) {
-      const long long off = TC.tile_off[(long long)(r / kTS) * TC.nT + c / kTS];
-      TC.T[off + (c % kTS) * kTS + r % kTS] = Sb[e];
+    const int br = lo, bc = P.bsr_col[blk];
+    if (3 * br + i >= 3 * bc + j) {
+      const int tr = br / kTileBlocks, tc = bc / kTileBlocks;
+      const long long off = TC.tile_off[(long long)tr * TC.nT + tc];
+      TC.T[off + (3 * (bc - tc * kTileBlocks) + j) * kTS + 3 * (br - tr * kTileBlocks) + i] = Sb[e];
     }
   } else {
-    const int p = (int)(e - P.nnzb * 9) + TC.n;   // padding rows of the last tile
-    if (p < TC.nT * kTS) TC.T[TC.tile_off[(long long)(p / kTS) * TC.nT + p / kTS] + (p % kTS) * kTS + p % kTS] = 1.0;
+    // identity on the pad row of every tile and on the unused rows of the last one: slot q of tile t
+    const long long q = e - P.nnzb * 9;
+    const int t = (int)(q / kTS), l = (int)(q % kTS);
+    if (t < TC.nT && (l == kTU || t * kTU + l >= TC.n)) TC.T[TC.tile_off[(long long)t * TC.nT + t] + l * kTS + l] = 1.0;
   }
 }
 
@@ -60,13 +75,11 @@ __device__ __forceinline__ void tile_load2(const double* __restrict__ g0, double
 #pragma unroll
   for (int u = 0; u < 8; ++u) { const int e = threadIdx.x + 256 * u; reinterpret_cast<double2*>(s0 + (e >> 5) * kTLd)[e & 31] = v[u]; reinterpret_cast<double2*>(s1 + (e >> 5) * kTLd)[e & 31] = v[8 + u]; }
 }
-// warp `I` (0..7) computes rows 8I..8I+7 of C: acc[J] = the lane's two entries (row 8I+g, cols 8J+2tg, 8J+2tg+1)
+// warp `I` (0..7) accumulates rows 8I..8I+7 of C into acc: acc[J] = the lane's two entries (row 8I+g, cols 8J+2tg, 8J+2tg+1)
 __device__ __forceinline__ void tile_abt(const double* __restrict__ As, const double* __restrict__ Bs, int I, int lane, double (&acc)[8][2]) {
   const int g = lane >> 2, tg = lane & 3;
   const double* pa = As + tg * kTLd + 8 * I + g;
   const double* pb = Bs + tg * kTLd + g;
-#pragma unroll
-  for (int J = 0; J < 8; ++J) { acc[J][0] = 0.0; acc[J][1] = 0.0; }
 #pragma unroll 4
   for (int ks = 0; ks < kTS / 4; ++ks) {
     const double av = pa[4 * ks * kTLd];
@@ -88,7 +101,7 @@ constexpr int kPanelSmemDoubles = 2 * kTS * kTLd + 16 + kTS * 4 + 4 * kTS;
 #ifdef PANEL_PROF
 __device__ long long g_panel_prof[80];
 #endif
-__global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int k, LMState* st) {
+__global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_begin, LMState* st) {
   extern __shared__ __align__(16) double sm[];
   double* As = sm;                          // A(i,k), column-major, pitch kTLd
   double* Bs = As + kTS * kTLd;             // W, column-major, pitch kTLd
@@ -97,15 +110,17 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int k, LMS
                                             // the 16 block rows of a warp are adjacent (no bank conflicts)
   double* sWrow = sPan + kTS * 4;           // final rows 4 jb.. of W: sWrow[i * 64 + c]
   __shared__ int failed;
-  if (!gate_run(st) || st->lin_fail) return;   // lin_fail is written only at the very end (by CTA 0)
+  if (!gate_run(st) || st->lin_fail) return;   // uniform per CTA; a failing column only ever stores garbage that nobody uses
   // a warp holds two block columns (tx) and all block rows (ty): at any step it is either left of the pivot column (W
   // updates only) or right of it (A updates only), so the two roles do not serialise inside a warp
   const int tid = threadIdx.x, tx = tid >> 4, ty = tid & 15;
-  const int na = TC.col_ptr[k + 1] - TC.col_ptr[k];
+  const int k = TC.pan_k[pan_begin + blockIdx.x], px = TC.pan_x[pan_begin + blockIdx.x];
+  const int na = px >= 0 ? 1 : 0;
+  const bool first = px < 0 || px == TC.col_ptr[k];   // this CTA stores W of its column
   const double* G = TC.T + TC.tile_off[(long long)k * TC.nT + k];
   double* Gi = nullptr;
   if (na > 0) {   // start fetching this CTA's tile; it is not needed before the product
-    Gi = TC.T + TC.tile_off[(long long)TC.col_rows[TC.col_ptr[k] + blockIdx.x] * TC.nT + k];
+    Gi = TC.T + TC.tile_off[(long long)TC.col_rows[px] * TC.nT + k];
     for (int e = tid; e < kTileDoubles / 2; e += 256) {
       const int c = e >> 5, r2 = e & 31;
       const unsigned dst = (unsigned)__cvta_generic_to_shared(As + c * kTLd + 2 * r2);
@@ -229,18 +244,20 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int k, LMS
       for (int i = 0; i < 4; ++i) {
         const double v = (ty > tx || (ty == tx && i >= c)) ? w[i][c] : 0.0;
         Bs[(4 * tx + c) * kTLd + 4 * ty + i] = v;
-        if (blockIdx.x == 0) Wk[(4 * tx + c) * kTS + 4 * ty + i] = v;
+        if (first) Wk[(4 * tx + c) * kTS + 4 * ty + i] = v;
       }
   }
   if (na > 0) asm volatile("cp.async.wait_group 0;");
   __syncthreads();
-  if (blockIdx.x == 0 && tid == 0 && failed) st->lin_fail = 1;
+  if (tid == 0 && failed) st->lin_fail = 1;   // every CTA of a column sees the same pivots
 #ifdef PANEL_PROF
   if (tid == 255) g_panel_prof[65] = clock64();
 #endif
   if (na == 0) return;
   const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
   double acc[8][2];
+#pragma unroll
+  for (int J = 0; J < 8; ++J) { acc[J][0] = 0.0; acc[J][1] = 0.0; }
   tile_abt(As, Bs, warp, lane, acc);
 #pragma unroll
   for (int J = 0; J < 8; ++J) {
@@ -249,28 +266,27 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int k, LMS
   }
 }
 
-// ---- syrk: A(i,j) -= L(i,k) L(j,k)^T for every pair i >= j of non-zero tiles of column k ----
-__global__ void __launch_bounds__(256) tile_syrk_kernel(TileChol TC, int k, const LMState* st) {
+// ---- syrk: A(i,j) -= sum_k L(i,k) L(j,k)^T over the source columns of this level; one CTA per destination tile ----
+__global__ void __launch_bounds__(256) tile_syrk_kernel(TileChol TC, int upd_begin, const LMState* st) {
   extern __shared__ __align__(16) double sm[];
   if (!gate_run(st) || st->lin_fail) return;
   double* As = sm; double* Bs = sm + kTS * kTLd;
-  // triangular decode of the pair index: p = x (x + 1) / 2 + y, x >= y
-  const int p = blockIdx.x;
-  int x = (int)((sqrt(8.0 * p + 1.0) - 1.0) * 0.5);
-  while (x * (x + 1) / 2 > p) --x;
-  while ((x + 1) * (x + 2) / 2 <= p) ++x;
-  const int y = p - x * (x + 1) / 2;
-  const int base = TC.col_ptr[k], i = TC.col_rows[base + x], j = TC.col_rows[base + y];
+  const int d = upd_begin + blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tg = lane & 3;
-  double* C = TC.T + TC.tile_off[(long long)i * TC.nT + j];
+  double* C = TC.T + TC.upd_dst[d];
   double cv[8][2];                      // the destination entries, fetched alongside the operands
 #pragma unroll
   for (int J = 0; J < 8; ++J) { cv[J][0] = C[(8 * J + 2 * tg) * kTS + 8 * warp + g]; cv[J][1] = C[(8 * J + 2 * tg + 1) * kTS + 8 * warp + g]; }
-  if (i != j) tile_load2(TC.T + TC.tile_off[(long long)i * TC.nT + k], As, TC.T + TC.tile_off[(long long)j * TC.nT + k], Bs);
-  else tile_load(TC.T + TC.tile_off[(long long)i * TC.nT + k], As);
-  __syncthreads();
   double acc[8][2];
-  tile_abt(As, i != j ? Bs : As, warp, lane, acc);
+#pragma unroll
+  for (int J = 0; J < 8; ++J) { acc[J][0] = 0.0; acc[J][1] = 0.0; }
+  for (int it = TC.upd_ptr[d]; it < TC.upd_ptr[d + 1]; ++it) {
+    const long long oa = TC.upd_a[it], ob = TC.upd_b[it];
+    if (oa != ob) tile_load2(TC.T + oa, As, TC.T + ob, Bs); else tile_load(TC.T + oa, As);
+    __syncthreads();
+    tile_abt(As, oa != ob ? Bs : As, warp, lane, acc);
+    __syncthreads();
+  }
 #pragma unroll
   for (int J = 0; J < 8; ++J) {
     C[(8 * J + 2 * tg) * kTS + 8 * warp + g] = cv[J][0] - acc[J][0];
@@ -278,108 +294,94 @@ __global__ void __launch_bounds__(256) tile_syrk_kernel(TileChol TC, int k, cons
   }
 }
 
-// ---- triangular solves with the tile factor; one CTA, 1024 threads ----
-// Per tile column the loads of W_k and of the column's tiles are issued together (they do not depend on the running
-// solution), so a column costs about one L2 round trip instead of one per tile. kSolveBatch tiles at a time.
-constexpr int kSolveBatch = 4;
-__global__ void __launch_bounds__(1024) tile_solve_kernel(TileChol TC, const double* __restrict__ rhs, double* __restrict__ yf, const LMState* st) {
-  __shared__ double part[kSolveBatch][16][kTS];   // forward: partial products per column group
-  __shared__ double xs[kSolveBatch][kTS], ys[kTS];
-  if (!gate_run(st) || st->lin_fail) return;
-  const int tid = threadIdx.x, nT = TC.nT, n = TC.n;
-  double* b = TC.b;
-  for (int i = tid; i < nT * kTS; i += 1024) b[i] = i < n ? rhs[i] : 0.0;
+// ---- substitutions with the tile factor, level by level; 256-thread CTAs ----
+// y = M x for a column-major 64x64 tile (x in shared memory): thread (cg, r) takes 16 columns of row r, the four column
+// groups are combined through shared memory. Returns the result for row `tid` in threads 0..63.
+__device__ __forceinline__ double tile_mv(const double* __restrict__ M, const double* xs, double (*part)[kTS], int tid) {
+  const int cg = tid >> 6, r = tid & 63;
+  double v[16];
+#pragma unroll
+  for (int q = 0; q < 16; ++q) v[q] = M[(16 * cg + q) * kTS + r];
+  double s = 0.0;
+#pragma unroll
+  for (int q = 0; q < 16; ++q) s += v[q] * xs[16 * cg + q];
+  part[cg][r] = s;
   __syncthreads();
-  // forward: y_k = W_k b_k, b_i -= L(i,k) y_k.  Thread (cg, r): column group cg = tid >> 6 (4 columns), row r = tid & 63
-  {
-    const int cg = tid >> 6, r = tid & 63;
-    for (int k = 0; k < nT; ++k) {
-      const int c0 = TC.col_ptr[k], na = TC.col_ptr[k + 1] - c0;
-      const double* Wk = TC.W + (size_t)k * kTileDoubles;
-      double w[4], l[kSolveBatch][4];
+  double tot = 0.0;
+  if (tid < kTS) tot = part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
+  __syncthreads();
+  return tot;
+}
+// y = M^T x: output c = tid >> 2, four lanes split the rows, shuffle reduction; every lane of the group holds the result
+__device__ __forceinline__ double tile_mv_t(const double* __restrict__ M, const double* xs, int tid) {
+  const int c = tid >> 2, sub = tid & 3;
+  double v[16];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) w[q] = Wk[(4 * cg + q) * kTS + r];
+  for (int q = 0; q < 16; ++q) v[q] = M[c * kTS + 16 * sub + q];
+  double s = 0.0;
 #pragma unroll
-      for (int t = 0; t < kSolveBatch; ++t) if (t < na) {
-        const double* Lt = TC.T + TC.tile_off[(long long)TC.col_rows[c0 + t] * nT + k];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) l[t][q] = Lt[(4 * cg + q) * kTS + r];
-      }
-      if (tid < kTS) ys[tid] = b[k * kTS + tid];
-      __syncthreads();
-      { double s = 0.0;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) s += w[q] * ys[4 * cg + q];
-        part[0][cg][r] = s; }
-      __syncthreads();
-      if (tid < kTS) { double s = 0.0; for (int q = 0; q < 16; ++q) s += part[0][q][tid]; xs[0][tid] = s; b[k * kTS + tid] = s; }
-      __syncthreads();
-      for (int t0 = 0; t0 < na; t0 += kSolveBatch) {
-        if (t0 > 0) {   // further batches of a tall column
-#pragma unroll
-          for (int t = 0; t < kSolveBatch; ++t) if (t0 + t < na) {
-            const double* Lt = TC.T + TC.tile_off[(long long)TC.col_rows[c0 + t0 + t] * nT + k];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) l[t][q] = Lt[(4 * cg + q) * kTS + r];
-          }
-        }
-#pragma unroll
-        for (int t = 0; t < kSolveBatch; ++t) if (t0 + t < na) {
-          double s = 0.0;
-#pragma unroll
-          for (int q = 0; q < 4; ++q) s += l[t][q] * xs[0][4 * cg + q];
-          part[t][cg][r] = s;
-        }
-        __syncthreads();
-        if (tid < kSolveBatch * kTS) {
-          const int t = tid >> 6, rr = tid & 63;
-          if (t0 + t < na) { double s = 0.0; for (int q = 0; q < 16; ++q) s += part[t][q][rr]; b[TC.col_rows[c0 + t0 + t] * kTS + rr] -= s; }
-        }
-        __syncthreads();
-      }
-    }
+  for (int q = 0; q < 16; ++q) s += v[q] * xs[16 * sub + q];
+  s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2);
+  return s;
+}
+__global__ void __launch_bounds__(256) tile_rhs_kernel(TileChol TC, const double* __restrict__ rhs, const LMState* st) {
+  if (!gate_run(st) || st->lin_fail) return;
+  const int e = blockIdx.x * 256 + threadIdx.x;
+  if (e >= TC.nT * kTS) return;
+  const int t = e >> 6, l = e & 63, srow = t * kTU + l;
+  TC.b[e] = (l < kTU && srow < TC.n) ? rhs[srow] : 0.0;
+}
+__global__ void __launch_bounds__(256) tile_out_kernel(TileChol TC, double* __restrict__ yf, const LMState* st) {
+  if (!gate_run(st) || st->lin_fail) return;
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i < TC.n) yf[i] = TC.b[(i / kTU) * kTS + i % kTU];
+}
+// forward, leaves: y_k = W_k b_k
+__global__ void __launch_bounds__(256) tile_fwd_first_kernel(TileChol TC, int col_begin, const LMState* st) {
+  __shared__ double xs[kTS]; __shared__ double part[4][kTS];
+  if (!gate_run(st) || st->lin_fail) return;
+  const int k = TC.lev_cols[col_begin + blockIdx.x], tid = threadIdx.x;
+  if (tid < kTS) xs[tid] = TC.b[k * kTS + tid];
+  __syncthreads();
+  const double yk = tile_mv(TC.W + (size_t)k * kTileDoubles, xs, part, tid);
+  if (tid < kTS) TC.b[k * kTS + tid] = yk;
+}
+// forward, one level: b_i -= sum_k L(i,k) y_k over the level's columns; if column i belongs to the next level its
+// right-hand side is complete now and y_i = W_i b_i follows in the same CTA
+__global__ void __launch_bounds__(256) tile_fwd_kernel(TileChol TC, int fw_begin, const LMState* st) {
+  __shared__ double xs[kTS]; __shared__ double part[4][kTS];
+  if (!gate_run(st) || st->lin_fail) return;
+  const int d = fw_begin + blockIdx.x, i = TC.fw_row[d], tid = threadIdx.x;
+  double bi = tid < kTS ? TC.b[i * kTS + tid] : 0.0;
+  for (int it = TC.fw_ptr[d]; it < TC.fw_ptr[d + 1]; ++it) {
+    if (tid < kTS) xs[tid] = TC.b[TC.fw_k[it] * kTS + tid];
+    __syncthreads();
+    bi -= tile_mv(TC.T + TC.fw_src[it], xs, part, tid);
   }
-  // backward: x_k = W_k^T (y_k - sum_i L(i,k)^T x_i).  Thread (c, sub): output c = tid >> 4, 16 lanes split the rows
-  {
-    const int c = tid >> 4, sub = tid & 15;
-    for (int k = nT - 1; k >= 0; --k) {
-      const int c0 = TC.col_ptr[k], na = TC.col_ptr[k + 1] - c0;
-      const double* Wk = TC.W + (size_t)k * kTileDoubles;
-      double w[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) w[q] = Wk[c * kTS + 4 * sub + q];
-      double t = sub == 0 ? b[k * kTS + c] : 0.0;
-      for (int t0 = 0; t0 < na; t0 += kSolveBatch) {
-        double l[kSolveBatch][4];
-#pragma unroll
-        for (int tt = 0; tt < kSolveBatch; ++tt) if (t0 + tt < na) {
-          const double* Lt = TC.T + TC.tile_off[(long long)TC.col_rows[c0 + t0 + tt] * nT + k];
-#pragma unroll
-          for (int q = 0; q < 4; ++q) l[tt][q] = Lt[c * kTS + 4 * sub + q];
-        }
-        if (tid < kSolveBatch * kTS) { const int tt = tid >> 6, rr = tid & 63; if (t0 + tt < na) xs[tt][rr] = b[TC.col_rows[c0 + t0 + tt] * kTS + rr]; }
-        __syncthreads();
-#pragma unroll
-        for (int tt = 0; tt < kSolveBatch; ++tt) if (t0 + tt < na) {
-#pragma unroll
-          for (int q = 0; q < 4; ++q) t -= l[tt][q] * xs[tt][4 * sub + q];
-        }
-        __syncthreads();
-      }
-#pragma unroll
-      for (int m = 1; m < 16; m <<= 1) t += __shfl_xor_sync(0xffffffffu, t, m);
-      if (sub == 0) ys[c] = t;
-      __syncthreads();
-      double xk = 0.0;
-#pragma unroll
-      for (int q = 0; q < 4; ++q) xk += w[q] * ys[4 * sub + q];
-#pragma unroll
-      for (int m = 1; m < 16; m <<= 1) xk += __shfl_xor_sync(0xffffffffu, xk, m);
-      if (sub == 0) b[k * kTS + c] = xk;
-      __syncthreads();
-    }
+  if (TC.fw_tail[d]) {
+    if (tid < kTS) xs[tid] = bi;
+    __syncthreads();
+    bi = tile_mv(TC.W + (size_t)i * kTileDoubles, xs, part, tid);
   }
-  for (int i = tid; i < n; i += 1024) yf[i] = b[i];
+  if (tid < kTS) TC.b[i * kTS + tid] = bi;
+}
+// backward, one level: x_k = W_k^T (y_k - sum_i L(i,k)^T x_i); the rows i of a column are its ancestors (done already)
+__global__ void __launch_bounds__(256) tile_bwd_kernel(TileChol TC, int col_begin, const LMState* st) {
+  __shared__ double xs[kTS];
+  if (!gate_run(st) || st->lin_fail) return;
+  const int k = TC.lev_cols[col_begin + blockIdx.x], tid = threadIdx.x, c = tid >> 2;
+  double t = TC.b[k * kTS + c];
+  for (int it = TC.col_ptr[k]; it < TC.col_ptr[k + 1]; ++it) {
+    const int i = TC.col_rows[it];
+    if (tid < kTS) xs[tid] = TC.b[i * kTS + tid];
+    __syncthreads();
+    t -= tile_mv_t(TC.T + TC.tile_off[(long long)i * TC.nT + k], xs, tid);
+    __syncthreads();
+  }
+  if ((tid & 3) == 0) xs[c] = t;
+  __syncthreads();
+  const double xk = tile_mv_t(TC.W + (size_t)k * kTileDoubles, xs, tid);
+  if ((tid & 3) == 0) TC.b[k * kTS + c] = xk;
 }
 
 }  // namespace bsnls
