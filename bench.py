@@ -208,7 +208,7 @@ def run_ours(args):
 
     mean = lambda k: float(np.mean([q[k] for q in parts]))
     br = {k: mean(k) for k in Solver.BREAKDOWN}
-    dense = nf_dim <= 3000
+    dense = nf_dim <= 160   # sliding windows keep a dense reduced system; everything larger is 3x3-block sparse
     eval_b, schur_b = algorithmic_bytes(info, nf_dim, dense)
     if not dense:
         schur_b += 72 * (2 * summ.reduced_system_nnz_blocks - nf_dim // 3)   # block-sparse S write (full symmetric storage)
