@@ -48,6 +48,7 @@ struct bsnls_handle {
   int device = 0;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+  cudaStream_t side = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // generic factors run beside the reprojection pass
   cudaEvent_t pev[10] = {};   // per-kernel marks for bsnls_last_breakdown_ms
   bool profiling = false; float breakdown[8] = {};
   std::string error;
@@ -187,12 +188,22 @@ void EnqueueEval(bsnls_handle* h) {  // phase A: residuals + Jacobians + cost at
   const DeviceProblem& P = h->P;
   LMState* st = h->d_state.as<LMState>();
   MARK(h, 0);
+  // the generic factors (IMU, priors, relative poses) are independent of the reprojection pass until the gradient is
+  // put together: they run on a side stream (fork / join by events, which also works under stream capture)
+  const bool fork = h->ngf && h->nobs;
+  if (fork) {
+    cudaEventRecord(h->ev_fork, h->stream); cudaStreamWaitEvent(h->side, h->ev_fork, 0);
+    eval_generic_kernel<0><<<BlocksFor(h->ngf, 4), 128, 0, h->side>>>(P, h->d_x.as<double>(), h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_cost_part.as<double>() + h->nb_eval, st);
+    h->launches++;
+    cudaEventRecord(h->ev_join, h->side);
+  }
   if (h->nobs) {
     LAUNCH(h, pose_prep_kernel, BlocksFor(h->np, 128), 128, P, h->d_x.as<double>(), h->d_pose_tab.as<double>(), st);
     LAUNCH(h, eval_reproj_pose_kernel, h->nb_eval, 256, P, h->d_x.as<double>(), h->d_pose_tab.as<double>(), h->d_Jrec.as<double>(), h->d_cost_part.as<double>(), h->d_pose_part.as<double>(), st);
   }
   MARK(h, 1);
-  if (h->ngf) LAUNCH(h, eval_generic_kernel<0>, BlocksFor(h->ngf, 4), 128, P, h->d_x.as<double>(), h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_cost_part.as<double>() + h->nb_eval, st);
+  if (fork) cudaStreamWaitEvent(h->stream, h->ev_join, 0);
+  else if (h->ngf) LAUNCH(h, eval_generic_kernel<0>, BlocksFor(h->ngf, 4), 128, P, h->d_x.as<double>(), h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_cost_part.as<double>() + h->nb_eval, st);
   MARK(h, 2);
 }
 template <int G> void LaunchLandmark(bsnls_handle* h, const Options& o) {
@@ -204,36 +215,64 @@ void EnqueueLandmark(bsnls_handle* h, const Options& o) {  // phase B
   switch (h->G) { case 4: LaunchLandmark<4>(h, o); break; case 8: LaunchLandmark<8>(h, o); break;
                   case 16: LaunchLandmark<16>(h, o); break; default: LaunchLandmark<32>(h, o); }
 }
-int EnqueueGradient(bsnls_handle* h, const Options& o) {  // phase C: gradient, column norms, scale, gradient norms
+// Phases C and D1 of a pass, ordered so that a sharded solve needs ONE exchange: everything that only needs this
+// rank's observations first (pose gradient / column norms, cost and landmark-gradient norms, the shard's reduced
+// system), then one grouped all-reduce, then the kernels that need the sums (generic-factor gradient, Jacobi scale,
+// f-block gradient norms, generic rows of S, damping).
+void EnqueueGradientLocal(bsnls_handle* h) {
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
   if (h->np) LAUNCH(h, pose_reduce_kernel, BlocksFor(h->np * 27, 128), 128, P, h->d_pose_part.as<double>(), h->d_poseH.as<double>(), h->d_gradL.as<double>(), h->d_colsqL.as<double>(), st);
-  const double* gS = h->d_gradL.as<double>(); const double* cS = h->d_colsqL.as<double>();
-  if (h->world > 1) {
-    // pose gradient / column norms are sums over the observations of every rank. Out of place: the kernels above are
-    // gated by the device state, the collective is not, so it must be idempotent when they did not run.
-    Nccl().GroupStart();
-    int rc = Nccl().AllReduce(h->d_gradL.p, h->d_gradS.p, P.nf_dim, kNcclFloat64, kNcclSum, h->comm, h->stream);
-    if (rc == kNcclSuccess) rc = Nccl().AllReduce(h->d_colsqL.p, h->d_colsqS.p, P.nf_dim, kNcclFloat64, kNcclSum, h->comm, h->stream);
-    Nccl().GroupEnd();
-    if (rc != kNcclSuccess) return h->fail(BSNLS_ERR_CUDA, "ncclAllReduce(gradient): %s", Nccl().GetErrorString(rc));
-    gS = h->d_gradS.as<double>(); cS = h->d_colsqS.as<double>();
+  if (h->world == 1) return;   // one GPU: a single norm / reduction launch after the generic-factor gradient does it all
+  const int nbe = h->nb_act_e;
+  if (nbe) LAUNCH(h, grad_norm_kernel, nbe, 256, P, h->d_x.as<double>(), h->d_grad.as<double>(), h->d_gsq_part.as<double>(), h->d_gmax_part.as<double>(), 0, st);
+  RedList L{}; L.gate = 2; L.count = 0; L.keep = 0;
+  if (h->nobs) L.d[L.count++] = Desc(h->d_cost_part.as<double>(), h->nb_eval, 0, RED_COST, false);
+  if (nbe) L.d[L.count++] = Desc(h->d_gsq_part.as<double>(), nbe, 0, RED_GRAD_SQ, false);
+  if (nbe) L.d[L.count++] = Desc(h->d_gmax_part.as<double>(), nbe, 1, 0, false);
+  LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), st);
+}
+// with_system: the exchange of a full pass (reduced system + gradient + scalars); otherwise gradient + scalars only
+int EnqueueExchange(bsnls_handle* h, bool with_system) {
+  if (h->world <= 1) return BSNLS_OK;
+  const DeviceProblem& P = h->P;
+  // Pose gradient / column norms go out of place: the kernels that rebuild them are gated by the device state, the
+  // collective is not, so it must be idempotent when they did not run. S and rhs are rebuilt on every pass; red[] is
+  // only read by the (equally gated) controller.
+  Nccl().GroupStart();
+  int rc = kNcclSuccess;
+  if (with_system) {
+    const size_t s_count = h->sparse ? (size_t)h->nnzb * 9 : (size_t)P.nf_dim * P.nf_dim;
+    rc = Nccl().AllReduce(h->d_S.p, h->d_S.p, s_count, kNcclFloat64, kNcclSum, h->comm, h->stream);
+    if (rc == kNcclSuccess) rc = Nccl().AllReduce(h->d_rhs.p, h->d_rhs.p, P.nf_dim, kNcclFloat64, kNcclSum, h->comm, h->stream);
   }
+  if (rc == kNcclSuccess) rc = Nccl().AllReduce(h->d_gradL.p, h->d_gradS.p, P.nf_dim, kNcclFloat64, kNcclSum, h->comm, h->stream);
+  if (rc == kNcclSuccess) rc = Nccl().AllReduce(h->d_colsqL.p, h->d_colsqS.p, P.nf_dim, kNcclFloat64, kNcclSum, h->comm, h->stream);
+  if (rc == kNcclSuccess) rc = Nccl().AllReduce(h->d_red.p, h->d_red.p, RED_NUM, kNcclFloat64, kNcclSum, h->comm, h->stream);
+  if (rc == kNcclSuccess) rc = Nccl().AllReduce(h->d_red.as<double>() + kRedLocalMax, h->d_red.as<double>() + kRedLocalMax, 1, kNcclFloat64, kNcclMax, h->comm, h->stream);
+  Nccl().GroupEnd();
+  return rc == kNcclSuccess ? BSNLS_OK : h->fail(BSNLS_ERR_CUDA, "ncclAllReduce(exchange): %s", Nccl().GetErrorString(rc));
+}
+void EnqueueGradientGlobal(bsnls_handle* h, const Options& o) {
+  const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
+  const double* gS = h->world > 1 ? h->d_gradS.as<double>() : h->d_gradL.as<double>();
+  const double* cS = h->world > 1 ? h->d_colsqS.as<double>() : h->d_colsqL.as<double>();
   LAUNCH(h, gf_grad_kernel, BlocksFor(3 * h->nf, 128), 128, P, h->d_gfJ.as<double>(), h->d_gfR.as<double>(), gS, cS, h->d_is_pose.as<unsigned char>(),
          h->d_grad.as<double>(), h->d_colsq.as<double>(), h->d_scale.as<double>(), o, st);
-  LAUNCH(h, grad_norm_kernel, h->nb_act, 256, P, h->d_x.as<double>(), h->d_grad.as<double>(), h->d_gsq_part.as<double>(), h->d_gmax_part.as<double>(), st);
-  RedList L{}; L.gate = 2; L.count = 0;
   const int nbe = h->nb_act_e, nbf = h->nb_act - h->nb_act_e;
-  if (h->nobs) L.d[L.count++] = Desc(h->d_cost_part.as<double>(), h->nb_eval, 0, RED_COST, false);
+  const bool one = h->world == 1;
+  if (one) LAUNCH(h, grad_norm_kernel, h->nb_act, 256, P, h->d_x.as<double>(), h->d_grad.as<double>(), h->d_gsq_part.as<double>(), h->d_gmax_part.as<double>(), 0, st);
+  else if (nbf) LAUNCH(h, grad_norm_kernel, nbf, 256, P, h->d_x.as<double>(), h->d_grad.as<double>(), h->d_gsq_part.as<double>(), h->d_gmax_part.as<double>(), nbe, st);
+  RedList L{}; L.gate = 2; L.count = 0; L.keep = one ? 0 : 1;   // sharded: replicated slots, added to what the exchange left in red[]
+  if (one && h->nobs) L.d[L.count++] = Desc(h->d_cost_part.as<double>(), h->nb_eval, 0, RED_COST, false);
+  if (one && nbe) L.d[L.count++] = Desc(h->d_gsq_part.as<double>(), nbe, 0, RED_GRAD_SQ, false);
+  if (one && nbe) L.d[L.count++] = Desc(h->d_gmax_part.as<double>(), nbe, 1, 0, false);
   if (h->ngf_active) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_eval, h->ngf_active, 0, RED_COST, true);
   if (h->ngf > h->ngf_active) L.d[L.count++] = Desc(h->d_cost_part.as<double>() + h->nb_eval + h->ngf_active, h->ngf - h->ngf_active, 0, RED_FIXED, true);
-  if (nbe) L.d[L.count++] = Desc(h->d_gsq_part.as<double>(), nbe, 0, RED_GRAD_SQ, false);
   if (nbf) L.d[L.count++] = Desc(h->d_gsq_part.as<double>() + nbe, nbf, 0, RED_GRAD_SQ, true);
-  if (nbe) L.d[L.count++] = Desc(h->d_gmax_part.as<double>(), nbe, 1, 0, false);
   if (nbf) L.d[L.count++] = Desc(h->d_gmax_part.as<double>() + nbe, nbf, 1, 0, true);
   LAUNCH(h, reduce_kernel, 1, 256, L, h->d_red.as<double>(), st);
-  return AllReduceScalars(h);
 }
-int EnqueueAssemble(bsnls_handle* h, const Options& o) {  // phase D1: reduced system S, rhs
+void EnqueueAssembleLocal(bsnls_handle* h) {  // phase D1, this rank's share: S and rhs from its landmarks
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
   const size_t s_count = h->sparse ? (size_t)h->nnzb * 9 : (size_t)P.nf_dim * P.nf_dim;
   MARK(h, 5);
@@ -247,18 +286,36 @@ int EnqueueAssemble(bsnls_handle* h, const Options& o) {  // phase D1: reduced s
   if (h->npairs && h->nchunks) LAUNCH(h, pair_reduce_kernel, BlocksFor(h->npairs, 4), 144, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), h->d_poseH.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
   else if (h->npairs) LAUNCH(h, pair_kernel, BlocksFor(h->npairs, 4), 128, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
   MARK(h, 7);
-  if (h->world > 1) {  // the one exchange step of the path: sum the per-shard reduced camera systems over NVLink
-    Nccl().GroupStart();
-    int rc = AllReduce(h, h->d_S.as<double>(), s_count, kNcclSum);
-    if (rc == BSNLS_OK) rc = AllReduce(h, h->d_rhs.as<double>(), P.nf_dim, kNcclSum);
-    Nccl().GroupEnd();
-    if (rc != BSNLS_OK) return rc;
-  }
-  MARK(h, 9);
+}
+void EnqueueAssembleFinish(bsnls_handle* h, const Options& o) {  // generic-factor rows of S, gradient into rhs, damping
+  const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
   if (h->ngdest) LAUNCH(h, gf_schur_kernel, BlocksFor(h->ngdest, 16), 144, P, h->d_gfJ.as<double>(), h->d_S.as<double>(), st);
   LAUNCH(h, finish_system_kernel, BlocksFor(P.nf_dim, 256), 256, P, h->d_grad.as<double>(), h->d_colsq.as<double>(), h->d_scale.as<double>(),
          h->d_is_pose.as<unsigned char>(), h->d_S.as<double>(), h->d_rhs.as<double>(), o, st);
   MARK(h, 8);
+}
+// The Jacobian half of a pass (after EnqueueEval / EnqueueLandmark) up to the controller's input; with_system also
+// assembles the reduced system. Kernel order is the same on one GPU, where the exchange is a no-op.
+int EnqueueLinearise(bsnls_handle* h, const Options& o, bool with_system) {
+  EnqueueGradientLocal(h);
+  if (h->world == 1 && with_system) {
+    // one GPU: nothing to exchange, so the gradient / norm kernels (small, latency-bound) run on the side stream
+    // while the main stream assembles the reduced system
+    cudaEventRecord(h->ev_fork, h->stream); cudaStreamWaitEvent(h->side, h->ev_fork, 0);
+    std::swap(h->stream, h->side);
+    EnqueueGradientGlobal(h, o);
+    std::swap(h->stream, h->side);
+    cudaEventRecord(h->ev_join, h->side);
+    EnqueueAssembleLocal(h);
+    MARK(h, 9);
+    cudaStreamWaitEvent(h->stream, h->ev_join, 0);
+    return BSNLS_OK;
+  }
+  if (with_system) EnqueueAssembleLocal(h);
+  const int rc = EnqueueExchange(h, with_system);
+  if (rc != BSNLS_OK) return rc;
+  MARK(h, 9);
+  EnqueueGradientGlobal(h, o);
   return BSNLS_OK;
 }
 void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular solves
@@ -385,7 +442,8 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
   h->opt = o; h->device = dev;
   if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaEventCreate(&h->ev0)) != cudaSuccess || (e = cudaEventCreate(&h->ev1)) != cudaSuccess ||
-      (e = cudaEventCreate(&h->ev2)) != cudaSuccess) {
+      (e = cudaEventCreate(&h->ev2)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking)) != cudaSuccess ||
+      (e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)) != cudaSuccess || (e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming)) != cudaSuccess) {
     g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
   }
   if ((e = cudaFuncSetAttribute(chunk_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, syrk_smem_bytes(kChunkSlots))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
@@ -405,6 +463,9 @@ void bsnls_destroy(bsnls_handle* h) {
   if (h->graph_tail) cudaGraphExecDestroy(h->graph_tail);
   if (h->comm) Nccl().CommDestroy(h->comm);
   if (h->stream) cudaStreamDestroy(h->stream);
+  if (h->side) cudaStreamDestroy(h->side);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->ev2) cudaEventDestroy(h->ev2);
@@ -1142,17 +1203,17 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
   const bool timed = h->opt.max_solver_time_in_seconds < 1e8 && h->world == 1;
   auto enqueue_tail = [&]() -> int {   // Jacobian pass that closes an accepted step (or IterationZero)
     EnqueueEval(h);
-    int r2 = EnqueueGradient(h, o);
+    int r2 = EnqueueLinearise(h, o, false);
     LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
     return r2;
   };
   auto enqueue_pass = [&]() -> int {   // one LM iteration
     EnqueueEval(h);
     EnqueueLandmark(h, o);
-    int r2 = EnqueueGradient(h, o);
+    int r2 = EnqueueLinearise(h, o, true);
     if (r2 != BSNLS_OK) return r2;
     LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
-    if ((r2 = EnqueueAssemble(h, o)) != BSNLS_OK) return r2;
+    EnqueueAssembleFinish(h, o);
     if (h->pcg) { r2 = EnqueueSparseSolve(h); if (r2 != BSNLS_OK) return r2; } else EnqueueDenseSolve(h);
     if ((r2 = EnqueueStep(h)) != BSNLS_OK) return r2;
     LAUNCH(h, ctrl_end_iteration_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
@@ -1273,9 +1334,9 @@ int bsnls_run_schur(bsnls_handle* h, double radius) {
   MARK(h, 3);
   EnqueueLandmark(h, o);
   MARK(h, 4);
-  int rc = EnqueueGradient(h, o);
-  if (rc == BSNLS_OK) rc = EnqueueAssemble(h, o);
+  int rc = EnqueueLinearise(h, o, true);
   if (rc != BSNLS_OK) { h->profiling = false; return rc; }
+  EnqueueAssembleFinish(h, o);
   CK(cudaEventRecord(h->ev1, h->stream));
   h->profiling = false;
   CK(cudaStreamSynchronize(h->stream)); CK(cudaGetLastError());
@@ -1338,7 +1399,7 @@ int bsnls_evaluate(bsnls_handle* h, double* cost, double* residuals, int64_t* nu
   const Options o = MakeOptions(h->opt);
   LMState* st = h->d_state.as<LMState>();
   if (h->world > 1) return h->fail(BSNLS_ERR_UNSUPPORTED, "bsnls_evaluate is a single-GPU call (residuals live on the rank that owns their landmark)");
-  EnqueueEval(h); EnqueueLandmark(h, o); rc = EnqueueGradient(h, o);
+  EnqueueEval(h); EnqueueLandmark(h, o); rc = EnqueueLinearise(h, o, false);
   if (rc != BSNLS_OK) return rc;
   // include factors whose blocks are all constant in the cost (Problem::Evaluate evaluates every residual block)
   RedList L{}; L.gate = 0; L.count = 0;

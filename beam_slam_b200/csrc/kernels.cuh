@@ -459,10 +459,11 @@ __device__ __forceinline__ void quat_plus(const double* x, const double* d, doub
 }
 __global__ void __launch_bounds__(256) grad_norm_kernel(DeviceProblem P, const double* __restrict__ x,
                                                         const double* __restrict__ grad, double* __restrict__ part_sq,
-                                                        double* __restrict__ part_max, const LMState* st) {
+                                                        double* __restrict__ part_max, int block0, const LMState* st) {
   if (!gate_jac(st)) return;
   __shared__ double sm[256];
-  const int i = blockIdx.x * 256 + threadIdx.x;
+  const int blk = blockIdx.x + block0;   // launched in two parts: landmark blocks before the exchange, f-blocks after it
+  const int i = blk * 256 + threadIdx.x;
   double sq = 0.0, mx = 0.0;
   if (i < P.num_active && P.active_blocks[i] >= 0) {
     const int b = P.active_blocks[i], off = P.blk_off[b], t = P.blk_tan[b];
@@ -476,7 +477,7 @@ __global__ void __launch_bounds__(256) grad_norm_kernel(DeviceProblem P, const d
   }
   const double ts = block_sum<256>(sq, sm); __syncthreads();
   const double tm = block_max<256>(mx, sm);
-  if (threadIdx.x == 0) { part_sq[blockIdx.x] = ts; part_max[blockIdx.x] = tm; }
+  if (threadIdx.x == 0) { part_sq[blk] = ts; part_max[blk] = tm; }
 }
 
 // ===================================================================================================
@@ -1322,12 +1323,12 @@ constexpr int kRedLocalMax = 2 * RED_NUM, kRedReplMax = 2 * RED_NUM + 1, kRedSiz
 __device__ __forceinline__ double red_sum(const double* red, int slot) { return red[slot] + red[RED_NUM + slot]; }
 __device__ __forceinline__ double red_max(const double* red) { return fmax(red[kRedLocalMax], red[kRedReplMax]); }
 struct RedDesc { const double* src; int n; int op; int slot; };  // op 0 = sum, 1 = max; slot already offset by RED_NUM when replicated
-struct RedList { RedDesc d[10]; int count; int gate; };          // gate 0 always, 1 run, 2 jac
+struct RedList { RedDesc d[10]; int count; int gate; int keep; };   // gate 0 always, 1 run, 2 jac; keep: add to red[] instead of starting from zero
 __global__ void __launch_bounds__(256) reduce_kernel(RedList L, double* __restrict__ red, const LMState* st) {
   if (L.gate == 1 && !gate_run(st)) return;
   if (L.gate == 2 && !gate_jac(st)) return;
   __shared__ double sm[256];
-  if (threadIdx.x < kRedSize) red[threadIdx.x] = 0.0;   // slots not produced by this phase must not carry stale sums
+  if (!L.keep && threadIdx.x < kRedSize) red[threadIdx.x] = 0.0;   // slots not produced by this phase must not carry stale sums
   __syncthreads();
   for (int q = 0; q < L.count; ++q) {
     const RedDesc d = L.d[q];
