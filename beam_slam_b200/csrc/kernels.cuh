@@ -176,6 +176,7 @@ __global__ void __launch_bounds__(256, EVAL_MINB) eval_reproj_pose_kernel(Device
                                                                double* __restrict__ pose_part, const LMState* st) {
   if (!gate_jac(st)) return;
   __shared__ double sm[8][33];
+  __shared__ double2 sOut[256 * 9];                                      // Jacobian records of the CTA, pitch 9 (conflict-free)
   __shared__ __align__(16) double sT[kPoseTab];                          // the pose's table: read by every thread (broadcast)
   __shared__ __align__(16) double sCam[kEvalSmemCams * BSNLS_CAMERA_STRIDE];   // the first few cameras (usually all of them)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -202,7 +203,9 @@ __global__ void __launch_bounds__(256, EVAL_MINB) eval_reproj_pose_kernel(Device
     cost = reprojection_evaluate_tab(cam, pixel, q, T, Pw, r, Jq, JP);
     if (P.pose_q_tan[a] < 0) { for (int k = 0; k < 6; ++k) Jq[k] = 0.0; }
     const double ts = P.pose_t_tan[a] < 0 ? 0.0 : -1.0;   // d r / d t = ts * d r / d P
-    double2* out = reinterpret_cast<double2*>(Jrec + (size_t)it * kJRec);
+    // the record goes through shared memory so that the CTA's records (contiguous in the pose-major list) leave as
+    // whole 512-byte warp stores instead of 32 separate lines per store instruction
+    double2* out = sOut + threadIdx.x * 9;
     out[0] = make_double2(JP[0], JP[1]); out[1] = make_double2(JP[2], JP[3]); out[2] = make_double2(JP[4], JP[5]);
     out[3] = make_double2(r[0], r[1]);
     out[4] = make_double2(Jq[0], Jq[1]); out[5] = make_double2(Jq[2], Jq[3]); out[6] = make_double2(Jq[4], Jq[5]);
@@ -219,6 +222,12 @@ __global__ void __launch_bounds__(256, EVAL_MINB) eval_reproj_pose_kernel(Device
   }
   sm[warp][lane] = warp_transpose_sum32(v, lane);   // entry `lane` of this warp: 0..26 pose data, 27 cost
   __syncthreads();
+  {
+    const int nrec = min(256, iv.z - iv.y);
+    double2* dst = reinterpret_cast<double2*>(Jrec + (size_t)iv.y * kJRec);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { const int e = threadIdx.x + 256 * u; if ((e >> 3) < nrec) dst[e] = sOut[(e >> 3) * 9 + (e & 7)]; }
+  }
   if (threadIdx.x < 28) {
     double tot = 0.0;
 #pragma unroll
