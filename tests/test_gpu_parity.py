@@ -229,6 +229,25 @@ def test_run_to_run_determinism():
     assert out[0] == out[1]
 
 
+def test_loop_closure_graph_on_the_tile_path_matches_oracle():
+    """Config 4 at a tenth of its size: 200 keyframes with loop closures, reduced system 1 200. The tile-sparse Cholesky
+    runs with its nested-dissection order (20 tiles, the loop-closure tiles end up in separators) and must reproduce
+    the oracle's dense solve iteration by iteration."""
+    g = host.HashGraph.synthetic(4, scale=0.1)
+    p, opts = g.flatten(), host.HashGraph.synthetic_options(4)
+    s = Solver(opts)
+    s.set_problem(p)
+    summ, its = s.solve()
+    so, ito, xo = orc.solve(p, opts)
+    assert summ.message == so.message and len(its) == len(ito)
+    for a, b in zip(its, ito):
+        assert a.step_is_successful == b.step_is_successful
+        assert abs(a.cost - b.cost) <= 1e-9 * abs(b.cost)
+        assert abs(a.trust_region_radius - b.trust_region_radius) <= 1e-9 * b.trust_region_radius
+    assert abs(summ.final_cost - so.final_cost) <= 1e-9 * so.final_cost
+    assert _rel(s.get_values(), xo) < 1e-7
+
+
 @pytest.mark.parametrize("cfg,scale", [(2, 0.25), (3, 0.02)])
 def test_block_sparse_pcg_matches_dense_and_oracle(cfg, scale):
     """K7: block-sparse reduced system + block-Jacobi PCG against the dense DMMA Cholesky path and the oracle.
