@@ -72,9 +72,9 @@ struct bsnls_handle {
   std::vector<int> gd_row, gd_col;
   bool tiled = false; std::vector<int> f_api;   // tile-sparse Cholesky; internal f position -> API (program-order) position
   TileChol TC{}; std::vector<int> tc_col_ptr; DevMem d_tc_tile_off, d_tc_col_ptr, d_tc_col_rows, d_tc_T, d_tc_W, d_tc_b; size_t tc_T_bytes = 0;
-  struct TcLevel { int col_begin, ncols, pan_begin, npan, upd_begin, nupd, fw_begin, nfw; };   // one level of the elimination tree
+  struct TcLevel { int col_begin, ncols, pan_begin, npan, upd_begin, nupd, fw_begin, nfw, bw_begin, nbw; };   // one level of the elimination tree
   std::vector<TcLevel> tc_levels;
-  DevMem d_tc_pan_k, d_tc_pan_x, d_tc_upd_ptr, d_tc_upd_dst, d_tc_upd_a, d_tc_upd_b, d_tc_fw_ptr, d_tc_fw_row, d_tc_fw_tail, d_tc_fw_src, d_tc_fw_k, d_tc_lev_cols;
+  DevMem d_tc_pan_k, d_tc_pan_x, d_tc_upd_ptr, d_tc_upd_dst, d_tc_upd_a, d_tc_upd_b, d_tc_fw_ptr, d_tc_fw_row, d_tc_fw_tail, d_tc_fw_src, d_tc_fw_k, d_tc_lev_cols, d_tc_bw_ptr, d_tc_bw_col, d_tc_bw_tail, d_tc_bw_src, d_tc_bw_i, d_tc_roots; int tc_nroots = 0;
   bool chunk_fma = false; int chunk_max_slots = 1; DevMem d_syrk_plan, d_chunk_tile_off, d_pp_toff, d_pp_info;
   int nchunks = 0; DevMem d_obs_slot, d_chunk_end, d_chunk_begin, d_chunk_nslots, d_chunk_part_off, d_chunk_cpart_off, d_pp_ptr, d_pp_off, d_pp_coff, d_part, d_cpart;
   bool sparse = false, pcg = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
@@ -334,7 +334,8 @@ void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular so
     LAUNCH(h, tile_rhs_kernel, (TC.nT * kTS + 255) / 256, 256, TC, h->d_rhs.as<double>(), st);
     LAUNCH(h, tile_fwd_first_kernel, h->tc_levels[0].ncols, 256, TC, h->tc_levels[0].col_begin, st);
     for (const auto& L : h->tc_levels) if (L.nfw > 0) LAUNCH(h, tile_fwd_kernel, L.nfw, 256, TC, L.fw_begin, st);
-    for (size_t lv = h->tc_levels.size(); lv-- > 0;) LAUNCH(h, tile_bwd_kernel, h->tc_levels[lv].ncols, 256, TC, h->tc_levels[lv].col_begin, st);
+    LAUNCH(h, tile_bwd_first_kernel, h->tc_nroots, 256, TC, st);
+    for (size_t lv = h->tc_levels.size(); lv-- > 0;) if (h->tc_levels[lv].nbw > 0) LAUNCH(h, tile_bwd_kernel, h->tc_levels[lv].nbw, 256, TC, h->tc_levels[lv].bw_begin, st);
     LAUNCH(h, tile_out_kernel, (TC.n + 255) / 256, 256, TC, h->d_yf.as<double>(), st);
     return;
   }
@@ -1021,6 +1022,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   std::vector<long long> tc_tile_off; std::vector<int> tc_col_rows; long long tc_tiles = 0;
   std::vector<int> tc_pan_k, tc_pan_x, tc_upd_ptr, tc_fw_ptr, tc_fw_row, tc_fw_tail, tc_lev_cols;
   std::vector<long long> tc_upd_dst, tc_upd_a, tc_upd_b, tc_fw_src; std::vector<int> tc_fw_k;
+  std::vector<int> tc_bw_ptr, tc_bw_col, tc_bw_tail, tc_bw_i, tc_roots; std::vector<long long> tc_bw_src;
   h->tc_col_ptr.clear(); h->tc_levels.clear();
   if (h->tiled) {
     const int nT = (h->nf + kTileBlocks - 1) / kTileBlocks;
@@ -1057,7 +1059,11 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       // the forward substitution the destination rows with their source tiles.
       std::vector<std::vector<int>> by_level(nlev);
       for (int k = 0; k < nT; ++k) by_level[level[k]].push_back(k);
-      tc_upd_ptr.push_back(0); tc_fw_ptr.push_back(0);
+      tc_upd_ptr.push_back(0); tc_fw_ptr.push_back(0); tc_bw_ptr.push_back(0);
+      for (int k = 0; k < nT; ++k) if (col[k].empty()) tc_roots.push_back(k);   // backward substitution starts from the columns without rows
+      // backward: per level (of the SOURCE rows) the destination columns that have rows on it
+      std::vector<std::vector<std::pair<int, int>>> bw_by_level(nlev);   // (dest column, source row)
+      for (int k = 0; k < nT; ++k) for (int i : col[k]) bw_by_level[level[i]].push_back({k, i});
       for (int lv = 0; lv < nlev; ++lv) {
         bsnls_handle::TcLevel L{};
         L.col_begin = (int)tc_lev_cols.size(); L.pan_begin = (int)tc_pan_k.size(); L.upd_begin = (int)tc_upd_ptr.size() - 1; L.fw_begin = (int)tc_fw_ptr.size() - 1;
@@ -1083,6 +1089,15 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
         if (!fs.empty()) tc_fw_ptr.push_back((int)tc_fw_src.size());
         L.ncols = (int)tc_lev_cols.size() - L.col_begin; L.npan = (int)tc_pan_k.size() - L.pan_begin;
         L.nupd = (int)tc_upd_ptr.size() - 1 - L.upd_begin; L.nfw = (int)tc_fw_ptr.size() - 1 - L.fw_begin;
+        L.bw_begin = (int)tc_bw_ptr.size() - 1;
+        auto& bw = bw_by_level[lv];       // already grouped by destination column (k ascending), rows ascending
+        for (size_t q = 0; q < bw.size(); ++q) {
+          const int k = bw[q].first, i = bw[q].second;
+          if (q == 0 || bw[q - 1].first != k) { if (q) tc_bw_ptr.push_back((int)tc_bw_src.size()); tc_bw_col.push_back(k); tc_bw_tail.push_back(level[col[k][0]] == lv ? 1 : 0); }
+          tc_bw_src.push_back(tc_tile_off[(size_t)i * nT + k]); tc_bw_i.push_back(i);
+        }
+        if (!bw.empty()) tc_bw_ptr.push_back((int)tc_bw_src.size());
+        L.nbw = (int)tc_bw_ptr.size() - 1 - L.bw_begin;
         h->tc_levels.push_back(L);
       }
     }
@@ -1101,6 +1116,12 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     if (tc_col_rows.empty()) tc_col_rows.push_back(0);
     if (tc_upd_dst.empty()) { tc_upd_dst.push_back(0); tc_upd_a.push_back(0); tc_upd_b.push_back(0); }
     if (tc_fw_row.empty()) { tc_fw_row.push_back(0); tc_fw_tail.push_back(0); tc_fw_src.push_back(0); tc_fw_k.push_back(0); }
+    if (tc_bw_col.empty()) { tc_bw_col.push_back(0); tc_bw_tail.push_back(0); tc_bw_src.push_back(0); tc_bw_i.push_back(0); }
+    h->tc_nroots = (int)tc_roots.size();
+    CK(upload(h->d_tc_bw_ptr, tc_bw_ptr, s)); CK(upload(h->d_tc_bw_col, tc_bw_col, s)); CK(upload(h->d_tc_bw_tail, tc_bw_tail, s)); CK(upload(h->d_tc_bw_src, tc_bw_src, s));
+    CK(upload(h->d_tc_bw_i, tc_bw_i, s)); CK(upload(h->d_tc_roots, tc_roots, s));
+    h->TC.bw_ptr = h->d_tc_bw_ptr.as<int>(); h->TC.bw_col = h->d_tc_bw_col.as<int>(); h->TC.bw_tail = h->d_tc_bw_tail.as<int>(); h->TC.bw_src = h->d_tc_bw_src.as<long long>();
+    h->TC.bw_i = h->d_tc_bw_i.as<int>(); h->TC.roots = h->d_tc_roots.as<int>();
     CK(upload(h->d_tc_pan_k, tc_pan_k, s)); CK(upload(h->d_tc_pan_x, tc_pan_x, s)); CK(upload(h->d_tc_upd_ptr, tc_upd_ptr, s)); CK(upload(h->d_tc_upd_dst, tc_upd_dst, s));
     CK(upload(h->d_tc_upd_a, tc_upd_a, s)); CK(upload(h->d_tc_upd_b, tc_upd_b, s)); CK(upload(h->d_tc_fw_ptr, tc_fw_ptr, s)); CK(upload(h->d_tc_fw_row, tc_fw_row, s));
     CK(upload(h->d_tc_fw_tail, tc_fw_tail, s)); CK(upload(h->d_tc_fw_src, tc_fw_src, s)); CK(upload(h->d_tc_fw_k, tc_fw_k, s)); CK(upload(h->d_tc_lev_cols, tc_lev_cols, s));

@@ -36,6 +36,7 @@ struct TileChol {
   const int* pan_k; const int* pan_x;   // panel CTAs: column, index into col_rows (-1: the column has no tile below the diagonal)
   const int* upd_ptr; const long long* upd_dst; const long long* upd_a; const long long* upd_b;   // update destinations and their source tile pairs
   const int* fw_ptr; const int* fw_row; const int* fw_tail; const long long* fw_src; const int* fw_k;   // forward substitution
+  const int* bw_ptr; const int* bw_col; const int* bw_tail; const long long* bw_src; const int* bw_i; const int* roots;   // backward substitution
 };
 
 // ---- scatter the 3x3-block CSR system into the tiles (lower triangle), identity on the padding ----
@@ -312,15 +313,16 @@ __device__ __forceinline__ double tile_mv(const double* __restrict__ M, const do
   __syncthreads();
   return tot;
 }
-// y = M^T x: output c = tid >> 2, four lanes split the rows, shuffle reduction; every lane of the group holds the result
+// y = M^T x: output c = tid >> 2, four lanes split the rows (interleaved 16-byte pieces, so the four lanes of an output
+// read 64 contiguous bytes per instruction), shuffle reduction; every lane of the group holds the result
 __device__ __forceinline__ double tile_mv_t(const double* __restrict__ M, const double* xs, int tid) {
   const int c = tid >> 2, sub = tid & 3;
-  double v[16];
+  double2 v[8];
 #pragma unroll
-  for (int q = 0; q < 16; ++q) v[q] = M[c * kTS + 16 * sub + q];
+  for (int q = 0; q < 8; ++q) v[q] = reinterpret_cast<const double2*>(M + c * kTS)[4 * q + sub];
   double s = 0.0;
 #pragma unroll
-  for (int q = 0; q < 16; ++q) s += v[q] * xs[16 * sub + q];
+  for (int q = 0; q < 8; ++q) s += v[q].x * xs[8 * q + 2 * sub] + v[q].y * xs[8 * q + 2 * sub + 1];
   s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2);
   return s;
 }
@@ -365,23 +367,37 @@ __global__ void __launch_bounds__(256) tile_fwd_kernel(TileChol TC, int fw_begin
   }
   if (tid < kTS) TC.b[i * kTS + tid] = bi;
 }
-// backward, one level: x_k = W_k^T (y_k - sum_i L(i,k)^T x_i); the rows i of a column are its ancestors (done already)
-__global__ void __launch_bounds__(256) tile_bwd_kernel(TileChol TC, int col_begin, const LMState* st) {
+// backward, roots of the elimination forest (columns without rows): x_k = W_k^T y_k
+__global__ void __launch_bounds__(256) tile_bwd_first_kernel(TileChol TC, const LMState* st) {
   __shared__ double xs[kTS];
   if (!gate_run(st) || st->lin_fail) return;
-  const int k = TC.lev_cols[col_begin + blockIdx.x], tid = threadIdx.x, c = tid >> 2;
-  double t = TC.b[k * kTS + c];
-  for (int it = TC.col_ptr[k]; it < TC.col_ptr[k + 1]; ++it) {
-    const int i = TC.col_rows[it];
-    if (tid < kTS) xs[tid] = TC.b[i * kTS + tid];
-    __syncthreads();
-    t -= tile_mv_t(TC.T + TC.tile_off[(long long)i * TC.nT + k], xs, tid);
-    __syncthreads();
-  }
-  if ((tid & 3) == 0) xs[c] = t;
+  const int k = TC.roots[blockIdx.x], tid = threadIdx.x, c = tid >> 2;
+  if (tid < kTS) xs[tid] = TC.b[k * kTS + tid];
   __syncthreads();
   const double xk = tile_mv_t(TC.W + (size_t)k * kTileDoubles, xs, tid);
+  __syncthreads();
   if ((tid & 3) == 0) TC.b[k * kTS + c] = xk;
+}
+// backward, one level (top-down): the solution of the level's columns i is pushed to every column k that has a tile in
+// row i: t_k -= L(i,k)^T x_i. One CTA per destination column; the rows of a column are its ancestors, the parent the
+// lowest of them, so when the parent's level has been applied t_k is complete and x_k = W_k^T t_k follows in the same CTA.
+__global__ void __launch_bounds__(256) tile_bwd_kernel(TileChol TC, int bw_begin, const LMState* st) {
+  __shared__ double xs[kTS];
+  if (!gate_run(st) || st->lin_fail) return;
+  const int d = bw_begin + blockIdx.x, k = TC.bw_col[d], tid = threadIdx.x, c = tid >> 2;
+  double t = TC.b[k * kTS + c];
+  for (int it = TC.bw_ptr[d]; it < TC.bw_ptr[d + 1]; ++it) {
+    if (tid < kTS) xs[tid] = TC.b[TC.bw_i[it] * kTS + tid];
+    __syncthreads();
+    t -= tile_mv_t(TC.T + TC.bw_src[it], xs, tid);
+    __syncthreads();
+  }
+  if (TC.bw_tail[d]) {
+    if ((tid & 3) == 0) xs[c] = t;
+    __syncthreads();
+    t = tile_mv_t(TC.W + (size_t)k * kTileDoubles, xs, tid);
+  }
+  if ((tid & 3) == 0) TC.b[k * kTS + c] = t;
 }
 
 }  // namespace bsnls
