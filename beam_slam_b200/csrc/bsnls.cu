@@ -670,7 +670,9 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     // elimination tree instead of one tile column at a time.
     {
       const int nTf = h->nf / kTileBlocks;            // full tiles; a partial last tile stays last
-      if (nTf > kNdLeaf) {
+      int nd_leaf = kNdLeaf;                          // BSNLS_ND_LEAF: tuning knob (tiles per leaf of the dissection)
+      if (const char* ev = std::getenv("BSNLS_ND_LEAF")) nd_leaf = std::max(1, std::atoi(ev));
+      if (nTf > nd_leaf) {
         std::vector<int> pos(h->nf); for (int k = 0; k < h->nf; ++k) pos[orderv[k]] = k;
         std::vector<std::vector<int>> tadj(nTf);
         for (int u = 0; u < h->nf; ++u) {
@@ -681,7 +683,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
         std::vector<int> torder, idx(nTf, -1); torder.reserve(nTf);
         std::function<void(std::vector<int>&)> nd = [&](std::vector<int>& tl) {
           const int m = (int)tl.size();
-          if (m <= kNdLeaf) { torder.insert(torder.end(), tl.begin(), tl.end()); return; }
+          if (m <= nd_leaf) { torder.insert(torder.end(), tl.begin(), tl.end()); return; }
           for (int a = 0; a < m; ++a) idx[tl[a]] = a;
           const int mid = m / 2; int w = 0;
           for (int a = 0; a < mid; ++a) for (int v : tadj[tl[a]]) { const int b = idx[v]; if (b >= mid && b - a <= kNdShort) w = std::max(w, b - mid + 1); }

@@ -21,7 +21,7 @@ constexpr int kTileBlocks = 21;      // f-blocks per tile
 constexpr int kTU = 3 * kTileBlocks; // unknowns per tile (63); row/column 63 of every tile is an identity pad
 constexpr int kTLd = 68;             // shared-memory pitch of a tile (68 mod 16 = 4: conflict-free 64-bit fragment loads)
 constexpr int kTileDoubles = kTS * kTS;
-constexpr int kNdLeaf = 8, kNdShort = 6;   // nested dissection: tiles per leaf, longest edge (in tiles) that counts as band
+constexpr int kNdLeaf = 4, kNdShort = 6;   // nested dissection: tiles per leaf, longest edge (in tiles) that counts as band
 
 struct TileChol {
   int nT, n;
