@@ -75,8 +75,8 @@ struct bsnls_handle {
   struct TcLevel { int col_begin, ncols, pan_begin, npan, upd_begin, nupd, fw_begin, nfw, bw_begin, nbw; };   // one level of the elimination tree
   std::vector<TcLevel> tc_levels;
   DevMem d_tc_pan_k, d_tc_pan_x, d_tc_upd_ptr, d_tc_upd_dst, d_tc_upd_a, d_tc_upd_b, d_tc_fw_ptr, d_tc_fw_row, d_tc_fw_tail, d_tc_fw_src, d_tc_fw_k, d_tc_lev_cols, d_tc_bw_ptr, d_tc_bw_col, d_tc_bw_tail, d_tc_bw_src, d_tc_bw_i, d_tc_roots; int tc_nroots = 0;
-  bool chunk_fma = false; int chunk_max_slots = 1; DevMem d_syrk_plan, d_chunk_tile_off, d_pp_toff, d_pp_info;
-  int nchunks = 0; DevMem d_obs_slot, d_chunk_end, d_chunk_begin, d_chunk_nslots, d_chunk_part_off, d_chunk_cpart_off, d_pp_ptr, d_pp_off, d_pp_coff, d_part, d_cpart;
+  int chunk_max_slots = 1; DevMem d_syrk_plan, d_chunk_tile_off, d_pp_toff, d_pp_info;
+  int nchunks = 0; DevMem d_obs_slot, d_chunk_end, d_chunk_begin, d_chunk_nslots, d_pp_ptr, d_part;
   bool sparse = false, pcg = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
   // residual-block bookkeeping for bsnls_evaluate (program order)
   struct ResRef { int type; int idx; int row; };   // idx: sorted-observation id or generic-factor id
@@ -280,11 +280,10 @@ void EnqueueAssembleLocal(bsnls_handle* h) {  // phase D1, this rank's share: S 
   if (h->world > 1) cudaMemsetAsync(h->d_rhs.p, 0, sizeof(double) * P.nf_dim, h->stream);
   MARK(h, 6);
   if (h->nchunks) {
-    if (h->chunk_fma) LAUNCH_SMEM(h, chunk_accum_kernel, h->nchunks, 256, kChunkSmemBytes, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), st);
-    else LAUNCH_SMEM(h, chunk_syrk_kernel, h->nchunks, 256, syrk_smem_bytes(h->chunk_max_slots), P, h->d_Vrec.as<double>(), h->d_lmz.as<double>(), h->d_part.as<double>(), st);
+    LAUNCH_SMEM(h, chunk_syrk_kernel, h->nchunks, 256, syrk_smem_bytes(h->chunk_max_slots), P, h->d_Vrec.as<double>(), h->d_lmz.as<double>(), h->d_part.as<double>(), st);
   }
-  if (h->npairs && h->nchunks) LAUNCH(h, pair_reduce_kernel, BlocksFor(h->npairs, 4), 144, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), h->d_poseH.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
-  else if (h->npairs) LAUNCH(h, pair_kernel, BlocksFor(h->npairs, 4), 128, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_cpart.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
+  if (h->npairs && h->nchunks) LAUNCH(h, pair_reduce_kernel, BlocksFor(h->npairs, 4), 144, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_lmz.as<double>(), h->d_poseH.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
+  else if (h->npairs) LAUNCH(h, pair_kernel, BlocksFor(h->npairs, 4), 128, P, h->d_Vrec.as<double>(), h->d_lmz.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
   MARK(h, 7);
 }
 void EnqueueAssembleFinish(bsnls_handle* h, const Options& o) {  // generic-factor rows of S, gradient into rhs, damping
@@ -450,7 +449,6 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
   if ((e = cudaFuncSetAttribute(chunk_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, syrk_smem_bytes(kChunkSlots))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(tile_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * kPanelSmemDoubles))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(tile_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * 2 * kTS * kTLd))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
-  if ((e = cudaFuncSetAttribute(chunk_accum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kChunkSmemBytes)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   for (auto& ev : h->pev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   *out = h;
   return BSNLS_OK;
@@ -757,10 +755,9 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   // ---- chunks: consecutive landmarks whose poses fit kChunkSlots slots are accumulated on chip by one CTA ----
   std::vector<unsigned short> obs_slot(nobs_local, 0xFFFF);
   std::vector<int> chunk_begin, chunk_end, chunk_nslots, chunk_pose;      // landmark range [begin, end) of each chunk
-  std::vector<long long> chunk_part_off, chunk_cpart_off, chunk_tile_off;
+  std::vector<long long> chunk_tile_off;
   long long tile_size = 0;
   std::vector<char> wide(h->ne, 0);
-  long long part_size = 0, cpart_size = 0;
   {
     std::vector<int> stamp(h->np, -1), cur_poses;
     // chunk size: about 1400 chunks (~5 waves of 2 CTAs x 148 SMs) balances the tail of the last wave against the
@@ -776,10 +773,8 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       for (int e = c_begin; e < end; ++e) if (!wide[e]) for (int k = lm_ptr_local[e]; k < lm_ptr_local[e + 1]; ++k) obs_slot[k] = (unsigned short)(stamp[s_pose[k]] | (((e - c_begin) % kSyrkStageLm) << 8));
       chunk_begin.push_back(c_begin); chunk_end.push_back(end); chunk_nslots.push_back((int)cur_poses.size());
       for (int q = 0; q < kChunkSlots; ++q) chunk_pose.push_back(q < (int)cur_poses.size() ? cur_poses[q] : -1);
-      chunk_part_off.push_back(part_size); chunk_cpart_off.push_back(cpart_size); chunk_tile_off.push_back(tile_size);
+      chunk_tile_off.push_back(tile_size);
       { const long long nt2 = (6 * (long long)cur_poses.size() + 8) >> 3; tile_size += nt2 * (nt2 + 1) / 2 * 64; }
-      const long long ns = (long long)cur_poses.size();
-      part_size += ns * (ns + 1) / 2 * 36; cpart_size += ns * 6;
       for (int pz : cur_poses) stamp[pz] = -1;
       cur_poses.clear(); c_begin = end; c_obs = 0; c_kmax = 0;
     };
@@ -808,11 +803,11 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   if (std::getenv("BSNLS_DEBUG")) {
     long long slots = 0, nwide = 0; for (int v : chunk_nslots) slots += v; for (char w : wide) nwide += w;
     std::fprintf(stderr, "[bsnls] rank %d: %d landmarks, %d obs, %d poses, %d pairs, %d chunks (avg %.1f slots, %.1f landmarks), %lld wide landmarks, partial buffer %.1f MB\n",
-                 h->rank, h->ne, nobs_local, h->np, h->npairs, h->nchunks, h->nchunks ? (double)slots / h->nchunks : 0.0, h->nchunks ? (double)h->ne / h->nchunks : 0.0, nwide, part_size * 8e-6);
+                 h->rank, h->ne, nobs_local, h->np, h->npairs, h->nchunks, h->nchunks ? (double)slots / h->nchunks : 0.0, h->nchunks ? (double)h->ne / h->nchunks : 0.0, nwide, tile_size * 8e-6);
   }
   // ---- per pair: partial blocks produced by the chunks, and items of the wide landmarks ----
   std::vector<int> pair_ptr(h->npairs + 1, 0), item_i, item_j, pp_ptr(h->npairs + 1, 0);
-  std::vector<long long> pp_off, pp_coff, pp_toff; std::vector<int> pp_info;
+  std::vector<long long> pp_toff; std::vector<int> pp_info;
   {
     std::vector<int> cnt(h->npairs, 0), pcnt(h->npairs, 0);
     for (int e = 0; e < h->ne; ++e) {
@@ -830,7 +825,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     }
     for (int k = 0; k < h->npairs; ++k) { pair_ptr[k + 1] = pair_ptr[k] + cnt[k]; pp_ptr[k + 1] = pp_ptr[k] + pcnt[k]; }
     const int64_t nitems = pair_ptr[h->npairs];
-    item_i.resize(nitems); item_j.resize(nitems); pp_off.resize(pp_ptr[h->npairs]); pp_coff.resize(pp_ptr[h->npairs]); pp_toff.resize(pp_ptr[h->npairs]); pp_info.resize(pp_ptr[h->npairs]);
+    item_i.resize(nitems); item_j.resize(nitems); pp_toff.resize(pp_ptr[h->npairs]); pp_info.resize(pp_ptr[h->npairs]);
     std::vector<int> cur(pair_ptr.begin(), pair_ptr.end() - 1), pcur(pp_ptr.begin(), pp_ptr.end() - 1);
     for (int e = 0; e < h->ne; ++e) {
       if (!wide[e]) continue;
@@ -850,8 +845,6 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
         auto kit = key_id.find(key_of(chunk_pose[(size_t)c * kChunkSlots + A], chunk_pose[(size_t)c * kChunkSlots + B]));
         if (kit == key_id.end()) continue;
         const int id = kit->second;
-        pp_off[pcur[id]] = chunk_part_off[c] + (long long)q * 36;
-        pp_coff[pcur[id]] = A == B ? chunk_cpart_off[c] + (long long)A * 6 : -1;
         pp_toff[pcur[id]] = chunk_tile_off[c]; pp_info[pcur[id]] = A | (B << 8) | (ns << 16);
         pcur[id]++;
       }
@@ -1001,12 +994,10 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_pair_a, h->pair_a, s)); CK(upload(h->d_pair_b, h->pair_b, s)); CK(upload(h->d_pair_ptr, pair_ptr, s));
   CK(upload(h->d_item_i, item_i, s)); CK(upload(h->d_item_j, item_j, s));
   CK(upload(h->d_obs_slot, obs_slot, s)); CK(upload(h->d_chunk_begin, chunk_begin, s)); CK(upload(h->d_chunk_end, chunk_end, s)); CK(upload(h->d_chunk_nslots, chunk_nslots, s));
-  CK(upload(h->d_chunk_part_off, chunk_part_off, s)); CK(upload(h->d_chunk_cpart_off, chunk_cpart_off, s));
-  CK(upload(h->d_pp_ptr, pp_ptr, s)); CK(upload(h->d_pp_off, pp_off, s)); CK(upload(h->d_pp_coff, pp_coff, s));
-  h->chunk_fma = std::getenv("BSNLS_CHUNK_FMA") != nullptr;   // scalar-FMA chunk kernel (pair-block partial format), kept for comparison
+  CK(upload(h->d_pp_ptr, pp_ptr, s));
   { std::vector<int> plan((kSyrkMaxNt + 1) * 8 * kSyrkMaxStrips); syrk_build_plan(plan.data()); CK(upload(h->d_syrk_plan, plan, s)); }
   CK(upload(h->d_chunk_tile_off, chunk_tile_off, s)); CK(upload(h->d_pp_toff, pp_toff, s)); CK(upload(h->d_pp_info, pp_info, s));
-  CK(h->d_part.alloc(sizeof(double) * (size_t)std::max(part_size, tile_size))); CK(h->d_cpart.alloc(sizeof(double) * (size_t)cpart_size));
+  CK(h->d_part.alloc(sizeof(double) * (size_t)tile_size));
   CK(upload(h->d_fg_ptr, fg_ptr, s)); CK(upload(h->d_fg_fac, fg_fac, s)); CK(upload(h->d_fg_lb, fg_lb, s));
   CK(upload(h->d_gd_row, h->gd_row, s)); CK(upload(h->d_gd_col, h->gd_col, s)); CK(upload(h->d_gd_ptr, gd_ptr, s));
   CK(upload(h->d_gd_fac, gd_fac, s)); CK(upload(h->d_gd_bi, gd_bi, s)); CK(upload(h->d_gd_bj, gd_bj, s)); CK(upload(h->d_is_pose, is_pose, s));
@@ -1171,9 +1162,8 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   P.num_pairs = h->npairs; P.pair_a = h->d_pair_a.as<int>(); P.pair_b = h->d_pair_b.as<int>(); P.pair_ptr = h->d_pair_ptr.as<int>();
   P.item_i = h->d_item_i.as<int>(); P.item_j = h->d_item_j.as<int>();
   P.num_chunks = h->nchunks; P.obs_slot = h->d_obs_slot.as<unsigned short>(); P.syrk_plan = h->d_syrk_plan.as<int>(); P.chunk_begin = h->d_chunk_begin.as<int>(); P.chunk_end = h->d_chunk_end.as<int>(); P.chunk_nslots = h->d_chunk_nslots.as<int>();
-  P.chunk_part_off = h->d_chunk_part_off.as<long long>(); P.chunk_cpart_off = h->d_chunk_cpart_off.as<long long>();
-  P.pp_ptr = h->d_pp_ptr.as<int>(); P.pp_off = h->d_pp_off.as<long long>(); P.pp_coff = h->d_pp_coff.as<long long>();
-  P.tile_mode = h->chunk_fma ? 0 : 1; P.chunk_tile_off = h->d_chunk_tile_off.as<long long>(); P.pp_toff = h->d_pp_toff.as<long long>(); P.pp_info = h->d_pp_info.as<int>();
+  P.pp_ptr = h->d_pp_ptr.as<int>();
+  P.chunk_tile_off = h->d_chunk_tile_off.as<long long>(); P.pp_toff = h->d_pp_toff.as<long long>(); P.pp_info = h->d_pp_info.as<int>();
   P.fg_ptr = h->d_fg_ptr.as<int>(); P.fg_fac = h->d_fg_fac.as<int>(); P.fg_lb = h->d_fg_lb.as<int>();
   P.num_gdest = h->ngdest; P.gd_row = h->d_gd_row.as<int>(); P.gd_col = h->d_gd_col.as<int>(); P.gd_ptr = h->d_gd_ptr.as<int>();
   P.gd_fac = h->d_gd_fac.as<int>(); P.gd_bi = h->d_gd_bi.as<int>(); P.gd_bj = h->d_gd_bj.as<int>();

@@ -13,15 +13,13 @@ namespace bsnls {
 
 constexpr int kJRec = 16;   // per observation, one 128-byte line: E[6] (2x3 wrt landmark) | r[2] | Fq[6] (2x3 wrt the q tangent) | ts | 0
                             // the 2x3 block wrt t is ts * E with ts = -1 (0 when t is held constant): see reprojection_evaluate_tab
-constexpr int kVRec = 24;   // per observation: V[18] (6x3 = F^T E C) | c[6] (= V z)
+constexpr int kVRec = 18;   // per observation: V (6x3 = F^T E C), 144 bytes. c = V z is formed where it is needed from lm_z
 constexpr int kGfMaxBlocks = 10, kGfMaxRes = 15, kGfMaxAmbient = 32;
 constexpr int kChunkSlots = 22;        // poses per chunk: 22*23/2 = 253 pair blocks <= 256 threads
 constexpr int kChunkMinObs = 100000;   // below this many observations per shard the item-list path is used instead
 constexpr int kChunkMaxObs = 4096;     // observations per chunk (load balance vs. partial-block traffic)
 constexpr int kChunkMaxLm = 4096;      // landmarks per chunk (bounds the stage table of chunk_syrk_kernel)
 constexpr int kChunkSlack = 2;          // a chunk closes when its pose set exceeds (longest track in it) + slack: keeps most pairs present
-constexpr int kChunkStageDoubles = 11008;   // staging buffer (86 KiB): two CTAs per SM
-constexpr int kChunkSmemBytes = kChunkStageDoubles * 8;
 
 struct LMState {
   // trust region (ceres LevenbergMarquardtStrategy)
@@ -60,16 +58,15 @@ struct DeviceProblem {
   const int* gf_joff; const int* gf_roff;     // offsets into gfJ (nres x 3*nblk row-major) and gfR
   // S pair blocks (pose a <= pose b) and their items
   int num_pairs; const int* pair_a; const int* pair_b; const int* pair_ptr; const int* item_i; const int* item_j;
-  // chunks: landmark ranges accumulated on chip (chunk_accum_kernel); per observation the slot of its pose in its chunk
+  // chunks: landmark ranges accumulated on chip (chunk_syrk_kernel); per observation the slot of its pose in its chunk
   // (255: landmark handled through the item list); per pair the partial blocks the chunks produced
     // pose-major evaluation: items (pose, begin, end, 0) over the pose-sorted observation list and that list's inputs
   int num_eval_items; const int* obs_pm /* position of a (landmark-major) observation in the pose-major list = its Jacobian record */; const int4* eval_items; const int* eval_item_ptr; const int* pm_lm_off; const int* pm_cam; const double* pm_pixel;
   int num_chunks; const unsigned short* obs_slot /* slot | (landmark - chunk begin) % 16 << 8; slot 255 = not in a chunk */; const int* syrk_plan; const int* chunk_begin; const int* chunk_end; const int* chunk_nslots;
-  const long long* chunk_part_off; const long long* chunk_cpart_off;
-  const int* pp_ptr; const long long* pp_off; const long long* pp_coff;
+  const int* pp_ptr;
   // tile format of the tensor-core chunk kernel: raw 8x8 tiles of sum W W^T per chunk; per partial-list entry the
   // chunk's tile offset and (slot A | slot B << 8 | slots << 16)
-  int tile_mode; const long long* chunk_tile_off; const long long* pp_toff; const int* pp_info;
+  const long long* chunk_tile_off; const long long* pp_toff; const int* pp_info;
   // generic-factor contributions: per f-block (gradient / column norms) and per 3x3 destination of S
   const int* fg_ptr; const int* fg_fac; const int* fg_lb;            // CSR over f-blocks (nf)
   int num_gdest; const int* gd_row; const int* gd_col; const int* gd_ptr; const int* gd_fac; const int* gd_bi; const int* gd_bj;
@@ -416,16 +413,14 @@ __global__ void __launch_bounds__(256) landmark_kernel(DeviceProblem P, const do
       F0[0] = f0.x; F0[1] = f0.y; F0[2] = f1.x; F0[3] = ts * E0[0]; F0[4] = ts * E0[1]; F0[5] = ts * E0[2];
       F1[0] = f1.y; F1[1] = f2.x; F1[2] = f2.y; F1[3] = ts * E1[0]; F1[4] = ts * E1[1]; F1[5] = ts * E1[2]; }
     double2* out = reinterpret_cast<double2*>(Vrec + (size_t)o * kVRec);
-    double v[24];
+    double v[18];
 #pragma unroll
     for (int a = 0; a < 6; ++a) {
       const double w0 = F0[a] * E0[0] + F1[a] * E1[0], w1 = F0[a] * E0[1] + F1[a] * E1[1], w2 = F0[a] * E0[2] + F1[a] * E1[2];
-      const double v0 = w0 * i00, v1 = w0 * i10 + w1 * i11, v2 = w0 * i20 + w1 * i21 + w2 * i22;
-      v[3 * a] = v0; v[3 * a + 1] = v1; v[3 * a + 2] = v2;
-      v[18 + a] = v0 * z0 + v1 * z1 + v2 * z2;
+      v[3 * a] = w0 * i00; v[3 * a + 1] = w0 * i10 + w1 * i11; v[3 * a + 2] = w0 * i20 + w1 * i21 + w2 * i22;
     }
 #pragma unroll
-    for (int k = 0; k < 12; ++k) out[k] = make_double2(v[2 * k], v[2 * k + 1]);
+    for (int k = 0; k < 9; ++k) out[k] = make_double2(v[2 * k], v[2 * k + 1]);
   }
 }
 
@@ -490,129 +485,12 @@ __global__ void __launch_bounds__(256) grad_norm_kernel(DeviceProblem P, const d
 }
 
 // ===================================================================================================
-// K5b (on-chip): S -= sum_l V_a V_b^T accumulated per CHUNK of landmarks. One CTA per chunk; the poses of the chunk
-// occupy <= 22 slots, every (slot A <= slot B) pair block is owned by one thread (36 register accumulators), so
-// there are no conflicts and no atomics: a thread walks the landmarks of the chunk in order and adds V_A V_B^T
-// whenever the landmark is seen by both poses. V records are staged batch-wise in shared memory (each record is
-// read from HBM exactly once, coalesced). When fewer than 128 pair blocks exist, several thread groups take
-// alternate landmarks and are combined in a fixed order. Output: partial pair blocks + per-slot sums of c = V z,
-// reduced across chunks by pair_kernel.
-// ===================================================================================================
-__global__ void __launch_bounds__(256, 2) chunk_accum_kernel(DeviceProblem P, const double* __restrict__ Vrec,
-                                                          double* __restrict__ part, double* __restrict__ cpart,
-                                                          const LMState* st) {
-  extern __shared__ __align__(16) double stage[];   // [landmark in batch][slot][25]  (24 used; odd stride: conflict-free)
-  __shared__ unsigned int mask[512];
-  __shared__ unsigned char pA[256], pB[256];
-  if (!gate_run(st)) return;
-  const int c = blockIdx.x, tid = threadIdx.x;
-  const int ns = P.chunk_nslots[c], npair = ns * (ns + 1) / 2;
-  const int groups = max(1, 256 / npair);
-  const int l_begin = P.chunk_begin[c], l_end = P.chunk_end[c];
-  if (tid < npair) {   // q -> (A <= B), row-major over the upper triangle
-    int q = tid, A = 0;
-    while (q >= ns - A) { q -= ns - A; ++A; }
-    pA[tid] = (unsigned char)A; pB[tid] = (unsigned char)(A + q);
-  }
-  __syncthreads();
-  const int grp = tid / npair, q = tid - grp * npair;
-  const bool worker = grp < groups;
-  const int A = worker ? pA[q] : 0, B = worker ? pB[q] : 0;
-  double acc[36], cacc[6];
-#pragma unroll
-  for (int k = 0; k < 36; ++k) acc[k] = 0.0;
-#pragma unroll
-  for (int k = 0; k < 6; ++k) cacc[k] = 0.0;
-  const int lstride = ns * 25;
-  const int batch = min(512, kChunkStageDoubles / lstride);
-  for (int l0 = l_begin; l0 < l_end; l0 += batch) {
-    const int l1 = min(l_end, l0 + batch);
-    const int o0 = P.lm_ptr[l0], o1 = P.lm_ptr[l1];
-    for (int l = tid; l < l1 - l0; l += 256) mask[l] = 0u;
-    __syncthreads();
-    // staging: 12 lanes per record (one double2 each), 21 records in flight per sweep, 4 sweeps unrolled so that the
-    // independent global loads overlap (8 warps per SM cannot hide HBM latency otherwise)
-    if (tid < 252) {
-      const int sub = tid % 12, oo = tid / 12;
-      for (int ob = o0 + oo; ob < o1; ob += 84) {
-        double2 v[4]; int sl[4], ll[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int o = ob + 21 * u;
-          const bool ok = o < o1;
-          sl[u] = ok ? (int)(P.obs_slot[o] & 255) : 255;
-          ll[u] = ok ? P.obs_lm[o] - l0 : 0;
-          v[u] = ok ? reinterpret_cast<const double2*>(Vrec + (size_t)o * kVRec)[sub] : make_double2(0.0, 0.0);
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          if (sl[u] == 255) continue;
-          double* dst = stage + ll[u] * lstride + sl[u] * 25 + 2 * sub;
-          dst[0] = v[u].x; dst[1] = v[u].y;
-          if (sub == 0) atomicOr(&mask[ll[u]], 1u << sl[u]);
-        }
-      }
-    }
-    __syncthreads();
-    if (worker) {
-      for (int l = grp; l < l1 - l0; l += groups) {
-        const unsigned int m = mask[l];
-        if (!((m >> A) & 1u) || !((m >> B) & 1u)) continue;
-        const double* va = stage + l * lstride + A * 25;
-        const double* vb = stage + l * lstride + B * 25;
-        double Vb[18];
-#pragma unroll
-        for (int k = 0; k < 18; ++k) Vb[k] = vb[k];
-#pragma unroll
-        for (int i = 0; i < 6; ++i) {
-          const double a0 = va[3 * i], a1 = va[3 * i + 1], a2 = va[3 * i + 2];   // rows of V_A are streamed (register budget)
-#pragma unroll
-          for (int j = 0; j < 6; ++j) acc[6 * i + j] += a0 * Vb[3 * j] + a1 * Vb[3 * j + 1] + a2 * Vb[3 * j + 2];
-        }
-        if (A == B) {
-#pragma unroll
-          for (int k = 0; k < 6; ++k) cacc[k] += va[18 + k];
-        }
-      }
-    }
-    __syncthreads();
-  }
-  // combine the thread groups in a fixed order (group 0 + group 1 + ...) and write the chunk's partial blocks
-  double* out = part + P.chunk_part_off[c];
-  double* cout = cpart + P.chunk_cpart_off[c];
-  for (int g = 1; g < groups; ++g) {
-    if (worker && grp == g) {
-#pragma unroll
-      for (int k = 0; k < 36; ++k) stage[q * 43 + k] = acc[k];
-#pragma unroll
-      for (int k = 0; k < 6; ++k) stage[q * 43 + 36 + k] = cacc[k];
-    }
-    __syncthreads();
-    if (worker && grp == 0) {
-#pragma unroll
-      for (int k = 0; k < 36; ++k) acc[k] += stage[q * 43 + k];
-#pragma unroll
-      for (int k = 0; k < 6; ++k) cacc[k] += stage[q * 43 + 36 + k];
-    }
-    __syncthreads();
-  }
-  if (worker && grp == 0) {
-#pragma unroll
-    for (int k = 0; k < 36; ++k) out[(size_t)q * 36 + k] = acc[k];
-    if (A == B) {
-#pragma unroll
-      for (int k = 0; k < 6; ++k) cout[A * 6 + k] = cacc[k];
-    }
-  }
-}
-
-// ===================================================================================================
 // K5b (tensor): the chunk accumulation as a symmetric rank-k update on the FP64 tensor cores. For a chunk with ns pose
 // slots, stack the V records of landmark l into a (6 ns + 1) x 3 block column W_l (rows of absent slots zero, last
 // row = z_l^T); then  sum_l W_l W_l^T  holds every pair block sum_l V_A V_B^T and, in its last column, sum_l V_A z_l
 // (the Schur right-hand side). W is staged in shared memory 32 landmarks (96 columns) at a time; each warp owns a
 // contiguous range of the upper-triangular 8x8 tiles and issues mma.sync.m8n8k4.f64 (DMMA) on them.
-// Deterministic: fixed tile ownership, fixed k order. Same outputs as chunk_accum_kernel.
+// Deterministic: fixed tile ownership, fixed k order.
 // ===================================================================================================
 constexpr int kSyrkStageLm = 16;                 // landmarks per stage
 constexpr int kSyrkKB = 3 * kSyrkStageLm;        // 48 columns of W per stage = 12 k-steps
@@ -800,7 +678,7 @@ __device__ __forceinline__ void store_sub3(double* S, int ld, int rt, int ct, co
   else { for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) S[(size_t)(rt + i) * ld + ct + j] = B[3 * i + j]; }
 }
 __global__ void __launch_bounds__(128) pair_kernel(DeviceProblem P, const double* __restrict__ Vrec,
-                                                   const double* __restrict__ part, const double* __restrict__ cpart,
+                                                   const double* __restrict__ lm_z,
                                                    const double* __restrict__ pose_H, const double* __restrict__ grad,
                                                    double* __restrict__ S, double* __restrict__ rhs, const LMState* st) {
   if (!gate_run(st)) return;
@@ -826,20 +704,10 @@ __global__ void __launch_bounds__(128) pair_kernel(DeviceProblem P, const double
 #pragma unroll
       for (int j = 0; j < 6; ++j)
         acc[6 * i + j] += Vi[3 * i] * Vj[3 * j] + Vi[3 * i + 1] * Vj[3 * j + 1] + Vi[3 * i + 2] * Vj[3 * j + 2];
-    if (oi == oj) {
+    if (oi == oj) {   // c = V z of this observation: the Schur right-hand side
+      const double* z = lm_z + 3 * (size_t)P.obs_lm[oi];
 #pragma unroll
-      for (int k = 0; k < 3; ++k) { const double2 u = vi[9 + k]; cacc[2 * k] += u.x; cacc[2 * k + 1] += u.y; }
-    }
-  }
-  // partial blocks accumulated on chip by the chunks that contain both poses (fixed list order)
-  for (int it = P.pp_ptr[pb] + lane; it < P.pp_ptr[pb + 1]; it += 32) {
-    const double2* pp = reinterpret_cast<const double2*>(part + P.pp_off[it]);
-#pragma unroll
-    for (int k = 0; k < 18; ++k) { const double2 u = pp[k]; acc[2 * k] += u.x; acc[2 * k + 1] += u.y; }
-    const long long co = P.pp_coff[it];
-    if (co >= 0) {
-#pragma unroll
-      for (int k = 0; k < 6; ++k) cacc[k] += cpart[co + k];
+      for (int k = 0; k < 6; ++k) cacc[k] += Vi[3 * k] * z[0] + Vi[3 * k + 1] * z[1] + Vi[3 * k + 2] * z[2];
     }
   }
 #pragma unroll
@@ -880,7 +748,7 @@ __global__ void __launch_bounds__(128) pair_kernel(DeviceProblem P, const double
 // contributions of wide landmarks from the item list, subtracts from sum F^T F on the diagonal blocks and writes
 // S (dense lower triangle or 3x3 block-sparse) and the reduced right-hand side. 4 pairs per 144-thread CTA.
 __global__ void __launch_bounds__(144) pair_reduce_kernel(DeviceProblem P, const double* __restrict__ Vrec,
-                                                          const double* __restrict__ part, const double* __restrict__ cpart,
+                                                          const double* __restrict__ part, const double* __restrict__ lm_z,
                                                           const double* __restrict__ pose_H, double* __restrict__ S,
                                                           double* __restrict__ rhs, const LMState* st) {
   if (!gate_run(st)) return;
@@ -889,7 +757,7 @@ __global__ void __launch_bounds__(144) pair_reduce_kernel(DeviceProblem P, const
   const int a = P.pair_a[pb], b = P.pair_b[pb];
   const int i = e / 6, j = e - 6 * i;
   double acc = 0.0, cacc = 0.0;
-  if (P.tile_mode) {
+  {
     for (int it = P.pp_ptr[pb]; it < P.pp_ptr[pb + 1]; ++it) {
       const int info = P.pp_info[it], A = info & 255, B = (info >> 8) & 255, ns = info >> 16;
       const int nt = (6 * ns + 8) >> 3;
@@ -903,17 +771,12 @@ __global__ void __launch_bounds__(144) pair_reduce_kernel(DeviceProblem P, const
         cacc += tp[(size_t)(I * nt - I * (I - 1) / 2 + (J - I)) * 64 + (r & 7) * 8 + (c & 7)];
       }
     }
-  } else {
-    for (int it = P.pp_ptr[pb]; it < P.pp_ptr[pb + 1]; ++it) {
-      acc += part[P.pp_off[it] + e];
-      if (e < 6 && P.pp_coff[it] >= 0) cacc += cpart[P.pp_coff[it] + e];
-    }
   }
   for (int it = P.pair_ptr[pb]; it < P.pair_ptr[pb + 1]; ++it) {   // wide landmarks
     const int oi = P.item_i[it], oj = P.item_j[it];
     const double* vi = Vrec + (size_t)oi * kVRec + 3 * i; const double* vj = Vrec + (size_t)oj * kVRec + 3 * j;
     acc += vi[0] * vj[0] + vi[1] * vj[1] + vi[2] * vj[2];
-    if (e < 6 && oi == oj) cacc += Vrec[(size_t)oi * kVRec + 18 + e];
+    if (e < 6 && oi == oj) { const double* z = lm_z + 3 * (size_t)P.obs_lm[oi]; const double* ve = Vrec + (size_t)oi * kVRec + 3 * e; cacc += ve[0] * z[0] + ve[1] * z[1] + ve[2] * z[2]; }
   }
   const int sa = i / 3, sb = j / 3, ii = i - 3 * sa, jj = j - 3 * sb;
   const int ta = (sa ? P.pose_t_tan[a] : P.pose_q_tan[a]), tb = (sb ? P.pose_t_tan[b] : P.pose_q_tan[b]);
