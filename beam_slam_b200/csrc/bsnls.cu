@@ -75,6 +75,7 @@ struct bsnls_handle {
   struct TcLevel { int col_begin, ncols, pan_begin, npan, upd_begin, nupd, fw_begin, nfw, bw_begin, nbw; };   // one level of the elimination tree
   std::vector<TcLevel> tc_levels;
   DevMem d_tc_pan_k, d_tc_pan_x, d_tc_upd_ptr, d_tc_upd_dst, d_tc_upd_a, d_tc_upd_b, d_tc_fw_ptr, d_tc_fw_row, d_tc_fw_tail, d_tc_fw_src, d_tc_fw_k, d_tc_lev_cols, d_tc_bw_ptr, d_tc_bw_col, d_tc_bw_tail, d_tc_bw_src, d_tc_bw_i, d_tc_roots; int tc_nroots = 0;
+  long long nlow = 0; DevMem d_low_slot, d_low_slot_t, d_xsend, d_xrecv;   // sharded solve: lower-triangular blocks of S, packed exchange buffers
   int chunk_max_slots = 1; DevMem d_syrk_plan, d_chunk_tile_off, d_pp_toff, d_pp_info;
   int nchunks = 0; DevMem d_obs_slot, d_chunk_end, d_chunk_begin, d_chunk_nslots, d_pp_ptr, d_part;
   bool sparse = false, pcg = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
@@ -238,6 +239,16 @@ int EnqueueExchange(bsnls_handle* h, bool with_system) {
   // Pose gradient / column norms go out of place: the kernels that rebuild them are gated by the device state, the
   // collective is not, so it must be idempotent when they did not run. S and rhs are rebuilt on every pass; red[] is
   // only read by the (equally gated) controller.
+  if (h->sparse) {   // one packed buffer, one collective (lower-triangular blocks of S only)
+    const ExchangeLayout X{h->nlow * 9, P.nf_dim, h->world, h->rank, RED_NUM, kRedLocalMax, h->d_low_slot.as<int>(), h->d_low_slot_t.as<int>()};
+    const long long total = X.nS + 3LL * P.nf_dim + RED_NUM + h->world, first = with_system ? 0 : X.nS + P.nf_dim;
+    const unsigned grid = (unsigned)((total - first + 255) / 256);
+    LAUNCH(h, pack_exchange_kernel, grid, 256, X, first, h->d_S.as<double>(), h->d_rhs.as<double>(), h->d_gradL.as<double>(), h->d_colsqL.as<double>(), h->d_red.as<double>(), h->d_xsend.as<double>());
+    const int rc1 = Nccl().AllReduce(h->d_xsend.as<double>() + first, h->d_xrecv.as<double>() + first, (size_t)(total - first), kNcclFloat64, kNcclSum, h->comm, h->stream);
+    if (rc1 != kNcclSuccess) return h->fail(BSNLS_ERR_CUDA, "ncclAllReduce(exchange): %s", Nccl().GetErrorString(rc1));
+    LAUNCH(h, unpack_exchange_kernel, grid, 256, X, first, h->d_xrecv.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), h->d_gradS.as<double>(), h->d_colsqS.as<double>(), h->d_red.as<double>());
+    return BSNLS_OK;
+  }
   Nccl().GroupStart();
   int rc = kNcclSuccess;
   if (with_system) {
@@ -927,6 +938,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     if (pose_t_tan[a] >= 0) for (int k = 0; k < 3; ++k) is_pose[pose_t_tan[a] - ne_dim + k] = 1;
   }
   // ---- block-sparse pattern of the reduced system (3x3 blocks over f-blocks, full symmetric) ----
+  std::vector<int> low_slot, low_slot_t;
   std::vector<int> diag_slot(h->nf, 0), pair_slot((size_t)h->npairs * 8, -1), gd_slot((size_t)h->ngdest * 2, -1);
   h->bsr_rowptr.assign(h->nf + 1, 0); h->bsr_col.clear(); h->nnzb = 0;
   {
@@ -957,6 +969,12 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       }
     }
     for (int d = 0; d < h->ngdest; ++d) { gd_slot[2 * (size_t)d] = slot(h->gd_row[d], h->gd_col[d]); gd_slot[2 * (size_t)d + 1] = slot(h->gd_col[d], h->gd_row[d]); }
+    if (h->world > 1)
+      for (int r = 0; r < h->nf; ++r)
+        for (int k = h->bsr_rowptr[r]; k < h->bsr_rowptr[r + 1]; ++k) {
+          const int c = h->bsr_col[k];
+          if (c <= r) { low_slot.push_back(k); low_slot_t.push_back(c < r ? slot(c, r) : -1); }
+        }
   }
   // residual order for bsnls_evaluate
   h->res_order.assign(total, {0, 0, 0});
@@ -1000,6 +1018,12 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(h->d_part.alloc(sizeof(double) * (size_t)tile_size));
   CK(upload(h->d_fg_ptr, fg_ptr, s)); CK(upload(h->d_fg_fac, fg_fac, s)); CK(upload(h->d_fg_lb, fg_lb, s));
   CK(upload(h->d_gd_row, h->gd_row, s)); CK(upload(h->d_gd_col, h->gd_col, s)); CK(upload(h->d_gd_ptr, gd_ptr, s));
+  h->nlow = (long long)low_slot.size();
+  if (h->world > 1 && h->sparse) {
+    CK(upload(h->d_low_slot, low_slot, s)); CK(upload(h->d_low_slot_t, low_slot_t, s));
+    const size_t xn = 9 * (size_t)h->nlow + 3 * (size_t)nf_dim + RED_NUM + h->world;
+    CK(h->d_xsend.alloc(sizeof(double) * xn)); CK(h->d_xrecv.alloc(sizeof(double) * xn));
+  }
   CK(upload(h->d_gd_fac, gd_fac, s)); CK(upload(h->d_gd_bi, gd_bi, s)); CK(upload(h->d_gd_bj, gd_bj, s)); CK(upload(h->d_is_pose, is_pose, s));
   CK(upload(h->d_bsr_rowptr, h->bsr_rowptr, s)); CK(upload(h->d_bsr_col, h->bsr_col, s)); CK(upload(h->d_diag_slot, diag_slot, s));
   CK(upload(h->d_pair_slot, pair_slot, s)); CK(upload(h->d_gd_slot, gd_slot, s));

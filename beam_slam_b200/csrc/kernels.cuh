@@ -799,6 +799,46 @@ __global__ void __launch_bounds__(144) pair_reduce_kernel(DeviceProblem P, const
   else if (r >= c) S[(size_t)c * ld + r] = v; else S[(size_t)r * ld + c] = v;
 }
 
+// Sharded solve: everything a pass exchanges travels in ONE all-reduce (sum) of a packed buffer:
+//   [ lower-triangular blocks of the (symmetric) block-sparse S | rhs | pose gradient | pose column norms |
+//     rank-local scalar sums | one slot per rank for the rank-local max ]
+// pack gathers it (the segments before `first` are left out in a Jacobian-only pass), unpack scatters the sums: S blocks
+// to the block and its transpose, the max as the maximum over the per-rank slots.
+struct ExchangeLayout { long long nS; int nf_dim, world, rank, num_sums, max_slot; const int* low_slot; const int* low_slot_t; };
+__global__ void __launch_bounds__(256) pack_exchange_kernel(ExchangeLayout X, long long first, const double* __restrict__ S, const double* __restrict__ rhs,
+                                                            const double* __restrict__ gradL, const double* __restrict__ colsqL, const double* __restrict__ red,
+                                                            double* __restrict__ out) {
+  const long long e = first + (long long)blockIdx.x * 256 + threadIdx.x;
+  const long long o1 = X.nS + X.nf_dim, o2 = o1 + X.nf_dim, o3 = o2 + X.nf_dim, o4 = o3 + X.num_sums, o5 = o4 + X.world;
+  if (e >= o5) return;
+  double v;
+  if (e < X.nS) v = S[(size_t)X.low_slot[e / 9] * 9 + e % 9];
+  else if (e < o1) v = rhs[e - X.nS];
+  else if (e < o2) v = gradL[e - o1];
+  else if (e < o3) v = colsqL[e - o2];
+  else if (e < o4) v = red[e - o3];
+  else v = (e - o4 == X.rank) ? red[X.max_slot] : 0.0;
+  out[e] = v;
+}
+__global__ void __launch_bounds__(256) unpack_exchange_kernel(ExchangeLayout X, long long first, const double* __restrict__ in, double* __restrict__ S,
+                                                              double* __restrict__ rhs, double* __restrict__ gradS, double* __restrict__ colsqS,
+                                                              double* __restrict__ red) {
+  const long long e = first + (long long)blockIdx.x * 256 + threadIdx.x;
+  const long long o1 = X.nS + X.nf_dim, o2 = o1 + X.nf_dim, o3 = o2 + X.nf_dim, o4 = o3 + X.num_sums, o5 = o4 + X.world;
+  if (e >= o5) return;
+  const double v = in[e];
+  if (e < X.nS) {
+    const int i = (int)(e / 9), w = (int)(e % 9);
+    S[(size_t)X.low_slot[i] * 9 + w] = v;
+    const int t = X.low_slot_t[i];
+    if (t >= 0) S[(size_t)t * 9 + 3 * (w % 3) + w / 3] = v;
+  } else if (e < o1) rhs[e - X.nS] = v;
+  else if (e < o2) gradS[e - o1] = v;
+  else if (e < o3) colsqS[e - o2] = v;
+  else if (e < o4) red[e - o3] = v;
+  else if (e == o4) { double m = v; for (int r = 1; r < X.world; ++r) m = fmax(m, in[o4 + r]); red[X.max_slot] = m; }
+}
+
 // K6c: generic-factor contributions to S (3x3 destinations, row >= col) and to rhs. 9 threads per destination.
 __global__ void __launch_bounds__(144) gf_schur_kernel(DeviceProblem P, const double* __restrict__ gfJ,
                                                        double* __restrict__ S, const LMState* st) {
