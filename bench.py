@@ -222,7 +222,7 @@ def run_ours(args):
            "data": "synthetic",
            "config": {"workload": CONFIG_NAMES[args.config], "scale": args.scale, "keyframes": info["num_keyframes"],
                       "landmarks": info["num_landmarks"], "observations": nobs, "reduced_system_dim": nf_dim,
-                      "l2": "inputs larger than L2 (Jacobian + elimination records %.0f MB)" % (352e-6 * nobs) if nobs * 352 > 130e6 else "inputs fit in L2 (latency-bound config)",
+                      "l2": "inputs larger than L2 (Jacobian + elimination records %.0f MB)" % (272e-6 * nobs) if nobs * 272 > 130e6 else "inputs fit in L2 (latency-bound config)",
                       "multi_gpu": "single GPU" if world == 1 else f"landmarks sharded over {world} GPUs, NCCL all-reduce of the reduced camera system per step"},
            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                         "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms": dom_ms,
