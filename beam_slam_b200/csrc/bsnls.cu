@@ -1258,7 +1258,7 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
     return BSNLS_OK;
   };
   // Small reduced systems are launch-latency bound: replay captured graphs instead of enqueuing kernel by kernel.
-  const bool graphs = h->use_graphs && h->world == 1 && h->P.nf_dim <= 4096 && !h->pcg;
+  const bool graphs = h->use_graphs && h->world == 1 && !h->pcg;   // the launch sequence of a pass is fixed per problem (the cooperative PCG launch is not captured)
   if (graphs && (!h->graphs_valid || h->graph_recs != recs)) {
     if (h->graph_pass) { cudaGraphExecDestroy(h->graph_pass); h->graph_pass = nullptr; }
     if (h->graph_tail) { cudaGraphExecDestroy(h->graph_tail); h->graph_tail = nullptr; }
