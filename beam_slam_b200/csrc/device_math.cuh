@@ -167,9 +167,12 @@ __device__ __forceinline__ double reprojection_evaluate_tab(const CameraModel& c
     r[0] = xmul(cam.w, xsub(pixel[0], u));
     r[1] = xmul(cam.w, xsub(pixel[1], v));
   }
-  const double z = Pc[2], z2 = z * z;
+  const double z = Pc[2];
   // d_E_d_P_CAMERA = [fx/z 0 -fx X/z^2; 0 fy/z -fy Y/z^2]; A = d_E_d_P_CAMERA * R_cb without the structural-zero products
-  const double d00 = cam.fx / z, d02 = -cam.fx * Pc[0] / z2, d11 = cam.fy / z, d12 = -cam.fy * Pc[1] / z2;
+  // one reciprocal instead of four divisions: this block is analytic (not differenced), so a last-bit difference to the
+  // reference's fx / z, fx X / z^2 is harmless (unlike the forward-difference block below, which is kept bit-exact)
+  const double iz = 1.0 / z, iz2 = iz * iz;
+  const double d00 = cam.fx * iz, d02 = -cam.fx * Pc[0] * iz2, d11 = cam.fy * iz, d12 = -cam.fy * Pc[1] * iz2;
   double A[6];
 #pragma unroll
   for (int j = 0; j < 3; ++j) {
