@@ -115,9 +115,10 @@ typedef struct bsnls_problem {
 
 /* Subset of ceres::Solver::Options that fuse loads (fuse_core/src/ceres_options.cpp:75-200) and that the
    trust-region path consults. Defaults = Ceres defaults (bsnls_default_options). */
-enum { BSNLS_LINEAR_DENSE_SCHUR = 0, /* Schur + dense DMMA Cholesky of the reduced system */
+enum { BSNLS_LINEAR_DENSE_SCHUR = 0, /* Schur + direct Cholesky of the reduced system: in registers up to 160 unknowns,
+                                        tile-sparse level-scheduled DMMA Cholesky above (fails if the factor needs > 24 GB) */
        BSNLS_LINEAR_ITERATIVE_SCHUR = 1, /* Schur + block-sparse PCG (block-Jacobi) */
-       BSNLS_LINEAR_AUTO = 2 };
+       BSNLS_LINEAR_AUTO = 2 };          /* direct; block-sparse PCG only if the tile factor would not fit */
 typedef struct bsnls_options {
   int32_t max_num_iterations;            /* 50 */
   double max_solver_time_in_seconds;     /* 1e9 */
@@ -212,7 +213,8 @@ int bsnls_get_ordering(bsnls_handle* handle, int32_t* e_blocks, int32_t* num_e, 
    col f-block position) pairs sorted by (row, col). Pass NULL pointers to query the count. */
 int bsnls_get_reduced_pattern(bsnls_handle* handle, int32_t* rows, int32_t* cols, int64_t* count);
 /* Linearise at the current values with the given trust-region radius and return the dense reduced system
-   (lower triangle filled, column-major, dim x dim) and its right-hand side. For tests; dense mode only. */
+   (full symmetric matrix, column-major, dim x dim, in the program order of bsnls_get_ordering) and its right-hand
+   side. For tests: the matrix is expanded on the host whatever the internal storage is. */
 int bsnls_get_reduced_system(bsnls_handle* handle, double radius, double* S, double* rhs, int32_t dim);
 
 /* ---- per-kernel entry points (one pass of the hot path; what bench.py's roofline times) ---- */
