@@ -761,7 +761,11 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   h->n_eval_items = (int)(eval_items.size() / 4); h->nb_eval = h->n_eval_items;
   h->obs_pm_h.assign(nobs_local, 0); for (int it = 0; it < nobs_local; ++it) h->obs_pm_h[pose_obs[it]] = it;
   const double avg_track = ne_g ? (double)nobs / ne_g : 0.0;
-  h->G = avg_track <= 5.0 ? 4 : avg_track <= 12.0 ? 8 : avg_track <= 24.0 ? 16 : 32;
+  // lanes per landmark: throughput-bound shards do best with about three observations per lane (landmark 0.179 -> 0.174 ms
+  // on config 4), latency-bound windows with one or two (C1 solve 1.22 vs 1.34 ms)
+  if (h->ne >= 20000) h->G = avg_track <= 12.5 ? 4 : avg_track <= 25.0 ? 8 : avg_track <= 50.0 ? 16 : 32;
+  else h->G = avg_track <= 5.0 ? 4 : avg_track <= 12.0 ? 8 : avg_track <= 24.0 ? 16 : 32;
+  if (const char* ev = std::getenv("BSNLS_LM_LANES")) { const int g = std::atoi(ev); if (g == 4 || g == 8 || g == 16 || g == 32) h->G = g; }   // tuning knob: lanes per landmark
 
   // ---- chunks: consecutive landmarks whose poses fit kChunkSlots slots are accumulated on chip by one CTA ----
   std::vector<unsigned short> obs_slot(nobs_local, 0xFFFF);
