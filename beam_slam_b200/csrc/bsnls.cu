@@ -406,14 +406,36 @@ int GatherValues(bsnls_handle* h) {
   return AllReduce(h, h->d_x.as<double>(), (size_t)h->num_values, kNcclSum);
 }
 
-int InitState(bsnls_handle* h, bool keep_scale) {
+int InitState(bsnls_handle* h, bool keep_scale, double radius = 0.0) {
   LMState s{};
-  s.radius = h->opt.initial_trust_region_radius; s.decrease_factor = 2.0;
+  s.radius = radius > 0.0 ? radius : h->opt.initial_trust_region_radius; s.decrease_factor = 2.0;
   s.need_jacobian = 1; s.scale_ready = keep_scale ? 1 : 0; s.max_records = h->max_records;
   cudaError_t e = cudaMemcpyAsync(h->d_state.p, &s, sizeof(s), cudaMemcpyHostToDevice, h->stream);
   if (e != cudaSuccess) return h->fail(BSNLS_ERR_CUDA, "state upload: %s", cudaGetErrorString(e));
   e = cudaMemsetAsync(h->d_red.p, 0, sizeof(double) * 32, h->stream);
   if (e != cudaSuccess) return h->fail(BSNLS_ERR_CUDA, "red memset: %s", cudaGetErrorString(e));
+  return BSNLS_OK;
+}
+
+int EnqueueTail(bsnls_handle* h, const Options& o, bsnls_iteration* recs) {   // Jacobian pass that closes an accepted step (or IterationZero)
+  LMState* st = h->d_state.as<LMState>();
+  EnqueueEval(h);
+  const int rc = EnqueueLinearise(h, o, false);
+  LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
+  return rc;
+}
+int EnqueuePass(bsnls_handle* h, const Options& o, bsnls_iteration* recs) {   // one LM iteration
+  LMState* st = h->d_state.as<LMState>();
+  EnqueueEval(h);
+  EnqueueLandmark(h, o);
+  int rc = EnqueueLinearise(h, o, true);
+  if (rc != BSNLS_OK) return rc;
+  LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
+  EnqueueAssembleFinish(h, o);
+  if (h->pcg) { rc = EnqueueSparseSolve(h); if (rc != BSNLS_OK) return rc; } else EnqueueDenseSolve(h);
+  if ((rc = EnqueueStep(h)) != BSNLS_OK) return rc;
+  LAUNCH(h, ctrl_end_iteration_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
+  LAUNCH(h, apply_step_kernel, BlocksFor((int)h->num_values, 256), 256, h->d_x.as<double>(), h->d_xc.as<double>(), (int)h->num_values, st);
   return BSNLS_OK;
 }
 
@@ -1242,25 +1264,8 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
   // a wall-clock budget is a per-process decision; ranks of a sharded solve must issue identical collectives, so the
   // budget is only honoured on a single GPU
   const bool timed = h->opt.max_solver_time_in_seconds < 1e8 && h->world == 1;
-  auto enqueue_tail = [&]() -> int {   // Jacobian pass that closes an accepted step (or IterationZero)
-    EnqueueEval(h);
-    int r2 = EnqueueLinearise(h, o, false);
-    LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
-    return r2;
-  };
-  auto enqueue_pass = [&]() -> int {   // one LM iteration
-    EnqueueEval(h);
-    EnqueueLandmark(h, o);
-    int r2 = EnqueueLinearise(h, o, true);
-    if (r2 != BSNLS_OK) return r2;
-    LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
-    EnqueueAssembleFinish(h, o);
-    if (h->pcg) { r2 = EnqueueSparseSolve(h); if (r2 != BSNLS_OK) return r2; } else EnqueueDenseSolve(h);
-    if ((r2 = EnqueueStep(h)) != BSNLS_OK) return r2;
-    LAUNCH(h, ctrl_end_iteration_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
-    LAUNCH(h, apply_step_kernel, BlocksFor((int)h->num_values, 256), 256, h->d_x.as<double>(), h->d_xc.as<double>(), (int)h->num_values, st);
-    return BSNLS_OK;
-  };
+  auto enqueue_tail = [&]() -> int { return EnqueueTail(h, o, recs); };
+  auto enqueue_pass = [&]() -> int { return EnqueuePass(h, o, recs); };
   // Small reduced systems are launch-latency bound: replay captured graphs instead of enqueuing kernel by kernel.
   const bool graphs = h->use_graphs && h->world == 1 && !h->pcg;   // the launch sequence of a pass is fixed per problem (the cooperative PCG launch is not captured)
   if (graphs && (!h->graphs_valid || h->graph_recs != recs)) {
@@ -1426,6 +1431,79 @@ int bsnls_get_reduced_system(bsnls_handle* h, double radius, double* S, double* 
   CK(cudaMemcpyAsync(S, h->d_S.p, sizeof(double) * (size_t)dim * dim, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
   for (int c = 0; c < dim; ++c) for (int r = 0; r < c; ++r) S[(size_t)c * dim + r] = S[(size_t)r * dim + c];  // mirror the lower triangle
+  return BSNLS_OK;
+}
+
+int bsnls_get_reduced_blocks(bsnls_handle* h, double radius, int32_t* rows, int32_t* cols, double* vals, int64_t* count, double* rhs) {
+  if (!h || !count) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "no problem");
+  int64_t n = 0;
+  int rc = bsnls_get_reduced_pattern(h, nullptr, nullptr, &n);
+  if (rc != BSNLS_OK) return rc;
+  if (!rows || !cols || !vals) { *count = n; return BSNLS_OK; }
+  if (*count < n) return h->fail(BSNLS_ERR_INVALID, "block buffers too small");
+  if ((rc = bsnls_get_reduced_pattern(h, rows, cols, count)) != BSNLS_OK) return rc;
+  if ((rc = bsnls_run_eval(h, nullptr)) != BSNLS_OK) return rc;
+  if ((rc = bsnls_run_schur(h, radius)) != BSNLS_OK) return rc;
+  const int dim = h->P.nf_dim;
+  std::vector<double> r(dim);
+  CK(cudaMemcpyAsync(r.data(), h->d_rhs.p, sizeof(double) * dim, cudaMemcpyDeviceToHost, h->stream));
+  std::memset(vals, 0, sizeof(double) * 9 * (size_t)n);
+  auto find = [&](int ar, int ac) -> int64_t {   // (row, col) pairs are sorted
+    int64_t lo = 0, hi = n;
+    while (lo < hi) { const int64_t m = (lo + hi) / 2; if (rows[m] < ar || (rows[m] == ar && cols[m] < ac)) lo = m + 1; else hi = m; }
+    return (lo < n && rows[lo] == ar && cols[lo] == ac) ? lo : -1;
+  };
+  if (h->sparse) {
+    std::vector<double> blocks((size_t)h->nnzb * 9);
+    CK(cudaMemcpyAsync(blocks.data(), h->d_S.p, sizeof(double) * blocks.size(), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    for (int br = 0; br < h->nf; ++br)
+      for (int k = h->bsr_rowptr[br]; k < h->bsr_rowptr[br + 1]; ++k) {
+        const int ar = h->f_api[br], ac = h->f_api[h->bsr_col[k]];
+        if (ar < ac) continue;
+        const int64_t q = find(ar, ac);
+        if (q < 0) return h->fail(BSNLS_ERR_STATE, "reduced-system block outside the reported pattern");
+        std::memcpy(vals + 9 * q, blocks.data() + (size_t)k * 9, sizeof(double) * 9);
+      }
+    if (rhs) for (int br = 0; br < h->nf; ++br) for (int i = 0; i < 3; ++i) rhs[3 * h->f_api[br] + i] = r[3 * br + i];
+    return BSNLS_OK;
+  }
+  std::vector<double> S((size_t)dim * dim);
+  CK(cudaMemcpyAsync(S.data(), h->d_S.p, sizeof(double) * S.size(), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  for (int64_t q = 0; q < n; ++q)
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) {
+      const int rr = 3 * rows[q] + i, cc = 3 * cols[q] + j;
+      vals[9 * q + 3 * i + j] = rr >= cc ? S[(size_t)cc * dim + rr] : S[(size_t)rr * dim + cc];   // lower triangle, column-major
+    }
+  if (rhs) std::memcpy(rhs, r.data(), sizeof(double) * dim);
+  return BSNLS_OK;
+}
+
+int bsnls_trial_step(bsnls_handle* h, const double* values, double radius, int32_t keep_jacobi_scale, bsnls_iteration* out, int32_t* num_out) {
+  if (!h || !out || !num_out) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_trial_step before bsnls_set_problem");
+  if (!(radius > 0)) return h->fail(BSNLS_ERR_INVALID, "radius must be positive");
+  CK(cudaSetDevice(h->device));
+  if (values) CK(cudaMemcpyAsync(h->d_x.p, values, sizeof(double) * h->num_values, cudaMemcpyHostToDevice, h->stream));
+  const Options o = MakeOptions(h->opt);
+  h->max_records = std::max(h->max_records, 4);
+  CK(h->d_recs.alloc(sizeof(bsnls_iteration) * h->max_records));
+  int rc = InitState(h, keep_jacobi_scale != 0, radius);
+  if (rc != BSNLS_OK) return rc;
+  bsnls_iteration* recs = h->d_recs.as<bsnls_iteration>();
+  CK(cudaMemcpyAsync(h->d_xc.p, h->d_x.p, sizeof(double) * h->num_values, cudaMemcpyDeviceToDevice, h->stream));
+  if ((rc = EnqueueXNorm(h)) != BSNLS_OK) return rc;
+  if ((rc = EnqueuePass(h, o, recs)) != BSNLS_OK) return rc;
+  if ((rc = EnqueueTail(h, o, recs)) != BSNLS_OK) return rc;
+  LMState hs; bsnls_iteration hrec[2];
+  CK(cudaMemcpyAsync(&hs, h->d_state.p, sizeof(hs), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpyAsync(hrec, recs, sizeof(hrec), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream)); CK(cudaGetLastError());
+  *num_out = std::min(hs.num_records, 2);
+  for (int i = 0; i < *num_out; ++i) out[i] = hrec[i];
+  h->jac_valid = false;
   return BSNLS_OK;
 }
 

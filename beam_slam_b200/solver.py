@@ -99,6 +99,26 @@ class Solver:
         self._check(self._lib.bsnls_get_reduced_system(self._h, radius, S.ctypes.data_as(_pf64), rhs.ctypes.data_as(_pf64), dim))
         return S, rhs  # S is symmetric, so the column-major buffer reads the same row-major
 
+    def reduced_blocks(self, radius):
+        """Lower-triangular 3x3 blocks of the reduced system on its structural pattern: rows, cols, vals (n,3,3), rhs."""
+        n = C.c_int64(0)
+        self._check(self._lib.bsnls_get_reduced_blocks(self._h, radius, None, None, None, C.byref(n), None))
+        r, c, v = np.zeros(n.value, np.int32), np.zeros(n.value, np.int32), np.zeros((n.value, 3, 3))
+        _, f = self.ordering()
+        rhs = np.zeros(3 * len(f))
+        self._check(self._lib.bsnls_get_reduced_blocks(self._h, radius, r.ctypes.data_as(_pi32), c.ctypes.data_as(_pi32),
+                                                       v.ctypes.data_as(_pf64), C.byref(n), rhs.ctypes.data_as(_pf64)))
+        return r, c, v, rhs
+
+    def trial_step(self, values, radius, keep_jacobi_scale):
+        """One LM step from `values` with the given trust-region radius: list of 1 or 2 iteration records."""
+        out = (cabi.Iteration * 2)()
+        n = C.c_int32(0)
+        v = None if values is None else np.ascontiguousarray(values, np.float64)
+        self._check(self._lib.bsnls_trial_step(self._h, None if v is None else v.ctypes.data_as(_pf64), radius,
+                                               1 if keep_jacobi_scale else 0, out, C.byref(n)))
+        return [out[i] for i in range(n.value)]
+
     def run_eval(self):
         c = C.c_double()
         self._check(self._lib.bsnls_run_eval(self._h, C.byref(c)))

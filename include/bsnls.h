@@ -217,6 +217,20 @@ int bsnls_get_reduced_pattern(bsnls_handle* handle, int32_t* rows, int32_t* cols
    side. For tests: the matrix is expanded on the host whatever the internal storage is. */
 int bsnls_get_reduced_system(bsnls_handle* handle, double radius, double* S, double* rhs, int32_t dim);
 
+/* Same system on its structural pattern, for graphs whose dense matrix does not fit: the lower-triangular 3x3 blocks in the
+   order of bsnls_get_reduced_pattern (rows / cols are filled as that call fills them), 9 doubles per block, row-major.
+   Pass NULL pointers to query the count. */
+int bsnls_get_reduced_blocks(bsnls_handle* handle, double radius, int32_t* rows, int32_t* cols, double* vals,
+                             int64_t* count, double* rhs);
+/* One Levenberg-Marquardt step from a given point, for teacher-forced parity checks (no counterpart in the reference:
+   ceres::Solve does not expose single steps). Uploads `values` (NULL: keep the current ones), starts from
+   trust-region radius `radius`, evaluates (record 0: cost and gradient norms at the point), takes one step (record 1:
+   step norm, cost change, relative decrease, the radius after the update). keep_jacobi_scale != 0 reuses the column
+   scaling of the previous solve / trial step on this handle (Ceres freezes it at iteration 0). num_out < 2 when the
+   step ended the minimisation (tolerance reached). An accepted step stays applied to the handle's values. */
+int bsnls_trial_step(bsnls_handle* handle, const double* values, double radius, int32_t keep_jacobi_scale,
+                     bsnls_iteration* out, int32_t* num_out);
+
 /* ---- per-kernel entry points (one pass of the hot path; what bench.py's roofline times) ---- */
 /* K1-K4: evaluate every factor (residual, tangent Jacobian, loss correction), cost, gradient. */
 int bsnls_run_eval(bsnls_handle* handle, double* cost);
@@ -243,7 +257,8 @@ int64_t bsnls_launch_count(const bsnls_handle* handle);
    observation; d_cost one double. `stream` is a cudaStream_t (NULL = default stream); the call only enqueues.
    Scratch is a fixed 128 KiB array inside the library, shared by all calls on a device (calls that overlap on the
    GPU race), resident on every GPU that loads the library; its address is looked up on the first call per
-   device, which should precede any stream capture. More than BSNLS_NOALLOC_MAX_OBSERVATIONS observations are
+   device, which should precede any stream capture. The device is the CURRENT one (cudaGetDevice) at the time of the
+   call: make the device that owns `stream` and the buffers current before calling. More than BSNLS_NOALLOC_MAX_OBSERVATIONS observations are
    refused (BSNLS_ERR_INVALID); error_message (optional, error_capacity bytes) receives the reason. */
 enum { BSNLS_NOALLOC_MAX_OBSERVATIONS = 4194304 };
 int bsnls_reprojection_cost_noalloc(const double* d_values, const int32_t* d_q_offset, const int32_t* d_t_offset,

@@ -5,8 +5,9 @@
 // (dependencies/fuse/fuse_graphs/src/hash_graph.cpp:416-426): ceres::Problem construction semantics
 // (constant blocks removed), residual-block evaluation with manifold + robust-loss correction
 // (fuse's own restatement: dependencies/fuse/fuse_constraints/src/marginalize_variables.cpp:281-399),
-// Ceres' TrustRegionMinimizer + LevenbergMarquardtStrategy + SchurEliminator with a dense Cholesky of the
-// reduced system (Ceres 1.14/2.0 public sources, third-party, not vendored).
+// Ceres' TrustRegionMinimizer + LevenbergMarquardtStrategy + SchurEliminator with a Cholesky of the reduced system
+// (dense for windows, block-sparse with a sparse LL^T for the refinement-sized graphs: oracle_sparse.h)
+// (Ceres 1.14/2.0 public sources, third-party, not vendored).
 // Elimination ordering = explicit two groups (block_group 0 first), program order inside each group.
 //
 // Parity status: factor, manifold and linearisation math pinned to the reference's golden vectors
@@ -19,6 +20,7 @@
 #include <vector>
 
 #include "oracle_factors.h"
+#include "oracle_sparse.h"
 
 namespace orc {
 
@@ -272,21 +274,31 @@ static double Evaluate(const Model& M, const double* x, Workspace* W, bool want_
   double cost = 0.0;
   for (int64_t i = 0; i < n; ++i) cost += W->costs[i];
   if (want_jac) {
-    W->grad.assign(M.ntan, 0.0);
-    for (int64_t i = 0; i < n; ++i) {
-      const ResBlock& r = M.rb[i];
-      if (r.removed) continue;
-      const double* J = W->jac.data() + r.jac; const double* rs = W->res.data() + r.row;
-      for (int b = 0; b < r.nb; ++b) {
-        if (r.jcols[b] < 0) continue;
-        const int blk = r.blocks[b];
-        for (int k = 0; k < M.lsize[blk]; ++k) {
-          double acc = 0.0;
-          for (int rr = 0; rr < r.nr; ++rr) acc += J[rr * r.ncols + r.jcols[b] + k] * rs[rr];
-          W->grad[M.tan[blk] + k] += acc;
+    // gradient = J^T r: per-thread partial vectors over static slices of the residual blocks, summed in thread order
+    // (deterministic for a given thread count; Ceres' ProgramEvaluator does the same with per-thread scratch)
+    const int nth = omp_get_max_threads();
+    std::vector<std::vector<double>> part(nth);
+#pragma omp parallel
+    {
+      std::vector<double>& g = part[omp_get_thread_num()]; g.assign(M.ntan, 0.0);
+#pragma omp for schedule(static)
+      for (int64_t i = 0; i < n; ++i) {
+        const ResBlock& r = M.rb[i];
+        if (r.removed) continue;
+        const double* J = W->jac.data() + r.jac; const double* rs = W->res.data() + r.row;
+        for (int b = 0; b < r.nb; ++b) {
+          if (r.jcols[b] < 0) continue;
+          const int blk = r.blocks[b];
+          for (int k = 0; k < M.lsize[blk]; ++k) {
+            double acc = 0.0;
+            for (int rr = 0; rr < r.nr; ++rr) acc += J[rr * r.ncols + r.jcols[b] + k] * rs[rr];
+            g[M.tan[blk] + k] += acc;
+          }
         }
       }
     }
+    W->grad.assign(M.ntan, 0.0);
+    for (int t = 0; t < nth; ++t) if (!part[t].empty()) for (int k = 0; k < M.ntan; ++k) W->grad[k] += part[t][k];
   }
   return cost;
 }
@@ -314,23 +326,36 @@ static double ActiveNorm(const Model& M, const double* a, const double* b /*null
 }
 
 static void ColumnSqNorm(const Model& M, const Workspace& W, std::vector<double>* out) {
-  out->assign(M.ntan, 0.0);
-  for (const ResBlock& r : M.rb) {
-    if (r.removed) continue;
-    const double* J = W.jac.data() + r.jac;
-    for (int b = 0; b < r.nb; ++b) {
-      if (r.jcols[b] < 0) continue;
-      const int blk = r.blocks[b];
-      for (int k = 0; k < M.lsize[blk]; ++k) {
-        double acc = 0.0;
-        for (int rr = 0; rr < r.nr; ++rr) { const double v = J[rr * r.ncols + r.jcols[b] + k]; acc += v * v; }
-        (*out)[M.tan[blk] + k] += acc;
+  const int nth = omp_get_max_threads();
+  const int64_t n = (int64_t)M.rb.size();
+  std::vector<std::vector<double>> part(nth);
+#pragma omp parallel
+  {
+    std::vector<double>& c = part[omp_get_thread_num()]; c.assign(M.ntan, 0.0);
+#pragma omp for schedule(static)
+    for (int64_t i = 0; i < n; ++i) {
+      const ResBlock& r = M.rb[i];
+      if (r.removed) continue;
+      const double* J = W.jac.data() + r.jac;
+      for (int b = 0; b < r.nb; ++b) {
+        if (r.jcols[b] < 0) continue;
+        const int blk = r.blocks[b];
+        for (int k = 0; k < M.lsize[blk]; ++k) {
+          double acc = 0.0;
+          for (int rr = 0; rr < r.nr; ++rr) { const double v = J[rr * r.ncols + r.jcols[b] + k]; acc += v * v; }
+          c[M.tan[blk] + k] += acc;
+        }
       }
     }
   }
+  out->assign(M.ntan, 0.0);
+  for (int t = 0; t < nth; ++t) if (!part[t].empty()) for (int k = 0; k < M.ntan; ++k) (*out)[k] += part[t][k];
 }
 static void ScaleColumns(const Model& M, Workspace* W, const std::vector<double>& scale) {
-  for (const ResBlock& r : M.rb) {
+  const int64_t n = (int64_t)M.rb.size();
+#pragma omp parallel for schedule(static)
+  for (int64_t i = 0; i < n; ++i) {
+    const ResBlock& r = M.rb[i];
     if (r.removed) continue;
     double* J = W->jac.data() + r.jac;
     for (int b = 0; b < r.nb; ++b) {
@@ -386,26 +411,72 @@ static bool InvertSPD(const double* A, int n, double* inv) {
   return true;
 }
 
-// SchurEliminator::Eliminate (schur_eliminator_impl.h): dense reduced system over f-blocks in program order.
+// Linear-algebra mode of the reduced system: 0 = automatic (dense up to kDenseLimit unknowns, block-sparse above),
+// 1 = always dense, 2 = always block-sparse. Set through oracle_set_linear_mode (tests cross-check the two).
+static int g_linear_mode = 0;
+static const int kDenseLimit = 2400;
+static bool UseSparse(const Model& M) { return g_linear_mode == 2 || (g_linear_mode == 0 && M.nf_dim > kDenseLimit); }
+
+// SchurEliminator::Eliminate (schur_eliminator_impl.h): reduced system over f-blocks in program order, stored dense
+// (small windows) or block-sparse on the structural pattern (oracle_sparse.h).
 // J is whatever W holds (Jacobi-scaled in the LM loop), D = LM diagonal (per tangent column, e then f).
 struct Reduced {
-  std::vector<double> S, rhs;     // nf x nf row-major (full symmetric), nf
+  bool sparse = false;
+  std::vector<double> S, rhs;     // dense: nf x nf row-major (full symmetric); sparse: block values of `pat`
+  BlockPattern pat; SparseCholesky chol; bool have_pattern = false;
   std::vector<double> ete_inv;    // per e-block ls x ls
   std::vector<double> ge;         // E^T r per e-block
 };
-static bool BuildReduced(const Model& M, const Workspace& W, const double* D, Reduced* R) {
+static void BuildPattern(const Model& M, Reduced* R) {
+  const int nfb = (int)M.fblocks.size(), ne0 = M.ne_dim;
+  std::vector<int> fpos(M.P->num_blocks, -1), ls(nfb);
+  for (int k = 0; k < nfb; ++k) { fpos[M.fblocks[k]] = k; ls[k] = M.lsize[M.fblocks[k]]; }
+  LazyAdj A(nfb);
+  std::vector<int> cl;
+  for (size_t e = 0; e < M.eblocks.size(); ++e) {
+    cl.clear();
+    for (int ri : M.e_rows[e]) { const ResBlock& r = M.rb[ri]; for (int b = 0; b < r.nb; ++b) if (r.jcols[b] >= 0 && fpos[r.blocks[b]] >= 0) cl.push_back(fpos[r.blocks[b]]); }
+    std::sort(cl.begin(), cl.end()); cl.erase(std::unique(cl.begin(), cl.end()), cl.end());
+    A.AddClique(cl);
+  }
+  for (int ri : M.f_rows) {
+    const ResBlock& r = M.rb[ri]; cl.clear();
+    for (int b = 0; b < r.nb; ++b) if (r.jcols[b] >= 0 && fpos[r.blocks[b]] >= 0) cl.push_back(fpos[r.blocks[b]]);
+    A.AddClique(cl);
+  }
+  FinishPattern(&A, ls, &R->pat);
+  (void)ne0;
+  R->chol.Analyse(R->pat);
+  R->have_pattern = true;
+}
+struct DenseAcc {
+  double* S; int nf;
+  inline void Add(int r, int c, double v) { S[(size_t)r * nf + c] += v; }
+};
+struct SparseAcc {
+  double* V; const BlockPattern* P; int lr = -1, lc = -1; int64_t lo = 0; int ljs = 0;
+  inline void Add(int r, int c, double v) {
+    const int br = P->blk_of[r], bc = P->blk_of[c];
+    if (br != lr || bc != lc) { lr = br; lc = bc; lo = P->voff[P->Slot(br, bc)]; ljs = P->ls[bc]; }
+    V[lo + (int64_t)(r - P->off[br]) * ljs + (c - P->off[bc])] += v;
+  }
+};
+static inline void Init(DenseAcc& a, double* S, int nf, const BlockPattern*) { a.S = S; a.nf = nf; }
+static inline void Init(SparseAcc& a, double* S, int, const BlockPattern* P) { a.V = S; a.P = P; }
+template <class Acc>
+static bool BuildReducedT(const Model& M, const Workspace& W, const double* D, Reduced* R, size_t nS) {
   const int nf = M.nf_dim, ne0 = M.ne_dim;
   const int nthreads = omp_get_max_threads();
   std::vector<std::vector<double>> Sloc(nthreads), rloc(nthreads);
   R->ete_inv.assign((size_t)M.eblocks.size() * 9, 0.0); R->ge.assign((size_t)M.eblocks.size() * 3, 0.0);
   bool ok = true;
+  auto make_acc = [&](double* S) { Acc a{}; Init(a, S, nf, &R->pat); return a; };
 #pragma omp parallel
   {
     const int tid = omp_get_thread_num();
     std::vector<double>& S = Sloc[tid]; std::vector<double>& rhs = rloc[tid];
-    S.assign((size_t)nf * nf, 0.0); rhs.assign(nf, 0.0);
-    std::vector<double> FtE;   // per row-block: ncols_f x le
-    std::vector<int> fcol;
+    S.assign(nS, 0.0); rhs.assign(nf, 0.0);
+    Acc acc = make_acc(S.data());
 #pragma omp for schedule(static)
     for (int64_t e = 0; e < (int64_t)M.eblocks.size(); ++e) {
       const int eb = M.eblocks[e], le = M.lsize[eb];
@@ -417,17 +488,16 @@ static bool BuildReduced(const Model& M, const Workspace& W, const double* D, Re
         const double* J = W.jac.data() + r.jac; const double* rs = W.res.data() + r.row;
         int ec = -1; for (int b = 0; b < r.nb; ++b) if (r.jcols[b] >= 0 && r.blocks[b] == eb) ec = r.jcols[b];
         for (int a = 0; a < le; ++a) {
-          for (int c = 0; c < le; ++c) { double acc = 0; for (int rr = 0; rr < r.nr; ++rr) acc += J[rr * r.ncols + ec + a] * J[rr * r.ncols + ec + c]; ete[a * le + c] += acc; }
-          double acc = 0; for (int rr = 0; rr < r.nr; ++rr) acc += J[rr * r.ncols + ec + a] * rs[rr]; g[a] += acc;
+          for (int c = 0; c < le; ++c) { double acc2 = 0; for (int rr = 0; rr < r.nr; ++rr) acc2 += J[rr * r.ncols + ec + a] * J[rr * r.ncols + ec + c]; ete[a * le + c] += acc2; }
+          double acc2 = 0; for (int rr = 0; rr < r.nr; ++rr) acc2 += J[rr * r.ncols + ec + a] * rs[rr]; g[a] += acc2;
         }
       }
       double inv[9];
       if (!InvertSPD(ete, le, inv)) { ok = false; continue; }
       for (int k = 0; k < le * le; ++k) R->ete_inv[e * 9 + k] = inv[k];
       for (int k = 0; k < le; ++k) R->ge[e * 3 + k] = g[k];
-      double invg[3]; for (int a = 0; a < le; ++a) { double acc = 0; for (int c = 0; c < le; ++c) acc += inv[a * le + c] * g[c]; invg[a] = acc; }
+      double invg[3]; for (int a = 0; a < le; ++a) { double acc2 = 0; for (int c = 0; c < le; ++c) acc2 += inv[a * le + c] * g[c]; invg[a] = acc2; }
       // pass 2: F^T F, F^T r, and collect F^T E per (row block, f column)
-      // gather the global f columns touched by this chunk
       struct Col { int gcol; double fte[3]; };
       std::vector<Col> cols;
       for (int ri : M.e_rows[e]) {
@@ -439,16 +509,15 @@ static bool BuildReduced(const Model& M, const Workspace& W, const double* D, Re
           const int blk = r.blocks[b], gc0 = M.tan[blk] - ne0;
           for (int k = 0; k < M.lsize[blk]; ++k) {
             const int lc = r.jcols[b] + k;
-            // F^T r
-            double acc = 0; for (int rr = 0; rr < r.nr; ++rr) acc += J[rr * r.ncols + lc] * rs[rr];
-            rhs[gc0 + k] += acc;
+            double acc2 = 0; for (int rr = 0; rr < r.nr; ++rr) acc2 += J[rr * r.ncols + lc] * rs[rr];
+            rhs[gc0 + k] += acc2;
             // F^T F against every f column of the same residual block
             for (int b2 = 0; b2 < r.nb; ++b2) {
               if (r.jcols[b2] < 0 || r.blocks[b2] == eb) continue;
               const int blk2 = r.blocks[b2], gc2 = M.tan[blk2] - ne0;
               for (int k2 = 0; k2 < M.lsize[blk2]; ++k2) {
                 double a2 = 0; for (int rr = 0; rr < r.nr; ++rr) a2 += J[rr * r.ncols + lc] * J[rr * r.ncols + r.jcols[b2] + k2];
-                S[(size_t)(gc0 + k) * nf + gc2 + k2] += a2;
+                acc.Add(gc0 + k, gc2 + k2, a2);
               }
             }
             // F^T E accumulated per global column (a camera may be hit by several rows of the chunk)
@@ -461,19 +530,22 @@ static bool BuildReduced(const Model& M, const Workspace& W, const double* D, Re
       }
       // S -= (F^T E) inv (E^T F); rhs -= (F^T E) inv g
       for (const Col& ci : cols) {
-        double t[3]; for (int a = 0; a < le; ++a) { double acc = 0; for (int c = 0; c < le; ++c) acc += ci.fte[c] * inv[c * le + a]; t[a] = acc; }
-        double acc = 0; for (int a = 0; a < le; ++a) acc += ci.fte[a] * invg[a];
-        rhs[ci.gcol] -= acc;
-        for (const Col& cj : cols) { double a2 = 0; for (int a = 0; a < le; ++a) a2 += t[a] * cj.fte[a]; S[(size_t)ci.gcol * nf + cj.gcol] -= a2; }
+        double t[3]; for (int a = 0; a < le; ++a) { double acc2 = 0; for (int c = 0; c < le; ++c) acc2 += ci.fte[c] * inv[c * le + a]; t[a] = acc2; }
+        double acc2 = 0; for (int a = 0; a < le; ++a) acc2 += ci.fte[a] * invg[a];
+        rhs[ci.gcol] -= acc2;
+        for (const Col& cj : cols) { double a2 = 0; for (int a = 0; a < le; ++a) a2 += t[a] * cj.fte[a]; acc.Add(ci.gcol, cj.gcol, -a2); }
       }
     }
   }
   if (!ok) return false;
-  R->S.assign((size_t)nf * nf, 0.0); R->rhs.assign(nf, 0.0);
+  R->S.assign(nS, 0.0); R->rhs.assign(nf, 0.0);
   for (int t = 0; t < nthreads; ++t) {
-    for (size_t k = 0; k < R->S.size(); ++k) R->S[k] += Sloc[t][k];
+#pragma omp parallel for schedule(static)
+    for (int64_t k = 0; k < (int64_t)nS; ++k) R->S[k] += Sloc[t][k];
     for (int k = 0; k < nf; ++k) R->rhs[k] += rloc[t][k];
+    std::vector<double>().swap(Sloc[t]);
   }
+  Acc acc = make_acc(R->S.data());
   // rows without an e-block (NoEBlockRowsUpdate) and D_f^2
   for (int ri : M.f_rows) {
     const ResBlock& r = M.rb[ri];
@@ -483,20 +555,35 @@ static bool BuildReduced(const Model& M, const Workspace& W, const double* D, Re
       const int blk = r.blocks[b], gc0 = M.tan[blk] - ne0;
       for (int k = 0; k < M.lsize[blk]; ++k) {
         const int lc = r.jcols[b] + k;
-        double acc = 0; for (int rr = 0; rr < r.nr; ++rr) acc += J[rr * r.ncols + lc] * rs[rr];
-        R->rhs[gc0 + k] += acc;
+        double acc2 = 0; for (int rr = 0; rr < r.nr; ++rr) acc2 += J[rr * r.ncols + lc] * rs[rr];
+        R->rhs[gc0 + k] += acc2;
         for (int b2 = 0; b2 < r.nb; ++b2) {
           if (r.jcols[b2] < 0) continue;
           const int blk2 = r.blocks[b2], gc2 = M.tan[blk2] - ne0;
           for (int k2 = 0; k2 < M.lsize[blk2]; ++k2) {
             double a2 = 0; for (int rr = 0; rr < r.nr; ++rr) a2 += J[rr * r.ncols + lc] * J[rr * r.ncols + r.jcols[b2] + k2];
-            R->S[(size_t)(gc0 + k) * nf + gc2 + k2] += a2;
+            acc.Add(gc0 + k, gc2 + k2, a2);
           }
         }
       }
     }
   }
-  if (D) for (int k = 0; k < nf; ++k) R->S[(size_t)k * nf + k] += D[ne0 + k] * D[ne0 + k];
+  if (D) for (int k = 0; k < nf; ++k) acc.Add(k, k, D[ne0 + k] * D[ne0 + k]);
+  return true;
+}
+static bool BuildReduced(const Model& M, const Workspace& W, const double* D, Reduced* R) {
+  R->sparse = UseSparse(M);
+  if (!R->sparse) return BuildReducedT<DenseAcc>(M, W, D, R, (size_t)M.nf_dim * M.nf_dim);
+  if (!R->have_pattern) BuildPattern(M, R);
+  return BuildReducedT<SparseAcc>(M, W, D, R, (size_t)R->pat.nvals);
+}
+// Solve S y = rhs by Cholesky (dense LL^T, or the sparse factorisation on the block pattern); false if S is not SPD.
+static bool SolveReduced(const Model& M, Reduced* R, std::vector<double>* yf) {
+  *yf = R->rhs;
+  if (R->sparse) { if (!R->chol.Factor(R->S)) return false; R->chol.Solve(yf->data()); return true; }
+  std::vector<double> L = R->S;
+  if (!CholeskyLower(L, M.nf_dim)) return false;
+  CholeskySolve(L, M.nf_dim, yf->data());
   return true;
 }
 
@@ -529,8 +616,10 @@ static void SetMessage(bsnls_summary* s, const char* m) { std::snprintf(s->messa
 
 // ceres TrustRegionMinimizer::Minimize with LevenbergMarquardtStrategy (monotonic steps, no inner
 // iterations, no bounds — none of which the reference enables, ceres_options.cpp:75-200).
+// trace (optional): the parameter vector at the start of every attempted step, one after the other (iteration k's
+// linearisation point is entry k-1), for the teacher-forced per-step parity test.
 static int Solve(const bsnls_problem* P, const bsnls_options* opt, bsnls_summary* sum, bsnls_iteration* its,
-                 int max_its, double* x_out) {
+                 int max_its, double* x_out, std::vector<double>* trace = nullptr) {
   const auto t0 = std::chrono::steady_clock::now();
   Model M;
   std::memset(sum, 0, sizeof(*sum));
@@ -581,6 +670,7 @@ static int Solve(const bsnls_problem* P, const bsnls_options* opt, bsnls_summary
     if (radius < opt->min_trust_region_radius) { sum->termination_type = BSNLS_CONVERGENCE; msg = "Minimum trust region radius reached."; break; }
     const bsnls_iteration prev = it;
     std::memset(&it, 0, sizeof(it)); it.iteration = prev.iteration + 1;
+    if (trace) trace->insert(trace->end(), x.begin(), x.end());
     // ComputeTrustRegionStep — LevenbergMarquardtStrategy::ComputeStep
     if (!reuse_diagonal) {
       ColumnSqNorm(M, W, &diag);
@@ -588,10 +678,9 @@ static int Solve(const bsnls_problem* P, const bsnls_options* opt, bsnls_summary
     }
     for (int k = 0; k < M.ntan; ++k) lmD[k] = std::sqrt(diag[k] / radius);
     bool solved = BuildReduced(M, W, lmD.data(), &R);
-    std::vector<double> L;
-    if (solved) { L = R.S; solved = CholeskyLower(L, M.nf_dim); }
+    std::vector<double> yf;
+    if (solved) solved = SolveReduced(M, &R, &yf);
     if (solved) {
-      std::vector<double> yf = R.rhs; CholeskySolve(L, M.nf_dim, yf.data());
       BackSubstitute(M, W, R, yf.data(), step.data());
       for (int k = 0; k < M.ntan; ++k) { if (!std::isfinite(step[k])) solved = false; step[k] = -step[k]; }
     }
@@ -745,10 +834,64 @@ int oracle_reduced_system(const bsnls_problem* P, const bsnls_options* opt, doub
     D[k] = std::sqrt(d / radius) / s;
   }
   orc::Reduced R;
-  if (!orc::BuildReduced(M, W, D.data(), &R)) return BSNLS_ERR_INVALID;
+  const int saved = orc::g_linear_mode; orc::g_linear_mode = 1;   // this entry point returns the dense matrix
+  const bool ok = orc::BuildReduced(M, W, D.data(), &R);
+  orc::g_linear_mode = saved;
+  if (!ok) return BSNLS_ERR_INVALID;
   std::memcpy(S, R.S.data(), sizeof(double) * R.S.size());
   std::memcpy(rhs, R.rhs.data(), sizeof(double) * R.rhs.size());
   return BSNLS_OK;
+}
+// Same system as oracle_reduced_system for graphs whose dense matrix does not fit: the lower-triangular 3x3 (in general
+// ls_r x ls_c) blocks of S on its structural pattern, sorted by (row, col) in f-block positions of the program order,
+// values row-major, 9 doubles reserved per block. Call with vals == NULL to get the count.
+int oracle_reduced_blocks(const bsnls_problem* P, const bsnls_options* opt, double radius, int32_t* rows, int32_t* cols,
+                          double* vals, int64_t* count, double* rhs) {
+  orc::Model M; if (!orc::BuildModel(P, &M)) return BSNLS_ERR_INVALID;
+  const int saved = orc::g_linear_mode; orc::g_linear_mode = 2;
+  orc::Reduced R;
+  if (!vals) {
+    orc::BuildPattern(M, &R);
+    int64_t n = 0;
+    for (int i = 0; i < R.pat.nfb; ++i) for (int s = R.pat.rowptr[i]; s < R.pat.rowptr[i + 1]; ++s) n += R.pat.col[s] <= i;
+    *count = n; orc::g_linear_mode = saved; return BSNLS_OK;
+  }
+  orc::Workspace W; orc::Evaluate(M, M.x.data(), &W, true);
+  std::vector<double> c, D(M.ntan);
+  orc::ColumnSqNorm(M, W, &c);
+  for (int k = 0; k < M.ntan; ++k) {
+    const double s = opt->jacobi_scaling ? 1.0 / (1.0 + std::sqrt(c[k])) : 1.0;
+    const double d = std::min(std::max(c[k] * s * s, opt->min_lm_diagonal), opt->max_lm_diagonal);
+    D[k] = std::sqrt(d / radius) / s;
+  }
+  const bool ok = orc::BuildReduced(M, W, D.data(), &R);
+  orc::g_linear_mode = saved;
+  if (!ok) return BSNLS_ERR_INVALID;
+  int64_t n = 0;
+  for (int i = 0; i < R.pat.nfb; ++i)
+    for (int s = R.pat.rowptr[i]; s < R.pat.rowptr[i + 1]; ++s) {
+      const int j = R.pat.col[s]; if (j > i) continue;
+      if (n >= *count) return BSNLS_ERR_INVALID;
+      rows[n] = i; cols[n] = j;
+      for (int k = 0; k < 9; ++k) vals[9 * n + k] = 0.0;
+      for (int a = 0; a < R.pat.ls[i]; ++a) for (int b = 0; b < R.pat.ls[j]; ++b) vals[9 * n + 3 * a + b] = R.S[R.pat.voff[s] + (int64_t)a * R.pat.ls[j] + b];
+      ++n;
+    }
+  *count = n;
+  if (rhs) std::memcpy(rhs, R.rhs.data(), sizeof(double) * R.rhs.size());
+  return BSNLS_OK;
+}
+void oracle_set_linear_mode(int32_t mode) { orc::g_linear_mode = mode; }
+// oracle_solve + the linearisation point of every attempted step (num_values doubles each, at most max_trace points)
+int oracle_solve_trace(const bsnls_problem* P, const bsnls_options* opt, bsnls_summary* sum, bsnls_iteration* its,
+                       int32_t max_its, double* x_out, double* x_trace, int32_t max_trace, int32_t* num_trace) {
+  std::vector<double> tr;
+  const int rc = orc::Solve(P, opt, sum, its, max_its, x_out, &tr);
+  int64_t nv = 0; for (int b = 0; b < P->num_blocks; ++b) nv += P->block_size[b];
+  const int n = nv ? (int)(tr.size() / nv) : 0;
+  if (num_trace) *num_trace = n;
+  if (x_trace) std::memcpy(x_trace, tr.data(), sizeof(double) * nv * std::min(n, max_trace));
+  return rc;
 }
 int oracle_get_ordering(const bsnls_problem* P, int32_t* e_blocks, int32_t* ne, int32_t* f_blocks, int32_t* nf) {
   orc::Model M; if (!orc::BuildModel(P, &M)) return BSNLS_ERR_INVALID;

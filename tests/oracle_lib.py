@@ -39,6 +39,11 @@ def load():
     lib.oracle_time_eval_schur.argtypes = [C.POINTER(cabi.Problem), C.POINTER(cabi.Options), C.c_double, C.c_int32,
                                            _pi32]
     lib.oracle_time_eval_schur.restype = C.c_double
+    lib.oracle_set_linear_mode.argtypes = [C.c_int32]
+    lib.oracle_reduced_blocks.argtypes = [C.POINTER(cabi.Problem), C.POINTER(cabi.Options), C.c_double, _pi32, _pi32, _pf64,
+                                          C.POINTER(C.c_int64), _pf64]
+    lib.oracle_solve_trace.argtypes = [C.POINTER(cabi.Problem), C.POINTER(cabi.Options), C.POINTER(cabi.Summary),
+                                       C.POINTER(cabi.Iteration), C.c_int32, _pf64, _pf64, C.c_int32, _pi32]
     _lib = lib
     return lib
 
@@ -56,6 +61,43 @@ def solve(problem, options=None, max_iters=256):
     rc = lib.oracle_solve(C.byref(problem.c), C.byref(options), C.byref(s), its, max_iters, _p(x))
     assert rc == 0, s.message
     return s, [its[i] for i in range(min(s.num_iterations, max_iters))], x
+
+
+LINEAR_AUTO, LINEAR_DENSE, LINEAR_SPARSE = 0, 1, 2
+
+
+def set_linear_mode(mode):
+    """Reduced-system storage / Cholesky of the oracle: automatic (dense up to 2400 unknowns), dense, block-sparse."""
+    load().oracle_set_linear_mode(mode)
+
+
+def solve_trace(problem, options=None, max_iters=256):
+    """solve() + the linearisation point of every attempted step: trace[k-1] is where iteration k linearised."""
+    lib = load()
+    options = options or cabi.Options.defaults()
+    s = cabi.Summary()
+    its = (cabi.Iteration * max_iters)()
+    x = np.zeros(problem.num_values)
+    trace = np.zeros((max_iters, problem.num_values))
+    n = C.c_int32()
+    rc = lib.oracle_solve_trace(C.byref(problem.c), C.byref(options), C.byref(s), its, max_iters, _p(x), _p(trace), max_iters, C.byref(n))
+    assert rc == 0, s.message
+    return s, [its[i] for i in range(min(s.num_iterations, max_iters))], x, trace[:min(n.value, max_iters)].copy()
+
+
+def reduced_blocks(problem, radius, options=None):
+    """Lower-triangular 3x3 blocks of the reduced system on its structural pattern: rows, cols (f-block positions in
+    program order, sorted by (row, col)), vals (n, 3, 3), rhs."""
+    lib = load()
+    options = options or cabi.Options.defaults()
+    n = C.c_int64()
+    assert lib.oracle_reduced_blocks(C.byref(problem.c), C.byref(options), radius, None, None, None, C.byref(n), None) == 0
+    rows, cols, vals = np.zeros(n.value, np.int32), np.zeros(n.value, np.int32), np.zeros((n.value, 3, 3))
+    _, f = ordering(problem)
+    rhs = np.zeros(3 * len(f))
+    assert lib.oracle_reduced_blocks(C.byref(problem.c), C.byref(options), radius, rows.ctypes.data_as(_pi32),
+                                     cols.ctypes.data_as(_pi32), _p(vals), C.byref(n), _p(rhs)) == 0
+    return rows, cols, vals, rhs
 
 
 def evaluate(problem):

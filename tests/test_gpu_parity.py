@@ -21,8 +21,10 @@ from beam_slam_b200.solver import BsnlsError, Solver
 
 pytestmark = pytest.mark.gpu
 
-# C3x0.5 has a 600-dim reduced system: the tile-sparse Cholesky with its internal block reordering
-CASES = [(1, 1.0), (2, 0.25), (3, 0.02), (3, 0.5)]
+# C1, C2, C3 at the sizes BASELINE.json names, plus scaled-down ones that exercise the other code paths (C3x0.5 has a
+# 600-dim reduced system: the tile-sparse Cholesky with its internal block reordering). C4 / C5 at full size:
+# tests/test_gpu_parity_full.py.
+CASES = [(1, 1.0), (2, 0.25), (2, 1.0), (3, 0.02), (3, 0.5), (3, 1.0)]
 
 
 def _rel(a, b):

@@ -236,3 +236,72 @@ def test_cauchy_corrector_against_fuse_linearize_formula():
     assert np.allclose(J1, np.sqrt(rho1) * J0, rtol=1e-14)
     cost, _, _ = orc.evaluate(_reproj_problem(*args, 1.0, cabi.LOSS_CAUCHY, 5.0))
     assert abs(cost - 0.5 * 25.0 * np.log(1 + s / 25.0)) < 1e-12 * max(1, cost)
+
+
+def simple_two_state_problem():
+    """bs_models/tests/imu_preintegration_tests.cpp:292-404 (Simple2StateFG): two IMU states (q, p, v, bg, ba) with literal
+    values; priors at the origin on state 1 (pose, velocity, both biases; unit covariance) and relative constraints from
+    state 1 to state 2 (pose +1 m in x, velocity +1 m/s in x, biases +0.001 in x; unit covariance). Returns the flat
+    problem and the optimum the reference asserts, block by block."""
+    b = ProblemBuilder()
+    o1 = b.add_quaternion([0.952, 0.038, -0.189, 0.239]); p1 = b.add_block([1.5, -3.0, 1.0]); v1 = b.add_block([1.5, -3.0, 1.0])
+    bg1 = b.add_block([4e-5, 5e-5, 6e-5]); ba1 = b.add_block([1e-5, 2e-5, 3e-5])
+    o2 = b.add_quaternion([0.944, -0.128, 0.145, -0.269]); p2 = b.add_block([-1.5, 3.0, -1.0]); v2 = b.add_block([-1.5, 3.0, -1.0])
+    bg2 = b.add_block([4e-5, 5e-5, 6e-5]); ba2 = b.add_block([1e-5, 2e-5, 3e-5])
+    I6, I3 = np.eye(6).ravel(), np.eye(3).ravel()
+    b.add_factor(cabi.FACTOR_ABSOLUTE_POSE, [p1, o1], np.concatenate([[0, 0, 0, 1, 0, 0, 0], I6]))
+    for blk in (v1, bg1, ba1):
+        b.add_factor(cabi.FACTOR_ABSOLUTE_VEC3, [blk], np.concatenate([[0, 0, 0], I3]))
+    b.add_factor(cabi.FACTOR_RELATIVE_POSE, [p1, o1, p2, o2], np.concatenate([[1, 0, 0, 1, 0, 0, 0], I6]))
+    b.add_factor(cabi.FACTOR_RELATIVE_VEC3, [v1, v2], np.concatenate([[1, 0, 0], I3]))
+    for x1, x2 in ((bg1, bg2), (ba1, ba2)):
+        b.add_factor(cabi.FACTOR_RELATIVE_VEC3, [x1, x2], np.concatenate([[0.001, 0, 0], I3]))
+    expect = [[1, 0, 0, 0], [0, 0, 0], [0, 0, 0], [0, 0, 0], [0, 0, 0],
+              [1, 0, 0, 0], [1, 0, 0], [1, 0, 0], [0.001, 0, 0], [0.001, 0, 0]]
+    return b.build(), expect
+
+
+def check_two_state_optimum(x, expect):
+    """Tolerances of imu_preintegration_tests.cpp:418-466: 1e-3 on quaternion components, 1e-5 on everything else."""
+    o = 0
+    for e in expect:
+        got = np.asarray(x[o:o + len(e)])
+        o += len(e)
+        assert np.abs(got - e).max() < (1e-3 if len(e) == 4 else 1e-5), (got, e)
+
+
+def test_simple_two_state_graph_reaches_the_reference_optimum():
+    p, expect = simple_two_state_problem()
+    s, its, x = orc.solve(p)
+    assert s.termination_type == cabi.CONVERGENCE
+    check_two_state_optimum(x, expect)
+
+
+def test_sparse_and_dense_reduced_system_paths_agree():
+    """The block-sparse reduced system + sparse Cholesky (oracle/oracle_sparse.h, used for configs 4 and 5) against the
+    dense path on graphs small enough for both: same blocks, same structural pattern, same iterations."""
+    from beam_slam_b200 import host
+    for cfg, scale in ((2, 0.5), (4, 0.05)):
+        g = host.HashGraph.synthetic(cfg, scale=scale)
+        p, o = g.flatten(), host.HashGraph.synthetic_options(cfg)
+        try:
+            orc.set_linear_mode(orc.LINEAR_DENSE)
+            sd, itd, xd = orc.solve(p, o)
+            orc.set_linear_mode(orc.LINEAR_SPARSE)
+            ss, its, xs = orc.solve(p, o)
+        finally:
+            orc.set_linear_mode(orc.LINEAR_AUTO)
+        assert sd.message == ss.message and len(itd) == len(its)
+        for a, b in zip(itd, its):
+            assert abs(a.cost - b.cost) <= 1e-9 * b.cost
+        assert abs(itd[1].step_norm - its[1].step_norm) <= 1e-9 * its[1].step_norm
+        S, rhs = orc.reduced_system(p, 1e4, o)
+        r, c, v, rh = orc.reduced_blocks(p, 1e4, o)
+        nf = S.shape[0] // 3
+        Sb = S.reshape(nf, 3, nf, 3).transpose(0, 2, 1, 3)
+        assert np.abs(Sb[r, c] - v).max() <= 1e-12 * np.abs(S).max()
+        mask = np.zeros((nf, nf), bool)
+        mask[r, c] = True
+        mask[c, r] = True
+        assert np.abs(Sb[~mask]).max() == 0.0          # nothing outside the structural pattern
+        assert np.abs(rh - rhs).max() <= 1e-12 * np.abs(rhs).max()

@@ -7,7 +7,8 @@ image, so the number of observations per call is capped.
 
 The test drives the entry point through the C-ABI with caller-owned device buffers (torch tensors stand in for the
 caller's arena) and compares the cost with what the handle-based entry point bsnls_evaluate returns for the same
-observations: two calls in a row, the second on a smaller set so stale scratch from the first would show.
+observations (and with the CPU oracle's cost): two calls in a row, the second on a smaller set so stale scratch from
+the first would show.
 Collected last on purpose (file name), and independent of what ran before it.
 """
 import ctypes as C
@@ -15,6 +16,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
+import oracle_lib as orc
 from beam_slam_b200 import cabi, host
 from beam_slam_b200.solver import Solver
 
@@ -64,6 +66,7 @@ def test_noalloc_cost_matches_evaluate_on_two_calls_in_a_row():
         expect, _, _ = s.evaluate()                # existing entry point (allocates through its handle)
         got = _noalloc_cost(lib, q, torch)
         assert abs(got - expect) <= 1e-12 * expect, (keep, got, expect)
+        assert abs(got - orc.evaluate(q)[0]) <= 1e-12 * expect   # and against the CPU checker, not only the sibling entry point
         s.close()
     # beyond the fixed scratch: refused with a reason, nothing launched
     msg = C.create_string_buffer(256)
