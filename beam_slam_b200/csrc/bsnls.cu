@@ -27,19 +27,68 @@ const int kStride[BSNLS_NUM_FACTOR_TYPES] = {BSNLS_REPROJECTION_STRIDE, BSNLS_IM
                                              BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE,
                                              BSNLS_ORIENTATION_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_VEC3_STRIDE};
 
+// Device memory of a handle. bsnls_set_problem carves every buffer of a problem out of ONE device arena and fills the
+// uploaded ones from ONE pinned staging buffer with a single host-to-device copy (a sliding window re-flattens its graph
+// every smoother cycle: ~100 cudaMalloc + ~70 pageable copies per cycle cost more than the solve). While an arena is
+// recording (g_rec != nullptr) DevMem::alloc / upload only reserve offsets; Arena::Commit sizes the arena (growing it
+// with 25 % head room, so later windows of similar size allocate nothing), resolves the pointers and issues the copy.
+struct DevMem;
+struct Arena {
+  char* base = nullptr; size_t cap = 0;          // device
+  char* stage = nullptr; size_t stage_cap = 0;   // pinned host mirror of the uploaded region [0, up_used)
+  size_t up_used = 0, work_used = 0;
+  std::vector<DevMem*> members;
+  static size_t Align(size_t n) { return (n + 255) & ~size_t(255); }
+  void Begin() { up_used = 0; work_used = 0; members.clear(); }
+  cudaError_t StageReserve(size_t n) {
+    if (n <= stage_cap) return cudaSuccess;
+    const size_t nc = std::max(std::max(2 * stage_cap, n + n / 4), size_t(1) << 20);
+    char* ns = nullptr;
+    cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&ns), nc, cudaHostAllocDefault);
+    if (e != cudaSuccess) return e;
+    if (stage) { std::memcpy(ns, stage, up_used); cudaFreeHost(stage); }
+    stage = ns; stage_cap = nc;
+    return cudaSuccess;
+  }
+  cudaError_t Commit(cudaStream_t s);
+  void Release() { if (base) cudaFree(base); if (stage) cudaFreeHost(stage); base = nullptr; stage = nullptr; cap = stage_cap = 0; }
+};
+thread_local Arena* g_rec = nullptr;
+
 struct DevMem {
   void* p = nullptr; size_t bytes = 0;
-  ~DevMem() { if (p) cudaFree(p); }
+  bool view = false, in_work = false; size_t off = 0;   // view: inside the handle's arena (not owned)
+  ~DevMem() { if (p && !view) cudaFree(p); }
   cudaError_t alloc(size_t n) {
-    if (p && n <= bytes) return cudaSuccess;
-    if (p) { cudaFree(p); p = nullptr; bytes = 0; }
     if (n == 0) n = 8;
+    if (g_rec) {   // reserve a slot of the arena's work region
+      if (p && !view) cudaFree(p);
+      p = nullptr; view = true; in_work = true; bytes = n; off = g_rec->work_used; g_rec->work_used += Arena::Align(n);
+      g_rec->members.push_back(this);
+      return cudaSuccess;
+    }
+    if (p && !view && n <= bytes) return cudaSuccess;
+    if (p && !view) cudaFree(p);
+    p = nullptr; bytes = 0; view = false;
     cudaError_t e = cudaMalloc(&p, n);
     if (e == cudaSuccess) bytes = n;
     return e;
   }
   template <typename T> T* as() const { return static_cast<T*>(p); }
 };
+cudaError_t Arena::Commit(cudaStream_t s) {
+  const size_t up = Align(up_used), need = up + work_used;
+  if (need > cap) {
+    if (base) { cudaError_t e0 = cudaStreamSynchronize(s); if (e0 != cudaSuccess) return e0; cudaFree(base); base = nullptr; cap = 0; }
+    const size_t nc = need + need / 4 + (size_t(1) << 16);
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&base), nc);
+    if (e != cudaSuccess) return e;
+    cap = nc;
+  }
+  for (DevMem* m : members) m->p = base + (m->in_work ? up + m->off : m->off);
+  members.clear();
+  return up_used ? cudaMemcpyAsync(base, stage, up_used, cudaMemcpyHostToDevice, s) : cudaSuccess;
+}
 
 }  // namespace
 
@@ -58,9 +107,10 @@ struct bsnls_handle {
   // kernel is gated by the device state, so replaying the graph replaces ~40 stream launches per iteration
   int64_t graph_pass_launches = 0, graph_tail_launches = 0; const void* graph_recs = nullptr;
   cudaGraphExec_t graph_pass = nullptr, graph_tail = nullptr; bool graphs_valid = false; bool use_graphs = true;
+  int solves_on_structure = 0;   // graphs are captured from the second solve of one structure on: capture + instantiation cost more than one solve's launches
   float last_eval_ms = 0, last_schur_ms = 0;
   int rank = 0, world = 1; NcclComm comm = nullptr;
-  int lm_lo = 0, lm_hi = 0, ne_global = 0, nobs_global = 0, nb_act_e = 0; DevMem d_owned;
+  int lm_lo = 0, lm_hi = 0, ne_global = 0, nobs_global = 0, nb_act_e = 0; DevMem d_owned, d_flag;
 
   // host-side structure
   int num_blocks = 0; int64_t num_values = 0;
@@ -90,6 +140,7 @@ struct bsnls_handle {
   DevMem d_eval_items, d_eval_item_ptr, d_pm_lm_off, d_pm_cam, d_pm_pixel, d_pose_tab, d_pose_part;
 
   DeviceProblem P{};
+  Arena arena;   // every buffer bsnls_set_problem creates lives here
   // device memory
   DevMem d_blk_off, d_blk_size, d_blk_tan, d_blk_manifold, d_active, d_pose_q_off, d_pose_t_off, d_pose_q_tan,
       d_pose_t_tan, d_pose_ptr, d_pose_obs, d_obs_pose, d_obs_lm, d_obs_cam, d_obs_pixel, d_lm_ptr, d_lm_off, d_cams,
@@ -121,6 +172,17 @@ struct bsnls_handle {
 namespace {
 
 template <typename T> cudaError_t upload(DevMem& m, const std::vector<T>& v, cudaStream_t s) {
+  if (g_rec) {   // copy into the pinned staging mirror; the device pointer is resolved by Arena::Commit
+    const size_t n = std::max<size_t>(v.size() * sizeof(T), 8);
+    cudaError_t e = g_rec->StageReserve(g_rec->up_used + Arena::Align(n));
+    if (e != cudaSuccess) return e;
+    if (m.p && !m.view) cudaFree(m.p);
+    m.p = nullptr; m.view = true; m.in_work = false; m.bytes = n; m.off = g_rec->up_used;
+    if (!v.empty()) std::memcpy(g_rec->stage + m.off, v.data(), v.size() * sizeof(T));
+    g_rec->up_used += Arena::Align(n);
+    g_rec->members.push_back(&m);
+    return cudaSuccess;
+  }
   cudaError_t e = m.alloc(v.size() * sizeof(T));
   if (e != cudaSuccess || v.empty()) return e;
   return cudaMemcpyAsync(m.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s);
@@ -494,6 +556,7 @@ void bsnls_destroy(bsnls_handle* h) {
   if (h->graph_pass) cudaGraphExecDestroy(h->graph_pass);
   if (h->graph_tail) cudaGraphExecDestroy(h->graph_tail);
   if (h->comm) Nccl().CommDestroy(h->comm);
+  h->arena.Release();
   if (h->stream) cudaStreamDestroy(h->stream);
   if (h->side) cudaStreamDestroy(h->side);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
@@ -509,8 +572,14 @@ int bsnls_set_options(bsnls_handle* h, const bsnls_options* o) {
   if (!h || !o) return BSNLS_ERR_INVALID;
   std::string why;
   if (!ValidOptions(*o, &why)) return h->fail(BSNLS_ERR_INVALID, "invalid options: %s", why.c_str());
-  const int dev = h->opt.device; h->opt = *o; h->opt.device = dev;
-  h->graphs_valid = false;   // kernel arguments (options) are baked into the captured graphs
+  const int dev = h->opt.device;
+  bsnls_options n = *o; n.device = dev;
+  const bool solver_changed = n.linear_solver != h->opt.linear_solver;
+  // kernel arguments (options) are baked into the captured graphs: re-capture only when something changed
+  { bsnls_options a = n, b = h->opt; a.max_solver_time_in_seconds = b.max_solver_time_in_seconds = 0.0;   // the budget is a host-side check
+    if (std::memcmp(&a, &b, sizeof(a)) != 0) h->graphs_valid = false; }
+  h->opt = n;
+  if (solver_changed && h->has_problem) h->has_problem = false;   // the reduced-system storage depends on the linear solver: set_problem again
   return BSNLS_OK;
 }
 
@@ -612,20 +681,35 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   for (int k = 0; k < nobs; ++k) g_pose[k] = obs_pose[order[k]];
 
   // ---- pose-pair blocks of the reduced system: pattern of the WHOLE graph (identical on every rank) ----
-  std::unordered_map<uint64_t, int> key_id;
-  auto key_of = [&](int a2, int b2) { return (uint64_t)std::min(a2, b2) * (uint64_t)h->np + (uint64_t)std::max(a2, b2); };
+  // Pair (a <= b) exists iff some landmark is seen by both poses. Built per pose with a stamp array over the poses of
+  // the landmarks it observes (no hashing); pair id = position in (a, b) order; lookups go through pair_row / pair_b.
+  std::vector<int> pair_row;            // CSR over a: pairs [pair_row[a], pair_row[a+1]) have pose a and ascending b >= a
   h->pair_a.clear(); h->pair_b.clear();
   {
-    key_id.reserve((size_t)h->np * 16);
-    for (int e = 0; e < ne_g; ++e)
-      for (int i = lm_ptr[e]; i < lm_ptr[e + 1]; ++i)
-        for (int j = i; j < lm_ptr[e + 1]; ++j) key_id.emplace(key_of(g_pose[i], g_pose[j]), 0);
-    std::vector<uint64_t> keys; keys.reserve(key_id.size());
-    for (auto& kv : key_id) keys.push_back(kv.first);
-    std::sort(keys.begin(), keys.end());
-    for (size_t k = 0; k < keys.size(); ++k) { key_id[keys[k]] = (int)k; h->pair_a.push_back((int)(keys[k] / h->np)); h->pair_b.push_back((int)(keys[k] % h->np)); }
-    h->npairs = (int)keys.size();
+    std::vector<int> gp_ptr(h->np + 1, 0), gp_lm(nobs);
+    for (int k = 0; k < nobs; ++k) gp_ptr[g_pose[k] + 1]++;
+    for (int a = 0; a < h->np; ++a) gp_ptr[a + 1] += gp_ptr[a];
+    { std::vector<int> cur(gp_ptr.begin(), gp_ptr.end() - 1); for (int e = 0; e < ne_g; ++e) for (int k = lm_ptr[e]; k < lm_ptr[e + 1]; ++k) gp_lm[cur[g_pose[k]]++] = e; }
+    std::vector<int> stamp(h->np, -1), row;
+    pair_row.assign(h->np + 1, 0);
+    for (int a = 0; a < h->np; ++a) {
+      row.clear();
+      for (int q = gp_ptr[a]; q < gp_ptr[a + 1]; ++q) {
+        const int e = gp_lm[q];
+        for (int k = lm_ptr[e]; k < lm_ptr[e + 1]; ++k) { const int b = g_pose[k]; if (b >= a && stamp[b] != a) { stamp[b] = a; row.push_back(b); } }
+      }
+      std::sort(row.begin(), row.end());
+      for (int b : row) { h->pair_a.push_back(a); h->pair_b.push_back(b); }
+      pair_row[a + 1] = (int)h->pair_b.size();
+    }
+    h->npairs = (int)h->pair_b.size();
   }
+  auto pair_id = [&](int a2, int b2) -> int {   // -1: the two poses share no landmark
+    const int a = std::min(a2, b2), b = std::max(a2, b2);
+    const int* r0 = h->pair_b.data() + pair_row[a]; const int* r1 = h->pair_b.data() + pair_row[a + 1];
+    const int* p = std::lower_bound(r0, r1, b);
+    return (p != r1 && *p == b) ? (int)(p - h->pair_b.data()) : -1;
+  };
   // ---- pose ranking for locality: breadth-first order of the co-visibility graph from a peripheral pose ----
   std::vector<int> pose_rank(h->np, -1);
   {
@@ -850,14 +934,14 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     for (int e = 0; e < h->ne; ++e) {
       if (!wide[e]) continue;
       for (int i = lm_ptr_local[e]; i < lm_ptr_local[e + 1]; ++i)
-        for (int j = i; j < lm_ptr_local[e + 1]; ++j) cnt[key_id[key_of(s_pose[i], s_pose[j])]] += (s_pose[i] == s_pose[j] && i != j) ? 2 : 1;
+        for (int j = i; j < lm_ptr_local[e + 1]; ++j) cnt[pair_id(s_pose[i], s_pose[j])] += (s_pose[i] == s_pose[j] && i != j) ? 2 : 1;
     }
     for (int c = 0; c < h->nchunks; ++c) {
       const int ns = chunk_nslots[c];
       for (int A = 0; A < ns; ++A) for (int B = A; B < ns; ++B) {
         // two poses of a chunk need not share a landmark: such a slot pair is not a block of S (its partial block stays zero)
-        auto kit = key_id.find(key_of(chunk_pose[(size_t)c * kChunkSlots + A], chunk_pose[(size_t)c * kChunkSlots + B]));
-        if (kit != key_id.end()) pcnt[kit->second]++;
+        const int id = pair_id(chunk_pose[(size_t)c * kChunkSlots + A], chunk_pose[(size_t)c * kChunkSlots + B]);
+        if (id >= 0) pcnt[id]++;
       }
     }
     for (int k = 0; k < h->npairs; ++k) { pair_ptr[k + 1] = pair_ptr[k] + cnt[k]; pp_ptr[k + 1] = pp_ptr[k] + pcnt[k]; }
@@ -869,7 +953,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       for (int i = lm_ptr_local[e]; i < lm_ptr_local[e + 1]; ++i)
         for (int j = i; j < lm_ptr_local[e + 1]; ++j) {
           const int a = s_pose[i], b = s_pose[j];
-          const int id = key_id[key_of(a, b)];
+          const int id = pair_id(a, b);
           if (a < b || i == j) { item_i[cur[id]] = i; item_j[cur[id]] = j; cur[id]++; }
           else if (a > b) { item_i[cur[id]] = j; item_j[cur[id]] = i; cur[id]++; }
           else { item_i[cur[id]] = i; item_j[cur[id]] = j; cur[id]++; item_i[cur[id]] = j; item_j[cur[id]] = i; cur[id]++; }
@@ -879,9 +963,8 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       const int ns = chunk_nslots[c];
       int q = 0;
       for (int A = 0; A < ns; ++A) for (int B = A; B < ns; ++B, ++q) {
-        auto kit = key_id.find(key_of(chunk_pose[(size_t)c * kChunkSlots + A], chunk_pose[(size_t)c * kChunkSlots + B]));
-        if (kit == key_id.end()) continue;
-        const int id = kit->second;
+        const int id = pair_id(chunk_pose[(size_t)c * kChunkSlots + A], chunk_pose[(size_t)c * kChunkSlots + B]);
+        if (id < 0) continue;
         pp_toff[pcur[id]] = chunk_tile_off[c]; pp_info[pcur[id]] = A | (B << 8) | (ns << 16);
         pcur[id]++;
       }
@@ -913,12 +996,13 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   }
   std::stable_sort(refs.begin(), refs.end(), [](const GfRef& a, const GfRef& b) { return a.removed < b.removed; });
   h->ngf = (int)refs.size(); h->ngf_active = 0;
-  std::map<std::pair<int, int>, int> gf_id;  // (type, index in group) -> gf id
+  std::vector<std::vector<int>> gf_id(BSNLS_NUM_FACTOR_TYPES);  // [type][index in group] -> gf id
+  for (const bsnls_factor_group* G : gfg) gf_id[G->type].assign(G->count, -1);
   int64_t joff = 0, roff = 0;
   for (int f = 0; f < h->ngf; ++f) {
     const bsnls_factor_group* G = refs[f].g; const int i = refs[f].i, nbk = kNumBlocks[G->type], nr = kNumRes[G->type], stride = kStride[G->type];
     if (!refs[f].removed) h->ngf_active++;
-    gf_id[{G->type, i}] = f;
+    gf_id[G->type][i] = f;
     gf_type.push_back(G->type); gf_nblk.push_back(nbk); gf_nres.push_back(nr);
     for (int b = 0; b < kGfMaxBlocks; ++b) gf_blocks.push_back(b < nbk ? G->blocks[(int64_t)i * nbk + b] : -1);
     gf_coff.push_back((long long)gf_consts.size());
@@ -1012,7 +1096,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
         const int ri = G.res_index[i];
         if (ri < 0 || ri >= total || seen[ri]) return h->fail(BSNLS_ERR_INVALID, "res_index is not a permutation of 0..N-1");
         seen[ri] = 1;
-        h->res_order[ri] = {G.type, G.type == BSNLS_FACTOR_REPROJECTION ? inv_order[i] : gf_id[{G.type, i}], 0};
+        h->res_order[ri] = {G.type, G.type == BSNLS_FACTOR_REPROJECTION ? inv_order[i] : gf_id[G.type][i], 0};
       }
     }
     int row = 0;
@@ -1020,8 +1104,10 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     h->num_res_rows = row;
   }
 
-  // ---- upload ----
+  // ---- upload: one arena, one staged copy (see Arena) ----
   cudaStream_t s = h->stream;
+  struct RecGuard { ~RecGuard() { g_rec = nullptr; } } rec_guard;
+  h->arena.Begin(); g_rec = &h->arena;
   CK(upload(h->d_blk_off, h->blk_off, s)); CK(upload(h->d_blk_size, h->blk_size, s)); CK(upload(h->d_blk_tan, h->blk_tan, s));
   CK(upload(h->d_blk_manifold, h->blk_manifold, s)); CK(upload(h->d_active, h->active_blocks, s));
   CK(upload(h->d_pose_q_off, pose_q_off, s)); CK(upload(h->d_pose_t_off, pose_t_off, s)); CK(upload(h->d_pose_q_tan, pose_q_tan, s));
@@ -1150,7 +1236,6 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(h->d_Jrec.alloc(sizeof(double) * kJRec * (size_t)h->nobs)); CK(h->d_Vrec.alloc(sizeof(double) * kVRec * (size_t)h->nobs));
   CK(h->d_minv.alloc(sizeof(double) * 6 * (size_t)h->ne)); CK(h->d_lmz.alloc(sizeof(double) * 3 * (size_t)h->ne)); CK(h->d_grad.alloc(sizeof(double) * ntan)); CK(h->d_colsq.alloc(sizeof(double) * ntan));
   CK(h->d_gradL.alloc(sizeof(double) * nf_dim)); CK(h->d_colsqL.alloc(sizeof(double) * nf_dim));
-  CK(cudaMemsetAsync(h->d_gradL.p, 0, sizeof(double) * nf_dim, s)); CK(cudaMemsetAsync(h->d_colsqL.p, 0, sizeof(double) * nf_dim, s));  // non-pose entries stay 0
   if (h->world > 1) { CK(h->d_gradS.alloc(sizeof(double) * nf_dim)); CK(h->d_colsqS.alloc(sizeof(double) * nf_dim)); }
   CK(h->d_scale.alloc(sizeof(double) * ntan)); CK(h->d_y.alloc(sizeof(double) * ntan)); CK(h->d_yf.alloc(sizeof(double) * nf_dim));
   CK(h->d_rhs.alloc(sizeof(double) * nf_dim)); CK(h->d_S.alloc(sizeof(double) * (h->sparse ? (size_t)h->nnzb * 9 : (size_t)nf_dim * nf_dim)));
@@ -1163,19 +1248,13 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     h->tc_nroots = (int)tc_roots.size();
     CK(upload(h->d_tc_bw_ptr, tc_bw_ptr, s)); CK(upload(h->d_tc_bw_col, tc_bw_col, s)); CK(upload(h->d_tc_bw_tail, tc_bw_tail, s)); CK(upload(h->d_tc_bw_src, tc_bw_src, s));
     CK(upload(h->d_tc_bw_i, tc_bw_i, s)); CK(upload(h->d_tc_roots, tc_roots, s));
-    h->TC.bw_ptr = h->d_tc_bw_ptr.as<int>(); h->TC.bw_col = h->d_tc_bw_col.as<int>(); h->TC.bw_tail = h->d_tc_bw_tail.as<int>(); h->TC.bw_src = h->d_tc_bw_src.as<long long>();
-    h->TC.bw_i = h->d_tc_bw_i.as<int>(); h->TC.roots = h->d_tc_roots.as<int>();
     CK(upload(h->d_tc_pan_k, tc_pan_k, s)); CK(upload(h->d_tc_pan_x, tc_pan_x, s)); CK(upload(h->d_tc_upd_ptr, tc_upd_ptr, s)); CK(upload(h->d_tc_upd_dst, tc_upd_dst, s));
     CK(upload(h->d_tc_upd_a, tc_upd_a, s)); CK(upload(h->d_tc_upd_b, tc_upd_b, s)); CK(upload(h->d_tc_fw_ptr, tc_fw_ptr, s)); CK(upload(h->d_tc_fw_row, tc_fw_row, s));
     CK(upload(h->d_tc_fw_tail, tc_fw_tail, s)); CK(upload(h->d_tc_fw_src, tc_fw_src, s)); CK(upload(h->d_tc_fw_k, tc_fw_k, s)); CK(upload(h->d_tc_lev_cols, tc_lev_cols, s));
-    h->TC.pan_k = h->d_tc_pan_k.as<int>(); h->TC.pan_x = h->d_tc_pan_x.as<int>(); h->TC.upd_ptr = h->d_tc_upd_ptr.as<int>(); h->TC.upd_dst = h->d_tc_upd_dst.as<long long>();
-    h->TC.upd_a = h->d_tc_upd_a.as<long long>(); h->TC.upd_b = h->d_tc_upd_b.as<long long>(); h->TC.fw_ptr = h->d_tc_fw_ptr.as<int>(); h->TC.fw_row = h->d_tc_fw_row.as<int>();
-    h->TC.fw_tail = h->d_tc_fw_tail.as<int>(); h->TC.fw_src = h->d_tc_fw_src.as<long long>(); h->TC.fw_k = h->d_tc_fw_k.as<int>(); h->TC.lev_cols = h->d_tc_lev_cols.as<int>();
     CK(upload(h->d_tc_tile_off, tc_tile_off, s)); CK(upload(h->d_tc_col_ptr, h->tc_col_ptr, s)); CK(upload(h->d_tc_col_rows, tc_col_rows, s));
     h->tc_T_bytes = sizeof(double) * kTileDoubles * (size_t)tc_tiles;
     CK(h->d_tc_T.alloc(h->tc_T_bytes)); CK(h->d_tc_W.alloc(sizeof(double) * kTileDoubles * (size_t)nT)); CK(h->d_tc_b.alloc(sizeof(double) * kTS * (size_t)nT));
-    h->TC.nT = nT; h->TC.n = nf_dim; h->TC.tile_off = h->d_tc_tile_off.as<long long>(); h->TC.col_ptr = h->d_tc_col_ptr.as<int>();
-    h->TC.col_rows = h->d_tc_col_rows.as<int>(); h->TC.T = h->d_tc_T.as<double>(); h->TC.W = h->d_tc_W.as<double>(); h->TC.b = h->d_tc_b.as<double>();
+    h->TC.nT = nT; h->TC.n = nf_dim;
   }
   if (h->pcg) {
     int dev_sms = 0, per_sm = 0;
@@ -1193,8 +1272,36 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(h->d_step_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_candsq_part.alloc(sizeof(double) * h->nb_act));
   CK(h->d_gsq_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_gmax_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_xsq_part.alloc(sizeof(double) * h->nb_act));
   CK(h->d_red.alloc(sizeof(double) * 32)); CK(h->d_state.alloc(sizeof(LMState)));
+  CK(h->arena.Commit(s)); g_rec = nullptr;   // pointers are valid from here on
+  CK(cudaMemsetAsync(h->d_gradL.p, 0, sizeof(double) * nf_dim, s)); CK(cudaMemsetAsync(h->d_colsqL.p, 0, sizeof(double) * nf_dim, s));  // non-pose entries stay 0
   CK(cudaMemcpyAsync(h->d_x.p, pr->block_values, sizeof(double) * off, cudaMemcpyHostToDevice, s));
   CK(cudaMemsetAsync(h->d_y.p, 0, sizeof(double) * ntan, s));
+  if (h->tiled) {
+    h->TC.bw_ptr = h->d_tc_bw_ptr.as<int>();
+    h->TC.bw_col = h->d_tc_bw_col.as<int>();
+    h->TC.bw_tail = h->d_tc_bw_tail.as<int>();
+    h->TC.bw_src = h->d_tc_bw_src.as<long long>();
+    h->TC.bw_i = h->d_tc_bw_i.as<int>();
+    h->TC.roots = h->d_tc_roots.as<int>();
+    h->TC.pan_k = h->d_tc_pan_k.as<int>();
+    h->TC.pan_x = h->d_tc_pan_x.as<int>();
+    h->TC.upd_ptr = h->d_tc_upd_ptr.as<int>();
+    h->TC.upd_dst = h->d_tc_upd_dst.as<long long>();
+    h->TC.upd_a = h->d_tc_upd_a.as<long long>();
+    h->TC.upd_b = h->d_tc_upd_b.as<long long>();
+    h->TC.fw_ptr = h->d_tc_fw_ptr.as<int>();
+    h->TC.fw_row = h->d_tc_fw_row.as<int>();
+    h->TC.fw_tail = h->d_tc_fw_tail.as<int>();
+    h->TC.fw_src = h->d_tc_fw_src.as<long long>();
+    h->TC.fw_k = h->d_tc_fw_k.as<int>();
+    h->TC.lev_cols = h->d_tc_lev_cols.as<int>();
+    h->TC.tile_off = h->d_tc_tile_off.as<long long>();
+    h->TC.col_ptr = h->d_tc_col_ptr.as<int>();
+    h->TC.col_rows = h->d_tc_col_rows.as<int>();
+    h->TC.T = h->d_tc_T.as<double>();
+    h->TC.W = h->d_tc_W.as<double>();
+    h->TC.b = h->d_tc_b.as<double>();
+  }
 
   DeviceProblem& P = h->P;
   P.num_blocks = nb; P.num_active = (int)h->active_blocks.size(); P.blk_off = h->d_blk_off.as<int>(); P.blk_size = h->d_blk_size.as<int>();
@@ -1220,7 +1327,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   P.sparse = h->sparse ? 1 : 0; P.nnzb = h->nnzb; P.bsr_rowptr = h->d_bsr_rowptr.as<int>(); P.bsr_col = h->d_bsr_col.as<int>();
   P.diag_slot = h->d_diag_slot.as<int>(); P.pair_slot = h->d_pair_slot.as<int>(); P.gd_slot = h->d_gd_slot.as<int>();
   CK(cudaStreamSynchronize(s));  // host vectors above go out of scope
-  h->has_problem = true; h->graphs_valid = false;
+  h->has_problem = true; h->graphs_valid = false; h->solves_on_structure = 0;
   return BSNLS_OK;
 }
 
@@ -1261,13 +1368,31 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
   CK(cudaMemcpyAsync(h->d_xc.p, h->d_x.p, sizeof(double) * h->num_values, cudaMemcpyDeviceToDevice, h->stream));  // constant blocks
   CK(cudaEventRecord(h->ev0, h->stream));
   if ((rc = EnqueueXNorm(h)) != BSNLS_OK) return rc;
-  // a wall-clock budget is a per-process decision; ranks of a sharded solve must issue identical collectives, so the
-  // budget is only honoured on a single GPU
-  const bool timed = h->opt.max_solver_time_in_seconds < 1e8 && h->world == 1;
+  // A wall-clock budget (optimizeFor, hash_graph.cpp:428-444) is checked on the host before every pass, as Ceres checks it
+  // when it finalises an iteration. Ranks of a sharded solve must issue identical collectives, so they agree on the
+  // decision first (max over ranks of the "spent" flag).
+  const bool timed = h->opt.max_solver_time_in_seconds < 1e8;
+  auto budget_spent = [&](int* spent) -> int {
+    *spent = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() >= h->opt.max_solver_time_in_seconds ? 1 : 0;
+    if (h->world <= 1) return BSNLS_OK;
+    double f = *spent;
+    CK(h->d_flag.alloc(sizeof(double)));
+    CK(cudaMemcpyAsync(h->d_flag.p, &f, sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    const int rc2 = AllReduce(h, h->d_flag.as<double>(), 1, kNcclMax);
+    if (rc2 != BSNLS_OK) return rc2;
+    CK(cudaMemcpyAsync(&f, h->d_flag.p, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    *spent = f > 0.0 ? 1 : 0;
+    return BSNLS_OK;
+  };
   auto enqueue_tail = [&]() -> int { return EnqueueTail(h, o, recs); };
   auto enqueue_pass = [&]() -> int { return EnqueuePass(h, o, recs); };
   // Small reduced systems are launch-latency bound: replay captured graphs instead of enqueuing kernel by kernel.
-  const bool graphs = h->use_graphs && h->world == 1 && !h->pcg;   // the launch sequence of a pass is fixed per problem (the cooperative PCG launch is not captured)
+  // the launch sequence of a pass is fixed per problem (the cooperative PCG launch is not captured). A structure that is
+  // solved once (a sliding window changes every smoother cycle) is launched directly; big reduced systems (hundreds of
+  // launches per pass) are captured at once.
+  const bool graphs = h->use_graphs && h->world == 1 && !h->pcg && (h->solves_on_structure > 0 || h->tiled);
+  h->solves_on_structure++;
   if (graphs && (!h->graphs_valid || h->graph_recs != recs)) {
     if (h->graph_pass) { cudaGraphExecDestroy(h->graph_pass); h->graph_pass = nullptr; }
     if (h->graph_tail) { cudaGraphExecDestroy(h->graph_tail); h->graph_tail = nullptr; }
@@ -1289,22 +1414,25 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
     h->graphs_valid = true;
   }
   for (int pass = 0; pass <= max_it; ++pass) {
+    if (timed && pass < max_it) {
+      int spent = 0;
+      if ((rc = budget_spent(&spent)) != BSNLS_OK) return rc;
+      if (spent) {
+        // iteration zero, or the Jacobian pass an accepted step still needs for its record; then stop (NO_CONVERGENCE)
+        if ((rc = enqueue_tail()) != BSNLS_OK) return rc;
+        LAUNCH(h, set_done_kernel, 1, 1, st, (int)BSNLS_NO_CONVERGENCE, (int)MSG_MAX_TIME);
+        break;
+      }
+    }
     if (pass == max_it) {
       if (graphs) { CK(cudaGraphLaunch(h->graph_tail, h->stream)); h->launches += h->graph_tail_launches; } else if ((rc = enqueue_tail()) != BSNLS_OK) return rc;
       break;
     }
     if (graphs) { CK(cudaGraphLaunch(h->graph_pass, h->stream)); h->launches += h->graph_pass_launches; } else if ((rc = enqueue_pass()) != BSNLS_OK) return rc;
     if (timed || (pass & 3) == 3) {
-      // poll the device state so that converged solves stop enqueuing; with a time budget also check the clock
+      // poll the device state so that converged solves stop enqueuing (every rank reads the same replicated state)
       LMState hs; CK(cudaMemcpyAsync(&hs, st, sizeof(hs), cudaMemcpyDeviceToHost, h->stream)); CK(cudaStreamSynchronize(h->stream));
       if (hs.done) break;
-      const double el = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-      if (timed && el >= h->opt.max_solver_time_in_seconds) {
-        // an accepted step still needs its Jacobian pass to be recorded; then stop (NO_CONVERGENCE)
-        if ((rc = enqueue_tail()) != BSNLS_OK) return rc;
-        LAUNCH(h, set_done_kernel, 1, 1, st, (int)BSNLS_NO_CONVERGENCE, (int)MSG_MAX_TIME);
-        break;
-      }
     }
   }
   if ((rc = GatherValues(h)) != BSNLS_OK) return rc;

@@ -35,7 +35,24 @@ def load_library():
     lib.bsfuse_current_values.argtypes = [G, C.POINTER(C.c_double)]
     lib.bsfuse_set_values.argtypes = [G, C.POINTER(C.c_double)]
     lib.bsfuse_optimize.argtypes = [G, C.POINTER(cabi.Options), C.POINTER(cabi.Summary), C.POINTER(cabi.Iteration), C.c_int]
+    lib.bsfuse_optimize_for.argtypes = [G, C.c_double, C.POINTER(cabi.Options), C.POINTER(cabi.Summary), C.POINTER(cabi.Iteration), C.c_int]
+    lib.bsfuse_last_timing.argtypes = [G, C.POINTER(C.c_double)]
     lib.bsfuse_evaluate.argtypes = [G, C.POINTER(C.c_double)]
+    R = C.c_void_p
+    lib.bsfuse_replay_new.argtypes = [C.c_int, C.c_int, C.c_uint64]
+    lib.bsfuse_replay_new.restype = R
+    lib.bsfuse_replay_free.argtypes = [R]
+    lib.bsfuse_replay_error.argtypes = [R]
+    lib.bsfuse_replay_error.restype = C.c_char_p
+    lib.bsfuse_replay_done.argtypes = [R]
+    lib.bsfuse_replay_advance.argtypes = [R]
+    lib.bsfuse_replay_advance.restype = C.c_double
+    lib.bsfuse_replay_flatten.argtypes = [R]
+    lib.bsfuse_replay_flatten.restype = C.POINTER(cabi.Problem)
+    lib.bsfuse_replay_observations.argtypes = [R]
+    lib.bsfuse_replay_observations.restype = C.c_longlong
+    lib.bsfuse_replay_optimize.argtypes = [R, C.POINTER(cabi.Options), C.POINTER(cabi.Summary), C.POINTER(cabi.Iteration), C.c_int, C.POINTER(C.c_double)]
+    lib.bsfuse_replay_current_values.argtypes = [R, C.POINTER(C.c_double)]
     lib.bsfuse_uuid_name.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t, C.c_char_p]
     lib.bsfuse_uuid_stamped.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_char_p]
     lib.bsfuse_uuid_landmark.argtypes = [C.c_char_p, C.c_uint64, C.c_char_p]
@@ -132,12 +149,22 @@ class HashGraph:
         v = np.ascontiguousarray(values, np.float64)
         self._lib.bsfuse_set_values(self._g, v.ctypes.data_as(C.POINTER(C.c_double)))
 
-    def optimize(self, options=None, max_iters=256):
-        """GpuHashGraph::optimize: flatten in createProblem order, solve on the GPU, write variables back."""
+    TIMING = ("flatten_s", "upload_s", "solve_s", "download_s", "structure_reused")
+
+    def last_timing(self):
+        """Host wall-clock split of the last optimize(): flatten (or value gather), bsnls_set_problem (or
+        bsnls_set_values), bsnls_solve, bsnls_get_values + scatter; structure_reused = 1 when the device problem was kept."""
+        t = (C.c_double * 5)()
+        self._lib.bsfuse_last_timing(self._g, t)
+        return dict(zip(self.TIMING, [float(v) for v in t]))
+
+    def optimize(self, options=None, max_iters=256, max_time_s=None):
+        """GpuHashGraph::optimize (optimizeFor when max_time_s is given): flatten in createProblem order (or just gather
+        the values when the graph's structure is unchanged), solve on the GPU, write variables back."""
         options = options or cabi.Options.defaults()
         s = cabi.Summary()
         its = (cabi.Iteration * max_iters)()
-        rc = self._lib.bsfuse_optimize(self._g, C.byref(options), C.byref(s), its, max_iters)
+        rc = self._lib.bsfuse_optimize_for(self._g, -1.0 if max_time_s is None else float(max_time_s), C.byref(options), C.byref(s), its, max_iters)
         if rc == -1:
             raise ValueError(self._lib.bsfuse_last_error(self._g).decode())
         if rc != 0:
@@ -149,3 +176,53 @@ class HashGraph:
         if self._lib.bsfuse_evaluate(self._g, C.byref(c)) != 0:
             raise RuntimeError(self._lib.bsfuse_last_error(self._g).decode())
         return c.value
+
+
+class SmootherReplay:
+    """Python face of bsfuse::SmootherReplay (host/smoother_replay.h): the fixed-lag smoother's cycle — new keyframe in,
+    oldest keyframe pseudo-marginalised, optimize — on a synthetic VIO trajectory."""
+
+    def __init__(self, total_keyframes, window_keyframes=10, seed=0):
+        self._lib = load_library()
+        self._r = self._lib.bsfuse_replay_new(total_keyframes, window_keyframes, seed)
+        err = self._lib.bsfuse_replay_error(self._r)
+        if err:
+            raise ValueError(err.decode())
+
+    def __del__(self):
+        if getattr(self, "_r", None):
+            self._lib.bsfuse_replay_free(self._r)
+            self._r = None
+
+    def done(self):
+        return bool(self._lib.bsfuse_replay_done(self._r))
+
+    def advance(self):
+        t = self._lib.bsfuse_replay_advance(self._r)
+        if t < 0:
+            raise RuntimeError(self._lib.bsfuse_replay_error(self._r).decode())
+        return t
+
+    def flatten(self):
+        cp = self._lib.bsfuse_replay_flatten(self._r)
+        if not cp:
+            raise ValueError(self._lib.bsfuse_replay_error(self._r).decode())
+        return problem_to_numpy(cp.contents)
+
+    def observations(self):
+        return int(self._lib.bsfuse_replay_observations(self._r))
+
+    def optimize(self, options=None, max_iters=64):
+        options = options or cabi.Options.defaults()
+        s = cabi.Summary()
+        its = (cabi.Iteration * max_iters)()
+        t = (C.c_double * 5)()
+        rc = self._lib.bsfuse_replay_optimize(self._r, C.byref(options), C.byref(s), its, max_iters, t)
+        if rc != 0:
+            raise RuntimeError(self._lib.bsfuse_replay_error(self._r).decode())
+        return s, [its[i] for i in range(min(s.num_iterations, max_iters))], dict(zip(HashGraph.TIMING, [float(v) for v in t]))
+
+    def current_values(self, n):
+        v = np.zeros(n)
+        self._lib.bsfuse_replay_current_values(self._r, v.ctypes.data_as(C.POINTER(C.c_double)))
+        return v

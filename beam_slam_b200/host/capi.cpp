@@ -3,6 +3,7 @@
 #include <memory>
 
 #include "gpu_hash_graph.h"
+#include "smoother_replay.h"
 #include "synthetic.h"
 
 using namespace bsfuse;
@@ -57,38 +58,94 @@ void bsfuse_current_values(bsfuse_graph* g, double* out) {
 }
 void bsfuse_set_values(bsfuse_graph* g, const double* values) { g->flat.ScatterValues(values); }
 
-// GpuHashGraph::optimize through the public interface; fills the C summary for python.
-int bsfuse_optimize(bsfuse_graph* g, const bsnls_options* o, bsnls_summary* s, bsnls_iteration* its, int max_its) {
+}  // extern "C"
+
+namespace {
+SolverOptions FromC(const bsnls_options* o) {
+  SolverOptions so;
+  so.max_num_iterations = o->max_num_iterations; so.max_solver_time_in_seconds = o->max_solver_time_in_seconds;
+  so.function_tolerance = o->function_tolerance; so.gradient_tolerance = o->gradient_tolerance;
+  so.parameter_tolerance = o->parameter_tolerance; so.initial_trust_region_radius = o->initial_trust_region_radius;
+  so.max_trust_region_radius = o->max_trust_region_radius; so.min_trust_region_radius = o->min_trust_region_radius;
+  so.min_relative_decrease = o->min_relative_decrease; so.min_lm_diagonal = o->min_lm_diagonal;
+  so.max_lm_diagonal = o->max_lm_diagonal; so.max_num_consecutive_invalid_steps = o->max_num_consecutive_invalid_steps;
+  so.jacobi_scaling = o->jacobi_scaling != 0; so.linear_solver = o->linear_solver;
+  return so;
+}
+void ToC(const SolverSummary& r, bsnls_summary* s, bsnls_iteration* its, int max_its) {
+  std::memset(s, 0, sizeof(*s));
+  s->termination_type = r.termination_type; s->num_iterations = static_cast<int>(r.iterations.size());
+  s->num_successful_steps = r.num_successful_steps; s->num_unsuccessful_steps = r.num_unsuccessful_steps;
+  s->initial_cost = r.initial_cost; s->final_cost = r.final_cost; s->fixed_cost = r.fixed_cost;
+  s->total_time_in_seconds = r.total_time_in_seconds; s->device_time_in_seconds = r.device_time_in_seconds;
+  s->num_e_blocks = r.num_e_blocks; s->num_f_blocks = r.num_f_blocks; s->reduced_system_dim = r.reduced_system_dim;
+  s->linear_solver_used = r.linear_solver_used; s->reduced_system_nnz_blocks = r.reduced_system_nnz_blocks;
+  std::snprintf(s->message, sizeof(s->message), "%s", r.message.c_str());
+  for (int i = 0; i < s->num_iterations && i < max_its && its; ++i) {
+    const IterationSummary& a = r.iterations[i];
+    its[i] = bsnls_iteration{a.iteration, a.step_is_valid, a.step_is_successful, a.linear_solver_iterations, a.cost,
+                             a.cost_change, a.gradient_max_norm, a.gradient_norm, a.step_norm, a.relative_decrease,
+                             a.trust_region_radius};
+  }
+}
+void TimingOut(const GpuHashGraph& g, double out[5]) {
+  const auto& t = g.lastTiming();
+  out[0] = t.flatten; out[1] = t.upload; out[2] = t.solve; out[3] = t.download; out[4] = t.structure_reused ? 1.0 : 0.0;
+}
+}  // namespace
+
+struct bsfuse_replay { std::unique_ptr<SmootherReplay> r; FlatProblem flat; std::string error; };
+
+extern "C" {
+
+// GpuHashGraph::optimize / optimizeFor (max_time_s >= 0) through the public interface; fills the C summary for python.
+int bsfuse_optimize_for(bsfuse_graph* g, double max_time_s, const bsnls_options* o, bsnls_summary* s, bsnls_iteration* its, int max_its) {
   try {
-    SolverOptions so;
-    so.max_num_iterations = o->max_num_iterations; so.max_solver_time_in_seconds = o->max_solver_time_in_seconds;
-    so.function_tolerance = o->function_tolerance; so.gradient_tolerance = o->gradient_tolerance;
-    so.parameter_tolerance = o->parameter_tolerance; so.initial_trust_region_radius = o->initial_trust_region_radius;
-    so.max_trust_region_radius = o->max_trust_region_radius; so.min_trust_region_radius = o->min_trust_region_radius;
-    so.min_relative_decrease = o->min_relative_decrease; so.min_lm_diagonal = o->min_lm_diagonal;
-    so.max_lm_diagonal = o->max_lm_diagonal; so.max_num_consecutive_invalid_steps = o->max_num_consecutive_invalid_steps;
-    so.jacobi_scaling = o->jacobi_scaling != 0; so.linear_solver = o->linear_solver;
-    g->last = g->graph.optimize(so);
-    const SolverSummary& r = g->last;
-    std::memset(s, 0, sizeof(*s));
-    s->termination_type = r.termination_type; s->num_iterations = static_cast<int>(r.iterations.size());
-    s->num_successful_steps = r.num_successful_steps; s->num_unsuccessful_steps = r.num_unsuccessful_steps;
-    s->initial_cost = r.initial_cost; s->final_cost = r.final_cost; s->fixed_cost = r.fixed_cost;
-    s->total_time_in_seconds = r.total_time_in_seconds; s->device_time_in_seconds = r.device_time_in_seconds;
-    s->num_e_blocks = r.num_e_blocks; s->num_f_blocks = r.num_f_blocks; s->reduced_system_dim = r.reduced_system_dim;
-    s->linear_solver_used = r.linear_solver_used; s->reduced_system_nnz_blocks = r.reduced_system_nnz_blocks;
-    std::snprintf(s->message, sizeof(s->message), "%s", r.message.c_str());
-    for (int i = 0; i < s->num_iterations && i < max_its && its; ++i) {
-      const IterationSummary& a = r.iterations[i];
-      its[i] = bsnls_iteration{a.iteration, a.step_is_valid, a.step_is_successful, a.linear_solver_iterations, a.cost,
-                               a.cost_change, a.gradient_max_norm, a.gradient_norm, a.step_norm, a.relative_decrease,
-                               a.trust_region_radius};
-    }
+    const SolverOptions so = FromC(o);
+    g->last = max_time_s >= 0 ? g->graph.optimizeFor(max_time_s, so) : g->graph.optimize(so);
+    ToC(g->last, s, its, max_its);
     // keep g->flat in step with the graph the solve used
     g->flat = g->graph.lastProblem(); g->flat.Finalize();
     return 0;
   } catch (const std::invalid_argument& e) { g->error = e.what(); return -1; }
   catch (const std::exception& e) { g->error = e.what(); return -3; }
+}
+int bsfuse_optimize(bsfuse_graph* g, const bsnls_options* o, bsnls_summary* s, bsnls_iteration* its, int max_its) {
+  return bsfuse_optimize_for(g, -1.0, o, s, its, max_its);
+}
+// host wall-clock split of the last optimize: flatten | set_problem or set_values | solve | get_values + scatter | reused (0/1)
+void bsfuse_last_timing(bsfuse_graph* g, double out[5]) { TimingOut(g->graph, out); }
+
+// ---- sliding-window replay (smoother_replay.h) ----
+bsfuse_replay* bsfuse_replay_new(int total_keyframes, int window_keyframes, uint64_t seed) {
+  auto* h = new bsfuse_replay();
+  try { h->r.reset(new SmootherReplay(total_keyframes, window_keyframes, seed)); }
+  catch (const std::exception& e) { h->error = e.what(); }
+  return h;
+}
+void bsfuse_replay_free(bsfuse_replay* h) { delete h; }
+const char* bsfuse_replay_error(bsfuse_replay* h) { return h->error.c_str(); }
+int bsfuse_replay_done(bsfuse_replay* h) { return !h->r || h->r->Done(); }
+// steps 1-2 of a smoother cycle (transaction + pseudo-marginalisation); returns host seconds, < 0 on error
+double bsfuse_replay_advance(bsfuse_replay* h) {
+  try { return h->r->Advance(); } catch (const std::exception& e) { h->error = e.what(); return -1.0; }
+}
+const bsnls_problem* bsfuse_replay_flatten(bsfuse_replay* h) {
+  try { Flatten(h->r->graph(), &h->flat); return &h->flat.c; } catch (const std::exception& e) { h->error = e.what(); return nullptr; }
+}
+long long bsfuse_replay_observations(bsfuse_replay* h) { return h->r->num_observations(); }
+int bsfuse_replay_optimize(bsfuse_replay* h, const bsnls_options* o, bsnls_summary* s, bsnls_iteration* its, int max_its, double timing[5]) {
+  try {
+    const SolverSummary r = h->r->graph().optimize(FromC(o));
+    ToC(r, s, its, max_its);
+    if (timing) TimingOut(h->r->graph(), timing);
+    return 0;
+  } catch (const std::invalid_argument& e) { h->error = e.what(); return -1; }
+  catch (const std::exception& e) { h->error = e.what(); return -3; }
+}
+void bsfuse_replay_current_values(bsfuse_replay* h, double* out) {   // in the order of the last bsfuse_replay_flatten
+  for (size_t b = 0; b < h->flat.block_variable.size(); ++b)
+    std::memcpy(out + h->flat.block_offset[b], h->flat.block_variable[b]->data(), sizeof(double) * h->flat.block_size[b]);
 }
 int bsfuse_evaluate(bsfuse_graph* g, double* cost) {
   try { return g->graph.evaluate(cost, nullptr, nullptr) ? 0 : -3; }

@@ -1,7 +1,6 @@
 #include "flatten.h"
 
 #include <cstring>
-#include <map>
 
 namespace bsfuse {
 
@@ -51,13 +50,43 @@ void FlatProblem::ScatterValues(const double* values) const {
     std::memcpy(block_variable[b]->data(), values + block_offset[b], sizeof(double) * block_size[b]);
 }
 
+void FlatProblem::GatherValues() {
+  for (size_t b = 0; b < block_variable.size(); ++b)
+    std::memcpy(block_values.data() + block_offset[b], block_variable[b]->data(), sizeof(double) * block_size[b]);
+}
+
+namespace {
+// first sight of a constraint in this graph: type() string dispatch, variable objects, camera class
+void ResolveHint(const HashGraph& graph, const Constraint& c, FlatProblem& P) {
+  auto ti = TypeTable().find(c.type());
+  if (ti == TypeTable().end()) throw std::invalid_argument("constraint type not supported by the GPU path: " + c.type());
+  const TypeInfo& info = ti->second;
+  if (static_cast<int>(c.variables().size()) != info.nblocks) throw std::invalid_argument("unexpected variable count for " + c.type());
+  Constraint::FlatHint& hnt = c.flat_hint;
+  hnt.type = info.type; hnt.nblocks = info.nblocks; hnt.stride = info.stride; hnt.camera = -1;
+  for (int b = 0; b < info.nblocks; ++b) hnt.vars[b] = &graph.getVariable(c.variables()[b]);  // variables_.at(uuid), :515
+  if (info.type == BSNLS_FACTOR_REPROJECTION) {
+    const auto& pl = c.payload();
+    std::vector<double> cam(pl.begin() + 2, pl.begin() + 19);  // K(4), T(12), w
+    cam.push_back(c.loss() ? static_cast<double>(c.loss()->type) : static_cast<double>(BSNLS_LOSS_NONE));
+    cam.push_back(c.loss() ? c.loss()->a : 0.0); cam.push_back(0.0);
+    auto it = P.camera_index.find(cam);
+    if (it == P.camera_index.end()) {
+      it = P.camera_index.emplace(cam, static_cast<int32_t>(P.cameras.size() / BSNLS_CAMERA_STRIDE)).first;
+      P.cameras.insert(P.cameras.end(), cam.begin(), cam.end());
+    }
+    hnt.camera = it->second;
+  }
+  hnt.owner = &graph;
+}
+}  // namespace
+
 void Flatten(const HashGraph& graph, FlatProblem* out) {
   FlatProblem& P = *out;
-  P = FlatProblem();
   const auto& vars = graph.getVariables();
-  std::unordered_map<UUID, int32_t, UuidHash> index;
-  index.reserve(vars.size() * 2);
-  P.block_size.reserve(vars.size());
+  P.block_size.clear(); P.block_manifold.clear(); P.block_group.clear(); P.block_constant.clear(); P.block_values.clear();
+  P.block_offset.clear(); P.block_variable.clear(); P.block_uuid.clear();
+  P.block_size.reserve(vars.size()); P.block_values.reserve(vars.size() * 4);
   int64_t off = 0;
   // createProblem, first loop (hash_graph.cpp:478-504)
   for (const auto& kv : vars) {
@@ -65,12 +94,13 @@ void Flatten(const HashGraph& graph, FlatProblem* out) {
     for (size_t i = 0; i < v.size(); ++i)
       if (v.lowerBound(i) > std::numeric_limits<double>::lowest() || v.upperBound(i) < std::numeric_limits<double>::max())
         throw std::invalid_argument("bounded variables are not supported by the GPU path: " + v.type());
-    index.emplace(kv.first, static_cast<int32_t>(P.block_size.size()));
+    v.flat_index = static_cast<int32_t>(P.block_size.size());
     P.block_size.push_back(static_cast<int32_t>(v.size()));
     P.block_manifold.push_back(v.manifold() == Variable::kQuaternion ? BSNLS_MANIFOLD_QUATERNION : BSNLS_MANIFOLD_EUCLIDEAN);
     P.block_constant.push_back((v.holdConstant() || graph.isVariableOnHold(kv.first)) ? 1 : 0);
     // elimination groups: landmarks first (explicit two-group ordering)
-    const bool landmark = v.type() == "bs_variables::Point3DLandmark" || v.type() == "bs_variables::InverseDepthLandmark";
+    const std::string& ty = v.type();
+    const bool landmark = ty.size() > 14 && ty.compare(0, 14, "bs_variables::") == 0 && (ty == "bs_variables::Point3DLandmark" || ty == "bs_variables::InverseDepthLandmark");
     P.block_group.push_back(landmark ? 0 : 1);
     P.block_offset.push_back(off);
     P.block_variable.push_back(&v);
@@ -78,38 +108,29 @@ void Flatten(const HashGraph& graph, FlatProblem* out) {
     for (size_t i = 0; i < v.size(); ++i) P.block_values.push_back(v.data()[i]);
     off += static_cast<int64_t>(v.size());
   }
-  P.groups.assign(BSNLS_NUM_FACTOR_TYPES, FlatProblem::Group());
-  for (int t = 0; t < BSNLS_NUM_FACTOR_TYPES; ++t) P.groups[t].type = t;
-  std::map<std::vector<double>, int32_t> camera_index;
+  if (P.groups.size() != BSNLS_NUM_FACTOR_TYPES) P.groups.assign(BSNLS_NUM_FACTOR_TYPES, FlatProblem::Group());
+  for (int t = 0; t < BSNLS_NUM_FACTOR_TYPES; ++t) {
+    FlatProblem::Group& g = P.groups[t];
+    g.type = t; g.blocks.clear(); g.aux.clear(); g.loss_type.clear(); g.res_index.clear(); g.consts.clear(); g.loss_param.clear();
+  }
   int32_t res_index = 0;
   // createProblem, second loop (hash_graph.cpp:506-521)
   for (const auto& kv : graph.getConstraints()) {
     const Constraint& c = *kv.second;
-    auto ti = TypeTable().find(c.type());
-    if (ti == TypeTable().end()) throw std::invalid_argument("constraint type not supported by the GPU path: " + c.type());
-    const TypeInfo& info = ti->second;
-    FlatProblem::Group& g = P.groups[info.type];
-    if (static_cast<int>(c.variables().size()) != info.nblocks)
-      throw std::invalid_argument("unexpected variable count for " + c.type());
-    for (const UUID& u : c.variables()) g.blocks.push_back(index.at(u));  // variables_.at(uuid), :515
-    const int lt = c.loss() ? static_cast<int>(c.loss()->type) : BSNLS_LOSS_NONE;
-    const double la = c.loss() ? c.loss()->a : 0.0;
+    if (c.flat_hint.owner != &graph) ResolveHint(graph, c, P);
+    const Constraint::FlatHint& hnt = c.flat_hint;
+    FlatProblem::Group& g = P.groups[hnt.type];
+    for (int b = 0; b < hnt.nblocks; ++b) g.blocks.push_back(hnt.vars[b]->flat_index);
     const auto& pl = c.payload();
-    if (info.type == BSNLS_FACTOR_REPROJECTION) {
+    if (hnt.type == BSNLS_FACTOR_REPROJECTION) {
       g.consts.push_back(pl[0]); g.consts.push_back(pl[1]);
-      std::vector<double> cam(pl.begin() + 2, pl.begin() + 19);  // K(4), T(12), w
-      cam.push_back(static_cast<double>(lt)); cam.push_back(la); cam.push_back(0.0);
-      auto it = camera_index.find(cam);
-      if (it == camera_index.end()) {
-        it = camera_index.emplace(cam, static_cast<int32_t>(P.cameras.size() / BSNLS_CAMERA_STRIDE)).first;
-        P.cameras.insert(P.cameras.end(), cam.begin(), cam.end());
-      }
-      g.aux.push_back(it->second);
+      g.aux.push_back(hnt.camera);
     } else {
       const size_t n0 = g.consts.size();
-      g.consts.resize(n0 + info.stride, 0.0);
-      std::memcpy(g.consts.data() + n0, pl.data(), sizeof(double) * std::min<size_t>(pl.size(), info.stride));
-      g.loss_type.push_back(lt); g.loss_param.push_back(la);
+      g.consts.resize(n0 + hnt.stride, 0.0);
+      std::memcpy(g.consts.data() + n0, pl.data(), sizeof(double) * std::min<size_t>(pl.size(), hnt.stride));
+      g.loss_type.push_back(c.loss() ? static_cast<int>(c.loss()->type) : BSNLS_LOSS_NONE);
+      g.loss_param.push_back(c.loss() ? c.loss()->a : 0.0);
     }
     g.res_index.push_back(res_index++);
   }

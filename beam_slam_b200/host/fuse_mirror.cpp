@@ -139,7 +139,7 @@ std::string SolverSummary::FullReport() const {
 }
 
 // ---- HashGraph containers: semantics of fuse_graphs/src/hash_graph.cpp:100-301 ----
-void HashGraph::clear() { constraints_.clear(); variables_.clear(); variables_on_hold_.clear(); constraints_by_variable_uuid_.clear(); }
+void HashGraph::clear() { constraints_.clear(); variables_.clear(); variables_on_hold_.clear(); constraints_by_variable_uuid_.clear(); ++structure_version_; }
 
 bool HashGraph::addConstraint(Constraint::SharedPtr c) {
   if (!c) return false;
@@ -150,6 +150,7 @@ bool HashGraph::addConstraint(Constraint::SharedPtr c) {
                              ") that uses an unknown variable (" + uuid::to_string(v) + ").");
   for (const auto& v : c->variables()) constraints_by_variable_uuid_[v].insert(c->uuid());
   constraints_.emplace(c->uuid(), std::move(c));
+  ++structure_version_;
   return true;
 }
 bool HashGraph::removeConstraint(const UUID& u) {
@@ -157,6 +158,7 @@ bool HashGraph::removeConstraint(const UUID& u) {
   if (it == constraints_.end()) return false;
   for (const auto& v : it->second->variables()) constraints_by_variable_uuid_[v].erase(u);
   constraints_.erase(it);
+  ++structure_version_;
   return true;
 }
 const Constraint& HashGraph::getConstraint(const UUID& u) const {
@@ -174,8 +176,17 @@ std::vector<UUID> HashGraph::getConnectedConstraints(const UUID& variable) const
 bool HashGraph::addVariable(Variable::SharedPtr v) {
   if (!v) return false;
   auto it = variables_.find(v->uuid());
-  if (it != variables_.end()) { it->second = std::move(v); return true; }  // update in place (hash_graph.cpp:229-238)
+  if (it != variables_.end()) {
+    // update in place (hash_graph.cpp:229-238). The stored object keeps its identity (constraints of this graph cache
+    // pointers to it); only a change of shape or hold flag is a structural change.
+    Variable& old = *it->second;
+    if (old.size() != v->size() || old.manifold() != v->manifold() || old.holdConstant() != v->holdConstant() || old.type() != v->type()) ++structure_version_;
+    const int32_t keep = old.flat_index;
+    old = *v; old.flat_index = keep;
+    return true;
+  }
   variables_.emplace(v->uuid(), std::move(v));
+  ++structure_version_;
   return true;
 }
 bool HashGraph::removeVariable(const UUID& u) {
@@ -187,6 +198,7 @@ bool HashGraph::removeVariable(const UUID& u) {
   variables_.erase(it);
   if (c != constraints_by_variable_uuid_.end()) constraints_by_variable_uuid_.erase(c);
   variables_on_hold_.erase(u);
+  ++structure_version_;
   return true;
 }
 Variable& HashGraph::getVariable(const UUID& u) const {
@@ -196,6 +208,7 @@ Variable& HashGraph::getVariable(const UUID& u) const {
 }
 void HashGraph::holdVariable(const UUID& u, bool hold) {
   if (hold) variables_on_hold_.insert(u); else variables_on_hold_.erase(u);
+  ++structure_version_;
 }
 
 }  // namespace bsfuse

@@ -60,6 +60,9 @@ class Variable {
   SharedPtr clone() const { return std::make_shared<Variable>(*this); }
   Variable(UUID u, std::string type, std::vector<double> d, Manifold m, bool hold = false)
       : uuid_(u), type_(std::move(type)), data_(std::move(d)), manifold_(m), hold_constant_(hold) {}
+  // position of this variable in the last flattened problem of the graph that holds it (GpuHashGraph keeps it; inside
+  // fuse the subclass keeps the same number in a side table keyed by the variable pointer)
+  mutable int32_t flat_index = -1;
  private:
   UUID uuid_; std::string type_; std::vector<double> data_; Manifold manifold_; bool hold_constant_;
 };
@@ -105,7 +108,12 @@ class Constraint {
   const std::string& source() const { return source_; }
   const std::vector<UUID>& variables() const { return variables_; }
   Loss::SharedPtr loss() const { return loss_; }
-  void loss(Loss::SharedPtr l) { loss_ = std::move(l); }
+  void loss(Loss::SharedPtr l) { loss_ = std::move(l); flat_hint.owner = nullptr; }
+  // What the flattener resolved for this constraint the first time it saw it in a graph (type dispatch, variable
+  // objects, camera class): the SoA mirror kept up to date at addConstraint time instead of re-deriving it on every
+  // optimize (hash_graph.cpp:506-521 re-news every cost function per solve).
+  struct FlatHint { const void* owner = nullptr; int type = -1, nblocks = 0, stride = 0, camera = -1; Variable* vars[10] = {}; };
+  mutable FlatHint flat_hint;
   const std::vector<double>& payload() const { return payload_; }
   Constraint(UUID u, std::string type, std::string source, std::vector<UUID> vars, std::vector<double> payload)
       : uuid_(u), type_(std::move(type)), source_(std::move(source)), variables_(std::move(vars)),
@@ -207,6 +215,8 @@ class HashGraph {
   const Variables& getVariables() const { return variables_; }
   void holdVariable(const UUID& u, bool hold_constant = true);
   bool isVariableOnHold(const UUID& u) const { return variables_on_hold_.count(u) > 0; }
+  // bumped by every call that changes which blocks / factors exist or which blocks are held; values do not count
+  uint64_t structureVersion() const { return structure_version_; }
   // the three virtuals of fuse_core::Graph on the hot path (graph.h; hash_graph.h:317,331-333,355-356)
   virtual SolverSummary optimize(const SolverOptions& options = SolverOptions()) = 0;
   virtual SolverSummary optimizeFor(double max_optimization_time_s, const SolverOptions& options = SolverOptions()) = 0;
@@ -216,6 +226,7 @@ class HashGraph {
   Variables variables_;
   std::unordered_set<UUID, UuidHash> variables_on_hold_;
   std::unordered_map<UUID, std::unordered_set<UUID, UuidHash>, UuidHash> constraints_by_variable_uuid_;
+  uint64_t structure_version_ = 1;
 };
 
 }  // namespace bsfuse

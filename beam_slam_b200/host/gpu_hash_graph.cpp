@@ -23,6 +23,8 @@ GpuHashGraph::GpuHashGraph() = default;
 GpuHashGraph::~GpuHashGraph() { if (handle_) bsnls_destroy(handle_); }
 
 void GpuHashGraph::EnsureHandle(const SolverOptions& options) const {
+  if (handle_ && options.linear_solver != last_options_.linear_solver) flat_version_ = 0;   // reduced-system storage changes
+  last_options_ = options;
   bsnls_options c; ToCOptions(options, &c);
   if (!handle_) {
     if (bsnls_create(&c, &handle_) != BSNLS_OK) {
@@ -34,21 +36,53 @@ void GpuHashGraph::EnsureHandle(const SolverOptions& options) const {
   }
 }
 
+int GpuHashGraph::SyncProblem() const {
+  using clk = std::chrono::steady_clock;
+  const auto t0 = clk::now();
+  if (flat_version_ == structureVersion() && flat_version_ != 0) {
+    // same blocks, same factors (constraints are immutable once added, as in fuse): only Variable::data() moved
+    flat_.GatherValues();
+    const auto t1 = clk::now();
+    const int rc = bsnls_set_values(handle_, flat_.block_values.data());
+    timing_.flatten = std::chrono::duration<double>(t1 - t0).count();
+    timing_.upload = std::chrono::duration<double>(clk::now() - t1).count();
+    timing_.structure_reused = true;
+    return rc;
+  }
+  Flatten(*this, &flat_);  // createProblem
+  const auto t1 = clk::now();
+  timing_.flatten = std::chrono::duration<double>(t1 - t0).count();
+  timing_.structure_reused = false;
+  if (flat_.cgroups.empty() || flat_.block_size.empty()) { flat_version_ = 0; timing_.upload = 0; return BSNLS_OK; }
+  const int rc = bsnls_set_problem(handle_, &flat_.c);
+  flat_version_ = rc == BSNLS_OK ? structureVersion() : 0;
+  timing_.upload = std::chrono::duration<double>(clk::now() - t1).count();
+  return rc;
+}
+
 SolverSummary GpuHashGraph::optimize(const SolverOptions& options) {
   const auto t0 = std::chrono::steady_clock::now();
   std::string err;
   if (!options.IsValid(&err)) throw std::invalid_argument("Invalid solver options: " + err);
-  Flatten(*this, &flat_);  // createProblem
   SolverSummary s;
-  if (flat_.cgroups.empty() || flat_.block_size.empty()) {  // empty problem: Ceres converges at once
+  if (getConstraints().empty() || getVariables().empty()) {  // empty problem: Ceres converges at once
     s.termination_type = SolverSummary::CONVERGENCE; s.message = "Function tolerance reached. No non-constant parameter blocks found.";
     return s;
   }
   EnsureHandle(options);
   bsnls_summary cs{};
   std::vector<bsnls_iteration> its(static_cast<size_t>(options.max_num_iterations) + 2);
-  int rc = bsnls_set_problem(handle_, &flat_.c);
+  int rc = SyncProblem();
+  const auto t1 = std::chrono::steady_clock::now();
+  if (rc == BSNLS_OK && options.max_solver_time_in_seconds < 1e8) {
+    // optimizeFor: what createProblem's counterpart took is charged against the budget (hash_graph.cpp:433-439)
+    bsnls_options c; ToCOptions(options, &c);
+    c.max_solver_time_in_seconds = std::max(0.0, options.max_solver_time_in_seconds - std::chrono::duration<double>(t1 - t0).count());
+    rc = bsnls_set_options(handle_, &c);
+  }
   if (rc == BSNLS_OK) rc = bsnls_solve(handle_, &cs, its.data(), static_cast<int32_t>(its.size()));
+  const auto t2 = std::chrono::steady_clock::now();
+  timing_.solve = std::chrono::duration<double>(t2 - t1).count(); timing_.download = 0;
   if (rc != BSNLS_OK) {
     s.termination_type = SolverSummary::FAILURE;
     s.message = std::string("bsnls: ") + bsnls_last_error(handle_);
@@ -76,24 +110,24 @@ SolverSummary GpuHashGraph::optimize(const SolverOptions& options) {
       return s;
     }
     flat_.ScatterValues(flat_.block_values.data());  // Ceres' in-place update of Variable::data()
+    timing_.download = std::chrono::duration<double>(std::chrono::steady_clock::now() - t2).count();
   }
   s.total_time_in_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   return s;
 }
 
 SolverSummary GpuHashGraph::optimizeFor(double max_time_s, const SolverOptions& options) {
-  // The reference subtracts the createProblem time from the budget (hash_graph.cpp:433-439); flattening happens
-  // inside optimize(), so the whole budget is handed down and the device loop checks its own clock.
+  // The reference subtracts the createProblem time from the budget (hash_graph.cpp:433-439): optimize() does the same
+  // with the time flattening and bsnls_set_problem took before it hands the rest to the device loop.
   SolverOptions o = options;
   o.max_solver_time_in_seconds = std::max(0.0, max_time_s);
   return optimize(o);
 }
 
 bool GpuHashGraph::evaluate(double* cost, std::vector<double>* residuals, std::vector<double>* gradient) const {
-  Flatten(*this, &flat_);
-  if (flat_.cgroups.empty()) { if (cost) *cost = 0.0; if (residuals) residuals->clear(); if (gradient) gradient->clear(); return true; }
-  EnsureHandle(SolverOptions());
-  if (bsnls_set_problem(handle_, &flat_.c) != BSNLS_OK) return false;
+  if (getConstraints().empty() || getVariables().empty()) { if (cost) *cost = 0.0; if (residuals) residuals->clear(); if (gradient) gradient->clear(); return true; }
+  EnsureHandle(last_options_);
+  if (SyncProblem() != BSNLS_OK) return false;
   int64_t nr = 0, ng = 0;
   if (bsnls_evaluate(handle_, cost, nullptr, &nr, nullptr, &ng) != BSNLS_OK) return false;
   if (residuals) residuals->assign(nr, 0.0);

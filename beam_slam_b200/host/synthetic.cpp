@@ -108,7 +108,12 @@ SolverOptions SyntheticSolverOptions(int config) {
 }
 
 SyntheticInfo BuildSynthetic(int config, double scale, uint64_t seed, HashGraph* graph, std::vector<std::pair<UUID, std::vector<double>>>* truth) {
-  const ConfigSpec spec = Spec(config);
+  return BuildSyntheticTrajectory(config, scale, seed, 0, graph, truth);
+}
+double SyntheticKeyframeTime(int k) { return 1.0 + 0.7 * k; }
+SyntheticInfo BuildSyntheticTrajectory(int config, double scale, uint64_t seed, int keyframes, HashGraph* graph, std::vector<std::pair<UUID, std::vector<double>>>* truth) {
+  ConfigSpec spec = Spec(config);
+  if (keyframes > 0) { spec.lm = static_cast<int>(std::lround(spec.lm * (double)keyframes / spec.kf)); spec.kf = keyframes; }
   SyntheticInfo info{};
   Rng rng(seed ? seed : 1000 + config);
   SeedConstraintUuids((seed ? seed : 1000 + config) * 7919 + 13);
@@ -133,7 +138,7 @@ SyntheticInfo BuildSynthetic(int config, double scale, uint64_t seed, HashGraph*
   };
   for (int k = 0; k < nkf; ++k) {
     Kf& f = kfs[k];
-    f.t = 1.0 + 0.7 * k;
+    f.t = SyntheticKeyframeTime(k);
     Attitude(f.t, f.R); RotToQuat(f.R, f.q); Position(f.t, f.p); Velocity(f.t, f.v);
     const Time stamp = Time::fromSec(f.t);
     f.vq = variables::Orientation3DStamped(stamp); f.vp = variables::Position3DStamped(stamp);

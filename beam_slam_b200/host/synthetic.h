@@ -14,6 +14,12 @@ struct SyntheticInfo {
 // for tests; seed 0 = 1000 + config. truth (optional) receives ground-truth values per variable UUID.
 SyntheticInfo BuildSynthetic(int config, double scale, uint64_t seed, HashGraph* graph,
                              std::vector<std::pair<UUID, std::vector<double>>>* truth = nullptr);
+// Same graph family over a longer trajectory: `keyframes` (> 0) replaces the config's keyframe count and scales the
+// landmark count with it (source of the sliding-window replay, smoother_replay.h). Keyframe k is stamped
+// SyntheticKeyframeTime(k).
+SyntheticInfo BuildSyntheticTrajectory(int config, double scale, uint64_t seed, int keyframes, HashGraph* graph,
+                                       std::vector<std::pair<UUID, std::vector<double>>>* truth = nullptr);
+double SyntheticKeyframeTime(int k);
 // Solver options the survey names per config (vio.yaml:13-17 for 1-2, Ceres defaults for 3-5).
 SolverOptions SyntheticSolverOptions(int config);
 
