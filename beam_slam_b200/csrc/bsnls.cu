@@ -148,7 +148,8 @@ struct bsnls_handle {
       d_gf_roff, d_pair_a, d_pair_b, d_pair_ptr, d_item_i, d_item_j, d_fg_ptr, d_fg_fac, d_fg_lb, d_gd_row, d_gd_col,
       d_gd_ptr, d_gd_fac, d_gd_bi, d_gd_bj, d_is_pose, d_bsr_rowptr, d_bsr_col, d_diag_slot, d_pair_slot, d_gd_slot,
       d_pcg_x, d_pcg_r, d_pcg_z, d_pcg_p, d_pcg_Ap, d_pcg_Minv, d_pcg_part;
-  DevMem d_lmz, d_gradL, d_colsqL, d_gradS, d_colsqS;
+  DevMem d_lmz, d_gradL, d_colsqL, d_gradS, d_colsqS, d_zero;
+  cudaEvent_t ev_stage = nullptr; bool stage_busy = false;
   DevMem d_x, d_xc, d_x0, d_Jrec, d_Vrec, d_minv, d_grad, d_colsq, d_scale, d_y, d_yf, d_rhs, d_S, d_poseH, d_gfJ,
       d_gfR, d_cost_part, d_cand_part, d_model_part, d_step_part, d_candsq_part, d_gsq_part, d_gmax_part, d_xsq_part,
       d_red, d_state, d_recs;
@@ -538,7 +539,7 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
   if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaEventCreate(&h->ev0)) != cudaSuccess || (e = cudaEventCreate(&h->ev1)) != cudaSuccess ||
       (e = cudaEventCreate(&h->ev2)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking)) != cudaSuccess ||
-      (e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)) != cudaSuccess || (e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming)) != cudaSuccess) {
+      (e = cudaEventCreateWithFlags(&h->ev_stage, cudaEventDisableTiming)) != cudaSuccess || (e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)) != cudaSuccess || (e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming)) != cudaSuccess) {
     g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
   }
   if ((e = cudaFuncSetAttribute(chunk_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, syrk_smem_bytes(kChunkSlots))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
@@ -559,6 +560,7 @@ void bsnls_destroy(bsnls_handle* h) {
   h->arena.Release();
   if (h->stream) cudaStreamDestroy(h->stream);
   if (h->side) cudaStreamDestroy(h->side);
+  if (h->ev_stage) cudaEventDestroy(h->ev_stage);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
   if (h->ev0) cudaEventDestroy(h->ev0);
@@ -576,8 +578,15 @@ int bsnls_set_options(bsnls_handle* h, const bsnls_options* o) {
   bsnls_options n = *o; n.device = dev;
   const bool solver_changed = n.linear_solver != h->opt.linear_solver;
   // kernel arguments (options) are baked into the captured graphs: re-capture only when something changed
-  { bsnls_options a = n, b = h->opt; a.max_solver_time_in_seconds = b.max_solver_time_in_seconds = 0.0;   // the budget is a host-side check
-    if (std::memcmp(&a, &b, sizeof(a)) != 0) h->graphs_valid = false; }
+  { const bsnls_options &a = n, &b = h->opt;   // field by field (the struct has padding); the time budget is a host-side check
+    const bool same = a.max_num_iterations == b.max_num_iterations && a.function_tolerance == b.function_tolerance &&
+        a.gradient_tolerance == b.gradient_tolerance && a.parameter_tolerance == b.parameter_tolerance &&
+        a.initial_trust_region_radius == b.initial_trust_region_radius && a.max_trust_region_radius == b.max_trust_region_radius &&
+        a.min_trust_region_radius == b.min_trust_region_radius && a.min_relative_decrease == b.min_relative_decrease &&
+        a.min_lm_diagonal == b.min_lm_diagonal && a.max_lm_diagonal == b.max_lm_diagonal &&
+        a.max_num_consecutive_invalid_steps == b.max_num_consecutive_invalid_steps && a.jacobi_scaling == b.jacobi_scaling &&
+        a.linear_solver == b.linear_solver && a.pcg_max_iterations == b.pcg_max_iterations && a.pcg_tolerance == b.pcg_tolerance;
+    if (!same) h->graphs_valid = false; }
   h->opt = n;
   if (solver_changed && h->has_problem) h->has_problem = false;   // the reduced-system storage depends on the linear solver: set_problem again
   return BSNLS_OK;
@@ -587,6 +596,14 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   if (!h || !pr) return BSNLS_ERR_INVALID;
   CK(cudaSetDevice(h->device));
   h->has_problem = false; h->jac_valid = false;
+  const bool dbg = std::getenv("BSNLS_DEBUG") != nullptr;
+  auto tphase = std::chrono::steady_clock::now();
+  auto phase = [&](const char* name) {   // BSNLS_DEBUG: host time of each analysis phase
+    if (!dbg) return;
+    const auto now = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[bsnls] set_problem %-28s %8.3f ms\n", name, 1e3 * std::chrono::duration<double>(now - tphase).count());
+    tphase = now;
+  };
   const int nb = pr->num_blocks;
   if (nb <= 0) return h->fail(BSNLS_ERR_INVALID, "problem has no parameter blocks");
   // ---- blocks ----
@@ -680,6 +697,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   std::vector<int> g_pose(nobs);   // pose of every observation of the graph, landmark-sorted (the pair pattern is global)
   for (int k = 0; k < nobs; ++k) g_pose[k] = obs_pose[order[k]];
 
+  phase("blocks + observation sort");
   // ---- pose-pair blocks of the reduced system: pattern of the WHOLE graph (identical on every rank) ----
   // Pair (a <= b) exists iff some landmark is seen by both poses. Built per pose with a stamp array over the poses of
   // the landmarks it observes (no hashing); pair id = position in (a, b) order; lookups go through pair_row / pair_b.
@@ -710,6 +728,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     const int* p = std::lower_bound(r0, r1, b);
     return (p != r1 && *p == b) ? (int)(p - h->pair_b.data()) : -1;
   };
+  phase("pair pattern");
   // ---- pose ranking for locality: breadth-first order of the co-visibility graph from a peripheral pose ----
   std::vector<int> pose_rank(h->np, -1);
   {
@@ -821,6 +840,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     for (int k = 0; k < h->nf; ++k) { rank[orderv[k]] = k; h->f_api[k] = orderv[k]; }
     for (int b = 0; b < nb; ++b) if (fpos[b] >= 0) fpos[b] = rank[fpos[b]];
   }
+  phase("pose / f-block ordering");
   h->blk_tan.assign(nb, -1);
   for (int b = 0; b < nb; ++b) if (fpos[b] >= 0) h->blk_tan[b] = ne_dim + 3 * fpos[b];
   for (int e = 0; e < h->ne; ++e) h->blk_tan[h->eblocks[lo + lperm[e]]] = 3 * e;
@@ -873,6 +893,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   else h->G = avg_track <= 5.0 ? 4 : avg_track <= 12.0 ? 8 : avg_track <= 24.0 ? 16 : 32;
   if (const char* ev = std::getenv("BSNLS_LM_LANES")) { const int g = std::atoi(ev); if (g == 4 || g == 8 || g == 16 || g == 32) h->G = g; }   // tuning knob: lanes per landmark
 
+  phase("observation tables");
   // ---- chunks: consecutive landmarks whose poses fit kChunkSlots slots are accumulated on chip by one CTA ----
   std::vector<unsigned short> obs_slot(nobs_local, 0xFFFF);
   std::vector<int> chunk_begin, chunk_end, chunk_nslots, chunk_pose;      // landmark range [begin, end) of each chunk
@@ -926,6 +947,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     std::fprintf(stderr, "[bsnls] rank %d: %d landmarks, %d obs, %d poses, %d pairs, %d chunks (avg %.1f slots, %.1f landmarks), %lld wide landmarks, partial buffer %.1f MB\n",
                  h->rank, h->ne, nobs_local, h->np, h->npairs, h->nchunks, h->nchunks ? (double)slots / h->nchunks : 0.0, h->nchunks ? (double)h->ne / h->nchunks : 0.0, nwide, tile_size * 8e-6);
   }
+  phase("chunks");
   // ---- per pair: partial blocks produced by the chunks, and items of the wide landmarks ----
   std::vector<int> pair_ptr(h->npairs + 1, 0), item_i, item_j, pp_ptr(h->npairs + 1, 0);
   std::vector<long long> pp_toff; std::vector<int> pp_info;
@@ -977,6 +999,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     }
   }
 
+  phase("pair partial lists");
   // ---- generic factors (type-major; factors whose blocks are all constant go last: fixed cost) ----
   std::vector<int> gf_type, gf_nblk, gf_nres, gf_blocks, gf_loss_type, gf_joff, gf_roff;
   std::vector<long long> gf_coff; std::vector<double> gf_consts, gf_loss_a;
@@ -1104,10 +1127,13 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     h->num_res_rows = row;
   }
 
+  phase("generic factors + S pattern");
   // ---- upload: one arena, one staged copy (see Arena) ----
   cudaStream_t s = h->stream;
   struct RecGuard { ~RecGuard() { g_rec = nullptr; } } rec_guard;
+  if (h->stage_busy) { CK(cudaEventSynchronize(h->ev_stage)); h->stage_busy = false; }   // the previous problem's staged copy
   h->arena.Begin(); g_rec = &h->arena;
+  CK(h->arena.StageReserve((size_t)nobs_local * 72 + (size_t)nb * 48 + (size_t)off * 9 + (size_t)h->npairs * 64 + (size_t(1) << 20)));   // one pinned allocation instead of a doubling series
   CK(upload(h->d_blk_off, h->blk_off, s)); CK(upload(h->d_blk_size, h->blk_size, s)); CK(upload(h->d_blk_tan, h->blk_tan, s));
   CK(upload(h->d_blk_manifold, h->blk_manifold, s)); CK(upload(h->d_active, h->active_blocks, s));
   CK(upload(h->d_pose_q_off, pose_q_off, s)); CK(upload(h->d_pose_t_off, pose_t_off, s)); CK(upload(h->d_pose_q_tan, pose_q_tan, s));
@@ -1144,6 +1170,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     for (int b = 0; b < nb; ++b) if (epos[b] >= 0) { const unsigned char mine = (epos[b] >= lo && epos[b] < hi) ? 1 : 0; for (int k = 0; k < h->blk_size[b]; ++k) owned[h->blk_off[b] + k] = mine; }
     CK(upload(h->d_owned, owned, s));
   }
+  phase("staging of uploads");
   // work buffers
   const int ntan = ne_dim + nf_dim;
   // ---- tile-sparse Cholesky: symbolic factorisation at tile granularity (structure only; fixed per problem) ----
@@ -1231,13 +1258,21 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       }
     }
   }
+  phase("tile symbolic factorisation");
   h->nb_obs = h->nobs ? BlocksFor(h->nobs, 256) : 0; h->nb_lm = h->ne ? BlocksFor(h->ne * h->G, 256) : 0; h->nb_act = BlocksFor((int)h->active_blocks.size(), 256);
-  CK(h->d_x.alloc(sizeof(double) * off)); CK(h->d_xc.alloc(sizeof(double) * off)); CK(h->d_x0.alloc(sizeof(double) * off));
+  { // parameter values travel with the staged structure copy
+    cudaError_t e = g_rec->StageReserve(g_rec->up_used + Arena::Align(sizeof(double) * off)); if (e != cudaSuccess) return h->fail(BSNLS_ERR_CUDA, "staging: %s", cudaGetErrorString(e));
+    DevMem& m = h->d_x; if (m.p && !m.view) cudaFree(m.p);
+    m.p = nullptr; m.view = true; m.in_work = false; m.bytes = sizeof(double) * off; m.off = g_rec->up_used;
+    std::memcpy(g_rec->stage + m.off, pr->block_values, sizeof(double) * off);
+    g_rec->up_used += Arena::Align(sizeof(double) * off); g_rec->members.push_back(&m);
+  }
+  CK(h->d_xc.alloc(sizeof(double) * off)); CK(h->d_x0.alloc(sizeof(double) * off));
   CK(h->d_Jrec.alloc(sizeof(double) * kJRec * (size_t)h->nobs)); CK(h->d_Vrec.alloc(sizeof(double) * kVRec * (size_t)h->nobs));
   CK(h->d_minv.alloc(sizeof(double) * 6 * (size_t)h->ne)); CK(h->d_lmz.alloc(sizeof(double) * 3 * (size_t)h->ne)); CK(h->d_grad.alloc(sizeof(double) * ntan)); CK(h->d_colsq.alloc(sizeof(double) * ntan));
-  CK(h->d_gradL.alloc(sizeof(double) * nf_dim)); CK(h->d_colsqL.alloc(sizeof(double) * nf_dim));
+  CK(h->d_zero.alloc(sizeof(double) * (2 * (size_t)nf_dim + ntan)));   // gradL | colsqL | y: start at zero, cleared by one memset
   if (h->world > 1) { CK(h->d_gradS.alloc(sizeof(double) * nf_dim)); CK(h->d_colsqS.alloc(sizeof(double) * nf_dim)); }
-  CK(h->d_scale.alloc(sizeof(double) * ntan)); CK(h->d_y.alloc(sizeof(double) * ntan)); CK(h->d_yf.alloc(sizeof(double) * nf_dim));
+  CK(h->d_scale.alloc(sizeof(double) * ntan)); CK(h->d_yf.alloc(sizeof(double) * nf_dim));
   CK(h->d_rhs.alloc(sizeof(double) * nf_dim)); CK(h->d_S.alloc(sizeof(double) * (h->sparse ? (size_t)h->nnzb * 9 : (size_t)nf_dim * nf_dim)));
   if (h->tiled) {
     const int nT = (h->nf + kTileBlocks - 1) / kTileBlocks;
@@ -1272,10 +1307,14 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(h->d_step_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_candsq_part.alloc(sizeof(double) * h->nb_act));
   CK(h->d_gsq_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_gmax_part.alloc(sizeof(double) * h->nb_act)); CK(h->d_xsq_part.alloc(sizeof(double) * h->nb_act));
   CK(h->d_red.alloc(sizeof(double) * 32)); CK(h->d_state.alloc(sizeof(LMState)));
+  phase("work buffers + tile tables");
   CK(h->arena.Commit(s)); g_rec = nullptr;   // pointers are valid from here on
-  CK(cudaMemsetAsync(h->d_gradL.p, 0, sizeof(double) * nf_dim, s)); CK(cudaMemsetAsync(h->d_colsqL.p, 0, sizeof(double) * nf_dim, s));  // non-pose entries stay 0
-  CK(cudaMemcpyAsync(h->d_x.p, pr->block_values, sizeof(double) * off, cudaMemcpyHostToDevice, s));
-  CK(cudaMemsetAsync(h->d_y.p, 0, sizeof(double) * ntan, s));
+  CK(cudaEventRecord(h->ev_stage, s)); h->stage_busy = true;
+  // views into the zeroed block (non-pose entries of gradL / colsqL stay 0)
+  h->d_gradL.p = h->d_zero.p; h->d_gradL.view = true; h->d_gradL.bytes = sizeof(double) * nf_dim;
+  h->d_colsqL.p = h->d_zero.as<double>() + nf_dim; h->d_colsqL.view = true; h->d_colsqL.bytes = sizeof(double) * nf_dim;
+  h->d_y.p = h->d_zero.as<double>() + 2 * (size_t)nf_dim; h->d_y.view = true; h->d_y.bytes = sizeof(double) * ntan;
+  CK(cudaMemsetAsync(h->d_zero.p, 0, sizeof(double) * (2 * (size_t)nf_dim + ntan), s));
   if (h->tiled) {
     h->TC.bw_ptr = h->d_tc_bw_ptr.as<int>();
     h->TC.bw_col = h->d_tc_bw_col.as<int>();
@@ -1326,7 +1365,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   P.gd_fac = h->d_gd_fac.as<int>(); P.gd_bi = h->d_gd_bi.as<int>(); P.gd_bj = h->d_gd_bj.as<int>();
   P.sparse = h->sparse ? 1 : 0; P.nnzb = h->nnzb; P.bsr_rowptr = h->d_bsr_rowptr.as<int>(); P.bsr_col = h->d_bsr_col.as<int>();
   P.diag_slot = h->d_diag_slot.as<int>(); P.pair_slot = h->d_pair_slot.as<int>(); P.gd_slot = h->d_gd_slot.as<int>();
-  CK(cudaStreamSynchronize(s));  // host vectors above go out of scope
+  phase("arena commit + copy");   // asynchronous: the next set_problem waits on ev_stage before it reuses the staging buffer
   h->has_problem = true; h->graphs_valid = false; h->solves_on_structure = 0;
   return BSNLS_OK;
 }

@@ -10,7 +10,7 @@ using namespace bsfuse;
 
 struct bsfuse_graph {
   GpuHashGraph graph;
-  FlatProblem flat;
+  const FlatProblem& flat() const { return graph.lastProblem(); }   // the graph's own SoA view (bsfuse_flatten refreshes it)
   std::vector<std::pair<UUID, std::vector<double>>> truth;
   SolverSummary last;
   std::string error;
@@ -36,27 +36,27 @@ void bsfuse_synthetic_options(int config, bsnls_options* out) { ToCOptions(Synth
 
 // createProblem-order flattening; the returned struct and its arrays stay valid until the next flatten/free.
 const bsnls_problem* bsfuse_flatten(bsfuse_graph* g) {
-  try { Flatten(g->graph, &g->flat); return &g->flat.c; }
+  try { return &g->graph.flattened().c; }
   catch (const std::exception& e) { g->error = e.what(); return nullptr; }
 }
-long long bsfuse_num_values(bsfuse_graph* g) { return static_cast<long long>(g->flat.block_values.size()); }
-void bsfuse_block_uuid(bsfuse_graph* g, int block, unsigned char out[16]) { std::memcpy(out, g->flat.block_uuid[block].data.data(), 16); }
+long long bsfuse_num_values(bsfuse_graph* g) { return static_cast<long long>(g->flat().block_values.size()); }
+void bsfuse_block_uuid(bsfuse_graph* g, int block, unsigned char out[16]) { std::memcpy(out, g->flat().block_uuid[block].data.data(), 16); }
 // ground truth in the flattened block order (NaN where unknown)
 void bsfuse_truth_values(bsfuse_graph* g, double* out) {
   std::unordered_map<UUID, const std::vector<double>*, UuidHash> m;
   for (const auto& kv : g->truth) m[kv.first] = &kv.second;
-  for (size_t b = 0; b < g->flat.block_uuid.size(); ++b) {
-    auto it = m.find(g->flat.block_uuid[b]);
-    for (int k = 0; k < g->flat.block_size[b]; ++k)
-      out[g->flat.block_offset[b] + k] = it == m.end() ? std::nan("") : (*it->second)[k];
+  for (size_t b = 0; b < g->flat().block_uuid.size(); ++b) {
+    auto it = m.find(g->flat().block_uuid[b]);
+    for (int k = 0; k < g->flat().block_size[b]; ++k)
+      out[g->flat().block_offset[b] + k] = it == m.end() ? std::nan("") : (*it->second)[k];
   }
 }
 // current Variable::data() in the flattened block order
 void bsfuse_current_values(bsfuse_graph* g, double* out) {
-  for (size_t b = 0; b < g->flat.block_variable.size(); ++b)
-    std::memcpy(out + g->flat.block_offset[b], g->flat.block_variable[b]->data(), sizeof(double) * g->flat.block_size[b]);
+  for (size_t b = 0; b < g->flat().block_variable.size(); ++b)
+    std::memcpy(out + g->flat().block_offset[b], g->flat().block_variable[b]->data(), sizeof(double) * g->flat().block_size[b]);
 }
-void bsfuse_set_values(bsfuse_graph* g, const double* values) { g->flat.ScatterValues(values); }
+void bsfuse_set_values(bsfuse_graph* g, const double* values) { g->flat().ScatterValues(values); }
 
 }  // extern "C"
 
@@ -94,7 +94,7 @@ void TimingOut(const GpuHashGraph& g, double out[5]) {
 }
 }  // namespace
 
-struct bsfuse_replay { std::unique_ptr<SmootherReplay> r; FlatProblem flat; std::string error; };
+struct bsfuse_replay { std::unique_ptr<SmootherReplay> r; std::string error; };
 
 extern "C" {
 
@@ -104,8 +104,6 @@ int bsfuse_optimize_for(bsfuse_graph* g, double max_time_s, const bsnls_options*
     const SolverOptions so = FromC(o);
     g->last = max_time_s >= 0 ? g->graph.optimizeFor(max_time_s, so) : g->graph.optimize(so);
     ToC(g->last, s, its, max_its);
-    // keep g->flat in step with the graph the solve used
-    g->flat = g->graph.lastProblem(); g->flat.Finalize();
     return 0;
   } catch (const std::invalid_argument& e) { g->error = e.what(); return -1; }
   catch (const std::exception& e) { g->error = e.what(); return -3; }
@@ -131,7 +129,7 @@ double bsfuse_replay_advance(bsfuse_replay* h) {
   try { return h->r->Advance(); } catch (const std::exception& e) { h->error = e.what(); return -1.0; }
 }
 const bsnls_problem* bsfuse_replay_flatten(bsfuse_replay* h) {
-  try { Flatten(h->r->graph(), &h->flat); return &h->flat.c; } catch (const std::exception& e) { h->error = e.what(); return nullptr; }
+  try { return &h->r->graph().flattened().c; } catch (const std::exception& e) { h->error = e.what(); return nullptr; }
 }
 long long bsfuse_replay_observations(bsfuse_replay* h) { return h->r->num_observations(); }
 int bsfuse_replay_optimize(bsfuse_replay* h, const bsnls_options* o, bsnls_summary* s, bsnls_iteration* its, int max_its, double timing[5]) {
@@ -144,8 +142,9 @@ int bsfuse_replay_optimize(bsfuse_replay* h, const bsnls_options* o, bsnls_summa
   catch (const std::exception& e) { h->error = e.what(); return -3; }
 }
 void bsfuse_replay_current_values(bsfuse_replay* h, double* out) {   // in the order of the last bsfuse_replay_flatten
-  for (size_t b = 0; b < h->flat.block_variable.size(); ++b)
-    std::memcpy(out + h->flat.block_offset[b], h->flat.block_variable[b]->data(), sizeof(double) * h->flat.block_size[b]);
+  const FlatProblem& f = h->r->graph().lastProblem();
+  for (size_t b = 0; b < f.block_variable.size(); ++b)
+    std::memcpy(out + f.block_offset[b], f.block_variable[b]->data(), sizeof(double) * f.block_size[b]);
 }
 int bsfuse_evaluate(bsfuse_graph* g, double* cost) {
   try { return g->graph.evaluate(cost, nullptr, nullptr) ? 0 : -3; }

@@ -77,7 +77,7 @@ void ResolveHint(const HashGraph& graph, const Constraint& c, FlatProblem& P) {
     }
     hnt.camera = it->second;
   }
-  hnt.owner = &graph;
+  hnt.owner = &P;   // variable objects belong to the graph, the camera index to this FlatProblem's table: one FlatProblem serves one graph
 }
 }  // namespace
 
@@ -117,7 +117,7 @@ void Flatten(const HashGraph& graph, FlatProblem* out) {
   // createProblem, second loop (hash_graph.cpp:506-521)
   for (const auto& kv : graph.getConstraints()) {
     const Constraint& c = *kv.second;
-    if (c.flat_hint.owner != &graph) ResolveHint(graph, c, P);
+    if (c.flat_hint.owner != &P) ResolveHint(graph, c, P);
     const Constraint::FlatHint& hnt = c.flat_hint;
     FlatProblem::Group& g = P.groups[hnt.type];
     for (int b = 0; b < hnt.nblocks; ++b) g.blocks.push_back(hnt.vars[b]->flat_index);

@@ -23,7 +23,7 @@ GpuHashGraph::GpuHashGraph() = default;
 GpuHashGraph::~GpuHashGraph() { if (handle_) bsnls_destroy(handle_); }
 
 void GpuHashGraph::EnsureHandle(const SolverOptions& options) const {
-  if (handle_ && options.linear_solver != last_options_.linear_solver) flat_version_ = 0;   // reduced-system storage changes
+  if (handle_ && options.linear_solver != last_options_.linear_solver) device_version_ = 0;   // reduced-system storage changes
   last_options_ = options;
   bsnls_options c; ToCOptions(options, &c);
   if (!handle_) {
@@ -36,26 +36,29 @@ void GpuHashGraph::EnsureHandle(const SolverOptions& options) const {
   }
 }
 
+const FlatProblem& GpuHashGraph::flattened() const {
+  if (flat_version_ == structureVersion() && flat_version_ != 0) flat_.GatherValues();   // only Variable::data() moved
+  else { Flatten(*this, &flat_); flat_version_ = structureVersion(); }                 // createProblem
+  return flat_;
+}
+
 int GpuHashGraph::SyncProblem() const {
   using clk = std::chrono::steady_clock;
   const auto t0 = clk::now();
-  if (flat_version_ == structureVersion() && flat_version_ != 0) {
-    // same blocks, same factors (constraints are immutable once added, as in fuse): only Variable::data() moved
-    flat_.GatherValues();
-    const auto t1 = clk::now();
-    const int rc = bsnls_set_values(handle_, flat_.block_values.data());
-    timing_.flatten = std::chrono::duration<double>(t1 - t0).count();
-    timing_.upload = std::chrono::duration<double>(clk::now() - t1).count();
-    timing_.structure_reused = true;
-    return rc;
-  }
-  Flatten(*this, &flat_);  // createProblem
+  flattened();
   const auto t1 = clk::now();
   timing_.flatten = std::chrono::duration<double>(t1 - t0).count();
-  timing_.structure_reused = false;
-  if (flat_.cgroups.empty() || flat_.block_size.empty()) { flat_version_ = 0; timing_.upload = 0; return BSNLS_OK; }
-  const int rc = bsnls_set_problem(handle_, &flat_.c);
-  flat_version_ = rc == BSNLS_OK ? structureVersion() : 0;
+  int rc = BSNLS_OK;
+  if (flat_.cgroups.empty() || flat_.block_size.empty()) { device_version_ = 0; timing_.upload = 0; timing_.structure_reused = false; return BSNLS_OK; }
+  if (device_version_ == flat_version_ && device_version_ != 0) {
+    // same blocks, same factors (constraints are immutable once added, as in fuse): the device problem stays, values move
+    rc = bsnls_set_values(handle_, flat_.block_values.data());
+    timing_.structure_reused = true;
+  } else {
+    rc = bsnls_set_problem(handle_, &flat_.c);
+    device_version_ = rc == BSNLS_OK ? flat_version_ : 0;
+    timing_.structure_reused = false;
+  }
   timing_.upload = std::chrono::duration<double>(clk::now() - t1).count();
   return rc;
 }

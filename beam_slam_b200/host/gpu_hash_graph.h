@@ -21,6 +21,9 @@ class GpuHashGraph : public HashGraph {
   // Problem::Evaluate with default EvaluateOptions (hash_graph.cpp:446-455)
   bool evaluate(double* cost, std::vector<double>* residuals, std::vector<double>* gradient) const override;
   const FlatProblem& lastProblem() const { return flat_; }
+  // createProblem-order SoA view of the graph as it is now (re-flattened only if the structure changed, else the values
+  // are gathered); the returned object stays owned by the graph
+  const FlatProblem& flattened() const;
   // host wall-clock split of the last optimize(), seconds: flatten (or value gather), bsnls_set_problem (or
   // bsnls_set_values), bsnls_solve, bsnls_get_values + scatter; and whether the device problem was reused
   struct Timing { double flatten = 0, upload = 0, solve = 0, download = 0; bool structure_reused = false; };
@@ -32,7 +35,8 @@ class GpuHashGraph : public HashGraph {
   int SyncProblem() const;
   mutable bsnls_handle* handle_ = nullptr;
   mutable FlatProblem flat_;
-  mutable uint64_t flat_version_ = 0;     // structureVersion() the device problem was built from (0: none)
+  mutable uint64_t flat_version_ = 0;     // structureVersion() flat_ was built from (0: none)
+  mutable uint64_t device_version_ = 0;   // structureVersion() the device problem was built from (0: none)
   mutable Timing timing_;
   mutable SolverOptions last_options_;   // evaluate() keeps the handle's options (re-capturing CUDA graphs costs more than a solve)
 };

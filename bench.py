@@ -81,42 +81,79 @@ def algorithmic_bytes(info, nf_dim, dense):
     return eval_b, schur_b
 
 
-def cpu_sample(config, scale, steps=2):
-    """Oracle (CPU port of the reference's Ceres path) on a bounded sample of the same workload."""
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def load_traffic():
+    """Per-launch DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of the hot kernels, from the committed
+    `ncu --set full` capture (profiles/): {"capture": ..., "kernels": {name: bytes}, "stages": {stage: [names]}}."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    return json.load(open(p)) if os.path.exists(p) else None
+
+
+def cpu_pass(p, steps, warmup):
+    """Oracle (CPU restatement of the reference's Ceres path) on the SAME graph, every host core: seconds per
+    eval + Schur pass (residuals, Jacobians, landmark elimination into the block-sparse reduced system)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as orc
-    sample_scale = min(scale, {1: 1.0, 2: 1.0, 3: 1.0, 4: 0.1, 5: 0.02}[config])
-    g, p, _ = build_problem(config, sample_scale)
-    sec, threads = orc.time_eval_schur(p, 1e4, steps)
-    return g.info["num_observations"] / sec, threads, f"config {config} at scale {sample_scale}: {g.info['num_keyframes']} kf, " \
-        f"{g.info['num_landmarks']} lm, {g.info['num_observations']} obs; best of {steps} eval+Schur passes"
+    cores = host_cores()
+    orc.set_num_threads(cores)     # torchrun exports OMP_NUM_THREADS=1
+    for _ in range(warmup):
+        orc.time_eval_schur(p, 1e4, 1)
+    ts = []
+    for _ in range(steps):
+        sec, threads = orc.time_eval_schur(p, 1e4, 1)
+        ts.append(sec)
+    return ts, threads
 
 
 def run_reference(args):
+    """The reference arm: the reference's own (CPU) implementation of the path — Ceres is not installable here, so its
+    restatement under oracle/ — on the GPU arm's workload (same graph, same size), all host cores, rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     t0 = time.time()
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import oracle_lib as orc
-    sample_scale = min(args.scale, {1: 1.0, 2: 1.0, 3: 1.0, 4: 0.1, 5: 0.02}[args.config])
-    g, p, _ = build_problem(args.config, sample_scale)
-    for _ in range(args.warmup):
-        orc.time_eval_schur(p, 1e4, 1)
-    ts = []
-    for _ in range(args.steps):
-        sec, threads = orc.time_eval_schur(p, 1e4, 1)
-        ts.append(sec)
+    g, p, _ = build_problem(args.config, args.scale)
+    ts, threads = cpu_pass(p, args.steps, min(args.warmup, 1))
     nobs = g.info["num_observations"]
     v = nobs * len(ts) / sum(ts)
-    sample = f"config {args.config} at scale {sample_scale}: {g.info['num_keyframes']} kf, {g.info['num_landmarks']} lm, {nobs} obs per step"
+    sample = f"config {args.config} at scale {args.scale}: {g.info['num_keyframes']} kf, {g.info['num_landmarks']} lm, {nobs} obs per step (one eval+Schur pass per step)"
     print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": "obs/s", "n_gpus": args.gpus, "steps": args.steps,
-                      "warmup": args.warmup, "ms_per_step": 1e3 * sum(ts) / len(ts), "higher_is_better": True, "scaling": "strong",
+                      "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * sum(ts) / len(ts), "higher_is_better": True, "scaling": "strong",
                       "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                      "config": {"workload": CONFIG_NAMES[args.config], "sample": sample},
-                      "cpu_baseline": {"value": v, "unit": "obs/s", "cores": threads, "kind": "port", "sample": sample},
+                      "config": {"workload": CONFIG_NAMES[args.config], "scale": args.scale, "observations": nobs, "sample": sample},
+                      "cpu_baseline": {"value": v, "unit": "obs/s", "cores": threads, "host_cores": host_cores(), "kind": "port", "sample": sample},
                       "e2e": {"value": v, "unit": "obs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                       "wall_s": time.time() - t0}))
+
+
+def smoother_cycles(host, opts, cycles=24):
+    """The fixed-lag smoother's call pattern on a 10-keyframe VIO window (fixed_lag_smoother.cpp:220-281): every cycle a
+    keyframe enters, the oldest is pseudo-marginalised, optimize() runs on the changed graph. Wall clock of optimize()
+    (flatten + bsnls_set_problem + solve + write-back), median over the cycles after two warm-ups."""
+    r = host.SmootherReplay(cycles + 12, 10)
+    walls, parts, dev, its_n, upd = [], [], [], [], []
+    for _ in range(cycles):
+        upd.append(r.advance())
+        t0 = time.perf_counter()
+        s, its, timing = r.optimize(opts)
+        walls.append(time.perf_counter() - t0)
+        parts.append(timing)
+        dev.append(s.device_time_in_seconds)
+        its_n.append(s.num_iterations)
+    k = slice(2, None)
+    med = lambda v: float(np.median(v[k]))
+    return {"pattern": "one keyframe added + oldest pseudo-marginalised per cycle, structure rebuilt every call",
+            "optimize_wall_ms_median": 1e3 * med(walls), "optimize_wall_ms_max": 1e3 * float(np.max(walls[k])),
+            "flatten_ms": 1e3 * med([q["flatten_s"] for q in parts]), "set_problem_ms": 1e3 * med([q["upload_s"] for q in parts]),
+            "solve_ms": 1e3 * med([q["solve_s"] for q in parts]), "writeback_ms": 1e3 * med([q["download_s"] for q in parts]),
+            "solve_device_ms": 1e3 * med(dev), "graph_update_ms (caller side)": 1e3 * med(upd),
+            "iterations_median": float(np.median(its_n[k])), "observations": r.observations(), "cycles": cycles}
 
 
 def run_ours(args):
@@ -150,6 +187,13 @@ def run_ours(args):
         if world > 1:
             dist.barrier()
 
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     for _ in range(args.warmup):
         s.run_eval()
         s.run_schur(1e4)
@@ -169,11 +213,7 @@ def run_ours(args):
     barrier()
     wall = time.time() - wall0
     launches = s.launch_count() - launches0
-    dev_ms = sum(ev_ms) + sum(sc_ms)
-    if world > 1:
-        t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_ms = float(t.item())
+    dev_ms = max_over_ranks(sum(ev_ms) + sum(sc_ms))
     if wall < 0.6:
         # the timed region is shorter than nvidia-smi's sampling period: keep the same kernels running (untimed) so
         # that the clock / throttle record is taken under the same load. Same count on every rank (collectives inside).
@@ -181,10 +221,10 @@ def run_ours(args):
             s.run_eval()
             s.run_schur(1e4)
     clocks = sampler.stop()
-    clocks["sampled"] = "during the timed region" if wall >= 0.6 else "same kernels looped for 0.8 s right after the timed region (region too short to sample)" 
+    clocks["sampled"] = "during the timed region" if wall >= 0.6 else "same kernels looped for 0.8 s right after the timed region (region too short to sample)"
     value = nobs * args.steps / (dev_ms * 1e-3)
 
-    # end to end through the C-ABI with host buffers: H2D of the step's parameter values, eval + Schur, D2H of the cost
+    # pass level, through the C-ABI with host buffers: H2D of the step's parameter values, eval + Schur, D2H of the cost
     x_host = torch.from_numpy(p.block_values.copy()).pin_memory().numpy()
     barrier()
     t0 = time.time()
@@ -193,18 +233,64 @@ def run_ours(args):
         s.run_eval()
         s.run_schur(1e4)
     barrier()
-    e2e_s = time.time() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e = nobs * args.steps / e2e_s
+    pass_e2e = nobs * args.steps / max_over_ranks(time.time() - t0)
 
     # whole-solve numbers (LM iterations/s) on the same graph
     s.set_values(p.block_values)
     summ, its = s.solve()
+    s.set_values(p.block_values)
+    summ, its = s.solve()          # second solve of the structure: CUDA-graph replay where graphs are used
     lm_iters = max(1, summ.num_iterations - 1)
     lm_iters_per_s = lm_iters / summ.device_time_in_seconds if summ.device_time_in_seconds > 0 else None
+    lm = {"iterations": summ.num_iterations, "lm_iters_per_s": lm_iters_per_s, "solve_device_ms": summ.device_time_in_seconds * 1e3,
+          "termination": summ.message.decode(), "initial_cost": summ.initial_cost, "final_cost": summ.final_cost}
+
+    # The plug-in call a fuse user makes: GpuHashGraph::optimize with host buffers in and out (Variable::data()):
+    # flatten or value gather, bsnls_set_problem or bsnls_set_values, bsnls_solve, bsnls_get_values, scatter.
+    # One GPU only (the graph-level drop-in is the single-GPU path; the sharded solve is driven through the C-ABI).
+    plug = None
+    if world == 1:
+        x0 = g.current_values()
+        first = None
+        walls, splits, iters = [], [], []
+        for i in range(args.warmup + args.steps):
+            g.set_values(x0)                      # the caller's new estimates; not part of optimize()
+            t0 = time.perf_counter()
+            sg, itg = g.optimize(opts)
+            w = time.perf_counter() - t0
+            if i == 0:
+                first = {"wall_ms": 1e3 * w, **{k: (1e3 * v if k.endswith("_s") else v) for k, v in g.last_timing().items()}}
+            if i >= args.warmup:
+                walls.append(w)
+                splits.append(g.last_timing())
+                iters.append(max(1, sg.num_iterations - 1))
+        tot = sum(walls)
+        plug = {"call": "GpuHashGraph::optimize (flatten | set_problem or set_values | solve | get_values + scatter), host buffers in and out",
+                "value": nobs * sum(iters) / tot, "unit": "obs/s", "optimize_wall_ms": 1e3 * tot / len(walls), "lm_steps_per_call": float(np.mean(iters)),
+                "flatten_or_gather_ms": 1e3 * float(np.mean([q["flatten_s"] for q in splits])), "upload_ms": 1e3 * float(np.mean([q["upload_s"] for q in splits])),
+                "solve_ms": 1e3 * float(np.mean([q["solve_s"] for q in splits])), "writeback_ms": 1e3 * float(np.mean([q["download_s"] for q in splits])),
+                "structure_reused": bool(splits[-1]["structure_reused"]), "first_call": first,
+                "h2d_bytes_per_step": int(8 * p.num_values), "d2h_bytes_per_step": int(8 * p.num_values + 88 * sg.num_iterations),
+                "note": "value = observations x LM steps per call / wall time of the call; every LM step passes every observation through residual + Jacobian + Schur"}
+        assert abs(sg.final_cost - summ.final_cost) <= 1e-9 * summ.final_cost
+
+    # N > 1: the sharded solve against a single-GPU solve of the same graph on rank 0 (parity of the NCCL path where the
+    # driver runs N ranks)
+    if world > 1:
+        if rank == 0:
+            o1 = host.HashGraph.synthetic_options(args.config)
+            o1.device = local
+            s1 = Solver(o1)
+            s1.set_problem(p)
+            sm1, it1 = s1.solve()
+            lm["rel_diff_vs_single_gpu"] = {
+                "iterations_equal": len(it1) == len(its),
+                "max_cost_rel_diff_per_iteration": max(abs(a.cost - b.cost) / abs(b.cost) for a, b in zip(its, it1)),
+                "final_cost_rel_diff": abs(summ.final_cost - sm1.final_cost) / abs(sm1.final_cost),
+                "first_step_norm_rel_diff": abs(its[1].step_norm - it1[1].step_norm) / it1[1].step_norm if len(its) > 1 and len(it1) > 1 else None,
+                "single_gpu_solve_device_ms": sm1.device_time_in_seconds * 1e3}
+            s1.close()
+        barrier()
 
     mean = lambda k: float(np.mean([q[k] for q in parts]))
     br = {k: mean(k) for k in Solver.BREAKDOWN}
@@ -217,43 +303,57 @@ def run_ours(args):
     dom = max(stages, key=lambda k: stages[k][0])
     dom_ms, dom_bytes = stages[dom]
     achieved = dom_bytes / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    tr = load_traffic()
+    traffic, traffic_detail = None, None
+    if tr and world == 1 and args.config == tr.get("config") and args.scale == tr.get("scale"):
+        names = tr["stages"].get(dom, [])
+        traffic = int(sum(tr["kernels"][n] for n in names)) if names else None
+        traffic_detail = {"capture": tr["capture"], "dram_bytes_per_launch": tr["kernels"],
+                          "dram_over_algorithmic": {st: sum(tr["kernels"][n] for n in ns) / stages[st][1] for st, ns in tr["stages"].items() if st in stages}}
+    e2e = {"value": plug["value"], "unit": "obs/s", "h2d_bytes_per_step": plug["h2d_bytes_per_step"], "d2h_bytes_per_step": plug["d2h_bytes_per_step"],
+           "call": plug["call"], "optimize_wall_ms": plug["optimize_wall_ms"]} if plug else \
+          {"value": pass_e2e, "unit": "obs/s", "h2d_bytes_per_step": int(8 * p.num_values), "d2h_bytes_per_step": 8 * 16,
+           "call": "bsnls_set_values + bsnls_run_eval + bsnls_run_schur per step (sharded solve: driven through the C-ABI)"}
     out = {"metric": METRIC, "value": value, "unit": "obs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
            "data": "synthetic",
            "config": {"workload": CONFIG_NAMES[args.config], "scale": args.scale, "keyframes": info["num_keyframes"],
                       "landmarks": info["num_landmarks"], "observations": nobs, "reduced_system_dim": nf_dim,
+                      "generator": "analytic smooth trajectory (closed-form position, Euler-angle attitude), not the basalt quintic B-spline of SURVEY 8(d)",
                       "l2": "inputs larger than L2 (Jacobian + elimination records %.0f MB)" % (272e-6 * nobs) if nobs * 272 > 130e6 else "inputs fit in L2 (latency-bound config)",
                       "multi_gpu": "single GPU" if world == 1 else f"landmarks sharded over {world} GPUs, NCCL all-reduce of the reduced camera system per step"},
            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                        "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms": dom_ms,
+                        "traffic": traffic, "traffic_detail": traffic_detail, "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms": dom_ms,
                         "whole_pass_frac": (eval_b + schur_b) / (dev_ms / args.steps * 1e-3) / 1e9 / peak, "per": "GPU"},
            "kernel_ms": br,
-           "e2e": {"value": e2e, "unit": "obs/s", "h2d_bytes_per_step": int(8 * p.num_values), "d2h_bytes_per_step": 8 * 16},
-           "gpu_launches": launches, "clocks": clocks,
-           "lm": {"iterations": summ.num_iterations, "lm_iters_per_s": lm_iters_per_s, "solve_device_ms": summ.device_time_in_seconds * 1e3,
-                  "termination": summ.message.decode(), "initial_cost": summ.initial_cost, "final_cost": summ.final_cost},
+           "e2e": e2e,
+           "e2e_pass": {"value": pass_e2e, "unit": "obs/s", "call": "bsnls_set_values + bsnls_run_eval + bsnls_run_schur per step", "h2d_bytes_per_step": int(8 * p.num_values), "d2h_bytes_per_step": 8 * 16},
+           "plugin_optimize": plug,
+           "gpu_launches": launches, "clocks": clocks, "lm": lm,
            "setup_s": {"generate+flatten": t_build, "set_problem": t_setup}, "wall_s_timed": wall}
     if rank == 0:
         if world == 1:
             try:
-                v, threads, sample = cpu_sample(args.config, args.scale)
-                out["cpu_baseline"] = {"value": v, "unit": "obs/s", "cores": threads, "kind": "port", "sample": sample}
+                ts, threads = cpu_pass(p, 3, 1)
+                out["cpu_baseline"] = {"value": nobs * len(ts) / sum(ts), "unit": "obs/s", "cores": threads, "host_cores": host_cores(), "kind": "port",
+                                       "sample": f"the same graph at full size ({nobs} obs): 3 eval+Schur passes after 1 warm-up, {1e3 * sum(ts) / len(ts):.0f} ms each"}
             except Exception as e:  # the baseline is reported, never required
                 out["cpu_baseline"] = {"value": None, "unit": "obs/s", "cores": 0, "kind": "port", "sample": f"failed: {e}"}
-            try:  # the latency-bound sliding-window target of the north star: whole solve of the 10-keyframe VIO window
-                g1 = host.HashGraph.synthetic(1)
-                p1 = g1.flatten()
+            try:  # the latency-bound sliding-window target of the north star: the 10-keyframe VIO window
                 o1 = host.HashGraph.synthetic_options(1)
                 o1.device = local
-                s1 = Solver(o1)
-                s1.set_problem(p1)
-                dev = []
-                for _ in range(8):
-                    s1.set_values(p1.block_values)
-                    sm1, _ = s1.solve()
+                g1 = host.HashGraph.synthetic(1)
+                x1 = g1.current_values() if g1.flatten() is not None else None
+                walls, dev = [], []
+                for _ in range(10):
+                    g1.set_values(x1)
+                    t0 = time.perf_counter()
+                    sm1, _ = g1.optimize(o1)
+                    walls.append(time.perf_counter() - t0)
                     dev.append(sm1.device_time_in_seconds * 1e3)
-                out["vio_window"] = {"config": CONFIG_NAMES[1], "solve_device_ms_median": float(np.median(dev[2:])),
-                                     "iterations": sm1.num_iterations, "observations": g1.info["num_observations"]}
+                out["vio_window"] = {"config": CONFIG_NAMES[1], "iterations": sm1.num_iterations, "observations": g1.info["num_observations"],
+                                     "unchanged_graph": {"optimize_wall_ms_median": 1e3 * float(np.median(walls[3:])), "solve_device_ms_median": float(np.median(dev[3:]))},
+                                     "smoother_cycles": smoother_cycles(host, o1)}
             except Exception as e:
                 out["vio_window"] = {"error": str(e)}
         print(json.dumps(out))

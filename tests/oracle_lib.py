@@ -40,6 +40,7 @@ def load():
                                            _pi32]
     lib.oracle_time_eval_schur.restype = C.c_double
     lib.oracle_set_linear_mode.argtypes = [C.c_int32]
+    lib.oracle_set_num_threads.argtypes = [C.c_int32]
     lib.oracle_reduced_blocks.argtypes = [C.POINTER(cabi.Problem), C.POINTER(cabi.Options), C.c_double, _pi32, _pi32, _pf64,
                                           C.POINTER(C.c_int64), _pf64]
     lib.oracle_solve_trace.argtypes = [C.POINTER(cabi.Problem), C.POINTER(cabi.Options), C.POINTER(cabi.Summary),
@@ -64,6 +65,11 @@ def solve(problem, options=None, max_iters=256):
 
 
 LINEAR_AUTO, LINEAR_DENSE, LINEAR_SPARSE = 0, 1, 2
+
+
+def set_num_threads(n):
+    """OpenMP threads of the oracle (torchrun sets OMP_NUM_THREADS=1 for its workers)."""
+    load().oracle_set_num_threads(int(n))
 
 
 def set_linear_mode(mode):
