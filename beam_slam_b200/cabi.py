@@ -188,6 +188,7 @@ def load_library():
     lib.bsnls_trial_step.argtypes = [H, _pf64, C.c_double, C.c_int32, C.POINTER(Iteration), _pi32]
     lib.bsnls_run_eval.argtypes = [H, _pf64]
     lib.bsnls_run_schur.argtypes = [H, C.c_double]
+    lib.bsnls_run_pass.argtypes = [H, C.c_double, _pf64]
     lib.bsnls_last_kernel_ms.argtypes = [H, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.bsnls_last_breakdown_ms.argtypes = [H, C.POINTER(C.c_float)]
     lib.bsnls_last_breakdown_ms.restype = C.c_int
@@ -201,7 +202,7 @@ def load_library():
     lib.bsnls_create_sharded.argtypes = [C.POINTER(Options), C.c_int32, C.c_int32, C.c_char * 128, C.POINTER(H)]
     for name in ("bsnls_create", "bsnls_set_problem", "bsnls_set_values", "bsnls_set_options", "bsnls_solve",
                  "bsnls_get_values", "bsnls_evaluate", "bsnls_get_ordering", "bsnls_get_reduced_pattern",
-                 "bsnls_get_reduced_system", "bsnls_get_reduced_blocks", "bsnls_trial_step", "bsnls_run_eval", "bsnls_run_schur", "bsnls_last_kernel_ms",
+                 "bsnls_get_reduced_system", "bsnls_get_reduced_blocks", "bsnls_trial_step", "bsnls_run_eval", "bsnls_run_schur", "bsnls_run_pass", "bsnls_last_kernel_ms",
                  "bsnls_nccl_unique_id", "bsnls_create_sharded"):
         getattr(lib, name).restype = C.c_int
     _lib = lib

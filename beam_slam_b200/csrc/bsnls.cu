@@ -127,6 +127,7 @@ struct bsnls_handle {
   DevMem d_tc_pan_k, d_tc_pan_x, d_tc_upd_ptr, d_tc_upd_dst, d_tc_upd_a, d_tc_upd_b, d_tc_fw_ptr, d_tc_fw_row, d_tc_fw_tail, d_tc_fw_src, d_tc_fw_k, d_tc_lev_cols, d_tc_bw_ptr, d_tc_bw_col, d_tc_bw_tail, d_tc_bw_src, d_tc_bw_i, d_tc_roots; int tc_nroots = 0;
   long long nlow = 0; DevMem d_low_slot, d_low_slot_t, d_xsend, d_xrecv;   // sharded solve: lower-triangular blocks of S, packed exchange buffers
   int chunk_max_slots = 1; DevMem d_syrk_plan, d_chunk_tile_off, d_pp_toff, d_pp_info;
+  bool fused = false; DevMem d_chunk_pose, d_chunk_stage_ptr, d_stage_lm, d_pc_ptr, d_pc_idx;   // chunk-major fused pass
   int nchunks = 0; DevMem d_obs_slot, d_chunk_end, d_chunk_begin, d_chunk_nslots, d_pp_ptr, d_part;
   bool sparse = false, pcg = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
   // residual-block bookkeeping for bsnls_evaluate (program order)
@@ -248,10 +249,33 @@ int AllReduceScalars(bsnls_handle* h) {  // rank-local partial sums and the loca
 }
 RedDesc Desc(const double* src, int n, int op, int slot, bool replicated) { return RedDesc{src, n, op, op ? (replicated ? kRedReplMax : kRedLocalMax) : slot + (replicated ? RED_NUM : 0)}; }
 
-void EnqueueEval(bsnls_handle* h) {  // phase A: residuals + Jacobians + cost at x
+// chunk-major fused pass: Jacobians (or their stored records), landmark elimination and, with_system, the chunk tiles
+void EnqueueFused(bsnls_handle* h, const Options& o, int with_system, int force_load) {
+  LAUNCH_SMEM(h, chunk_fused_kernel, h->nchunks, 256, fused_smem_bytes(h->chunk_max_slots), h->P, h->d_x.as<double>(), h->d_pose_tab.as<double>(), h->d_Jrec.as<double>(),
+              h->d_minv.as<double>(), h->d_grad.as<double>(), h->d_colsq.as<double>(), h->d_scale.as<double>(), h->d_lmz.as<double>(), h->d_part.as<double>(),
+              h->d_pose_part.as<double>(), h->d_cost_part.as<double>(), o, h->d_state.as<LMState>(), with_system, force_load);
+}
+// phase A: residuals + Jacobians + cost at x. fused_system: in the fused mode, also eliminate and accumulate the tiles
+void EnqueueEval(bsnls_handle* h, int fused_system = 0) {
   const DeviceProblem& P = h->P;
   LMState* st = h->d_state.as<LMState>();
   MARK(h, 0);
+  if (h->fused) {
+    const Options o = MakeOptions(h->opt);
+    const bool fork = h->ngf > 0;
+    if (fork) {
+      cudaEventRecord(h->ev_fork, h->stream); cudaStreamWaitEvent(h->side, h->ev_fork, 0);
+      eval_generic_kernel<0><<<BlocksFor(h->ngf, 4), 128, 0, h->side>>>(P, h->d_x.as<double>(), h->d_gfJ.as<double>(), h->d_gfR.as<double>(), h->d_cost_part.as<double>() + h->nb_eval, st);
+      h->launches++;
+      cudaEventRecord(h->ev_join, h->side);
+    }
+    LAUNCH(h, pose_prep_kernel, BlocksFor(h->np, 128), 128, P, h->d_x.as<double>(), h->d_pose_tab.as<double>(), st);
+    EnqueueFused(h, o, fused_system, 0);
+    MARK(h, 1);
+    if (fork) cudaStreamWaitEvent(h->stream, h->ev_join, 0);
+    MARK(h, 2);
+    return;
+  }
   // the generic factors (IMU, priors, relative poses) are independent of the reprojection pass until the gradient is
   // put together: they run on a side stream (fork / join by events, which also works under stream capture)
   const bool fork = h->ngf && h->nobs;
@@ -276,6 +300,7 @@ template <int G> void LaunchLandmark(bsnls_handle* h, const Options& o) {
 }
 void EnqueueLandmark(bsnls_handle* h, const Options& o) {  // phase B
   if (!h->ne) return;
+  if (h->fused) { EnqueueFused(h, o, 1, 1); return; }   // stored Jacobian records -> elimination + chunk tiles
   switch (h->G) { case 4: LaunchLandmark<4>(h, o); break; case 8: LaunchLandmark<8>(h, o); break;
                   case 16: LaunchLandmark<16>(h, o); break; default: LaunchLandmark<32>(h, o); }
 }
@@ -285,7 +310,8 @@ void EnqueueLandmark(bsnls_handle* h, const Options& o) {  // phase B
 // f-block gradient norms, generic rows of S, damping).
 void EnqueueGradientLocal(bsnls_handle* h) {
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
-  if (h->np) LAUNCH(h, pose_reduce_kernel, BlocksFor(h->np * 27, 128), 128, P, h->d_pose_part.as<double>(), h->d_poseH.as<double>(), h->d_gradL.as<double>(), h->d_colsqL.as<double>(), st);
+  if (h->np) LAUNCH(h, pose_reduce_kernel, BlocksFor(h->np * 27, 128), 128, P, h->d_pose_part.as<double>(), h->fused ? h->d_pc_ptr.as<int>() : h->d_eval_item_ptr.as<int>(),
+                    h->fused ? h->d_pc_idx.as<int>() : (const int*)nullptr, h->d_poseH.as<double>(), h->d_gradL.as<double>(), h->d_colsqL.as<double>(), st);
   if (h->world == 1) return;   // one GPU: a single norm / reduction launch after the generic-factor gradient does it all
   const int nbe = h->nb_act_e;
   if (nbe) LAUNCH(h, grad_norm_kernel, nbe, 256, P, h->d_x.as<double>(), h->d_grad.as<double>(), h->d_gsq_part.as<double>(), h->d_gmax_part.as<double>(), 0, st);
@@ -353,7 +379,7 @@ void EnqueueAssembleLocal(bsnls_handle* h) {  // phase D1, this rank's share: S 
   cudaMemsetAsync(h->d_S.p, 0, sizeof(double) * s_count, h->stream);
   if (h->world > 1) cudaMemsetAsync(h->d_rhs.p, 0, sizeof(double) * P.nf_dim, h->stream);
   MARK(h, 6);
-  if (h->nchunks) {
+  if (h->nchunks && !h->fused) {
     LAUNCH_SMEM(h, chunk_syrk_kernel, h->nchunks, 256, syrk_smem_bytes(h->chunk_max_slots), P, h->d_Vrec.as<double>(), h->d_lmz.as<double>(), h->d_part.as<double>(), st);
   }
   if (h->npairs && h->nchunks) LAUNCH(h, pair_reduce_kernel, BlocksFor(h->npairs, 4), 144, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_lmz.as<double>(), h->d_poseH.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
@@ -489,8 +515,8 @@ int EnqueueTail(bsnls_handle* h, const Options& o, bsnls_iteration* recs) {   //
 }
 int EnqueuePass(bsnls_handle* h, const Options& o, bsnls_iteration* recs) {   // one LM iteration
   LMState* st = h->d_state.as<LMState>();
-  EnqueueEval(h);
-  EnqueueLandmark(h, o);
+  EnqueueEval(h, 1);
+  if (!h->fused) EnqueueLandmark(h, o);
   int rc = EnqueueLinearise(h, o, true);
   if (rc != BSNLS_OK) return rc;
   LAUNCH(h, ctrl_after_jacobian_kernel, 1, 1, st, h->d_red.as<double>(), recs, o);
@@ -543,6 +569,7 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
     g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA;
   }
   if ((e = cudaFuncSetAttribute(chunk_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, syrk_smem_bytes(kChunkSlots))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
+  if ((e = cudaFuncSetAttribute(chunk_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fused_smem_bytes(kChunkSlots))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(tile_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * kPanelSmemDoubles))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(tile_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * 2 * kTS * kTLd))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   for (auto& ev : h->pev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
@@ -897,6 +924,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   // ---- chunks: consecutive landmarks whose poses fit kChunkSlots slots are accumulated on chip by one CTA ----
   std::vector<unsigned short> obs_slot(nobs_local, 0xFFFF);
   std::vector<int> chunk_begin, chunk_end, chunk_nslots, chunk_pose;      // landmark range [begin, end) of each chunk
+  std::vector<int> chunk_stage_ptr, stage_lm;                              // stages of a chunk: <= 16 landmarks and <= kFuseMaxObs observations
   std::vector<long long> chunk_tile_off;
   long long tile_size = 0;
   std::vector<char> wide(h->ne, 0);
@@ -912,7 +940,15 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       if (cur_poses.empty()) { c_begin = end; c_obs = 0; c_kmax = 0; return; }   // only wide landmarks: nothing to accumulate on chip
       std::sort(cur_poses.begin(), cur_poses.end());           // slots in increasing pose id: slot A < B  <=>  pose a < b
       for (size_t q = 0; q < cur_poses.size(); ++q) stamp[cur_poses[q]] = (int)q;
-      for (int e = c_begin; e < end; ++e) if (!wide[e]) for (int k = lm_ptr_local[e]; k < lm_ptr_local[e + 1]; ++k) obs_slot[k] = (unsigned short)(stamp[s_pose[k]] | (((e - c_begin) % kSyrkStageLm) << 8));
+      chunk_stage_ptr.push_back((int)stage_lm.size());
+      int st_begin = c_begin, st_obs = 0;
+      for (int e = c_begin; e < end; ++e) {
+        const int k_e = lm_ptr_local[e + 1] - lm_ptr_local[e];
+        if (e > st_begin && (e - st_begin >= kSyrkStageLm || st_obs + k_e > kFuseMaxObs)) { stage_lm.push_back(st_begin); st_begin = e; st_obs = 0; }
+        st_obs += k_e;
+        if (!wide[e]) for (int k = lm_ptr_local[e]; k < lm_ptr_local[e + 1]; ++k) obs_slot[k] = (unsigned short)(stamp[s_pose[k]] | ((e - st_begin) << 8));
+      }
+      stage_lm.push_back(st_begin); stage_lm.push_back(end);
       chunk_begin.push_back(c_begin); chunk_end.push_back(end); chunk_nslots.push_back((int)cur_poses.size());
       for (int q = 0; q < kChunkSlots; ++q) chunk_pose.push_back(q < (int)cur_poses.size() ? cur_poses[q] : -1);
       chunk_tile_off.push_back(tile_size);
@@ -941,7 +977,23 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     close_chunk(h->ne);
   }
   h->nchunks = (int)chunk_nslots.size();
+  chunk_stage_ptr.push_back((int)stage_lm.size());
   h->chunk_max_slots = 1; for (int v : chunk_nslots) h->chunk_max_slots = std::max(h->chunk_max_slots, v);
+  // chunk-major fused pass (chunk_fused_kernel), opt-in with BSNLS_FUSED=1: it moves 2.2x fewer DRAM bytes than the
+  // three-kernel path but is slower on B200 (its phases serialise inside a CTA). Every landmark of the
+  // shard must go through a chunk.
+  { bool any_wide = false; for (char w : wide) any_wide = any_wide || w;
+    h->fused = h->nchunks > 0 && !any_wide && std::getenv("BSNLS_FUSED") != nullptr; }
+  std::vector<int> pc_ptr(h->np + 1, 0), pc_idx;   // per pose: its (chunk, slot) partial sums
+  if (h->fused) {
+    for (int c = 0; c < h->nchunks; ++c) for (int q = 0; q < chunk_nslots[c]; ++q) pc_ptr[chunk_pose[(size_t)c * kChunkSlots + q] + 1]++;
+    for (int a = 0; a < h->np; ++a) pc_ptr[a + 1] += pc_ptr[a];
+    pc_idx.resize(pc_ptr[h->np]);
+    std::vector<int> cur(pc_ptr.begin(), pc_ptr.end() - 1);
+    for (int c = 0; c < h->nchunks; ++c) for (int q = 0; q < chunk_nslots[c]; ++q) pc_idx[cur[chunk_pose[(size_t)c * kChunkSlots + q]]++] = c * kChunkSlots + q;
+    for (int it = 0; it < nobs_local; ++it) h->obs_pm_h[it] = it;   // Jacobian records live at their landmark-major position
+    h->nb_eval = h->nchunks;                                         // one cost partial per chunk
+  }
   if (std::getenv("BSNLS_DEBUG")) {
     long long slots = 0, nwide = 0; for (int v : chunk_nslots) slots += v; for (char w : wide) nwide += w;
     std::fprintf(stderr, "[bsnls] rank %d: %d landmarks, %d obs, %d poses, %d pairs, %d chunks (avg %.1f slots, %.1f landmarks), %lld wide landmarks, partial buffer %.1f MB\n",
@@ -1142,7 +1194,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_lm_ptr, lm_ptr_local, s)); CK(upload(h->d_lm_off, lm_off, s));
   CK(upload(h->d_obs_pm, h->obs_pm_h, s)); CK(upload(h->d_eval_items, eval_items, s)); CK(upload(h->d_eval_item_ptr, eval_item_ptr, s)); CK(upload(h->d_pm_lm_off, pm_lm_off, s));
   CK(upload(h->d_pm_cam, pm_cam, s)); CK(upload(h->d_pm_pixel, pm_pixel, s));
-  CK(h->d_pose_tab.alloc(sizeof(double) * kPoseTab * (size_t)std::max(1, h->np))); CK(h->d_pose_part.alloc(sizeof(double) * 27 * (size_t)std::max(1, h->n_eval_items)));
+  CK(h->d_pose_tab.alloc(sizeof(double) * kPoseTab * (size_t)std::max(1, h->np))); CK(h->d_pose_part.alloc(sizeof(double) * 27 * (size_t)std::max(1, h->fused ? h->nchunks * kChunkSlots : h->n_eval_items)));
   { std::vector<double> cams(pr->cameras, pr->cameras + (size_t)pr->num_cameras * BSNLS_CAMERA_STRIDE); CK(upload(h->d_cams, cams, s)); }
   CK(upload(h->d_gf_type, gf_type, s)); CK(upload(h->d_gf_nblk, gf_nblk, s)); CK(upload(h->d_gf_nres, gf_nres, s)); CK(upload(h->d_gf_blocks, gf_blocks, s));
   CK(upload(h->d_gf_coff, gf_coff, s)); CK(upload(h->d_gf_consts, gf_consts, s)); CK(upload(h->d_gf_loss_type, gf_loss_type, s));
@@ -1151,6 +1203,8 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_item_i, item_i, s)); CK(upload(h->d_item_j, item_j, s));
   CK(upload(h->d_obs_slot, obs_slot, s)); CK(upload(h->d_chunk_begin, chunk_begin, s)); CK(upload(h->d_chunk_end, chunk_end, s)); CK(upload(h->d_chunk_nslots, chunk_nslots, s));
   CK(upload(h->d_pp_ptr, pp_ptr, s));
+  CK(upload(h->d_chunk_pose, chunk_pose, s)); CK(upload(h->d_chunk_stage_ptr, chunk_stage_ptr, s)); CK(upload(h->d_stage_lm, stage_lm, s));
+  CK(upload(h->d_pc_ptr, pc_ptr, s)); CK(upload(h->d_pc_idx, pc_idx, s));
   { std::vector<int> plan((kSyrkMaxNt + 1) * 8 * kSyrkMaxStrips); syrk_build_plan(plan.data()); CK(upload(h->d_syrk_plan, plan, s)); }
   CK(upload(h->d_chunk_tile_off, chunk_tile_off, s)); CK(upload(h->d_pp_toff, pp_toff, s)); CK(upload(h->d_pp_info, pp_info, s));
   CK(h->d_part.alloc(sizeof(double) * (size_t)tile_size));
@@ -1268,7 +1322,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     g_rec->up_used += Arena::Align(sizeof(double) * off); g_rec->members.push_back(&m);
   }
   CK(h->d_xc.alloc(sizeof(double) * off)); CK(h->d_x0.alloc(sizeof(double) * off));
-  CK(h->d_Jrec.alloc(sizeof(double) * kJRec * (size_t)h->nobs)); CK(h->d_Vrec.alloc(sizeof(double) * kVRec * (size_t)h->nobs));
+  CK(h->d_Jrec.alloc(sizeof(double) * kJRec * (size_t)h->nobs)); CK(h->d_Vrec.alloc(h->fused ? 8 : sizeof(double) * kVRec * (size_t)h->nobs));   // the fused pass keeps V on chip
   CK(h->d_minv.alloc(sizeof(double) * 6 * (size_t)h->ne)); CK(h->d_lmz.alloc(sizeof(double) * 3 * (size_t)h->ne)); CK(h->d_grad.alloc(sizeof(double) * ntan)); CK(h->d_colsq.alloc(sizeof(double) * ntan));
   CK(h->d_zero.alloc(sizeof(double) * (2 * (size_t)nf_dim + ntan)));   // gradL | colsqL | y: start at zero, cleared by one memset
   if (h->world > 1) { CK(h->d_gradS.alloc(sizeof(double) * nf_dim)); CK(h->d_colsqS.alloc(sizeof(double) * nf_dim)); }
@@ -1357,6 +1411,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   P.gf_joff = h->d_gf_joff.as<int>(); P.gf_roff = h->d_gf_roff.as<int>();
   P.num_pairs = h->npairs; P.pair_a = h->d_pair_a.as<int>(); P.pair_b = h->d_pair_b.as<int>(); P.pair_ptr = h->d_pair_ptr.as<int>();
   P.item_i = h->d_item_i.as<int>(); P.item_j = h->d_item_j.as<int>();
+  P.chunk_max_slots = h->chunk_max_slots; P.chunk_pose = h->d_chunk_pose.as<int>(); P.chunk_stage_ptr = h->d_chunk_stage_ptr.as<int>(); P.stage_lm = h->d_stage_lm.as<int>();
   P.num_chunks = h->nchunks; P.obs_slot = h->d_obs_slot.as<unsigned short>(); P.syrk_plan = h->d_syrk_plan.as<int>(); P.chunk_begin = h->d_chunk_begin.as<int>(); P.chunk_end = h->d_chunk_end.as<int>(); P.chunk_nslots = h->d_chunk_nslots.as<int>();
   P.pp_ptr = h->d_pp_ptr.as<int>();
   P.chunk_tile_off = h->d_chunk_tile_off.as<long long>(); P.pp_toff = h->d_pp_toff.as<long long>(); P.pp_info = h->d_pp_info.as<int>();
@@ -1560,6 +1615,40 @@ int bsnls_run_schur(bsnls_handle* h, double radius) {
   return BSNLS_OK;
 }
 
+int bsnls_run_pass(bsnls_handle* h, double radius, double* cost) {
+  if (!h) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_run_pass before bsnls_set_problem");
+  if (!(radius > 0)) return h->fail(BSNLS_ERR_INVALID, "radius must be positive");
+  CK(cudaSetDevice(h->device));
+  int rc = InitState(h, false, radius);
+  if (rc != BSNLS_OK) return rc;
+  const Options o = MakeOptions(h->opt);
+  h->profiling = true;
+  CK(cudaEventRecord(h->ev0, h->stream));
+  EnqueueEval(h, 1);
+  MARK(h, 3);
+  if (!h->fused) EnqueueLandmark(h, o);
+  MARK(h, 4);
+  rc = EnqueueLinearise(h, o, true);
+  if (rc != BSNLS_OK) { h->profiling = false; return rc; }
+  EnqueueAssembleFinish(h, o);
+  CK(cudaEventRecord(h->ev1, h->stream));
+  h->profiling = false;
+  // cost = what the gradient pass reduced (local + replicated parts)
+  double red[kRedSize];
+  CK(cudaMemcpyAsync(red, h->d_red.p, sizeof(red), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream)); CK(cudaGetLastError());
+  if (cost) *cost = red[RED_COST] + red[RED_NUM + RED_COST];
+  float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+  h->last_eval_ms = ms; h->last_schur_ms = 0.f;
+  cudaEventElapsedTime(&h->breakdown[0], h->pev[0], h->pev[1]); cudaEventElapsedTime(&h->breakdown[1], h->pev[1], h->pev[2]);
+  cudaEventElapsedTime(&h->breakdown[2], h->pev[3], h->pev[4]); cudaEventElapsedTime(&h->breakdown[3], h->pev[4], h->pev[5]);
+  cudaEventElapsedTime(&h->breakdown[4], h->pev[5], h->pev[6]); cudaEventElapsedTime(&h->breakdown[5], h->pev[6], h->pev[7]);
+  cudaEventElapsedTime(&h->breakdown[7], h->pev[7], h->pev[9]); cudaEventElapsedTime(&h->breakdown[6], h->pev[9], h->pev[8]);
+  h->jac_valid = true;
+  return BSNLS_OK;
+}
+
 int bsnls_last_kernel_ms(bsnls_handle* h, float* eval_ms, float* schur_ms) {
   if (!h) return BSNLS_ERR_INVALID;
   if (eval_ms) *eval_ms = h->last_eval_ms;
@@ -1685,7 +1774,7 @@ int bsnls_evaluate(bsnls_handle* h, double* cost, double* residuals, int64_t* nu
   const Options o = MakeOptions(h->opt);
   LMState* st = h->d_state.as<LMState>();
   if (h->world > 1) return h->fail(BSNLS_ERR_UNSUPPORTED, "bsnls_evaluate is a single-GPU call (residuals live on the rank that owns their landmark)");
-  EnqueueEval(h); EnqueueLandmark(h, o); rc = EnqueueLinearise(h, o, false);
+  EnqueueEval(h); if (!h->fused) EnqueueLandmark(h, o); rc = EnqueueLinearise(h, o, false);
   if (rc != BSNLS_OK) return rc;
   // include factors whose blocks are all constant in the cost (Problem::Evaluate evaluates every residual block)
   RedList L{}; L.gate = 0; L.count = 0;

@@ -62,6 +62,7 @@ struct DeviceProblem {
   // (255: landmark handled through the item list); per pair the partial blocks the chunks produced
     // pose-major evaluation: items (pose, begin, end, 0) over the pose-sorted observation list and that list's inputs
   int num_eval_items; const int* obs_pm /* position of a (landmark-major) observation in the pose-major list = its Jacobian record */; const int4* eval_items; const int* eval_item_ptr; const int* pm_lm_off; const int* pm_cam; const double* pm_pixel;
+  int chunk_max_slots; const int* chunk_pose /* kChunkSlots per chunk: pose of each slot */; const int* chunk_stage_ptr /* per chunk: first entry of stage_lm (one more entry than stages) */; const int* stage_lm /* first landmark of each stage */;
   int num_chunks; const unsigned short* obs_slot /* slot | (landmark - chunk begin) % 16 << 8; slot 255 = not in a chunk */; const int* syrk_plan; const int* chunk_begin; const int* chunk_end; const int* chunk_nslots;
   const int* pp_ptr;
   // tile format of the tensor-core chunk kernel: raw 8x8 tiles of sum W W^T per chunk; per partial-list entry the
@@ -234,14 +235,15 @@ __global__ void __launch_bounds__(256, EVAL_MINB) eval_reproj_pose_kernel(Device
 }
 // One thread per (pose, entry): sums the pose's item partials in item order; writes pose_H and the rank-local gradient /
 // column-norm entries of the pose's q and t blocks (index = tangent - ne_dim).
-__global__ void __launch_bounds__(128) pose_reduce_kernel(DeviceProblem P, const double* __restrict__ pose_part, double* __restrict__ pose_H,
-                                                          double* __restrict__ grad, double* __restrict__ colsq, const LMState* st) {
+// part_idx (optional): the pose's partials are the listed entries of pose_part (chunk-major pass: one per (chunk, slot)).
+__global__ void __launch_bounds__(128) pose_reduce_kernel(DeviceProblem P, const double* __restrict__ pose_part, const int* __restrict__ part_ptr, const int* __restrict__ part_idx,
+                                                          double* __restrict__ pose_H, double* __restrict__ grad, double* __restrict__ colsq, const LMState* st) {
   if (!gate_jac(st)) return;
   const int tid = blockIdx.x * 128 + threadIdx.x;
   const int a = tid / 27, k = tid - a * 27;
   if (a >= P.num_poses) return;
   double sum = 0.0;
-  for (int it = P.eval_item_ptr[a]; it < P.eval_item_ptr[a + 1]; ++it) sum += pose_part[(size_t)it * 27 + k];
+  for (int it = part_ptr[a]; it < part_ptr[a + 1]; ++it) sum += pose_part[(size_t)(part_idx ? part_idx[it] : it) * 27 + k];
   const int tq = P.pose_q_tan[a], tt = P.pose_t_tan[a];
   if (k < 21) {
     pose_H[(size_t)a * 21 + k] = sum;
@@ -496,7 +498,7 @@ constexpr int kSyrkStageLm = 16;                 // landmarks per stage
 constexpr int kSyrkKB = 3 * kSyrkStageLm;        // 48 columns of W per stage = 12 k-steps
 constexpr int kSyrkLD = 52;                      // row pitch in doubles: 52 mod 16 = 4 keeps the 64-bit fragment loads conflict-free
 constexpr int kSyrkMaxTiles = 22;                // tiles per warp at 22 slots: ceil(153 / 8) + imbalance of the strip plan
-constexpr int kSyrkMaxStages = kChunkMaxLm / kSyrkStageLm + 2;
+constexpr int kSyrkMaxStages = 2 * (kChunkMaxLm / kSyrkStageLm) + 2;   // stages close at 16 landmarks or 256 observations
 constexpr int kSyrkLanesPerRec = 9, kSyrkRecPerPass = 28, kSyrkInFlight = 8;   // 9 lanes x double2 = V (18 doubles); 28 records per pass of 252 threads
 __host__ __device__ inline int syrk_smem_bytes(int nslots) { return 2 * (((6 * nslots + 1 + 7) >> 3) * 8) * kSyrkLD * 8; }
 
@@ -562,15 +564,14 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
                                                             double* __restrict__ part, const LMState* st) {
   extern __shared__ __align__(16) double Wsm[];    // two stage buffers W[row * kSyrkLD + k]
   __shared__ int sPlan[8 * kSyrkMaxStrips];
-  __shared__ int sO[kSyrkMaxStages];               // first observation of every stage of this chunk
+  __shared__ int sO[kSyrkMaxStages], sL[kSyrkMaxStages];   // first observation / first landmark of every stage of this chunk
   if (!gate_run(st)) return;
   const int c = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
   const int ns = P.chunk_nslots[c], nrow = 6 * ns + 1, nt = (nrow + 7) >> 3, nrow8 = nt * 8;
-  const int l_begin = P.chunk_begin[c], l_end = P.chunk_end[c];
-  const int nst = (l_end - l_begin + kSyrkStageLm - 1) / kSyrkStageLm;
+  const int sp0 = P.chunk_stage_ptr[c], nst = P.chunk_stage_ptr[c + 1] - sp0 - 1;   // stages: <= 16 landmarks and <= 256 observations (host table)
   double* const buf0 = Wsm; double* const buf1 = Wsm + nrow8 * kSyrkLD;
   if (tid < 8 * kSyrkMaxStrips) sPlan[tid] = P.syrk_plan[nt * 8 * kSyrkMaxStrips + tid];
-  for (int s = tid; s <= nst; s += 256) sO[s] = P.lm_ptr[min(l_begin + s * kSyrkStageLm, l_end)];
+  for (int s = tid; s <= nst; s += 256) { sL[s] = P.stage_lm[sp0 + s]; sO[s] = P.lm_ptr[P.stage_lm[sp0 + s]]; }
   const int frag = g * kSyrkLD + tg;
   // accumulators of this warp's tiles; a group at a time in registers, the rest waits in (L1-resident) local memory
   double accs[kSyrkMaxTiles][2];
@@ -583,7 +584,7 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
   const int off0 = (e0 / 3) * kSyrkLD + e0 % 3, off1 = (e1 / 3) * kSyrkLD + e1 % 3;
   double2 v[kSyrkInFlight]; int meta[kSyrkInFlight]; double zreg = 0.0;
   auto prefetch = [&](int s) {
-    const int la = l_begin + s * kSyrkStageLm, o0 = sO[s], o1 = sO[s + 1];
+    const int la = sL[s], o0 = sO[s], o1 = sO[s + 1];
 #pragma unroll
     for (int u = 0; u < kSyrkInFlight; ++u) {
       const int o = o0 + oo + kSyrkRecPerPass * u;
@@ -591,7 +592,7 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
       meta[u] = ok ? (int)P.obs_slot[o] : 255;
       v[u] = ok ? reinterpret_cast<const double2*>(Vrec + (size_t)o * kVRec)[sub] : make_double2(0.0, 0.0);
     }
-    zreg = tid < 3 * (min(l_end, la + kSyrkStageLm) - la) ? lm_z[3 * (size_t)la + tid] : 0.0;
+    zreg = tid < 3 * (sL[s + 1] - la) ? lm_z[3 * (size_t)la + tid] : 0.0;
   };
   auto clear = [&](double* Wb) {
     for (int e = tid; e < nrow8 * (kSyrkKB / 2); e += 256) {
@@ -600,7 +601,7 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
     }
   };
   auto commit = [&](double* Wb, int s) {
-    const int la = l_begin + s * kSyrkStageLm, o0 = sO[s], o1 = sO[s + 1];
+    const int la = sL[s], o0 = sO[s], o1 = sO[s + 1];
 #pragma unroll
     for (int u = 0; u < kSyrkInFlight; ++u) {
       if ((meta[u] & 255) == 255) continue;   // out of range, or a wide landmark (handled through the item list)
@@ -615,7 +616,7 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
         double* base = Wb + 6 * (m & 255) * kSyrkLD + 3 * (m >> 8);
         base[off0] = w.x; base[off1] = w.y;
       }
-    if (tid < 3 * (min(l_end, la + kSyrkStageLm) - la)) Wb[(6 * ns) * kSyrkLD + tid] = zreg;
+    if (tid < 3 * (sL[s + 1] - la)) Wb[(6 * ns) * kSyrkLD + tid] = zreg;
   };
   __syncthreads();
   prefetch(0); clear(buf0);
@@ -627,7 +628,7 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
     const bool more = s + 1 < nst;
     if (more) { prefetch(s + 1); clear(nxt); }
     __syncthreads();
-    const int nl = min(l_end, l_begin + (s + 1) * kSyrkStageLm) - (l_begin + s * kSyrkStageLm);
+    const int nl = sL[s + 1] - sL[s];
     const int ksteps = (3 * nl + 3) >> 2;
     int ab = 0;
     for (int q = 0; q < kSyrkMaxStrips; ++q) {
@@ -663,6 +664,246 @@ __global__ void __launch_bounds__(256, 2) chunk_syrk_kernel(DeviceProblem P, con
     const int t = I * nt - I * (I - 1) / 2 + (J0 - I);
     for (int u = 0; u < U; ++u, ++ab)
       reinterpret_cast<double2*>(tout + (size_t)(t + u) * 64)[lane] = make_double2(accs[ab][0], accs[ab][1]);
+  }
+}
+
+// ===================================================================================================
+// K1 + K5a + K5b fused ("chunk-major pass"): one CTA per chunk takes its observations from the parameter values to the
+// chunk's partial tiles of the reduced system without a round trip through HBM in between:
+//   stage by stage (<= 16 landmarks, <= 256 observations):
+//     A1  one thread per observation: residual + Jacobian (bit-identical to eval_reproj_pose_kernel: same device function,
+//         pose tables of the chunk's <= 22 poses in shared memory) -> record in shared memory (and, coalesced, to Jrec for
+//         the back-substitution).  If the Jacobian is still valid (rejected step: only the damping changed) the records
+//         are read back instead.
+//     A2  E^T E (6) and E^T r (3) per landmark, summed in observation order
+//     A3  3x3 Cholesky, inverse factor, z = C^T E^T r (one thread per landmark); landmark outputs to global
+//     A4  V = F^T E C per observation straight into the stage's W block in shared memory; the pose's sum F^T F (21) and
+//         sum F^T r (6) advance in registers of a fixed (slot, entry) thread, in landmark order
+//     B   sum W W^T on the FP64 tensor cores (DMMA), as in chunk_syrk_kernel
+//   end: raw tiles, per-(chunk, slot) pose sums and the chunk's cost go out.
+// Removes the V records (144 B/observation written and read back), the second read of the Jacobian records and two
+// kernel boundaries. Deterministic: fixed ownership, fixed orders, no atomics. Used when the shard has chunks and no
+// wide landmark (track longer than the slot table, or a pose seeing a landmark twice); otherwise the three-kernel path.
+// ===================================================================================================
+constexpr int kFuseMaxObs = 256;
+__host__ __device__ inline size_t fused_smem_bytes(int nslots) {
+  const size_t nrow8 = (size_t)(((6 * nslots + 1 + 7) >> 3) * 8);
+  return 8 * (nrow8 * kSyrkLD + (size_t)kFuseMaxObs * kJRec + (size_t)nslots * (kPoseTab + 4) + kEvalSmemCams * BSNLS_CAMERA_STRIDE + 2 * kSyrkStageLm * 9) +
+         2 * (size_t)nslots * kSyrkStageLm + 4 * (size_t)nslots + 64;
+}
+__global__ void __launch_bounds__(256, 2) chunk_fused_kernel(DeviceProblem P, const double* __restrict__ x, const double* __restrict__ tab,
+                                                             double* __restrict__ Jrec, double* __restrict__ lm_minv, double* __restrict__ grad,
+                                                             double* __restrict__ colsq, double* __restrict__ scale, double* __restrict__ lm_z,
+                                                             double* __restrict__ part, double* __restrict__ pose_part, double* __restrict__ cost_part,
+                                                             Options opt, LMState* st, int with_system, int force_load) {
+  extern __shared__ __align__(16) double fsm[];
+  __shared__ int sPlan[8 * kSyrkMaxStrips];
+  __shared__ double sRed[256];
+  if (!gate_run(st)) return;
+  const bool eval = st->need_jacobian && !force_load;
+  if (!with_system && !eval) return;
+  const int c = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
+  const int ns = P.chunk_nslots[c], nrow = 6 * ns + 1, nt = (nrow + 7) >> 3, nrow8 = nt * 8;
+  const int msl = P.chunk_max_slots;
+  double* const Wb = fsm;
+  double* const sJ = Wb + (size_t)(((6 * msl + 1 + 7) >> 3) * 8) * kSyrkLD;
+  double* const sT = sJ + kFuseMaxObs * kJRec;
+  double* const sQ = sT + msl * kPoseTab;
+  double* const sCam = sQ + msl * 4;
+  double* const sLmA = sCam + kEvalSmemCams * BSNLS_CAMERA_STRIDE;   // per landmark: E^T E (6), E^T r (3)
+  double* const sLmB = sLmA + kSyrkStageLm * 9;                      // per landmark: inverse factor (6), z (3)
+  unsigned short* const sAt = reinterpret_cast<unsigned short*>(sLmB + kSyrkStageLm * 9);   // [slot][landmark of the stage] -> observation of the stage
+  unsigned char* const sFlag = reinterpret_cast<unsigned char*>(sAt + msl * kSyrkStageLm);   // per slot: bit 0 q free, bit 1 t free
+  if (tid < 8 * kSyrkMaxStrips) sPlan[tid] = P.syrk_plan[nt * 8 * kSyrkMaxStrips + tid];
+  if (tid < ns) {
+    const int a = P.chunk_pose[c * kChunkSlots + tid];
+    sFlag[tid] = (unsigned char)((P.pose_q_tan[a] >= 0 ? 1 : 0) | (P.pose_t_tan[a] >= 0 ? 2 : 0));
+    if (eval) { const int qo = P.pose_q_off[a]; for (int k = 0; k < 4; ++k) sQ[4 * tid + k] = x[qo + k]; }
+  }
+  if (eval) {
+    for (int e = tid; e < ns * kPoseTab; e += 256) { const int sl = e / kPoseTab; sT[e] = tab[(size_t)P.chunk_pose[c * kChunkSlots + sl] * kPoseTab + (e - sl * kPoseTab)]; }
+    for (int e = tid; e < min(P.num_cams, kEvalSmemCams) * BSNLS_CAMERA_STRIDE; e += 256) sCam[e] = reinterpret_cast<const double*>(P.cams)[e];
+  }
+  const int frag = g * kSyrkLD + tg;
+  double accs[kSyrkMaxTiles][2];
+#pragma unroll
+  for (int i = 0; i < kSyrkMaxTiles; ++i) { accs[i][0] = 0.0; accs[i][1] = 0.0; }
+  // pose sums: item = (slot, entry of 27) -> (i, j) of the packed upper triangle of F^T F, or row i of F^T r
+  double pacc[3] = {0.0, 0.0, 0.0}; int pi[3], pj[3];
+#pragma unroll
+  for (int u = 0; u < 3; ++u) {
+    const int e = (tid + 256 * u) % 27;
+    int i = 0, k = e; if (e < 21) { while (k >= 6 - i) { k -= 6 - i; ++i; } pi[u] = i; pj[u] = i + k; } else { pi[u] = e - 21; pj[u] = -1; }
+  }
+  double cost_acc = 0.0;
+  const int sp0 = P.chunk_stage_ptr[c], nst = P.chunk_stage_ptr[c + 1] - sp0 - 1;
+  __syncthreads();
+  for (int s = 0; s < nst; ++s) {
+    const int la = P.stage_lm[sp0 + s], lb = P.stage_lm[sp0 + s + 1], nlm = lb - la;
+    const int o0 = P.lm_ptr[la], nobs = P.lm_ptr[lb] - o0;
+    // A0: clear W and the slot table of the stage
+    if (with_system)
+      for (int e = tid; e < nrow8 * (kSyrkKB / 2); e += 256) { const int r = e / (kSyrkKB / 2), k2 = e - r * (kSyrkKB / 2); reinterpret_cast<double2*>(Wb + r * kSyrkLD)[k2] = make_double2(0.0, 0.0); }
+    for (int e = tid; e < ns * kSyrkStageLm; e += 256) sAt[e] = 0xFFFF;
+    if (!eval) { const double2* src = reinterpret_cast<const double2*>(Jrec + (size_t)o0 * kJRec); double2* dst = reinterpret_cast<double2*>(sJ); for (int e = tid; e < nobs * 8; e += 256) dst[e] = src[e]; }
+    __syncthreads();
+    // A1: residual + Jacobian of one observation per thread
+    int slot = 0, lmslot = 0;
+    if (tid < nobs) {
+      const int o = o0 + tid, meta = P.obs_slot[o];
+      slot = meta & 255; lmslot = meta >> 8;
+      sAt[slot * kSyrkStageLm + lmslot] = (unsigned short)tid;
+      if (eval) {
+        const int po = P.lm_off[la + lmslot], ci = P.obs_cam[o];
+        const CameraModel cam = ci < kEvalSmemCams ? reinterpret_cast<const CameraModel*>(sCam)[ci] : P.cams[ci];
+        const double2 px = reinterpret_cast<const double2*>(P.obs_pixel)[o];
+        const double pixel[2] = {px.x, px.y};
+        const double Pw[3] = {x[po], x[po + 1], x[po + 2]};
+        double r[2], Jq[6], JP[6];
+        cost_acc += reprojection_evaluate_tab(cam, pixel, sQ + 4 * slot, sT + kPoseTab * slot, Pw, r, Jq, JP);
+        const unsigned char fl = sFlag[slot];
+        if (!(fl & 1)) { for (int k = 0; k < 6; ++k) Jq[k] = 0.0; }
+        double2* out = reinterpret_cast<double2*>(sJ + tid * kJRec);
+        out[0] = make_double2(JP[0], JP[1]); out[1] = make_double2(JP[2], JP[3]); out[2] = make_double2(JP[4], JP[5]);
+        out[3] = make_double2(r[0], r[1]);
+        out[4] = make_double2(Jq[0], Jq[1]); out[5] = make_double2(Jq[2], Jq[3]); out[6] = make_double2(Jq[4], Jq[5]);
+        out[7] = make_double2((fl & 2) ? -1.0 : 0.0, 0.0);
+      }
+    }
+    __syncthreads();
+    if (eval) { const double2* src = reinterpret_cast<const double2*>(sJ); double2* dst = reinterpret_cast<double2*>(Jrec + (size_t)o0 * kJRec); for (int e = tid; e < nobs * 8; e += 256) dst[e] = src[e]; }
+    // A2: normal equations of the stage's landmarks
+    if (tid < kSyrkStageLm * 9) {
+      const int lm = tid / 9, e = tid - 9 * lm;
+      if (lm < nlm) {
+        const int k0 = P.lm_ptr[la + lm] - o0, k1 = P.lm_ptr[la + lm + 1] - o0;
+        double sum = 0.0;
+        if (e < 6) {
+          const int i = e < 3 ? 0 : e < 5 ? 1 : 2, j = e < 3 ? e : e < 5 ? e - 2 : 2;
+          for (int k = k0; k < k1; ++k) { const double* rec = sJ + k * kJRec; sum += rec[i] * rec[j] + rec[3 + i] * rec[3 + j]; }
+        } else {
+          const int i = e - 6;
+          for (int k = k0; k < k1; ++k) { const double* rec = sJ + k * kJRec; sum += rec[i] * rec[6] + rec[3 + i] * rec[7]; }
+        }
+        sLmA[tid] = sum;
+      }
+    }
+    __syncthreads();
+    // A3: one thread per landmark: damping, Cholesky, inverse factor, z; landmark outputs
+    if (tid < nlm) {
+      const int l = la + tid, te = 3 * l;
+      const double* A = sLmA + 9 * tid;
+      const double a00 = A[0], a01 = A[1], a02 = A[2], a11 = A[3], a12 = A[4], a22 = A[5], g0 = A[6], g1 = A[7], g2 = A[8];
+      double s0, s1, s2;
+      if (!st->scale_ready) {
+        s0 = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(a00)) : 1.0; s1 = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(a11)) : 1.0;
+        s2 = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(a22)) : 1.0;
+        scale[te] = s0; scale[te + 1] = s1; scale[te + 2] = s2;
+      } else { s0 = scale[te]; s1 = scale[te + 1]; s2 = scale[te + 2]; }
+      const double radius = st->radius;
+      const double d0 = fmin(fmax(a00 * s0 * s0, opt.min_lm_diagonal), opt.max_lm_diagonal) / (radius * s0 * s0);
+      const double d1 = fmin(fmax(a11 * s1 * s1, opt.min_lm_diagonal), opt.max_lm_diagonal) / (radius * s1 * s1);
+      const double d2 = fmin(fmax(a22 * s2 * s2, opt.min_lm_diagonal), opt.max_lm_diagonal) / (radius * s2 * s2);
+      const double m00 = a00 + d0, m11 = a11 + d1, m22 = a22 + d2;
+      const double l00 = sqrt(m00), l10 = a01 / l00, l20 = a02 / l00;
+      const double t11 = m11 - l10 * l10; const double l11 = sqrt(t11), l21 = (a12 - l20 * l10) / l11;
+      const double t22 = m22 - l20 * l20 - l21 * l21; const double l22 = sqrt(t22);
+      if (!(m00 > 0.0) || !(t11 > 0.0) || !(t22 > 0.0)) { st->lin_fail = 1; }
+      const double i00 = 1.0 / l00, i11 = 1.0 / l11, i22 = 1.0 / l22;
+      const double i10 = -l10 * i00 * i11, i21 = -l21 * i11 * i22, i20 = -(l20 * i00 + l21 * i10) * i22;
+      const double z0 = i00 * g0, z1 = i10 * g0 + i11 * g1, z2 = i20 * g0 + i21 * g1 + i22 * g2;
+      double* B = sLmB + 9 * tid;
+      B[0] = i00; B[1] = i10; B[2] = i11; B[3] = i20; B[4] = i21; B[5] = i22; B[6] = z0; B[7] = z1; B[8] = z2;
+      double* mi = lm_minv + (size_t)l * 6;
+      mi[0] = i00 * i00 + i10 * i10 + i20 * i20; mi[1] = i10 * i11 + i20 * i21; mi[2] = i20 * i22;
+      mi[3] = i11 * i11 + i21 * i21; mi[4] = i21 * i22; mi[5] = i22 * i22;
+      grad[te] = g0; grad[te + 1] = g1; grad[te + 2] = g2;
+      colsq[te] = a00; colsq[te + 1] = a11; colsq[te + 2] = a22;
+      lm_z[te] = z0; lm_z[te + 1] = z1; lm_z[te + 2] = z2;
+    }
+    __syncthreads();
+    // A4: V = (F^T E) C into W; z row; pose sums
+    if (with_system) {
+      if (tid < nobs) {
+        const double* rec = sJ + tid * kJRec; const double* B = sLmB + 9 * lmslot;
+        const double E0[3] = {rec[0], rec[1], rec[2]}, E1[3] = {rec[3], rec[4], rec[5]}, ts = rec[14];
+        const double F0[6] = {rec[8], rec[9], rec[10], ts * E0[0], ts * E0[1], ts * E0[2]}, F1[6] = {rec[11], rec[12], rec[13], ts * E1[0], ts * E1[1], ts * E1[2]};
+        const double i00 = B[0], i10 = B[1], i11 = B[2], i20 = B[3], i21 = B[4], i22 = B[5];
+        double* wrow = Wb + (size_t)(6 * slot) * kSyrkLD + 3 * lmslot;
+#pragma unroll
+        for (int a = 0; a < 6; ++a) {
+          const double w0 = F0[a] * E0[0] + F1[a] * E1[0], w1 = F0[a] * E0[1] + F1[a] * E1[1], w2 = F0[a] * E0[2] + F1[a] * E1[2];
+          wrow[a * kSyrkLD] = w0 * i00; wrow[a * kSyrkLD + 1] = w0 * i10 + w1 * i11; wrow[a * kSyrkLD + 2] = w0 * i20 + w1 * i21 + w2 * i22;
+        }
+      }
+      if (tid < 3 * nlm) Wb[(size_t)(6 * ns) * kSyrkLD + tid] = sLmB[9 * (tid / 3) + 6 + tid % 3];
+    }
+    if (eval) {
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        const int it = tid + 256 * u;
+        if (it >= 27 * ns) break;
+        const unsigned short* at = sAt + (it / 27) * kSyrkStageLm;
+        const int i = pi[u], j = pj[u];
+        double acc = pacc[u];
+        for (int m = 0; m < nlm; ++m) {
+          const int t = at[m];
+          if (t == 0xFFFF) continue;
+          const double* rec = sJ + t * kJRec;
+          // F row 0 = (Fq[0..2], ts E0), row 1 = (Fq[3..5], ts E1)
+          const double ts = rec[14];
+          const double f0i = i < 3 ? rec[8 + i] : ts * rec[i - 3], f1i = i < 3 ? rec[11 + i] : ts * rec[i];
+          if (j >= 0) { const double f0j = j < 3 ? rec[8 + j] : ts * rec[j - 3], f1j = j < 3 ? rec[11 + j] : ts * rec[j]; acc += f0i * f0j + f1i * f1j; }
+          else acc += f0i * rec[6] + f1i * rec[7];
+        }
+        pacc[u] = acc;
+      }
+    }
+    __syncthreads();
+    // B: sum W W^T of the stage on the tensor cores
+    if (with_system) {
+      const int ksteps = (3 * nlm + 3) >> 2;
+      int ab = 0;
+      for (int q = 0; q < kSyrkMaxStrips; ++q) {
+        const int sp = sPlan[warp * kSyrkMaxStrips + q], U = sp >> 16;
+        if (U == 0) break;
+        const double* pa = Wb + 8 * (sp & 255) * kSyrkLD + frag; const double* pb = Wb + 8 * ((sp >> 8) & 255) * kSyrkLD + frag;
+        if (ksteps == kSyrkKB / 4) {
+          switch (U) {
+            case 4: syrk_strip<4, true>(pa, pb, ksteps, accs, ab); break;
+            case 3: syrk_strip<3, true>(pa, pb, ksteps, accs, ab); break;
+            case 2: syrk_strip<2, true>(pa, pb, ksteps, accs, ab); break;
+            default: syrk_strip<1, true>(pa, pb, ksteps, accs, ab); break;
+          }
+        } else {
+          switch (U) {
+            case 4: syrk_strip<4, false>(pa, pb, ksteps, accs, ab); break;
+            case 3: syrk_strip<3, false>(pa, pb, ksteps, accs, ab); break;
+            case 2: syrk_strip<2, false>(pa, pb, ksteps, accs, ab); break;
+            default: syrk_strip<1, false>(pa, pb, ksteps, accs, ab); break;
+          }
+        }
+        ab += U;
+      }
+    }
+    __syncthreads();
+  }
+  if (with_system) {
+    double* tout = part + P.chunk_tile_off[c];
+    int ab = 0;
+    for (int q = 0; q < kSyrkMaxStrips; ++q) {
+      const int sp = sPlan[warp * kSyrkMaxStrips + q], U = sp >> 16, I = sp & 255, J0 = (sp >> 8) & 255;
+      if (U == 0) break;
+      const int t = I * nt - I * (I - 1) / 2 + (J0 - I);
+      for (int u = 0; u < U; ++u, ++ab)
+        reinterpret_cast<double2*>(tout + (size_t)(t + u) * 64)[lane] = make_double2(accs[ab][0], accs[ab][1]);
+    }
+  }
+  if (eval) {
+#pragma unroll
+    for (int u = 0; u < 3; ++u) { const int it = tid + 256 * u; if (it < 27 * ns) pose_part[((size_t)c * kChunkSlots + it / 27) * 27 + it % 27] = pacc[u]; }
+    const double tot = block_sum<256>(cost_acc, sRed);
+    if (tid == 0) cost_part[c] = tot;
   }
 }
 

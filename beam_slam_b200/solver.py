@@ -127,6 +127,12 @@ class Solver:
     def run_schur(self, radius=1e4):
         self._check(self._lib.bsnls_run_schur(self._h, radius))
 
+    def run_pass(self, radius=1e4):
+        """One complete linearisation (residuals, Jacobians, landmark elimination, reduced system); returns the cost."""
+        c = C.c_double()
+        self._check(self._lib.bsnls_run_pass(self._h, radius, C.byref(c)))
+        return c.value
+
     def last_kernel_ms(self):
         a, b = C.c_float(), C.c_float()
         self._check(self._lib.bsnls_last_kernel_ms(self._h, C.byref(a), C.byref(b)))

@@ -236,6 +236,11 @@ int bsnls_trial_step(bsnls_handle* handle, const double* values, double radius, 
 int bsnls_run_eval(bsnls_handle* handle, double* cost);
 /* K5-K6: landmark elimination + reduced-system assembly for the given radius (needs a prior eval). */
 int bsnls_run_schur(bsnls_handle* handle, double radius);
+/* One complete linearisation as an LM iteration performs it: K1-K6 in one go (on large shards the chunk-major fused
+   kernel evaluates the Jacobians, eliminates the landmarks and accumulates the reduced system without writing the
+   intermediate records). cost (optional) = cost at the current values. bsnls_last_kernel_ms then reports the whole pass as
+   eval_ms (schur_ms = 0). */
+int bsnls_run_pass(bsnls_handle* handle, double radius, double* cost);
 /* milliseconds spent in the last bsnls_run_eval / bsnls_run_schur, by CUDA events on the handle's stream */
 int bsnls_last_kernel_ms(bsnls_handle* handle, float* eval_ms, float* schur_ms);
 /* per-kernel split of the last run_eval + run_schur, milliseconds:

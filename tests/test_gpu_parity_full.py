@@ -164,3 +164,22 @@ def test_simple_two_state_graph_reaches_the_reference_optimum():
     assert len(its) == len(ito)
     for a, b in zip(its, ito):
         assert abs(a.cost - b.cost) <= 1e-9 * max(abs(b.cost), 1e-30) + 1e-25
+
+
+def test_chunk_major_fused_pass_matches_oracle(monkeypatch):
+    """BSNLS_FUSED=1 selects chunk_fused_kernel (Jacobians, landmark elimination and the chunk tiles of the reduced system
+    in one kernel, V records never leave the chip). Same arithmetic per observation, different summation orders: held to
+    the same tolerances as the default three-kernel path."""
+    monkeypatch.setenv("BSNLS_FUSED", "1")
+    g = host.HashGraph.synthetic(3)          # 250 k observations: large enough for the chunk path
+    p, opts = g.flatten(), host.HashGraph.synthetic_options(3)
+    s = Solver(opts)
+    s.set_problem(p)
+    cost, res, grad = s.evaluate()
+    co, ro, go = orc.evaluate(p)
+    assert abs(cost - co) <= 1e-12 * co and _rel(res, ro) < 1e-15 and _rel(grad, go) < 1e-10
+    S, rhs = s.reduced_system(1e4)
+    So, rhso = orc.reduced_system(p, 1e4, opts)
+    assert _rel(S, So) < 1e-9 and _rel(rhs, rhso) < 1e-9
+    s.close()
+    assert _teacher_forced(p, opts) >= 3
