@@ -451,15 +451,7 @@ __global__ void __launch_bounds__(128) gf_grad_kernel(DeviceProblem P, const dou
   if (!st->scale_ready) scale[t] = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(cs)) : 1.0;   // Jacobi scale, frozen at iteration 0
 }
 
-// Jacobi scale of the f-blocks (iteration 0) and LM diagonal D_f^2; also gradient norms:
-// |x - (x (+) -g)| per active block (TrustRegionMinimizer::EvaluateGradientAndJacobian).
-__global__ void __launch_bounds__(256) fscale_kernel(DeviceProblem P, const double* __restrict__ colsq,
-                                                     double* __restrict__ scale, Options opt, const LMState* st) {
-  if (!gate_jac(st) || st->scale_ready) return;
-  const int j = blockIdx.x * 256 + threadIdx.x;
-  if (j >= P.nf_dim) return;
-  scale[P.ne_dim + j] = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(colsq[P.ne_dim + j])) : 1.0;
-}
+// gradient norms: |x - (x (+) -g)| per active block (TrustRegionMinimizer::EvaluateGradientAndJacobian).
 __device__ __forceinline__ void quat_plus(const double* x, const double* d, double* out) {
   double qd[4]; AngleAxisToQuaternion<double>(d, qd); QuaternionProduct<double>(x, qd, out);
 }

@@ -28,7 +28,9 @@ struct NcclApi {
   bool Load() {
     if (lib) return true;
     const char* env = std::getenv("BSNLS_NCCL_LIB");
-    const char* names[] = {env, "libnccl.so.2", "/opt/prime-rl/.venv/lib/python3.12/site-packages/nvidia/nccl/lib/libnccl.so.2", "libnccl.so"};
+    // BSNLS_NCCL_LIB overrides; otherwise the soname: resolved to the instance already mapped into the process (the one
+    // torch.distributed loaded) or through the loader's search path
+    const char* names[] = {env, "libnccl.so.2", "libnccl.so"};
     for (const char* n : names) {
       if (!n) continue;
       lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);

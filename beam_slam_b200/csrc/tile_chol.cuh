@@ -110,8 +110,12 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_be
   double* sPan = sLi + 16;                  // the panel: L(r, 4 jb + c) at sPan[((r & 3) * 16 + (r >> 2)) * 4 + c]: the rows 4 ty + i of
                                             // the 16 block rows of a warp are adjacent (no bank conflicts)
   double* sWrow = sPan + kTS * 4;           // final rows 4 jb.. of W: sWrow[i * 64 + c]
-  __shared__ int failed;
-  if (!gate_run(st) || st->lin_fail) return;   // uniform per CTA; a failing column only ever stores garbage that nobody uses
+  __shared__ int failed, sGate;
+  // another CTA of this launch may set lin_fail while this one starts: latch the gate once per CTA so that all of its
+  // warps take the same branch (a failing column only ever stores garbage that nobody uses)
+  if (threadIdx.x == 0) sGate = (!gate_run(st) || st->lin_fail) ? 1 : 0;
+  __syncthreads();
+  if (sGate) return;
   // a warp holds two block columns (tx) and all block rows (ty): at any step it is either left of the pivot column (W
   // updates only) or right of it (A updates only), so the two roles do not serialise inside a warp
   const int tid = threadIdx.x, tx = tid >> 4, ty = tid & 15;

@@ -56,6 +56,22 @@ def shard_problem(problem, rank, world):
                             problem.block_values, problem.cameras, groups), (lo, hi)
 
 
+def _point_at_loaded_nccl():
+    """The library resolves NCCL by soname at run time; tell it (BSNLS_NCCL_LIB) which instance this process already
+    mapped — the one torch.distributed uses — so that both share one NCCL."""
+    import os
+    if os.environ.get("BSNLS_NCCL_LIB"):
+        return
+    try:
+        with open("/proc/self/maps") as f:
+            for line in f:
+                if "libnccl.so" in line:
+                    os.environ["BSNLS_NCCL_LIB"] = line.split()[-1]
+                    return
+    except OSError:
+        pass
+
+
 def create_sharded_solver(options=None):
     """One Solver per rank of an initialised torch.distributed job (NCCL or gloo for the id exchange)."""
     import torch
@@ -65,6 +81,7 @@ def create_sharded_solver(options=None):
     if world == 1:
         return Solver(options)
     lib = cabi.load_library()
+    _point_at_loaded_nccl()
     buf = (C.c_char * 128)()
     if rank == 0 and lib.bsnls_nccl_unique_id(buf) != 0:
         raise RuntimeError(lib.bsnls_last_error(None).decode())
