@@ -110,7 +110,8 @@ struct bsnls_handle {
   int solves_on_structure = 0;   // graphs are captured from the second solve of one structure on: capture + instantiation cost more than one solve's launches
   float last_eval_ms = 0, last_schur_ms = 0;
   int rank = 0, world = 1; NcclComm comm = nullptr;
-  int lm_lo = 0, lm_hi = 0, ne_global = 0, nobs_global = 0, nb_act_e = 0; DevMem d_owned, d_flag;
+  int ne_global = 0, nobs_global = 0, nb_act_e = 0; DevMem d_owned, d_flag;
+  std::vector<int> shard_e;   // this rank's landmarks as positions in the elimination order (bsnls_get_shard)
 
   // host-side structure
   int num_blocks = 0; int64_t num_values = 0;
@@ -127,6 +128,7 @@ struct bsnls_handle {
   DevMem d_tc_pan_k, d_tc_pan_x, d_tc_upd_ptr, d_tc_upd_dst, d_tc_upd_a, d_tc_upd_b, d_tc_fw_ptr, d_tc_fw_row, d_tc_fw_tail, d_tc_fw_src, d_tc_fw_k, d_tc_lev_cols, d_tc_bw_ptr, d_tc_bw_col, d_tc_bw_tail, d_tc_bw_src, d_tc_bw_i, d_tc_roots; int tc_nroots = 0;
   long long nlow = 0; DevMem d_low_slot, d_low_slot_t, d_xsend, d_xrecv;   // sharded solve: lower-triangular blocks of S, packed exchange buffers
   int chunk_max_slots = 1; DevMem d_syrk_plan, d_chunk_tile_off, d_pp_toff, d_pp_info;
+  int n_local_pairs = 0; DevMem d_local_pairs;   // pairs with contributions from this rank's landmarks
   bool fused = false; DevMem d_chunk_pose, d_chunk_stage_ptr, d_stage_lm, d_pc_ptr, d_pc_idx;   // chunk-major fused pass
   int nchunks = 0; DevMem d_obs_slot, d_chunk_end, d_chunk_begin, d_chunk_nslots, d_pp_ptr, d_part;
   bool sparse = false, pcg = false; int64_t nnzb = 0; std::vector<int> bsr_rowptr, bsr_col; int pcg_grid = 0;
@@ -330,12 +332,12 @@ int EnqueueExchange(bsnls_handle* h, bool with_system) {
   // only read by the (equally gated) controller.
   if (h->sparse) {   // one packed buffer, one collective (lower-triangular blocks of S only)
     const ExchangeLayout X{h->nlow * 9, P.nf_dim, h->world, h->rank, RED_NUM, kRedLocalMax, h->d_low_slot.as<int>(), h->d_low_slot_t.as<int>()};
-    const long long total = X.nS + 3LL * P.nf_dim + RED_NUM + h->world, first = with_system ? 0 : X.nS + P.nf_dim;
+    const long long total = X.nS + 3LL * P.nf_dim + RED_NUM + h->world + 1, first = with_system ? 0 : X.nS + P.nf_dim;
     const unsigned grid = (unsigned)((total - first + 255) / 256);
-    LAUNCH(h, pack_exchange_kernel, grid, 256, X, first, h->d_S.as<double>(), h->d_rhs.as<double>(), h->d_gradL.as<double>(), h->d_colsqL.as<double>(), h->d_red.as<double>(), h->d_xsend.as<double>());
+    LAUNCH(h, pack_exchange_kernel, grid, 256, X, first, h->d_S.as<double>(), h->d_rhs.as<double>(), h->d_gradL.as<double>(), h->d_colsqL.as<double>(), h->d_red.as<double>(), h->d_state.as<LMState>(), h->d_xsend.as<double>());
     const int rc1 = Nccl().AllReduce(h->d_xsend.as<double>() + first, h->d_xrecv.as<double>() + first, (size_t)(total - first), kNcclFloat64, kNcclSum, h->comm, h->stream);
     if (rc1 != kNcclSuccess) return h->fail(BSNLS_ERR_CUDA, "ncclAllReduce(exchange): %s", Nccl().GetErrorString(rc1));
-    LAUNCH(h, unpack_exchange_kernel, grid, 256, X, first, h->d_xrecv.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), h->d_gradS.as<double>(), h->d_colsqS.as<double>(), h->d_red.as<double>());
+    LAUNCH(h, unpack_exchange_kernel, grid, 256, X, first, h->d_xrecv.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), h->d_gradS.as<double>(), h->d_colsqS.as<double>(), h->d_red.as<double>(), h->d_state.as<LMState>());
     return BSNLS_OK;
   }
   Nccl().GroupStart();
@@ -382,13 +384,18 @@ void EnqueueAssembleLocal(bsnls_handle* h) {  // phase D1, this rank's share: S 
   if (h->nchunks && !h->fused) {
     LAUNCH_SMEM(h, chunk_syrk_kernel, h->nchunks, 256, syrk_smem_bytes(h->chunk_max_slots), P, h->d_Vrec.as<double>(), h->d_lmz.as<double>(), h->d_part.as<double>(), st);
   }
-  if (h->npairs && h->nchunks) LAUNCH(h, pair_reduce_kernel, BlocksFor(h->npairs, 4), 144, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_lmz.as<double>(), h->d_poseH.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
-  else if (h->npairs) LAUNCH(h, pair_kernel, BlocksFor(h->npairs, 4), 128, P, h->d_Vrec.as<double>(), h->d_lmz.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), st);
+  // sharded solve: only the pairs this rank's landmarks touch (the rest of S keeps the zeros of the clear)
+  const int* plist = h->world > 1 ? h->d_local_pairs.as<int>() : nullptr; const int npl = h->world > 1 ? h->n_local_pairs : h->npairs;
+  if (npl && h->nchunks) LAUNCH(h, pair_reduce_kernel, BlocksFor(npl, 4), 144, P, h->d_Vrec.as<double>(), h->d_part.as<double>(), h->d_lmz.as<double>(), h->d_poseH.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), plist, npl, st);
+  else if (npl) LAUNCH(h, pair_kernel, BlocksFor(npl, 4), 128, P, h->d_Vrec.as<double>(), h->d_lmz.as<double>(), h->d_poseH.as<double>(), h->d_grad.as<double>(), h->d_S.as<double>(), h->d_rhs.as<double>(), plist, npl, st);
+  // sharded solve: the rows of the generic factors go into rank 0's share BEFORE the exchange (the sum over ranks then
+  // holds them once), which takes their kernel off the critical path behind the collective
+  if (h->world > 1 && h->rank == 0 && h->ngdest) LAUNCH(h, gf_schur_kernel, BlocksFor(h->ngdest, 16), 144, P, h->d_gfJ.as<double>(), h->d_S.as<double>(), st);
   MARK(h, 7);
 }
-void EnqueueAssembleFinish(bsnls_handle* h, const Options& o) {  // generic-factor rows of S, gradient into rhs, damping
+void EnqueueAssembleFinish(bsnls_handle* h, const Options& o) {  // generic-factor rows of S (single GPU), gradient into rhs, damping
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
-  if (h->ngdest) LAUNCH(h, gf_schur_kernel, BlocksFor(h->ngdest, 16), 144, P, h->d_gfJ.as<double>(), h->d_S.as<double>(), st);
+  if (h->ngdest && h->world == 1) LAUNCH(h, gf_schur_kernel, BlocksFor(h->ngdest, 16), 144, P, h->d_gfJ.as<double>(), h->d_S.as<double>(), st);
   LAUNCH(h, finish_system_kernel, BlocksFor(P.nf_dim, 256), 256, P, h->d_grad.as<double>(), h->d_colsq.as<double>(), h->d_scale.as<double>(),
          h->d_is_pose.as<unsigned char>(), h->d_S.as<double>(), h->d_rhs.as<double>(), o, st);
   MARK(h, 8);
@@ -680,7 +687,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     if (pr->block_group[b] == 0) { epos[b] = (int)h->eblocks.size(); h->eblocks.push_back(b); }
     else { fpos[b] = (int)h->fblocks.size(); h->fblocks.push_back(b); }
   }
-  const int ne_g = (int)h->eblocks.size();   // eliminated blocks of the whole graph; this rank keeps [lm_lo, lm_hi)
+  const int ne_g = (int)h->eblocks.size();   // eliminated blocks of the whole graph; this rank keeps the set `mine` of them
   h->ne_global = ne_g; h->nf = (int)h->fblocks.size();
   const int nf_dim = 3 * h->nf;
   if (nf_dim == 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "no non-landmark parameter blocks to solve for");
@@ -714,13 +721,6 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   for (int e = 0; e < ne_g; ++e) { if (lm_count[e + 1] == 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "group-0 block without reprojection factors"); lm_count[e + 1] += lm_count[e]; }
   std::vector<int> lm_ptr = lm_count;
   { std::vector<int> cur(lm_ptr.begin(), lm_ptr.end() - 1); for (int i = 0; i < nobs; ++i) order[cur[obs_lm[i]]++] = i; }  // stable
-  // ---- landmark shard of this rank: contiguous range in elimination order, balanced by observation count ----
-  int lo = 0, hi = ne_g;
-  bsnls_shard_range(lm_ptr.data(), ne_g, h->rank, h->world, &lo, &hi);
-  h->lm_lo = lo; h->lm_hi = hi; h->ne = hi - lo;
-  const int ne_dim = 3 * h->ne;
-  const int nobs_local = lm_ptr[hi] - lm_ptr[lo];
-  h->nobs = nobs_local;
   std::vector<int> g_pose(nobs);   // pose of every observation of the graph, landmark-sorted (the pair pattern is global)
   for (int k = 0; k < nobs; ++k) g_pose[k] = obs_pose[order[k]];
 
@@ -776,17 +776,33 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       for (int v : comp2) pose_rank[v] = next_rank++;
     }
   }
-  // ---- internal landmark order of this shard: by the earliest pose that sees the landmark (keeps chunks local) ----
-  std::vector<int> lperm(h->ne);                   // new position -> position inside [lo, hi)
+  // ---- locality order of the landmarks: by the earliest (then the latest) pose that sees them, poses ranked along the
+  // trajectory (breadth-first order above). Consecutive landmarks then share poses, which keeps chunks tight; and the
+  // shard of a rank is a contiguous range of THIS order balanced by observation count, so a rank touches the poses of
+  // one stretch of the trajectory (full Jacobian-pass CTAs, few pair blocks) instead of every pose of the graph. ----
+  std::vector<int> mine;                           // this rank's landmarks: positions in the elimination order, in locality order
+  std::vector<char> is_mine(ne_g, 0);
   {
-    std::vector<std::pair<int, int>> key(h->ne);
-    for (int e = 0; e < h->ne; ++e) {
+    std::vector<std::pair<int, int>> key(ne_g);
+    std::vector<int> gl(ne_g);
+    for (int e = 0; e < ne_g; ++e) {
       int mn = 1 << 30, mx = -1;
-      for (int k = lm_ptr[lo + e]; k < lm_ptr[lo + e + 1]; ++k) { mn = std::min(mn, pose_rank[g_pose[k]]); mx = std::max(mx, pose_rank[g_pose[k]]); }
-      key[e] = {mn, mx}; lperm[e] = e;
+      for (int k = lm_ptr[e]; k < lm_ptr[e + 1]; ++k) { mn = std::min(mn, pose_rank[g_pose[k]]); mx = std::max(mx, pose_rank[g_pose[k]]); }
+      key[e] = {mn, mx}; gl[e] = e;
     }
-    std::stable_sort(lperm.begin(), lperm.end(), [&](int x, int y2) { return key[x] < key[y2]; });
+    std::stable_sort(gl.begin(), gl.end(), [&](int x, int y2) { return key[x] < key[y2]; });
+    std::vector<int> prefix(ne_g + 1, 0);
+    for (int q = 0; q < ne_g; ++q) prefix[q + 1] = prefix[q] + (lm_ptr[gl[q] + 1] - lm_ptr[gl[q]]);
+    int lo = 0, hi = ne_g;
+    bsnls_shard_range(prefix.data(), ne_g, h->rank, h->world, &lo, &hi);
+    mine.assign(gl.begin() + lo, gl.begin() + hi);
+    for (int e : mine) is_mine[e] = 1;
+    h->nobs = prefix[hi] - prefix[lo];
   }
+  h->ne = (int)mine.size();
+  h->shard_e.assign(mine.begin(), mine.end());
+  const int ne_dim = 3 * h->ne;
+  const int nobs_local = h->nobs;
   // ---- internal order of the f-blocks. The API order (h->fblocks, program order) keeps the two blocks of a pose far
   // apart, which makes the reduced system's envelope nearly full. For the tile-sparse factorisation the blocks are
   // renumbered with reverse Cuthill-McKee on the block graph (pose pairs + generic-factor cliques): a trajectory becomes
@@ -870,10 +886,10 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   phase("pose / f-block ordering");
   h->blk_tan.assign(nb, -1);
   for (int b = 0; b < nb; ++b) if (fpos[b] >= 0) h->blk_tan[b] = ne_dim + 3 * fpos[b];
-  for (int e = 0; e < h->ne; ++e) h->blk_tan[h->eblocks[lo + lperm[e]]] = 3 * e;
+  for (int e = 0; e < h->ne; ++e) h->blk_tan[h->eblocks[mine[e]]] = 3 * e;
   // active list: local landmarks, padded to a CTA boundary, then the (replicated) f-blocks
   h->active_blocks.clear();
-  for (int e = 0; e < h->ne; ++e) h->active_blocks.push_back(h->eblocks[lo + lperm[e]]);
+  for (int e = 0; e < h->ne; ++e) h->active_blocks.push_back(h->eblocks[mine[e]]);
   while (h->active_blocks.size() % 256) h->active_blocks.push_back(-1);
   h->nb_act_e = (int)h->active_blocks.size() / 256;
   for (int b : h->fblocks) h->active_blocks.push_back(b);
@@ -882,7 +898,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   {
     int kl = 0;
     for (int e = 0; e < h->ne; ++e) {
-      const int ge = lo + lperm[e];
+      const int ge = mine[e];
       lm_off[e] = h->blk_off[h->eblocks[ge]];
       for (int k = lm_ptr[ge]; k < lm_ptr[ge + 1]; ++k, ++kl) {
         const int i = order[k]; inv_order[i] = kl;
@@ -1001,7 +1017,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   }
   phase("chunks");
   // ---- per pair: partial blocks produced by the chunks, and items of the wide landmarks ----
-  std::vector<int> pair_ptr(h->npairs + 1, 0), item_i, item_j, pp_ptr(h->npairs + 1, 0);
+  std::vector<int> pair_ptr(h->npairs + 1, 0), item_i, item_j, pp_ptr(h->npairs + 1, 0), local_pairs;
   std::vector<long long> pp_toff; std::vector<int> pp_info;
   {
     std::vector<int> cnt(h->npairs, 0), pcnt(h->npairs, 0);
@@ -1044,6 +1060,9 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       }
     }
     h->nitems = nitems;
+    local_pairs.clear();
+    for (int k = 0; k < h->npairs; ++k) if (pair_ptr[k + 1] > pair_ptr[k] || pp_ptr[k + 1] > pp_ptr[k]) local_pairs.push_back(k);
+    h->n_local_pairs = (int)local_pairs.size();
     if (std::getenv("BSNLS_DEBUG")) {
       int mx = 0, mxc = 0; long long tot = 0; for (int k = 0; k < h->npairs; ++k) { mx = std::max(mx, pp_ptr[k + 1] - pp_ptr[k]); tot += pp_ptr[k + 1] - pp_ptr[k]; }
       for (int c = 0; c < h->nchunks; ++c) mxc = std::max(mxc, chunk_end[c] - chunk_begin[c]);
@@ -1202,7 +1221,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_pair_a, h->pair_a, s)); CK(upload(h->d_pair_b, h->pair_b, s)); CK(upload(h->d_pair_ptr, pair_ptr, s));
   CK(upload(h->d_item_i, item_i, s)); CK(upload(h->d_item_j, item_j, s));
   CK(upload(h->d_obs_slot, obs_slot, s)); CK(upload(h->d_chunk_begin, chunk_begin, s)); CK(upload(h->d_chunk_end, chunk_end, s)); CK(upload(h->d_chunk_nslots, chunk_nslots, s));
-  CK(upload(h->d_pp_ptr, pp_ptr, s));
+  CK(upload(h->d_pp_ptr, pp_ptr, s)); CK(upload(h->d_local_pairs, local_pairs, s));
   CK(upload(h->d_chunk_pose, chunk_pose, s)); CK(upload(h->d_chunk_stage_ptr, chunk_stage_ptr, s)); CK(upload(h->d_stage_lm, stage_lm, s));
   CK(upload(h->d_pc_ptr, pc_ptr, s)); CK(upload(h->d_pc_idx, pc_idx, s));
   { std::vector<int> plan((kSyrkMaxNt + 1) * 8 * kSyrkMaxStrips); syrk_build_plan(plan.data()); CK(upload(h->d_syrk_plan, plan, s)); }
@@ -1213,7 +1232,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   h->nlow = (long long)low_slot.size();
   if (h->world > 1 && h->sparse) {
     CK(upload(h->d_low_slot, low_slot, s)); CK(upload(h->d_low_slot_t, low_slot_t, s));
-    const size_t xn = 9 * (size_t)h->nlow + 3 * (size_t)nf_dim + RED_NUM + h->world;
+    const size_t xn = 9 * (size_t)h->nlow + 3 * (size_t)nf_dim + RED_NUM + h->world + 1;
     CK(h->d_xsend.alloc(sizeof(double) * xn)); CK(h->d_xrecv.alloc(sizeof(double) * xn));
   }
   CK(upload(h->d_gd_fac, gd_fac, s)); CK(upload(h->d_gd_bi, gd_bi, s)); CK(upload(h->d_gd_bj, gd_bj, s)); CK(upload(h->d_is_pose, is_pose, s));
@@ -1221,7 +1240,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_pair_slot, pair_slot, s)); CK(upload(h->d_gd_slot, gd_slot, s));
   { // ownership of parameter entries for the final gather of the sharded solve
     std::vector<unsigned char> owned((size_t)off, h->rank == 0 ? 1 : 0);
-    for (int b = 0; b < nb; ++b) if (epos[b] >= 0) { const unsigned char mine = (epos[b] >= lo && epos[b] < hi) ? 1 : 0; for (int k = 0; k < h->blk_size[b]; ++k) owned[h->blk_off[b] + k] = mine; }
+    for (int b = 0; b < nb; ++b) if (epos[b] >= 0) { const unsigned char own = is_mine[epos[b]] ? 1 : 0; for (int k = 0; k < h->blk_size[b]; ++k) owned[h->blk_off[b] + k] = own; }
     CK(upload(h->d_owned, owned, s));
   }
   phase("staging of uploads");
@@ -1849,6 +1868,14 @@ int bsnls_shard_range(const int32_t* lm_ptr, int32_t num_landmarks, int32_t rank
     return (int)(std::lower_bound(lm_ptr, lm_ptr + num_landmarks + 1, (int32_t)target) - lm_ptr);
   };
   *lo = std::min<int>(num_landmarks, cut(rank)); *hi = std::max<int>(*lo, std::min<int>(num_landmarks, cut(rank + 1)));
+  return BSNLS_OK;
+}
+
+int bsnls_get_shard(bsnls_handle* h, int32_t* e_positions, int32_t* count) {
+  if (!h || !count) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "no problem");
+  if (e_positions) { if (*count < (int)h->shard_e.size()) return h->fail(BSNLS_ERR_INVALID, "buffer too small"); std::memcpy(e_positions, h->shard_e.data(), sizeof(int) * h->shard_e.size()); }
+  *count = (int32_t)h->shard_e.size();
   return BSNLS_OK;
 }
 

@@ -913,10 +913,11 @@ __device__ __forceinline__ void store_sub3(double* S, int ld, int rt, int ct, co
 __global__ void __launch_bounds__(128) pair_kernel(DeviceProblem P, const double* __restrict__ Vrec,
                                                    const double* __restrict__ lm_z,
                                                    const double* __restrict__ pose_H, const double* __restrict__ grad,
-                                                   double* __restrict__ S, double* __restrict__ rhs, const LMState* st) {
+                                                   double* __restrict__ S, double* __restrict__ rhs, const int* __restrict__ pair_list, int num_list, const LMState* st) {
   if (!gate_run(st)) return;
-  const int pb = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (pb >= P.num_pairs) return;
+  const int idx = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (idx >= num_list) return;
+  const int pb = pair_list ? pair_list[idx] : idx;
   const int a = P.pair_a[pb], b = P.pair_b[pb];
   double acc[36], cacc[6];
 #pragma unroll
@@ -980,13 +981,15 @@ __global__ void __launch_bounds__(128) pair_kernel(DeviceProblem P, const double
 // chunk partials of its element in list order (coalesced: the 36 elements of a partial block are contiguous), adds the
 // contributions of wide landmarks from the item list, subtracts from sum F^T F on the diagonal blocks and writes
 // S (dense lower triangle or 3x3 block-sparse) and the reduced right-hand side. 4 pairs per 144-thread CTA.
+// pair_list (optional): the pairs this rank's landmarks contribute to (sharded solve); the others keep their zeros.
 __global__ void __launch_bounds__(144) pair_reduce_kernel(DeviceProblem P, const double* __restrict__ Vrec,
                                                           const double* __restrict__ part, const double* __restrict__ lm_z,
                                                           const double* __restrict__ pose_H, double* __restrict__ S,
-                                                          double* __restrict__ rhs, const LMState* st) {
+                                                          double* __restrict__ rhs, const int* __restrict__ pair_list, int num_list, const LMState* st) {
   if (!gate_run(st)) return;
-  const int pb = blockIdx.x * 4 + threadIdx.x / 36, e = threadIdx.x % 36;
-  if (pb >= P.num_pairs) return;
+  const int idx = blockIdx.x * 4 + threadIdx.x / 36, e = threadIdx.x % 36;
+  if (idx >= num_list) return;
+  const int pb = pair_list ? pair_list[idx] : idx;
   const int a = P.pair_a[pb], b = P.pair_b[pb];
   const int i = e / 6, j = e - 6 * i;
   double acc = 0.0, cacc = 0.0;
@@ -1034,16 +1037,17 @@ __global__ void __launch_bounds__(144) pair_reduce_kernel(DeviceProblem P, const
 
 // Sharded solve: everything a pass exchanges travels in ONE all-reduce (sum) of a packed buffer:
 //   [ lower-triangular blocks of the (symmetric) block-sparse S | rhs | pose gradient | pose column norms |
-//     rank-local scalar sums | one slot per rank for the rank-local max ]
+//     rank-local scalar sums | one slot per rank for the rank-local max | number of ranks whose elimination failed ]
 // pack gathers it (the segments before `first` are left out in a Jacobian-only pass), unpack scatters the sums: S blocks
 // to the block and its transpose, the max as the maximum over the per-rank slots.
 struct ExchangeLayout { long long nS; int nf_dim, world, rank, num_sums, max_slot; const int* low_slot; const int* low_slot_t; };
 __global__ void __launch_bounds__(256) pack_exchange_kernel(ExchangeLayout X, long long first, const double* __restrict__ S, const double* __restrict__ rhs,
                                                             const double* __restrict__ gradL, const double* __restrict__ colsqL, const double* __restrict__ red,
-                                                            double* __restrict__ out) {
+                                                            const LMState* st, double* __restrict__ out) {
   const long long e = first + (long long)blockIdx.x * 256 + threadIdx.x;
   const long long o1 = X.nS + X.nf_dim, o2 = o1 + X.nf_dim, o3 = o2 + X.nf_dim, o4 = o3 + X.num_sums, o5 = o4 + X.world;
-  if (e >= o5) return;
+  if (e > o5) return;
+  if (e == o5) { out[e] = st->lin_fail ? 1.0 : 0.0; return; }   // a failed landmark elimination on one rank fails the step on all of them
   double v;
   if (e < X.nS) v = S[(size_t)X.low_slot[e / 9] * 9 + e % 9];
   else if (e < o1) v = rhs[e - X.nS];
@@ -1055,10 +1059,11 @@ __global__ void __launch_bounds__(256) pack_exchange_kernel(ExchangeLayout X, lo
 }
 __global__ void __launch_bounds__(256) unpack_exchange_kernel(ExchangeLayout X, long long first, const double* __restrict__ in, double* __restrict__ S,
                                                               double* __restrict__ rhs, double* __restrict__ gradS, double* __restrict__ colsqS,
-                                                              double* __restrict__ red) {
+                                                              double* __restrict__ red, LMState* st) {
   const long long e = first + (long long)blockIdx.x * 256 + threadIdx.x;
   const long long o1 = X.nS + X.nf_dim, o2 = o1 + X.nf_dim, o3 = o2 + X.nf_dim, o4 = o3 + X.num_sums, o5 = o4 + X.world;
-  if (e >= o5) return;
+  if (e > o5) return;
+  if (e == o5) { if (in[e] > 0.0) st->lin_fail = 1; return; }
   const double v = in[e];
   if (e < X.nS) {
     const int i = (int)(e / 9), w = (int)(e % 9);

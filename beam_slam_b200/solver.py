@@ -85,6 +85,14 @@ class Solver:
         self._check(self._lib.bsnls_get_ordering(self._h, e.ctypes.data_as(_pi32), C.byref(ne), f.ctypes.data_as(_pi32), C.byref(nf)))
         return e[:ne.value].copy(), f[:nf.value].copy()
 
+    def shard(self):
+        """Positions (in the elimination order) of the landmarks this rank keeps."""
+        n = C.c_int32(0)
+        self._check(self._lib.bsnls_get_shard(self._h, None, C.byref(n)))
+        out = np.zeros(n.value, np.int32)
+        self._check(self._lib.bsnls_get_shard(self._h, out.ctypes.data_as(_pi32), C.byref(n)))
+        return out
+
     def reduced_pattern(self):
         n = C.c_int64(0)
         self._check(self._lib.bsnls_get_reduced_pattern(self._h, None, None, C.byref(n)))

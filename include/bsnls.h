@@ -272,10 +272,14 @@ int bsnls_reprojection_cost_noalloc(const double* d_values, const int32_t* d_q_o
                                     char* error_message, int32_t error_capacity);
 
 /* ---- multi-GPU: landmark-sharded solve, one process per GPU ---- */
-/* Partition used by the sharded solve: rank r keeps the landmarks [lo, hi) of the elimination order, chosen so that
-   every rank holds about the same number of observations (lm_ptr: prefix sums of observations per landmark,
-   num_landmarks + 1 entries). Host-only helper, no device needed. */
+/* Balanced cut of an ordered landmark list: rank r gets the entries [lo, hi), chosen so that every rank holds about the
+   same number of observations (lm_ptr: prefix sums of observations per landmark in that order, num_landmarks + 1
+   entries). Host-only helper, no device needed. The sharded solve applies it to the landmarks in LOCALITY order (by the
+   earliest pose along the trajectory that observes them), so that a rank works on one stretch of the trajectory. */
 int bsnls_shard_range(const int32_t* lm_ptr, int32_t num_landmarks, int32_t rank, int32_t world_size, int32_t* lo, int32_t* hi);
+/* The landmarks this rank keeps after bsnls_set_problem: positions in the elimination order of bsnls_get_ordering
+   (all of them on a single GPU). Pass NULL to query the count. The shards of all ranks partition the e-blocks. */
+int bsnls_get_shard(bsnls_handle* handle, int32_t* e_positions, int32_t* count);
 /* 128-byte NCCL unique id, generated on rank 0 and distributed by the caller (torch.distributed). */
 int bsnls_nccl_unique_id(char id[128]);
 /* Collective over all ranks. Every rank then calls bsnls_set_problem with the SAME full problem; the

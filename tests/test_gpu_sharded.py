@@ -35,7 +35,11 @@ def _worker(rank, world, port, cfg, scale, linear_solver, out):
     S, rhs = s.reduced_system(1e4)
     summ, its = s.solve()
     x = s.get_values()
+    shards = [None] * world
+    dist.all_gather_object(shards, s.shard().tolist())
     if rank == 0:
+        e_blocks, _ = s.ordering()
+        out["partition"] = (sorted(sum(shards, [])) == list(range(len(e_blocks))), [len(v) for v in shards])
         ref = Solver(opts)
         ref.set_problem(p)
         S1, rhs1 = ref.reduced_system(1e4)
@@ -53,7 +57,7 @@ def _worker(rank, world, port, cfg, scale, linear_solver, out):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("cfg,scale,ls", [(3, 0.05, 0), (3, 0.05, 1)])
+@pytest.mark.parametrize("cfg,scale,ls", [(3, 0.05, 0), (3, 0.05, 1), (4, 0.12, 0)])   # the last one is large enough for the on-chip chunk path
 def test_sharded_solve_matches_single_gpu(cfg, scale, ls):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
@@ -61,6 +65,7 @@ def test_sharded_solve_matches_single_gpu(cfg, scale, ls):
     world = 2
     out = mp.Manager().dict()
     mp.spawn(_worker, args=(world, _free_port(), cfg, scale, ls, out), nprocs=world, join=True)
+    assert out["partition"][0] and min(out["partition"][1]) > 0   # the shards partition the landmarks (locality order, balanced by observations)
     assert out["S"] < 1e-12 and out["rhs"] < 1e-12           # same blocks, different summation split
     assert out["n"][0] == out["n"][1] and out["term"][0] == out["term"][1]
     assert out["cost"] < 1e-9 and out["final"] < 1e-9
