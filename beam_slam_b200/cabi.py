@@ -189,6 +189,8 @@ def load_library():
     lib.bsnls_run_eval.argtypes = [H, _pf64]
     lib.bsnls_run_schur.argtypes = [H, C.c_double]
     lib.bsnls_run_pass.argtypes = [H, C.c_double, _pf64]
+    lib.bsnls_enable_breakdown.argtypes = [H, C.c_int32]
+    lib.bsnls_enable_breakdown.restype = C.c_int
     lib.bsnls_last_kernel_ms.argtypes = [H, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.bsnls_last_breakdown_ms.argtypes = [H, C.POINTER(C.c_float)]
     lib.bsnls_last_breakdown_ms.restype = C.c_int

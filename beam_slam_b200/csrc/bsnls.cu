@@ -107,6 +107,9 @@ struct bsnls_handle {
   // kernel is gated by the device state, so replaying the graph replaces ~40 stream launches per iteration
   int64_t graph_pass_launches = 0, graph_tail_launches = 0; const void* graph_recs = nullptr;
   cudaGraphExec_t graph_pass = nullptr, graph_tail = nullptr; bool graphs_valid = false; bool use_graphs = true;
+  bool nccl_warm = false;        // the communicator has run its first collectives (uncaptured)
+  cudaGraphExec_t graph_rp = nullptr; bool graph_rp_valid = false; int64_t graph_rp_launches = 0;   // bsnls_run_pass as one graph
+  bool breakdown_enabled = false;   // bsnls_enable_breakdown: direct launches with CUDA events between the kernels
   int solves_on_structure = 0;   // graphs are captured from the second solve of one structure on: capture + instantiation cost more than one solve's launches
   float last_eval_ms = 0, last_schur_ms = 0;
   int rank = 0, world = 1; NcclComm comm = nullptr;
@@ -590,6 +593,7 @@ void bsnls_destroy(bsnls_handle* h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   if (h->graph_pass) cudaGraphExecDestroy(h->graph_pass);
   if (h->graph_tail) cudaGraphExecDestroy(h->graph_tail);
+  if (h->graph_rp) cudaGraphExecDestroy(h->graph_rp);
   if (h->comm) Nccl().CommDestroy(h->comm);
   h->arena.Release();
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -620,7 +624,7 @@ int bsnls_set_options(bsnls_handle* h, const bsnls_options* o) {
         a.min_lm_diagonal == b.min_lm_diagonal && a.max_lm_diagonal == b.max_lm_diagonal &&
         a.max_num_consecutive_invalid_steps == b.max_num_consecutive_invalid_steps && a.jacobi_scaling == b.jacobi_scaling &&
         a.linear_solver == b.linear_solver && a.pcg_max_iterations == b.pcg_max_iterations && a.pcg_tolerance == b.pcg_tolerance;
-    if (!same) h->graphs_valid = false; }
+    if (!same) { h->graphs_valid = false; h->graph_rp_valid = false; } }
   h->opt = n;
   if (solver_changed && h->has_problem) h->has_problem = false;   // the reduced-system storage depends on the linear solver: set_problem again
   return BSNLS_OK;
@@ -1440,7 +1444,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   P.sparse = h->sparse ? 1 : 0; P.nnzb = h->nnzb; P.bsr_rowptr = h->d_bsr_rowptr.as<int>(); P.bsr_col = h->d_bsr_col.as<int>();
   P.diag_slot = h->d_diag_slot.as<int>(); P.pair_slot = h->d_pair_slot.as<int>(); P.gd_slot = h->d_gd_slot.as<int>();
   phase("arena commit + copy");   // asynchronous: the next set_problem waits on ev_stage before it reuses the staging buffer
-  h->has_problem = true; h->graphs_valid = false; h->solves_on_structure = 0;
+  h->has_problem = true; h->graphs_valid = false; h->graph_rp_valid = false; h->solves_on_structure = 0;
   return BSNLS_OK;
 }
 
@@ -1504,7 +1508,10 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
   // the launch sequence of a pass is fixed per problem (the cooperative PCG launch is not captured). A structure that is
   // solved once (a sliding window changes every smoother cycle) is launched directly; big reduced systems (hundreds of
   // launches per pass) are captured at once.
-  const bool graphs = h->use_graphs && h->world == 1 && !h->pcg && (h->solves_on_structure > 0 || h->tiled);
+  // Sharded solves replay graphs as well (the NCCL collectives are captured with the kernels): at 8 GPUs a pass is a few
+  // hundred microseconds of device work behind ~40 launches and two collectives, and enqueuing them one by one is slower
+  // than executing them. NCCL sets its connections up lazily, so the first collectives of a communicator run uncaptured.
+  const bool graphs = h->use_graphs && !h->pcg && (h->solves_on_structure > 0 || h->tiled) && (h->world == 1 || h->nccl_warm);
   h->solves_on_structure++;
   if (graphs && (!h->graphs_valid || h->graph_recs != recs)) {
     if (h->graph_pass) { cudaGraphExecDestroy(h->graph_pass); h->graph_pass = nullptr; }
@@ -1549,6 +1556,7 @@ int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32
     }
   }
   if ((rc = GatherValues(h)) != BSNLS_OK) return rc;
+  if (h->world > 1) h->nccl_warm = true;
   CK(cudaEventRecord(h->ev1, h->stream));
   LMState hs;
   CK(cudaMemcpyAsync(&hs, st, sizeof(hs), cudaMemcpyDeviceToHost, h->stream));
@@ -1634,6 +1642,12 @@ int bsnls_run_schur(bsnls_handle* h, double radius) {
   return BSNLS_OK;
 }
 
+int bsnls_enable_breakdown(bsnls_handle* h, int32_t on) {
+  if (!h) return BSNLS_ERR_INVALID;
+  h->breakdown_enabled = on != 0;
+  return BSNLS_OK;
+}
+
 int bsnls_run_pass(bsnls_handle* h, double radius, double* cost) {
   if (!h) return BSNLS_ERR_INVALID;
   if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_run_pass before bsnls_set_problem");
@@ -1642,17 +1656,38 @@ int bsnls_run_pass(bsnls_handle* h, double radius, double* cost) {
   int rc = InitState(h, false, radius);
   if (rc != BSNLS_OK) return rc;
   const Options o = MakeOptions(h->opt);
-  h->profiling = true;
+  auto enqueue = [&]() -> int {
+    EnqueueEval(h, 1);
+    MARK(h, 3);
+    if (!h->fused) EnqueueLandmark(h, o);
+    MARK(h, 4);
+    const int r2 = EnqueueLinearise(h, o, true);
+    if (r2 != BSNLS_OK) return r2;
+    EnqueueAssembleFinish(h, o);
+    return BSNLS_OK;
+  };
+  // One graph launch per pass unless the per-kernel breakdown is wanted (events cannot be timed inside a graph). The first
+  // pass of a sharded handle runs directly: NCCL connects lazily.
+  const bool graph = h->use_graphs && !h->breakdown_enabled && (h->world == 1 || h->nccl_warm);
+  if (graph && !h->graph_rp_valid) {
+    if (h->graph_rp) { cudaGraphExecDestroy(h->graph_rp); h->graph_rp = nullptr; }
+    cudaGraph_t g = nullptr;
+    const int64_t before = h->launches;
+    CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+    rc = enqueue();
+    const cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
+    if (rc != BSNLS_OK || ce != cudaSuccess) return h->fail(BSNLS_ERR_CUDA, "graph capture (run_pass): %s", cudaGetErrorString(ce));
+    CK(cudaGraphInstantiate(&h->graph_rp, g, 0)); cudaGraphDestroy(g);
+    h->graph_rp_launches = h->launches - before; h->launches = before;
+    h->graph_rp_valid = true;
+  }
+  h->profiling = !graph;
   CK(cudaEventRecord(h->ev0, h->stream));
-  EnqueueEval(h, 1);
-  MARK(h, 3);
-  if (!h->fused) EnqueueLandmark(h, o);
-  MARK(h, 4);
-  rc = EnqueueLinearise(h, o, true);
-  if (rc != BSNLS_OK) { h->profiling = false; return rc; }
-  EnqueueAssembleFinish(h, o);
+  if (graph) { CK(cudaGraphLaunch(h->graph_rp, h->stream)); h->launches += h->graph_rp_launches; }
+  else if ((rc = enqueue()) != BSNLS_OK) { h->profiling = false; return rc; }
   CK(cudaEventRecord(h->ev1, h->stream));
   h->profiling = false;
+  if (h->world > 1) h->nccl_warm = true;
   // cost = what the gradient pass reduced (local + replicated parts)
   double red[kRedSize];
   CK(cudaMemcpyAsync(red, h->d_red.p, sizeof(red), cudaMemcpyDeviceToHost, h->stream));
@@ -1660,10 +1695,12 @@ int bsnls_run_pass(bsnls_handle* h, double radius, double* cost) {
   if (cost) *cost = red[RED_COST] + red[RED_NUM + RED_COST];
   float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
   h->last_eval_ms = ms; h->last_schur_ms = 0.f;
-  cudaEventElapsedTime(&h->breakdown[0], h->pev[0], h->pev[1]); cudaEventElapsedTime(&h->breakdown[1], h->pev[1], h->pev[2]);
-  cudaEventElapsedTime(&h->breakdown[2], h->pev[3], h->pev[4]); cudaEventElapsedTime(&h->breakdown[3], h->pev[4], h->pev[5]);
-  cudaEventElapsedTime(&h->breakdown[4], h->pev[5], h->pev[6]); cudaEventElapsedTime(&h->breakdown[5], h->pev[6], h->pev[7]);
-  cudaEventElapsedTime(&h->breakdown[7], h->pev[7], h->pev[9]); cudaEventElapsedTime(&h->breakdown[6], h->pev[9], h->pev[8]);
+  if (!graph) {
+    cudaEventElapsedTime(&h->breakdown[0], h->pev[0], h->pev[1]); cudaEventElapsedTime(&h->breakdown[1], h->pev[1], h->pev[2]);
+    cudaEventElapsedTime(&h->breakdown[2], h->pev[3], h->pev[4]); cudaEventElapsedTime(&h->breakdown[3], h->pev[4], h->pev[5]);
+    cudaEventElapsedTime(&h->breakdown[4], h->pev[5], h->pev[6]); cudaEventElapsedTime(&h->breakdown[5], h->pev[6], h->pev[7]);
+    cudaEventElapsedTime(&h->breakdown[7], h->pev[7], h->pev[9]); cudaEventElapsedTime(&h->breakdown[6], h->pev[9], h->pev[8]);
+  }
   h->jac_valid = true;
   return BSNLS_OK;
 }

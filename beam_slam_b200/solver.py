@@ -141,6 +141,10 @@ class Solver:
         self._check(self._lib.bsnls_run_pass(self._h, radius, C.byref(c)))
         return c.value
 
+    def enable_breakdown(self, on=True):
+        """run_pass with CUDA events between its kernels (direct launches) instead of one graph launch."""
+        self._check(self._lib.bsnls_enable_breakdown(self._h, 1 if on else 0))
+
     def last_kernel_ms(self):
         a, b = C.c_float(), C.c_float()
         self._check(self._lib.bsnls_last_kernel_ms(self._h, C.byref(a), C.byref(b)))

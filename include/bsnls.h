@@ -241,6 +241,10 @@ int bsnls_run_schur(bsnls_handle* handle, double radius);
    intermediate records). cost (optional) = cost at the current values. bsnls_last_kernel_ms then reports the whole pass as
    eval_ms (schur_ms = 0). */
 int bsnls_run_pass(bsnls_handle* handle, double radius, double* cost);
+/* on != 0: bsnls_run_pass launches its kernels one by one with CUDA events between them, so that
+   bsnls_last_breakdown_ms reports the split; otherwise (default) the pass is one CUDA-graph launch and only the total is
+   timed. */
+int bsnls_enable_breakdown(bsnls_handle* handle, int32_t on);
 /* milliseconds spent in the last bsnls_run_eval / bsnls_run_schur, by CUDA events on the handle's stream */
 int bsnls_last_kernel_ms(bsnls_handle* handle, float* eval_ms, float* schur_ms);
 /* per-kernel split of the last run_eval + run_schur, milliseconds:
