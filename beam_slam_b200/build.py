@@ -31,10 +31,10 @@ def _deps(d, exts):
 def build_cuda(force=False, verbose=False):
     os.makedirs(LIB, exist_ok=True)
     out = os.path.join(LIB, "libbsnls.so")
-    deps = _deps(CSRC, (".cu", ".cuh")) + [os.path.join(HERE, "..", "include", "bsnls.h")]
+    deps = _deps(CSRC, (".cu", ".cuh", ".cpp")) + [os.path.join(HERE, "..", "include", "bsnls.h")]
     if force or _newer(out, deps):
         extra = os.environ.get("BSNLS_NVCC_EXTRA", "").split()   # A/B tuning of compile-time knobs (-DNAME=value)
-        cmd = [NVCC] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", out, os.path.join(CSRC, "bsnls.cu"), os.path.join(CSRC, "noalloc.cu")]
+        cmd = [NVCC] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", out, os.path.join(CSRC, "bsnls.cu"), os.path.join(CSRC, "noalloc.cu"), os.path.join(CSRC, "snapshot.cpp")]
         subprocess.check_call(cmd)
     return out
 

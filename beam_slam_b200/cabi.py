@@ -21,7 +21,7 @@ FACTOR_NRES = [2, 15, 15, 6, 6, 6, 3, 3, 3]
 FACTOR_STRIDE = [2, 288, 241, 43, 43, 43, 13, 12, 12]
 FACTOR_BLOCK_SIZES = [[4, 3, 3], [4, 3, 3, 3, 3, 4, 3, 3, 3, 3], [4, 3, 3, 3, 3], [3, 4, 3, 4],
                       [3, 4, 3, 4, 3, 4], [3, 4], [4, 4], [3], [3, 3]]
-LOSS_NONE, LOSS_CAUCHY, LOSS_HUBER = 0, 1, 2
+LOSS_NONE, LOSS_CAUCHY, LOSS_HUBER, LOSS_SOFTLONE, LOSS_ARCTAN, LOSS_TUKEY, LOSS_DCS, LOSS_FAIR, LOSS_GEMAN_MCCLURE, LOSS_WELSCH = range(10)
 NOALLOC_MAX_OBSERVATIONS = 4194304
 CAMERA_STRIDE = 20
 LINEAR_DENSE_SCHUR, LINEAR_ITERATIVE_SCHUR, LINEAR_AUTO = 0, 1, 2
@@ -147,6 +147,65 @@ class FlatProblem:
     def value(self, block):
         return self.block_values[self.offsets[block]:self.offsets[block + 1]]
 
+    def save(self, path):
+        """Write the snapshot file (bsnls_problem_save: the SoA buffers in createProblem order)."""
+        rc = load_library().bsnls_problem_save(C.byref(self.c), str(path).encode())
+        if rc != 0:
+            raise OSError(f"bsnls_problem_save({path}) failed: {rc}")
+
+    @classmethod
+    def load(cls, path):
+        """Read a snapshot file back (bsnls_problem_load) into numpy-owned arrays."""
+        lib = load_library()
+        pp = C.POINTER(Problem)()
+        rc = lib.bsnls_problem_load(str(path).encode(), C.byref(pp))
+        if rc != 0:
+            raise OSError(f"bsnls_problem_load({path}) failed: {rc}")
+        try:
+            cp = pp.contents
+            arr = lambda ptr, n, dt: np.ctypeslib.as_array(ptr, shape=(n,)).astype(dt, copy=True) if n else np.zeros(0, dt)
+            nb = cp.num_blocks
+            size = arr(cp.block_size, nb, np.int32)
+            groups = {}
+            for gi in range(cp.num_groups):
+                g = cp.groups[gi]
+                t, n = g.type, g.count
+                groups[t] = dict(blocks=arr(g.blocks, n * FACTOR_NBLOCKS[t], np.int32), consts=arr(g.consts, n * FACTOR_STRIDE[t], np.float64),
+                                 aux=arr(g.aux, n, np.int32) if g.aux else None, loss_type=arr(g.loss_type, n, np.int32) if g.loss_type else None,
+                                 loss_param=arr(g.loss_param, n, np.float64) if g.loss_param else None, res_index=arr(g.res_index, n, np.int32))
+            return cls(size, arr(cp.block_manifold, nb, np.int32), arr(cp.block_constant, nb, np.uint8), arr(cp.block_group, nb, np.int32),
+                       arr(cp.block_values, int(size.sum()), np.float64), arr(cp.cameras, cp.num_cameras * CAMERA_STRIDE, np.float64), groups)
+        finally:
+            lib.bsnls_problem_free(pp)
+
+    @classmethod
+    def load_numpy(cls, path):
+        """The same snapshot read with numpy alone (format: csrc/snapshot.cpp) — for consumers that must not load the
+        CUDA library, e.g. the CPU reference arm of bench.py."""
+        with open(path, "rb") as f:
+            if f.read(8) != b"BSNLS\x00\x01\x00":
+                raise OSError(f"{path}: not a bsnls snapshot (format 1)")
+            rd = lambda dt, n: np.fromfile(f, dtype=dt, count=n)
+            nb, ncam, ngroups, _ = (int(v) for v in rd(np.int32, 4))
+            size, manifold, group = rd(np.int32, nb), rd(np.int32, nb), rd(np.int32, nb)
+            constant = rd(np.uint8, nb)
+            f.read((8 - nb % 8) % 8)
+            values = rd(np.float64, int(size.sum()))
+            cameras = rd(np.float64, ncam * CAMERA_STRIDE)
+            groups = {}
+            for _ in range(ngroups):
+                t, n, has_aux, has_loss = (int(v) for v in rd(np.int32, 4))
+                g = dict(blocks=rd(np.int32, n * FACTOR_NBLOCKS[t]), consts=rd(np.float64, n * FACTOR_STRIDE[t]), res_index=rd(np.int32, n),
+                         aux=None, loss_type=None, loss_param=None)
+                if has_aux:
+                    g["aux"] = rd(np.int32, n)
+                if has_loss:
+                    g["loss_type"], g["loss_param"] = rd(np.int32, n), rd(np.float64, n)
+                if len(g["res_index"]) != n:
+                    raise OSError(f"{path}: truncated snapshot")
+                groups[t] = g
+        return cls(size, manifold, constant, group, values, cameras, groups)
+
     def with_values(self, values):
         p = FlatProblem.__new__(FlatProblem)
         p.__dict__.update(self.__dict__)
@@ -200,6 +259,12 @@ def load_library():
     lib.bsnls_reprojection_cost_noalloc.restype = C.c_int
     lib.bsnls_shard_range.argtypes = [_pi32, C.c_int32, C.c_int32, C.c_int32, _pi32, _pi32]
     lib.bsnls_shard_range.restype = C.c_int
+    lib.bsnls_problem_save.argtypes = [C.POINTER(Problem), C.c_char_p]
+    lib.bsnls_problem_save.restype = C.c_int
+    lib.bsnls_problem_load.argtypes = [C.c_char_p, C.POINTER(C.POINTER(Problem))]
+    lib.bsnls_problem_load.restype = C.c_int
+    lib.bsnls_problem_free.argtypes = [C.POINTER(Problem)]
+    lib.bsnls_problem_free.restype = None
     lib.bsnls_get_shard.argtypes = [H, _pi32, _pi32]
     lib.bsnls_get_shard.restype = C.c_int
     lib.bsnls_nccl_unique_id.argtypes = [C.c_char * 128]

@@ -57,7 +57,7 @@ struct CameraModel {  // one row of bsnls_problem::cameras
   double fx, fy, cx, cy; double T[12]; double w; double loss_type; double loss_a; double pad;
 };
 
-// ceres loss functions (loss_function.cc): rho[0..2]
+// ceres / fuse loss functions: rho[0..2] = rho(s), rho'(s), rho''(s). type = BSNLS_LOSS_* (include/bsnls.h)
 __device__ __forceinline__ void loss_evaluate(int type, double a, double s, double* rho) {
   if (type == 1) {  // CauchyLoss
     const double b = a * a, c = 1.0 / b;
@@ -67,6 +67,30 @@ __device__ __forceinline__ void loss_evaluate(int type, double a, double s, doub
     const double b = a * a;
     if (s > b) { const double r = sqrt(s); rho[0] = 2.0 * a * r - b; rho[1] = fmax(2.2250738585072014e-308, a / r); rho[2] = -rho[1] / (2.0 * s); }
     else { rho[0] = s; rho[1] = 1.0; rho[2] = 0.0; }
+  } else if (type == BSNLS_LOSS_SOFTLONE) {   // ceres::SoftLOneLoss
+    const double b = a * a, c = 1.0 / b;
+    const double sum = 1.0 + s * c, tmp = sqrt(sum);
+    rho[0] = 2.0 * b * (tmp - 1.0); rho[1] = fmax(2.2250738585072014e-308, 1.0 / tmp); rho[2] = -(c * rho[1]) / (2.0 * sum);
+  } else if (type == BSNLS_LOSS_ARCTAN) {     // ceres::ArctanLoss
+    const double b = 1.0 / (a * a);
+    const double sum = 1.0 + s * s * b, inv = 1.0 / sum;
+    rho[0] = a * atan2(s, a); rho[1] = fmax(2.2250738585072014e-308, inv); rho[2] = -2.0 * s * b * (inv * inv);
+  } else if (type == BSNLS_LOSS_TUKEY) {      // ceres::TukeyLoss (Ceres 2.x scaling)
+    const double b = a * a;
+    if (s <= b) { const double v = 1.0 - s / b, v2 = v * v; rho[0] = b / 3.0 * (1.0 - v2 * v); rho[1] = v2; rho[2] = -2.0 / b * v; }
+    else { rho[0] = b / 3.0; rho[1] = 0.0; rho[2] = 0.0; }
+  } else if (type == BSNLS_LOSS_DCS) {        // fuse_loss/src/loss_function.cpp:44-62
+    if (s > a) { const double inv = 1.0 / (a + s), scale = 2.0 * a * inv; rho[0] = a * (3.0 * s - a) * inv; rho[1] = scale * scale; rho[2] = -2.0 * inv * rho[1]; }
+    else { rho[0] = s; rho[1] = 1.0; rho[2] = 0.0; }
+  } else if (type == BSNLS_LOSS_FAIR) {       // fuse_loss/src/loss_function.cpp:64-73 (b = a^2)
+    const double r = sqrt(s), ra = r / a, sum = 1.0 + ra;
+    rho[0] = 2.0 * (a * a) * (ra - log(sum)); rho[1] = 1.0 / sum; rho[2] = r == 0.0 ? -1.7976931348623157e308 : -0.5 / (a * r * sum * sum);
+  } else if (type == BSNLS_LOSS_GEMAN_MCCLURE) {   // fuse_loss/src/loss_function.cpp:75-84
+    const double b = a * a, sum = b + s, inv = 1.0 / sum, scale = b * inv;
+    rho[0] = s * scale; rho[1] = scale * scale; rho[2] = -2.0 * inv * rho[1];
+  } else if (type == BSNLS_LOSS_WELSCH) {     // fuse_loss/src/loss_function.cpp:86-93
+    const double b = a * a, c = -1.0 / b, e = exp(s * c);
+    rho[0] = b * (1.0 - e); rho[1] = e; rho[2] = c * e;
   } else { rho[0] = s; rho[1] = 1.0; rho[2] = 0.0; }
 }
 // ceres Corrector (corrector.cc; restated in-tree at fuse_constraints/src/marginalize_variables.cpp:361-396):

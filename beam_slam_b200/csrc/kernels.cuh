@@ -138,9 +138,6 @@ __global__ void __launch_bounds__(256) eval_reproj_cost_kernel(DeviceProblem P, 
 // ===================================================================================================
 constexpr int kEvalSeg = 256, kEvalSmemCams = 8;
 static_assert(kPoseTab + kEvalSmemCams * BSNLS_CAMERA_STRIDE <= 256, "one staging pass");
-#ifndef EVAL_MINB
-#define EVAL_MINB 3
-#endif
 __global__ void __launch_bounds__(128) pose_prep_kernel(DeviceProblem P, const double* __restrict__ x, double* __restrict__ tab, const LMState* st) {
   if (!gate_jac(st)) return;
   const int a = blockIdx.x * 128 + threadIdx.x;
@@ -153,27 +150,22 @@ __global__ void __launch_bounds__(128) pose_prep_kernel(DeviceProblem P, const d
 #pragma unroll
   for (int k = 0; k < kPoseTab / 2; ++k) out[k] = make_double2(T[2 * k], T[2 * k + 1]);
 }
-// Sum of v[k] over the 32 lanes for all k at once; lane k returns total k. Each butterfly stage halves the number of
-// values a lane carries (31 exchanges instead of 32 x 5). Fixed order: deterministic.
-__device__ __forceinline__ double warp_transpose_sum32(double (&v)[32], int lane) {
-#pragma unroll
-  for (int m = 16; m >= 1; m >>= 1) {
-    const bool up = (lane & m) != 0;
-#pragma unroll
-    for (int i = 0; i < m; ++i) {
-      const double send = up ? v[i] : v[i + m], keep = up ? v[i + m] : v[i];
-      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
-    }
-  }
-  return v[0];
-}
 // One CTA per item = up to 256 consecutive observations of one pose in the pose-major list; one observation per thread.
 // Jacobian records are written at the pose-major position (contiguous per CTA); consumers go through obs_pm.
+// The pose's sums  sum F^T F (21 unique)  and  sum F^T r (6)  over the CTA's observations are one small Gram matrix:
+// stack the rows [F | r] (2 per observation, 7 wide, padded to 8) into A (512 x 8) and form A^T A on the FP64 tensor
+// cores. For mma.m8n8k4 the A^T fragment and the A fragment of a k-step are the same register (a[i][k] = b[k][i]), so a
+// warp spends one shared-memory load and one DMMA per four rows; the eight warps' tiles are added in warp order.
+// Deterministic (fixed order), and it frees the 32 registers per thread a shuffle reduction of 27 values would hold.
+#ifndef EVAL_MINB
+#define EVAL_MINB 3
+#endif
 __global__ void __launch_bounds__(256, EVAL_MINB) eval_reproj_pose_kernel(DeviceProblem P, const double* __restrict__ x, const double* __restrict__ tab,
                                                                double* __restrict__ Jrec, double* __restrict__ cost_part,
                                                                double* __restrict__ pose_part, const LMState* st) {
   if (!gate_jac(st)) return;
-  __shared__ double sm[8][33];
+  __shared__ double sm[8][66];
+  __shared__ double sCost[8];
   __shared__ double2 sOut[256 * 9];                                      // Jacobian records of the CTA, pitch 9 (conflict-free)
   __shared__ __align__(16) double sT[kPoseTab];                          // the pose's table: read by every thread (broadcast)
   __shared__ __align__(16) double sCam[kEvalSmemCams * BSNLS_CAMERA_STRIDE];   // the first few cameras (usually all of them)
@@ -185,9 +177,6 @@ __global__ void __launch_bounds__(256, EVAL_MINB) eval_reproj_pose_kernel(Device
     sCam[threadIdx.x - kPoseTab] = reinterpret_cast<const double*>(P.cams)[threadIdx.x - kPoseTab];
   __syncthreads();
   double cost = 0.0;
-  double v[32];
-#pragma unroll
-  for (int k = 0; k < 32; ++k) v[k] = 0.0;
   if (it < iv.z) {
     const int qo = P.pose_q_off[a];
     const double q[4] = {x[qo], x[qo + 1], x[qo + 2], x[qo + 3]};
@@ -208,17 +197,35 @@ __global__ void __launch_bounds__(256, EVAL_MINB) eval_reproj_pose_kernel(Device
     out[3] = make_double2(r[0], r[1]);
     out[4] = make_double2(Jq[0], Jq[1]); out[5] = make_double2(Jq[2], Jq[3]); out[6] = make_double2(Jq[4], Jq[5]);
     out[7] = make_double2(ts, 0.0);
-    const double F0[6] = {Jq[0], Jq[1], Jq[2], ts * JP[0], ts * JP[1], ts * JP[2]}, F1[6] = {Jq[3], Jq[4], Jq[5], ts * JP[3], ts * JP[4], ts * JP[5]};
-    int k = 0;
+  } else {
+    double2* out = sOut + threadIdx.x * 9;
 #pragma unroll
-    for (int i = 0; i < 6; ++i)
-#pragma unroll
-      for (int j = i; j < 6; ++j) v[k++] = F0[i] * F0[j] + F1[i] * F1[j];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) v[21 + i] = F0[i] * r[0] + F1[i] * r[1];
-    v[27] = cost;
+    for (int k = 0; k < 8; ++k) out[k] = make_double2(0.0, 0.0);   // rows of zeros in the Gram matrix below
   }
-  sm[warp][lane] = warp_transpose_sum32(v, lane);   // entry `lane` of this warp: 0..26 pose data, 27 cost
+#pragma unroll
+  for (int m = 16; m >= 1; m >>= 1) cost += __shfl_xor_sync(0xffffffffu, cost, m);
+  if (lane == 0) sCost[warp] = cost;
+  __syncwarp();
+  {   // Gram matrix of this warp's 64 rows [F | r | 0], read out of its records (E 0..5 | r 6,7 | Fq 8..13 | ts 14): row R of
+      // the warp = residual row (R & 1) of its observation R >> 1; column g < 3: Fq, 3..5: ts E, 6: r.  d[g][2 tg], d[g][2 tg + 1]
+    const int g = lane >> 2, tg = lane & 3;
+    // branch-free column select: element offset in the record for residual row 0 / 1, and whether it is scaled by ts
+    const int off0 = g < 3 ? 8 + g : g < 6 ? g - 3 : g == 6 ? 6 : 15, off1 = g < 3 ? 11 + g : g < 6 ? g : g == 6 ? 7 : 15;
+    const bool scaled = g >= 3 && g < 6;
+    double d0 = 0.0, d1 = 0.0, e0 = 0.0, e1 = 0.0;   // two accumulator pairs: halves the dependent DMMA chain
+    const double* recs = reinterpret_cast<const double*>(sOut + (size_t)(32 * warp) * 9);
+    const int offh = (tg & 1) ? off1 : off0;          // row R = 4 ks + tg: residual row R & 1 = tg & 1, observation 2 ks + (tg >> 1)
+    const double* rec = recs + (tg >> 1) * 18;
+#pragma unroll
+    for (int ks = 0; ks < 16; ks += 2) {
+      const double va = rec[(2 * ks) * 18 + offh] * (scaled ? rec[(2 * ks) * 18 + 14] : 1.0);
+      const double vb = rec[(2 * ks + 2) * 18 + offh] * (scaled ? rec[(2 * ks + 2) * 18 + 14] : 1.0);
+      dmma_m8n8k4(d0, d1, va, va);
+      dmma_m8n8k4(e0, e1, vb, vb);
+    }
+    d0 += e0; d1 += e1;
+    sm[warp][8 * g + 2 * tg] = d0; sm[warp][8 * g + 2 * tg + 1] = d1;
+  }
   __syncthreads();
   {
     const int nrec = min(256, iv.z - iv.y);
@@ -227,14 +234,22 @@ __global__ void __launch_bounds__(256, EVAL_MINB) eval_reproj_pose_kernel(Device
     for (int u = 0; u < 8; ++u) { const int e = threadIdx.x + 256 * u; if ((e >> 3) < nrec) dst[e] = sOut[(e >> 3) * 9 + (e & 7)]; }
   }
   if (threadIdx.x < 28) {
+    // entry k of the pose data: 0..20 = upper triangle of F^T F row-major, 21..26 = F^T r, 27 = cost
+    int src = 0;
+    if (threadIdx.x < 21) { int i = 0, k = threadIdx.x; while (k >= 6 - i) { k -= 6 - i; ++i; } src = 8 * i + i + k; }
+    else if (threadIdx.x < 27) src = 8 * (threadIdx.x - 21) + 6;
     double tot = 0.0;
+    if (threadIdx.x < 27) {
 #pragma unroll
-    for (int w = 0; w < 8; ++w) tot += sm[w][threadIdx.x];
-    if (threadIdx.x < 27) pose_part[(size_t)blockIdx.x * 27 + threadIdx.x] = tot; else cost_part[blockIdx.x] = tot;
+      for (int w = 0; w < 8; ++w) tot += sm[w][src];
+      pose_part[(size_t)blockIdx.x * 27 + threadIdx.x] = tot;
+    } else {
+#pragma unroll
+      for (int w = 0; w < 8; ++w) tot += sCost[w];
+      cost_part[blockIdx.x] = tot;
+    }
   }
 }
-// One thread per (pose, entry): sums the pose's item partials in item order; writes pose_H and the rank-local gradient /
-// column-norm entries of the pose's q and t blocks (index = tangent - ne_dim).
 // part_idx (optional): the pose's partials are the listed entries of pose_part (chunk-major pass: one per (chunk, slot)).
 __global__ void __launch_bounds__(128) pose_reduce_kernel(DeviceProblem P, const double* __restrict__ pose_part, const int* __restrict__ part_ptr, const int* __restrict__ part_idx,
                                                           double* __restrict__ pose_H, double* __restrict__ grad, double* __restrict__ colsq, const LMState* st) {

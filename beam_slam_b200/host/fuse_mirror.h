@@ -33,13 +33,15 @@ struct Time {  // ros::Time
 
 // ---- fuse_core::Loss (fuse_core/include/fuse_core/loss.h); plugins in fuse_loss/src ----
 struct Loss {
-  enum Type { kTrivial = 0, kCauchy = 1, kHuber = 2 };
+  enum Type { kTrivial = 0, kCauchy = 1, kHuber = 2, kSoftLOne = 3, kArctan = 4, kTukey = 5, kDCS = 6, kFair = 7, kGemanMcClure = 8, kWelsch = 9 };   // = BSNLS_LOSS_*
   Type type = kTrivial;
   double a = 0.0;
   using SharedPtr = std::shared_ptr<Loss>;
 };
 inline Loss::SharedPtr CauchyLoss(double a) { auto l = std::make_shared<Loss>(); l->type = Loss::kCauchy; l->a = a; return l; }
 inline Loss::SharedPtr HuberLoss(double a) { auto l = std::make_shared<Loss>(); l->type = Loss::kHuber; l->a = a; return l; }
+// the other one-parameter plugins of fuse_loss (src/*_loss.cpp): SoftLOne, Arctan, Tukey, DCS, Fair, GemanMcClure, Welsch
+inline Loss::SharedPtr MakeLoss(Loss::Type type, double a) { auto l = std::make_shared<Loss>(); l->type = type; l->a = a; return l; }
 
 // ---- fuse_core::Variable (fuse_core/include/fuse_core/variable.h:249-352) ----
 class Variable {

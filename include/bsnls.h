@@ -80,8 +80,13 @@ typedef enum bsnls_factor_type {
 enum { BSNLS_IMU_DELTA_STRIDE = 288, BSNLS_IMU_PRIOR_STRIDE = 241, BSNLS_POSE_STRIDE = 43,
        BSNLS_ORIENTATION_STRIDE = 13, BSNLS_VEC3_STRIDE = 12, BSNLS_REPROJECTION_STRIDE = 2 };
 
-/* fuse_loss plugins (dependencies/fuse/fuse_loss/src/) wrap ceres losses; value = ceres class. */
-enum { BSNLS_LOSS_NONE = 0, BSNLS_LOSS_CAUCHY = 1, BSNLS_LOSS_HUBER = 2 };
+/* fuse_loss plugins (dependencies/fuse/fuse_loss/src/ *.cpp) wrap ceres::LossFunction classes, one scale parameter `a` each.
+   CAUCHY .. TUKEY are Ceres' own classes (loss_function.cc, third-party; Tukey as in Ceres 2.x); DCS, FAIR, GEMAN_MCCLURE
+   and WELSCH are defined by fuse itself (fuse_loss/src/loss_function.cpp:44-103). Not covered: TolerantLoss (two
+   parameters), ComposedLoss, ScaledLoss. */
+enum { BSNLS_LOSS_NONE = 0, BSNLS_LOSS_CAUCHY = 1, BSNLS_LOSS_HUBER = 2, BSNLS_LOSS_SOFTLONE = 3, BSNLS_LOSS_ARCTAN = 4,
+       BSNLS_LOSS_TUKEY = 5, BSNLS_LOSS_DCS = 6, BSNLS_LOSS_FAIR = 7, BSNLS_LOSS_GEMAN_MCCLURE = 8, BSNLS_LOSS_WELSCH = 9,
+       BSNLS_NUM_LOSS_TYPES = 10 };
 
 /* One camera "class" shared by many reprojection factors: the members of
    EuclideanReprojectionConstraint (euclidean_reprojection_constraint.cpp:17-30) that do not vary per
@@ -274,6 +279,17 @@ int bsnls_reprojection_cost_noalloc(const double* d_values, const int32_t* d_q_o
                                     const int32_t* d_p_offset, const int32_t* d_camera_index, const double* d_pixel,
                                     const double* d_cameras, int32_t num_observations, double* d_cost, void* stream,
                                     char* error_message, int32_t error_capacity);
+
+/* ---- snapshot: the flattened problem on disk (host only, no device needed) ----
+   No replayable counterpart in the reference: its Boost serialisation keeps only pixel_ of the visual constraints
+   (bs_constraints/include/bs_constraints/visual/euclidean_reprojection_constraint.h:99-103), and constraint UUIDs are
+   random per run, so a graph read back from a bag cannot be solved again in the same order. The snapshot stores the SoA
+   buffers of bsnls_problem as the flattener produced them (createProblem order), so that the GPU path, the CPU checker
+   and a Ceres adapter consume identical arrays. Format: csrc/snapshot.cpp. bsnls_problem_load allocates; release with
+   bsnls_problem_free. */
+int bsnls_problem_save(const bsnls_problem* problem, const char* path);
+int bsnls_problem_load(const char* path, bsnls_problem** problem);
+void bsnls_problem_free(bsnls_problem* problem);
 
 /* ---- multi-GPU: landmark-sharded solve, one process per GPU ---- */
 /* Balanced cut of an ordered landmark list: rank r gets the entries [lo, hi), chosen so that every rank holds about the

@@ -919,6 +919,8 @@ int oracle_reduced_blocks(const bsnls_problem* P, const bsnls_options* opt, doub
   if (rhs) std::memcpy(rhs, R.rhs.data(), sizeof(double) * R.rhs.size());
   return BSNLS_OK;
 }
+// LossFunction::Evaluate of one loss class: rho(s), rho'(s), rho''(s)
+void oracle_loss(int32_t type, double a, double s, double* rho) { orc::LossEvaluate(type, a, s, rho); }
 void oracle_set_linear_mode(int32_t mode) { orc::g_linear_mode = mode; }
 // oracle_solve + the linearisation point of every attempted step (num_values doubles each, at most max_trace points)
 int oracle_solve_trace(const bsnls_problem* P, const bsnls_options* opt, bsnls_summary* sum, bsnls_iteration* its,

@@ -333,6 +333,30 @@ inline void LossEvaluate(int type, double a, double s, double rho[3]) {
     if (s > b) { const double r = std::sqrt(s); rho[0] = 2.0 * a * r - b;
       rho[1] = std::max(std::numeric_limits<double>::min(), a / r); rho[2] = -rho[1] / (2.0 * s); }
     else { rho[0] = s; rho[1] = 1.0; rho[2] = 0.0; }
+  } else if (type == BSNLS_LOSS_SOFTLONE) {   // ceres::SoftLOneLoss
+    const double b = a * a, c = 1.0 / b;
+    const double sum = 1.0 + s * c, tmp = std::sqrt(sum);
+    rho[0] = 2.0 * b * (tmp - 1.0); rho[1] = std::max(std::numeric_limits<double>::min(), 1.0 / tmp); rho[2] = -(c * rho[1]) / (2.0 * sum);
+  } else if (type == BSNLS_LOSS_ARCTAN) {     // ceres::ArctanLoss
+    const double b = 1.0 / (a * a);
+    const double sum = 1.0 + s * s * b, inv = 1.0 / sum;
+    rho[0] = a * std::atan2(s, a); rho[1] = std::max(std::numeric_limits<double>::min(), inv); rho[2] = -2.0 * s * b * (inv * inv);
+  } else if (type == BSNLS_LOSS_TUKEY) {      // ceres::TukeyLoss (Ceres 2.x scaling)
+    const double b = a * a;
+    if (s <= b) { const double v = 1.0 - s / b, v2 = v * v; rho[0] = b / 3.0 * (1.0 - v2 * v); rho[1] = v2; rho[2] = -2.0 / b * v; }
+    else { rho[0] = b / 3.0; rho[1] = 0.0; rho[2] = 0.0; }
+  } else if (type == BSNLS_LOSS_DCS) {        // fuse_loss/src/loss_function.cpp:44-62
+    if (s > a) { const double inv = 1.0 / (a + s), scale = 2.0 * a * inv; rho[0] = a * (3.0 * s - a) * inv; rho[1] = scale * scale; rho[2] = -2.0 * inv * rho[1]; }
+    else { rho[0] = s; rho[1] = 1.0; rho[2] = 0.0; }
+  } else if (type == BSNLS_LOSS_FAIR) {       // fuse_loss/src/loss_function.cpp:64-73 (b = a^2)
+    const double r = std::sqrt(s), ra = r / a, sum = 1.0 + ra;
+    rho[0] = 2.0 * (a * a) * (ra - std::log(sum)); rho[1] = 1.0 / sum; rho[2] = r == 0.0 ? -std::numeric_limits<double>::max() : -0.5 / (a * r * sum * sum);
+  } else if (type == BSNLS_LOSS_GEMAN_MCCLURE) {   // fuse_loss/src/loss_function.cpp:75-84
+    const double b = a * a, sum = b + s, inv = 1.0 / sum, scale = b * inv;
+    rho[0] = s * scale; rho[1] = scale * scale; rho[2] = -2.0 * inv * rho[1];
+  } else if (type == BSNLS_LOSS_WELSCH) {     // fuse_loss/src/loss_function.cpp:86-93
+    const double b = a * a, c = -1.0 / b, e = std::exp(s * c);
+    rho[0] = b * (1.0 - e); rho[1] = e; rho[2] = c * e;
   } else { rho[0] = s; rho[1] = 1.0; rho[2] = 0.0; }
 }
 

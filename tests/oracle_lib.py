@@ -40,6 +40,7 @@ def load():
                                            _pi32]
     lib.oracle_time_eval_schur.restype = C.c_double
     lib.oracle_set_linear_mode.argtypes = [C.c_int32]
+    lib.oracle_loss.argtypes = [C.c_int32, C.c_double, C.c_double, _pf64]
     lib.oracle_set_num_threads.argtypes = [C.c_int32]
     lib.oracle_reduced_blocks.argtypes = [C.POINTER(cabi.Problem), C.POINTER(cabi.Options), C.c_double, _pi32, _pi32, _pf64,
                                           C.POINTER(C.c_int64), _pf64]
@@ -65,6 +66,13 @@ def solve(problem, options=None, max_iters=256):
 
 
 LINEAR_AUTO, LINEAR_DENSE, LINEAR_SPARSE = 0, 1, 2
+
+
+def loss(loss_type, a, s):
+    """rho(s), rho'(s), rho''(s) of one loss class."""
+    rho = np.zeros(3)
+    load().oracle_loss(loss_type, a, s, _p(rho))
+    return rho
 
 
 def set_num_threads(n):

@@ -58,3 +58,34 @@ def test_product_package_never_references_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                 txt = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "liboracle" not in txt and "oracle_" not in txt and "oracle/" not in txt, os.path.join(dirpath, f)
+
+
+def test_snapshot_round_trip(tmp_path):
+    """bsnls_problem_save / bsnls_problem_load: every array of the flattened problem comes back bit for bit (host only),
+    the CPU checker gives the same answer on the copy, and a damaged file is refused."""
+    import numpy as np
+    import oracle_lib as orc
+    from beam_slam_b200 import host
+    p = host.HashGraph.synthetic(2, scale=0.1).flatten()
+    path = tmp_path / "c2.bsnls"
+    p.save(path)
+    q = cabi.FlatProblem.load(path)
+    for name in ("block_size", "block_manifold", "block_constant", "block_group", "block_values", "cameras"):
+        assert np.array_equal(getattr(p, name), getattr(q, name)), name
+    assert sorted(p.groups) == sorted(q.groups)
+    for t in p.groups:
+        for k, v in p.groups[t].items():
+            w = q.groups[t][k]
+            assert (v is None and w is None) or np.array_equal(v, w), (t, k)
+    assert orc.evaluate(p)[0] == orc.evaluate(q)[0]
+    q2 = cabi.FlatProblem.load_numpy(path)       # the numpy-only reader of the same format
+    assert np.array_equal(q2.block_values, p.block_values) and sorted(q2.groups) == sorted(p.groups)
+    assert all(np.array_equal(q2.groups[t]["blocks"], p.groups[t]["blocks"]) and np.array_equal(q2.groups[t]["consts"], p.groups[t]["consts"]) for t in p.groups)
+    raw = path.read_bytes()
+    bad = tmp_path / "bad.bsnls"
+    bad.write_bytes(b"XSNLS" + raw[5:])
+    with pytest.raises(OSError):
+        cabi.FlatProblem.load(bad)
+    bad.write_bytes(raw[:len(raw) // 2])     # truncated
+    with pytest.raises(OSError):
+        cabi.FlatProblem.load(bad)

@@ -149,6 +149,33 @@ def test_huber_loss_matches_oracle():
     assert _teacher_forced(q, opts) >= 2
 
 
+@pytest.mark.parametrize("loss", [cabi.LOSS_SOFTLONE, cabi.LOSS_ARCTAN, cabi.LOSS_TUKEY, cabi.LOSS_DCS, cabi.LOSS_FAIR,
+                                  cabi.LOSS_GEMAN_MCCLURE, cabi.LOSS_WELSCH])
+def test_other_fuse_loss_plugins_match_oracle(loss):
+    """The remaining one-parameter fuse_loss plugins (dependencies/fuse/fuse_loss/src/*_loss.cpp) on reprojection and
+    relative-pose factors: cost, corrected residuals, gradient and the reduced system against the oracle."""
+    g = host.HashGraph.synthetic(3, scale=0.02)
+    p = g.flatten()
+    cams = p.cameras.reshape(-1, cabi.CAMERA_STRIDE).copy()
+    cams[:, 17] = loss
+    cams[:, 18] = 2.0
+    groups = {t: dict(v) for t, v in p.groups.items()}
+    rp = groups[cabi.FACTOR_RELATIVE_POSE]
+    rp["loss_type"] = np.full(len(rp["res_index"]), loss, np.int32)
+    rp["loss_param"] = np.full(len(rp["res_index"]), 0.4)
+    q = cabi.FlatProblem(p.block_size, p.block_manifold, p.block_constant, p.block_group, p.block_values, cams.ravel(), groups)
+    opts = host.HashGraph.synthetic_options(3)
+    s = Solver(opts)
+    s.set_problem(q)
+    cost, res, grad = s.evaluate()
+    co, ro, go = orc.evaluate(q)
+    assert abs(co - orc.evaluate(p)[0]) > 1e-3 * co
+    assert abs(cost - co) <= 1e-12 * co and _rel(res, ro) < 1e-12 and _rel(grad, go) < 1e-10
+    S, rhs = s.reduced_system(1e4)
+    So, rhso = orc.reduced_system(q, 1e4, opts)
+    assert _rel(S, So) < 1e-9 and _rel(rhs, rhso) < 1e-9
+
+
 def test_simple_two_state_graph_reaches_the_reference_optimum():
     """bs_models/tests/imu_preintegration_tests.cpp:292-467 (Simple2StateFG): two IMU states with literal values, priors
     at the origin, relative constraints of one unit in x; the reference asserts the optimum at 1e-3 (quaternion) and

@@ -305,3 +305,31 @@ def test_sparse_and_dense_reduced_system_paths_agree():
         mask[c, r] = True
         assert np.abs(Sb[~mask]).max() == 0.0          # nothing outside the structural pattern
         assert np.abs(rh - rhs).max() <= 1e-12 * np.abs(rhs).max()
+
+
+ONE_PARAMETER_LOSSES = [cabi.LOSS_CAUCHY, cabi.LOSS_HUBER, cabi.LOSS_SOFTLONE, cabi.LOSS_ARCTAN, cabi.LOSS_TUKEY, cabi.LOSS_DCS,
+                        cabi.LOSS_FAIR, cabi.LOSS_GEMAN_MCCLURE, cabi.LOSS_WELSCH]
+
+
+def test_loss_functions_like_the_reference_tests():
+    """dependencies/fuse/fuse_loss/test/test_loss_function.cpp: (i) :63-103 rho' and rho'' agree with symmetric finite
+    differences of rho (h = 1e-4, 1e-6) and rho' >= 0; (ii) :112-168 the values at s = 0 of the four losses fuse defines
+    itself (DCS [0, 1, 0]; Fair [0, 1, -inf]; Geman-McClure [0, 1, -2/b]; Welsch [0, 1, -1/b], a = 0.7)."""
+    h = 1e-4
+    for lt in ONE_PARAMETER_LOSSES:
+        for s in (0.357, 1.792, 7.351, 33.0):          # both sides of every threshold for a = 0.7 and a = 2.5
+            for a in (0.7, 2.5):
+                if lt in (cabi.LOSS_HUBER, cabi.LOSS_TUKEY) and abs(s - a * a) < 2 * h:
+                    continue
+                if lt == cabi.LOSS_DCS and abs(s - a) < 2 * h:
+                    continue
+                rho, fwd, bwd = orc.loss(lt, a, s), orc.loss(lt, a, s + h), orc.loss(lt, a, s - h)
+                assert rho[1] >= 0.0
+                assert abs((fwd[0] - bwd[0]) / (2 * h) - rho[1]) < 1e-6, (lt, a, s)
+                assert abs((fwd[0] - 2 * rho[0] + bwd[0]) / (h * h) - rho[2]) < 1e-6, (lt, a, s)
+    a = 0.7
+    assert np.abs(orc.loss(cabi.LOSS_DCS, a, 0.0) - [0, 1, 0]).max() < 1e-6
+    r = orc.loss(cabi.LOSS_FAIR, a, 0.0)
+    assert abs(r[0]) < 1e-6 and abs(r[1] - 1) < 1e-6 and r[2] < -1e300
+    assert np.abs(orc.loss(cabi.LOSS_GEMAN_MCCLURE, a, 0.0) - [0, 1, -2 / (a * a)]).max() < 1e-6
+    assert np.abs(orc.loss(cabi.LOSS_WELSCH, a, 0.0) - [0, 1, -1 / (a * a)]).max() < 1e-6
