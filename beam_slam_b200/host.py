@@ -38,6 +38,8 @@ def load_library():
     lib.bsfuse_optimize_for.argtypes = [G, C.c_double, C.POINTER(cabi.Options), C.POINTER(cabi.Summary), C.POINTER(cabi.Iteration), C.c_int]
     lib.bsfuse_last_timing.argtypes = [G, C.POINTER(C.c_double)]
     lib.bsfuse_evaluate.argtypes = [G, C.POINTER(C.c_double)]
+    _pd = C.POINTER(C.c_double)
+    lib.bsfuse_preintegrate.argtypes = [_pd, C.c_int, C.c_double, _pd, _pd, _pd, C.c_double, _pd, _pd]
     R = C.c_void_p
     lib.bsfuse_replay_new.argtypes = [C.c_int, C.c_int, C.c_uint64]
     lib.bsfuse_replay_new.restype = R
@@ -176,6 +178,21 @@ class HashGraph:
         if self._lib.bsfuse_evaluate(self._g, C.byref(c)) != 0:
             raise RuntimeError(self._lib.bsfuse_last_error(self._g).decode())
         return c.value
+
+
+def preintegrate(imu, t_end, bg, ba, noise=(0.00057, 0.00094, 0.0000037, 0.0000024), info_weight=1.0):
+    """bs_common::PreIntegrator::Integrate on an IMU stream (rows t, w, a with t <= t_end): returns the delta
+    (t, q wxyz, p, v) and the constant block of a BSNLS_FACTOR_IMU_DELTA factor."""
+    lib = load_library()
+    imu = np.ascontiguousarray(imu, np.float64)
+    pd = C.POINTER(C.c_double)
+    bg, ba, noise = (np.ascontiguousarray(v, np.float64) for v in (bg, ba, noise))
+    delta, consts = np.zeros(11), np.zeros(cabi.FACTOR_STRIDE[cabi.FACTOR_IMU_DELTA])
+    rc = lib.bsfuse_preintegrate(imu.ctypes.data_as(pd), len(imu), float(t_end), bg.ctypes.data_as(pd), ba.ctypes.data_as(pd),
+                                 noise.ctypes.data_as(pd), float(info_weight), delta.ctypes.data_as(pd), consts.ctypes.data_as(pd))
+    if rc != 0:
+        raise ValueError("preintegration failed")
+    return dict(t=delta[0], q=delta[1:5].copy(), p=delta[5:8].copy(), v=delta[8:11].copy()), consts
 
 
 class SmootherReplay:

@@ -3,6 +3,7 @@
 #include <memory>
 
 #include "gpu_hash_graph.h"
+#include "preintegrator.h"
 #include "smoother_replay.h"
 #include "synthetic.h"
 
@@ -149,6 +150,22 @@ void bsfuse_replay_current_values(bsfuse_replay* h, double* out) {   // in the o
 int bsfuse_evaluate(bsfuse_graph* g, double* cost) {
   try { return g->graph.evaluate(cost, nullptr, nullptr) ? 0 : -3; }
   catch (const std::exception& e) { g->error = e.what(); return -3; }
+}
+
+// bs_common::PreIntegrator (host/preintegrator.cpp) on a caller-supplied IMU stream: rows (t, w[3], a[3]) sorted by time, all
+// with t <= t_end (ImuPreintegration keeps its buffer that way). bg / ba: bias estimates subtracted from the measurements
+// and stored as the factor's linearisation point. noise = (cov_gyro, cov_accel, cov_gyro_bias, cov_accel_bias).
+// delta_out: t, q (w,x,y,z), p, v; consts: the BSNLS_IMU_DELTA_STRIDE block of include/bsnls.h.
+int bsfuse_preintegrate(const double* imu7, int n, double t_end, const double bg[3], const double ba[3], const double noise[4],
+                        double info_weight, double delta_out[11], double consts[288]) {
+  if (!imu7 || n <= 0) return -1;
+  PreIntegrator pre; pre.Reset();
+  pre.cov_w = noise[0]; pre.cov_a = noise[1]; pre.cov_bg = noise[2]; pre.cov_ba = noise[3];
+  for (int i = 0; i < n; ++i) { IMUData d; d.t = imu7[7 * i]; for (int k = 0; k < 3; ++k) { d.w[k] = imu7[7 * i + 1 + k]; d.a[k] = imu7[7 * i + 4 + k]; } pre.data.push_back(d); }
+  if (!pre.Integrate(t_end, bg, ba, true, true, true)) return -1;
+  delta_out[0] = pre.delta.t; std::memcpy(delta_out + 1, pre.delta.q, 32); std::memcpy(delta_out + 5, pre.delta.p, 24); std::memcpy(delta_out + 8, pre.delta.v, 24);
+  pre.FillFactorConstants(bg, ba, info_weight, consts);
+  return 0;
 }
 
 // ---- host-logic probes for the CPU tests ----

@@ -1,0 +1,152 @@
+"""Pins the IMU preintegrator (A7) and the IMU-delta factor (A6) to what the reference's own test holds for them:
+bs_models/tests/imu_preintegration_tests.cpp, fixture ImuPreintegration_ZeroNoiseConstantBias (:470-523), tests
+BaseFunctionality (:525-699) and MultipleTransactions (:701-774), tolerances of tests/include/test_utils.h:77-81
+(quaternion 1e-6, position 1e-3, velocity 1e-3, biases 1e-9).
+
+The trajectory and IMU stream are the reference's: tests/golden/imu_spline.json was written by the reference's vendored
+generator (basalt::Se3Spline<5>, dependencies/basalt-headers-mirror) through oracle/tools/gen_imu_spline_golden.cpp, which
+repeats class Data of the test (:77-160). The checks:
+  * integrating the stream between two ground-truth states and predicting (ImuPreintegration::PredictState,
+    bs_models/src/lib/imu/imu_preintegration.cpp:220-244) lands on the next ground-truth state;
+  * the graph the transactions build — 15-DoF prior (cov 1e-9 I) on the first state, RelativeImuState3DStampedConstraint to
+    the next — optimises to the ground truth from the predicted start.
+CPU part: host preintegrator + oracle. GPU part: the same graphs through the C-ABI."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as orc
+from beam_slam_b200 import cabi, host
+from beam_slam_b200.builder import ProblemBuilder
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+G = np.array([0.0, 0.0, -9.80665])
+TOL = (1e-6, 1e-3, 1e-3, 1e-9, 1e-9)          # test_utils.h:77-81
+BG = np.array([0.0068, -0.0021, 0.0097])       # "small, random bias values": Random() / 100 and / 10 (:474-475)
+BA = np.array([0.053, -0.081, 0.024])
+ZERO_NOISE = (0.0, 0.0, 0.0, 0.0)              # the fixture zeroes the IMU's intrinsic noise (:481-484)
+
+
+def _data():
+    d = json.load(open(os.path.join(HERE, "golden", "imu_spline.json")))
+    imu = np.array(d["imu"])
+    imu[:, 1:4] += BG                          # msg.w += bg; msg.a += ba (:594-596)
+    imu[:, 4:7] += BA
+    return imu, d["states"]
+
+
+def _R(q):
+    w, x, y, z = q
+    return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                     [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                     [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+
+
+def _qmul(a, b):
+    return np.array([a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3], a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2],
+                     a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1], a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0]])
+
+
+def _predict(state, delta):                    # ImuPreintegration::PredictState (imu_preintegration.cpp:220-244)
+    dt, R = delta["t"], _R(state["q"])
+    return dict(q=_qmul(np.array(state["q"]), delta["q"]), v=np.array(state["v"]) + G * dt + R @ delta["v"],
+                p=np.array(state["p"]) + np.array(state["v"]) * dt + 0.5 * G * dt * dt + R @ delta["p"])
+
+
+def _near(got, want):
+    q = np.array(got["q"]) * (1.0 if np.dot(got["q"], want["q"]) >= 0 else -1.0)
+    assert np.abs(q - want["q"]).max() < TOL[0]
+    assert np.abs(np.array(got["p"]) - want["p"]).max() < TOL[1]
+    assert np.abs(np.array(got["v"]) - want["v"]).max() < TOL[2]
+
+
+def _segment(imu, t0, t1):
+    return imu[(imu[:, 0] >= t0 - 1e-9) & (imu[:, 0] <= t1 + 1e-9)]
+
+
+def _graph(states_init, deltas_consts, prior_state):
+    """prior (cov 1e-9 I) on the first state + one IMU-delta factor per consecutive pair; returns problem + block ids."""
+    b = ProblemBuilder()
+    ids = []
+    for s in states_init:
+        ids.append([b.add_quaternion(s["q"]), b.add_block(s["p"]), b.add_block(s["v"]), b.add_block(BG), b.add_block(BA)])
+    mean = np.concatenate([prior_state["q"], prior_state["p"], prior_state["v"], BG, BA])
+    A = np.eye(15) / np.sqrt(1e-9)              # cov_prior_noise = 1e-9 (:478): A = chol-U(cov^-1)
+    b.add_factor(cabi.FACTOR_IMU_PRIOR, ids[0], np.concatenate([mean, A.ravel()]))
+    for k, consts in enumerate(deltas_consts):
+        b.add_factor(cabi.FACTOR_IMU_DELTA, ids[k] + ids[k + 1], consts)
+    return b.build(), ids
+
+
+def _state_of(x, p, ids_k):
+    get = lambda blk: x[p.offsets[blk]:p.offsets[blk + 1]]
+    return dict(q=get(ids_k[0]), p=get(ids_k[1]), v=get(ids_k[2]), bg=get(ids_k[3]), ba=get(ids_k[4]))
+
+
+def _check_solution(x, p, ids, truth):
+    for k, want in enumerate(truth):
+        got = _state_of(x, p, ids[k])
+        _near(got, want)
+        assert np.abs(got["bg"] - BG).max() < TOL[3] and np.abs(got["ba"] - BA).max() < TOL[4]
+
+
+def _base_functionality():
+    imu, st = _data()
+    delta13, consts13 = host.preintegrate(_segment(imu, st[0]["t"], st[2]["t"]), st[2]["t"], BG, BA, ZERO_NOISE)
+    pred3 = _predict(st[0], delta13)
+    _near(pred3, st[2])                         # ExpectImuStateNear(IS_end, IS3) (:633-636)
+    return _graph([st[0], pred3], [consts13], st[0]) + ([st[0], st[2]],)
+
+
+def _multiple_transactions():
+    imu, st = _data()
+    d12, c12 = host.preintegrate(_segment(imu, st[0]["t"], st[1]["t"]), st[1]["t"], BG, BA, ZERO_NOISE)
+    pred2 = _predict(st[0], d12)
+    d23, c23 = host.preintegrate(_segment(imu, st[1]["t"], st[2]["t"]), st[2]["t"], BG, BA, ZERO_NOISE)
+    pred3 = _predict(pred2, d23)
+    _near(pred2, st[1])
+    _near(pred3, st[2])
+    return _graph([st[0], pred2, pred3], [c12, c23], st[0]) + ([st[0], st[1], st[2]],)
+
+
+def test_relative_motion_deltas_of_the_ground_truth_predict_the_next_state():
+    """:57-75 CalculateRelativeMotion + :574-590: exact deltas between ground-truth states reproduce them through
+    PredictState (ExpectImuStateEq)."""
+    _, st = _data()
+    for a, c in ((st[0], st[1]), (st[1], st[2])):
+        dt = c["t"] - a["t"]
+        Ra = _R(a["q"])
+        Rd = Ra.T @ _R(c["q"])
+        qd = np.array([0.5 * np.sqrt(max(1e-300, 1 + np.trace(Rd))), 0, 0, 0])
+        qd[1:] = np.array([Rd[2, 1] - Rd[1, 2], Rd[0, 2] - Rd[2, 0], Rd[1, 0] - Rd[0, 1]]) / (4 * qd[0])
+        delta = dict(t=dt, q=qd, v=Ra.T @ (np.array(c["v"]) - a["v"] - G * dt),
+                     p=Ra.T @ (np.array(c["p"]) - a["p"] - np.array(a["v"]) * dt - 0.5 * G * dt * dt))
+        got = _predict(a, delta)
+        assert np.abs(got["p"] - c["p"]).max() < 1e-9 and np.abs(got["v"] - c["v"]).max() < 1e-9
+        assert min(np.abs(got["q"] - c["q"]).max(), np.abs(got["q"] + c["q"]).max()) < 1e-9
+
+
+@pytest.mark.parametrize("build", [_base_functionality, _multiple_transactions], ids=["BaseFunctionality", "MultipleTransactions"])
+def test_preintegrated_graph_recovers_ground_truth_with_the_oracle(build):
+    p, ids, truth = build()
+    s, its, x = orc.solve(p)                    # graph.optimize() with default options (:679, :755-759)
+    assert s.termination_type == cabi.CONVERGENCE
+    _check_solution(x, p, ids, truth)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("build", [_base_functionality, _multiple_transactions], ids=["BaseFunctionality", "MultipleTransactions"])
+def test_preintegrated_graph_recovers_ground_truth_on_the_gpu(build):
+    from beam_slam_b200.solver import Solver
+    p, ids, truth = build()
+    s = Solver()
+    s.set_problem(p)
+    summ, its = s.solve()
+    assert summ.is_solution_usable()
+    _check_solution(s.get_values(), p, ids, truth)
+    so, ito, xo = orc.solve(p)
+    assert len(its) == len(ito)
+    for a, b in zip(its, ito):
+        assert abs(a.cost - b.cost) <= 1e-9 * max(abs(b.cost), 1e-30) + 1e-25
