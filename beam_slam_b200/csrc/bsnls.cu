@@ -734,6 +734,21 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   // the landmarks it observes (no hashing); pair id = position in (a, b) order; lookups go through pair_row / pair_b.
   std::vector<int> pair_row;            // CSR over a: pairs [pair_row[a], pair_row[a+1]) have pose a and ascending b >= a
   h->pair_a.clear(); h->pair_b.clear();
+  if (h->np <= 64) {
+    // sliding windows: one 64-bit pose mask per landmark, OR-ed into the rows of the poses it contains
+    std::vector<uint64_t> row(h->np, 0);
+    for (int e = 0; e < ne_g; ++e) {
+      uint64_t m = 0;
+      for (int k = lm_ptr[e]; k < lm_ptr[e + 1]; ++k) m |= uint64_t(1) << g_pose[k];
+      for (uint64_t t = m; t; t &= t - 1) row[__builtin_ctzll(t)] |= m;
+    }
+    pair_row.assign(h->np + 1, 0);
+    for (int a = 0; a < h->np; ++a) {
+      for (uint64_t t = row[a] >> a; t; t &= t - 1) { h->pair_a.push_back(a); h->pair_b.push_back(a + __builtin_ctzll(t)); }
+      pair_row[a + 1] = (int)h->pair_b.size();
+    }
+    h->npairs = (int)h->pair_b.size();
+  } else
   {
     std::vector<int> gp_ptr(h->np + 1, 0), gp_lm(nobs);
     for (int k = 0; k < nobs; ++k) gp_ptr[g_pose[k] + 1]++;
@@ -753,7 +768,13 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     }
     h->npairs = (int)h->pair_b.size();
   }
+  std::vector<int> pid_dense;   // small pose counts: direct table instead of a search per lookup
+  if (h->np <= 256) {
+    pid_dense.assign((size_t)h->np * h->np, -1);
+    for (int k = 0; k < h->npairs; ++k) { pid_dense[(size_t)h->pair_a[k] * h->np + h->pair_b[k]] = k; pid_dense[(size_t)h->pair_b[k] * h->np + h->pair_a[k]] = k; }
+  }
   auto pair_id = [&](int a2, int b2) -> int {   // -1: the two poses share no landmark
+    if (!pid_dense.empty()) return pid_dense[(size_t)a2 * h->np + b2];
     const int a = std::min(a2, b2), b = std::max(a2, b2);
     const int* r0 = h->pair_b.data() + pair_row[a]; const int* r1 = h->pair_b.data() + pair_row[a + 1];
     const int* p = std::lower_bound(r0, r1, b);
