@@ -243,6 +243,8 @@ def load_library():
     lib.bsnls_get_ordering.argtypes = [H, _pi32, _pi32, _pi32, _pi32]
     lib.bsnls_get_reduced_pattern.argtypes = [H, _pi32, _pi32, C.POINTER(C.c_int64)]
     lib.bsnls_get_reduced_system.argtypes = [H, C.c_double, _pf64, _pf64, C.c_int32]
+    lib.bsnls_get_covariance.argtypes = [H, _pi32, C.c_int32, C.c_int32, _pf64]
+    lib.bsnls_get_covariance.restype = C.c_int
     lib.bsnls_get_reduced_blocks.argtypes = [H, C.c_double, _pi32, _pi32, _pf64, C.POINTER(C.c_int64), _pf64]
     lib.bsnls_trial_step.argtypes = [H, _pf64, C.c_double, C.c_int32, C.POINTER(Iteration), _pi32]
     lib.bsnls_run_eval.argtypes = [H, _pf64]

@@ -11,6 +11,8 @@
 #include <unordered_map>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>   // header-only NVTX v3: ranges around the C-ABI calls and the phases of a pass (nsys / ncu --nvtx)
+
 #include "kernels.cuh"
 #include "tile_chol.cuh"
 #include "nccl_dyn.h"
@@ -18,6 +20,8 @@
 using namespace bsnls;
 
 namespace {
+
+struct NvtxRange { explicit NvtxRange(const char* name) { nvtxRangePushA(name); } ~NvtxRange() { nvtxRangePop(); } };
 
 thread_local std::string g_create_error;
 
@@ -262,6 +266,7 @@ void EnqueueFused(bsnls_handle* h, const Options& o, int with_system, int force_
 }
 // phase A: residuals + Jacobians + cost at x. fused_system: in the fused mode, also eliminate and accumulate the tiles
 void EnqueueEval(bsnls_handle* h, int fused_system = 0) {
+  NvtxRange nvtx_range("enqueue: residuals + Jacobians");
   const DeviceProblem& P = h->P;
   LMState* st = h->d_state.as<LMState>();
   MARK(h, 0);
@@ -406,6 +411,7 @@ void EnqueueAssembleFinish(bsnls_handle* h, const Options& o) {  // generic-fact
 // The Jacobian half of a pass (after EnqueueEval / EnqueueLandmark) up to the controller's input; with_system also
 // assembles the reduced system. Kernel order is the same on one GPU, where the exchange is a no-op.
 int EnqueueLinearise(bsnls_handle* h, const Options& o, bool with_system) {
+  NvtxRange nvtx_range("enqueue: gradient + reduced-system assembly");
   EnqueueGradientLocal(h);
   if (h->world == 1 && with_system) {
     // one GPU: nothing to exchange, so the gradient / norm kernels (small, latency-bound) run on the side stream
@@ -427,17 +433,21 @@ int EnqueueLinearise(bsnls_handle* h, const Options& o, bool with_system) {
   EnqueueGradientGlobal(h, o);
   return BSNLS_OK;
 }
-void EnqueueDenseSolve(bsnls_handle* h) {  // phase D2: Cholesky + triangular solves
+// factor = false: the tile factor of the previous call is reused (another right-hand side of the same matrix)
+void EnqueueDenseSolve(bsnls_handle* h, bool factor = true) {  // phase D2: Cholesky + triangular solves
+  NvtxRange nvtx_range("enqueue: Cholesky of the reduced system");
   const int n = h->P.nf_dim; LMState* st = h->d_state.as<LMState>();
   double* Sd = h->d_S.as<double>();
   if (h->tiled) {
     const TileChol& TC = h->TC;
     const size_t smem = sizeof(double) * 2 * kTS * kTLd;
-    cudaMemsetAsync(TC.T, 0, h->tc_T_bytes, h->stream);
-    LAUNCH(h, bsr_to_tiles_kernel, (unsigned)((h->nnzb * 9 + (long long)TC.nT * kTS + 255) / 256), 256, h->P, TC, h->d_S.as<double>(), st);
-    for (const auto& L : h->tc_levels) {   // factorisation, one level of the elimination tree at a time
-      LAUNCH_SMEM(h, tile_panel_kernel, L.npan, 256, sizeof(double) * kPanelSmemDoubles, TC, L.pan_begin, st);
-      if (L.nupd > 0) LAUNCH_SMEM(h, tile_syrk_kernel, L.nupd, 256, smem, TC, L.upd_begin, st);
+    if (factor) {
+      cudaMemsetAsync(TC.T, 0, h->tc_T_bytes, h->stream);
+      LAUNCH(h, bsr_to_tiles_kernel, (unsigned)((h->nnzb * 9 + (long long)TC.nT * kTS + 255) / 256), 256, h->P, TC, h->d_S.as<double>(), st);
+      for (const auto& L : h->tc_levels) {   // factorisation, one level of the elimination tree at a time
+        LAUNCH_SMEM(h, tile_panel_kernel, L.npan, 256, sizeof(double) * kPanelSmemDoubles, TC, L.pan_begin, st);
+        if (L.nupd > 0) LAUNCH_SMEM(h, tile_syrk_kernel, L.nupd, 256, smem, TC, L.upd_begin, st);
+      }
     }
     // substitutions, level by level: forward (bottom-up), backward (top-down)
     LAUNCH(h, tile_rhs_kernel, (TC.nT * kTS + 255) / 256, 256, TC, h->d_rhs.as<double>(), st);
@@ -465,6 +475,7 @@ template <int G> void LaunchBacksub(bsnls_handle* h) {
          h->d_y.as<double>(), h->d_model_part.as<double>(), h->d_state.as<LMState>());
 }
 int EnqueueStep(bsnls_handle* h) {  // phase D3: back-substitution, model cost, candidate, candidate cost
+  NvtxRange nvtx_range("enqueue: back-substitution + candidate");
   const DeviceProblem& P = h->P; LMState* st = h->d_state.as<LMState>();
   if (h->ne) switch (h->G) { case 4: LaunchBacksub<4>(h); break; case 8: LaunchBacksub<8>(h); break;
                              case 16: LaunchBacksub<16>(h); break; default: LaunchBacksub<32>(h); }
@@ -631,6 +642,7 @@ int bsnls_set_options(bsnls_handle* h, const bsnls_options* o) {
 }
 
 int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
+  NvtxRange nvtx_range("bsnls_set_problem");
   if (!h || !pr) return BSNLS_ERR_INVALID;
   CK(cudaSetDevice(h->device));
   h->has_problem = false; h->jac_valid = false;
@@ -1489,6 +1501,7 @@ int bsnls_get_values(bsnls_handle* h, double* v) {
 }
 
 int bsnls_solve(bsnls_handle* h, bsnls_summary* sum, bsnls_iteration* its, int32_t max_its_out) {
+  NvtxRange nvtx_range("bsnls_solve");
   if (!h || !sum) return BSNLS_ERR_INVALID;
   if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_solve before bsnls_set_problem");
   CK(cudaSetDevice(h->device));
@@ -1670,6 +1683,7 @@ int bsnls_enable_breakdown(bsnls_handle* h, int32_t on) {
 }
 
 int bsnls_run_pass(bsnls_handle* h, double radius, double* cost) {
+  NvtxRange nvtx_range("bsnls_run_pass");
   if (!h) return BSNLS_ERR_INVALID;
   if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_run_pass before bsnls_set_problem");
   if (!(radius > 0)) return h->fail(BSNLS_ERR_INVALID, "radius must be positive");
@@ -1814,7 +1828,76 @@ int bsnls_get_reduced_blocks(bsnls_handle* h, double radius, int32_t* rows, int3
   return BSNLS_OK;
 }
 
+// replaces HashGraph::getCovariance (hash_graph.cpp:303-414) for pairs of non-landmark blocks: columns of the inverse of the
+// undamped reduced system (= the f-f part of (J^T J)^-1), one triangular solve per column on the factor of one
+// linearisation.
+int bsnls_get_covariance(bsnls_handle* h, const int32_t* pairs, int32_t num_pairs, int32_t use_tangent_space, double* out) {
+  NvtxRange nvtx_range("bsnls_get_covariance");
+  if (!h || (num_pairs > 0 && (!pairs || !out)) || num_pairs < 0) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_get_covariance before bsnls_set_problem");
+  if (num_pairs == 0) return BSNLS_OK;
+  if (h->pcg) return h->fail(BSNLS_ERR_UNSUPPORTED, "covariance needs the direct solver (the iterative solver keeps no factor)");
+  CK(cudaSetDevice(h->device));
+  const int ne_dim = h->P.ne_dim, nf_dim = h->P.nf_dim;
+  std::vector<int> col_of(h->num_blocks, -1);     // requested block -> slot in the list of solved block columns
+  std::vector<int> cols;
+  for (int q = 0; q < 2 * num_pairs; ++q) {
+    const int b = pairs[q];
+    if (b < 0 || b >= h->num_blocks) return h->fail(BSNLS_ERR_INVALID, "covariance request: block index out of range");
+    if (h->blk_tan[b] < 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "covariance request: block %d is constant or unused (ceres::Covariance has no block for it)", b);
+    if (h->blk_tan[b] < ne_dim) return h->fail(BSNLS_ERR_UNSUPPORTED, "covariance request: block %d is an eliminated landmark; only blocks of the reduced system are supported", b);
+    if (col_of[b] < 0 && (q & 1)) { col_of[b] = (int)cols.size(); cols.push_back(b); }
+  }
+  // linearise at the current values without damping: radius -> infinity makes D^2 vanish
+  int rc = InitState(h, false, 1e300);
+  if (rc != BSNLS_OK) return rc;
+  const Options o = MakeOptions(h->opt);
+  LMState* st = h->d_state.as<LMState>();
+  EnqueueEval(h, 1);
+  if (!h->fused) EnqueueLandmark(h, o);
+  if ((rc = EnqueueLinearise(h, o, true)) != BSNLS_OK) return rc;
+  EnqueueAssembleFinish(h, o);
+  std::vector<double> sol((size_t)cols.size() * 3 * nf_dim);
+  for (size_t c = 0; c < cols.size(); ++c)
+    for (int k = 0; k < 3; ++k) {
+      const int j = h->blk_tan[cols[c]] - ne_dim + k;
+      LAUNCH(h, unit_rhs_kernel, BlocksFor(nf_dim, 256), 256, h->d_rhs.as<double>(), nf_dim, j);
+      EnqueueDenseSolve(h, c == 0 && k == 0);
+      CK(cudaMemcpyAsync(sol.data() + (c * 3 + k) * nf_dim, h->d_yf.p, sizeof(double) * nf_dim, cudaMemcpyDeviceToHost, h->stream));
+    }
+  LMState hs;
+  CK(cudaMemcpyAsync(&hs, st, sizeof(hs), cudaMemcpyDeviceToHost, h->stream));
+  std::vector<double> x;
+  if (!use_tangent_space) { x.resize(h->num_values); CK(cudaMemcpyAsync(x.data(), h->d_x.p, sizeof(double) * h->num_values, cudaMemcpyDeviceToHost, h->stream)); }
+  CK(cudaStreamSynchronize(h->stream)); CK(cudaGetLastError());
+  h->jac_valid = false;
+  if (hs.lin_fail) return h->fail(BSNLS_ERR_STATE, "the normal equations are rank deficient at the current values: no covariance (ceres::Covariance::Compute returns false)");
+  auto plus_jacobian = [&](int b, double* J /* size x 3 */) {   // ambient = J tangent
+    if (h->blk_manifold[b] == BSNLS_MANIFOLD_QUATERNION) {
+      const double* q = x.data() + h->blk_off[b];
+      const double v[12] = {-q[1], -q[2], -q[3], q[0], -q[3], q[2], q[3], q[0], -q[1], -q[2], q[1], q[0]};
+      for (int e = 0; e < 12; ++e) J[e] = 0.5 * v[e];
+    } else { for (int e = 0; e < 9; ++e) J[e] = (e % 4 == 0) ? 1.0 : 0.0; }
+  };
+  for (int q = 0; q < num_pairs; ++q) {
+    const int bi = pairs[2 * q], bj = pairs[2 * q + 1];
+    const int ri = h->blk_tan[bi] - ne_dim, cj = col_of[bj];
+    double T[9];
+    for (int a = 0; a < 3; ++a) for (int k = 0; k < 3; ++k) T[3 * a + k] = sol[((size_t)cj * 3 + k) * nf_dim + ri + a];
+    double* dst = out + 16 * (size_t)q;
+    std::memset(dst, 0, sizeof(double) * 16);
+    if (use_tangent_space) { std::memcpy(dst, T, sizeof(T)); continue; }
+    const int si = h->blk_size[bi], sj = h->blk_size[bj];
+    double Ji[12], Jj[12], M[12];
+    plus_jacobian(bi, Ji); plus_jacobian(bj, Jj);
+    for (int a = 0; a < si; ++a) for (int k = 0; k < 3; ++k) { double acc = 0; for (int m = 0; m < 3; ++m) acc += Ji[3 * a + m] * T[3 * m + k]; M[3 * a + k] = acc; }
+    for (int a = 0; a < si; ++a) for (int c = 0; c < sj; ++c) { double acc = 0; for (int k = 0; k < 3; ++k) acc += M[3 * a + k] * Jj[3 * c + k]; dst[a * sj + c] = acc; }
+  }
+  return BSNLS_OK;
+}
+
 int bsnls_trial_step(bsnls_handle* h, const double* values, double radius, int32_t keep_jacobi_scale, bsnls_iteration* out, int32_t* num_out) {
+  NvtxRange nvtx_range("bsnls_trial_step");
   if (!h || !out || !num_out) return BSNLS_ERR_INVALID;
   if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_trial_step before bsnls_set_problem");
   if (!(radius > 0)) return h->fail(BSNLS_ERR_INVALID, "radius must be positive");
@@ -1841,6 +1924,7 @@ int bsnls_trial_step(bsnls_handle* h, const double* values, double radius, int32
 }
 
 int bsnls_evaluate(bsnls_handle* h, double* cost, double* residuals, int64_t* num_residuals, double* gradient, int64_t* num_gradient) {
+  NvtxRange nvtx_range("bsnls_evaluate");
   if (!h) return BSNLS_ERR_INVALID;
   if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_evaluate before bsnls_set_problem");
   CK(cudaSetDevice(h->device));

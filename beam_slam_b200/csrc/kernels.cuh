@@ -1598,6 +1598,11 @@ __global__ void __launch_bounds__(256) mask_owned_kernel(double* __restrict__ x,
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i < n && !owned[i]) x[i] = 0.0;
 }
+// right-hand side e_j (covariance columns: S^-1 e_j)
+__global__ void __launch_bounds__(256) unit_rhs_kernel(double* __restrict__ rhs, int n, int j) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i < n) rhs[i] = i == j ? 1.0 : 0.0;
+}
 __global__ void set_done_kernel(LMState* st, int termination, int msg) { if (!st->done) { st->done = 1; st->termination = termination; st->message_id = msg; } }
 
 }  // namespace bsnls

@@ -38,6 +38,7 @@ def load_library():
     lib.bsfuse_optimize_for.argtypes = [G, C.c_double, C.POINTER(cabi.Options), C.POINTER(cabi.Summary), C.POINTER(cabi.Iteration), C.c_int]
     lib.bsfuse_last_timing.argtypes = [G, C.POINTER(C.c_double)]
     lib.bsfuse_evaluate.argtypes = [G, C.POINTER(C.c_double)]
+    lib.bsfuse_get_covariance.argtypes = [G, C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(C.c_double)]
     _pd = C.POINTER(C.c_double)
     lib.bsfuse_preintegrate.argtypes = [_pd, C.c_int, C.c_double, _pd, _pd, _pd, C.c_double, _pd, _pd]
     R = C.c_void_p
@@ -172,6 +173,19 @@ class HashGraph:
         if rc != 0:
             raise RuntimeError(self._lib.bsfuse_last_error(self._g).decode())
         return s, [its[i] for i in range(min(s.num_iterations, max_iters))]
+
+    def covariance(self, block_pairs, tangent_space=True):
+        """GpuHashGraph::getCovariance for pairs of block indices (positions in flatten() order): 3x3 tangent blocks, or
+        flat ambient blocks."""
+        pr = np.ascontiguousarray(block_pairs, np.int32).reshape(-1, 2)
+        out = np.zeros((len(pr), 16))
+        rc = self._lib.bsfuse_get_covariance(self._g, pr.ctypes.data_as(C.POINTER(C.c_int)), len(pr), 1 if tangent_space else 0,
+                                             out.ctypes.data_as(C.POINTER(C.c_double)))
+        if rc == -1:
+            raise KeyError(self._lib.bsfuse_last_error(self._g).decode())
+        if rc != 0:
+            raise RuntimeError(self._lib.bsfuse_last_error(self._g).decode())
+        return [out[k, :9].reshape(3, 3).copy() for k in range(len(pr))] if tangent_space else [out[k].copy() for k in range(len(pr))]
 
     def evaluate(self):
         c = C.c_double()

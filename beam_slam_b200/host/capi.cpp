@@ -115,6 +115,21 @@ int bsfuse_optimize(bsfuse_graph* g, const bsnls_options* o, bsnls_summary* s, b
 // host wall-clock split of the last optimize: flatten | set_problem or set_values | solve | get_values + scatter | reused (0/1)
 void bsfuse_last_timing(bsfuse_graph* g, double out[5]) { TimingOut(g->graph, out); }
 
+// GpuHashGraph::getCovariance for pairs given as block indices of the last flatten (mapped to UUIDs here, so the call runs
+// through the graph interface); out: 16 doubles reserved per pair
+int bsfuse_get_covariance(bsfuse_graph* g, const int* block_pairs, int n, int use_tangent_space, double* out) {
+  try {
+    const FlatProblem& f = g->graph.flattened();
+    std::vector<std::pair<UUID, UUID>> req;
+    for (int i = 0; i < n; ++i) req.emplace_back(f.block_uuid.at(block_pairs[2 * i]), f.block_uuid.at(block_pairs[2 * i + 1]));
+    std::vector<std::vector<double>> m;
+    g->graph.getCovariance(req, m, use_tangent_space != 0);
+    for (int i = 0; i < n; ++i) { std::memset(out + 16 * i, 0, sizeof(double) * 16); std::memcpy(out + 16 * i, m[i].data(), sizeof(double) * m[i].size()); }
+    return 0;
+  } catch (const std::out_of_range& e) { g->error = e.what(); return -1; }
+  catch (const std::exception& e) { g->error = e.what(); return -3; }
+}
+
 // ---- sliding-window replay (smoother_replay.h) ----
 bsfuse_replay* bsfuse_replay_new(int total_keyframes, int window_keyframes, uint64_t seed) {
   auto* h = new bsfuse_replay();

@@ -223,6 +223,11 @@ class HashGraph {
   virtual SolverSummary optimize(const SolverOptions& options = SolverOptions()) = 0;
   virtual SolverSummary optimizeFor(double max_optimization_time_s, const SolverOptions& options = SolverOptions()) = 0;
   virtual bool evaluate(double* cost, std::vector<double>* residuals, std::vector<double>* gradient) const = 0;
+  // getCovariance(covariance_requests, covariance_matrices, options, use_tangent_space) (hash_graph.cpp:303-414): one
+  // row-major block per requested variable pair; std::out_of_range for an unknown UUID, std::runtime_error when the
+  // blocks cannot be computed
+  virtual void getCovariance(const std::vector<std::pair<UUID, UUID>>& covariance_requests,
+                             std::vector<std::vector<double>>& covariance_matrices, bool use_tangent_space = true) const = 0;
  protected:
   Constraints constraints_;
   Variables variables_;

@@ -127,6 +127,25 @@ SolverSummary GpuHashGraph::optimizeFor(double max_time_s, const SolverOptions& 
   return optimize(o);
 }
 
+void GpuHashGraph::getCovariance(const std::vector<std::pair<UUID, UUID>>& requests, std::vector<std::vector<double>>& matrices,
+                                 bool use_tangent_space) const {
+  if (requests.empty()) return;   // "Avoid doing a bunch of work if the request is empty" (hash_graph.cpp:309-313)
+  for (const auto& r : requests) { getVariable(r.first); getVariable(r.second); }   // std::out_of_range, as :337-349
+  EnsureHandle(last_options_);
+  if (SyncProblem() != BSNLS_OK) throw std::runtime_error(std::string("Could not compute requested covariance blocks: ") + bsnls_last_error(handle_));
+  std::vector<int32_t> pairs; pairs.reserve(2 * requests.size());
+  for (const auto& r : requests) { pairs.push_back(getVariable(r.first).flat_index); pairs.push_back(getVariable(r.second).flat_index); }
+  std::vector<double> out(16 * requests.size());
+  if (bsnls_get_covariance(handle_, pairs.data(), static_cast<int32_t>(requests.size()), use_tangent_space ? 1 : 0, out.data()) != BSNLS_OK)
+    throw std::runtime_error(std::string("Could not compute requested covariance blocks: ") + bsnls_last_error(handle_));
+  matrices.resize(requests.size());
+  for (size_t i = 0; i < requests.size(); ++i) {
+    const Variable& a = getVariable(requests[i].first); const Variable& b = getVariable(requests[i].second);
+    const size_t n = use_tangent_space ? a.localSize() * b.localSize() : a.size() * b.size();
+    matrices[i].assign(out.begin() + 16 * i, out.begin() + 16 * i + n);
+  }
+}
+
 bool GpuHashGraph::evaluate(double* cost, std::vector<double>* residuals, std::vector<double>* gradient) const {
   if (getConstraints().empty() || getVariables().empty()) { if (cost) *cost = 0.0; if (residuals) residuals->clear(); if (gradient) gradient->clear(); return true; }
   EnsureHandle(last_options_);

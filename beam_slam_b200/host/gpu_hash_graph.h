@@ -20,6 +20,10 @@ class GpuHashGraph : public HashGraph {
   SolverSummary optimizeFor(double max_optimization_time_s, const SolverOptions& options = SolverOptions()) override;
   // Problem::Evaluate with default EvaluateOptions (hash_graph.cpp:446-455)
   bool evaluate(double* cost, std::vector<double>* residuals, std::vector<double>* gradient) const override;
+  // ceres::Covariance on the GPU: blocks of the inverse normal matrix at the current values (hash_graph.cpp:303-414).
+  // Landmark blocks are not supported (std::runtime_error), as are constant blocks (Ceres has no covariance for them).
+  void getCovariance(const std::vector<std::pair<UUID, UUID>>& covariance_requests,
+                     std::vector<std::vector<double>>& covariance_matrices, bool use_tangent_space = true) const override;
   const FlatProblem& lastProblem() const { return flat_; }
   // createProblem-order SoA view of the graph as it is now (re-flattened only if the structure changed, else the values
   // are gathered); the returned object stays owned by the graph

@@ -107,6 +107,15 @@ class Solver:
         self._check(self._lib.bsnls_get_reduced_system(self._h, radius, S.ctypes.data_as(_pf64), rhs.ctypes.data_as(_pf64), dim))
         return S, rhs  # S is symmetric, so the column-major buffer reads the same row-major
 
+    def covariance(self, pairs, tangent_space=True, sizes=None):
+        """HashGraph::getCovariance: list of covariance blocks for (block_i, block_j) pairs at the current values."""
+        pr = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
+        out = np.zeros((len(pr), 16))
+        self._check(self._lib.bsnls_get_covariance(self._h, pr.ctypes.data_as(_pi32), len(pr), 1 if tangent_space else 0, out.ctypes.data_as(_pf64)))
+        if tangent_space:
+            return [out[k, :9].reshape(3, 3).copy() for k in range(len(pr))]
+        return [out[k, :sizes[i] * sizes[j]].reshape(sizes[i], sizes[j]).copy() for k, (i, j) in enumerate(pr)]
+
     def reduced_blocks(self, radius):
         """Lower-triangular 3x3 blocks of the reduced system on its structural pattern: rows, cols, vals (n,3,3), rhs."""
         n = C.c_int64(0)

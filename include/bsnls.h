@@ -210,6 +210,14 @@ int bsnls_get_values(bsnls_handle* handle, double* block_values);
 int bsnls_evaluate(bsnls_handle* handle, double* cost, double* residuals, int64_t* num_residuals,
                    double* gradient, int64_t* num_gradient);
 
+/* replaces: HashGraph::getCovariance (hash_graph.cpp:303-414) -> ceres::Covariance::Compute + GetCovarianceBlock[InTangentSpace]
+   at the current values. pairs: num_pairs x 2 block indices; out: 16 doubles reserved per pair, the block row-major at the
+   start of its slot — tangent space (fuse's default): 3 x 3; otherwise ambient size_i x size_j (quaternion rows / columns
+   through the plus-Jacobian, as Ceres lifts them). Supported: pairs of non-constant blocks of the reduced system (poses,
+   velocities, biases, extrinsics); a request for an eliminated landmark or a constant block fails with
+   BSNLS_ERR_UNSUPPORTED, a rank-deficient problem with BSNLS_ERR_STATE (Ceres: Compute returns false). Direct solver only. */
+int bsnls_get_covariance(bsnls_handle* handle, const int32_t* pairs, int32_t num_pairs, int32_t use_tangent_space, double* out);
+
 /* ---- introspection used by the parity tests ("ordering and sparsity pattern bit-exact") ---- */
 /* e-block / f-block lists in elimination order: indices into the caller's block arrays. */
 int bsnls_get_ordering(bsnls_handle* handle, int32_t* e_blocks, int32_t* num_e, int32_t* f_blocks,
