@@ -8,6 +8,7 @@
 #include <functional>
 #include <map>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -42,8 +43,10 @@ struct Arena {
   char* stage = nullptr; size_t stage_cap = 0;   // pinned host mirror of the uploaded region [0, up_used)
   size_t up_used = 0, work_used = 0;
   std::vector<DevMem*> members;
+  struct Deferred { DevMem* m; const void* src; size_t bytes; };
+  std::vector<Deferred> deferred;   // large arrays skip the staging mirror: copied straight from the caller's vector at Commit
   static size_t Align(size_t n) { return (n + 255) & ~size_t(255); }
-  void Begin() { up_used = 0; work_used = 0; members.clear(); }
+  void Begin() { up_used = 0; work_used = 0; members.clear(); deferred.clear(); }
   cudaError_t StageReserve(size_t n) {
     if (n <= stage_cap) return cudaSuccess;
     const size_t nc = std::max(std::max(2 * stage_cap, n + n / 4), size_t(1) << 20);
@@ -91,7 +94,10 @@ cudaError_t Arena::Commit(cudaStream_t s) {
   }
   for (DevMem* m : members) m->p = base + (m->in_work ? up + m->off : m->off);
   members.clear();
-  return up_used ? cudaMemcpyAsync(base, stage, up_used, cudaMemcpyHostToDevice, s) : cudaSuccess;
+  cudaError_t e = up_used ? cudaMemcpyAsync(base, stage, up_used, cudaMemcpyHostToDevice, s) : cudaSuccess;
+  for (const Deferred& d : deferred) if (e == cudaSuccess) e = cudaMemcpyAsync(d.m->p, d.src, d.bytes, cudaMemcpyHostToDevice, s);   // pageable source: returns once staged
+  deferred.clear();
+  return e;
 }
 
 }  // namespace
@@ -182,7 +188,13 @@ struct bsnls_handle {
 
 namespace {
 
+constexpr size_t kDeferBytes = size_t(1) << 20;
 template <typename T> cudaError_t upload(DevMem& m, const std::vector<T>& v, cudaStream_t s) {
+  if (g_rec && v.size() * sizeof(T) >= kDeferBytes) {   // large: no second host copy; v must outlive Arena::Commit (function-scope vectors of set_problem)
+    cudaError_t e = m.alloc(v.size() * sizeof(T));
+    if (e == cudaSuccess) g_rec->deferred.push_back({&m, v.data(), v.size() * sizeof(T)});
+    return e;
+  }
   if (g_rec) {   // copy into the pinned staging mirror; the device pointer is resolved by Arena::Commit
     const size_t n = std::max<size_t>(v.size() * sizeof(T), 8);
     cudaError_t e = g_rec->StageReserve(g_rec->up_used + Arena::Align(n));
@@ -240,6 +252,16 @@ const char* MessageText(int id) {
 }
 
 int BlocksFor(int n, int per) { return std::max(1, (n + per - 1) / per); }
+
+// Host-side structure analysis of a refinement-sized graph (millions of observations) runs in slices on host threads;
+// sliding windows (below `grain` items per thread) stay on the calling thread. fn(begin, end) must only write its slice.
+template <class F> void ParallelFor(int n, int grain, F fn) {
+  int nt = (int)std::min<long long>(std::min(16u, std::max(1u, std::thread::hardware_concurrency())), (long long)n / std::max(1, grain));
+  if (nt <= 1) { fn(0, n); return; }
+  std::vector<std::thread> th;
+  for (int t = 0; t < nt; ++t) th.emplace_back([&, t]() { fn((int)((long long)n * t / nt), (int)((long long)n * (t + 1) / nt)); });
+  for (auto& x : th) x.join();
+}
 
 // ---- enqueue helpers (all asynchronous on h->stream) ----
 // ---- NCCL exchange of the landmark-sharded solve (no-ops on a single GPU) ----
@@ -766,16 +788,22 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     for (int k = 0; k < nobs; ++k) gp_ptr[g_pose[k] + 1]++;
     for (int a = 0; a < h->np; ++a) gp_ptr[a + 1] += gp_ptr[a];
     { std::vector<int> cur(gp_ptr.begin(), gp_ptr.end() - 1); for (int e = 0; e < ne_g; ++e) for (int k = lm_ptr[e]; k < lm_ptr[e + 1]; ++k) gp_lm[cur[g_pose[k]]++] = e; }
-    std::vector<int> stamp(h->np, -1), row;
+    // rows of different poses are independent: host threads take slices of the poses, each with its own stamp array
+    std::vector<std::vector<int>> rows(h->np);
+    ParallelFor(h->np, 64, [&](int a0, int a1) {
+      std::vector<int> stamp(h->np, -1);
+      for (int a = a0; a < a1; ++a) {
+        std::vector<int>& row = rows[a];
+        for (int q = gp_ptr[a]; q < gp_ptr[a + 1]; ++q) {
+          const int e = gp_lm[q];
+          for (int k = lm_ptr[e]; k < lm_ptr[e + 1]; ++k) { const int b = g_pose[k]; if (b >= a && stamp[b] != a) { stamp[b] = a; row.push_back(b); } }
+        }
+        std::sort(row.begin(), row.end());
+      }
+    });
     pair_row.assign(h->np + 1, 0);
     for (int a = 0; a < h->np; ++a) {
-      row.clear();
-      for (int q = gp_ptr[a]; q < gp_ptr[a + 1]; ++q) {
-        const int e = gp_lm[q];
-        for (int k = lm_ptr[e]; k < lm_ptr[e + 1]; ++k) { const int b = g_pose[k]; if (b >= a && stamp[b] != a) { stamp[b] = a; row.push_back(b); } }
-      }
-      std::sort(row.begin(), row.end());
-      for (int b : row) { h->pair_a.push_back(a); h->pair_b.push_back(b); }
+      for (int b : rows[a]) { h->pair_a.push_back(a); h->pair_b.push_back(b); }
       pair_row[a + 1] = (int)h->pair_b.size();
     }
     h->npairs = (int)h->pair_b.size();
@@ -933,17 +961,19 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   std::vector<int> s_pose(nobs_local), s_lm(nobs_local), s_cam(nobs_local), inv_order(nobs, -1), lm_ptr_local(h->ne + 1, 0), lm_off(h->ne);
   std::vector<double> s_pixel(2 * (size_t)nobs_local);
   {
-    int kl = 0;
-    for (int e = 0; e < h->ne; ++e) {
-      const int ge = mine[e];
-      lm_off[e] = h->blk_off[h->eblocks[ge]];
-      for (int k = lm_ptr[ge]; k < lm_ptr[ge + 1]; ++k, ++kl) {
-        const int i = order[k]; inv_order[i] = kl;
-        s_pose[kl] = obs_pose[i]; s_lm[kl] = e; s_cam[kl] = rg->aux[i];
-        s_pixel[2 * (size_t)kl] = rg->consts[2 * (size_t)i]; s_pixel[2 * (size_t)kl + 1] = rg->consts[2 * (size_t)i + 1];
+    for (int e = 0; e < h->ne; ++e) lm_ptr_local[e + 1] = lm_ptr_local[e] + (lm_ptr[mine[e] + 1] - lm_ptr[mine[e]]);
+    ParallelFor(h->ne, 20000, [&](int e0, int e1) {
+      for (int e = e0; e < e1; ++e) {
+        const int ge = mine[e];
+        lm_off[e] = h->blk_off[h->eblocks[ge]];
+        int kl = lm_ptr_local[e];
+        for (int k = lm_ptr[ge]; k < lm_ptr[ge + 1]; ++k, ++kl) {
+          const int i = order[k]; inv_order[i] = kl;
+          s_pose[kl] = obs_pose[i]; s_lm[kl] = e; s_cam[kl] = rg->aux[i];
+          s_pixel[2 * (size_t)kl] = rg->consts[2 * (size_t)i]; s_pixel[2 * (size_t)kl + 1] = rg->consts[2 * (size_t)i + 1];
+        }
       }
-      lm_ptr_local[e + 1] = kl;
-    }
+    });
   }
   std::vector<int> pose_q_off(h->np), pose_t_off(h->np), pose_q_tan(h->np), pose_t_tan(h->np), pose_ptr(h->np + 1, 0), pose_obs(nobs_local);
   for (int a = 0; a < h->np; ++a) {
@@ -960,12 +990,15 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     for (int b = pose_ptr[a]; b < pose_ptr[a + 1]; b += kEvalSeg) { eval_items.push_back(a); eval_items.push_back(b); eval_items.push_back(std::min(b + kEvalSeg, pose_ptr[a + 1])); eval_items.push_back(0); }
     eval_item_ptr[a + 1] = (int)(eval_items.size() / 4);
   }
-  for (int it = 0; it < nobs_local; ++it) {
-    const int o = pose_obs[it];
-    pm_lm_off[it] = lm_off[s_lm[o]]; pm_cam[it] = s_cam[o]; pm_pixel[2 * (size_t)it] = s_pixel[2 * (size_t)o]; pm_pixel[2 * (size_t)it + 1] = s_pixel[2 * (size_t)o + 1];
-  }
+  h->obs_pm_h.assign(nobs_local, 0);
+  ParallelFor(nobs_local, 200000, [&](int i0, int i1) {
+    for (int it = i0; it < i1; ++it) {
+      const int o = pose_obs[it];
+      pm_lm_off[it] = lm_off[s_lm[o]]; pm_cam[it] = s_cam[o]; pm_pixel[2 * (size_t)it] = s_pixel[2 * (size_t)o]; pm_pixel[2 * (size_t)it + 1] = s_pixel[2 * (size_t)o + 1];
+      h->obs_pm_h[o] = it;
+    }
+  });
   h->n_eval_items = (int)(eval_items.size() / 4); h->nb_eval = h->n_eval_items;
-  h->obs_pm_h.assign(nobs_local, 0); for (int it = 0; it < nobs_local; ++it) h->obs_pm_h[pose_obs[it]] = it;
   const double avg_track = ne_g ? (double)nobs / ne_g : 0.0;
   // lanes per landmark: throughput-bound shards do best with about three observations per lane (landmark 0.179 -> 0.174 ms
   // on config 4), latency-bound windows with one or two (C1 solve 1.22 vs 1.34 ms)
@@ -1241,7 +1274,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   struct RecGuard { ~RecGuard() { g_rec = nullptr; } } rec_guard;
   if (h->stage_busy) { CK(cudaEventSynchronize(h->ev_stage)); h->stage_busy = false; }   // the previous problem's staged copy
   h->arena.Begin(); g_rec = &h->arena;
-  CK(h->arena.StageReserve((size_t)nobs_local * 72 + (size_t)nb * 48 + (size_t)off * 9 + (size_t)h->npairs * 64 + (size_t(1) << 20)));   // one pinned allocation instead of a doubling series
+  CK(h->arena.StageReserve(std::min<size_t>((size_t)nobs_local * 72 + (size_t)nb * 48 + (size_t)off * 9 + (size_t)h->npairs * 64, size_t(24) << 20) + (size_t(1) << 20)));   // one pinned allocation for the small arrays (arrays above 1 MB bypass the mirror)
   CK(upload(h->d_blk_off, h->blk_off, s)); CK(upload(h->d_blk_size, h->blk_size, s)); CK(upload(h->d_blk_tan, h->blk_tan, s));
   CK(upload(h->d_blk_manifold, h->blk_manifold, s)); CK(upload(h->d_active, h->active_blocks, s));
   CK(upload(h->d_pose_q_off, pose_q_off, s)); CK(upload(h->d_pose_t_off, pose_t_off, s)); CK(upload(h->d_pose_q_tan, pose_q_tan, s));
@@ -1275,8 +1308,9 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(upload(h->d_gd_fac, gd_fac, s)); CK(upload(h->d_gd_bi, gd_bi, s)); CK(upload(h->d_gd_bj, gd_bj, s)); CK(upload(h->d_is_pose, is_pose, s));
   CK(upload(h->d_bsr_rowptr, h->bsr_rowptr, s)); CK(upload(h->d_bsr_col, h->bsr_col, s)); CK(upload(h->d_diag_slot, diag_slot, s));
   CK(upload(h->d_pair_slot, pair_slot, s)); CK(upload(h->d_gd_slot, gd_slot, s));
+  std::vector<unsigned char> owned;   // function scope: large uploads are copied at Commit
   { // ownership of parameter entries for the final gather of the sharded solve
-    std::vector<unsigned char> owned((size_t)off, h->rank == 0 ? 1 : 0);
+    owned.assign((size_t)off, h->rank == 0 ? 1 : 0);
     for (int b = 0; b < nb; ++b) if (epos[b] >= 0) { const unsigned char own = is_mine[epos[b]] ? 1 : 0; for (int k = 0; k < h->blk_size[b]; ++k) owned[h->blk_off[b] + k] = own; }
     CK(upload(h->d_owned, owned, s));
   }
