@@ -26,7 +26,19 @@ int main(int argc, char** argv) {
   cudaMemcpy(dT0, T.data(), T.size() * 8, cudaMemcpyHostToDevice); cudaMemcpy(doff, off.data(), off.size() * 8, cudaMemcpyHostToDevice);
   cudaMemcpy(dcp, col_ptr.data(), col_ptr.size() * 4, cudaMemcpyHostToDevice); if (na) cudaMemcpy(dcr, col_rows.data(), col_rows.size() * 4, cudaMemcpyHostToDevice);
   cudaMemset(dst, 0, sizeof(LMState));
-  TileChol TC{nT, nT * 64, doff, dcp, dcr, dT, dW, db};
+  TileChol TC{}; TC.nT = nT; TC.n = nT * 64; TC.tile_off = doff; TC.col_ptr = dcp; TC.col_rows = dcr; TC.T = dT; TC.W = dW; TC.b = db;
+  {   // level schedule of the one column: panel CTA x works on tile col_rows[x]; update destinations (i, j), 1 <= j <= i, from column 0
+    std::vector<int> pk(std::max(1, na), 0), px(std::max(1, na), -1), up; std::vector<long long> ud, ua, ub;
+    for (int x = 0; x < na; ++x) px[x] = x;
+    up.push_back(0);
+    for (int i = 1; i < nT; ++i) for (int j = 1; j <= i; ++j) { ud.push_back(off[(size_t)i * nT + j]); ua.push_back(off[(size_t)i * nT]); ub.push_back(off[(size_t)j * nT]); up.push_back((int)ua.size()); }
+    int *dpk, *dpx, *dup; long long *dud, *dua, *dub;
+    cudaMalloc(&dpk, pk.size() * 4); cudaMalloc(&dpx, px.size() * 4); cudaMalloc(&dup, up.size() * 4);
+    cudaMalloc(&dud, (ud.size() + 1) * 8); cudaMalloc(&dua, (ua.size() + 1) * 8); cudaMalloc(&dub, (ub.size() + 1) * 8);
+    cudaMemcpy(dpk, pk.data(), pk.size() * 4, cudaMemcpyHostToDevice); cudaMemcpy(dpx, px.data(), px.size() * 4, cudaMemcpyHostToDevice); cudaMemcpy(dup, up.data(), up.size() * 4, cudaMemcpyHostToDevice);
+    if (!ud.empty()) { cudaMemcpy(dud, ud.data(), ud.size() * 8, cudaMemcpyHostToDevice); cudaMemcpy(dua, ua.data(), ua.size() * 8, cudaMemcpyHostToDevice); cudaMemcpy(dub, ub.data(), ub.size() * 8, cudaMemcpyHostToDevice); }
+    TC.pan_k = dpk; TC.pan_x = dpx; TC.upd_ptr = dup; TC.upd_dst = dud; TC.upd_a = dua; TC.upd_b = dub;
+  }
   const size_t psm = sizeof(double) * kPanelSmemDoubles, ssm = sizeof(double) * 2 * kTS * kTLd;
   cudaFuncSetAttribute(tile_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psm);
   cudaFuncSetAttribute(tile_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssm);
@@ -60,7 +72,7 @@ int main(int argc, char** argv) {
 #ifdef PANEL_PROF
   { long long pr[80]; cudaMemcpyFromSymbol(pr, g_panel_prof, sizeof(pr));
     printf("start->step0 %lld, steps:", pr[0] - pr[70]); for (int j = 4; j <= 64; j += 4) printf(" %lld", pr[j] - pr[j - 4]); printf(", epilogue %lld\n", pr[65] - pr[64]);
-    printf("step 5: diag block %lld cycles; observer: barrier1->end of (b) %lld, barrier2 wait %lld, (c) %lld\n", pr[71], pr[72] - pr[20], pr[73] - pr[72], pr[74] - pr[73]); }
+    printf("step 5: diag block %lld cycles; observer: barrier -> end of the update %lld\n", pr[71], pr[74] - pr[20]); }
 #endif
   LMState hs; cudaMemcpy(&hs, dst, sizeof(hs), cudaMemcpyDeviceToHost); printf("lin_fail %d, cuda: %s\n", hs.lin_fail, cudaGetErrorString(cudaGetLastError()));
   return 0;
