@@ -172,24 +172,29 @@ __global__ void __launch_bounds__(256, EVAL_MINB) eval_reproj_pose_kernel(Device
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int4 iv = P.eval_items[blockIdx.x];   // pose, begin, end in the pose-major list
   const int a = iv.x, it = iv.y + threadIdx.x;
+  // the observation's own inputs first: the landmark point is a dependent gather (offset, then three doubles somewhere in
+  // x), whose latency then overlaps the staging of the pose table and its barrier instead of following them
+  const bool live = it < iv.z;
+  int po = 0, ci = 0; double2 px = make_double2(0.0, 0.0);
+  if (live) { po = P.pm_lm_off[it]; ci = P.pm_cam[it]; px = reinterpret_cast<const double2*>(P.pm_pixel)[it]; }
+  const int qo = P.pose_q_off[a];
+  const int tq = P.pose_q_tan[a], tt = P.pose_t_tan[a];
+  double Pw[3] = {0.0, 0.0, 0.0};
+  if (live) { Pw[0] = x[po]; Pw[1] = x[po + 1]; Pw[2] = x[po + 2]; }
+  const double q[4] = {x[qo], x[qo + 1], x[qo + 2], x[qo + 3]};
   if (threadIdx.x < kPoseTab) sT[threadIdx.x] = tab[(size_t)a * kPoseTab + threadIdx.x];
   else if (threadIdx.x - kPoseTab < min(P.num_cams, kEvalSmemCams) * BSNLS_CAMERA_STRIDE)
     sCam[threadIdx.x - kPoseTab] = reinterpret_cast<const double*>(P.cams)[threadIdx.x - kPoseTab];
   __syncthreads();
   double cost = 0.0;
-  if (it < iv.z) {
-    const int qo = P.pose_q_off[a];
-    const double q[4] = {x[qo], x[qo + 1], x[qo + 2], x[qo + 3]};
+  if (live) {
     const double* T = sT;
-    const int po = P.pm_lm_off[it], ci = P.pm_cam[it];
     const CameraModel cam = ci < kEvalSmemCams ? reinterpret_cast<const CameraModel*>(sCam)[ci] : P.cams[ci];
-    const double2 px = reinterpret_cast<const double2*>(P.pm_pixel)[it];
     const double pixel[2] = {px.x, px.y};
-    const double Pw[3] = {x[po], x[po + 1], x[po + 2]};
     double r[2], Jq[6], JP[6];
     cost = reprojection_evaluate_tab(cam, pixel, q, T, Pw, r, Jq, JP);
-    if (P.pose_q_tan[a] < 0) { for (int k = 0; k < 6; ++k) Jq[k] = 0.0; }
-    const double ts = P.pose_t_tan[a] < 0 ? 0.0 : -1.0;   // d r / d t = ts * d r / d P
+    if (tq < 0) { for (int k = 0; k < 6; ++k) Jq[k] = 0.0; }
+    const double ts = tt < 0 ? 0.0 : -1.0;   // d r / d t = ts * d r / d P
     // the record goes through shared memory so that the CTA's records (contiguous in the pose-major list) leave as
     // whole 512-byte warp stores instead of 32 separate lines per store instruction
     double2* out = sOut + threadIdx.x * 9;
@@ -373,10 +378,31 @@ __global__ void __launch_bounds__(256) landmark_kernel(DeviceProblem P, const do
   const bool valid = l < P.ne;
   const int start = valid ? P.lm_ptr[l] : 0, end = valid ? P.lm_ptr[l + 1] : 0;
   double a00 = 0, a01 = 0, a02 = 0, a11 = 0, a12 = 0, a22 = 0, g0 = 0, g1 = 0, g2 = 0;
-  for (int o = start + sub; o < end; o += G) {
+  // A lane's observations are independent gathers (index, then a 128-byte record somewhere in Jrec): they are issued in
+  // batches of kLmBatch so that their latencies overlap instead of adding up. The record positions of the first batch
+  // (usually all of a lane's observations) are kept for the second pass.
+  constexpr int kLmBatch = 3;
+  int pm0[kLmBatch];
+#pragma unroll
+  for (int u = 0; u < kLmBatch; ++u) { const int o = start + sub + u * G; pm0[u] = o < end ? P.obs_pm[o] : -1; }
+  {
+    double2 e0[kLmBatch], e1[kLmBatch], e2[kLmBatch], r[kLmBatch];
+#pragma unroll
+    for (int u = 0; u < kLmBatch; ++u) {
+      if (pm0[u] >= 0) { const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)pm0[u] * kJRec); e0[u] = rec[0]; e1[u] = rec[1]; e2[u] = rec[2]; r[u] = rec[3]; }
+      else { e0[u] = e1[u] = e2[u] = r[u] = make_double2(0.0, 0.0); }
+    }
+#pragma unroll
+    for (int u = 0; u < kLmBatch; ++u) {
+      // E row0 = (e0.x, e0.y, e1.x), row1 = (e1.y, e2.x, e2.y)
+      a00 += e0[u].x * e0[u].x + e1[u].y * e1[u].y; a01 += e0[u].x * e0[u].y + e1[u].y * e2[u].x; a02 += e0[u].x * e1[u].x + e1[u].y * e2[u].y;
+      a11 += e0[u].y * e0[u].y + e2[u].x * e2[u].x; a12 += e0[u].y * e1[u].x + e2[u].x * e2[u].y; a22 += e1[u].x * e1[u].x + e2[u].y * e2[u].y;
+      g0 += e0[u].x * r[u].x + e1[u].y * r[u].y; g1 += e0[u].y * r[u].x + e2[u].x * r[u].y; g2 += e1[u].x * r[u].x + e2[u].y * r[u].y;
+    }
+  }
+  for (int o = start + sub + kLmBatch * G; o < end; o += G) {   // tracks longer than kLmBatch * G
     const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec);
     const double2 e0 = rec[0], e1 = rec[1], e2 = rec[2], r = rec[3];
-    // E row0 = (e0.x, e0.y, e1.x), row1 = (e1.y, e2.x, e2.y)
     a00 += e0.x * e0.x + e1.y * e1.y; a01 += e0.x * e0.y + e1.y * e2.x; a02 += e0.x * e1.x + e1.y * e2.y;
     a11 += e0.y * e0.y + e2.x * e2.x; a12 += e0.y * e1.x + e2.x * e2.y; a22 += e1.x * e1.x + e2.y * e2.y;
     g0 += e0.x * r.x + e1.y * r.y; g1 += e0.y * r.x + e2.x * r.y; g2 += e1.x * r.x + e2.y * r.y;
@@ -421,8 +447,7 @@ __global__ void __launch_bounds__(256) landmark_kernel(DeviceProblem P, const do
     lm_z[te] = z0; lm_z[te + 1] = z1; lm_z[te + 2] = z2;   // z = C^T E^T r: the Schur right-hand side is sum V z
   }
   // pass 2: V = (F^T E) C with C = Linv^T (upper):  V[:,0] = W0 i00; V[:,1] = W0 i10 + W1 i11; V[:,2] = W0 i20 + W1 i21 + W2 i22
-  for (int o = start + sub; o < end; o += G) {
-    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec);
+  auto emit = [&](int o, const double2* rec) {
     const double2 e0 = rec[0], e1 = rec[1], e2 = rec[2];
     const double E0[3] = {e0.x, e0.y, e1.x}, E1[3] = {e1.y, e2.x, e2.y};
     double F0[6], F1[6];
@@ -438,7 +463,10 @@ __global__ void __launch_bounds__(256) landmark_kernel(DeviceProblem P, const do
     }
 #pragma unroll
     for (int k = 0; k < 9; ++k) out[k] = make_double2(v[2 * k], v[2 * k + 1]);
-  }
+  };
+#pragma unroll
+  for (int u = 0; u < kLmBatch; ++u) if (pm0[u] >= 0) emit(start + sub + u * G, reinterpret_cast<const double2*>(Jrec + (size_t)pm0[u] * kJRec));
+  for (int o = start + sub + kLmBatch * G; o < end; o += G) emit(o, reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec));
 }
 
 // K6b: generic-factor contributions to the gradient and the column norms of every f-block.
