@@ -367,8 +367,11 @@ __global__ void __launch_bounds__(128) eval_generic_kernel(DeviceProblem P, cons
 // Outputs per landmark: Minv (6, symmetric (E^T E + D^2)^-1), g_e = E^T r, c_e = diag(E^T E), Jacobi scale;
 // per observation: V = F^T E C (6x3, Minv = C C^T) and c = V (C^T g_e) so that S -= sum V_a V_b^T, rhs -= c.
 // ===================================================================================================
+#ifndef LM_MINB
+#define LM_MINB 3
+#endif
 template <int G>
-__global__ void __launch_bounds__(256) landmark_kernel(DeviceProblem P, const double* __restrict__ Jrec,
+__global__ void __launch_bounds__(256, LM_MINB) landmark_kernel(DeviceProblem P, const double* __restrict__ Jrec,
                                                        double* __restrict__ Vrec, double* __restrict__ lm_minv,
                                                        double* __restrict__ grad, double* __restrict__ colsq,
                                                        double* __restrict__ scale, double* __restrict__ lm_z, Options opt, LMState* st) {
