@@ -136,9 +136,9 @@ struct bsnls_handle {
   std::vector<int> gd_row, gd_col;
   bool tiled = false; std::vector<int> f_api;   // tile-sparse Cholesky; internal f position -> API (program-order) position
   TileChol TC{}; std::vector<int> tc_col_ptr; DevMem d_tc_tile_off, d_tc_col_ptr, d_tc_col_rows, d_tc_T, d_tc_W, d_tc_b; size_t tc_T_bytes = 0;
-  struct TcLevel { int col_begin, ncols, pan_begin, npan, upd_begin, nupd, fw_begin, nfw, bw_begin, nbw; };   // one level of the elimination tree
+  struct TcLevel { int col_begin, ncols, pan_begin, npan, npan_tiles, upd_begin, nupd, fw_begin, nfw, bw_begin, nbw; };   // one level of the elimination tree
   std::vector<TcLevel> tc_levels;
-  DevMem d_tc_pan_k, d_tc_pan_x, d_tc_upd_ptr, d_tc_upd_dst, d_tc_upd_a, d_tc_upd_b, d_tc_fw_ptr, d_tc_fw_row, d_tc_fw_tail, d_tc_fw_src, d_tc_fw_k, d_tc_lev_cols, d_tc_bw_ptr, d_tc_bw_col, d_tc_bw_tail, d_tc_bw_src, d_tc_bw_i, d_tc_roots; int tc_nroots = 0;
+  DevMem d_tc_pan_k, d_tc_pan_x, d_tc_upd_ptr, d_tc_upd_fac, d_tc_upd_dst, d_tc_upd_a, d_tc_upd_b, d_tc_fw_ptr, d_tc_fw_row, d_tc_fw_tail, d_tc_fw_src, d_tc_fw_k, d_tc_lev_cols, d_tc_bw_ptr, d_tc_bw_col, d_tc_bw_tail, d_tc_bw_src, d_tc_bw_i, d_tc_roots; int tc_nroots = 0;
   long long nlow = 0; DevMem d_low_slot, d_low_slot_t, d_xsend, d_xrecv;   // sharded solve: lower-triangular blocks of S, packed exchange buffers
   int chunk_max_slots = 1; DevMem d_syrk_plan, d_chunk_tile_off, d_pp_toff, d_pp_info;
   int n_local_pairs = 0; DevMem d_local_pairs;   // pairs with contributions from this rank's landmarks
@@ -462,12 +462,14 @@ void EnqueueDenseSolve(bsnls_handle* h, bool factor = true) {  // phase D2: Chol
   double* Sd = h->d_S.as<double>();
   if (h->tiled) {
     const TileChol& TC = h->TC;
-    const size_t smem = sizeof(double) * 2 * kTS * kTLd;
+    const size_t smem = sizeof(double) * kPanelSmemDoubles;
     if (factor) {
       cudaMemsetAsync(TC.T, 0, h->tc_T_bytes, h->stream);
       LAUNCH(h, bsr_to_tiles_kernel, (unsigned)((h->nnzb * 9 + (long long)TC.nT * kTS + 255) / 256), 256, h->P, TC, h->d_S.as<double>(), st);
+      bool first_level = true;
       for (const auto& L : h->tc_levels) {   // factorisation, one level of the elimination tree at a time
-        LAUNCH_SMEM(h, tile_panel_kernel, L.npan, 256, sizeof(double) * kPanelSmemDoubles, TC, L.pan_begin, st);
+        if (first_level || L.npan_tiles > 0) LAUNCH_SMEM(h, tile_panel_kernel, L.npan, 256, smem, TC, L.pan_begin, first_level ? 1 : 0, st);
+        first_level = false;
         if (L.nupd > 0) LAUNCH_SMEM(h, tile_syrk_kernel, L.nupd, 256, smem, TC, L.upd_begin, st);
       }
     }
@@ -614,7 +616,7 @@ int bsnls_create(const bsnls_options* options, bsnls_handle** out) {
   if ((e = cudaFuncSetAttribute(chunk_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, syrk_smem_bytes(kChunkSlots))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(chunk_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fused_smem_bytes(kChunkSlots))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   if ((e = cudaFuncSetAttribute(tile_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * kPanelSmemDoubles))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
-  if ((e = cudaFuncSetAttribute(tile_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * 2 * kTS * kTLd))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
+  if ((e = cudaFuncSetAttribute(tile_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * kPanelSmemDoubles))) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   for (auto& ev : h->pev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete h; return BSNLS_ERR_CUDA; }
   *out = h;
   return BSNLS_OK;
@@ -1320,7 +1322,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   // ---- tile-sparse Cholesky: symbolic factorisation at tile granularity (structure only; fixed per problem) ----
   // A tile holds kTileBlocks = 21 f-blocks (63 unknowns, the 64th row/column is an identity pad), so tiles never cut a block.
   std::vector<long long> tc_tile_off; std::vector<int> tc_col_rows; long long tc_tiles = 0;
-  std::vector<int> tc_pan_k, tc_pan_x, tc_upd_ptr, tc_fw_ptr, tc_fw_row, tc_fw_tail, tc_lev_cols;
+  std::vector<int> tc_pan_k, tc_pan_x, tc_upd_ptr, tc_upd_fac, tc_fw_ptr, tc_fw_row, tc_fw_tail, tc_lev_cols;
   std::vector<long long> tc_upd_dst, tc_upd_a, tc_upd_b, tc_fw_src; std::vector<int> tc_fw_k;
   std::vector<int> tc_bw_ptr, tc_bw_col, tc_bw_tail, tc_bw_i, tc_roots; std::vector<long long> tc_bw_src;
   h->tc_col_ptr.clear(); h->tc_levels.clear();
@@ -1367,17 +1369,19 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       for (int lv = 0; lv < nlev; ++lv) {
         bsnls_handle::TcLevel L{};
         L.col_begin = (int)tc_lev_cols.size(); L.pan_begin = (int)tc_pan_k.size(); L.upd_begin = (int)tc_upd_ptr.size() - 1; L.fw_begin = (int)tc_fw_ptr.size() - 1;
-        struct U { long long key; int k; }; std::vector<U> us; struct F { int row, k; }; std::vector<F> fs;
+        struct U { long long key; int k; }; std::vector<U> us;   // key: destinations that are factored afterwards first, then (row, column)
+        const long long kPlain = 1LL << 62; struct F { int row, k; }; std::vector<F> fs;
         for (int k : by_level[lv]) {
           tc_lev_cols.push_back(k);
           const int a = (int)col[k].size();
           if (a == 0) { tc_pan_k.push_back(k); tc_pan_x.push_back(-1); }
-          for (int x = 0; x < a; ++x) { tc_pan_k.push_back(k); tc_pan_x.push_back(h->tc_col_ptr[k] + x); fs.push_back({col[k][x], k}); for (int y2 = 0; y2 <= x; ++y2) us.push_back({(long long)col[k][x] * nT + col[k][y2], k}); }
+          for (int x = 0; x < a; ++x) { tc_pan_k.push_back(k); tc_pan_x.push_back(h->tc_col_ptr[k] + x); fs.push_back({col[k][x], k}); for (int y2 = 0; y2 <= x; ++y2) us.push_back({(long long)col[k][x] * nT + col[k][y2] + ((y2 == x && level[col[k][x]] == lv + 1) ? 0 : kPlain), k}); }
         }
         std::stable_sort(us.begin(), us.end(), [](const U& a2, const U& b2) { return a2.key < b2.key; });
         for (size_t q = 0; q < us.size(); ++q) {
-          const int i = (int)(us[q].key / nT), j = (int)(us[q].key % nT), k = us[q].k;
-          if (q == 0 || us[q].key != us[q - 1].key) { if (q) tc_upd_ptr.push_back((int)tc_upd_a.size()); tc_upd_dst.push_back(tc_tile_off[(size_t)i * nT + j]); }
+          const bool fac = us[q].key < kPlain; const long long key = fac ? us[q].key : us[q].key - kPlain;
+          const int i = (int)(key / nT), j = (int)(key % nT), k = us[q].k;
+          if (q == 0 || us[q].key != us[q - 1].key) { if (q) tc_upd_ptr.push_back((int)tc_upd_a.size()); tc_upd_dst.push_back(tc_tile_off[(size_t)i * nT + j]); tc_upd_fac.push_back(fac ? i : -1); }
           tc_upd_a.push_back(tc_tile_off[(size_t)i * nT + k]); tc_upd_b.push_back(tc_tile_off[(size_t)j * nT + k]);
         }
         if (!us.empty()) tc_upd_ptr.push_back((int)tc_upd_a.size());
@@ -1388,6 +1392,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
         }
         if (!fs.empty()) tc_fw_ptr.push_back((int)tc_fw_src.size());
         L.ncols = (int)tc_lev_cols.size() - L.col_begin; L.npan = (int)tc_pan_k.size() - L.pan_begin;
+        L.npan_tiles = 0; for (int q = L.pan_begin; q < L.pan_begin + L.npan; ++q) L.npan_tiles += tc_pan_x[q] >= 0 ? 1 : 0;
         L.nupd = (int)tc_upd_ptr.size() - 1 - L.upd_begin; L.nfw = (int)tc_fw_ptr.size() - 1 - L.fw_begin;
         L.bw_begin = (int)tc_bw_ptr.size() - 1;
         auto& bw = bw_by_level[lv];       // already grouped by destination column (k ascending), rows ascending
@@ -1399,6 +1404,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
         if (!bw.empty()) tc_bw_ptr.push_back((int)tc_bw_src.size());
         L.nbw = (int)tc_bw_ptr.size() - 1 - L.bw_begin;
         h->tc_levels.push_back(L);
+        if (std::getenv("BSNLS_DEBUG")) std::fprintf(stderr, "[bsnls]   level %d: %d columns, %d panel CTAs, %d update tiles (%d products)\n", lv, L.ncols, L.npan, L.nupd, (int)tc_upd_a.size() - tc_upd_ptr[L.upd_begin]);
       }
     }
   }
@@ -1421,13 +1427,13 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   if (h->tiled) {
     const int nT = (h->nf + kTileBlocks - 1) / kTileBlocks;
     if (tc_col_rows.empty()) tc_col_rows.push_back(0);
-    if (tc_upd_dst.empty()) { tc_upd_dst.push_back(0); tc_upd_a.push_back(0); tc_upd_b.push_back(0); }
+    if (tc_upd_dst.empty()) { tc_upd_dst.push_back(0); tc_upd_fac.push_back(-1); tc_upd_a.push_back(0); tc_upd_b.push_back(0); }
     if (tc_fw_row.empty()) { tc_fw_row.push_back(0); tc_fw_tail.push_back(0); tc_fw_src.push_back(0); tc_fw_k.push_back(0); }
     if (tc_bw_col.empty()) { tc_bw_col.push_back(0); tc_bw_tail.push_back(0); tc_bw_src.push_back(0); tc_bw_i.push_back(0); }
     h->tc_nroots = (int)tc_roots.size();
     CK(upload(h->d_tc_bw_ptr, tc_bw_ptr, s)); CK(upload(h->d_tc_bw_col, tc_bw_col, s)); CK(upload(h->d_tc_bw_tail, tc_bw_tail, s)); CK(upload(h->d_tc_bw_src, tc_bw_src, s));
     CK(upload(h->d_tc_bw_i, tc_bw_i, s)); CK(upload(h->d_tc_roots, tc_roots, s));
-    CK(upload(h->d_tc_pan_k, tc_pan_k, s)); CK(upload(h->d_tc_pan_x, tc_pan_x, s)); CK(upload(h->d_tc_upd_ptr, tc_upd_ptr, s)); CK(upload(h->d_tc_upd_dst, tc_upd_dst, s));
+    CK(upload(h->d_tc_pan_k, tc_pan_k, s)); CK(upload(h->d_tc_pan_x, tc_pan_x, s)); CK(upload(h->d_tc_upd_ptr, tc_upd_ptr, s)); CK(upload(h->d_tc_upd_fac, tc_upd_fac, s)); CK(upload(h->d_tc_upd_dst, tc_upd_dst, s));
     CK(upload(h->d_tc_upd_a, tc_upd_a, s)); CK(upload(h->d_tc_upd_b, tc_upd_b, s)); CK(upload(h->d_tc_fw_ptr, tc_fw_ptr, s)); CK(upload(h->d_tc_fw_row, tc_fw_row, s));
     CK(upload(h->d_tc_fw_tail, tc_fw_tail, s)); CK(upload(h->d_tc_fw_src, tc_fw_src, s)); CK(upload(h->d_tc_fw_k, tc_fw_k, s)); CK(upload(h->d_tc_lev_cols, tc_lev_cols, s));
     CK(upload(h->d_tc_tile_off, tc_tile_off, s)); CK(upload(h->d_tc_col_ptr, h->tc_col_ptr, s)); CK(upload(h->d_tc_col_rows, tc_col_rows, s));
@@ -1470,6 +1476,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     h->TC.pan_x = h->d_tc_pan_x.as<int>();
     h->TC.upd_ptr = h->d_tc_upd_ptr.as<int>();
     h->TC.upd_dst = h->d_tc_upd_dst.as<long long>();
+    h->TC.upd_fac = h->d_tc_upd_fac.as<int>();
     h->TC.upd_a = h->d_tc_upd_a.as<long long>();
     h->TC.upd_b = h->d_tc_upd_b.as<long long>();
     h->TC.fw_ptr = h->d_tc_fw_ptr.as<int>();

@@ -34,7 +34,7 @@ struct TileChol {
   // level schedule (see set_problem)
   const int* lev_cols;         // tile columns grouped by level
   const int* pan_k; const int* pan_x;   // panel CTAs: column, index into col_rows (-1: the column has no tile below the diagonal)
-  const int* upd_ptr; const long long* upd_dst; const long long* upd_a; const long long* upd_b;   // update destinations and their source tile pairs
+  const int* upd_ptr; const int* upd_fac; const long long* upd_dst; const long long* upd_a; const long long* upd_b;   // update destinations and their source tile pairs
   const int* fw_ptr; const int* fw_row; const int* fw_tail; const long long* fw_src; const int* fw_k;   // forward substitution
   const int* bw_ptr; const int* bw_col; const int* bw_tail; const long long* bw_src; const int* bw_i; const int* roots;   // backward substitution
 };
@@ -89,59 +89,32 @@ __device__ __forceinline__ void tile_abt(const double* __restrict__ As, const do
   }
 }
 
-// ---- panel: potrf of the diagonal tile, inverse of its factor, trsm of one tile below it ----
-// One CTA per non-zero tile below the diagonal (at least one CTA). Every CTA factors the 64x64 diagonal tile itself --
-// the same arithmetic, so the same bits, and no dependency between CTAs -- then multiplies its own tile:
-// L(i,k) = A(i,k) L_kk^-T = A(i,k) W^T with W = L_kk^-1. CTA 0 also stores W (the solve needs it).
-// The factorisation is right-looking on 4x4 register blocks (thread (ty, tx) owns rows 4ty.., columns 4tx..), four pivots
-// per step: the owner of the diagonal block factors it in registers and publishes the inverse of that 4x4 factor; the
-// threads of the block column multiply their blocks by it (the panel), and the rest of the matrix gets a rank-4 update.
-// The same row operations are applied to an identity, which turns it into W = L_kk^-1 in the same sweep: blocks right of
-// the pivot column update A entries, blocks left of it update W entries. Two barriers per four pivots.
-constexpr int kPanelSmemDoubles = 2 * kTS * kTLd + 16 + kTS * 4 + 4 * kTS;
+// ---- potrf of a diagonal tile together with the inverse of its factor ----
+// All 256 threads of a CTA. The factorisation is right-looking on 4x4 register blocks (thread (ty, tx) owns rows 4ty..,
+// columns 4tx..), four pivots per step: the owner of the diagonal block factors it in registers and publishes the inverse
+// of that 4x4 factor; the threads of the block column multiply their blocks by it (the panel), and the rest of the matrix
+// gets a rank-4 update. The same row operations are applied to an identity, which turns it into W = L_kk^-1 in the same
+// sweep: blocks right of the pivot column update A entries, blocks left of it update W entries. Two barriers per four
+// pivots. G: the tile (lower triangle), column-major with pitch ld, global or shared memory. W goes to Ws (shared, pitch
+// kTLd) and / or Wg (global, pitch kTS) when given. Returns true in the thread that met a non-positive pivot.
+constexpr int kFactorScratchDoubles = 16 + kTS * 4 + 4 * kTS;
+constexpr int kPanelSmemDoubles = 2 * kTS * kTLd + kFactorScratchDoubles;
 #ifdef PANEL_PROF
 __device__ long long g_panel_prof[80];
 #endif
-__global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_begin, LMState* st) {
-  extern __shared__ __align__(16) double sm[];
-  double* As = sm;                          // A(i,k), column-major, pitch kTLd
-  double* Bs = As + kTS * kTLd;             // W, column-major, pitch kTLd
-  double* sLi = Bs + kTS * kTLd;            // inverse of the 4x4 diagonal factor, row-major (lower)
+__device__ __forceinline__ bool tile_potrf_inv(const double* __restrict__ G, int ld, double* __restrict__ Ws, double* __restrict__ Wg, double* __restrict__ scratch) {
+  double* sLi = scratch;                    // inverse of the 4x4 diagonal factor, row-major (lower)
   double* sPan = sLi + 16;                  // the panel: L(r, 4 jb + c) at sPan[((r & 3) * 16 + (r >> 2)) * 4 + c]: the rows 4 ty + i of
                                             // the 16 block rows of a warp are adjacent (no bank conflicts)
   double* sWrow = sPan + kTS * 4;           // final rows 4 jb.. of W: sWrow[i * 64 + c]
-  __shared__ int failed, sGate;
-  // another CTA of this launch may set lin_fail while this one starts: latch the gate once per CTA so that all of its
-  // warps take the same branch (a failing column only ever stores garbage that nobody uses)
-  if (threadIdx.x == 0) sGate = (!gate_run(st) || st->lin_fail) ? 1 : 0;
-  __syncthreads();
-  if (sGate) return;
   // a warp holds two block columns (tx) and all block rows (ty): at any step it is either left of the pivot column (W
   // updates only) or right of it (A updates only), so the two roles do not serialise inside a warp
   const int tid = threadIdx.x, tx = tid >> 4, ty = tid & 15;
-  const int k = TC.pan_k[pan_begin + blockIdx.x], px = TC.pan_x[pan_begin + blockIdx.x];
-  const int na = px >= 0 ? 1 : 0;
-  const bool first = px < 0 || px == TC.col_ptr[k];   // this CTA stores W of its column
-  const double* G = TC.T + TC.tile_off[(long long)k * TC.nT + k];
-  double* Gi = nullptr;
-  if (na > 0) {   // start fetching this CTA's tile; it is not needed before the product
-    Gi = TC.T + TC.tile_off[(long long)TC.col_rows[px] * TC.nT + k];
-    for (int e = tid; e < kTileDoubles / 2; e += 256) {
-      const int c = e >> 5, r2 = e & 31;
-      const unsigned dst = (unsigned)__cvta_generic_to_shared(As + c * kTLd + 2 * r2);
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(Gi + 2 * e));
-    }
-    asm volatile("cp.async.commit_group;");
-  }
-#ifdef PANEL_PROF
-  if (tid == 255) g_panel_prof[70] = clock64();
-#endif
-  if (tid == 0) failed = 0;
   double a[4][4], w[4][4];
 #pragma unroll
   for (int c = 0; c < 4; ++c)
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { a[i][c] = ty >= tx ? G[(4 * tx + c) * kTS + 4 * ty + i] : 0.0; w[i][c] = (ty == tx && i == c) ? 1.0 : 0.0; }
+    for (int i = 0; i < 4; ++i) { a[i][c] = ty >= tx ? G[(4 * tx + c) * ld + 4 * ty + i] : 0.0; w[i][c] = (ty == tx && i == c) ? 1.0 : 0.0; }
   bool bad = false;
 #pragma unroll 1
   for (int jb = 0; jb < kTS / 4; ++jb) {
@@ -172,7 +145,7 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_be
 #ifdef PANEL_PROF
     if (tid == 255) g_panel_prof[4 * jb] = clock64();
 #endif
-    if (ty >= jb && (tx == jb || ty == jb)) {
+    if (ty >= jb && (tx == jb || (ty == jb && tx < jb))) {
       double Li[4][4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) { const double2 u0 = reinterpret_cast<const double2*>(sLi)[2 * i], u1 = reinterpret_cast<const double2*>(sLi)[2 * i + 1]; Li[i][0] = u0.x; Li[i][1] = u0.y; Li[i][2] = u1.x; Li[i][3] = u1.y; }
@@ -191,7 +164,7 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_be
           reinterpret_cast<double2*>(sPan)[2 * (16 * i + ty) + 1] = make_double2(l[2], l[3]);
         }
       }
-      if (ty == jb) {              // rows 4 jb.. of W are final: W = Li W
+      if (ty == jb) {              // rows 4 jb.. of W are final: W = Li W (block columns right of the pivot hold zeros)
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           double f[4];
@@ -239,18 +212,57 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_be
 #ifdef PANEL_PROF
   if (tid == 255) g_panel_prof[64] = clock64();
 #endif
-  if (bad) failed = 1;
-  // W (lower triangular) for the product and, from CTA 0, for the triangular solves
-  {
-    double* Wk = TC.W + (size_t)k * kTileDoubles;
 #pragma unroll
-    for (int c = 0; c < 4; ++c)
+  for (int c = 0; c < 4; ++c)
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const double v = (ty > tx || (ty == tx && i >= c)) ? w[i][c] : 0.0;
-        Bs[(4 * tx + c) * kTLd + 4 * ty + i] = v;
-        if (first) Wk[(4 * tx + c) * kTS + 4 * ty + i] = v;
+    for (int i = 0; i < 4; ++i) {
+      const double v = (ty > tx || (ty == tx && i >= c)) ? w[i][c] : 0.0;
+      if (Ws) Ws[(4 * tx + c) * kTLd + 4 * ty + i] = v;
+      if (Wg) Wg[(4 * tx + c) * kTS + 4 * ty + i] = v;
+    }
+  return bad;
+}
+
+// ---- panel: L(i,k) = A(i,k) L_kk^-T = A(i,k) W^T with W = L_kk^-1, one CTA per non-zero tile below the diagonal ----
+// factor_here (the first level, whose diagonal tiles nobody updates): every CTA of a column factors the diagonal tile itself
+// -- the same arithmetic, so the same bits, and no dependency between CTAs -- and the first one stores W (the solve needs
+// it). On every other level W was left by the update kernel of the level before (see tile_syrk_kernel) and is only loaded.
+__global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_begin, int factor_here, LMState* st) {
+  extern __shared__ __align__(16) double sm[];
+  double* As = sm;                          // A(i,k), column-major, pitch kTLd
+  double* Bs = As + kTS * kTLd;             // W, column-major, pitch kTLd
+  __shared__ int failed, sGate;
+  // another CTA of this launch may set lin_fail while this one starts: latch the gate once per CTA so that all of its
+  // warps take the same branch (a failing column only ever stores garbage that nobody uses)
+  if (threadIdx.x == 0) { sGate = (!gate_run(st) || st->lin_fail) ? 1 : 0; failed = 0; }
+  __syncthreads();
+  if (sGate) return;
+  const int tid = threadIdx.x;
+  const int k = TC.pan_k[pan_begin + blockIdx.x], px = TC.pan_x[pan_begin + blockIdx.x];
+  const int na = px >= 0 ? 1 : 0;
+  if (na == 0 && !factor_here) return;
+  const bool first = px < 0 || px == TC.col_ptr[k];   // this CTA stores W of its column
+  double* Gi = nullptr;
+  if (na > 0) {   // start fetching this CTA's tile; it is not needed before the product
+    Gi = TC.T + TC.tile_off[(long long)TC.col_rows[px] * TC.nT + k];
+    const double* Wk = TC.W + (size_t)k * kTileDoubles;
+    for (int e = tid; e < kTileDoubles / 2; e += 256) {
+      const int c = e >> 5, r2 = e & 31;
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(As + c * kTLd + 2 * r2);
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(Gi + 2 * e));
+      if (!factor_here) {
+        const unsigned dw = (unsigned)__cvta_generic_to_shared(Bs + c * kTLd + 2 * r2);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dw), "l"(Wk + 2 * e));
       }
+    }
+    asm volatile("cp.async.commit_group;");
+  }
+#ifdef PANEL_PROF
+  if (tid == 255) g_panel_prof[70] = clock64();
+#endif
+  if (factor_here) {
+    const bool bad = tile_potrf_inv(TC.T + TC.tile_off[(long long)k * TC.nT + k], kTS, Bs, first ? TC.W + (size_t)k * kTileDoubles : nullptr, Bs + kTS * kTLd);
+    if (bad) failed = 1;
   }
   if (na > 0) asm volatile("cp.async.wait_group 0;");
   __syncthreads();
@@ -272,13 +284,21 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_be
 }
 
 // ---- syrk: A(i,j) -= sum_k L(i,k) L(j,k)^T over the source columns of this level; one CTA per destination tile ----
-__global__ void __launch_bounds__(256) tile_syrk_kernel(TileChol TC, int upd_begin, const LMState* st) {
+// A destination that is the diagonal tile of a column of the NEXT level is final after this update (a column's level is
+// one above its last child's), so its CTA goes straight on to factor it and leaves W = L_jj^-1 for the next panel launch:
+// the 64-pivot chain then runs beside the other updates of the level instead of in front of the next one. Those
+// destinations come first in the level's list.
+__global__ void __launch_bounds__(256) tile_syrk_kernel(TileChol TC, int upd_begin, LMState* st) {
   extern __shared__ __align__(16) double sm[];
-  if (!gate_run(st) || st->lin_fail) return;
+  __shared__ int failed, sGate;
+  if (threadIdx.x == 0) { sGate = (!gate_run(st) || st->lin_fail) ? 1 : 0; failed = 0; }
+  __syncthreads();
+  if (sGate) return;
   double* As = sm; double* Bs = sm + kTS * kTLd;
   const int d = upd_begin + blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tg = lane & 3;
   double* C = TC.T + TC.upd_dst[d];
+  const int fac = TC.upd_fac[d];        // tile column to factor afterwards, or -1
   double cv[8][2];                      // the destination entries, fetched alongside the operands
 #pragma unroll
   for (int J = 0; J < 8; ++J) { cv[J][0] = C[(8 * J + 2 * tg) * kTS + 8 * warp + g]; cv[J][1] = C[(8 * J + 2 * tg + 1) * kTS + 8 * warp + g]; }
@@ -292,11 +312,24 @@ __global__ void __launch_bounds__(256) tile_syrk_kernel(TileChol TC, int upd_beg
     tile_abt(As, oa != ob ? Bs : As, warp, lane, acc);
     __syncthreads();
   }
+  if (fac < 0) {
+#pragma unroll
+    for (int J = 0; J < 8; ++J) {
+      C[(8 * J + 2 * tg) * kTS + 8 * warp + g] = cv[J][0] - acc[J][0];
+      C[(8 * J + 2 * tg + 1) * kTS + 8 * warp + g] = cv[J][1] - acc[J][1];
+    }
+    return;
+  }
+  // the final diagonal tile stays on chip: factor it, keep only W (nothing reads L_jj itself)
 #pragma unroll
   for (int J = 0; J < 8; ++J) {
-    C[(8 * J + 2 * tg) * kTS + 8 * warp + g] = cv[J][0] - acc[J][0];
-    C[(8 * J + 2 * tg + 1) * kTS + 8 * warp + g] = cv[J][1] - acc[J][1];
+    As[(8 * J + 2 * tg) * kTLd + 8 * warp + g] = cv[J][0] - acc[J][0];
+    As[(8 * J + 2 * tg + 1) * kTLd + 8 * warp + g] = cv[J][1] - acc[J][1];
   }
+  __syncthreads();
+  if (tile_potrf_inv(As, kTLd, nullptr, TC.W + (size_t)fac * kTileDoubles, Bs + kTS * kTLd)) failed = 1;
+  __syncthreads();
+  if (threadIdx.x == 0 && failed) st->lin_fail = 1;
 }
 
 // ---- substitutions with the tile factor, level by level; 256-thread CTAs ----

@@ -32,21 +32,22 @@ int main(int argc, char** argv) {
     for (int x = 0; x < na; ++x) px[x] = x;
     up.push_back(0);
     for (int i = 1; i < nT; ++i) for (int j = 1; j <= i; ++j) { ud.push_back(off[(size_t)i * nT + j]); ua.push_back(off[(size_t)i * nT]); ub.push_back(off[(size_t)j * nT]); up.push_back((int)ua.size()); }
-    int *dpk, *dpx, *dup; long long *dud, *dua, *dub;
+    int *dpk, *dpx, *dup, *duf; long long *dud, *dua, *dub;
+    std::vector<int> uf(ud.size() + 1, -1); cudaMalloc(&duf, uf.size() * 4); cudaMemcpy(duf, uf.data(), uf.size() * 4, cudaMemcpyHostToDevice); TC.upd_fac = duf;
     cudaMalloc(&dpk, pk.size() * 4); cudaMalloc(&dpx, px.size() * 4); cudaMalloc(&dup, up.size() * 4);
     cudaMalloc(&dud, (ud.size() + 1) * 8); cudaMalloc(&dua, (ua.size() + 1) * 8); cudaMalloc(&dub, (ub.size() + 1) * 8);
     cudaMemcpy(dpk, pk.data(), pk.size() * 4, cudaMemcpyHostToDevice); cudaMemcpy(dpx, px.data(), px.size() * 4, cudaMemcpyHostToDevice); cudaMemcpy(dup, up.data(), up.size() * 4, cudaMemcpyHostToDevice);
     if (!ud.empty()) { cudaMemcpy(dud, ud.data(), ud.size() * 8, cudaMemcpyHostToDevice); cudaMemcpy(dua, ua.data(), ua.size() * 8, cudaMemcpyHostToDevice); cudaMemcpy(dub, ub.data(), ub.size() * 8, cudaMemcpyHostToDevice); }
     TC.pan_k = dpk; TC.pan_x = dpx; TC.upd_ptr = dup; TC.upd_dst = dud; TC.upd_a = dua; TC.upd_b = dub;
   }
-  const size_t psm = sizeof(double) * kPanelSmemDoubles, ssm = sizeof(double) * 2 * kTS * kTLd;
+  const size_t psm = sizeof(double) * kPanelSmemDoubles, ssm = psm;
   cudaFuncSetAttribute(tile_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psm);
   cudaFuncSetAttribute(tile_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssm);
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
   float ms;
   for (int pass = 0; pass < 2; ++pass) {
     cudaEventRecord(e0);
-    for (int r = 0; r < reps; ++r) { cudaMemcpyAsync(dT, dT0, T.size() * 8, cudaMemcpyDeviceToDevice); tile_panel_kernel<<<na > 0 ? na : 1, 256, psm>>>(TC, 0, dst); }
+    for (int r = 0; r < reps; ++r) { cudaMemcpyAsync(dT, dT0, T.size() * 8, cudaMemcpyDeviceToDevice); tile_panel_kernel<<<na > 0 ? na : 1, 256, psm>>>(TC, 0, 1, dst); }
     cudaEventRecord(e1); cudaEventSynchronize(e1); cudaEventElapsedTime(&ms, e0, e1);
   }
   float base;
@@ -59,7 +60,7 @@ int main(int argc, char** argv) {
     printf("syrk (%d pairs): %.2f us per launch\n", na * (na + 1) / 2, 1e3 * ms / reps);
   }
   // check W L = I and L(1,0) L_kk^T = A(1,0) using the host factor
-  cudaMemcpyAsync(dT, dT0, T.size() * 8, cudaMemcpyDeviceToDevice); tile_panel_kernel<<<na > 0 ? na : 1, 256, psm>>>(TC, 0, dst);
+  cudaMemcpyAsync(dT, dT0, T.size() * 8, cudaMemcpyDeviceToDevice); tile_panel_kernel<<<na > 0 ? na : 1, 256, psm>>>(TC, 0, 1, dst);
   std::vector<double> W(kTileDoubles), L(64 * 64, 0.0), X(kTileDoubles);
   cudaMemcpy(W.data(), dW, kTileDoubles * 8, cudaMemcpyDeviceToHost);
   for (int j = 0; j < 64; ++j) { double d = T[j * 64 + j]; for (int m = 0; m < j; ++m) d -= L[j * 64 + m] * L[j * 64 + m]; d = std::sqrt(d); L[j * 64 + j] = d;
@@ -72,7 +73,7 @@ int main(int argc, char** argv) {
 #ifdef PANEL_PROF
   { long long pr[80]; cudaMemcpyFromSymbol(pr, g_panel_prof, sizeof(pr));
     printf("start->step0 %lld, steps:", pr[0] - pr[70]); for (int j = 4; j <= 64; j += 4) printf(" %lld", pr[j] - pr[j - 4]); printf(", epilogue %lld\n", pr[65] - pr[64]);
-    printf("step 5: diag block %lld cycles; observer: barrier -> end of the update %lld\n", pr[71], pr[74] - pr[20]); }
+    printf("step 5: diag block %lld cycles; observer (thread 255): barrier 1 -> before barrier 2 %lld, wait in barrier 2 (the panel threads) %lld, update %lld, update end -> next barrier 1 %lld\n", pr[71], pr[72] - pr[20], pr[73] - pr[72], pr[74] - pr[73], pr[24] - pr[74]); }
 #endif
   LMState hs; cudaMemcpy(&hs, dst, sizeof(hs), cudaMemcpyDeviceToHost); printf("lin_fail %d, cuda: %s\n", hs.lin_fail, cudaGetErrorString(cudaGetLastError()));
   return 0;
