@@ -135,7 +135,7 @@ struct bsnls_handle {
   std::vector<int> pair_a, pair_b;
   std::vector<int> gd_row, gd_col;
   bool tiled = false; std::vector<int> f_api;   // tile-sparse Cholesky; internal f position -> API (program-order) position
-  TileChol TC{}; std::vector<int> tc_col_ptr; DevMem d_tc_tile_off, d_tc_col_ptr, d_tc_col_rows, d_tc_T, d_tc_W, d_tc_b; size_t tc_T_bytes = 0;
+  TileChol TC{}; std::vector<int> tc_col_ptr, tc_blk_slot; int tc_nT = 0; DevMem d_tc_blk_slot, d_tc_slot_blk, d_tc_tile_off, d_tc_col_ptr, d_tc_col_rows, d_tc_T, d_tc_W, d_tc_b; size_t tc_T_bytes = 0;
   struct TcLevel { int col_begin, ncols, pan_begin, npan, npan_tiles, upd_begin, nupd, fw_begin, nfw, bw_begin, nbw; };   // one level of the elimination tree
   std::vector<TcLevel> tc_levels;
   DevMem d_tc_pan_k, d_tc_pan_x, d_tc_upd_ptr, d_tc_upd_fac, d_tc_upd_dst, d_tc_upd_a, d_tc_upd_b, d_tc_fw_ptr, d_tc_fw_row, d_tc_fw_tail, d_tc_fw_src, d_tc_fw_k, d_tc_lev_cols, d_tc_bw_ptr, d_tc_bw_col, d_tc_bw_tail, d_tc_bw_src, d_tc_bw_i, d_tc_roots; int tc_nroots = 0;
@@ -872,8 +872,8 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   const int nobs_local = h->nobs;
   // ---- internal order of the f-blocks. The API order (h->fblocks, program order) keeps the two blocks of a pose far
   // apart, which makes the reduced system's envelope nearly full. For the tile-sparse factorisation the blocks are
-  // renumbered with reverse Cuthill-McKee on the block graph (pose pairs + generic-factor cliques): a trajectory becomes
-  // a band, loop closures a few long rows. From here on fpos[] is the INTERNAL position; f_api[] maps back.
+  // renumbered by a nested dissection of the block graph (pose pairs + generic-factor cliques). From here on fpos[] is
+  // the INTERNAL position; f_api[] maps back.
   h->f_api.resize(h->nf); for (int k = 0; k < h->nf; ++k) h->f_api[k] = k;
   if (h->tiled) {
     std::vector<std::vector<int>> adj(h->nf);
@@ -889,33 +889,109 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
         for (int b1 = 0; b1 < nbk; ++b1) for (int b2 = 0; b2 < b1; ++b2) link(fpos[G->blocks[i * nbk + b1]], fpos[G->blocks[i * nbk + b2]]);
     }
     for (auto& v : adj) { std::sort(v.begin(), v.end()); v.erase(std::unique(v.begin(), v.end()), v.end()); }
-    std::vector<int> rank(h->nf, -1), orderv; orderv.reserve(h->nf);
-    std::vector<char> seen(h->nf, 0);
-    auto bfs = [&](int start, std::vector<int>& out, bool mark) {
-      std::vector<char> local; std::vector<char>& sn = mark ? seen : local; if (!mark) local.assign(h->nf, 0);
-      const size_t first = out.size(); out.push_back(start); sn[start] = 1;
-      for (size_t q = first; q < out.size(); ++q) {
-        std::vector<int> nb2; for (int v : adj[out[q]]) if (!sn[v] && (mark || !seen[v])) { sn[v] = 1; nb2.push_back(v); }
-        std::sort(nb2.begin(), nb2.end(), [&](int x, int y2) { return adj[x].size() != adj[y2].size() ? adj[x].size() < adj[y2].size() : x < y2; });
-        out.insert(out.end(), nb2.begin(), nb2.end());
+    // Two candidate orders, each with the slot (position in the padded sequence, kTileBlocks per tile) of every block; the
+    // one whose tile-level symbolic factorisation is cheaper wins (BSNLS_ORDER=graph|band forces one).
+    struct Candidate { std::vector<int> order, slot; int nT = 0, levels = 0; long long tiles = 0, products = 0; double cost = 0.0; };
+    int nd_leaf = kNdLeaf;                          // BSNLS_ND_LEAF: tuning knob (tiles per leaf of the dissection)
+    if (const char* ev = std::getenv("BSNLS_ND_LEAF")) nd_leaf = std::max(1, std::atoi(ev));
+    auto evaluate = [&](Candidate& c) {             // levels of the elimination tree and tile products, as the factorisation below finds them
+      std::vector<int> tile(h->nf); for (int k = 0; k < h->nf; ++k) tile[c.order[k]] = c.slot[k] / kTileBlocks;
+      std::vector<std::vector<int>> col(c.nT);
+      for (int v = 0; v < h->nf; ++v) for (int u : adj[v]) if (tile[u] > tile[v]) col[tile[v]].push_back(tile[u]);
+      std::vector<int> level(c.nT, 0); c.levels = 0; c.tiles = 0; c.products = 0;
+      for (int k = 0; k < c.nT; ++k) {
+        std::sort(col[k].begin(), col[k].end()); col[k].erase(std::unique(col[k].begin(), col[k].end()), col[k].end());
+        const long long a = (long long)col[k].size(); c.tiles += 1 + a; c.products += a * (a + 1) / 2; c.levels = std::max(c.levels, level[k] + 1);
+        if (a > 0) { const int par = col[k][0]; col[par].insert(col[par].end(), col[k].begin() + 1, col[k].end()); level[par] = std::max(level[par], level[k] + 1); }
       }
+      c.cost = 30.0 * c.levels + 0.03 * (double)c.products;   // microseconds: a launch pair per level is latency, the products are throughput
     };
-    for (int v0 = 0; v0 < h->nf; ++v0) {
-      if (seen[v0]) continue;
-      std::vector<int> probe; bfs(v0, probe, false);           // pseudo-peripheral start: the far end of a sweep from v0
-      std::vector<int> probe2; bfs(probe.back(), probe2, false);
-      bfs(probe2.back(), orderv, true);
-    }
-    std::reverse(orderv.begin(), orderv.end());
-    // Nested dissection at tile granularity on top of the RCM line. A tile holds kTileBlocks consecutive blocks; the
-    // line of tiles is cut in the middle by a separator as wide as the band (plus one endpoint of every long edge --
-    // loop closures -- that crosses the cut), the halves are ordered recursively and the separator goes last. Tile
-    // columns of different leaves are then independent, so the factorisation advances level by level of the
-    // elimination tree instead of one tile column at a time.
-    {
+    // (a) Nested dissection of the block graph (George's automatic dissection: the separator is a level set of a
+    // breadth-first sweep from a pseudo-peripheral block, picked small and near the middle; blocks of it without a
+    // neighbour on the far side go back to the near side). Done on blocks, not tiles: a loop closure costs the separator
+    // one 3-block, not a whole tile, so a trajectory with closures every few keyframes keeps separators of a tile or two.
+    // Every region (leaf or separator) then starts on a tile boundary -- the slots left over are identity padding -- so
+    // that tile columns of different leaves stay independent.
+    auto order_graph = [&](Candidate& c) {
+      std::vector<int>& orderv = c.order; orderv.clear(); orderv.reserve(h->nf);
+      std::vector<int> region_end;
+      const int leaf_blocks = nd_leaf * kTileBlocks;
+      std::vector<int> in_set(h->nf, -1), lev(h->nf, 0), vis(h->nf, 0); int vis_id = 0, next_id = 0;
+      auto bfs = [&](int start, int id, std::vector<int>& out) {   // Cuthill-McKee sweep over the blocks of set `id`
+        ++vis_id; out.clear(); out.push_back(start); vis[start] = vis_id; lev[start] = 0;
+        for (size_t q = 0; q < out.size(); ++q) {
+          const int u = out[q]; const size_t first = out.size();
+          for (int v : adj[u]) if (in_set[v] == id && vis[v] != vis_id) { vis[v] = vis_id; lev[v] = lev[u] + 1; out.push_back(v); }
+          std::sort(out.begin() + first, out.end(), [&](int x, int y2) { return adj[x].size() != adj[y2].size() ? adj[x].size() < adj[y2].size() : x < y2; });
+        }
+      };
+      std::function<void(std::vector<int>&)> nd = [&](std::vector<int>& nodes) {
+        if (nodes.empty()) return;
+        const int id = next_id++;
+        for (int v : nodes) in_set[v] = id;
+        std::vector<int> o1, o2;
+        bfs(nodes[0], id, o1);
+        if (o1.size() < nodes.size()) {               // not connected: one component at a time
+          std::vector<int> rest; for (int v : nodes) if (vis[v] != vis_id) rest.push_back(v);
+          nd(o1); nd(rest); return;
+        }
+        bfs(o1.back(), id, o2); bfs(o2.back(), id, o1);
+        const int L = lev[o1.back()];
+        if ((int)nodes.size() <= leaf_blocks || L < 2) {
+          orderv.insert(orderv.end(), o1.rbegin(), o1.rend()); region_end.push_back((int)orderv.size()); return;
+        }
+        std::vector<int> cnt(L + 1, 0); for (int v : o1) cnt[lev[v]]++;
+        int best = 1; long long best_score = -1, below = cnt[0];
+        for (int l = 1; l < L; ++l) {
+          const long long above = (long long)o1.size() - below - cnt[l], score = 4LL * cnt[l] + std::llabs(below - above);
+          if (best_score < 0 || score < best_score) { best_score = score; best = l; }
+          below += cnt[l];
+        }
+        std::vector<int> A, B, S;
+        for (int v : o1) {
+          if (lev[v] < best) A.push_back(v);
+          else if (lev[v] > best) B.push_back(v);
+          else { bool far = false; for (int u : adj[v]) if (in_set[u] == id && lev[u] == best + 1) { far = true; break; }
+                 (far ? S : A).push_back(v); }
+        }
+        // leaves give the blocks beyond their last full tile to the separator while its last tile has room (A ends and B
+        // starts next to the separator): a tile less per leaf at no cost to the separator
+        int room = (kTileBlocks - (int)S.size() % kTileBlocks) % kTileBlocks;
+        if ((int)A.size() <= leaf_blocks && (int)A.size() > kTileBlocks) { const int r = (int)A.size() % kTileBlocks; if (r > 0 && r <= room) { S.insert(S.end(), A.end() - r, A.end()); A.resize(A.size() - r); room -= r; } }
+        if ((int)B.size() <= leaf_blocks && (int)B.size() > kTileBlocks) { const int r = (int)B.size() % kTileBlocks; if (r > 0 && r <= room) { S.insert(S.end(), B.begin(), B.begin() + r); B.erase(B.begin(), B.begin() + r); room -= r; } }
+        nd(A); nd(B);
+        orderv.insert(orderv.end(), S.begin(), S.end()); region_end.push_back((int)orderv.size());
+      };
+      std::vector<int> all(h->nf); for (int k = 0; k < h->nf; ++k) all[k] = k;
+      nd(all);
+      c.slot.assign(h->nf, 0); int slot = 0, k0 = 0;
+      for (int e : region_end) { for (int k = k0; k < e; ++k) c.slot[k] = slot + (k - k0); slot += (e - k0 + kTileBlocks - 1) / kTileBlocks * kTileBlocks; k0 = e; }
+      c.nT = slot / kTileBlocks;
+    };
+    // (b) Reverse Cuthill-McKee line (a trajectory becomes a band) cut by a nested dissection at tile granularity: the
+    // line of tiles is cut in the middle by a separator as wide as the band (plus one endpoint tile of every long edge
+    // that crosses the cut), the halves are ordered recursively and the separator goes last. No padding: the better
+    // choice for a pure band, the worse one as soon as long edges are frequent.
+    auto order_band = [&](Candidate& c) {
+      std::vector<int>& orderv = c.order; orderv.clear(); orderv.reserve(h->nf);
+      std::vector<char> seen(h->nf, 0);
+      auto bfs = [&](int start, std::vector<int>& out, bool mark) {
+        std::vector<char> local; std::vector<char>& sn = mark ? seen : local; if (!mark) local.assign(h->nf, 0);
+        const size_t first = out.size(); out.push_back(start); sn[start] = 1;
+        for (size_t q = first; q < out.size(); ++q) {
+          std::vector<int> nb2; for (int v : adj[out[q]]) if (!sn[v] && (mark || !seen[v])) { sn[v] = 1; nb2.push_back(v); }
+          std::sort(nb2.begin(), nb2.end(), [&](int x, int y2) { return adj[x].size() != adj[y2].size() ? adj[x].size() < adj[y2].size() : x < y2; });
+          out.insert(out.end(), nb2.begin(), nb2.end());
+        }
+      };
+      for (int v0 = 0; v0 < h->nf; ++v0) {
+        if (seen[v0]) continue;
+        std::vector<int> probe; bfs(v0, probe, false);           // pseudo-peripheral start: the far end of a sweep from v0
+        std::vector<int> probe2; bfs(probe.back(), probe2, false);
+        bfs(probe2.back(), orderv, true);
+      }
+      std::reverse(orderv.begin(), orderv.end());
       const int nTf = h->nf / kTileBlocks;            // full tiles; a partial last tile stays last
-      int nd_leaf = kNdLeaf;                          // BSNLS_ND_LEAF: tuning knob (tiles per leaf of the dissection)
-      if (const char* ev = std::getenv("BSNLS_ND_LEAF")) nd_leaf = std::max(1, std::atoi(ev));
       if (nTf > nd_leaf) {
         std::vector<int> pos(h->nf); for (int k = 0; k < h->nf; ++k) pos[orderv[k]] = k;
         std::vector<std::vector<int>> tadj(nTf);
@@ -946,7 +1022,22 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
         for (int k = nTf * kTileBlocks; k < h->nf; ++k) order2.push_back(orderv[k]);
         orderv.swap(order2);
       }
+      c.slot.resize(h->nf); for (int k = 0; k < h->nf; ++k) c.slot[k] = k;
+      c.nT = (h->nf + kTileBlocks - 1) / kTileBlocks;
+    };
+    Candidate cg, cb;
+    const char* force = std::getenv("BSNLS_ORDER");
+    const bool want_graph = !force || std::strcmp(force, "band") != 0, want_band = !force || std::strcmp(force, "graph") != 0;
+    if (want_graph) { order_graph(cg); evaluate(cg); }
+    if (want_band) { order_band(cb); evaluate(cb); }
+    const bool pick_graph = want_graph && (!want_band || cg.cost < cb.cost);
+    if (std::getenv("BSNLS_DEBUG")) {
+      if (want_graph) std::fprintf(stderr, "[bsnls] order 'graph': %d tile columns, %d levels, %lld tiles, %lld products (cost %.0f)%s\n", cg.nT, cg.levels, cg.tiles, cg.products, cg.cost, pick_graph ? " <- used" : "");
+      if (want_band) std::fprintf(stderr, "[bsnls] order 'band':  %d tile columns, %d levels, %lld tiles, %lld products (cost %.0f)%s\n", cb.nT, cb.levels, cb.tiles, cb.products, cb.cost, pick_graph ? "" : " <- used");
     }
+    Candidate& win = pick_graph ? cg : cb;
+    std::vector<int> rank(h->nf, -1); std::vector<int>& orderv = win.order;
+    h->tc_blk_slot = win.slot; h->tc_nT = win.nT;
     for (int k = 0; k < h->nf; ++k) { rank[orderv[k]] = k; h->f_api[k] = orderv[k]; }
     for (int b = 0; b < nb; ++b) if (fpos[b] >= 0) fpos[b] = rank[fpos[b]];
   }
@@ -1324,15 +1415,15 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   std::vector<long long> tc_tile_off; std::vector<int> tc_col_rows; long long tc_tiles = 0;
   std::vector<int> tc_pan_k, tc_pan_x, tc_upd_ptr, tc_upd_fac, tc_fw_ptr, tc_fw_row, tc_fw_tail, tc_lev_cols;
   std::vector<long long> tc_upd_dst, tc_upd_a, tc_upd_b, tc_fw_src; std::vector<int> tc_fw_k;
-  std::vector<int> tc_bw_ptr, tc_bw_col, tc_bw_tail, tc_bw_i, tc_roots; std::vector<long long> tc_bw_src;
+  std::vector<int> tc_bw_ptr, tc_bw_col, tc_bw_tail, tc_bw_i, tc_roots, tc_slot_blk; std::vector<long long> tc_bw_src;
   h->tc_col_ptr.clear(); h->tc_levels.clear();
   if (h->tiled) {
-    const int nT = (h->nf + kTileBlocks - 1) / kTileBlocks;
+    const int nT = h->tc_nT;
     std::vector<std::vector<int>> col(nT);     // non-zero tiles strictly below the diagonal, per tile column
     for (int r = 0; r < h->nf; ++r)
       for (int k = h->bsr_rowptr[r]; k < h->bsr_rowptr[r + 1]; ++k) {
         const int c = h->bsr_col[k];
-        if (c < r && r / kTileBlocks > c / kTileBlocks) col[c / kTileBlocks].push_back(r / kTileBlocks);
+        if (c < r && h->tc_blk_slot[r] / kTileBlocks > h->tc_blk_slot[c] / kTileBlocks) col[h->tc_blk_slot[c] / kTileBlocks].push_back(h->tc_blk_slot[r] / kTileBlocks);
       }
     std::vector<int> level(nT, 0);
     for (int k = 0; k < nT; ++k) {
@@ -1425,7 +1516,10 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   CK(h->d_scale.alloc(sizeof(double) * ntan)); CK(h->d_yf.alloc(sizeof(double) * nf_dim));
   CK(h->d_rhs.alloc(sizeof(double) * nf_dim)); CK(h->d_S.alloc(sizeof(double) * (h->sparse ? (size_t)h->nnzb * 9 : (size_t)nf_dim * nf_dim)));
   if (h->tiled) {
-    const int nT = (h->nf + kTileBlocks - 1) / kTileBlocks;
+    const int nT = h->tc_nT;
+    tc_slot_blk.assign((size_t)nT * kTileBlocks, -1);
+    for (int r = 0; r < h->nf; ++r) tc_slot_blk[h->tc_blk_slot[r]] = r;
+    CK(upload(h->d_tc_blk_slot, h->tc_blk_slot, s)); CK(upload(h->d_tc_slot_blk, tc_slot_blk, s));
     if (tc_col_rows.empty()) tc_col_rows.push_back(0);
     if (tc_upd_dst.empty()) { tc_upd_dst.push_back(0); tc_upd_fac.push_back(-1); tc_upd_a.push_back(0); tc_upd_b.push_back(0); }
     if (tc_fw_row.empty()) { tc_fw_row.push_back(0); tc_fw_tail.push_back(0); tc_fw_src.push_back(0); tc_fw_k.push_back(0); }
@@ -1477,6 +1571,8 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     h->TC.upd_ptr = h->d_tc_upd_ptr.as<int>();
     h->TC.upd_dst = h->d_tc_upd_dst.as<long long>();
     h->TC.upd_fac = h->d_tc_upd_fac.as<int>();
+    h->TC.blk_slot = h->d_tc_blk_slot.as<int>();
+    h->TC.slot_blk = h->d_tc_slot_blk.as<int>();
     h->TC.upd_a = h->d_tc_upd_a.as<long long>();
     h->TC.upd_b = h->d_tc_upd_b.as<long long>();
     h->TC.fw_ptr = h->d_tc_fw_ptr.as<int>();

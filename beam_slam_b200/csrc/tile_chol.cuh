@@ -3,12 +3,13 @@
 // The reduced camera system of a trajectory is banded once poses are ordered along the trajectory (plus a few long
 // rows per loop closure). It is stored as 64x64 tiles (21 f-blocks = 63 unknowns + one identity pad row each), only
 // those that are structurally non-zero after a symbolic factorisation at tile granularity (host, set_problem).
-// The tile order is a nested dissection of the band, so tile columns on one level of the elimination tree are
-// independent; the right-looking factorisation advances one LEVEL per launch pair:
-//   panel  potrf of the diagonal tile together with W = L_kk^-1, then L(i,k) = A(i,k) W^T as a tile product
-//          (one CTA per non-zero tile below the diagonal of every column of the level, each factoring the diagonal
-//          tile redundantly)
-//   syrk   A(i,j) -= sum_k L(i,k) L(j,k)^T over the level's columns k (one CTA per destination tile, fixed k order)
+// The block order is a nested dissection of the block graph; every leaf and separator starts on a tile boundary (unused
+// slots of its last tile are identity padding), so tile columns on one level of the elimination tree are independent;
+// the right-looking factorisation advances one LEVEL per launch pair:
+//   panel  L(i,k) = A(i,k) W^T with W = L_kk^-1 as a tile product (one CTA per non-zero tile below the diagonal of
+//          every column of the level)
+//   syrk   A(i,j) -= sum_k L(i,k) L(j,k)^T over the level's columns k (one CTA per destination tile, fixed k order);
+//          a diagonal tile that this update completes is factored on the spot (potrf together with W = L^-1)
 // and so do the two substitutions. The tile products run on the FP64 tensor cores (mma.sync m8n8k4). The launch
 // sequence depends on the structure only, so it is fixed per problem. Replaces SuiteSparse/Eigen sparse Cholesky inside
 // ceres' SPARSE_SCHUR.
@@ -25,6 +26,8 @@ constexpr int kNdLeaf = 4, kNdShort = 6;   // nested dissection: tiles per leaf,
 
 struct TileChol {
   int nT, n;
+  const int* blk_slot;         // [nf] slot of an f-block: tile = slot / kTileBlocks, position in the tile = slot % kTileBlocks
+  const int* slot_blk;         // [nT * kTileBlocks] the inverse; -1: padding (identity)
   const long long* tile_off;   // [nT * nT], (i, j) with i >= j at i * nT + j: offset of the tile in T (doubles) or -1
   const int* col_ptr;          // [nT + 1] ranges into col_rows: non-zero tiles strictly below the diagonal of tile column k
   const int* col_rows;
@@ -49,15 +52,15 @@ __global__ void __launch_bounds__(256) bsr_to_tiles_kernel(DeviceProblem P, Tile
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (P.bsr_rowptr[mid] <= blk) lo = mid; else hi = mid; }
     const int br = lo, bc = P.bsr_col[blk];
     if (3 * br + i >= 3 * bc + j) {
-      const int tr = br / kTileBlocks, tc = bc / kTileBlocks;
+      const int sr = TC.blk_slot[br], sc = TC.blk_slot[bc], tr = sr / kTileBlocks, tc = sc / kTileBlocks;
       const long long off = TC.tile_off[(long long)tr * TC.nT + tc];
-      TC.T[off + (3 * (bc - tc * kTileBlocks) + j) * kTS + 3 * (br - tr * kTileBlocks) + i] = Sb[e];
+      TC.T[off + (3 * (sc - tc * kTileBlocks) + j) * kTS + 3 * (sr - tr * kTileBlocks) + i] = Sb[e];
     }
   } else {
-    // identity on the pad row of every tile and on the unused rows of the last one: slot q of tile t
+    // identity on the pad row of every tile and on the rows of its unused slots: row l of tile t
     const long long q = e - P.nnzb * 9;
     const int t = (int)(q / kTS), l = (int)(q % kTS);
-    if (t < TC.nT && (l == kTU || t * kTU + l >= TC.n)) TC.T[TC.tile_off[(long long)t * TC.nT + t] + l * kTS + l] = 1.0;
+    if (t < TC.nT && (l == kTU || TC.slot_blk[t * kTileBlocks + l / 3] < 0)) TC.T[TC.tile_off[(long long)t * TC.nT + t] + l * kTS + l] = 1.0;
   }
 }
 
@@ -367,13 +370,13 @@ __global__ void __launch_bounds__(256) tile_rhs_kernel(TileChol TC, const double
   if (!gate_run(st) || st->lin_fail) return;
   const int e = blockIdx.x * 256 + threadIdx.x;
   if (e >= TC.nT * kTS) return;
-  const int t = e >> 6, l = e & 63, srow = t * kTU + l;
-  TC.b[e] = (l < kTU && srow < TC.n) ? rhs[srow] : 0.0;
+  const int t = e >> 6, l = e & 63, blk = l < kTU ? TC.slot_blk[t * kTileBlocks + l / 3] : -1;
+  TC.b[e] = blk >= 0 ? rhs[3 * blk + l % 3] : 0.0;
 }
 __global__ void __launch_bounds__(256) tile_out_kernel(TileChol TC, double* __restrict__ yf, const LMState* st) {
   if (!gate_run(st) || st->lin_fail) return;
   const int i = blockIdx.x * 256 + threadIdx.x;
-  if (i < TC.n) yf[i] = TC.b[(i / kTU) * kTS + i % kTU];
+  if (i < TC.n) { const int slot = TC.blk_slot[i / 3]; yf[i] = TC.b[(slot / kTileBlocks) * kTS + 3 * (slot % kTileBlocks) + i % 3]; }
 }
 // forward, leaves: y_k = W_k b_k
 __global__ void __launch_bounds__(256) tile_fwd_first_kernel(TileChol TC, int col_begin, const LMState* st) {
