@@ -93,136 +93,121 @@ __device__ __forceinline__ void tile_abt(const double* __restrict__ As, const do
 }
 
 // ---- potrf of a diagonal tile together with the inverse of its factor ----
-// All 256 threads of a CTA. The factorisation is right-looking on 4x4 register blocks (thread (ty, tx) owns rows 4ty..,
-// columns 4tx..), four pivots per step: the owner of the diagonal block factors it in registers and publishes the inverse
-// of that 4x4 factor; the threads of the block column multiply their blocks by it (the panel), and the rest of the matrix
-// gets a rank-4 update. The same row operations are applied to an identity, which turns it into W = L_kk^-1 in the same
-// sweep: blocks right of the pivot column update A entries, blocks left of it update W entries. Two barriers per four
-// pivots. G: the tile (lower triangle), column-major with pitch ld, global or shared memory. W goes to Ws (shared, pitch
-// kTLd) and / or Wg (global, pitch kTS) when given. Returns true in the thread that met a non-positive pivot.
-constexpr int kFactorScratchDoubles = 16 + kTS * 4 + 4 * kTS;
-constexpr int kPanelSmemDoubles = 2 * kTS * kTLd + kFactorScratchDoubles;
-#ifdef PANEL_PROF
-__device__ long long g_panel_prof[80];
-#endif
-__device__ __forceinline__ bool tile_potrf_inv(const double* __restrict__ G, int ld, double* __restrict__ Ws, double* __restrict__ Wg, double* __restrict__ scratch) {
-  double* sLi = scratch;                    // inverse of the 4x4 diagonal factor, row-major (lower)
-  double* sPan = sLi + 16;                  // the panel: L(r, 4 jb + c) at sPan[((r & 3) * 16 + (r >> 2)) * 4 + c]: the rows 4 ty + i of
-                                            // the 16 block rows of a warp are adjacent (no bank conflicts)
-  double* sWrow = sPan + kTS * 4;           // final rows 4 jb.. of W: sWrow[i * 64 + c]
-  // a warp holds two block columns (tx) and all block rows (ty): at any step it is either left of the pivot column (W
-  // updates only) or right of it (A updates only), so the two roles do not serialise inside a warp
-  const int tid = threadIdx.x, tx = tid >> 4, ty = tid & 15;
-  double a[4][4], w[4][4];
+// All 256 threads of a CTA; the tile A (lower triangle, column-major, pitch kTLd) sits in shared memory and is destroyed,
+// W = L^-1 is built in a second shared tile Ws (full tile, zeros above the diagonal) and copied to Wg when given.
+// Right-looking on 8-column blocks; per block k:
+//   potrf8   warp 0, every lane redundantly in registers: the 8x8 Cholesky of the diagonal block (a chain of 8 rsqrt) and,
+//            one column per lane, the inverse of that factor -> W(k,k)
+//   phase 2  L(i,k) = A(i,k) W(k,k)^T for the blocks below, and the block row k of W: W(k,j) = W(k,k) Wt(k,j)  (j < k)
+//   phase 3  A(i,j) -= L(i,k) L(j,k)^T (k < j <= i) and the same row operations on the identity that becomes W:
+//            Wt(i,j) -= L(i,k) W(k,j) (j <= k < i)
+// Phases 2 and 3 are 8x8x8 tile products on the FP64 tensor cores (two DMMA each), dealt to the warps tile by tile.
+// Look-ahead: in phase 3 warp 0 takes only the next diagonal block and factors it at once, while the other seven warps
+// finish the update -- the pivot chain (64 dependent rsqrt, ~100 cycles each) is nearly all of the critical path.
+// Returns true (in every thread of warp 0) when a pivot was not positive.
+constexpr int kPanelSmemDoubles = 2 * kTS * kTLd;
+__constant__ unsigned char c_tri8[36][2] = {{0,0},{1,0},{1,1},{2,0},{2,1},{2,2},{3,0},{3,1},{3,2},{3,3},{4,0},{4,1},{4,2},{4,3},{4,4},{5,0},{5,1},{5,2},{5,3},{5,4},{5,5},
+                                            {6,0},{6,1},{6,2},{6,3},{6,4},{6,5},{6,6},{7,0},{7,1},{7,2},{7,3},{7,4},{7,5},{7,6},{7,7}};
+// fragments of mma.m8n8k4 (g = lane / 4, tg = lane % 4) from a column-major matrix M with pitch kTLd:
+//   RK: element (row r0 + g, column c0 + 4 ks + tg)  -- the A operand X, or the B operand Y of X Y^T
+//   KN: element (row k0 + 4 ks + tg, column n0 + g)  -- the B operand Z of X Z
+#define TC_FRAG_RK(M, r0, c0, ks) (M)[((c0) + 4 * (ks) + tg) * kTLd + (r0) + g]
+#define TC_FRAG_KN(M, k0, n0, ks) (M)[((n0) + g) * kTLd + (k0) + 4 * (ks) + tg]
+__device__ __forceinline__ bool potrf8_inv(const double* __restrict__ As, double* __restrict__ Ws, int c0, int lane) {
+  // every lane: the lower triangle of the 8x8 block in registers (broadcast loads), the same arithmetic in every lane
+  double a[8][8];
 #pragma unroll
-  for (int c = 0; c < 4; ++c)
+  for (int c = 0; c < 8; ++c)
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { a[i][c] = ty >= tx ? G[(4 * tx + c) * ld + 4 * ty + i] : 0.0; w[i][c] = (ty == tx && i == c) ? 1.0 : 0.0; }
-  bool bad = false;
-#pragma unroll 1
-  for (int jb = 0; jb < kTS / 4; ++jb) {
-    if (ty == jb && tx == jb) {   // 4x4 Cholesky of the diagonal block and the inverse of its factor
-#ifdef PANEL_PROF
-      const long long ta = clock64();
-#endif
-      const double r0 = rsqrt(a[0][0]);
-      const double l10 = a[1][0] * r0, l20 = a[2][0] * r0, l30 = a[3][0] * r0;
-      const double d1 = a[1][1] - l10 * l10, r1 = rsqrt(d1);
-      const double l21 = (a[2][1] - l20 * l10) * r1, l31 = (a[3][1] - l30 * l10) * r1;
-      const double d2 = a[2][2] - l20 * l20 - l21 * l21, r2 = rsqrt(d2);
-      const double l32 = (a[3][2] - l30 * l20 - l31 * l21) * r2;
-      const double d3 = a[3][3] - l30 * l30 - l31 * l31 - l32 * l32, r3 = rsqrt(d3);
-      bad = bad || !(a[0][0] > 0.0) || !(d1 > 0.0) || !(d2 > 0.0) || !(d3 > 0.0);
-      const double i10 = -l10 * r0 * r1, i21 = -l21 * r1 * r2, i32 = -l32 * r2 * r3;
-      const double i20 = -(l20 * r0 + l21 * i10) * r2, i31 = -(l31 * r1 + l32 * i21) * r3;
-      const double i30 = -(l30 * r0 + l31 * i10 + l32 * i20) * r3;
-      sLi[0] = r0; sLi[1] = 0.0; sLi[2] = 0.0; sLi[3] = 0.0;
-      sLi[4] = i10; sLi[5] = r1; sLi[6] = 0.0; sLi[7] = 0.0;
-      sLi[8] = i20; sLi[9] = i21; sLi[10] = r2; sLi[11] = 0.0;
-      sLi[12] = i30; sLi[13] = i31; sLi[14] = i32; sLi[15] = r3;
-#ifdef PANEL_PROF
-      if (jb == 5) g_panel_prof[71] = clock64() - ta;
-#endif
-    }
-    __syncthreads();
-#ifdef PANEL_PROF
-    if (tid == 255) g_panel_prof[4 * jb] = clock64();
-#endif
-    if (ty >= jb && (tx == jb || (ty == jb && tx < jb))) {
-      double Li[4][4];
+    for (int r = c & ~1; r < 8; r += 2) { const double2 v = *reinterpret_cast<const double2*>(As + (c0 + c) * kTLd + c0 + r); a[r][c] = v.x; a[r + 1][c] = v.y; }
+  double rs[8]; bool bad = false;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { const double2 u0 = reinterpret_cast<const double2*>(sLi)[2 * i], u1 = reinterpret_cast<const double2*>(sLi)[2 * i + 1]; Li[i][0] = u0.x; Li[i][1] = u0.y; Li[i][2] = u1.x; Li[i][3] = u1.y; }
-      if (tx == jb && ty > jb) {   // panel block: L = A Li^T
+  for (int j = 0; j < 8; ++j) {
+    bad = bad || !(a[j][j] > 0.0);
+    rs[j] = rsqrt(a[j][j]);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          double l[4];
+    for (int i = j + 1; i < 8; ++i) a[i][j] *= rs[j];
 #pragma unroll
-          for (int c = 0; c < 4; ++c) { double sacc = 0.0;
+    for (int k = j + 1; k < 8; ++k)
 #pragma unroll
-            for (int m = 0; m <= c; ++m) sacc += a[i][m] * Li[c][m];
-            l[c] = sacc; }
-#pragma unroll
-          for (int c = 0; c < 4; ++c) a[i][c] = l[c];
-          reinterpret_cast<double2*>(sPan)[2 * (16 * i + ty)] = make_double2(l[0], l[1]);
-          reinterpret_cast<double2*>(sPan)[2 * (16 * i + ty) + 1] = make_double2(l[2], l[3]);
-        }
-      }
-      if (ty == jb) {              // rows 4 jb.. of W are final: W = Li W (block columns right of the pivot hold zeros)
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          double f[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) { double sacc = 0.0;
-#pragma unroll
-            for (int m = 0; m <= i; ++m) sacc += Li[i][m] * w[m][c];
-            f[i] = sacc; }
-#pragma unroll
-          for (int i = 0; i < 4; ++i) { w[i][c] = f[i]; sWrow[i * kTS + 4 * tx + c] = f[i]; }
-        }
-      }
-    }
-#ifdef PANEL_PROF
-    if (tid == 255 && jb == 5) g_panel_prof[72] = clock64();
-#endif
-    __syncthreads();
-#ifdef PANEL_PROF
-    if (tid == 255 && jb == 5) g_panel_prof[73] = clock64();
-#endif
-    if (ty > jb && ty >= tx) {    // rank-4 update with the panel rows of this thread
-      double Pr[4][4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) { const double2 u0 = reinterpret_cast<const double2*>(sPan)[2 * (16 * i + ty)], u1 = reinterpret_cast<const double2*>(sPan)[2 * (16 * i + ty) + 1]; Pr[i][0] = u0.x; Pr[i][1] = u0.y; Pr[i][2] = u1.x; Pr[i][3] = u1.y; }
-      if (tx > jb) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          const double2 u0 = reinterpret_cast<const double2*>(sPan)[2 * (16 * c + tx)], u1 = reinterpret_cast<const double2*>(sPan)[2 * (16 * c + tx) + 1];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) a[i][c] -= Pr[i][0] * u0.x + Pr[i][1] * u0.y + Pr[i][2] * u1.x + Pr[i][3] * u1.y;
-        }
-      } else {
-#pragma unroll
-        for (int m = 0; m < 4; ++m) {
-          const double2 u0 = reinterpret_cast<const double2*>(sWrow + m * kTS)[2 * tx], u1 = reinterpret_cast<const double2*>(sWrow + m * kTS)[2 * tx + 1];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) { w[i][0] -= Pr[i][m] * u0.x; w[i][1] -= Pr[i][m] * u0.y; w[i][2] -= Pr[i][m] * u1.x; w[i][3] -= Pr[i][m] * u1.y; }
-        }
-      }
-    }
-#ifdef PANEL_PROF
-    if (tid == 255 && jb == 5) g_panel_prof[74] = clock64();
-#endif
+      for (int i = k; i < 8; ++i) a[i][k] -= a[i][j] * a[k][j];
   }
-#ifdef PANEL_PROF
-  if (tid == 255) g_panel_prof[64] = clock64();
-#endif
+  // column c = lane % 8 of the inverse by forward substitution: w_k = (delta_kc - sum_{m<k} L_km w_m) / L_kk
+  const int c = lane & 7;
+  double w[8], acc[8];
 #pragma unroll
-  for (int c = 0; c < 4; ++c)
+  for (int k = 0; k < 8; ++k) acc[k] = (k == c) ? 1.0 : 0.0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const double v = (ty > tx || (ty == tx && i >= c)) ? w[i][c] : 0.0;
-      if (Ws) Ws[(4 * tx + c) * kTLd + 4 * ty + i] = v;
-      if (Wg) Wg[(4 * tx + c) * kTS + 4 * ty + i] = v;
+  for (int k = 0; k < 8; ++k) {
+    w[k] = acc[k] * rs[k];
+#pragma unroll
+    for (int i = k + 1; i < 8; ++i) acc[i] -= a[i][k] * w[k];
+  }
+  if (lane < 8) {
+#pragma unroll
+    for (int r = 0; r < 8; r += 2) *reinterpret_cast<double2*>(Ws + (c0 + c) * kTLd + c0 + r) = make_double2(w[r], w[r + 1]);
+  }
+  return bad;
+}
+__device__ __forceinline__ bool tile_potrf_inv(double* __restrict__ As, double* __restrict__ Ws, double* __restrict__ Wg) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
+  for (int e = tid; e < kTS * kTLd / 2; e += 256) reinterpret_cast<double2*>(Ws)[e] = make_double2(0.0, 0.0);
+  __syncthreads();
+  bool bad = false;
+  if (warp == 0) bad = potrf8_inv(As, Ws, 0, lane);
+  __syncthreads();
+#pragma unroll 1
+  for (int kb = 0; kb < 8; ++kb) {
+    const int c0 = 8 * kb, m8 = 7 - kb;
+    // ---- phase 2: the panel below block k, and block row k of W ----
+    for (int t = warp; t < m8 + kb; t += 8) {
+      double d0 = 0.0, d1 = 0.0;
+      if (t < m8) {
+        const int r0 = c0 + 8 + 8 * t;
+        const double a0 = TC_FRAG_RK(As, r0, c0, 0), a1 = TC_FRAG_RK(As, r0, c0, 1), b0 = TC_FRAG_RK(Ws, c0, c0, 0), b1 = TC_FRAG_RK(Ws, c0, c0, 1);
+        dmma_m8n8k4(d0, d1, a0, b0); dmma_m8n8k4(d0, d1, a1, b1);
+        As[(c0 + 2 * tg) * kTLd + r0 + g] = d0; As[(c0 + 2 * tg + 1) * kTLd + r0 + g] = d1;
+      } else {
+        const int n0 = 8 * (t - m8);
+        const double a0 = TC_FRAG_RK(Ws, c0, c0, 0), a1 = TC_FRAG_RK(Ws, c0, c0, 1), b0 = TC_FRAG_KN(Ws, c0, n0, 0), b1 = TC_FRAG_KN(Ws, c0, n0, 1);
+        dmma_m8n8k4(d0, d1, a0, b0); dmma_m8n8k4(d0, d1, a1, b1);
+        Ws[(n0 + 2 * tg) * kTLd + c0 + g] = d0; Ws[(n0 + 2 * tg + 1) * kTLd + c0 + g] = d1;
+      }
     }
+    if (kb == 7) break;
+    __syncthreads();
+    // ---- phase 3: trailing update of A and of W; warp 0: the next diagonal block, then its factorisation ----
+    if (warp == 0) {
+      const int r0 = c0 + 8;
+      double d0 = As[(r0 + 2 * tg) * kTLd + r0 + g], d1 = As[(r0 + 2 * tg + 1) * kTLd + r0 + g];
+      const double a0 = -TC_FRAG_RK(As, r0, c0, 0), a1 = -TC_FRAG_RK(As, r0, c0, 1), b0 = TC_FRAG_RK(As, r0, c0, 0), b1 = TC_FRAG_RK(As, r0, c0, 1);
+      dmma_m8n8k4(d0, d1, a0, b0); dmma_m8n8k4(d0, d1, a1, b1);
+      As[(r0 + 2 * tg) * kTLd + r0 + g] = d0; As[(r0 + 2 * tg + 1) * kTLd + r0 + g] = d1;
+      __syncwarp();
+      bad = potrf8_inv(As, Ws, r0, lane) || bad;
+    } else {
+      const int ntri = m8 * (m8 + 1) / 2 - 1, nw = m8 * (kb + 1);
+      for (int u = warp - 1; u < ntri + nw; u += 7) {
+        if (u < ntri) {      // A(i,j) -= L(i,k) L(j,k)^T
+          const int r0 = c0 + 8 + 8 * c_tri8[u + 1][0], n0 = c0 + 8 + 8 * c_tri8[u + 1][1];
+          double d0 = As[(n0 + 2 * tg) * kTLd + r0 + g], d1 = As[(n0 + 2 * tg + 1) * kTLd + r0 + g];
+          const double a0 = -TC_FRAG_RK(As, r0, c0, 0), a1 = -TC_FRAG_RK(As, r0, c0, 1), b0 = TC_FRAG_RK(As, n0, c0, 0), b1 = TC_FRAG_RK(As, n0, c0, 1);
+          dmma_m8n8k4(d0, d1, a0, b0); dmma_m8n8k4(d0, d1, a1, b1);
+          As[(n0 + 2 * tg) * kTLd + r0 + g] = d0; As[(n0 + 2 * tg + 1) * kTLd + r0 + g] = d1;
+        } else {             // Wt(i,j) -= L(i,k) W(k,j)
+          const int v = u - ntri, r0 = c0 + 8 + 8 * (v / (kb + 1)), n0 = 8 * (v % (kb + 1));
+          double d0 = Ws[(n0 + 2 * tg) * kTLd + r0 + g], d1 = Ws[(n0 + 2 * tg + 1) * kTLd + r0 + g];
+          const double a0 = -TC_FRAG_RK(As, r0, c0, 0), a1 = -TC_FRAG_RK(As, r0, c0, 1), b0 = TC_FRAG_KN(Ws, c0, n0, 0), b1 = TC_FRAG_KN(Ws, c0, n0, 1);
+          dmma_m8n8k4(d0, d1, a0, b0); dmma_m8n8k4(d0, d1, a1, b1);
+          Ws[(n0 + 2 * tg) * kTLd + r0 + g] = d0; Ws[(n0 + 2 * tg + 1) * kTLd + r0 + g] = d1;
+        }
+      }
+    }
+    __syncthreads();
+  }
+  __syncthreads();
+  if (Wg)
+    for (int e = tid; e < kTileDoubles / 2; e += 256) { const int c = e >> 5, r2 = e & 31; reinterpret_cast<double2*>(Wg)[e] = *reinterpret_cast<const double2*>(Ws + c * kTLd + 2 * r2); }
   return bad;
 }
 
@@ -245,35 +230,17 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_be
   const int na = px >= 0 ? 1 : 0;
   if (na == 0 && !factor_here) return;
   const bool first = px < 0 || px == TC.col_ptr[k];   // this CTA stores W of its column
-  double* Gi = nullptr;
-  if (na > 0) {   // start fetching this CTA's tile; it is not needed before the product
-    Gi = TC.T + TC.tile_off[(long long)TC.col_rows[px] * TC.nT + k];
-    const double* Wk = TC.W + (size_t)k * kTileDoubles;
-    for (int e = tid; e < kTileDoubles / 2; e += 256) {
-      const int c = e >> 5, r2 = e & 31;
-      const unsigned dst = (unsigned)__cvta_generic_to_shared(As + c * kTLd + 2 * r2);
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(Gi + 2 * e));
-      if (!factor_here) {
-        const unsigned dw = (unsigned)__cvta_generic_to_shared(Bs + c * kTLd + 2 * r2);
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dw), "l"(Wk + 2 * e));
-      }
-    }
-    asm volatile("cp.async.commit_group;");
-  }
-#ifdef PANEL_PROF
-  if (tid == 255) g_panel_prof[70] = clock64();
-#endif
   if (factor_here) {
-    const bool bad = tile_potrf_inv(TC.T + TC.tile_off[(long long)k * TC.nT + k], kTS, Bs, first ? TC.W + (size_t)k * kTileDoubles : nullptr, Bs + kTS * kTLd);
-    if (bad) failed = 1;
+    tile_load(TC.T + TC.tile_off[(long long)k * TC.nT + k], As);
+    __syncthreads();
+    if (tile_potrf_inv(As, Bs, first ? TC.W + (size_t)k * kTileDoubles : nullptr)) failed = 1;
+    __syncthreads();
+    if (tid == 0 && failed) st->lin_fail = 1;   // every CTA of a column sees the same pivots
   }
-  if (na > 0) asm volatile("cp.async.wait_group 0;");
-  __syncthreads();
-  if (tid == 0 && failed) st->lin_fail = 1;   // every CTA of a column sees the same pivots
-#ifdef PANEL_PROF
-  if (tid == 255) g_panel_prof[65] = clock64();
-#endif
   if (na == 0) return;
+  double* Gi = TC.T + TC.tile_off[(long long)TC.col_rows[px] * TC.nT + k];
+  if (factor_here) tile_load(Gi, As); else tile_load2(Gi, As, TC.W + (size_t)k * kTileDoubles, Bs);
+  __syncthreads();
   const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
   double acc[8][2];
 #pragma unroll
@@ -330,7 +297,7 @@ __global__ void __launch_bounds__(256) tile_syrk_kernel(TileChol TC, int upd_beg
     As[(8 * J + 2 * tg + 1) * kTLd + 8 * warp + g] = cv[J][1] - acc[J][1];
   }
   __syncthreads();
-  if (tile_potrf_inv(As, kTLd, nullptr, TC.W + (size_t)fac * kTileDoubles, Bs + kTS * kTLd)) failed = 1;
+  if (tile_potrf_inv(As, Bs, TC.W + (size_t)fac * kTileDoubles)) failed = 1;
   __syncthreads();
   if (threadIdx.x == 0 && failed) st->lin_fail = 1;
 }

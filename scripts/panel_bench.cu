@@ -70,11 +70,6 @@ int main(int argc, char** argv) {
   if (na) { cudaMemcpy(X.data(), dT + kTileDoubles, kTileDoubles * 8, cudaMemcpyDeviceToHost); double e2 = 0;
     for (int r = 0; r < 64; ++r) for (int c = 0; c < 64; ++c) { double s = 0; for (int m = 0; m <= c; ++m) s += X[m * 64 + r] * L[c * 64 + m]; e2 = std::fmax(e2, std::fabs(s - T[kTileDoubles + c * 64 + r])); }
     printf("max |L10 Lkk^T - A10| = %.3e\n", e2); }
-#ifdef PANEL_PROF
-  { long long pr[80]; cudaMemcpyFromSymbol(pr, g_panel_prof, sizeof(pr));
-    printf("start->step0 %lld, steps:", pr[0] - pr[70]); for (int j = 4; j <= 64; j += 4) printf(" %lld", pr[j] - pr[j - 4]); printf(", epilogue %lld\n", pr[65] - pr[64]);
-    printf("step 5: diag block %lld cycles; observer (thread 255): barrier 1 -> before barrier 2 %lld, wait in barrier 2 (the panel threads) %lld, update %lld, update end -> next barrier 1 %lld\n", pr[71], pr[72] - pr[20], pr[73] - pr[72], pr[74] - pr[73], pr[24] - pr[74]); }
-#endif
   LMState hs; cudaMemcpy(&hs, dst, sizeof(hs), cudaMemcpyDeviceToHost); printf("lin_fail %d, cuda: %s\n", hs.lin_fail, cudaGetErrorString(cudaGetLastError()));
   return 0;
 }
