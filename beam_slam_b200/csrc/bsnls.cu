@@ -135,7 +135,7 @@ struct bsnls_handle {
   std::vector<int> pair_a, pair_b;
   std::vector<int> gd_row, gd_col;
   bool tiled = false; std::vector<int> f_api;   // tile-sparse Cholesky; internal f position -> API (program-order) position
-  TileChol TC{}; std::vector<int> tc_col_ptr, tc_blk_slot; int tc_nT = 0; DevMem d_tc_blk_slot, d_tc_slot_blk, d_tc_tile_off, d_tc_col_ptr, d_tc_col_rows, d_tc_T, d_tc_W, d_tc_b; size_t tc_T_bytes = 0;
+  TileChol TC{}; std::vector<int> tc_col_ptr, tc_blk_slot; int tc_nT = 0; DevMem d_tc_blk_slot, d_tc_slot_blk, d_tc_row_ptr, d_tc_row_tile, d_tc_braw, d_tc_P, d_tc_tile_off, d_tc_col_ptr, d_tc_col_rows, d_tc_T, d_tc_W, d_tc_b; size_t tc_T_bytes = 0;
   struct TcLevel { int col_begin, ncols, pan_begin, npan, npan_tiles, upd_begin, nupd, fw_begin, nfw, bw_begin, nbw; };   // one level of the elimination tree
   std::vector<TcLevel> tc_levels;
   DevMem d_tc_pan_k, d_tc_pan_x, d_tc_upd_ptr, d_tc_upd_fac, d_tc_upd_dst, d_tc_upd_a, d_tc_upd_b, d_tc_fw_ptr, d_tc_fw_row, d_tc_fw_tail, d_tc_fw_src, d_tc_fw_k, d_tc_lev_cols, d_tc_bw_ptr, d_tc_bw_col, d_tc_bw_tail, d_tc_bw_src, d_tc_bw_i, d_tc_roots; int tc_nroots = 0;
@@ -466,17 +466,21 @@ void EnqueueDenseSolve(bsnls_handle* h, bool factor = true) {  // phase D2: Chol
     if (factor) {
       cudaMemsetAsync(TC.T, 0, h->tc_T_bytes, h->stream);
       LAUNCH(h, bsr_to_tiles_kernel, (unsigned)((h->nnzb * 9 + (long long)TC.nT * kTS + 255) / 256), 256, h->P, TC, h->d_S.as<double>(), st);
+      // the forward substitution is part of the panel kernels: the right-hand side goes into the tile slots first
+      LAUNCH(h, tile_rhs_kernel, (TC.nT * kTS + 255) / 256, 256, TC, h->d_rhs.as<double>(), TC.braw, st);
       bool first_level = true;
       for (const auto& L : h->tc_levels) {   // factorisation, one level of the elimination tree at a time
-        if (first_level || L.npan_tiles > 0) LAUNCH_SMEM(h, tile_panel_kernel, L.npan, 256, smem, TC, L.pan_begin, first_level ? 1 : 0, st);
+        LAUNCH_SMEM(h, tile_panel_kernel, L.npan, 256, smem, TC, L.pan_begin, first_level ? 1 : 0, st);
         first_level = false;
         if (L.nupd > 0) LAUNCH_SMEM(h, tile_syrk_kernel, L.nupd, 256, smem, TC, L.upd_begin, st);
       }
     }
-    // substitutions, level by level: forward (bottom-up), backward (top-down)
-    LAUNCH(h, tile_rhs_kernel, (TC.nT * kTS + 255) / 256, 256, TC, h->d_rhs.as<double>(), st);
-    LAUNCH(h, tile_fwd_first_kernel, h->tc_levels[0].ncols, 256, TC, h->tc_levels[0].col_begin, st);
-    for (const auto& L : h->tc_levels) if (L.nfw > 0) LAUNCH(h, tile_fwd_kernel, L.nfw, 256, TC, L.fw_begin, st);
+    // substitutions, level by level: forward (bottom-up; only for another right-hand side of a kept factor), backward (top-down)
+    if (!factor) {
+      LAUNCH(h, tile_rhs_kernel, (TC.nT * kTS + 255) / 256, 256, TC, h->d_rhs.as<double>(), TC.b, st);
+      LAUNCH(h, tile_fwd_first_kernel, h->tc_levels[0].ncols, 256, TC, h->tc_levels[0].col_begin, st);
+      for (const auto& L : h->tc_levels) if (L.nfw > 0) LAUNCH(h, tile_fwd_kernel, L.nfw, 256, TC, L.fw_begin, st);
+    }
     LAUNCH(h, tile_bwd_first_kernel, h->tc_nroots, 256, TC, st);
     for (size_t lv = h->tc_levels.size(); lv-- > 0;) if (h->tc_levels[lv].nbw > 0) LAUNCH(h, tile_bwd_kernel, h->tc_levels[lv].nbw, 256, TC, h->tc_levels[lv].bw_begin, st);
     LAUNCH(h, tile_out_kernel, (TC.n + 255) / 256, 256, TC, h->d_yf.as<double>(), st);
@@ -1415,7 +1419,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   std::vector<long long> tc_tile_off; std::vector<int> tc_col_rows; long long tc_tiles = 0;
   std::vector<int> tc_pan_k, tc_pan_x, tc_upd_ptr, tc_upd_fac, tc_fw_ptr, tc_fw_row, tc_fw_tail, tc_lev_cols;
   std::vector<long long> tc_upd_dst, tc_upd_a, tc_upd_b, tc_fw_src; std::vector<int> tc_fw_k;
-  std::vector<int> tc_bw_ptr, tc_bw_col, tc_bw_tail, tc_bw_i, tc_roots, tc_slot_blk; std::vector<long long> tc_bw_src;
+  std::vector<int> tc_bw_ptr, tc_bw_col, tc_bw_tail, tc_bw_i, tc_roots, tc_slot_blk, tc_row_ptr, tc_row_tile; std::vector<long long> tc_bw_src;
   h->tc_col_ptr.clear(); h->tc_levels.clear();
   if (h->tiled) {
     const int nT = h->tc_nT;
@@ -1446,6 +1450,13 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
       for (int k = 0; k < nT; ++k) {
         tc_tile_off[(size_t)k * nT + k] = (t++) * kTileDoubles;
         for (int i : col[k]) { tc_tile_off[(size_t)i * nT + k] = (t++) * kTileDoubles; tc_col_rows.push_back(i); }
+      }
+      { // rows of the factor: the tiles (k, j), j < k, for the forward substitution inside the panel kernels
+        std::vector<std::vector<int>> rows(nT);
+        for (int j = 0; j < nT; ++j) for (int i : col[j]) rows[i].push_back((int)(tc_tile_off[(size_t)i * nT + j] / kTileDoubles));
+        tc_row_ptr.assign(nT + 1, 0);
+        for (int k = 0; k < nT; ++k) { tc_row_ptr[k + 1] = tc_row_ptr[k] + (int)rows[k].size(); tc_row_tile.insert(tc_row_tile.end(), rows[k].begin(), rows[k].end()); }
+        if (tc_row_tile.empty()) tc_row_tile.push_back(0);
       }
       // level schedule: tile columns of one level of the elimination tree are independent. Per level: the panel CTAs
       // (column, tile below the diagonal), the destination tiles of the updates with their source columns, and for
@@ -1520,6 +1531,8 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     tc_slot_blk.assign((size_t)nT * kTileBlocks, -1);
     for (int r = 0; r < h->nf; ++r) tc_slot_blk[h->tc_blk_slot[r]] = r;
     CK(upload(h->d_tc_blk_slot, h->tc_blk_slot, s)); CK(upload(h->d_tc_slot_blk, tc_slot_blk, s));
+    CK(upload(h->d_tc_row_ptr, tc_row_ptr, s)); CK(upload(h->d_tc_row_tile, tc_row_tile, s));
+    CK(h->d_tc_braw.alloc(sizeof(double) * kTS * (size_t)nT)); CK(h->d_tc_P.alloc(sizeof(double) * kTS * (size_t)tc_tiles));
     if (tc_col_rows.empty()) tc_col_rows.push_back(0);
     if (tc_upd_dst.empty()) { tc_upd_dst.push_back(0); tc_upd_fac.push_back(-1); tc_upd_a.push_back(0); tc_upd_b.push_back(0); }
     if (tc_fw_row.empty()) { tc_fw_row.push_back(0); tc_fw_tail.push_back(0); tc_fw_src.push_back(0); tc_fw_k.push_back(0); }
@@ -1573,6 +1586,8 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     h->TC.upd_fac = h->d_tc_upd_fac.as<int>();
     h->TC.blk_slot = h->d_tc_blk_slot.as<int>();
     h->TC.slot_blk = h->d_tc_slot_blk.as<int>();
+    h->TC.row_ptr = h->d_tc_row_ptr.as<int>(); h->TC.row_tile = h->d_tc_row_tile.as<int>();
+    h->TC.braw = h->d_tc_braw.as<double>(); h->TC.P = h->d_tc_P.as<double>();
     h->TC.upd_a = h->d_tc_upd_a.as<long long>();
     h->TC.upd_b = h->d_tc_upd_b.as<long long>();
     h->TC.fw_ptr = h->d_tc_fw_ptr.as<int>();

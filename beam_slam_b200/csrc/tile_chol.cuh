@@ -34,6 +34,9 @@ struct TileChol {
   double* T;                   // tile storage, each tile column-major 64x64
   double* W;                   // [nT][64*64] inverses of the diagonal factors (lower triangular, column-major)
   double* b;                   // [nT * 64] right-hand side / solution scratch
+  double* braw;                // [nT * 64] right-hand side in tile slots, as tile_rhs_kernel leaves it for the fused forward substitution
+  double* P;                   // [tiles * 64] forward-substitution products L(i,k) y_k, one vector per tile below the diagonal
+  const int* row_ptr; const int* row_tile;   // per tile row k: the tiles (k, j), j < k, as indices into P (j ascending)
   // level schedule (see set_problem)
   const int* lev_cols;         // tile columns grouped by level
   const int* pan_k; const int* pan_x;   // panel CTAs: column, index into col_rows (-1: the column has no tile below the diagonal)
@@ -215,6 +218,9 @@ __device__ __forceinline__ bool tile_potrf_inv(double* __restrict__ As, double* 
 // factor_here (the first level, whose diagonal tiles nobody updates): every CTA of a column factors the diagonal tile itself
 // -- the same arithmetic, so the same bits, and no dependency between CTAs -- and the first one stores W (the solve needs
 // it). On every other level W was left by the update kernel of the level before (see tile_syrk_kernel) and is only loaded.
+// The forward substitution rides along: with W_k on chip every CTA of column k forms y_k = W_k (b_k - sum_j L(k,j) y_j)
+// from the product vectors the panel CTAs of row k's tiles left in P (lower levels, fixed order j ascending; the first CTA
+// stores y_k), and after its own tile product adds P(i,k) = L(i,k) y_k from the accumulators. No separate launches.
 __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_begin, int factor_here, LMState* st) {
   extern __shared__ __align__(16) double sm[];
   double* As = sm;                          // A(i,k), column-major, pitch kTLd
@@ -228,8 +234,8 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_be
   const int tid = threadIdx.x;
   const int k = TC.pan_k[pan_begin + blockIdx.x], px = TC.pan_x[pan_begin + blockIdx.x];
   const int na = px >= 0 ? 1 : 0;
-  if (na == 0 && !factor_here) return;
-  const bool first = px < 0 || px == TC.col_ptr[k];   // this CTA stores W of its column
+  const bool first = px < 0 || px == TC.col_ptr[k];   // this CTA stores W and y of its column
+  __shared__ double sv[kTS], sy[kTS], spart[4][kTS];
   if (factor_here) {
     tile_load(TC.T + TC.tile_off[(long long)k * TC.nT + k], As);
     __syncthreads();
@@ -237,10 +243,26 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_be
     __syncthreads();
     if (tid == 0 && failed) st->lin_fail = 1;   // every CTA of a column sees the same pivots
   }
-  if (na == 0) return;
-  double* Gi = TC.T + TC.tile_off[(long long)TC.col_rows[px] * TC.nT + k];
-  if (factor_here) tile_load(Gi, As); else tile_load2(Gi, As, TC.W + (size_t)k * kTileDoubles, Bs);
+  double* Gi = na > 0 ? TC.T + TC.tile_off[(long long)TC.col_rows[px] * TC.nT + k] : nullptr;
+  if (na > 0) { if (factor_here) tile_load(Gi, As); else tile_load2(Gi, As, TC.W + (size_t)k * kTileDoubles, Bs); }
+  else if (!factor_here) tile_load(TC.W + (size_t)k * kTileDoubles, Bs);
+  if (tid < kTS) {       // right-hand side of the column minus the products of the tiles left of the diagonal
+    double v = TC.braw[k * kTS + tid];
+    for (int q = TC.row_ptr[k]; q < TC.row_ptr[k + 1]; ++q) v -= TC.P[(size_t)TC.row_tile[q] * kTS + tid];
+    sv[tid] = v;
+  }
   __syncthreads();
+  {                      // y_k = W_k v: thread (cg, r) takes 16 columns of row r
+    const int cg = tid >> 6, r = tid & 63;
+    double s2 = 0.0;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) s2 += Bs[(16 * cg + q) * kTLd + r] * sv[16 * cg + q];
+    spart[cg][r] = s2;
+    __syncthreads();
+    if (tid < kTS) { const double y = spart[0][tid] + spart[1][tid] + spart[2][tid] + spart[3][tid]; sy[tid] = y; if (first) TC.b[k * kTS + tid] = y; }
+    __syncthreads();
+  }
+  if (na == 0) return;
   const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
   double acc[8][2];
 #pragma unroll
@@ -251,6 +273,11 @@ __global__ void __launch_bounds__(256) tile_panel_kernel(TileChol TC, int pan_be
     Gi[(8 * J + 2 * tg) * kTS + 8 * warp + g] = acc[J][0];
     Gi[(8 * J + 2 * tg + 1) * kTS + 8 * warp + g] = acc[J][1];
   }
+  double ps = 0.0;       // P(i,k) = L(i,k) y_k: the lane's 16 entries of row 8 warp + g, then the four lanes of the row
+#pragma unroll
+  for (int J = 0; J < 8; ++J) ps += acc[J][0] * sy[8 * J + 2 * tg] + acc[J][1] * sy[8 * J + 2 * tg + 1];
+  ps += __shfl_xor_sync(0xffffffffu, ps, 1); ps += __shfl_xor_sync(0xffffffffu, ps, 2);
+  if (tg == 0) TC.P[(size_t)((Gi - TC.T) / kTileDoubles) * kTS + 8 * warp + g] = ps;
 }
 
 // ---- syrk: A(i,j) -= sum_k L(i,k) L(j,k)^T over the source columns of this level; one CTA per destination tile ----
@@ -333,12 +360,12 @@ __device__ __forceinline__ double tile_mv_t(const double* __restrict__ M, const 
   s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2);
   return s;
 }
-__global__ void __launch_bounds__(256) tile_rhs_kernel(TileChol TC, const double* __restrict__ rhs, const LMState* st) {
+__global__ void __launch_bounds__(256) tile_rhs_kernel(TileChol TC, const double* __restrict__ rhs, double* __restrict__ dst, const LMState* st) {
   if (!gate_run(st) || st->lin_fail) return;
   const int e = blockIdx.x * 256 + threadIdx.x;
   if (e >= TC.nT * kTS) return;
   const int t = e >> 6, l = e & 63, blk = l < kTU ? TC.slot_blk[t * kTileBlocks + l / 3] : -1;
-  TC.b[e] = blk >= 0 ? rhs[3 * blk + l % 3] : 0.0;
+  dst[e] = blk >= 0 ? rhs[3 * blk + l % 3] : 0.0;
 }
 __global__ void __launch_bounds__(256) tile_out_kernel(TileChol TC, double* __restrict__ yf, const LMState* st) {
   if (!gate_run(st) || st->lin_fail) return;

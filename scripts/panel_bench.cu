@@ -26,7 +26,9 @@ int main(int argc, char** argv) {
   cudaMemcpy(dT0, T.data(), T.size() * 8, cudaMemcpyHostToDevice); cudaMemcpy(doff, off.data(), off.size() * 8, cudaMemcpyHostToDevice);
   cudaMemcpy(dcp, col_ptr.data(), col_ptr.size() * 4, cudaMemcpyHostToDevice); if (na) cudaMemcpy(dcr, col_rows.data(), col_rows.size() * 4, cudaMemcpyHostToDevice);
   cudaMemset(dst, 0, sizeof(LMState));
-  TileChol TC{}; TC.nT = nT; TC.n = nT * 64; TC.tile_off = doff; TC.col_ptr = dcp; TC.col_rows = dcr; TC.T = dT; TC.W = dW; TC.b = db;
+  double *dbraw, *dP; int *drp, *drt;
+  cudaMalloc(&dbraw, nT * 64 * 8); cudaMemset(dbraw, 0, nT * 64 * 8); cudaMalloc(&dP, (size_t)(nT + nT * nT) * 64 * 8); cudaMalloc(&drp, (nT + 1) * 4); cudaMemset(drp, 0, (nT + 1) * 4); cudaMalloc(&drt, 4);
+  TileChol TC{}; TC.braw = dbraw; TC.P = dP; TC.row_ptr = drp; TC.row_tile = drt; TC.nT = nT; TC.n = nT * 64; TC.tile_off = doff; TC.col_ptr = dcp; TC.col_rows = dcr; TC.T = dT; TC.W = dW; TC.b = db;
   {   // level schedule of the one column: panel CTA x works on tile col_rows[x]; update destinations (i, j), 1 <= j <= i, from column 0
     std::vector<int> pk(std::max(1, na), 0), px(std::max(1, na), -1), up; std::vector<long long> ud, ua, ub;
     for (int x = 0; x < na; ++x) px[x] = x;
