@@ -1416,8 +1416,42 @@ __global__ void __launch_bounds__(256) backsub_kernel(DeviceProblem P, const dou
   const int l = gtid / G, sub = gtid % G;
   const bool valid = l < P.ne;
   const int start = valid ? P.lm_ptr[l] : 0, end = valid ? P.lm_ptr[l + 1] : 0;
+  // The first kBsKeep observations of a lane stay in registers between the two passes (E, r and u = F y_pose): with four
+  // lanes per landmark that covers tracks of up to 12, so the records are read from HBM once; their loads are issued
+  // together. Longer tracks re-read the rest.
+  constexpr int kBsKeep = 3;
+  double2 ke0[kBsKeep], ke1[kBsKeep], ke2[kBsKeep], kr[kBsKeep]; double ku0[kBsKeep], ku1[kBsKeep];
+  {
+    double2 rc[kBsKeep][8]; int tq[kBsKeep], tt[kBsKeep];
+#pragma unroll
+    for (int b = 0; b < kBsKeep; ++b) {
+      const int o = start + sub + b * G;
+      if (o < end) {
+        const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) rc[b][q] = rec[q];
+        const int pose = P.obs_pose[o]; tq[b] = P.pose_q_tan[pose]; tt[b] = P.pose_t_tan[pose];
+      } else {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) rc[b][q] = make_double2(0.0, 0.0);
+        tq[b] = -1; tt[b] = -1;
+      }
+    }
+#pragma unroll
+    for (int b = 0; b < kBsKeep; ++b) {
+      double yp[6];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) { yp[k] = tq[b] >= 0 ? yf[tq[b] - P.ne_dim + k] : 0.0; yp[3 + k] = tt[b] >= 0 ? yf[tt[b] - P.ne_dim + k] : 0.0; }
+      const double2 e0 = rc[b][0], e1 = rc[b][1], e2 = rc[b][2], f0 = rc[b][4], f1 = rc[b][5], f2 = rc[b][6]; const double ts = rc[b][7].x;
+      ke0[b] = e0; ke1[b] = e1; ke2[b] = e2; kr[b] = rc[b][3];
+      ku0[b] = f0.x * yp[0] + f0.y * yp[1] + f1.x * yp[2] + ts * (e0.x * yp[3] + e0.y * yp[4] + e1.x * yp[5]);
+      ku1[b] = f1.y * yp[0] + f2.x * yp[1] + f2.y * yp[2] + ts * (e1.y * yp[3] + e2.x * yp[4] + e2.y * yp[5]);
+    }
+  }
   double t0 = 0, t1 = 0, t2 = 0;
-  for (int o = start + sub; o < end; o += G) {
+#pragma unroll
+  for (int b = 0; b < kBsKeep; ++b) { t0 += ke0[b].x * ku0[b] + ke1[b].y * ku1[b]; t1 += ke0[b].y * ku0[b] + ke2[b].x * ku1[b]; t2 += ke1[b].x * ku0[b] + ke2[b].y * ku1[b]; }
+  for (int o = start + sub + kBsKeep * G; o < end; o += G) {
     const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec);
     const int pose = P.obs_pose[o];
     const int tq = P.pose_q_tan[pose], tt = P.pose_t_tan[pose];
@@ -1441,7 +1475,13 @@ __global__ void __launch_bounds__(256) backsub_kernel(DeviceProblem P, const dou
     if (sub == 0) { y[3 * l] = ye0; y[3 * l + 1] = ye1; y[3 * l + 2] = ye2; }
   }
   double mc = 0.0;
-  for (int o = start + sub; o < end; o += G) {
+#pragma unroll
+  for (int b = 0; b < kBsKeep; ++b) {   // empty slots hold zeros and add nothing
+    const double m0 = ku0[b] + ke0[b].x * ye0 + ke0[b].y * ye1 + ke1[b].x * ye2;
+    const double m1 = ku1[b] + ke1[b].y * ye0 + ke2[b].x * ye1 + ke2[b].y * ye2;
+    mc += m0 * (kr[b].x - 0.5 * m0) + m1 * (kr[b].y - 0.5 * m1);
+  }
+  for (int o = start + sub + kBsKeep * G; o < end; o += G) {
     const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec);
     const int pose = P.obs_pose[o];
     const int tq = P.pose_q_tan[pose], tt = P.pose_t_tan[pose];

@@ -7,6 +7,6 @@ from beam_slam_b200.solver import Solver
 cfg = int(sys.argv[1]); scale = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0
 g = host.HashGraph.synthetic(cfg, scale=scale); p = g.flatten(); opts = host.HashGraph.synthetic_options(cfg)
 s = Solver(opts); s.set_problem(p)
-for _ in range(2):
+for _ in range(4):
     s.set_values(p.block_values); summ, its = s.solve()
 print(summ.message.decode(), summ.num_iterations, summ.device_time_in_seconds * 1e3, "ms")
