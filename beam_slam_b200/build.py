@@ -44,7 +44,7 @@ def build_host(force=False):
     out = os.path.join(LIB, "libbsfuse.so")
     deps = _deps(HOST, (".cpp", ".h")) + [os.path.join(LIB, "libbsnls.so")]
     if force or _newer(out, deps):
-        cmd = ["g++", "-std=c++17", "-O2", "-march=x86-64-v3", "-fPIC", "-shared", "-Wall", "-o", out] + \
+        cmd = ["g++", "-std=c++17", "-O2", "-march=x86-64-v3", "-fPIC", "-shared", "-pthread", "-Wall", "-o", out] + \
               [os.path.join(HOST, s) for s in HOST_SOURCES] + ["-L" + LIB, "-lbsnls", "-Wl,-rpath,$ORIGIN"]
         subprocess.check_call(cmd)
     return out

@@ -1,6 +1,8 @@
 #include "flatten.h"
 
+#include <algorithm>
 #include <cstring>
+#include <thread>
 
 namespace bsfuse {
 
@@ -45,14 +47,30 @@ void FlatProblem::Finalize() {
   c.groups = cgroups.data();
 }
 
+namespace {
+// Variable values live in one heap object per variable (as in fuse): copying 200 k of them one by one is bound by cache
+// misses, so large graphs split the range over a few threads (a window of some hundred variables stays on the caller's).
+template <typename F> void ForBlocks(size_t n, const F& body) {
+  constexpr size_t kGrain = 16384;
+  const size_t nt = std::min<size_t>(std::min<size_t>(8, std::max(1u, std::thread::hardware_concurrency())), n / kGrain);
+  if (nt <= 1) { body(0, n); return; }
+  std::vector<std::thread> pool;
+  for (size_t t = 1; t < nt; ++t) pool.emplace_back([&, t] { body(n * t / nt, n * (t + 1) / nt); });
+  body(0, n / nt);
+  for (auto& th : pool) th.join();
+}
+}  // namespace
+
 void FlatProblem::ScatterValues(const double* values) const {
-  for (size_t b = 0; b < block_variable.size(); ++b)
-    std::memcpy(block_variable[b]->data(), values + block_offset[b], sizeof(double) * block_size[b]);
+  ForBlocks(block_variable.size(), [&](size_t b0, size_t b1) {
+    for (size_t b = b0; b < b1; ++b) std::memcpy(block_variable[b]->data(), values + block_offset[b], sizeof(double) * block_size[b]);
+  });
 }
 
 void FlatProblem::GatherValues() {
-  for (size_t b = 0; b < block_variable.size(); ++b)
-    std::memcpy(block_values.data() + block_offset[b], block_variable[b]->data(), sizeof(double) * block_size[b]);
+  ForBlocks(block_variable.size(), [&](size_t b0, size_t b1) {
+    for (size_t b = b0; b < b1; ++b) std::memcpy(block_values.data() + block_offset[b], block_variable[b]->data(), sizeof(double) * block_size[b]);
+  });
 }
 
 namespace {
