@@ -52,6 +52,27 @@ class ProblemBuilder:
         self.nres += 1
         return len(g["res_index"]) - 1
 
+    def add_marginal(self, blocks, A, b, x_bar):
+        """fuse_constraints::MarginalConstraint (marginal_constraint.h:85-96): blocks in order, A[i] = rows x 3 per block
+        (tangent columns), b = rows, x_bar[i] = the block's linearisation point (ambient). Rows <= 15, blocks <= 10."""
+        n, rows = len(blocks), len(b)
+        assert 1 <= n <= cabi.MARGINAL_MAX_BLOCKS and rows <= cabi.MARGINAL_MAX_ROWS
+        c = np.zeros(cabi.FACTOR_STRIDE[cabi.FACTOR_MARGINAL])
+        c[0] = n
+        off = 0
+        for i, blk in enumerate(blocks):
+            xb = np.asarray(x_bar[i], np.float64).reshape(-1)
+            assert xb.size == self.size[blk]
+            c[1 + i] = xb.size
+            c[26 + off:26 + off + xb.size] = xb
+            off += xb.size
+            Ai = np.asarray(A[i], np.float64).reshape(rows, 3)
+            for r in range(rows):
+                c[58 + r * 30 + 3 * i:58 + r * 30 + 3 * i + 3] = Ai[r]
+        c[11:11 + rows] = np.asarray(b, np.float64)
+        slots = list(blocks) + [-1] * (cabi.MARGINAL_MAX_BLOCKS - n)
+        return self.add_factor(cabi.FACTOR_MARGINAL, slots, c)
+
     def build(self):
         cams = np.asarray(self.cameras, np.float64) if self.cameras else np.zeros((0, cabi.CAMERA_STRIDE))
         groups = {t: {k: np.asarray(v) for k, v in g.items()} for t, g in self.factors.items()}

@@ -26,11 +26,18 @@ struct NvtxRange { explicit NvtxRange(const char* name) { nvtxRangePushA(name); 
 
 thread_local std::string g_create_error;
 
-const int kNumBlocks[BSNLS_NUM_FACTOR_TYPES] = {3, 10, 5, 4, 6, 2, 2, 1, 2};
-const int kNumRes[BSNLS_NUM_FACTOR_TYPES] = {2, 15, 15, 6, 6, 6, 3, 3, 3};
+const int kNumBlocks[BSNLS_NUM_FACTOR_TYPES] = {3, 10, 5, 4, 6, 2, 2, 1, 2, BSNLS_MARGINAL_MAX_BLOCKS};   // block slots per factor in a group's `blocks`
+const int kNumRes[BSNLS_NUM_FACTOR_TYPES] = {2, 15, 15, 6, 6, 6, 3, 3, 3, BSNLS_MARGINAL_MAX_ROWS};
 const int kStride[BSNLS_NUM_FACTOR_TYPES] = {BSNLS_REPROJECTION_STRIDE, BSNLS_IMU_DELTA_STRIDE, BSNLS_IMU_PRIOR_STRIDE,
                                              BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE,
-                                             BSNLS_ORIENTATION_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_VEC3_STRIDE};
+                                             BSNLS_ORIENTATION_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_MARGINAL_STRIDE};
+// blocks factor i of a group really uses: the marginal prior lists its blocks first and pads the slots with -1
+inline int UsedBlocks(const bsnls_factor_group& G, int64_t i) {
+  const int nbk = kNumBlocks[G.type];
+  if (G.type != BSNLS_FACTOR_MARGINAL) return nbk;
+  int n = 0; while (n < nbk && G.blocks[i * nbk + n] >= 0) ++n;
+  return n;
+}
 
 // Device memory of a handle. bsnls_set_problem carves every buffer of a problem out of ONE device arena and fills the
 // uploaded ones from ONE pinned staging buffer with a single host-to-device copy (a sliding window re-flattens its graph
@@ -714,12 +721,18 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     const int nbk = kNumBlocks[G.type];
     for (int64_t i = 0; i < G.count; ++i) {
       bool any = false;
-      for (int b = 0; b < nbk; ++b) {
+      const int used = UsedBlocks(G, i);
+      if (G.type == BSNLS_FACTOR_MARGINAL) {   // the shape in consts must agree with the block list and the block sizes
+        const double* c = G.consts + i * BSNLS_MARGINAL_STRIDE;
+        if (used < 1 || (int)c[0] != used) return h->fail(BSNLS_ERR_INVALID, "marginal factor: block count and consts[0] disagree");
+        for (int b = 0; b < used; ++b) { const int blk = G.blocks[i * nbk + b]; if (blk >= 0 && blk < nb && (int)c[1 + b] != pr->block_size[blk]) return h->fail(BSNLS_ERR_INVALID, "marginal factor: block size table disagrees with the problem"); }
+      }
+      for (int b = 0; b < used; ++b) {
         const int blk = G.blocks[i * nbk + b];
         if (blk < 0 || blk >= nb) return h->fail(BSNLS_ERR_INVALID, "block index out of range");
         any = any || !pr->block_constant[blk];
       }
-      if (any) for (int b = 0; b < nbk; ++b) { const int blk = G.blocks[i * nbk + b]; if (!pr->block_constant[blk]) active[blk] = 1; }
+      if (any) for (int b = 0; b < used; ++b) { const int blk = G.blocks[i * nbk + b]; if (!pr->block_constant[blk]) active[blk] = 1; }
     }
   }
   std::sort(gfg.begin(), gfg.end(), [](const bsnls_factor_group* a, const bsnls_factor_group* b) { return a->type < b->type; });
@@ -889,8 +902,10 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     }
     for (const bsnls_factor_group* G : gfg) {
       const int nbk = kNumBlocks[G->type];
-      for (int64_t i = 0; i < G->count; ++i)
-        for (int b1 = 0; b1 < nbk; ++b1) for (int b2 = 0; b2 < b1; ++b2) link(fpos[G->blocks[i * nbk + b1]], fpos[G->blocks[i * nbk + b2]]);
+      for (int64_t i = 0; i < G->count; ++i) {
+        const int used = UsedBlocks(*G, i);
+        for (int b1 = 0; b1 < used; ++b1) for (int b2 = 0; b2 < b1; ++b2) link(fpos[G->blocks[i * nbk + b1]], fpos[G->blocks[i * nbk + b2]]);
+      }
     }
     for (auto& v : adj) { std::sort(v.begin(), v.end()); v.erase(std::unique(v.begin(), v.end()), v.end()); }
     // Two candidate orders, each with the slot (position in the padded sequence, kTileBlocks per tile) of every block; the
@@ -1247,7 +1262,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     const int nbk = kNumBlocks[G->type];
     for (int i = 0; i < G->count; ++i) {
       bool any = false;
-      for (int b = 0; b < nbk; ++b) {
+      for (int b = 0; b < UsedBlocks(*G, i); ++b) {
         const int blk = G->blocks[(int64_t)i * nbk + b];
         any = any || !pr->block_constant[blk];
         if (epos[blk] >= 0) return h->fail(BSNLS_ERR_UNSUPPORTED, "a non-reprojection factor references an elimination-group-0 block");
@@ -1261,11 +1276,11 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
   for (const bsnls_factor_group* G : gfg) gf_id[G->type].assign(G->count, -1);
   int64_t joff = 0, roff = 0;
   for (int f = 0; f < h->ngf; ++f) {
-    const bsnls_factor_group* G = refs[f].g; const int i = refs[f].i, nbk = kNumBlocks[G->type], nr = kNumRes[G->type], stride = kStride[G->type];
+    const bsnls_factor_group* G = refs[f].g; const int i = refs[f].i, slots = kNumBlocks[G->type], nbk = UsedBlocks(*G, i), nr = kNumRes[G->type], stride = kStride[G->type];
     if (!refs[f].removed) h->ngf_active++;
     gf_id[G->type][i] = f;
     gf_type.push_back(G->type); gf_nblk.push_back(nbk); gf_nres.push_back(nr);
-    for (int b = 0; b < kGfMaxBlocks; ++b) gf_blocks.push_back(b < nbk ? G->blocks[(int64_t)i * nbk + b] : -1);
+    for (int b = 0; b < kGfMaxBlocks; ++b) gf_blocks.push_back(b < nbk ? G->blocks[(int64_t)i * slots + b] : -1);
     gf_coff.push_back((long long)gf_consts.size());
     gf_consts.insert(gf_consts.end(), G->consts + (int64_t)i * stride, G->consts + (int64_t)(i + 1) * stride);
     gf_loss_type.push_back(G->loss_type ? G->loss_type[i] : 0); gf_loss_a.push_back(G->loss_param ? G->loss_param[i] : 0.0);

@@ -430,6 +430,40 @@ template <typename T> __device__ __forceinline__ void ImuDelta(const double* __r
   for (int k = 0; k < 3; ++k) { r[9 + k] = bg_j[k] - bg_i[k]; r[12 + k] = ba_j[k] - ba_i[k]; }
   ApplyLeft<T, 15>(c + 62, r);
 }
+// fuse_constraints/src/marginal_cost_function.cpp:58-113: r = b + sum_i A_i Minus(x_bar_i, x_i). The reference's Jacobian
+// is A_i times the Minus Jacobian evaluated at x_i (orientation_3d_stamped.h:130-142) -- not the derivative of the angle-axis
+// difference -- so the dual part of a quaternion block's delta is that linear map applied to the dual parts of x.
+__device__ __forceinline__ double TVal(double x) { return x; }
+__device__ __forceinline__ double TVal(const Dual& x) { return x.a; }
+__device__ __forceinline__ double TDer(double) { return 0.0; }
+__device__ __forceinline__ double TDer(const Dual& x) { return x.v; }
+__device__ __forceinline__ void TSet(double& t, double a, double) { t = a; }
+__device__ __forceinline__ void TSet(Dual& t, double a, double v) { t = Dual(a, v); }
+template <typename T> __device__ __forceinline__ void MarginalFactor(const double* __restrict__ c, const T* p, T* r) {
+  const int nb = (int)c[0];
+  const double* bvec = c + 11; const double* xbar = c + 26; const double* A = c + 58;
+  for (int i = 0; i < BSNLS_MARGINAL_MAX_ROWS; ++i) r[i] = T(bvec[i]);
+  int off = 0;
+  for (int b = 0; b < nb; ++b) {
+    const int sz = (int)c[1 + b];
+    T d[3];
+    if (sz == 4) {
+      const double x[4] = {TVal(p[off]), TVal(p[off + 1]), TVal(p[off + 2]), TVal(p[off + 3])};
+      const double dx[4] = {TDer(p[off]), TDer(p[off + 1]), TDer(p[off + 2]), TDer(p[off + 3])};
+      double aa[3]; PriorOrientationDelta<double>(x, xbar + off, aa);
+      TSet(d[0], aa[0], 2.0 * (-x[1] * dx[0] + x[0] * dx[1] + x[3] * dx[2] - x[2] * dx[3]));
+      TSet(d[1], aa[1], 2.0 * (-x[2] * dx[0] - x[3] * dx[1] + x[0] * dx[2] + x[1] * dx[3]));
+      TSet(d[2], aa[2], 2.0 * (-x[3] * dx[0] + x[2] * dx[1] - x[1] * dx[2] + x[0] * dx[3]));
+    } else {
+      for (int k = 0; k < 3; ++k) d[k] = p[off + k] - xbar[off + k];
+    }
+    for (int i = 0; i < BSNLS_MARGINAL_MAX_ROWS; ++i) {
+      const double* a = A + i * 30 + 3 * b;
+      r[i] = r[i] + (a[0] * d[0] + a[1] * d[1] + a[2] * d[2]);
+    }
+    off += sz;
+  }
+}
 // Dispatch over the non-reprojection factor types (ids of bsnls_factor_type); p = concatenated ambient blocks.
 template <typename T> __device__ __forceinline__ void EvalGenericFactor(int type, const double* __restrict__ c, const T* p, T* r) {
   switch (type) {
@@ -449,6 +483,7 @@ template <typename T> __device__ __forceinline__ void EvalGenericFactor(int type
     case 6: DeltaOrientation(p, p + 4, c, r); ApplyLeft<T, 3>(c + 4, r); break;
     case 7: for (int k = 0; k < 3; ++k) r[k] = p[k] - c[k]; ApplyLeft<T, 3>(c + 3, r); break;
     case 8: for (int k = 0; k < 3; ++k) r[k] = (p[3 + k] - p[k]) - c[k]; ApplyLeft<T, 3>(c + 3, r); break;
+    case 9: MarginalFactor(c, p, r); break;
     default: break;
   }
 }

@@ -74,11 +74,21 @@ typedef enum bsnls_factor_type {
      bs_common/src/bs_common/utils.cpp:88-158). blocks: x  |  x1,x2; consts: mean|delta[3], A[9]. */
   BSNLS_FACTOR_ABSOLUTE_VEC3 = 7,
   BSNLS_FACTOR_RELATIVE_VEC3 = 8,
-  BSNLS_NUM_FACTOR_TYPES = 9
+  /* fuse_constraints::MarginalConstraint -> MarginalCostFunction (fuse_constraints/src/marginal_cost_function.cpp:41-113):
+     the linear prior that marginalizeVariables leaves on the remaining variables (marginalize_variables.cpp:166-258),
+     cost(x) = || A1 (x1 (-) x1_bar) + ... + An (xn (-) xn_bar) + b ||^2, (-) = the variable's Minus (quaternion: angle-axis of
+     x_bar^-1 * x, orientation_3d_stamped.h:117-128; vectors: difference); the Jacobian is Ai times the Minus Jacobian at x
+     (:130-142), as the reference takes it. The only type with a variable shape: BSNLS_MARGINAL_MAX_BLOCKS block slots per
+     factor in `blocks` (unused slots -1, used ones first), at most BSNLS_MARGINAL_MAX_ROWS residual rows (unused rows zero).
+     consts (BSNLS_MARGINAL_STRIDE): n (number of blocks), size[10] (ambient size of block i: 3 or 4; 0 unused), b[15],
+     x_bar[32] (ambient, blocks packed in order), A[15][30] row-major (three tangent columns per block, blocks in order). */
+  BSNLS_FACTOR_MARGINAL = 9,
+  BSNLS_NUM_FACTOR_TYPES = 10
 } bsnls_factor_type;
 
 enum { BSNLS_IMU_DELTA_STRIDE = 288, BSNLS_IMU_PRIOR_STRIDE = 241, BSNLS_POSE_STRIDE = 43,
-       BSNLS_ORIENTATION_STRIDE = 13, BSNLS_VEC3_STRIDE = 12, BSNLS_REPROJECTION_STRIDE = 2 };
+       BSNLS_ORIENTATION_STRIDE = 13, BSNLS_VEC3_STRIDE = 12, BSNLS_REPROJECTION_STRIDE = 2,
+       BSNLS_MARGINAL_MAX_BLOCKS = 10, BSNLS_MARGINAL_MAX_ROWS = 15, BSNLS_MARGINAL_STRIDE = 1 + 10 + 15 + 32 + 15 * 30 };
 
 /* fuse_loss plugins (dependencies/fuse/fuse_loss/src/ *.cpp) wrap ceres::LossFunction classes, one scale parameter `a` each.
    CAUCHY .. TUKEY are Ceres' own classes (loss_function.cc, third-party; Tukey as in Ceres 2.x); DCS, FAIR, GEMAN_MCCLURE

@@ -25,17 +25,17 @@
 namespace orc {
 
 static int NumBlocks(int type) {
-  static const int n[BSNLS_NUM_FACTOR_TYPES] = {3, 10, 5, 4, 6, 2, 2, 1, 2};
+  static const int n[BSNLS_NUM_FACTOR_TYPES] = {3, 10, 5, 4, 6, 2, 2, 1, 2, BSNLS_MARGINAL_MAX_BLOCKS};   // block slots per factor
   return n[type];
 }
 static int NumRes(int type) {
-  static const int n[BSNLS_NUM_FACTOR_TYPES] = {2, 15, 15, 6, 6, 6, 3, 3, 3};
+  static const int n[BSNLS_NUM_FACTOR_TYPES] = {2, 15, 15, 6, 6, 6, 3, 3, 3, BSNLS_MARGINAL_MAX_ROWS};
   return n[type];
 }
 static int ConstStride(int type) {
   static const int n[BSNLS_NUM_FACTOR_TYPES] = {BSNLS_REPROJECTION_STRIDE, BSNLS_IMU_DELTA_STRIDE,
       BSNLS_IMU_PRIOR_STRIDE, BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE,
-      BSNLS_ORIENTATION_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_VEC3_STRIDE};
+      BSNLS_ORIENTATION_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_MARGINAL_STRIDE};
   return n[type];
 }
 
@@ -58,6 +58,7 @@ static void EvaluateCost(const bsnls_problem* P, int type, const double* consts,
       AutoDiffEvaluate<RelOrientationFunctor, 8>(consts, params, residual, jac); break;
     case BSNLS_FACTOR_ABSOLUTE_VEC3: AutoDiffEvaluate<AbsVec3Functor, 3>(consts, params, residual, jac); break;
     case BSNLS_FACTOR_RELATIVE_VEC3: AutoDiffEvaluate<RelVec3Functor, 6>(consts, params, residual, jac); break;
+    case BSNLS_FACTOR_MARGINAL: MarginalEvaluate(consts, params, residual, jac); break;
   }
 }
 
@@ -139,6 +140,7 @@ static bool BuildModel(const bsnls_problem* P, Model* M) {
       ResBlock& r = M->rb[ri];
       r.type = G.type; r.idx = i; r.nb = nbk; r.nr = NumRes(G.type);
       for (int b = 0; b < nbk; ++b) r.blocks[b] = G.blocks[(int64_t)i * nbk + b];
+      if (G.type == BSNLS_FACTOR_MARGINAL) { r.nb = 0; while (r.nb < nbk && r.blocks[r.nb] >= 0) ++r.nb; }   // used slots first, -1 after
     }
   }
   // Program reduction (ceres reduced_program: RemoveFixedBlocks)

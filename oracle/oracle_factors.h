@@ -320,6 +320,40 @@ inline void QuatMinus(const double* x1, const double* x2, double* delta) {
   QuaternionProduct(inv, x2, qd); QuaternionToAngleAxis(qd, delta);
 }
 
+// fuse_constraints::MarginalCostFunction::Evaluate (fuse_constraints/src/marginal_cost_function.cpp:58-113):
+// residual = b + sum_i A_i Minus(x_bar_i, x_i); jacobian_i = A_i * MinusJacobian(x_i) for a quaternion block
+// (orientation_3d_stamped.h:130-142), A_i for a vector block. consts as documented at BSNLS_FACTOR_MARGINAL.
+inline void MarginalEvaluate(const double* c, const double* const* params, double* residual, double** jac) {
+  const int nb = (int)c[0];
+  const double* bvec = c + 11; const double* xbar = c + 26; const double* A = c + 58;
+  for (int i = 0; i < BSNLS_MARGINAL_MAX_ROWS; ++i) residual[i] = bvec[i];
+  int off = 0;
+  for (int b = 0; b < nb; ++b) {
+    const int sz = (int)c[1 + b];
+    double d[3];
+    if (sz == 4) QuatMinus(xbar + off, params[b], d);
+    else for (int k = 0; k < 3; ++k) d[k] = params[b][k] - xbar[off + k];
+    for (int i = 0; i < BSNLS_MARGINAL_MAX_ROWS; ++i) {
+      const double* a = A + i * 30 + 3 * b;
+      residual[i] += a[0] * d[0] + a[1] * d[1] + a[2] * d[2];
+    }
+    if (jac && jac[b]) {
+      if (sz == 4) {
+        const double* x = params[b];
+        const double x0 = 2 * x[0], x1 = 2 * x[1], x2 = 2 * x[2], x3 = 2 * x[3];
+        const double Jm[12] = {-x1, x0, x3, -x2,  -x2, -x3, x0, x1,  -x3, x2, -x1, x0};   // 3x4 row-major
+        for (int i = 0; i < BSNLS_MARGINAL_MAX_ROWS; ++i) {
+          const double* a = A + i * 30 + 3 * b;
+          for (int k = 0; k < 4; ++k) jac[b][i * 4 + k] = a[0] * Jm[k] + a[1] * Jm[4 + k] + a[2] * Jm[8 + k];
+        }
+      } else {
+        for (int i = 0; i < BSNLS_MARGINAL_MAX_ROWS; ++i) for (int k = 0; k < 3; ++k) jac[b][i * 3 + k] = A[i * 30 + 3 * b + k];
+      }
+    }
+    off += sz;
+  }
+}
+
 // ceres::CauchyLoss / HuberLoss ::Evaluate (ceres/loss_function.cc); fuse wrappers:
 // dependencies/fuse/fuse_loss/src/cauchy_loss.cpp:65-68, huber_loss.cpp.
 inline void LossEvaluate(int type, double a, double s, double rho[3]) {

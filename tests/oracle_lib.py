@@ -125,11 +125,12 @@ def evaluate(problem):
     return cost.value, res, grad
 
 
-def cost_function(problem, ftype, index):
-    """Raw CostFunction::Evaluate: residual, list of ambient row-major Jacobians per block."""
+def cost_function(problem, ftype, index, sizes=None):
+    """Raw CostFunction::Evaluate: residual, list of ambient row-major Jacobians per block (sizes: the ambient block sizes of
+    a factor type with a variable shape -- the marginal prior)."""
     lib = load()
     nr = cabi.FACTOR_NRES[ftype]
-    sizes = cabi.FACTOR_BLOCK_SIZES[ftype]
+    sizes = sizes if sizes is not None else cabi.FACTOR_BLOCK_SIZES[ftype]
     res = np.zeros(nr)
     jac = np.zeros(nr * sum(sizes))
     assert lib.oracle_cost_function(C.byref(problem.c), ftype, index, _p(res), _p(jac)) == 0
