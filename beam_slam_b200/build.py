@@ -14,7 +14,7 @@ HOST = os.path.join(HERE, "host")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-shared", "-cudart", "static"]
-HOST_SOURCES = ["fuse_mirror.cpp", "flatten.cpp", "gpu_hash_graph.cpp", "preintegrator.cpp", "synthetic.cpp", "smoother_replay.cpp", "capi.cpp"]
+HOST_SOURCES = ["fuse_mirror.cpp", "flatten.cpp", "gpu_hash_graph.cpp", "preintegrator.cpp", "synthetic.cpp", "smoother_replay.cpp", "marginalize.cpp", "capi.cpp"]
 
 
 def _newer(target, sources):

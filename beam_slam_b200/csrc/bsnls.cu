@@ -156,7 +156,7 @@ struct bsnls_handle {
   struct ResRef { int type; int idx; int row; };   // idx: sorted-observation id or generic-factor id
   std::vector<ResRef> res_order; int64_t num_res_rows = 0;
   int64_t gfJ_size = 0, gfR_size = 0;
-  std::vector<int> gf_roff_h, gf_nres_h;
+  std::vector<int> gf_roff_h, gf_nres_h, gf_joff_h, gf_nblk_h;
   int nb_obs = 0, nb_lm = 0, nb_act = 0;  // partial-sum block counts
   int n_eval_items = 0, nb_eval = 0;      // pose-major Jacobian pass: warp items, blocks of 8 items (cost partials at x)
   std::vector<int> obs_pm_h; DevMem d_obs_pm;
@@ -1287,7 +1287,7 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     gf_joff.push_back((int)joff); gf_roff.push_back((int)roff);
     joff += (int64_t)nr * 3 * nbk; roff += nr;
   }
-  h->gfJ_size = joff; h->gfR_size = roff; h->gf_roff_h = gf_roff; h->gf_nres_h = gf_nres;
+  h->gfJ_size = joff; h->gfR_size = roff; h->gf_roff_h = gf_roff; h->gf_nres_h = gf_nres; h->gf_joff_h = gf_joff; h->gf_nblk_h = gf_nblk;
   // contributions per f-block and per S destination
   std::vector<int> fg_ptr(h->nf + 1, 0), fg_fac, fg_lb;
   {
@@ -2132,6 +2132,45 @@ int bsnls_evaluate(bsnls_handle* h, double* cost, double* residuals, int64_t* nu
     for (int b = 0; b < h->num_blocks; ++b) { if (h->blk_tan[b] < 0) continue; for (int k = 0; k < 3; ++k) gradient[n + k] = grad[h->blk_tan[b] + k]; n += 3; }
   }
   h->jac_valid = true;
+  return BSNLS_OK;
+}
+
+int bsnls_linearize(bsnls_handle* h, int32_t count, const int32_t* residual_blocks, double* residuals, double* jacobians) {
+  NvtxRange nvtx_range("bsnls_linearize");
+  if (!h) return BSNLS_ERR_INVALID;
+  if (!h->has_problem) return h->fail(BSNLS_ERR_STATE, "bsnls_linearize before bsnls_set_problem");
+  if (count < 0 || (count > 0 && (!residual_blocks || !residuals || !jacobians))) return h->fail(BSNLS_ERR_INVALID, "bsnls_linearize: null argument");
+  if (h->world > 1) return h->fail(BSNLS_ERR_UNSUPPORTED, "bsnls_linearize is a single-GPU call");
+  for (int q = 0; q < count; ++q) if (residual_blocks[q] < 0 || residual_blocks[q] >= (int)h->res_order.size()) return h->fail(BSNLS_ERR_INVALID, "bsnls_linearize: residual block %d out of range", residual_blocks[q]);
+  CK(cudaSetDevice(h->device));
+  int rc = InitState(h, false);
+  if (rc != BSNLS_OK) return rc;
+  EnqueueEval(h);     // residuals and Jacobians of every factor at the current values, loss correction applied
+  std::vector<double> jrec((size_t)h->nobs * kJRec), gfr(h->gfR_size), gfj(h->gfJ_size);
+  if (h->nobs) CK(cudaMemcpyAsync(jrec.data(), h->d_Jrec.p, sizeof(double) * jrec.size(), cudaMemcpyDeviceToHost, h->stream));
+  if (h->gfR_size) CK(cudaMemcpyAsync(gfr.data(), h->d_gfR.p, sizeof(double) * gfr.size(), cudaMemcpyDeviceToHost, h->stream));
+  if (h->gfJ_size) CK(cudaMemcpyAsync(gfj.data(), h->d_gfJ.p, sizeof(double) * gfj.size(), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream)); CK(cudaGetLastError());
+  constexpr int kR = BSNLS_MARGINAL_MAX_ROWS, kC = 30;
+  std::memset(residuals, 0, sizeof(double) * kR * (size_t)count); std::memset(jacobians, 0, sizeof(double) * kR * kC * (size_t)count);
+  for (int q = 0; q < count; ++q) {
+    const auto& r = h->res_order[residual_blocks[q]];
+    double* R = residuals + (size_t)q * kR; double* J = jacobians + (size_t)q * kR * kC;
+    if (r.type == BSNLS_FACTOR_REPROJECTION) {   // record: E[6] | r[2] | Fq[6] | ts; blocks q, t, landmark; F_t = ts E
+      const double* rec = jrec.data() + (size_t)h->obs_pm_h[r.idx] * kJRec;
+      for (int i = 0; i < 2; ++i) {
+        R[i] = rec[6 + i];
+        for (int k = 0; k < 3; ++k) { J[i * kC + k] = rec[8 + 3 * i + k]; J[i * kC + 3 + k] = rec[14] * rec[3 * i + k]; J[i * kC + 6 + k] = rec[3 * i + k]; }
+      }
+    } else {
+      const int f = r.idx, nr = h->gf_nres_h[f], ncol = 3 * h->gf_nblk_h[f];
+      for (int i = 0; i < nr; ++i) {
+        R[i] = gfr[h->gf_roff_h[f] + i];
+        for (int k = 0; k < ncol; ++k) J[i * kC + k] = gfj[(size_t)h->gf_joff_h[f] + (size_t)i * ncol + k];
+      }
+    }
+  }
+  h->jac_valid = false;
   return BSNLS_OK;
 }
 

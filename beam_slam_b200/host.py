@@ -39,6 +39,11 @@ def load_library():
     lib.bsfuse_last_timing.argtypes = [G, C.POINTER(C.c_double)]
     lib.bsfuse_evaluate.argtypes = [G, C.POINTER(C.c_double)]
     lib.bsfuse_get_covariance.argtypes = [G, C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(C.c_double)]
+    lib.bsfuse_build_pose_chain.argtypes = [G, C.c_int, C.c_uint64]
+    lib.bsfuse_marginalize.argtypes = [G, C.c_char_p, C.c_int, C.POINTER(C.c_int)]
+    _pi = C.POINTER(C.c_int)
+    lib.bsfuse_marginalize_next.argtypes = [C.c_int, _pi, _pi, _pi, C.POINTER(C.c_double), C.POINTER(C.c_double), _pi, _pi,
+                                            C.POINTER(C.c_double), C.POINTER(C.c_double)]
     _pd = C.POINTER(C.c_double)
     lib.bsfuse_preintegrate.argtypes = [_pd, C.c_int, C.c_double, _pd, _pd, _pd, C.c_double, _pd, _pd]
     R = C.c_void_p
@@ -118,6 +123,28 @@ class HashGraph:
         g.config = config
         return g
 
+    @classmethod
+    def pose_chain(cls, n, seed=0):
+        """n stamped poses, a prior on the first, odometry between neighbours and the links 0-2 and 1-3 (no landmarks)."""
+        g = cls()
+        if g._lib.bsfuse_build_pose_chain(g._g, n, seed) != 0:
+            raise ValueError(g._lib.bsfuse_last_error(g._g).decode())
+        g.config = 3
+        return g
+
+    def marginalize(self, uuids):
+        """fuse_constraints::marginalizeVariables (host/marginalize.h) for the variables with these UUIDs, then
+        Graph::update with the transaction. Returns (constraints removed, marginal constraints added, variables removed)."""
+        out = (C.c_int * 3)()
+        rc = self._lib.bsfuse_marginalize(self._g, b"".join(uuids), len(uuids), out)
+        if rc == -1:
+            raise KeyError(self._lib.bsfuse_last_error(self._g).decode())
+        if rc == -2:
+            raise ValueError(self._lib.bsfuse_last_error(self._g).decode())
+        if rc != 0:
+            raise RuntimeError(self._lib.bsfuse_last_error(self._g).decode())
+        return tuple(int(v) for v in out)
+
     @staticmethod
     def synthetic_options(config):
         o = cabi.Options()
@@ -130,7 +157,9 @@ class HashGraph:
             raise ValueError(self._lib.bsfuse_last_error(self._g).decode())
         return problem_to_numpy(cp.contents)
 
-    def block_uuids(self, n):
+    def block_uuids(self, n=None):
+        """UUID (16 bytes) of the first n blocks (default: all), in flatten() order."""
+        n = len(self.flatten().block_size) if n is None else n
         out = []
         buf = C.create_string_buffer(16)
         for i in range(n):
@@ -192,6 +221,22 @@ class HashGraph:
         if self._lib.bsfuse_evaluate(self._g, C.byref(c)) != 0:
             raise RuntimeError(self._lib.bsfuse_last_error(self._g).decode())
         return c.value
+
+
+def marginalize_next(terms):
+    """fuse_constraints::detail::marginalizeNext (host/marginalize.cpp). terms: list of (variables, [A_i rows x 3], b).
+    Returns (variables, [A_i], b) of the marginal on the variables other than the lowest-ordered one."""
+    lib = load_library()
+    rows = np.array([len(t[2]) for t in terms], np.int32); nv = np.array([len(t[0]) for t in terms], np.int32)
+    vs = np.array([v for t in terms for v in t[0]], np.int32)
+    A = np.concatenate([np.asarray(a, np.float64).reshape(-1) for t in terms for a in t[1]])
+    b = np.concatenate([np.asarray(t[2], np.float64) for t in terms])
+    onv = C.c_int(); ov = np.zeros(16, np.int32); oA = np.zeros(16 * 64 * 3); ob = np.zeros(64)
+    pi, pd = C.POINTER(C.c_int), C.POINTER(C.c_double)
+    r = lib.bsfuse_marginalize_next(len(terms), rows.ctypes.data_as(pi), nv.ctypes.data_as(pi), vs.ctypes.data_as(pi), A.ctypes.data_as(pd),
+                                    b.ctypes.data_as(pd), C.byref(onv), ov.ctypes.data_as(pi), oA.ctypes.data_as(pd), ob.ctypes.data_as(pd))
+    n = onv.value
+    return [int(v) for v in ov[:n]], [oA[i * r * 3:(i + 1) * r * 3].reshape(r, 3).copy() for i in range(n)], ob[:r].copy()
 
 
 def preintegrate(imu, t_end, bg, ba, noise=(0.00057, 0.00094, 0.0000037, 0.0000024), info_weight=1.0):

@@ -1,8 +1,11 @@
 // C interface over the host-side mirror, for the ctypes plumbing in beam_slam_b200/host.py.
 #include <cstring>
+#include <cmath>
 #include <memory>
+#include <random>
 
 #include "gpu_hash_graph.h"
+#include "marginalize.h"
 #include "preintegrator.h"
 #include "smoother_replay.h"
 #include "synthetic.h"
@@ -128,6 +131,79 @@ int bsfuse_get_covariance(bsfuse_graph* g, const int* block_pairs, int n, int us
     return 0;
   } catch (const std::out_of_range& e) { g->error = e.what(); return -1; }
   catch (const std::exception& e) { g->error = e.what(); return -3; }
+}
+
+// ---- marginalisation (marginalize.h) ----
+// A small pose graph without landmarks for the marginalisation tests: n stamped poses on a helix, a prior on the first,
+// odometry between neighbours and two longer links (0-2, 1-3), measurements from the truth plus noise, values perturbed.
+int bsfuse_build_pose_chain(bsfuse_graph* g, int n, uint64_t seed) {
+  try {
+    if (n < 4) throw std::invalid_argument("pose chain: at least four poses");
+    std::mt19937_64 rng(seed); std::normal_distribution<double> N(0.0, 1.0);
+    struct Pose { double q[4], p[3]; Variable::SharedPtr vq, vp; };
+    std::vector<Pose> ps(n);
+    auto qmul = [](const double* a, const double* b, double* r) {
+      r[0] = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3]; r[1] = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+      r[2] = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1]; r[3] = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0]; };
+    auto qrot = [&](const double* q, const double* v, double* r) { const double vq[4] = {0, v[0], v[1], v[2]}, qc[4] = {q[0], -q[1], -q[2], -q[3]}; double t[4], u[4]; qmul(q, vq, t); qmul(t, qc, u); r[0] = u[1]; r[1] = u[2]; r[2] = u[3]; };
+    auto small_q = [&](double sigma, double* q) { const double a[3] = {sigma * N(rng), sigma * N(rng), sigma * N(rng)}; const double nrm = std::sqrt(1.0 + 0.25 * (a[0] * a[0] + a[1] * a[1] + a[2] * a[2])); q[0] = 1.0 / nrm; for (int k = 0; k < 3; ++k) q[1 + k] = 0.5 * a[k] / nrm; };
+    for (int k = 0; k < n; ++k) {
+      const double th = 0.35 * k;
+      ps[k].q[0] = std::cos(0.5 * th); ps[k].q[1] = 0.1 * std::sin(0.5 * th); ps[k].q[2] = 0.2 * std::sin(0.5 * th); ps[k].q[3] = std::sqrt(1.0 - 0.05) * std::sin(0.5 * th);
+      const double nq = std::sqrt(ps[k].q[0] * ps[k].q[0] + ps[k].q[1] * ps[k].q[1] + ps[k].q[2] * ps[k].q[2] + ps[k].q[3] * ps[k].q[3]);
+      for (double& v : ps[k].q) v /= nq;
+      ps[k].p[0] = 2.0 * std::cos(th); ps[k].p[1] = 2.0 * std::sin(th); ps[k].p[2] = 0.1 * k;
+      const Time t(10 + k, 0);
+      ps[k].vq = variables::Orientation3DStamped(t); ps[k].vp = variables::Position3DStamped(t);
+      double dq[4], qv[4]; small_q(0.02, dq); qmul(ps[k].q, dq, qv);
+      for (int i = 0; i < 4; ++i) ps[k].vq->data()[i] = qv[i];
+      for (int i = 0; i < 3; ++i) ps[k].vp->data()[i] = ps[k].p[i] + 0.05 * N(rng);
+      g->graph.addVariable(ps[k].vp); g->graph.addVariable(ps[k].vq);
+    }
+    double cov[36] = {0}; for (int i = 0; i < 6; ++i) cov[i * 6 + i] = i < 3 ? 4e-4 : 1e-4;
+    double mean[7] = {ps[0].p[0], ps[0].p[1], ps[0].p[2], ps[0].q[0], ps[0].q[1], ps[0].q[2], ps[0].q[3]};
+    g->graph.addConstraint(constraints::AbsolutePose3DStamped("PRIOR", *ps[0].vp, *ps[0].vq, mean, cov));
+    auto rel = [&](int a, int b) {
+      const double qa_c[4] = {ps[a].q[0], -ps[a].q[1], -ps[a].q[2], -ps[a].q[3]};
+      double d[3] = {ps[b].p[0] - ps[a].p[0], ps[b].p[1] - ps[a].p[1], ps[b].p[2] - ps[a].p[2]}, dp[3], dq[4], nq[4], dqn[4];
+      qrot(qa_c, d, dp); qmul(qa_c, ps[b].q, dq); small_q(0.01, nq); qmul(dq, nq, dqn);
+      const double delta[7] = {dp[0] + 0.02 * N(rng), dp[1] + 0.02 * N(rng), dp[2] + 0.02 * N(rng), dqn[0], dqn[1], dqn[2], dqn[3]};
+      g->graph.addConstraint(constraints::RelativePose3DStamped("ODOM", *ps[a].vp, *ps[a].vq, *ps[b].vp, *ps[b].vq, delta, cov));
+    };
+    for (int k = 0; k + 1 < n; ++k) rel(k, k + 1);
+    rel(0, 2); rel(1, 3);
+    return 0;
+  } catch (const std::exception& e) { g->error = e.what(); return -1; }
+}
+// marginalizeVariables + Graph::update for the variables with the given UUIDs (16 bytes each). out: constraints removed,
+// marginal constraints added, variables removed. -1: unknown variable, -2: a marginal does not fit the GPU factor, -3: other
+int bsfuse_marginalize(bsfuse_graph* g, const unsigned char* uuids, int n, int out[3]) {
+  try {
+    std::vector<UUID> v(n);
+    for (int i = 0; i < n; ++i) std::memcpy(v[i].data.data(), uuids + 16 * i, 16);
+    const Transaction t = marginalizeVariables("MARGINALIZATION", v, g->graph);
+    UpdateGraph(g->graph, t);
+    out[0] = static_cast<int>(t.removed_constraints.size()); out[1] = static_cast<int>(t.added_constraints.size()); out[2] = static_cast<int>(t.removed_variables.size());
+    return 0;
+  } catch (const std::out_of_range& e) { g->error = e.what(); return -1; }
+  catch (const std::invalid_argument& e) { g->error = e.what(); return -2; }
+  catch (const std::exception& e) { g->error = e.what(); return -3; }
+}
+// detail::marginalizeNext on flat arrays (all blocks three columns wide): term t has term_rows[t] rows and term_nvars[t]
+// variables; vars, A (rows x 3 per variable, row-major) and b are the terms' data one after the other. Outputs sized by
+// the caller (at most 16 variables, 64 rows). Returns the number of rows of the marginal.
+int bsfuse_marginalize_next(int nterms, const int* term_rows, const int* term_nvars, const int* vars, const double* A, const double* b,
+                            int* out_nvars, int* out_vars, double* out_A, double* out_b) {
+  std::vector<LinearTerm> terms(nterms);
+  for (int t = 0; t < nterms; ++t) {
+    for (int i = 0; i < term_nvars[t]; ++i) { terms[t].variables.push_back(static_cast<unsigned int>(*vars++)); terms[t].cols.push_back(3); terms[t].A.emplace_back(A, A + 3 * term_rows[t]); A += 3 * term_rows[t]; }
+    terms[t].b.assign(b, b + term_rows[t]); b += term_rows[t];
+  }
+  const LinearTerm m = marginalizeNext(terms);
+  *out_nvars = static_cast<int>(m.variables.size());
+  for (size_t i = 0; i < m.variables.size(); ++i) { out_vars[i] = static_cast<int>(m.variables[i]); std::memcpy(out_A, m.A[i].data(), sizeof(double) * m.A[i].size()); out_A += m.A[i].size(); }
+  std::memcpy(out_b, m.b.data(), sizeof(double) * m.b.size());
+  return static_cast<int>(m.b.size());
 }
 
 // ---- sliding-window replay (smoother_replay.h) ----

@@ -7,18 +7,20 @@
 namespace bsfuse {
 
 namespace {
-struct TypeInfo { int type; int nblocks; int stride; };
+struct TypeInfo { int type; int nblocks; int stride; int nres; };
 const std::unordered_map<std::string, TypeInfo>& TypeTable() {
   static const std::unordered_map<std::string, TypeInfo> t = {
-      {"bs_constraints::EuclideanReprojectionConstraint", {BSNLS_FACTOR_REPROJECTION, 3, BSNLS_REPROJECTION_STRIDE}},
-      {"bs_constraints::RelativeImuState3DStampedConstraint", {BSNLS_FACTOR_IMU_DELTA, 10, BSNLS_IMU_DELTA_STRIDE}},
-      {"bs_constraints::AbsoluteImuState3DStampedConstraint", {BSNLS_FACTOR_IMU_PRIOR, 5, BSNLS_IMU_PRIOR_STRIDE}},
-      {"fuse_constraints::RelativePose3DStampedConstraint", {BSNLS_FACTOR_RELATIVE_POSE, 4, BSNLS_POSE_STRIDE}},
-      {"bs_constraints::RelativePose3DStampedWithExtrinsicsConstraint", {BSNLS_FACTOR_RELATIVE_POSE_EXTRINSICS, 6, BSNLS_POSE_STRIDE}},
-      {"fuse_constraints::AbsolutePose3DStampedConstraint", {BSNLS_FACTOR_ABSOLUTE_POSE, 2, BSNLS_POSE_STRIDE}},
-      {"fuse_constraints::RelativeOrientation3DStampedConstraint", {BSNLS_FACTOR_RELATIVE_ORIENTATION, 2, BSNLS_ORIENTATION_STRIDE}},
-      {"bs_constraints::AbsoluteConstraint3D", {BSNLS_FACTOR_ABSOLUTE_VEC3, 1, BSNLS_VEC3_STRIDE}},
-      {"bs_constraints::RelativeConstraint3D", {BSNLS_FACTOR_RELATIVE_VEC3, 2, BSNLS_VEC3_STRIDE}},
+      {"bs_constraints::EuclideanReprojectionConstraint", {BSNLS_FACTOR_REPROJECTION, 3, BSNLS_REPROJECTION_STRIDE, 2}},
+      {"bs_constraints::RelativeImuState3DStampedConstraint", {BSNLS_FACTOR_IMU_DELTA, 10, BSNLS_IMU_DELTA_STRIDE, 15}},
+      {"bs_constraints::AbsoluteImuState3DStampedConstraint", {BSNLS_FACTOR_IMU_PRIOR, 5, BSNLS_IMU_PRIOR_STRIDE, 15}},
+      {"fuse_constraints::RelativePose3DStampedConstraint", {BSNLS_FACTOR_RELATIVE_POSE, 4, BSNLS_POSE_STRIDE, 6}},
+      {"bs_constraints::RelativePose3DStampedWithExtrinsicsConstraint", {BSNLS_FACTOR_RELATIVE_POSE_EXTRINSICS, 6, BSNLS_POSE_STRIDE, 6}},
+      {"fuse_constraints::AbsolutePose3DStampedConstraint", {BSNLS_FACTOR_ABSOLUTE_POSE, 2, BSNLS_POSE_STRIDE, 6}},
+      {"fuse_constraints::RelativeOrientation3DStampedConstraint", {BSNLS_FACTOR_RELATIVE_ORIENTATION, 2, BSNLS_ORIENTATION_STRIDE, 3}},
+      {"bs_constraints::AbsoluteConstraint3D", {BSNLS_FACTOR_ABSOLUTE_VEC3, 1, BSNLS_VEC3_STRIDE, 3}},
+      {"bs_constraints::RelativeConstraint3D", {BSNLS_FACTOR_RELATIVE_VEC3, 2, BSNLS_VEC3_STRIDE, 3}},
+      // the only type with a variable number of blocks: nblocks here = slots in the block list (marginal_constraint.h:85-96)
+      {"fuse_constraints::MarginalConstraint", {BSNLS_FACTOR_MARGINAL, BSNLS_MARGINAL_MAX_BLOCKS, BSNLS_MARGINAL_STRIDE, BSNLS_MARGINAL_MAX_ROWS}},
   };
   return t;
 }
@@ -79,10 +81,11 @@ void ResolveHint(const HashGraph& graph, const Constraint& c, FlatProblem& P) {
   auto ti = TypeTable().find(c.type());
   if (ti == TypeTable().end()) throw std::invalid_argument("constraint type not supported by the GPU path: " + c.type());
   const TypeInfo& info = ti->second;
-  if (static_cast<int>(c.variables().size()) != info.nblocks) throw std::invalid_argument("unexpected variable count for " + c.type());
+  const int nvar = static_cast<int>(c.variables().size());
+  if (info.type == BSNLS_FACTOR_MARGINAL ? (nvar < 1 || nvar > info.nblocks) : nvar != info.nblocks) throw std::invalid_argument("unexpected variable count for " + c.type());
   Constraint::FlatHint& hnt = c.flat_hint;
-  hnt.type = info.type; hnt.nblocks = info.nblocks; hnt.stride = info.stride; hnt.camera = -1;
-  for (int b = 0; b < info.nblocks; ++b) hnt.vars[b] = &graph.getVariable(c.variables()[b]);  // variables_.at(uuid), :515
+  hnt.type = info.type; hnt.nblocks = nvar; hnt.slots = info.nblocks; hnt.nres = info.nres; hnt.stride = info.stride; hnt.camera = -1;
+  for (int b = 0; b < nvar; ++b) hnt.vars[b] = &graph.getVariable(c.variables()[b]);  // variables_.at(uuid), :515
   if (info.type == BSNLS_FACTOR_REPROJECTION) {
     const auto& pl = c.payload();
     std::vector<double> cam(pl.begin() + 2, pl.begin() + 19);  // K(4), T(12), w
@@ -138,7 +141,7 @@ void Flatten(const HashGraph& graph, FlatProblem* out) {
     if (c.flat_hint.owner != &P) ResolveHint(graph, c, P);
     const Constraint::FlatHint& hnt = c.flat_hint;
     FlatProblem::Group& g = P.groups[hnt.type];
-    for (int b = 0; b < hnt.nblocks; ++b) g.blocks.push_back(hnt.vars[b]->flat_index);
+    for (int b = 0; b < hnt.slots; ++b) g.blocks.push_back(b < hnt.nblocks ? hnt.vars[b]->flat_index : -1);
     const auto& pl = c.payload();
     if (hnt.type == BSNLS_FACTOR_REPROJECTION) {
       g.consts.push_back(pl[0]); g.consts.push_back(pl[1]);
@@ -150,6 +153,7 @@ void Flatten(const HashGraph& graph, FlatProblem* out) {
       g.loss_type.push_back(c.loss() ? static_cast<int>(c.loss()->type) : BSNLS_LOSS_NONE);
       g.loss_param.push_back(c.loss() ? c.loss()->a : 0.0);
     }
+    c.flat_hint.res_index = res_index;
     g.res_index.push_back(res_index++);
   }
   P.Finalize();

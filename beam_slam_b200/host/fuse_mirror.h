@@ -114,7 +114,9 @@ class Constraint {
   // What the flattener resolved for this constraint the first time it saw it in a graph (type dispatch, variable
   // objects, camera class): the SoA mirror kept up to date at addConstraint time instead of re-deriving it on every
   // optimize (hash_graph.cpp:506-521 re-news every cost function per solve).
-  struct FlatHint { const void* owner = nullptr; int type = -1, nblocks = 0, stride = 0, camera = -1; Variable* vars[10] = {}; };
+  // slots: entries per factor in the group's block list (a marginal prior pads its unused ones with -1); res_index: the
+  // constraint's createProblem number in the last flatten (what bsnls_linearize takes)
+  struct FlatHint { const void* owner = nullptr; int type = -1, nblocks = 0, slots = 0, nres = 0, stride = 0, camera = -1, res_index = -1; Variable* vars[10] = {}; };
   mutable FlatHint flat_hint;
   const std::vector<double>& payload() const { return payload_; }
   Constraint(UUID u, std::string type, std::string source, std::vector<UUID> vars, std::vector<double> payload)

@@ -119,6 +119,19 @@ SolverSummary GpuHashGraph::optimize(const SolverOptions& options) {
   return s;
 }
 
+void GpuHashGraph::Linearize(const std::vector<const Constraint*>& constraints, std::vector<double>* residuals, std::vector<double>* jacobians) const {
+  EnsureHandle(last_options_);
+  if (SyncProblem() != BSNLS_OK) throw std::runtime_error(std::string("linearize: ") + bsnls_last_error(handle_));
+  std::vector<int32_t> ids;
+  for (const Constraint* c : constraints) {
+    if (c->flat_hint.owner != &flat_ || c->flat_hint.res_index < 0) throw std::logic_error("linearize: the constraint is not part of this graph");
+    ids.push_back(c->flat_hint.res_index);
+  }
+  residuals->assign(ids.size() * BSNLS_MARGINAL_MAX_ROWS, 0.0); jacobians->assign(ids.size() * BSNLS_MARGINAL_MAX_ROWS * 30, 0.0);
+  if (bsnls_linearize(handle_, static_cast<int32_t>(ids.size()), ids.data(), residuals->data(), jacobians->data()) != BSNLS_OK)
+    throw std::runtime_error(std::string("linearize: ") + bsnls_last_error(handle_));
+}
+
 SolverSummary GpuHashGraph::optimizeFor(double max_time_s, const SolverOptions& options) {
   // The reference subtracts the createProblem time from the budget (hash_graph.cpp:433-439): optimize() does the same
   // with the time flattening and bsnls_set_problem took before it hands the rest to the device loop.

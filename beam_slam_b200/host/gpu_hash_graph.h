@@ -32,6 +32,11 @@ class GpuHashGraph : public HashGraph {
   // bsnls_set_values), bsnls_solve, bsnls_get_values + scatter; and whether the device problem was reused
   struct Timing { double flatten = 0, upload = 0, solve = 0, download = 0; bool structure_reused = false; };
   const Timing& lastTiming() const { return timing_; }
+  // fuse_constraints::detail::linearize (marginalize_variables.cpp:281-399) of constraints of this graph at the current
+  // values, on the device (bsnls_linearize): per constraint BSNLS_MARGINAL_MAX_ROWS residuals and a
+  // BSNLS_MARGINAL_MAX_ROWS x 30 row-major tangent Jacobian, three columns per variable of the constraint.
+  // std::runtime_error if the device call fails.
+  void Linearize(const std::vector<const Constraint*>& constraints, std::vector<double>* residuals, std::vector<double>* jacobians) const;
  private:
   void EnsureHandle(const SolverOptions& options) const;
   // Brings the device problem up to date with the graph: unchanged structure (structureVersion) -> values only;

@@ -229,6 +229,14 @@ int bsnls_evaluate(bsnls_handle* handle, double* cost, double* residuals, int64_
 int bsnls_get_covariance(bsnls_handle* handle, const int32_t* pairs, int32_t num_pairs, int32_t use_tangent_space, double* out);
 
 /* ---- introspection used by the parity tests ("ordering and sparsity pattern bit-exact") ---- */
+/* replaces: fuse_constraints::detail::linearize (fuse_constraints/src/marginalize_variables.cpp:281-399) for `count`
+   residual blocks given by their createProblem numbers (res_index), at the values the handle holds: the loss-corrected
+   residual (BSNLS_MARGINAL_MAX_ROWS doubles per block, unused rows zero) and the tangent-space Jacobian
+   (BSNLS_MARGINAL_MAX_ROWS x 30 row-major per block: three columns per parameter block in the factor's block order, unused
+   ones zero). One evaluation of residuals and Jacobians on the device serves the whole batch; marginalizeVariables of the
+   host mirror (host/marginalize.cpp) is its caller. Single GPU. */
+int bsnls_linearize(bsnls_handle* handle, int32_t count, const int32_t* residual_blocks, double* residuals, double* jacobians);
+
 /* e-block / f-block lists in elimination order: indices into the caller's block arrays. */
 int bsnls_get_ordering(bsnls_handle* handle, int32_t* e_blocks, int32_t* num_e, int32_t* f_blocks,
                        int32_t* num_f);

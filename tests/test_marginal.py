@@ -97,3 +97,74 @@ def test_marginal_factor_shape_is_checked():
     p = cabi.FlatProblem(p.block_size, p.block_manifold, p.block_constant, p.block_group, p.block_values, p.cameras, p.groups)
     with pytest.raises(BsnlsError):
         Solver().set_problem(p)
+
+
+def test_marginalize_next_reproduces_the_reference_golden_values():
+    """test_marginalize_variables.cpp:358-414 (MarginalizeNext): the literal terms and the literal expected marginal."""
+    from beam_slam_b200 import host
+    A1 = [[0.99999999999999922284, 4.4999993911720714834e-08, -2.9999995598828377297e-08],
+          [-3.181980062078038074e-08, 0.70710678118654701763, 1.0606600528428877794e-08],
+          [1.7320505793505525105e-08, -8.6602525498080673572e-09, 0.57735026918962550901]]
+    b1 = [-2.9999995786018886696e-08, -4.2426400911723613558e-08, -5.1961516896187549911e-08]
+    A21 = [[0.99999999999996114219, -1.8482708254510815671e-07, -2.873543621662033587e-07],
+           [1.3069243487082160549e-07, 0.70710678118650927004, -2.5352115484711390536e-07],
+           [1.6590414383954588118e-07, 2.0699913566568639567e-07, 0.57735026918958520792]]
+    A22 = [[-0.91999992754510684367, -0.39191852892782985673, -2.8735440640859089001e-07],
+           [0.27712824947756498073, -0.6505381874582485402, -2.5352112979770691226e-07],
+           [7.1505019336171038447e-08, 2.5546009342625186633e-07, -0.57735026918958520792]]
+    b2 = [7.1706607563166841896e-07, -4.0638046747479327072e-07, 2.1341989211309879704e-07]
+    variables, A, b = host.marginalize_next([([1], [A1], b1), ([3, 1], [A21, A22], b2)])
+    assert variables == [3]
+    A_expected = np.array([[-0.686835139329528, 0.064384601986636, 0.000000153209328],
+                           [0.000000000000000, -0.509885650799691, 0.000000079984512],
+                           [0.000000000000000, 0.000000000000000, 0.408248290463911]])
+    b_expected = np.array([-0.000000497197868, 0.000000315186479, 0.000000114168337])
+    assert np.abs(A[0] - A_expected).max() < 1e-9 and np.abs(b - b_expected).max() < 1e-9
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("which", [0, 1])
+def test_marginalizing_a_pose_leaves_the_solution_and_covariance_of_the_others_unchanged(which):
+    """The check of test_marginalize_variables.cpp:416-560 (optimise, marginalise, re-optimise: values and covariances of the
+    remaining variables agree to 1e-5) on a pose graph: pose 0 (prior + two links -> one marginal on three poses' worth
+    of blocks) or pose 1 (three links)."""
+    from beam_slam_b200 import host
+    g = host.HashGraph.pose_chain(6, seed=4)
+    o = host.HashGraph.synthetic_options(3)
+    s, its = g.optimize(o)
+    assert s.is_solution_usable()
+    p = g.flatten(); uu = g.block_uuids(); x = g.current_values()
+    # the two blocks of the pose to remove: the ones of the `which`-th stamp (pose k has stamp 10 + k)
+    from beam_slam_b200.host import load_library
+    import ctypes as C
+    lib = load_library()
+    def stamped(kind, k):
+        buf = C.create_string_buffer(16); lib.bsfuse_uuid_stamped(kind.encode(), 10 + k, 0, buf); return buf.raw
+    gone = [stamped("fuse_variables::Position3DStamped", which), stamped("fuse_variables::Orientation3DStamped", which)]
+    assert all(u in uu for u in gone)
+    keep = [b for b in range(len(p.block_size)) if uu[b] not in gone]
+    before = {uu[b]: x[p.offsets[b]:p.offsets[b] + p.block_size[b]].copy() for b in keep}
+    cov_before = dict(zip([uu[b] for b in keep], g.covariance([(b, b) for b in keep])))
+    removed_c, added_c, removed_v = g.marginalize(gone)
+    assert removed_v == 2 and removed_c == 3 and added_c >= 1
+    s2, _ = g.optimize(o)
+    assert s2.is_solution_usable()
+    p2 = g.flatten(); uu2 = g.block_uuids(); x2 = g.current_values()
+    assert len(p2.block_size) == len(p.block_size) - 2 and cabi.FACTOR_MARGINAL in p2.groups
+    cov_after = dict(zip(uu2, g.covariance([(b, b) for b in range(len(p2.block_size))])))
+    for b in range(len(p2.block_size)):
+        assert np.abs(x2[p2.offsets[b]:p2.offsets[b] + p2.block_size[b]] - before[uu2[b]]).max() < 1e-5
+        assert np.abs(cov_after[uu2[b]] - cov_before[uu2[b]]).max() < 1e-5
+    with pytest.raises(KeyError):
+        g.marginalize(gone)          # already removed: std::out_of_range
+
+
+@pytest.mark.gpu
+def test_marginal_that_does_not_fit_the_gpu_factor_is_refused():
+    """A keyframe of a visual window touches hundreds of landmarks: more blocks than BSNLS_MARGINAL_MAX_BLOCKS."""
+    from beam_slam_b200 import host
+    g = host.HashGraph.synthetic(1)
+    p = g.flatten(); uu = g.block_uuids()
+    pose_q = int(p.groups[cabi.FACTOR_REPROJECTION]["blocks"][0, 0])
+    with pytest.raises(ValueError):
+        g.marginalize([uu[pose_q]])
