@@ -270,6 +270,8 @@ def load_library():
     lib.bsnls_problem_free.restype = None
     lib.bsnls_get_shard.argtypes = [H, _pi32, _pi32]
     lib.bsnls_get_shard.restype = C.c_int
+    lib.bsnls_linearize.argtypes = [H, C.c_int32, _pi32, _pf64, _pf64]
+    lib.bsnls_linearize.restype = C.c_int
     lib.bsnls_nccl_unique_id.argtypes = [C.c_char * 128]
     lib.bsnls_create_sharded.argtypes = [C.POINTER(Options), C.c_int32, C.c_int32, C.c_char * 128, C.POINTER(H)]
     for name in ("bsnls_create", "bsnls_set_problem", "bsnls_set_values", "bsnls_set_options", "bsnls_solve",

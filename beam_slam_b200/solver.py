@@ -78,6 +78,14 @@ class Solver:
                                              grad.ctypes.data_as(_pf64), C.byref(ng)))
         return cost.value, res, grad
 
+    def linearize(self, residual_blocks):
+        """bsnls_linearize: per residual block (createProblem number) the loss-corrected residual (15, zero padded) and the
+        tangent Jacobian (15 x 30: three columns per parameter block in the factor's block order)."""
+        ids = np.ascontiguousarray(residual_blocks, np.int32)
+        res, jac = np.zeros((len(ids), 15)), np.zeros((len(ids), 15, 30))
+        self._check(self._lib.bsnls_linearize(self._h, len(ids), ids.ctypes.data_as(_pi32), res.ctypes.data_as(_pf64), jac.ctypes.data_as(_pf64)))
+        return res, jac
+
     def ordering(self):
         nb = len(self.problem.block_size)
         e, f = np.zeros(nb, np.int32), np.zeros(nb, np.int32)

@@ -168,3 +168,29 @@ def test_marginal_that_does_not_fit_the_gpu_factor_is_refused():
     pose_q = int(p.groups[cabi.FACTOR_REPROJECTION]["blocks"][0, 0])
     with pytest.raises(ValueError):
         g.marginalize([uu[pose_q]])
+
+
+@pytest.mark.gpu
+def test_device_linearisation_matches_the_oracle_for_every_factor_type():
+    """bsnls_linearize against the oracle's restatement of detail::linearize (marginalize_variables.cpp:281-399) on a
+    visual-inertial window (reprojection with Cauchy loss, IMU deltas, the 15-DoF prior) and on a refinement graph
+    (relative poses with Cauchy loss, the pose prior)."""
+    from beam_slam_b200 import host
+    from beam_slam_b200.solver import Solver
+    for cfg, scale in ((1, 1.0), (3, 0.02)):
+        p = host.HashGraph.synthetic(cfg, scale=scale).flatten()
+        s = Solver(host.HashGraph.synthetic_options(cfg)); s.set_problem(p)
+        for t, g in p.groups.items():
+            n = len(g["res_index"]); pick = sorted(set([0, n // 2, n - 1]))
+            res, jac = s.linearize([int(g["res_index"][i]) for i in pick])
+            nr = cabi.FACTOR_NRES[t]
+            for q, i in enumerate(pick):
+                ro, Jo = orc.linearize(p, t, i)
+                assert np.abs(res[q, :nr] - ro).max() <= 1e-11 * max(1.0, np.abs(ro).max())
+                col = 0
+                for b, blk in enumerate(g["blocks"][i]):
+                    if blk < 0 or p.block_constant[blk]:
+                        continue
+                    assert np.abs(jac[q, :nr, 3 * b:3 * b + 3] - Jo[:, col:col + 3]).max() <= 1e-9 * max(1.0, np.abs(Jo).max())
+                    col += 3
+                assert col == Jo.shape[1]
