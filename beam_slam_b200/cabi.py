@@ -14,14 +14,15 @@ LIB_PATH = os.path.join(_HERE, "lib", "libbsnls.so")
 # ---- enums (include/bsnls.h) ----
 MANIFOLD_EUCLIDEAN, MANIFOLD_QUATERNION = 0, 1
 (FACTOR_REPROJECTION, FACTOR_IMU_DELTA, FACTOR_IMU_PRIOR, FACTOR_RELATIVE_POSE, FACTOR_RELATIVE_POSE_EXTRINSICS,
- FACTOR_ABSOLUTE_POSE, FACTOR_RELATIVE_ORIENTATION, FACTOR_ABSOLUTE_VEC3, FACTOR_RELATIVE_VEC3, FACTOR_MARGINAL) = range(10)
-NUM_FACTOR_TYPES = 10
+ FACTOR_ABSOLUTE_POSE, FACTOR_RELATIVE_ORIENTATION, FACTOR_ABSOLUTE_VEC3, FACTOR_RELATIVE_VEC3, FACTOR_MARGINAL,
+ FACTOR_GRAVITY_ALIGNMENT, FACTOR_ABSOLUTE_ORIENTATION) = range(12)
+NUM_FACTOR_TYPES = 12
 MARGINAL_MAX_BLOCKS, MARGINAL_MAX_ROWS = 10, 15
-FACTOR_NBLOCKS = [3, 10, 5, 4, 6, 2, 2, 1, 2, 10]   # block slots per factor (the marginal prior pads unused ones with -1)
-FACTOR_NRES = [2, 15, 15, 6, 6, 6, 3, 3, 3, 15]
-FACTOR_STRIDE = [2, 288, 241, 43, 43, 43, 13, 12, 12, 508]
+FACTOR_NBLOCKS = [3, 10, 5, 4, 6, 2, 2, 1, 2, 10, 1, 1]   # block slots per factor (the marginal prior pads unused ones with -1)
+FACTOR_NRES = [2, 15, 15, 6, 6, 6, 3, 3, 3, 15, 2, 3]
+FACTOR_STRIDE = [2, 288, 241, 43, 43, 43, 13, 12, 12, 508, 7, 13]
 FACTOR_BLOCK_SIZES = [[4, 3, 3], [4, 3, 3, 3, 3, 4, 3, 3, 3, 3], [4, 3, 3, 3, 3], [3, 4, 3, 4],
-                      [3, 4, 3, 4, 3, 4], [3, 4], [4, 4], [3], [3, 3]]
+                      [3, 4, 3, 4, 3, 4], [3, 4], [4, 4], [3], [3, 3], None, [4], [4]]
 LOSS_NONE, LOSS_CAUCHY, LOSS_HUBER, LOSS_SOFTLONE, LOSS_ARCTAN, LOSS_TUKEY, LOSS_DCS, LOSS_FAIR, LOSS_GEMAN_MCCLURE, LOSS_WELSCH = range(10)
 NOALLOC_MAX_OBSERVATIONS = 4194304
 CAMERA_STRIDE = 20

@@ -484,6 +484,10 @@ template <typename T> __device__ __forceinline__ void EvalGenericFactor(int type
     case 7: for (int k = 0; k < 3; ++k) r[k] = p[k] - c[k]; ApplyLeft<T, 3>(c + 3, r); break;
     case 8: for (int k = 0; k < 3; ++k) r[k] = (p[3 + k] - p[k]) - c[k]; ApplyLeft<T, 3>(c + 3, r); break;
     case 9: MarginalFactor(c, p, r); break;
+    case 10: {  // GravityAlignmentCostFunctor (gravity_alignment_cost_functor.h:53-66)
+      const T g[3] = {T(c[0]), T(c[1]), T(c[2])}; T w[3]; QuaternionRotatePoint(p, g, w);
+      r[0] = c[3] * w[0] + c[4] * w[1]; r[1] = c[5] * w[0] + c[6] * w[1]; break; }
+    case 11: PriorOrientationDelta(p, c, r); ApplyLeft<T, 3>(c + 4, r); break;   // NormalPriorOrientation3DCostFunctor
     default: break;
   }
 }

@@ -24,9 +24,9 @@
 
 namespace {
 const char kMagic[8] = {'B', 'S', 'N', 'L', 'S', 0, 1, 0};
-const int kNumBlocks[BSNLS_NUM_FACTOR_TYPES] = {3, 10, 5, 4, 6, 2, 2, 1, 2, BSNLS_MARGINAL_MAX_BLOCKS};
+const int kNumBlocks[BSNLS_NUM_FACTOR_TYPES] = {3, 10, 5, 4, 6, 2, 2, 1, 2, BSNLS_MARGINAL_MAX_BLOCKS, 1, 1};
 const int kStride[BSNLS_NUM_FACTOR_TYPES] = {BSNLS_REPROJECTION_STRIDE, BSNLS_IMU_DELTA_STRIDE, BSNLS_IMU_PRIOR_STRIDE, BSNLS_POSE_STRIDE,
-                                             BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE, BSNLS_ORIENTATION_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_MARGINAL_STRIDE};
+                                             BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE, BSNLS_ORIENTATION_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_MARGINAL_STRIDE, BSNLS_GRAVITY_STRIDE, BSNLS_ORIENTATION_STRIDE};
 struct Owned {   // a loaded problem owns its arrays: one allocation behind the public struct
   bsnls_problem p;
   std::vector<bsnls_factor_group> groups;

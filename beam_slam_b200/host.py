@@ -40,6 +40,7 @@ def load_library():
     lib.bsfuse_evaluate.argtypes = [G, C.POINTER(C.c_double)]
     lib.bsfuse_get_covariance.argtypes = [G, C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(C.c_double)]
     lib.bsfuse_build_pose_chain.argtypes = [G, C.c_int, C.c_uint64]
+    lib.bsfuse_build_orientation_chain.argtypes = [G]
     lib.bsfuse_marginalize.argtypes = [G, C.c_char_p, C.c_int, C.POINTER(C.c_int)]
     _pi = C.POINTER(C.c_int)
     lib.bsfuse_marginalize_next.argtypes = [C.c_int, _pi, _pi, _pi, C.POINTER(C.c_double), C.POINTER(C.c_double), _pi, _pi,
@@ -156,6 +157,15 @@ class HashGraph:
         if not cp:
             raise ValueError(self._lib.bsfuse_last_error(self._g).decode())
         return problem_to_numpy(cp.contents)
+
+    @classmethod
+    def orientation_chain(cls):
+        """The four orientations and four constraints of test_marginalize_variables.cpp:416-470, literal values."""
+        g = cls()
+        if g._lib.bsfuse_build_orientation_chain(g._g) != 0:
+            raise ValueError(g._lib.bsfuse_last_error(g._g).decode())
+        g.config = 3
+        return g
 
     def block_uuids(self, n=None):
         """UUID (16 bytes) of the first n blocks (default: all), in flatten() order."""

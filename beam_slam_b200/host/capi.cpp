@@ -175,6 +175,23 @@ int bsfuse_build_pose_chain(bsfuse_graph* g, int n, uint64_t seed) {
     return 0;
   } catch (const std::exception& e) { g->error = e.what(); return -1; }
 }
+// The graph of test_marginalize_variables.cpp:416-470 (MarginalizeVariables), literal values: orientations x1, x2, x3, l1
+// (stamps 1, 2, 3 and 3.5 s), a prior on x1 and the relative orientations x1-x2, x2-x3, x2-l1, covariance diag(1, 2, 3).
+int bsfuse_build_orientation_chain(bsfuse_graph* g) {
+  try {
+    auto make = [&](const Time& t, double w, double x, double y, double z) {
+      auto v = variables::Orientation3DStamped(t); v->data()[0] = w; v->data()[1] = x; v->data()[2] = y; v->data()[3] = z; g->graph.addVariable(v); return v; };
+    auto x1 = make(Time(1, 0), 0.927362, 0.1, 0.2, 0.3), x2 = make(Time(2, 0), 0.848625, 0.13798, 0.175959, 0.479411);
+    auto x3 = make(Time(3, 0), 0.735597, 0.170384, 0.144808, 0.63945), l1 = make(Time(3, 500000000), 0.803884, 0.304917, 0.268286, 0.434533);
+    const double cov[9] = {1, 0, 0, 0, 2, 0, 0, 0, 3};
+    const double mean1[4] = {0.92736185, 0.1, 0.2, 0.3}, d23[4] = {0.979795897, 0.0, 0.0, 0.2}, d4[4] = {0.979795897, 0.2, 0.0, 0.0};
+    g->graph.addConstraint(constraints::AbsoluteOrientation3DStamped("test", *x1, mean1, cov));
+    g->graph.addConstraint(constraints::RelativeOrientation3DStamped("test", *x1, *x2, d23, cov));
+    g->graph.addConstraint(constraints::RelativeOrientation3DStamped("test", *x2, *x3, d23, cov));
+    g->graph.addConstraint(constraints::RelativeOrientation3DStamped("test", *x2, *l1, d4, cov));
+    return 0;
+  } catch (const std::exception& e) { g->error = e.what(); return -1; }
+}
 // marginalizeVariables + Graph::update for the variables with the given UUIDs (16 bytes each). out: constraints removed,
 // marginal constraints added, variables removed. -1: unknown variable, -2: a marginal does not fit the GPU factor, -3: other
 int bsfuse_marginalize(bsfuse_graph* g, const unsigned char* uuids, int n, int out[3]) {

@@ -19,6 +19,9 @@ const std::unordered_map<std::string, TypeInfo>& TypeTable() {
       {"fuse_constraints::RelativeOrientation3DStampedConstraint", {BSNLS_FACTOR_RELATIVE_ORIENTATION, 2, BSNLS_ORIENTATION_STRIDE, 3}},
       {"bs_constraints::AbsoluteConstraint3D", {BSNLS_FACTOR_ABSOLUTE_VEC3, 1, BSNLS_VEC3_STRIDE, 3}},
       {"bs_constraints::RelativeConstraint3D", {BSNLS_FACTOR_RELATIVE_VEC3, 2, BSNLS_VEC3_STRIDE, 3}},
+      {"bs_constraints::AbsolutePose3DConstraint", {BSNLS_FACTOR_ABSOLUTE_POSE, 2, BSNLS_POSE_STRIDE, 6}},   // same functor as fuse's (absolute_pose_3d_constraint.cpp:45-50)
+      {"bs_constraints::GravityAlignmentStampedConstraint", {BSNLS_FACTOR_GRAVITY_ALIGNMENT, 1, BSNLS_GRAVITY_STRIDE, 2}},
+      {"fuse_constraints::AbsoluteOrientation3DStampedConstraint", {BSNLS_FACTOR_ABSOLUTE_ORIENTATION, 1, BSNLS_ORIENTATION_STRIDE, 3}},
       // the only type with a variable number of blocks: nblocks here = slots in the block list (marginal_constraint.h:85-96)
       {"fuse_constraints::MarginalConstraint", {BSNLS_FACTOR_MARGINAL, BSNLS_MARGINAL_MAX_BLOCKS, BSNLS_MARGINAL_STRIDE, BSNLS_MARGINAL_MAX_ROWS}},
   };

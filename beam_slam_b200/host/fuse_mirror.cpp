@@ -79,6 +79,18 @@ Constraint::SharedPtr RelativeOrientation3DStamped(const std::string& source, co
   return std::make_shared<Constraint>(NextConstraintUuid(), "fuse_constraints::RelativeOrientation3DStampedConstraint", source,
       std::vector<UUID>{q1.uuid(), q2.uuid()}, pl);
 }
+Constraint::SharedPtr AbsoluteOrientation3DStamped(const std::string& source, const Variable& q, const double mean[4], const double cov[9]) {
+  std::vector<double> pl(mean, mean + 4); pl.resize(13);
+  Require(SqrtInformationFromCovariance(cov, 3, pl.data() + 4), "AbsoluteOrientation3DStampedConstraint: covariance not SPD");
+  return std::make_shared<Constraint>(NextConstraintUuid(), "fuse_constraints::AbsoluteOrientation3DStampedConstraint", source,
+      std::vector<UUID>{q.uuid()}, pl);
+}
+Constraint::SharedPtr GravityAlignmentStamped(const std::string& source, const Variable& q, const double gravity_in_baselink[3], const double cov[4]) {
+  std::vector<double> pl(gravity_in_baselink, gravity_in_baselink + 3); pl.resize(7);
+  Require(SqrtInformationFromCovariance(cov, 2, pl.data() + 3), "GravityAlignmentStampedConstraint: covariance not SPD");
+  return std::make_shared<Constraint>(NextConstraintUuid(), "bs_constraints::GravityAlignmentStampedConstraint", source,
+      std::vector<UUID>{q.uuid()}, pl);
+}
 static std::vector<double> Vec3Payload(const double m[3], const double cov[9]) {
   std::vector<double> pl(m, m + 3); pl.resize(12);
   Require(SqrtInformationFromCovariance(cov, 3, pl.data() + 3), "vector constraint: covariance not SPD");

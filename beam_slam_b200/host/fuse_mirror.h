@@ -161,6 +161,10 @@ Constraint::SharedPtr AbsolutePose3DStamped(const std::string& source, const Var
 // fuse_constraints::RelativeOrientation3DStampedConstraint
 Constraint::SharedPtr RelativeOrientation3DStamped(const std::string& source, const Variable& q1,
     const Variable& q2, const double delta[4], const double cov[9]);
+// fuse_constraints::AbsoluteOrientation3DStampedConstraint (absolute_orientation_3d_stamped_constraint.cpp:49-58)
+Constraint::SharedPtr AbsoluteOrientation3DStamped(const std::string& source, const Variable& q, const double mean[4], const double cov[9]);
+// bs_constraints::GravityAlignmentStampedConstraint (gravity_alignment_stamped_constraint.cpp:12-18); cov is 2x2
+Constraint::SharedPtr GravityAlignmentStamped(const std::string& source, const Variable& q, const double gravity_in_baselink[3], const double cov[4]);
 // bs_constraints::AbsoluteConstraint<T> / RelativeConstraint<T> for 3-vectors (global/absolute_constraint.h:14-28)
 Constraint::SharedPtr AbsoluteVec3(const std::string& source, const Variable& x, const double mean[3], const double cov[9]);
 Constraint::SharedPtr RelativeVec3(const std::string& source, const Variable& x1, const Variable& x2,

@@ -83,11 +83,20 @@ typedef enum bsnls_factor_type {
      consts (BSNLS_MARGINAL_STRIDE): n (number of blocks), size[10] (ambient size of block i: 3 or 4; 0 unused), b[15],
      x_bar[32] (ambient, blocks packed in order), A[15][30] row-major (three tangent columns per block, blocks in order). */
   BSNLS_FACTOR_MARGINAL = 9,
-  BSNLS_NUM_FACTOR_TYPES = 10
+  /* bs_constraints::GravityAlignmentStampedConstraint -> GravityAlignmentCostFunctor
+     (bs_constraints/include/bs_constraints/global/gravity_alignment_cost_functor.h:32-75): the x and y components of
+     R(q_WORLD_BASELINK) * gravity_in_baselink, weighted. blocks: q; consts: gravity_in_baselink[3], A[4] (2x2 row-major). */
+  BSNLS_FACTOR_GRAVITY_ALIGNMENT = 10,
+  /* fuse_constraints::AbsoluteOrientation3DStampedConstraint -> NormalPriorOrientation3DCostFunctor
+     (fuse_constraints/include/fuse_constraints/normal_prior_orientation_3d_cost_functor.h:92-125).
+     blocks: q; consts: mean[4] (w,x,y,z), A[9]. (The prior of test_marginalize_variables.cpp:416-560.) */
+  BSNLS_FACTOR_ABSOLUTE_ORIENTATION = 11,
+  BSNLS_NUM_FACTOR_TYPES = 12
 } bsnls_factor_type;
 
 enum { BSNLS_IMU_DELTA_STRIDE = 288, BSNLS_IMU_PRIOR_STRIDE = 241, BSNLS_POSE_STRIDE = 43,
        BSNLS_ORIENTATION_STRIDE = 13, BSNLS_VEC3_STRIDE = 12, BSNLS_REPROJECTION_STRIDE = 2,
+       BSNLS_GRAVITY_STRIDE = 7,
        BSNLS_MARGINAL_MAX_BLOCKS = 10, BSNLS_MARGINAL_MAX_ROWS = 15, BSNLS_MARGINAL_STRIDE = 1 + 10 + 15 + 32 + 15 * 30 };
 
 /* fuse_loss plugins (dependencies/fuse/fuse_loss/src/ *.cpp) wrap ceres::LossFunction classes, one scale parameter `a` each.

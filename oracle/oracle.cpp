@@ -25,17 +25,17 @@
 namespace orc {
 
 static int NumBlocks(int type) {
-  static const int n[BSNLS_NUM_FACTOR_TYPES] = {3, 10, 5, 4, 6, 2, 2, 1, 2, BSNLS_MARGINAL_MAX_BLOCKS};   // block slots per factor
+  static const int n[BSNLS_NUM_FACTOR_TYPES] = {3, 10, 5, 4, 6, 2, 2, 1, 2, BSNLS_MARGINAL_MAX_BLOCKS, 1, 1};   // block slots per factor
   return n[type];
 }
 static int NumRes(int type) {
-  static const int n[BSNLS_NUM_FACTOR_TYPES] = {2, 15, 15, 6, 6, 6, 3, 3, 3, BSNLS_MARGINAL_MAX_ROWS};
+  static const int n[BSNLS_NUM_FACTOR_TYPES] = {2, 15, 15, 6, 6, 6, 3, 3, 3, BSNLS_MARGINAL_MAX_ROWS, 2, 3};
   return n[type];
 }
 static int ConstStride(int type) {
   static const int n[BSNLS_NUM_FACTOR_TYPES] = {BSNLS_REPROJECTION_STRIDE, BSNLS_IMU_DELTA_STRIDE,
       BSNLS_IMU_PRIOR_STRIDE, BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE,
-      BSNLS_ORIENTATION_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_MARGINAL_STRIDE};
+      BSNLS_ORIENTATION_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_MARGINAL_STRIDE, BSNLS_GRAVITY_STRIDE, BSNLS_ORIENTATION_STRIDE};
   return n[type];
 }
 
@@ -59,6 +59,8 @@ static void EvaluateCost(const bsnls_problem* P, int type, const double* consts,
     case BSNLS_FACTOR_ABSOLUTE_VEC3: AutoDiffEvaluate<AbsVec3Functor, 3>(consts, params, residual, jac); break;
     case BSNLS_FACTOR_RELATIVE_VEC3: AutoDiffEvaluate<RelVec3Functor, 6>(consts, params, residual, jac); break;
     case BSNLS_FACTOR_MARGINAL: MarginalEvaluate(consts, params, residual, jac); break;
+    case BSNLS_FACTOR_GRAVITY_ALIGNMENT: AutoDiffEvaluate<GravityAlignmentFunctor, 4>(consts, params, residual, jac); break;
+    case BSNLS_FACTOR_ABSOLUTE_ORIENTATION: AutoDiffEvaluate<AbsOrientationFunctor, 4>(consts, params, residual, jac); break;
   }
 }
 

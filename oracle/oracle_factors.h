@@ -50,6 +50,28 @@ struct RelOrientationFunctor {
   }
 };
 
+// fuse_constraints::NormalPriorOrientation3DCostFunctor::operator() (normal_prior_orientation_3d_cost_functor.h:92-125):
+// AbsoluteOrientation3DStampedConstraint; blocks q; consts mean[4], A[9]
+struct AbsOrientationFunctor {
+  static constexpr int kRes = 3; static constexpr int kBlocks = 1;
+  static const int* sizes() { static const int s[] = {4}; return s; }
+  template <typename T> static void eval(const double* c, const T* const* p, T* r) {
+    PriorOrientationDelta(p[0], c, r);
+    ApplyLeft<T, 3>(c + 4, r);
+  }
+};
+// bs_constraints::GravityAlignmentCostFunctor::operator() (bs_constraints/global/gravity_alignment_cost_functor.h:53-66):
+// blocks q_WORLD_BASELINK; consts gravity_in_baselink[3], A[4] (2x2 row-major)
+struct GravityAlignmentFunctor {
+  static constexpr int kRes = 2; static constexpr int kBlocks = 1;
+  static const int* sizes() { static const int s[] = {4}; return s; }
+  template <typename T> static void eval(const double* c, const T* const* p, T* r) {
+    const T g[3] = {T(c[0]), T(c[1]), T(c[2])}; T w[3];
+    QuaternionRotatePoint(p[0], g, w);
+    r[0] = c[3] * w[0] + c[4] * w[1]; r[1] = c[5] * w[0] + c[6] * w[1];
+  }
+};
+
 // fuse_constraints::NormalDeltaPose3DCostFunctor::operator()
 // (.../normal_delta_pose_3d_cost_functor.h:107-148): blocks p1,q1,p2,q2; consts b[7], A[36]
 template <typename T>

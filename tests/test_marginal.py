@@ -194,3 +194,68 @@ def test_device_linearisation_matches_the_oracle_for_every_factor_type():
                     assert np.abs(jac[q, :nr, 3 * b:3 * b + 3] - Jo[:, col:col + 3]).max() <= 1e-9 * max(1.0, np.abs(Jo).max())
                     col += 3
                 assert col == Jo.shape[1]
+
+
+def test_gravity_alignment_and_absolute_orientation_cost_functions():
+    """GravityAlignmentCostFunctor (bs_constraints/global/gravity_alignment_cost_functor.h:53-66): A [R(q) g]_xy;
+    NormalPriorOrientation3DCostFunctor (normal_prior_orientation_3d_cost_functor.h:92-125): A AngleAxis(mean^-1 * q)."""
+    q = _quat([0.9, 0.2, -0.3, 0.1]); g = np.array([0.1, -0.2, -9.7]); A2 = np.array([[2.0, 0.5], [0.0, 3.0]])
+    mean = _quat([0.95, 0.1, -0.2, 0.05]); A3 = np.triu(np.arange(1.0, 10.0).reshape(3, 3))
+    b = ProblemBuilder(); iq = b.add_quaternion(q)
+    b.add_factor(cabi.FACTOR_GRAVITY_ALIGNMENT, [iq], np.concatenate([g, A2.ravel()]))
+    b.add_factor(cabi.FACTOR_ABSOLUTE_ORIENTATION, [iq], np.concatenate([mean, A3.ravel()]))
+    p = b.build()
+    w, x, y, z = q
+    R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)], [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                  [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
+    res, _ = orc.cost_function(p, cabi.FACTOR_GRAVITY_ALIGNMENT, 0)
+    assert np.abs(res - A2 @ (R @ g)[:2]).max() < 1e-13
+    res, _ = orc.cost_function(p, cabi.FACTOR_ABSOLUTE_ORIENTATION, 0)
+    assert np.abs(res - A3 @ _minus(mean, q)).max() < 1e-13
+
+
+@pytest.mark.gpu
+def test_gravity_alignment_and_absolute_orientation_on_the_gpu_match_the_oracle():
+    from beam_slam_b200.solver import Solver
+    b = ProblemBuilder()
+    iq = b.add_quaternion(_quat([0.9, 0.2, -0.3, 0.1])); iq2 = b.add_quaternion(_quat([0.8, -0.1, 0.3, 0.4]))
+    b.add_factor(cabi.FACTOR_GRAVITY_ALIGNMENT, [iq], [0.0, 0.0, -9.81, 1.0, 0.2, 0.0, 1.5])
+    b.add_factor(cabi.FACTOR_GRAVITY_ALIGNMENT, [iq2], [0.1, 0.0, -9.8, 1.0, 0.0, 0.0, 1.0], loss_type=cabi.LOSS_CAUCHY, loss_param=1.0)
+    b.add_factor(cabi.FACTOR_ABSOLUTE_ORIENTATION, [iq], np.concatenate([_quat([0.95, 0.1, -0.2, 0.05]), np.eye(3).ravel()]))
+    b.add_factor(cabi.FACTOR_RELATIVE_ORIENTATION, [iq, iq2], np.concatenate([_quat([0.98, 0.0, 0.1, 0.15]), 2 * np.eye(3).ravel()]))
+    p = b.build()
+    s = Solver(); s.set_problem(p)
+    cost, res, grad = s.evaluate(); co, ro, go = orc.evaluate(p)
+    assert abs(cost - co) <= 1e-12 * co and np.abs(res - ro).max() <= 1e-12 * max(1.0, np.abs(ro).max()) and np.abs(grad - go).max() <= 1e-10 * max(1.0, np.abs(go).max())
+    summ, its = s.solve(); so, ito, xo = orc.solve(p)
+    assert len(its) == len(ito) and np.abs(s.get_values() - xo).max() < 1e-8
+    for a, c in zip(its, ito):
+        assert abs(a.cost - c.cost) <= 1e-9 * max(abs(c.cost), 1e-30) + 1e-22
+
+
+@pytest.mark.gpu
+def test_reference_marginalize_variables_scenario():
+    """test_marginalize_variables.cpp:416-560 with its literal graph: optimise, marginalise x1 (the prior and x1-x2 go, one
+    marginal constraint comes), re-optimise; x2, x3, l1 and their covariances agree to 1e-5 with the values before."""
+    import ctypes as C
+    from beam_slam_b200 import host
+    g = host.HashGraph.orientation_chain()
+    o = cabi.Options.defaults()
+    s, _ = g.optimize(o)
+    assert s.is_solution_usable()
+    p = g.flatten(); uu = g.block_uuids(); x = g.current_values()
+    buf = C.create_string_buffer(16); host.load_library().bsfuse_uuid_stamped(b"fuse_variables::Orientation3DStamped", 1, 0, buf)
+    x1 = buf.raw
+    keep = [b for b in range(4) if uu[b] != x1]
+    assert len(keep) == 3
+    before = {uu[b]: x[p.offsets[b]:p.offsets[b] + 4].copy() for b in keep}
+    cov_before = dict(zip([uu[b] for b in keep], g.covariance([(b, b) for b in keep])))
+    assert g.marginalize([x1]) == (2, 1, 1)
+    s2, _ = g.optimize(o)
+    assert s2.is_solution_usable()
+    p2 = g.flatten(); uu2 = g.block_uuids(); x2 = g.current_values()
+    assert len(p2.block_size) == 3
+    cov_after = g.covariance([(b, b) for b in range(3)])
+    for b in range(3):
+        assert np.abs(x2[p2.offsets[b]:p2.offsets[b] + 4] - before[uu2[b]]).max() < 1e-5
+        assert np.abs(cov_after[b] - cov_before[uu2[b]]).max() < 1e-5
