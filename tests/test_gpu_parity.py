@@ -250,6 +250,50 @@ def test_loop_closure_graph_on_the_tile_path_matches_oracle():
     assert _rel(s.get_values(), xo) < 1e-7
 
 
+@pytest.mark.parametrize("order", ["graph", "band"])
+def test_both_orderings_of_the_reduced_system_give_the_oracle_solve(order, monkeypatch):
+    """The two candidate orders of the f-blocks (nested dissection of the block graph with tile padding; reverse
+    Cuthill-McKee line + tile dissection) are only a permutation of the same factorisation: forced one at a time
+    (BSNLS_ORDER) both must reproduce the oracle."""
+    monkeypatch.setenv("BSNLS_ORDER", order)
+    g = host.HashGraph.synthetic(4, scale=0.15)
+    p, opts = g.flatten(), host.HashGraph.synthetic_options(4)
+    s = Solver(opts)
+    s.set_problem(p)
+    summ, its = s.solve()
+    so, ito, xo = orc.solve(p, opts)
+    assert len(its) == len(ito)
+    for a, b in zip(its, ito):
+        assert abs(a.cost - b.cost) <= 1e-9 * abs(b.cost)
+    assert _rel(s.get_values(), xo) < 1e-7
+
+
+def test_disconnected_reduced_system_on_the_tile_path():
+    """Two pose chains that share nothing (the dissection's component branch), 264 unknowns: the tile path must treat the
+    components independently and agree with the oracle; one of the chains is three poses long (a region smaller than a tile)."""
+    b = ProblemBuilder()
+    rng = np.random.default_rng(11)
+    def chain(n, origin):
+        ids = []
+        for k in range(n):
+            q = np.array([1.0, 0.02 * k, -0.01 * k, 0.03 * k]); q /= np.linalg.norm(q)
+            ids.append((b.add_block(origin + np.array([0.5 * k, 0.1 * k, 0.0]) + 0.05 * rng.normal(size=3)), b.add_quaternion(q)))
+        I6 = np.eye(6).ravel()
+        b.add_factor(cabi.FACTOR_ABSOLUTE_POSE, list(ids[0]), np.concatenate([origin, [1, 0, 0, 0], I6]))
+        for k in range(n - 1):
+            b.add_factor(cabi.FACTOR_RELATIVE_POSE, [*ids[k], *ids[k + 1]], np.concatenate([[0.5, 0.1, 0.0, 0.9995, 0.02, -0.01, 0.015], I6]),
+                         loss_type=cabi.LOSS_CAUCHY, loss_param=1.0)
+    chain(41, np.array([0.0, 0.0, 0.0])); chain(3, np.array([10.0, -5.0, 2.0]))
+    p = b.build()
+    s = Solver(); s.set_problem(p)
+    summ, its = s.solve()
+    so, ito, xo = orc.solve(p)
+    assert summ.termination_type == so.termination_type and len(its) == len(ito)
+    for a, c in zip(its, ito):
+        assert abs(a.cost - c.cost) <= 1e-9 * max(abs(c.cost), 1e-30) + 1e-22
+    assert _rel(s.get_values(), xo) < 1e-7
+
+
 @pytest.mark.parametrize("cfg,scale", [(2, 0.25), (3, 0.02)])
 def test_block_sparse_pcg_matches_dense_and_oracle(cfg, scale):
     """K7: block-sparse reduced system + block-Jacobi PCG against the dense DMMA Cholesky path and the oracle.
