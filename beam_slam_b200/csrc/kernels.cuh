@@ -381,27 +381,42 @@ __global__ void __launch_bounds__(256, LM_MINB) landmark_kernel(DeviceProblem P,
   const bool valid = l < P.ne;
   const int start = valid ? P.lm_ptr[l] : 0, end = valid ? P.lm_ptr[l + 1] : 0;
   double a00 = 0, a01 = 0, a02 = 0, a11 = 0, a12 = 0, a22 = 0, g0 = 0, g1 = 0, g2 = 0;
-  // A lane's observations are independent gathers (index, then a 128-byte record somewhere in Jrec): they are issued in
-  // batches of kLmBatch so that their latencies overlap instead of adding up. The record positions of the first batch
-  // (usually all of a lane's observations) are kept for the second pass.
+  // A lane's observations are independent gathers (index, then a 128-byte record somewhere in Jrec). A lane reading its
+  // own record with eight 16-byte loads makes every load instruction of the warp touch 32 different lines (32 L1 wavefronts
+  // for 512 bytes; ncu: the L1 data pipe was the busiest unit at 67 %, lg_throttle stalls). Instead the WARP moves records:
+  // lane q handles 16-byte piece q % 8 of the record of lane q / 8 (+4 per step), so an instruction covers four whole
+  // lines; the pieces go through a per-warp shared-memory buffer (pitch 144 bytes: conflict-free 16-byte accesses) from
+  // which every lane takes its own record. The V records leave the same way: written to the buffer by their lanes,
+  // stored by the warp in 16-byte pieces that are consecutive in memory (a landmark's records are contiguous in Vrec).
+  // Batches of kLmBatch observations per lane, record positions kept for the second pass.
   constexpr int kLmBatch = 3;
+  __shared__ double2 sRec[8][32 * 9];
+  const int lane = threadIdx.x & 31;
+  double2* const buf = sRec[threadIdx.x >> 5];
   int pm0[kLmBatch];
 #pragma unroll
   for (int u = 0; u < kLmBatch; ++u) { const int o = start + sub + u * G; pm0[u] = o < end ? P.obs_pm[o] : -1; }
-  {
-    double2 e0[kLmBatch], e1[kLmBatch], e2[kLmBatch], r[kLmBatch];
+  // the first `pieces` 16-byte pieces of the 32 records at positions pm (one per lane, -1: none) -> buf[lane * 9 + piece]
+  auto stage = [&](int pm, int pieces_log2) {
+    const int per = 1 << pieces_log2;                       // pieces per record: 4 (E, r) or 8 (the whole record)
 #pragma unroll
-    for (int u = 0; u < kLmBatch; ++u) {
-      if (pm0[u] >= 0) { const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)pm0[u] * kJRec); e0[u] = rec[0]; e1[u] = rec[1]; e2[u] = rec[2]; r[u] = rec[3]; }
-      else { e0[u] = e1[u] = e2[u] = r[u] = make_double2(0.0, 0.0); }
+    for (int j = 0; j < 8; ++j) {
+      if ((j << 5) >= (32 << pieces_log2)) break;
+      const int q = lane + 32 * j, slot = q >> pieces_log2, piece = q & (per - 1);
+      const int spm = __shfl_sync(0xffffffffu, pm, slot);
+      buf[slot * 9 + piece] = spm >= 0 ? reinterpret_cast<const double2*>(Jrec + (size_t)spm * kJRec)[piece] : make_double2(0.0, 0.0);
     }
+    __syncwarp();
+  };
 #pragma unroll
-    for (int u = 0; u < kLmBatch; ++u) {
-      // E row0 = (e0.x, e0.y, e1.x), row1 = (e1.y, e2.x, e2.y)
-      a00 += e0[u].x * e0[u].x + e1[u].y * e1[u].y; a01 += e0[u].x * e0[u].y + e1[u].y * e2[u].x; a02 += e0[u].x * e1[u].x + e1[u].y * e2[u].y;
-      a11 += e0[u].y * e0[u].y + e2[u].x * e2[u].x; a12 += e0[u].y * e1[u].x + e2[u].x * e2[u].y; a22 += e1[u].x * e1[u].x + e2[u].y * e2[u].y;
-      g0 += e0[u].x * r[u].x + e1[u].y * r[u].y; g1 += e0[u].y * r[u].x + e2[u].x * r[u].y; g2 += e1[u].x * r[u].x + e2[u].y * r[u].y;
-    }
+  for (int u = 0; u < kLmBatch; ++u) {
+    stage(pm0[u], 2);
+    const double2 e0 = buf[lane * 9], e1 = buf[lane * 9 + 1], e2 = buf[lane * 9 + 2], r = buf[lane * 9 + 3];
+    __syncwarp();
+    // E row0 = (e0.x, e0.y, e1.x), row1 = (e1.y, e2.x, e2.y); records of missing observations are zero
+    a00 += e0.x * e0.x + e1.y * e1.y; a01 += e0.x * e0.y + e1.y * e2.x; a02 += e0.x * e1.x + e1.y * e2.y;
+    a11 += e0.y * e0.y + e2.x * e2.x; a12 += e0.y * e1.x + e2.x * e2.y; a22 += e1.x * e1.x + e2.y * e2.y;
+    g0 += e0.x * r.x + e1.y * r.y; g1 += e0.y * r.x + e2.x * r.y; g2 += e1.x * r.x + e2.y * r.y;
   }
   for (int o = start + sub + kLmBatch * G; o < end; o += G) {   // tracks longer than kLmBatch * G
     const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec);
@@ -418,58 +433,82 @@ __global__ void __launch_bounds__(256, LM_MINB) landmark_kernel(DeviceProblem P,
     g0 += __shfl_xor_sync(0xffffffffu, g0, m); g1 += __shfl_xor_sync(0xffffffffu, g1, m);
     g2 += __shfl_xor_sync(0xffffffffu, g2, m);
   }
-  if (!valid) return;
+  // lanes without a landmark stay for the warp-wide record moves of the second pass (their records are empty)
   const int te = 3 * l;  // e-blocks occupy the first ne_dim tangent entries, 3 each
-  double s0, s1, s2;
-  if (!st->scale_ready) {
-    s0 = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(a00)) : 1.0; s1 = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(a11)) : 1.0;
-    s2 = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(a22)) : 1.0;
-    if (sub == 0) { scale[te] = s0; scale[te + 1] = s1; scale[te + 2] = s2; }
-  } else { s0 = scale[te]; s1 = scale[te + 1]; s2 = scale[te + 2]; }
-  // LM diagonal in unscaled coordinates: D^2 = clamp(c s^2) / (radius s^2)
-  const double radius = st->radius;
-  const double d0 = fmin(fmax(a00 * s0 * s0, opt.min_lm_diagonal), opt.max_lm_diagonal) / (radius * s0 * s0);
-  const double d1 = fmin(fmax(a11 * s1 * s1, opt.min_lm_diagonal), opt.max_lm_diagonal) / (radius * s1 * s1);
-  const double d2 = fmin(fmax(a22 * s2 * s2, opt.min_lm_diagonal), opt.max_lm_diagonal) / (radius * s2 * s2);
-  // Cholesky of M = E^T E + D^2 (lower L), Minv = L^-T L^-1, C = L^-T (upper), z = L^-1 g
-  const double m00 = a00 + d0, m11 = a11 + d1, m22 = a22 + d2;
-  const double l00 = sqrt(m00), l10 = a01 / l00, l20 = a02 / l00;
-  const double t11 = m11 - l10 * l10; const double l11 = sqrt(t11), l21 = (a12 - l20 * l10) / l11;
-  const double t22 = m22 - l20 * l20 - l21 * l21; const double l22 = sqrt(t22);
-  if (!(m00 > 0.0) || !(t11 > 0.0) || !(t22 > 0.0)) { st->lin_fail = 1; }
-  // Linv (lower): i00 = 1/l00, i10 = -l10 i00 / l11, i11 = 1/l11, i20 = -(l20 i00 + l21 i10)/l22, i21 = -l21 i11/l22, i22 = 1/l22
-  const double i00 = 1.0 / l00, i11 = 1.0 / l11, i22 = 1.0 / l22;
-  const double i10 = -l10 * i00 * i11, i21 = -l21 * i11 * i22, i20 = -(l20 * i00 + l21 * i10) * i22;
-  const double z0 = i00 * g0, z1 = i10 * g0 + i11 * g1, z2 = i20 * g0 + i21 * g1 + i22 * g2;
-  if (sub == 0) {
-    double* mi = lm_minv + (size_t)l * 6;  // Minv = Linv^T Linv, stored (00,01,02,11,12,22)
-    mi[0] = i00 * i00 + i10 * i10 + i20 * i20; mi[1] = i10 * i11 + i20 * i21; mi[2] = i20 * i22;
-    mi[3] = i11 * i11 + i21 * i21; mi[4] = i21 * i22; mi[5] = i22 * i22;
-    grad[te] = g0; grad[te + 1] = g1; grad[te + 2] = g2;
-    colsq[te] = a00; colsq[te + 1] = a11; colsq[te + 2] = a22;
-    lm_z[te] = z0; lm_z[te + 1] = z1; lm_z[te + 2] = z2;   // z = C^T E^T r: the Schur right-hand side is sum V z
+  double i00 = 0, i10 = 0, i11 = 0, i20 = 0, i21 = 0, i22 = 0;
+  if (valid) {
+    double s0, s1, s2;
+    if (!st->scale_ready) {
+      s0 = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(a00)) : 1.0; s1 = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(a11)) : 1.0;
+      s2 = opt.jacobi_scaling ? 1.0 / (1.0 + sqrt(a22)) : 1.0;
+      if (sub == 0) { scale[te] = s0; scale[te + 1] = s1; scale[te + 2] = s2; }
+    } else { s0 = scale[te]; s1 = scale[te + 1]; s2 = scale[te + 2]; }
+    // LM diagonal in unscaled coordinates: D^2 = clamp(c s^2) / (radius s^2)
+    const double radius = st->radius;
+    const double d0 = fmin(fmax(a00 * s0 * s0, opt.min_lm_diagonal), opt.max_lm_diagonal) / (radius * s0 * s0);
+    const double d1 = fmin(fmax(a11 * s1 * s1, opt.min_lm_diagonal), opt.max_lm_diagonal) / (radius * s1 * s1);
+    const double d2 = fmin(fmax(a22 * s2 * s2, opt.min_lm_diagonal), opt.max_lm_diagonal) / (radius * s2 * s2);
+    // Cholesky of M = E^T E + D^2 (lower L), Minv = L^-T L^-1, C = L^-T (upper), z = L^-1 g
+    const double m00 = a00 + d0, m11 = a11 + d1, m22 = a22 + d2;
+    const double l00 = sqrt(m00), l10 = a01 / l00, l20 = a02 / l00;
+    const double t11 = m11 - l10 * l10; const double l11 = sqrt(t11), l21 = (a12 - l20 * l10) / l11;
+    const double t22 = m22 - l20 * l20 - l21 * l21; const double l22 = sqrt(t22);
+    if (!(m00 > 0.0) || !(t11 > 0.0) || !(t22 > 0.0)) { st->lin_fail = 1; }
+    // Linv (lower): i00 = 1/l00, i10 = -l10 i00 / l11, i11 = 1/l11, i20 = -(l20 i00 + l21 i10)/l22, i21 = -l21 i11/l22, i22 = 1/l22
+    i00 = 1.0 / l00; i11 = 1.0 / l11; i22 = 1.0 / l22;
+    i10 = -l10 * i00 * i11; i21 = -l21 * i11 * i22; i20 = -(l20 * i00 + l21 * i10) * i22;
+    const double z0 = i00 * g0, z1 = i10 * g0 + i11 * g1, z2 = i20 * g0 + i21 * g1 + i22 * g2;
+    if (sub == 0) {
+      double* mi = lm_minv + (size_t)l * 6;  // Minv = Linv^T Linv, stored (00,01,02,11,12,22)
+      mi[0] = i00 * i00 + i10 * i10 + i20 * i20; mi[1] = i10 * i11 + i20 * i21; mi[2] = i20 * i22;
+      mi[3] = i11 * i11 + i21 * i21; mi[4] = i21 * i22; mi[5] = i22 * i22;
+      grad[te] = g0; grad[te + 1] = g1; grad[te + 2] = g2;
+      colsq[te] = a00; colsq[te + 1] = a11; colsq[te + 2] = a22;
+      lm_z[te] = z0; lm_z[te + 1] = z1; lm_z[te + 2] = z2;   // z = C^T E^T r: the Schur right-hand side is sum V z
+    }
   }
   // pass 2: V = (F^T E) C with C = Linv^T (upper):  V[:,0] = W0 i00; V[:,1] = W0 i10 + W1 i11; V[:,2] = W0 i20 + W1 i21 + W2 i22
-  auto emit = [&](int o, const double2* rec) {
-    const double2 e0 = rec[0], e1 = rec[1], e2 = rec[2];
+  auto make_v = [&](const double2 e0, const double2 e1, const double2 e2, const double2 f0, const double2 f1, const double2 f2, const double ts, double* v) {
     const double E0[3] = {e0.x, e0.y, e1.x}, E1[3] = {e1.y, e2.x, e2.y};
     double F0[6], F1[6];
-    { const double2 f0 = rec[4], f1 = rec[5], f2 = rec[6]; const double ts = rec[7].x;
-      F0[0] = f0.x; F0[1] = f0.y; F0[2] = f1.x; F0[3] = ts * E0[0]; F0[4] = ts * E0[1]; F0[5] = ts * E0[2];
-      F1[0] = f1.y; F1[1] = f2.x; F1[2] = f2.y; F1[3] = ts * E1[0]; F1[4] = ts * E1[1]; F1[5] = ts * E1[2]; }
-    double2* out = reinterpret_cast<double2*>(Vrec + (size_t)o * kVRec);
-    double v[18];
+    F0[0] = f0.x; F0[1] = f0.y; F0[2] = f1.x; F0[3] = ts * E0[0]; F0[4] = ts * E0[1]; F0[5] = ts * E0[2];
+    F1[0] = f1.y; F1[1] = f2.x; F1[2] = f2.y; F1[3] = ts * E1[0]; F1[4] = ts * E1[1]; F1[5] = ts * E1[2];
 #pragma unroll
-    for (int a = 0; a < 6; ++a) {
-      const double w0 = F0[a] * E0[0] + F1[a] * E1[0], w1 = F0[a] * E0[1] + F1[a] * E1[1], w2 = F0[a] * E0[2] + F1[a] * E1[2];
-      v[3 * a] = w0 * i00; v[3 * a + 1] = w0 * i10 + w1 * i11; v[3 * a + 2] = w0 * i20 + w1 * i21 + w2 * i22;
+    for (int a2 = 0; a2 < 6; ++a2) {
+      const double w0 = F0[a2] * E0[0] + F1[a2] * E1[0], w1 = F0[a2] * E0[1] + F1[a2] * E1[1], w2 = F0[a2] * E0[2] + F1[a2] * E1[2];
+      v[3 * a2] = w0 * i00; v[3 * a2 + 1] = w0 * i10 + w1 * i11; v[3 * a2 + 2] = w0 * i20 + w1 * i21 + w2 * i22;
     }
-#pragma unroll
-    for (int k = 0; k < 9; ++k) out[k] = make_double2(v[2 * k], v[2 * k + 1]);
   };
 #pragma unroll
-  for (int u = 0; u < kLmBatch; ++u) if (pm0[u] >= 0) emit(start + sub + u * G, reinterpret_cast<const double2*>(Jrec + (size_t)pm0[u] * kJRec));
-  for (int o = start + sub + kLmBatch * G; o < end; o += G) emit(o, reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec));
+  for (int u = 0; u < kLmBatch; ++u) {
+    stage(pm0[u], 3);
+    double v[18];
+    {
+      const double2* rec = buf + lane * 9;
+      make_v(rec[0], rec[1], rec[2], rec[4], rec[5], rec[6], rec[7].x, v);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 9; ++k) buf[lane * 9 + k] = make_double2(v[2 * k], v[2 * k + 1]);
+    __syncwarp();
+    const int o_mine = pm0[u] >= 0 ? start + sub + u * G : -1;
+#pragma unroll
+    for (int j = 0; j < 9; ++j) {           // 288 pieces of 16 bytes; piece q belongs to the record of lane q / 9
+      const int q = lane + 32 * j, slot = q / 9, part = q - 9 * slot;
+      const int o = __shfl_sync(0xffffffffu, o_mine, slot);
+      if (o >= 0) reinterpret_cast<double2*>(Vrec + (size_t)o * kVRec)[part] = buf[q];
+    }
+    __syncwarp();
+  }
+  if (!valid) return;
+  for (int o = start + sub + kLmBatch * G; o < end; o += G) {
+    const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec);
+    double v[18];
+    make_v(rec[0], rec[1], rec[2], rec[4], rec[5], rec[6], rec[7].x, v);
+    double2* out = reinterpret_cast<double2*>(Vrec + (size_t)o * kVRec);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) out[k] = make_double2(v[2 * k], v[2 * k + 1]);
+  }
 }
 
 // K6b: generic-factor contributions to the gradient and the column norms of every f-block.
