@@ -1456,36 +1456,36 @@ __global__ void __launch_bounds__(256) backsub_kernel(DeviceProblem P, const dou
   const bool valid = l < P.ne;
   const int start = valid ? P.lm_ptr[l] : 0, end = valid ? P.lm_ptr[l + 1] : 0;
   // The first kBsKeep observations of a lane stay in registers between the two passes (E, r and u = F y_pose): with four
-  // lanes per landmark that covers tracks of up to 12, so the records are read from HBM once; their loads are issued
-  // together. Longer tracks re-read the rest.
+  // lanes per landmark that covers tracks of up to 12, so the records are read from HBM once. They are fetched as in
+  // landmark_kernel: the warp loads 16-byte pieces that are consecutive in memory and every lane takes its own record
+  // from a per-warp shared-memory buffer. Longer tracks re-read the rest.
   constexpr int kBsKeep = 3;
+  __shared__ double2 sRec[8][32 * 9];
+  const int lane = threadIdx.x & 31;
+  double2* const buf = sRec[threadIdx.x >> 5];
   double2 ke0[kBsKeep], ke1[kBsKeep], ke2[kBsKeep], kr[kBsKeep]; double ku0[kBsKeep], ku1[kBsKeep];
-  {
-    double2 rc[kBsKeep][8]; int tq[kBsKeep], tt[kBsKeep];
 #pragma unroll
-    for (int b = 0; b < kBsKeep; ++b) {
-      const int o = start + sub + b * G;
-      if (o < end) {
-        const double2* rec = reinterpret_cast<const double2*>(Jrec + (size_t)P.obs_pm[o] * kJRec);
+  for (int b = 0; b < kBsKeep; ++b) {
+    const int o = start + sub + b * G;
+    const int pm = o < end ? P.obs_pm[o] : -1;
+    int tq = -1, tt = -1;
+    if (pm >= 0) { const int pose = P.obs_pose[o]; tq = P.pose_q_tan[pose]; tt = P.pose_t_tan[pose]; }
 #pragma unroll
-        for (int q = 0; q < 8; ++q) rc[b][q] = rec[q];
-        const int pose = P.obs_pose[o]; tq[b] = P.pose_q_tan[pose]; tt[b] = P.pose_t_tan[pose];
-      } else {
-#pragma unroll
-        for (int q = 0; q < 8; ++q) rc[b][q] = make_double2(0.0, 0.0);
-        tq[b] = -1; tt[b] = -1;
-      }
+    for (int j = 0; j < 8; ++j) {
+      const int q = lane + 32 * j, slot = q >> 3, piece = q & 7;
+      const int spm = __shfl_sync(0xffffffffu, pm, slot);
+      buf[slot * 9 + piece] = spm >= 0 ? reinterpret_cast<const double2*>(Jrec + (size_t)spm * kJRec)[piece] : make_double2(0.0, 0.0);
     }
+    __syncwarp();
+    double yp[6];
 #pragma unroll
-    for (int b = 0; b < kBsKeep; ++b) {
-      double yp[6];
-#pragma unroll
-      for (int k = 0; k < 3; ++k) { yp[k] = tq[b] >= 0 ? yf[tq[b] - P.ne_dim + k] : 0.0; yp[3 + k] = tt[b] >= 0 ? yf[tt[b] - P.ne_dim + k] : 0.0; }
-      const double2 e0 = rc[b][0], e1 = rc[b][1], e2 = rc[b][2], f0 = rc[b][4], f1 = rc[b][5], f2 = rc[b][6]; const double ts = rc[b][7].x;
-      ke0[b] = e0; ke1[b] = e1; ke2[b] = e2; kr[b] = rc[b][3];
-      ku0[b] = f0.x * yp[0] + f0.y * yp[1] + f1.x * yp[2] + ts * (e0.x * yp[3] + e0.y * yp[4] + e1.x * yp[5]);
-      ku1[b] = f1.y * yp[0] + f2.x * yp[1] + f2.y * yp[2] + ts * (e1.y * yp[3] + e2.x * yp[4] + e2.y * yp[5]);
-    }
+    for (int k = 0; k < 3; ++k) { yp[k] = tq >= 0 ? yf[tq - P.ne_dim + k] : 0.0; yp[3 + k] = tt >= 0 ? yf[tt - P.ne_dim + k] : 0.0; }
+    const double2* rc = buf + lane * 9;
+    const double2 e0 = rc[0], e1 = rc[1], e2 = rc[2], f0 = rc[4], f1 = rc[5], f2 = rc[6]; const double ts = rc[7].x;
+    ke0[b] = e0; ke1[b] = e1; ke2[b] = e2; kr[b] = rc[3];
+    __syncwarp();
+    ku0[b] = f0.x * yp[0] + f0.y * yp[1] + f1.x * yp[2] + ts * (e0.x * yp[3] + e0.y * yp[4] + e1.x * yp[5]);
+    ku1[b] = f1.y * yp[0] + f2.x * yp[1] + f2.y * yp[2] + ts * (e1.y * yp[3] + e2.x * yp[4] + e2.y * yp[5]);
   }
   double t0 = 0, t1 = 0, t2 = 0;
 #pragma unroll
