@@ -135,7 +135,7 @@ int bsfuse_get_covariance(bsfuse_graph* g, const int* block_pairs, int n, int us
 
 // ---- marginalisation (marginalize.h) ----
 // A small pose graph without landmarks for the marginalisation tests: n stamped poses on a helix, a prior on the first,
-// odometry between neighbours and two longer links (0-2, 1-3), measurements from the truth plus noise, values perturbed.
+// odometry between neighbours and the longer links 0-2, 1-3 (and 2-4 from six poses on), measurements from the truth plus noise, values perturbed.
 int bsfuse_build_pose_chain(bsfuse_graph* g, int n, uint64_t seed) {
   try {
     if (n < 4) throw std::invalid_argument("pose chain: at least four poses");
@@ -172,6 +172,7 @@ int bsfuse_build_pose_chain(bsfuse_graph* g, int n, uint64_t seed) {
     };
     for (int k = 0; k + 1 < n; ++k) rel(k, k + 1);
     rel(0, 2); rel(1, 3);
+    if (n >= 6) rel(2, 4);   // pose 2 then has four neighbours: its marginal is 18 rows tall
     return 0;
   } catch (const std::exception& e) { g->error = e.what(); return -1; }
 }

@@ -161,7 +161,15 @@ Transaction marginalizeVariables(const std::string& source, const std::vector<UU
     for (const LinearTerm& t : linear_terms[i]) {
       std::vector<const Variable*> vars;
       for (unsigned int idx : t.variables) vars.push_back(&graph.getVariable(variable_order[idx]));
-      transaction.added_constraints.push_back(constraints::Marginal(source, vars, t.A, t.b));
+      // the GPU factor holds BSNLS_MARGINAL_MAX_ROWS rows: a taller marginal leaves as several constraints over the same
+      // variables, one per block of rows -- the same cost, since a marginal constraint carries no loss function
+      const int rows = static_cast<int>(t.b.size());
+      for (int r0 = 0; r0 < rows; r0 += BSNLS_MARGINAL_MAX_ROWS) {
+        const int nr = std::min<int>(BSNLS_MARGINAL_MAX_ROWS, rows - r0);
+        std::vector<std::vector<double>> A;
+        for (size_t i = 0; i < t.A.size(); ++i) A.emplace_back(t.A[i].begin() + static_cast<size_t>(r0) * t.cols[i], t.A[i].begin() + static_cast<size_t>(r0 + nr) * t.cols[i]);
+        transaction.added_constraints.push_back(constraints::Marginal(source, vars, A, std::vector<double>(t.b.begin() + r0, t.b.begin() + r0 + nr)));
+      }
     }
   return transaction;
 }

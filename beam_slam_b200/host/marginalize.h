@@ -32,8 +32,9 @@ struct LinearTerm {
 };
 LinearTerm marginalizeNext(const std::vector<LinearTerm>& linear_terms);
 
-// throws std::invalid_argument when a marginal would need more than BSNLS_MARGINAL_MAX_BLOCKS blocks or
-// BSNLS_MARGINAL_MAX_ROWS rows, std::runtime_error when the device linearisation fails
+// throws std::invalid_argument when a marginal would need more than BSNLS_MARGINAL_MAX_BLOCKS blocks (a marginal with more
+// than BSNLS_MARGINAL_MAX_ROWS rows is emitted as several constraints, one per block of rows), std::runtime_error when the
+// device linearisation fails
 Transaction marginalizeVariables(const std::string& source, const std::vector<UUID>& marginalized_variables, GpuHashGraph& graph);
 
 // fuse_core::Graph::update (fuse_core/src/graph.cpp:69-95): added constraints, then removed constraints, then removed variables
