@@ -55,9 +55,12 @@ void FlatProblem::Finalize() {
 namespace {
 // Variable values live in one heap object per variable (as in fuse): copying 200 k of them one by one is bound by cache
 // misses, so large graphs split the range over a few threads (a window of some hundred variables stays on the caller's).
+#ifndef BSFUSE_COPY_THREADS
+#define BSFUSE_COPY_THREADS 8
+#endif
 template <typename F> void ForBlocks(size_t n, const F& body) {
-  constexpr size_t kGrain = 16384;
-  const size_t nt = std::min<size_t>(std::min<size_t>(8, std::max(1u, std::thread::hardware_concurrency())), n / kGrain);
+  constexpr size_t kGrain = 16384, kMaxThreads = BSFUSE_COPY_THREADS;
+  const size_t nt = std::min<size_t>(std::min<size_t>(kMaxThreads, std::max(1u, std::thread::hardware_concurrency())), n / kGrain);
   if (nt <= 1) { body(0, n); return; }
   std::vector<std::thread> pool;
   for (size_t t = 1; t < nt; ++t) pool.emplace_back([&, t] { body(n * t / nt, n * (t + 1) / nt); });
