@@ -259,3 +259,37 @@ def test_reference_marginalize_variables_scenario():
     for b in range(3):
         assert np.abs(x2[p2.offsets[b]:p2.offsets[b] + 4] - before[uu2[b]]).max() < 1e-5
         assert np.abs(cov_after[b] - cov_before[uu2[b]]).max() < 1e-5
+
+
+@pytest.mark.gpu
+def test_successive_marginalisation_relinearises_the_marginal_prior():
+    """Marginalise pose 0, then pose 1: the second step linearises the MarginalConstraint the first one left (it is tied to
+    pose 1), as marginalize_variables.cpp:203-224 does with any connected constraint. The optimum and the covariances of the
+    remaining poses still agree with the full graph's (1e-5); marginalising both poses in one call gives the same."""
+    import ctypes as C
+    from beam_slam_b200 import host
+    lib = host.load_library()
+    def stamped(kind, k):
+        buf = C.create_string_buffer(16); lib.bsfuse_uuid_stamped(kind.encode(), 10 + k, 0, buf); return buf.raw
+    def pose(k):
+        return [stamped("fuse_variables::Position3DStamped", k), stamped("fuse_variables::Orientation3DStamped", k)]
+    o = host.HashGraph.synthetic_options(3)
+    results = []
+    for steps in ([pose(0), pose(1)], [pose(0) + pose(1)]):
+        g = host.HashGraph.pose_chain(7, seed=9)
+        assert g.optimize(o)[0].is_solution_usable()
+        p = g.flatten(); uu = g.block_uuids(); x = g.current_values()
+        full = {uu[b]: x[p.offsets[b]:p.offsets[b] + p.block_size[b]].copy() for b in range(len(uu))}
+        cov_full = dict(zip(uu, g.covariance([(b, b) for b in range(len(uu))])))
+        for gone in steps:
+            g.marginalize(gone)
+            assert g.optimize(o)[0].is_solution_usable()
+        p2 = g.flatten(); uu2 = g.block_uuids(); x2 = g.current_values()
+        assert len(uu2) == len(uu) - 4 and cabi.FACTOR_MARGINAL in p2.groups
+        cov2 = g.covariance([(b, b) for b in range(len(uu2))])
+        for b in range(len(uu2)):
+            assert np.abs(x2[p2.offsets[b]:p2.offsets[b] + p2.block_size[b]] - full[uu2[b]]).max() < 1e-5
+            assert np.abs(cov2[b] - cov_full[uu2[b]]).max() < 1e-5
+        results.append({uu2[b]: x2[p2.offsets[b]:p2.offsets[b] + p2.block_size[b]].copy() for b in range(len(uu2))})
+    for u, v in results[0].items():
+        assert np.abs(v - results[1][u]).max() < 1e-6
