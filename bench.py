@@ -182,6 +182,36 @@ def smoother_cycles(host, opts, cycles=24):
             "iterations_median": float(np.median(its_n[k])), "observations": r.observations(), "cycles": cycles}
 
 
+def marginalization_cycles(host, opts, poses=40, cycles=12):
+    """The smoother's other branch (fixed_lag_smoother.cpp:269-272: fuse_constraints::marginalizeVariables) on a pose-graph
+    window (odometry + longer links, no landmarks): every cycle the oldest pose is marginalised for real -- its constraints
+    are linearised on the device (bsnls_linearize), eliminated on the host, a MarginalConstraint stays on its neighbours --
+    and optimize() runs on the changed graph."""
+    import ctypes as C
+    lib = host.load_library()
+
+    def pose(k):
+        out = []
+        for kind in (b"fuse_variables::Position3DStamped", b"fuse_variables::Orientation3DStamped"):
+            buf = C.create_string_buffer(16)
+            lib.bsfuse_uuid_stamped(kind, 10 + k, 0, buf)
+            out.append(buf.raw)
+        return out
+    g = host.HashGraph.pose_chain(poses, seed=2)
+    g.optimize(opts)
+    marg, opt, dev = [], [], []
+    for k in range(cycles):
+        t0 = time.perf_counter()
+        g.marginalize(pose(k))
+        t1 = time.perf_counter()
+        s, _ = g.optimize(opts)
+        t2 = time.perf_counter()
+        marg.append(t1 - t0); opt.append(t2 - t1); dev.append(s.device_time_in_seconds)
+    med = lambda v: 1e3 * float(np.median(v[2:]))
+    return {"pattern": f"pose graph of {poses} poses: the oldest pose truly marginalised per cycle (linearise on the device, QR on the host, MarginalConstraint), then optimize()",
+            "marginalize_wall_ms_median": med(marg), "optimize_wall_ms_median": med(opt), "solve_device_ms_median": med(dev), "cycles": cycles}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -387,6 +417,12 @@ def run_ours(args):
                                      "smoother_cycles": smoother_cycles(host, o1)}
             except Exception as e:
                 out["vio_window"] = {"error": str(e)}
+            try:
+                o3 = host.HashGraph.synthetic_options(3)
+                o3.device = local
+                out["marginalization"] = marginalization_cycles(host, o3)
+            except Exception as e:
+                out["marginalization"] = {"error": str(e)}
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
