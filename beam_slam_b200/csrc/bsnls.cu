@@ -170,7 +170,8 @@ struct bsnls_handle {
       d_gf_type, d_gf_nblk, d_gf_nres, d_gf_blocks, d_gf_coff, d_gf_consts, d_gf_loss_type, d_gf_loss_a, d_gf_joff,
       d_gf_roff, d_pair_a, d_pair_b, d_pair_ptr, d_item_i, d_item_j, d_fg_ptr, d_fg_fac, d_fg_lb, d_gd_row, d_gd_col,
       d_gd_ptr, d_gd_fac, d_gd_bi, d_gd_bj, d_is_pose, d_bsr_rowptr, d_bsr_col, d_diag_slot, d_pair_slot, d_gd_slot,
-      d_pcg_x, d_pcg_r, d_pcg_z, d_pcg_p, d_pcg_Ap, d_pcg_Minv, d_pcg_part;
+      d_pcg_x, d_pcg_r, d_pcg_z, d_pcg_p, d_pcg_Ap, d_pcg_Minv, d_pcg_part, d_pcgd_zsend, d_pcgd_zfull, d_pcgd_xsend, d_pcgd_scal, d_pcgd_state;
+  int pcgd_rb0 = 0, pcgd_rb1 = 0; int* pcgd_done_host = nullptr;   // sharded PCG: own block rows, pinned copy of the done flag
   DevMem d_lmz, d_gradL, d_colsqL, d_gradS, d_colsqS, d_zero;
   cudaEvent_t ev_stage = nullptr; bool stage_busy = false;
   DevMem d_x, d_xc, d_x0, d_Jrec, d_Vrec, d_minv, d_grad, d_colsq, d_scale, d_y, d_yf, d_rhs, d_S, d_poseH, d_gfJ,
@@ -496,7 +497,53 @@ void EnqueueDenseSolve(bsnls_handle* h, bool factor = true) {  // phase D2: Chol
   // sliding windows (n <= kRbMaxN): the whole matrix in registers, one CTA, factorisation and both substitutions
   LAUNCH(h, chol_reg_kernel, 1, kRbThreads, Sd, n, h->d_rhs.as<double>(), h->d_yf.as<double>(), st);
 }
+// K7 in the sharded solve: block rows of S partitioned over the ranks (kernels.cuh, pcgd_*). Not enqueue-only: the host
+// looks at the done flag every kPcgdPoll iterations (the flag is computed from all-reduced numbers, so every rank stops
+// at the same iteration and the collectives stay matched).
+int RunPartitionedPcg(bsnls_handle* h) {
+  constexpr int kPcgdPoll = 8;
+  const int n = h->P.nf_dim, rows = h->pcgd_rb1 - h->pcgd_rb0;
+  const int nblk_e = std::max(1, BlocksFor(std::max(rows, 1), 256)), nblk_w = std::max(1, BlocksFor(std::max(rows, 1), 8));
+  LMState* st = h->d_state.as<LMState>();
+  PcgDistBuf B{h->d_pcgd_xsend.as<double>(), h->d_pcg_r.as<double>(), h->d_pcg_p.as<double>(), h->d_pcg_Ap.as<double>(), h->d_pcg_Minv.as<double>(),
+               h->d_pcgd_zsend.as<double>(), h->d_pcgd_zfull.as<double>(), h->d_pcg_part.as<double>(), h->d_pcgd_scal.as<double>(),
+               h->d_pcgd_state.as<PcgDistState>(), h->pcgd_rb0, h->pcgd_rb1, nblk_e, h->opt.pcg_max_iterations, h->opt.pcg_tolerance};
+  const double* S = h->d_S.as<double>(); const double* rhs = h->d_rhs.as<double>();
+  CK(cudaMemsetAsync(h->d_pcgd_zsend.p, 0, sizeof(double) * (n + 3), h->stream));
+  CK(cudaMemsetAsync(h->d_pcgd_xsend.p, 0, sizeof(double) * n, h->stream));
+  LAUNCH(h, pcgd_init_kernel, nblk_e, 256, h->P, S, rhs, B, st);
+  LAUNCH(h, pcgd_sum_kernel, 1, 32, B.part, nblk_e, 3, B.zsend + n);
+  int rc = Nccl().AllReduce(B.zsend, B.zfull, (size_t)n + 3, kNcclFloat64, kNcclSum, h->comm, h->stream);
+  if (rc != kNcclSuccess) return h->fail(BSNLS_ERR_CUDA, "ncclAllReduce: %s", Nccl().GetErrorString(rc));
+  LAUNCH(h, pcgd_start_kernel, BlocksFor(n, 256), 256, n, B);
+  LAUNCH(h, pcgd_start_ctrl_kernel, 1, 1, n, B);
+  B.nblk = nblk_w;
+  PcgDistBuf Bu = B; Bu.nblk = nblk_e;
+  for (int it = 1; it <= h->opt.pcg_max_iterations; ++it) {
+    LAUNCH(h, pcgd_spmv_kernel, nblk_w, 256, h->P, S, B);
+    LAUNCH(h, pcgd_sum_kernel, 1, 32, B.part, nblk_w, 1, B.scal);
+    rc = Nccl().AllReduce(B.scal, B.scal, 1, kNcclFloat64, kNcclSum, h->comm, h->stream);
+    if (rc != kNcclSuccess) return h->fail(BSNLS_ERR_CUDA, "ncclAllReduce: %s", Nccl().GetErrorString(rc));
+    LAUNCH(h, pcgd_update_kernel, nblk_e, 256, Bu);
+    LAUNCH(h, pcgd_sum_kernel, 1, 32, B.part, nblk_e, 2, B.zsend + n);
+    rc = Nccl().AllReduce(B.zsend, B.zfull, (size_t)n + 2, kNcclFloat64, kNcclSum, h->comm, h->stream);
+    if (rc != kNcclSuccess) return h->fail(BSNLS_ERR_CUDA, "ncclAllReduce: %s", Nccl().GetErrorString(rc));
+    LAUNCH(h, pcgd_dir_kernel, BlocksFor(n, 256), 256, n, B);
+    LAUNCH(h, pcgd_ctrl_kernel, 1, 1, n, B);
+    if (it % kPcgdPoll == 0 || it == h->opt.pcg_max_iterations) {
+      CK(cudaMemcpyAsync(h->pcgd_done_host, &h->d_pcgd_state.as<PcgDistState>()->done, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+      CK(cudaStreamSynchronize(h->stream));
+      if (*h->pcgd_done_host) break;
+    }
+  }
+  // every rank needs the whole reduced step for its landmarks' back-substitution
+  rc = Nccl().AllReduce(B.x, h->d_yf.as<double>(), (size_t)n, kNcclFloat64, kNcclSum, h->comm, h->stream);
+  if (rc != kNcclSuccess) return h->fail(BSNLS_ERR_CUDA, "ncclAllReduce: %s", Nccl().GetErrorString(rc));
+  LAUNCH(h, pcgd_finish_kernel, 1, 1, B, st);
+  return BSNLS_OK;
+}
 int EnqueueSparseSolve(bsnls_handle* h) {  // phase D2 (K7): cooperative PCG, result in yf
+  if (h->world > 1 && std::getenv("BSNLS_PCG_REPLICATED") == nullptr) return RunPartitionedPcg(h);
   PcgBuffers B{h->d_yf.as<double>(), h->d_pcg_r.as<double>(), h->d_pcg_z.as<double>(), h->d_pcg_p.as<double>(), h->d_pcg_Ap.as<double>(),
                h->d_pcg_Minv.as<double>(), h->d_pcg_part.as<double>(), h->opt.pcg_max_iterations, h->opt.pcg_tolerance};
   DeviceProblem P = h->P; const double* S = h->d_S.as<double>(); const double* rhs = h->d_rhs.as<double>(); LMState* st = h->d_state.as<LMState>();
@@ -642,6 +689,7 @@ void bsnls_destroy(bsnls_handle* h) {
   if (h->graph_rp) cudaGraphExecDestroy(h->graph_rp);
   if (h->comm) Nccl().CommDestroy(h->comm);
   h->arena.Release();
+  if (h->pcgd_done_host) cudaFreeHost(h->pcgd_done_host);
   if (h->stream) cudaStreamDestroy(h->stream);
   if (h->side) cudaStreamDestroy(h->side);
   if (h->ev_stage) cudaEventDestroy(h->ev_stage);
@@ -1571,7 +1619,13 @@ int bsnls_set_problem(bsnls_handle* h, const bsnls_problem* pr) {
     h->pcg_grid = dev_sms * std::min(per_sm, 2);
     CK(h->d_pcg_x.alloc(sizeof(double) * nf_dim)); CK(h->d_pcg_r.alloc(sizeof(double) * nf_dim)); CK(h->d_pcg_z.alloc(sizeof(double) * nf_dim));
     CK(h->d_pcg_p.alloc(sizeof(double) * nf_dim)); CK(h->d_pcg_Ap.alloc(sizeof(double) * nf_dim)); CK(h->d_pcg_Minv.alloc(sizeof(double) * 9 * (size_t)h->nf));
-    CK(h->d_pcg_part.alloc(sizeof(double) * 5 * (size_t)h->pcg_grid));
+    CK(h->d_pcg_part.alloc(sizeof(double) * 5 * (size_t)std::max(h->pcg_grid, BlocksFor(h->nf, 8) + 1)));
+    if (h->world > 1) {   // block rows of S partitioned over the ranks, balanced by non-zero blocks
+      bsnls_shard_range(h->bsr_rowptr.data(), h->nf, h->rank, h->world, &h->pcgd_rb0, &h->pcgd_rb1);   // the rule of the landmark shards (tests/test_sharding_cpu.py)
+      CK(h->d_pcgd_zsend.alloc(sizeof(double) * (nf_dim + 3))); CK(h->d_pcgd_zfull.alloc(sizeof(double) * (nf_dim + 3))); CK(h->d_pcgd_xsend.alloc(sizeof(double) * nf_dim));
+      CK(h->d_pcgd_scal.alloc(sizeof(double) * 4)); CK(h->d_pcgd_state.alloc(sizeof(PcgDistState)));
+      if (!h->pcgd_done_host) CK(cudaMallocHost(&h->pcgd_done_host, sizeof(int)));
+    }
   } CK(h->d_poseH.alloc(sizeof(double) * 21 * (size_t)std::max(1, h->np)));
   CK(h->d_gfJ.alloc(sizeof(double) * joff)); CK(h->d_gfR.alloc(sizeof(double) * roff));
   CK(h->d_cost_part.alloc(sizeof(double) * (h->nb_eval + h->ngf + 1))); CK(h->d_cand_part.alloc(sizeof(double) * (h->nb_obs + h->ngf + 1)));

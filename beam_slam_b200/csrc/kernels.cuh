@@ -1440,6 +1440,129 @@ __global__ void __launch_bounds__(256) pcg_kernel(DeviceProblem P, const double*
   if (gtid == 0) { st->pcg_iters = it > B.max_iter ? B.max_iter : it; if (fail) st->lin_fail = 1; }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// K7, sharded solve: the same preconditioned conjugate gradients with the BLOCK ROWS of S partitioned over the ranks
+// (north star: "the PCG SpMV is partitioned by camera block"). Every rank holds the summed S (the exchange step), owns the
+// block rows [rb0, rb1) and keeps x, r, z only for them; the direction p is kept whole. Per CG iteration: SpMV on the own
+// rows + the own share of p.Ap, one scalar all-reduce; update of the own x, r, z, and one all-reduce that both assembles z
+// (every rank contributes its slice of a zero-padded vector) and sums r.r and r.z; p = z + beta p on every rank. The
+// host enqueues the iterations and looks at the (rank-identical) `done` flag every few of them. All sums are fixed-order
+// inside a rank; across ranks NCCL's order applies.
+struct PcgDistState { double rz, stop; int done, fail, iters; };
+struct PcgDistBuf { double* x; double* r; double* p; double* Ap; double* Minv; double* zsend; double* zfull; double* part; double* scal; PcgDistState* ps;
+                    int rb0, rb1, nblk; int max_iter; double tol; };
+// sums of per-CTA partials: dst[k] = sum_i part[k * nblk + i], k < nk, fixed order
+__global__ void __launch_bounds__(32) pcgd_sum_kernel(const double* __restrict__ part, int nblk, int nk, double* __restrict__ dst) {
+  if ((int)threadIdx.x < nk) { double acc = 0.0; for (int i = 0; i < nblk; ++i) acc += part[(size_t)threadIdx.x * nblk + i]; dst[threadIdx.x] = acc; }
+}
+// own rows: Minv, x = 0, r = b, z = Minv r (into the zero-padded send vector); partials of b.b, r.z and the count of bad blocks
+__global__ void __launch_bounds__(256) pcgd_init_kernel(DeviceProblem P, const double* __restrict__ S, const double* __restrict__ rhs, PcgDistBuf B, const LMState* st) {
+  __shared__ double sm[256];
+  const int br = B.rb0 + blockIdx.x * 256 + threadIdx.x;
+  double bb = 0.0, rz = 0.0, bad = 0.0;
+  if (br < B.rb1) {
+    const double* D = S + (size_t)P.diag_slot[br] * 9;
+    const double a = D[0], b = D[1], c = D[2], d = D[4], e = D[5], f = D[8];
+    const double A0 = d * f - e * e, A1 = c * e - b * f, A2 = b * e - c * d;
+    const double det = a * A0 + b * A1 + c * A2;
+    if (!(det > 0.0) || !(a > 0.0)) bad = 1.0;
+    const double id = 1.0 / det;
+    double* M = B.Minv + (size_t)br * 9;
+    M[0] = A0 * id; M[1] = A1 * id; M[2] = A2 * id; M[3] = A1 * id; M[4] = (a * f - c * c) * id; M[5] = (b * c - a * e) * id;
+    M[6] = A2 * id; M[7] = M[5]; M[8] = (a * d - b * b) * id;
+    const double r0 = rhs[3 * br], r1 = rhs[3 * br + 1], r2 = rhs[3 * br + 2];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const double z = M[3 * k] * r0 + M[3 * k + 1] * r1 + M[3 * k + 2] * r2, rk = k == 0 ? r0 : k == 1 ? r1 : r2;
+      B.x[3 * br + k] = 0.0; B.r[3 * br + k] = rk; B.zsend[3 * br + k] = z;
+      bb += rk * rk; rz += rk * z;
+    }
+  }
+  const double t0 = block_sum<256>(bb, sm); __syncthreads();
+  const double t1 = block_sum<256>(rz, sm); __syncthreads();
+  const double t2 = block_sum<256>(bad, sm);
+  if (threadIdx.x == 0) { B.part[blockIdx.x] = t0; B.part[B.nblk + blockIdx.x] = t1; B.part[2 * B.nblk + blockIdx.x] = t2; }
+  if (blockIdx.x == 0 && threadIdx.x == 0) { B.ps->done = (!gate_run(st) || st->lin_fail) ? 1 : 0; B.ps->fail = 0; B.ps->iters = 0; }
+}
+// every rank, whole vector: p = z; the scalars of the start
+__global__ void __launch_bounds__(256) pcgd_start_kernel(int n, PcgDistBuf B) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i < n) B.p[i] = B.zfull[i];
+}
+__global__ void pcgd_start_ctrl_kernel(int n, PcgDistBuf B) {
+  PcgDistState* ps = B.ps;
+  const double bb = B.zfull[n], rz = B.zfull[n + 1], bad = B.zfull[n + 2];
+  ps->rz = rz; ps->stop = B.tol * B.tol * bb;
+  if (bad > 0.0) { ps->fail = 1; ps->done = 1; }
+  if (!(bb > 0.0)) ps->done = 1;
+}
+// own rows: Ap = S p (warp per block row), per-CTA partial of p.Ap
+__global__ void __launch_bounds__(256) pcgd_spmv_kernel(DeviceProblem P, const double* __restrict__ S, PcgDistBuf B) {
+  __shared__ double sm[256];
+  double pAp = 0.0;
+  if (!B.ps->done) {
+    const int br = B.rb0 + blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (br < B.rb1) {
+      const int e0 = P.bsr_rowptr[br] * 9, e1 = P.bsr_rowptr[br + 1] * 9;
+      double y0 = 0.0, y1 = 0.0, y2 = 0.0;
+      for (int e = e0 + lane; e < e1; e += 32) {
+        const int blk = e / 9, w = e - 9 * blk, k = w / 3, c = w - 3 * k;
+        const double v = S[e] * B.p[3 * P.bsr_col[blk] + c];
+        if (k == 0) y0 += v; else if (k == 1) y1 += v; else y2 += v;
+      }
+#pragma unroll
+      for (int m = 1; m < 32; m <<= 1) { y0 += __shfl_xor_sync(0xffffffffu, y0, m); y1 += __shfl_xor_sync(0xffffffffu, y1, m); y2 += __shfl_xor_sync(0xffffffffu, y2, m); }
+      if (lane == 0) {
+        B.Ap[3 * br] = y0; B.Ap[3 * br + 1] = y1; B.Ap[3 * br + 2] = y2;
+        pAp = y0 * B.p[3 * br] + y1 * B.p[3 * br + 1] + y2 * B.p[3 * br + 2];
+      }
+    }
+  }
+  const double t = block_sum<256>(pAp, sm);
+  if (threadIdx.x == 0) B.part[blockIdx.x] = t;
+}
+// own rows: x += alpha p, r -= alpha Ap, z = Minv r; per-CTA partials of r.r and r.z. scal[0] = p.Ap summed over the ranks
+__global__ void __launch_bounds__(256) pcgd_update_kernel(PcgDistBuf B) {
+  __shared__ double sm[256];
+  const int br = B.rb0 + blockIdx.x * 256 + threadIdx.x;
+  double rr = 0.0, rz = 0.0;
+  const double pAp = B.scal[0];
+  if (!B.ps->done && pAp > 0.0 && br < B.rb1) {
+    const double alpha = B.ps->rz / pAp;
+    double r[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { B.x[3 * br + k] += alpha * B.p[3 * br + k]; r[k] = B.r[3 * br + k] - alpha * B.Ap[3 * br + k]; B.r[3 * br + k] = r[k]; rr += r[k] * r[k]; }
+    const double* M = B.Minv + (size_t)br * 9;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { const double z = M[3 * k] * r[0] + M[3 * k + 1] * r[1] + M[3 * k + 2] * r[2]; B.zsend[3 * br + k] = z; rz += r[k] * z; }
+  }
+  const double t0 = block_sum<256>(rr, sm); __syncthreads();
+  const double t1 = block_sum<256>(rz, sm);
+  if (threadIdx.x == 0) { B.part[blockIdx.x] = t0; B.part[B.nblk + blockIdx.x] = t1; }
+}
+// every rank, whole vector: p = z + beta p unless the iteration ended the solve
+__global__ void __launch_bounds__(256) pcgd_dir_kernel(int n, PcgDistBuf B) {
+  const double pAp = B.scal[0], rr = B.zfull[n], rzn = B.zfull[n + 1];
+  if (B.ps->done || !(pAp > 0.0) || rr <= B.ps->stop) return;
+  const double beta = rzn / B.ps->rz;
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i < n) B.p[i] = B.zfull[i] + beta * B.p[i];
+}
+__global__ void pcgd_ctrl_kernel(int n, PcgDistBuf B) {
+  PcgDistState* ps = B.ps;
+  if (ps->done) return;
+  const double pAp = B.scal[0], rr = B.zfull[n], rzn = B.zfull[n + 1];
+  ps->iters++;
+  if (!(pAp > 0.0)) { ps->fail = 1; ps->done = 1; }          // not positive definite
+  else if (rr <= ps->stop || ps->iters >= B.max_iter) ps->done = 1;
+  else ps->rz = rzn;
+}
+__global__ void pcgd_finish_kernel(PcgDistBuf B, LMState* st) {
+  if (!gate_run(st) || st->lin_fail) return;
+  st->pcg_iters = B.ps->iters;
+  if (B.ps->fail) st->lin_fail = 1;
+}
+
 // ===================================================================================================
 // K5c: back-substitution of the landmark steps and the model cost change
 //   y_e = Minv (g_e - sum E^T F y_f);  model_cost_change = sum_rows m (r - m/2), m = F y_f + E y_e  (delta = -y)
