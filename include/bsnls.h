@@ -141,7 +141,8 @@ typedef struct bsnls_problem {
    trust-region path consults. Defaults = Ceres defaults (bsnls_default_options). */
 enum { BSNLS_LINEAR_DENSE_SCHUR = 0, /* Schur + direct Cholesky of the reduced system: in registers up to 160 unknowns,
                                         tile-sparse level-scheduled DMMA Cholesky above (fails if the factor needs > 24 GB) */
-       BSNLS_LINEAR_ITERATIVE_SCHUR = 1, /* Schur + block-sparse PCG (block-Jacobi) */
+       BSNLS_LINEAR_ITERATIVE_SCHUR = 1, /* Schur + block-sparse PCG (block-Jacobi); in a sharded solve the block rows of the
+                                            reduced system are partitioned over the ranks (the same rule as bsnls_shard_range) */
        BSNLS_LINEAR_AUTO = 2 };          /* direct; block-sparse PCG only if the tile factor would not fit */
 typedef struct bsnls_options {
   int32_t max_num_iterations;            /* 50 */
