@@ -293,3 +293,21 @@ def test_successive_marginalisation_relinearises_the_marginal_prior():
         results.append({uu2[b]: x2[p2.offsets[b]:p2.offsets[b] + p2.block_size[b]].copy() for b in range(len(uu2))})
     for u, v in results[0].items():
         assert np.abs(v - results[1][u]).max() < 1e-6
+
+
+def test_snapshot_keeps_the_new_factor_types(tmp_path):
+    """The marginal prior (ten block slots, -1 padded), gravity alignment and the orientation prior survive
+    bsnls_problem_save / _load and the numpy reader bit for bit, and the oracle gives the same cost on the copy."""
+    p, _ = _problem()
+    b = ProblemBuilder()
+    iq = b.add_quaternion(_quat([0.9, 0.2, -0.3, 0.1]))
+    b.add_factor(cabi.FACTOR_GRAVITY_ALIGNMENT, [iq], [0.0, 0.0, -9.81, 1.0, 0.2, 0.0, 1.5])
+    b.add_factor(cabi.FACTOR_ABSOLUTE_ORIENTATION, [iq], np.concatenate([_quat([0.95, 0.1, -0.2, 0.05]), np.eye(3).ravel()]))
+    for k, prob in enumerate((p, b.build())):
+        path = tmp_path / f"p{k}.bsnls"
+        prob.save(path)
+        for q in (cabi.FlatProblem.load(path), cabi.FlatProblem.load_numpy(path)):
+            assert sorted(q.groups) == sorted(prob.groups)
+            for t in prob.groups:
+                assert np.array_equal(q.groups[t]["blocks"], prob.groups[t]["blocks"]) and np.array_equal(q.groups[t]["consts"], prob.groups[t]["consts"])
+            assert orc.evaluate(q)[0] == orc.evaluate(prob)[0]
