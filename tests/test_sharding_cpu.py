@@ -79,3 +79,54 @@ def test_shard_range_edge_cases():
     # more ranks than landmarks: empty shards are allowed, still a partition
     parts = [sharding.shard_range(lm_ptr, r, 8) for r in range(8)]
     assert parts[0][0] == 0 and parts[-1][1] == 4 and all(a[1] == b[0] and a[0] <= a[1] for a, b in zip(parts, parts[1:]))
+
+
+def _pcg_worker(rank, world, port, out):
+    """The sharded solve's conjugate gradients (csrc/bsnls.cu RunPartitionedPcg) restated with numpy + gloo: block rows of S
+    by bsnls_shard_range on the non-zero-block prefix, own x / r / z, whole p, one scalar all-reduce and one all-reduce of
+    the zero-padded z slice with the two dot products per iteration."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    p = host.HashGraph.synthetic(3, scale=0.05).flatten()
+    S, b = orc.reduced_system(p, 1e4)
+    n = len(b); nf = n // 3
+    blk = np.abs(S.reshape(nf, 3, nf, 3)).max(axis=(1, 3)) > 0
+    rowptr = np.concatenate([[0], np.cumsum(blk.sum(1))]).astype(np.int32)
+    rb0, rb1 = sharding.shard_range(rowptr, rank, world)
+    lo, hi = 3 * rb0, 3 * rb1
+    Minv = [np.linalg.inv(S[3 * i:3 * i + 3, 3 * i:3 * i + 3]) for i in range(nf)]
+    prec = lambda r, i0, i1: np.concatenate([Minv[i] @ r[3 * (i - i0):3 * (i - i0) + 3] for i in range(i0, i1)]) if i1 > i0 else np.zeros(0)
+    x = np.zeros(hi - lo); r = b[lo:hi].copy(); z = prec(r, rb0, rb1)
+    send = np.zeros(n + 2); send[lo:hi] = z; send[n] = r @ r; send[n + 1] = r @ z
+    t = torch.from_numpy(send.copy()); dist.all_reduce(t); full = t.numpy()
+    pvec = full[:n].copy(); bb, rz = full[n], full[n + 1]
+    iters = 0
+    for iters in range(1, 501):
+        Ap = S[lo:hi] @ pvec
+        t = torch.tensor([float(Ap @ pvec[lo:hi])], dtype=torch.float64); dist.all_reduce(t); pAp = float(t[0])
+        alpha = rz / pAp
+        x += alpha * pvec[lo:hi]; r -= alpha * Ap; z = prec(r, rb0, rb1)
+        send = np.zeros(n + 2); send[lo:hi] = z; send[n] = r @ r; send[n + 1] = r @ z
+        t = torch.from_numpy(send.copy()); dist.all_reduce(t); full = t.numpy()
+        if full[n] <= 1e-26 * bb:
+            break
+        pvec = full[:n] + (full[n + 1] / rz) * pvec; rz = full[n + 1]
+    xs = np.zeros(n); xs[lo:hi] = x
+    t = torch.from_numpy(xs); dist.all_reduce(t)
+    ranges = [None] * world
+    dist.all_gather_object(ranges, (rb0, rb1))
+    if rank == 0:
+        out["err"] = float(np.abs(t.numpy() - np.linalg.solve(S, b)).max() / np.abs(np.linalg.solve(S, b)).max())
+        out["iters"] = iters
+        out["ranges"] = ranges
+        out["nf"] = nf
+    dist.destroy_process_group()
+
+
+def test_two_rank_partitioned_conjugate_gradients():
+    world = 2
+    out = mp.Manager().dict()
+    mp.spawn(_pcg_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    (a0, a1), (b0, b1) = out["ranges"]
+    assert a0 == 0 and a1 == b0 and b1 == out["nf"] and a1 > a0 and b1 > b0     # the block rows are partitioned
+    assert out["err"] < 1e-9 and out["iters"] < 500
