@@ -1,7 +1,14 @@
 #include "flatten.h"
 
 #include <algorithm>
+#include <array>
+#include <functional>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <exception>
+#include <mutex>
 #include <thread>
 
 namespace bsfuse {
@@ -58,9 +65,9 @@ namespace {
 #ifndef BSFUSE_COPY_THREADS
 #define BSFUSE_COPY_THREADS 8
 #endif
-template <typename F> void ForBlocks(size_t n, const F& body) {
-  constexpr size_t kGrain = 16384, kMaxThreads = BSFUSE_COPY_THREADS;
-  const size_t nt = std::min<size_t>(std::min<size_t>(kMaxThreads, std::max(1u, std::thread::hardware_concurrency())), n / kGrain);
+template <typename F> void ForBlocks(size_t n, const F& body, size_t grain = 16384) {
+  constexpr size_t kMaxThreads = BSFUSE_COPY_THREADS;
+  const size_t nt = std::min<size_t>(std::min<size_t>(kMaxThreads, std::max(1u, std::thread::hardware_concurrency())), n / grain);
   if (nt <= 1) { body(0, n); return; }
   std::vector<std::thread> pool;
   for (size_t t = 1; t < nt; ++t) pool.emplace_back([&, t] { body(n * t / nt, n * (t + 1) / nt); });
@@ -82,33 +89,26 @@ void FlatProblem::GatherValues() {
 }
 
 namespace {
-// first sight of a constraint in this graph: type() string dispatch, variable objects, camera class
-void ResolveHint(const HashGraph& graph, const Constraint& c, FlatProblem& P) {
-  auto ti = TypeTable().find(c.type());
-  if (ti == TypeTable().end()) throw std::invalid_argument("constraint type not supported by the GPU path: " + c.type());
-  const TypeInfo& info = ti->second;
+// First sight of a constraint in this graph, part 1 (thread-safe: reads the graph, writes only the constraint's own hint):
+// type() string dispatch and the variable objects. `last` caches the previous constraint's type entry (graphs hold long
+// runs of one type).
+void ResolveHintTypeAndVariables(const HashGraph& graph, const Constraint& c, const std::pair<const std::string, TypeInfo>** last) {
+  if (!*last || (*last)->first != c.type()) {
+    auto ti = TypeTable().find(c.type());
+    if (ti == TypeTable().end()) throw std::invalid_argument("constraint type not supported by the GPU path: " + c.type());
+    *last = &*ti;
+  }
+  const TypeInfo& info = (*last)->second;
   const int nvar = static_cast<int>(c.variables().size());
   if (info.type == BSNLS_FACTOR_MARGINAL ? (nvar < 1 || nvar > info.nblocks) : nvar != info.nblocks) throw std::invalid_argument("unexpected variable count for " + c.type());
   Constraint::FlatHint& hnt = c.flat_hint;
   hnt.type = info.type; hnt.nblocks = nvar; hnt.slots = info.nblocks; hnt.nres = info.nres; hnt.stride = info.stride; hnt.camera = -1;
   for (int b = 0; b < nvar; ++b) hnt.vars[b] = &graph.getVariable(c.variables()[b]);  // variables_.at(uuid), :515
-  if (info.type == BSNLS_FACTOR_REPROJECTION) {
-    const auto& pl = c.payload();
-    std::vector<double> cam(pl.begin() + 2, pl.begin() + 19);  // K(4), T(12), w
-    cam.push_back(c.loss() ? static_cast<double>(c.loss()->type) : static_cast<double>(BSNLS_LOSS_NONE));
-    cam.push_back(c.loss() ? c.loss()->a : 0.0); cam.push_back(0.0);
-    auto it = P.camera_index.find(cam);
-    if (it == P.camera_index.end()) {
-      it = P.camera_index.emplace(cam, static_cast<int32_t>(P.cameras.size() / BSNLS_CAMERA_STRIDE)).first;
-      P.cameras.insert(P.cameras.end(), cam.begin(), cam.end());
-    }
-    hnt.camera = it->second;
-  }
-  hnt.owner = &P;   // variable objects belong to the graph, the camera index to this FlatProblem's table: one FlatProblem serves one graph
 }
 }  // namespace
 
 void Flatten(const HashGraph& graph, FlatProblem* out) {
+  const auto T0 = std::chrono::steady_clock::now(); auto lap = [&](const char* n) { if (std::getenv("BSFUSE_DEBUG")) std::fprintf(stderr, "[bsfuse] flatten %-20s %8.3f ms\n", n, 1e3 * std::chrono::duration<double>(std::chrono::steady_clock::now() - T0).count()); };
   FlatProblem& P = *out;
   const auto& vars = graph.getVariables();
   P.block_size.clear(); P.block_manifold.clear(); P.block_group.clear(); P.block_constant.clear(); P.block_values.clear();
@@ -135,33 +135,109 @@ void Flatten(const HashGraph& graph, FlatProblem* out) {
     for (size_t i = 0; i < v.size(); ++i) P.block_values.push_back(v.data()[i]);
     off += static_cast<int64_t>(v.size());
   }
+  lap("variables");
   if (P.groups.size() != BSNLS_NUM_FACTOR_TYPES) P.groups.assign(BSNLS_NUM_FACTOR_TYPES, FlatProblem::Group());
   for (int t = 0; t < BSNLS_NUM_FACTOR_TYPES; ++t) {
     FlatProblem::Group& g = P.groups[t];
     g.type = t; g.blocks.clear(); g.aux.clear(); g.loss_type.clear(); g.res_index.clear(); g.consts.clear(); g.loss_param.clear();
   }
-  int32_t res_index = 0;
-  // createProblem, second loop (hash_graph.cpp:506-521)
-  for (const auto& kv : graph.getConstraints()) {
-    const Constraint& c = *kv.second;
-    if (c.flat_hint.owner != &P) ResolveHint(graph, c, P);
-    const Constraint::FlatHint& hnt = c.flat_hint;
-    FlatProblem::Group& g = P.groups[hnt.type];
-    for (int b = 0; b < hnt.slots; ++b) g.blocks.push_back(b < hnt.nblocks ? hnt.vars[b]->flat_index : -1);
+  // createProblem, second loop (hash_graph.cpp:506-521). One sequential walk over the container fixes the order (residual
+  // block i = the i-th constraint of the walk); everything per constraint -- the hash lookups of its variables the first
+  // time it is seen, and writing its row of the SoA groups -- then runs on chunks of that list in parallel, each chunk
+  // at offsets known from a per-type count, so the result does not depend on the thread count.
+  std::vector<const Constraint*> all; all.reserve(graph.getConstraints().size());
+  for (const auto& kv : graph.getConstraints()) all.push_back(kv.second.get());
+  lap("constraint walk");
+  const size_t nc = all.size();
+  constexpr size_t kChunk = 16384;
+  const size_t nchunks = std::max<size_t>(1, (nc + kChunk - 1) / kChunk);
+  std::exception_ptr err; std::mutex err_mutex;
+  auto guarded = [&](const std::function<void(size_t)>& body) {     // body(chunk) on every chunk; the first exception is re-thrown
+    ForBlocks(nchunks, [&](size_t c0, size_t c1) {
+      try { for (size_t ch = c0; ch < c1; ++ch) body(ch); }
+      catch (...) { std::lock_guard<std::mutex> lock(err_mutex); if (!err) err = std::current_exception(); }
+    }, 1);
+    if (err) std::rethrow_exception(err);
+  };
+  // (1) constraints not seen before: type dispatch + variable objects; the camera classes each chunk meets, in order
+  std::vector<std::vector<std::array<double, BSNLS_CAMERA_STRIDE>>> chunk_cams(nchunks);
+  auto camera_key = [](const Constraint& c, double* key) {
     const auto& pl = c.payload();
-    if (hnt.type == BSNLS_FACTOR_REPROJECTION) {
-      g.consts.push_back(pl[0]); g.consts.push_back(pl[1]);
-      g.aux.push_back(hnt.camera);
-    } else {
-      const size_t n0 = g.consts.size();
-      g.consts.resize(n0 + hnt.stride, 0.0);
-      std::memcpy(g.consts.data() + n0, pl.data(), sizeof(double) * std::min<size_t>(pl.size(), hnt.stride));
-      g.loss_type.push_back(c.loss() ? static_cast<int>(c.loss()->type) : BSNLS_LOSS_NONE);
-      g.loss_param.push_back(c.loss() ? c.loss()->a : 0.0);
+    std::memcpy(key, pl.data() + 2, sizeof(double) * 17);  // K(4), T(12), w
+    key[17] = c.loss() ? static_cast<double>(c.loss()->type) : static_cast<double>(BSNLS_LOSS_NONE);
+    key[18] = c.loss() ? c.loss()->a : 0.0; key[19] = 0.0;
+  };
+  guarded([&](size_t ch) {
+    const std::pair<const std::string, TypeInfo>* last = nullptr;
+    std::array<double, BSNLS_CAMERA_STRIDE> key, prev; bool have_prev = false;
+    for (size_t i = ch * kChunk; i < std::min(nc, (ch + 1) * kChunk); ++i) {
+      const Constraint& c = *all[i];
+      if (c.flat_hint.owner == &P) continue;
+      ResolveHintTypeAndVariables(graph, c, &last);
+      if (c.flat_hint.type != BSNLS_FACTOR_REPROJECTION) continue;
+      camera_key(c, key.data());
+      if (have_prev && key == prev) continue;
+      prev = key; have_prev = true;
+      auto& seen = chunk_cams[ch];
+      if (std::find(seen.begin(), seen.end(), key) == seen.end()) seen.push_back(key);
     }
-    c.flat_hint.res_index = res_index;
-    g.res_index.push_back(res_index++);
+  });
+  for (size_t ch = 0; ch < nchunks; ++ch)            // camera table in order of first appearance along the walk
+    for (const auto& key : chunk_cams[ch]) {
+      std::vector<double> cam(key.begin(), key.end());
+      if (P.camera_index.find(cam) == P.camera_index.end()) {
+        P.camera_index.emplace(cam, static_cast<int32_t>(P.cameras.size() / BSNLS_CAMERA_STRIDE));
+        P.cameras.insert(P.cameras.end(), cam.begin(), cam.end());
+      }
+    }
+  lap("new constraints");
+  // (2) per-type counts of every chunk -> where each chunk writes
+  std::vector<std::array<int64_t, BSNLS_NUM_FACTOR_TYPES>> count(nchunks + 1);
+  guarded([&](size_t ch) {
+    count[ch + 1].fill(0);
+    for (size_t i = ch * kChunk; i < std::min(nc, (ch + 1) * kChunk); ++i) count[ch + 1][all[i]->flat_hint.type]++;
+  });
+  count[0].fill(0);
+  for (size_t ch = 0; ch < nchunks; ++ch) for (int t = 0; t < BSNLS_NUM_FACTOR_TYPES; ++t) count[ch + 1][t] += count[ch][t];
+  static const int kSlots[BSNLS_NUM_FACTOR_TYPES] = {3, 10, 5, 4, 6, 2, 2, 1, 2, BSNLS_MARGINAL_MAX_BLOCKS, 1, 1};
+  static const int kStrides[BSNLS_NUM_FACTOR_TYPES] = {BSNLS_REPROJECTION_STRIDE, BSNLS_IMU_DELTA_STRIDE, BSNLS_IMU_PRIOR_STRIDE, BSNLS_POSE_STRIDE, BSNLS_POSE_STRIDE,
+      BSNLS_POSE_STRIDE, BSNLS_ORIENTATION_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_VEC3_STRIDE, BSNLS_MARGINAL_STRIDE, BSNLS_GRAVITY_STRIDE, BSNLS_ORIENTATION_STRIDE};
+  for (int t = 0; t < BSNLS_NUM_FACTOR_TYPES; ++t) {
+    FlatProblem::Group& g = P.groups[t];
+    const size_t n = static_cast<size_t>(count[nchunks][t]);
+    g.blocks.assign(n * kSlots[t], -1); g.res_index.assign(n, 0); g.consts.assign(n * kStrides[t], 0.0);
+    if (t == BSNLS_FACTOR_REPROJECTION) g.aux.assign(n, 0); else { g.loss_type.assign(n, BSNLS_LOSS_NONE); g.loss_param.assign(n, 0.0); }
   }
+  // (3) the rows
+  guarded([&](size_t ch) {
+    std::array<int64_t, BSNLS_NUM_FACTOR_TYPES> at = count[ch];
+    std::array<double, BSNLS_CAMERA_STRIDE> key, prev; int32_t prev_cam = -1;
+    for (size_t i = ch * kChunk; i < std::min(nc, (ch + 1) * kChunk); ++i) {
+      const Constraint& c = *all[i];
+      Constraint::FlatHint& hnt = c.flat_hint;
+      FlatProblem::Group& g = P.groups[hnt.type];
+      const size_t k = static_cast<size_t>(at[hnt.type]++);
+      for (int b = 0; b < hnt.nblocks; ++b) g.blocks[k * hnt.slots + b] = hnt.vars[b]->flat_index;
+      const auto& pl = c.payload();
+      if (hnt.type == BSNLS_FACTOR_REPROJECTION) {
+        g.consts[2 * k] = pl[0]; g.consts[2 * k + 1] = pl[1];
+        if (hnt.owner != &P) {                       // camera class: the table is complete, lookups only
+          camera_key(c, key.data());
+          if (prev_cam < 0 || !(key == prev)) { prev_cam = P.camera_index.at(std::vector<double>(key.begin(), key.end())); prev = key; }
+          hnt.camera = prev_cam;
+        }
+        g.aux[k] = hnt.camera;
+      } else {
+        std::memcpy(g.consts.data() + k * hnt.stride, pl.data(), sizeof(double) * std::min<size_t>(pl.size(), hnt.stride));
+        g.loss_type[k] = c.loss() ? static_cast<int>(c.loss()->type) : BSNLS_LOSS_NONE;
+        g.loss_param[k] = c.loss() ? c.loss()->a : 0.0;
+      }
+      hnt.owner = &P;   // variable objects belong to the graph, the camera index to this FlatProblem's table: one FlatProblem serves one graph
+      hnt.res_index = static_cast<int32_t>(i);
+      g.res_index[k] = static_cast<int32_t>(i);
+    }
+  });
+  lap("constraints");
   P.Finalize();
 }
 
