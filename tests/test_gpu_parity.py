@@ -250,6 +250,23 @@ def test_loop_closure_graph_on_the_tile_path_matches_oracle():
     assert _rel(s.get_values(), xo) < 1e-7
 
 
+@pytest.mark.parametrize("lanes", [4, 32])
+def test_landmark_kernel_lane_counts(lanes, monkeypatch):
+    """Four lanes per landmark on config 2 (tracks of up to 20 observations: the lanes' fourth and later observations take
+    the kernel's remainder path, outside the warp-cooperative record moves) and 32 lanes: same solve as the oracle's."""
+    monkeypatch.setenv("BSNLS_LM_LANES", str(lanes))
+    g = host.HashGraph.synthetic(2)
+    p, opts = g.flatten(), host.HashGraph.synthetic_options(2)
+    s = Solver(opts)
+    s.set_problem(p)
+    summ, its = s.solve()
+    so, ito, xo = orc.solve(p, opts)
+    assert len(its) == len(ito)
+    for a, b in zip(its, ito):
+        assert abs(a.cost - b.cost) <= 1e-9 * abs(b.cost)
+    assert _rel(s.get_values(), xo) < 1e-7
+
+
 @pytest.mark.parametrize("order", ["graph", "band"])
 def test_both_orderings_of_the_reduced_system_give_the_oracle_solve(order, monkeypatch):
     """The two candidate orders of the f-blocks (nested dissection of the block graph with tile padding; reverse
